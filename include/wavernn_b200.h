@@ -1,0 +1,156 @@
+/* wavernn_b200.h — C ABI of the B200-native WaveRNN generation path.
+ *
+ * The reference (qingyundou/WaveRNN) is pure Python and has no FFI; the boundary it exposes for
+ * this path is the method `WaveRNN.generate(mels, save_path, batched, target, overlap, mu_law)`
+ * (models/fatchord_version.py:169) and `deepmind_version.WaveRNN.generate(seq_len)`
+ * (models/deepmind_version.py:75).  This header is what a Python-side binding of that method
+ * calls (wavernn_b200/binding.py; INTEGRATION.md shows the stub a reference maintainer adds).
+ *
+ * Conventions: plain pointers and sizes, no torch types.  Every function returns 0 on success
+ * or a negative wrnn_status; the message is available from wrnn_last_error().  No C++ exception
+ * crosses the ABI.  Unless a parameter says "device", pointers are HOST pointers owned by the
+ * caller; the library owns packed weights and workspaces.  One handle per GPU; a handle is not
+ * thread-safe; distinct handles may be driven from distinct host threads (the multi-GPU model:
+ * no collective on the path).  There is NO CPU fallback: without a CUDA device every compute
+ * entry point fails with WRNN_ERR_CUDA.
+ */
+#ifndef WAVERNN_B200_H
+#define WAVERNN_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+    WRNN_OK = 0,
+    WRNN_ERR_ARG = -1,      /* bad argument / shape (Python side raises ValueError)          */
+    WRNN_ERR_STATE = -2,    /* weights not loaded, wrong mode ... (RuntimeError)               */
+    WRNN_ERR_CUDA = -3,     /* CUDA runtime error, no device, kernel fault (RuntimeError)      */
+    WRNN_ERR_NOMEM = -4
+} wrnn_status;
+
+enum { WRNN_MODE_RAW = 0, WRNN_MODE_MOL = 1 };
+
+/* Constructor arguments of the reference model (fatchord_version.py:93-95). */
+typedef struct {
+    int32_t rnn_dims, fc_dims, bits, pad;
+    int32_t n_upsample;             /* number of entries used in upsample_factors (<= 8)   */
+    int32_t upsample_factors[8];
+    int32_t feat_dims, compute_dims, res_out_dims, res_blocks;
+    int32_t hop_length, sample_rate;
+    int32_t mode;                   /* WRNN_MODE_RAW / WRNN_MODE_MOL                        */
+} wrnn_config;
+
+/* One named checkpoint tensor, state_dict key and layout unchanged (fatchord_version.py:114-125,
+ * loaded like `load()` at :414-417).  dtype: 0 = float32, 1 = int64.  Borrowed, copied inside. */
+typedef struct {
+    const char *name;
+    const void *data;
+    int32_t dtype;
+    int32_t ndim;
+    int64_t shape[4];
+} wrnn_tensor;
+
+/* Pre-drawn noise for parity runs, in the reference's draw order (utils/distribution.py:106,118;
+ * Categorical.sample == argmax(p / Exp(1))).  steps x folds is the loop extent of the call.
+ *   MOL: u1 [steps][folds][10], u2 [steps][folds]      (uniform in [1e-5, 1-1e-5])
+ *   RAW: q  [steps][folds][n_classes]                    (Exp(1))
+ * NULL noise => in-kernel Philox keyed (seed, fold, step). */
+typedef struct {
+    const float *u1;
+    const float *u2;
+    const float *q;
+    int64_t steps;
+    int64_t folds;
+} wrnn_noise;
+
+typedef struct wrnn_handle wrnn_handle;
+
+/* ------------------------------------------------------------------ lifetime */
+int wrnn_create(const wrnn_config *cfg, int device, wrnn_handle **out);
+void wrnn_destroy(wrnn_handle *h);
+const char *wrnn_last_error(const wrnn_handle *h);          /* h may be NULL: create() errors */
+/* Replaces `model.load()` / the aliasing in get_gru_cell (fatchord_version.py:273-279,414-417):
+ * copies and packs the checkpoint for the kernels.  Unknown keys are ignored (strict=False);
+ * every key the path needs must be present by the time generate is called. */
+int wrnn_load_weights(wrnn_handle *h, const wrnn_tensor *tensors, int32_t n);
+/* 16x1 block pruning of the four GRU matrices: per gate, keep the
+ * `keep_fraction` of 16-row x 1-column blocks with largest L1 norm, zero the rest, and switch the
+ * loop kernel to the block-sparse mat-vec.  `masked_out` (optional, host) receives the four masked
+ * dense matrices concatenated in the order rnn1.ih, rnn1.hh, rnn2.ih, rnn2.hh. */
+int wrnn_prune_16x1(wrnn_handle *h, float keep_fraction, float *masked_out);
+
+/* ------------------------------------------------------------------ the path
+ * wrnn_generate == WaveRNN.generate for `n_utt` independent utterances (the reference takes one;
+ * fatchord_version.py:169-264).  mels[u] is (feat_dims, T[u]) row-major float32.  out[u] must hold
+ * (T[u]-1)*hop_length float64; out_len[u] receives that length.  Host buffers; the H2D/D2H
+ * copies are part of the call.  `cuda_stream` is a cudaStream_t (NULL = default stream); the call
+ * returns after the result is on the host.  Folds of all utterances run as one fold batch. */
+int wrnn_generate(wrnn_handle *h, const float *const *mels, const int32_t *T, int32_t n_utt,
+                  int32_t batched, int32_t target, int32_t overlap, int32_t mu_law,
+                  const wrnn_noise *noise, uint64_t seed,
+                  double *const *out, int64_t *out_len, void *cuda_stream);
+
+/* Same work split in three so a benchmark can time the device part with inputs resident in HBM:
+ * stage (H2D of mels) -> run (all kernels, asynchronous on the stream) -> fetch (D2H of waves). */
+int wrnn_stage(wrnn_handle *h, const float *const *mels, const int32_t *T, int32_t n_utt,
+               int32_t batched, int32_t target, int32_t overlap, int32_t mu_law,
+               const wrnn_noise *noise, void *cuda_stream);
+int wrnn_run_staged(wrnn_handle *h, uint64_t seed, void *cuda_stream);
+int wrnn_fetch(wrnn_handle *h, double *const *out, int64_t *out_len, void *cuda_stream);
+/* Device time of the last run's phases in ms (CUDA events on the launch stream): conditioning
+ * (+fold), per-sample loop, output tail; plus loop extent.  Valid after the stream is idle. */
+int wrnn_last_timing(wrnn_handle *h, float *ms_cond, float *ms_loop, float *ms_tail,
+                     int64_t *steps, int64_t *folds, int64_t *kernel_launches);
+/* Raw per-fold samples of the last run: (folds, steps) float32 (RAW mode: 2k/(C-1)-1). */
+int wrnn_fetch_samples(wrnn_handle *h, float *samples, void *cuda_stream);
+
+/* ------------------------------------------------------------------ components (parity tests) */
+/* UpsampleNetwork.forward on the zero-padded mel (fatchord_version.py:82-89,185-186).
+ * mel (feat_dims, T) -> mels_out (T*hop, feat_dims), aux_out (T*hop, res_out_dims), time-major. */
+int wrnn_upsample(wrnn_handle *h, const float *mel, int32_t T, float *mels_out, float *aux_out);
+/* fold_with_overlap (fatchord_version.py:293-340): x (L, F) -> out (folds, target+2*overlap, F).
+ * wrnn_num_folds gives the fold count for sizing `out`. */
+int64_t wrnn_num_folds(int64_t total_len, int64_t target, int64_t overlap);
+int wrnn_fold(wrnn_handle *h, const float *x, int64_t L, int32_t F, int64_t target, int64_t overlap,
+              float *out);
+/* xfade_and_unfold (fatchord_version.py:342-405): y (folds, target+2*overlap) float64 ->
+ * out (folds*(target+overlap)+overlap) float64. */
+int wrnn_unfold(wrnn_handle *h, const double *y, int64_t folds, int64_t target, int64_t overlap,
+                double *out);
+/* decode_mu_law(y, mu, from_labels=False) (utils/dsp.py:98-103) for samples y = 2k/(mu-1)-1 given
+ * as float32; out float64.  wrnn_mulaw_lut (host only, no GPU) fills the mu-entry table. */
+int wrnn_decode_mu_law(wrnn_handle *h, const float *y, int64_t n, int32_t mu, double *out);
+int wrnn_mulaw_lut(int32_t mu, double *lut);
+/* Host tables of the cross-fade / fade-out gains (numpy linspace semantics), host only. */
+int wrnn_xfade_tables(int64_t overlap, double *fade_in, double *fade_out);
+/* Teacher-forced logits == WaveRNN.forward (fatchord_version.py:131-167): x (n_seq, S) previous
+ * samples, mels (n_seq, feat_dims, S/hop + 2*pad) ALREADY padded -> logits (n_seq, S, n_classes). */
+int wrnn_forward_logits(wrnn_handle *h, const float *x, const float *mels, int32_t n_seq, int64_t S,
+                        float *logits);
+/* Which loop kernel the next run will use, for reports: "fma", "mma", "sparse". */
+const char *wrnn_loop_kernel_name(wrnn_handle *h, int64_t folds);
+/* Force a loop kernel: 0 = auto (mma when folds >= 16 and dims are the default ones), 1 = fma. */
+int wrnn_set_loop_kernel(wrnn_handle *h, int32_t which);
+
+/* ------------------------------------------------------------------ deepmind variant */
+typedef struct wrnn_dm_handle wrnn_dm_handle;
+int wrnn_dm_create(int32_t hidden_size, int32_t quantisation, int device, wrnn_dm_handle **out);
+void wrnn_dm_destroy(wrnn_dm_handle *h);
+const char *wrnn_dm_last_error(const wrnn_dm_handle *h);
+int wrnn_dm_load_weights(wrnn_dm_handle *h, const wrnn_tensor *tensors, int32_t n);
+/* deepmind_version.WaveRNN.generate (models/deepmind_version.py:75-165) for n_seq independent
+ * sequences (the reference runs one).  q_coarse/q_fine: optional Exp(1) noise
+ * [seq_len][n_seq][quantisation]; NULL => Philox(seed).  Outputs int64 (n_seq, seq_len):
+ * output = coarse*256 + fine - 32768 (utils/dsp.py:33-34). */
+int wrnn_dm_generate(wrnn_dm_handle *h, int64_t seq_len, int32_t n_seq, const float *q_coarse,
+                     const float *q_fine, uint64_t seed, int64_t *output, int64_t *coarse,
+                     int64_t *fine, void *cuda_stream);
+int wrnn_dm_last_timing(wrnn_dm_handle *h, float *ms_loop, int64_t *kernel_launches);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* WAVERNN_B200_H */

@@ -1,0 +1,132 @@
+"""Import the real reference (build container only) to pin the oracle.  TEST INFRASTRUCTURE.
+
+`/root/reference` is read-only and exists only in the build container; nothing on the GPU
+path may call this.  The shims are the ones listed in SURVEY.md F4/F6 and touch no arithmetic:
+  * stub `matplotlib` / `librosa` modules (`utils/display.py:1-3`, `utils/dsp.py:3`);
+  * `np.cumproduct = np.cumprod` (`models/fatchord_version.py:68`; removed in NumPy 2);
+  * `hp.configure(<reference>/hparams.py)`;
+  * `fatchord_version.save_wav` -> no-op (librosa.output.write_wav no longer exists);
+  * `deepmind_version.stream` -> accepts the 2-argument call at `deepmind_version.py:159`.
+"""
+import os
+import sys
+import types
+
+REF_ROOT = os.environ.get('WAVERNN_REFERENCE', '/root/reference')
+
+
+def available() -> bool:
+    return os.path.isfile(os.path.join(REF_ROOT, 'models', 'fatchord_version.py'))
+
+
+_loaded = None
+
+
+def load():
+    """-> (fatchord_version module, deepmind_version module, distribution module, dsp module)."""
+    global _loaded
+    if _loaded is not None:
+        return _loaded
+    if not available():
+        raise RuntimeError('reference tree not present (expected in the build container only)')
+    import numpy as np
+    if not hasattr(np, 'cumproduct'):
+        np.cumproduct = np.cumprod
+    for name in ('matplotlib', 'matplotlib.pyplot', 'librosa'):
+        if name not in sys.modules:
+            m = types.ModuleType(name)
+            m.use = lambda *a, **k: None
+            sys.modules[name] = m
+    sys.modules['matplotlib'].pyplot = sys.modules['matplotlib.pyplot']
+    clash = [k for k in sys.modules if k == 'utils' or k.startswith('utils.') or k == 'models'
+             or k.startswith('models.')]
+    if clash:
+        raise RuntimeError(f'module name clash with the reference tree: {clash}')
+    sys.path.insert(0, REF_ROOT)
+    try:
+        from utils import hparams as hp
+        if not hp.is_configured():
+            hp.configure(os.path.join(REF_ROOT, 'hparams.py'))
+        import models.fatchord_version as fv
+        import models.deepmind_version as dv
+        import utils.distribution as dist
+        import utils.dsp as dsp
+    finally:
+        sys.path.remove(REF_ROOT)
+    fv.save_wav = lambda x, path: None
+    dv.stream = lambda *a, **k: None
+    fv.stream = lambda *a, **k: None
+    _loaded = (fv, dv, dist, dsp)
+    return _loaded
+
+
+def build_fatchord(dims, state_dict_np):
+    """Reference `WaveRNN(**dims)` on CPU with the given checkpoint loaded (strict)."""
+    import contextlib
+    import io
+    import torch
+    fv, _, _, _ = load()
+    with contextlib.redirect_stdout(io.StringIO()):
+        model = fv.WaveRNN(**dims.ctor_kwargs())
+    sd = {k: torch.from_numpy(v.copy()) for k, v in state_dict_np.items()}
+    model.load_state_dict(sd, strict=True)
+    return model
+
+
+def build_deepmind(state_dict_np, hidden_size=896, quantisation=256):
+    import contextlib
+    import io
+    import torch
+    _, dv, _, _ = load()
+    with contextlib.redirect_stdout(io.StringIO()):
+        model = dv.WaveRNN(hidden_size=hidden_size, quantisation=quantisation)
+    model.load_state_dict({k: torch.from_numpy(v.copy()) for k, v in state_dict_np.items()}, strict=True)
+    return model
+
+
+class injected_noise:
+    """Context manager: make the reference consume pre-drawn noise.
+
+    MoL: `Tensor.uniform_` is replaced so the k-th call returns the k-th pre-drawn tensor
+    (shapes checked) — draw order per step is u1 `(1,B,10)` then u2 `(1,B)`
+    (`utils/distribution.py:106,118`).  RAW / deepmind: `Categorical.sample` is replaced by
+    `argmax(probs / q)` with pre-drawn `q ~ Exp(1)`, which is what ATen multinomial computes
+    (SURVEY.md F8).
+    """
+
+    def __init__(self, uniforms=None, exps=None):
+        self.uniforms = list(uniforms) if uniforms is not None else None
+        self.exps = list(exps) if exps is not None else None
+
+    def __enter__(self):
+        import torch
+        self._u = torch.Tensor.uniform_
+        self._s = torch.distributions.Categorical.sample
+        ctx = self
+        if self.uniforms is not None:
+            it = iter(self.uniforms)
+
+            def uniform_(t, *a, **k):
+                # only the sampler's draws; `get_gru_cell` builds nn.GRUCell whose
+                # reset_parameters also calls uniform_ (`fatchord_version.py:274`)
+                if len(a) != 2 or a[0] != 1e-5:
+                    return ctx._u(t, *a, **k)
+                v = next(it)
+                assert tuple(v.shape) == tuple(t.shape), (v.shape, t.shape)
+                return t.copy_(v)
+            torch.Tensor.uniform_ = uniform_
+        if self.exps is not None:
+            ie = iter(self.exps)
+
+            def sample(dist, sample_shape=torch.Size()):
+                q = next(ie)
+                assert tuple(q.shape) == tuple(dist.probs.shape), (q.shape, dist.probs.shape)
+                return torch.argmax(dist.probs / q, dim=-1)
+            torch.distributions.Categorical.sample = sample
+        return ctx
+
+    def __exit__(self, *exc):
+        import torch
+        torch.Tensor.uniform_ = self._u
+        torch.distributions.Categorical.sample = self._s
+        return False
