@@ -1,0 +1,270 @@
+#!/usr/bin/env python
+"""Benchmark of the WaveRNN batched generation path (BASELINE.json configs[1]).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+A "step" is one full `generate` of the workload: fatchord WaveRNN MoL (rnn 512, fc 512, hop 275),
+batched target=11000 overlap=550 on a synthetic 10 s mel (T=801 -> 20 folds x 12100 loop steps ->
+220 000 samples), one utterance per GPU (weak scaling, no collective on the path).
+  value : samples/s, device time (CUDA events) of stage-resident runs: conditioning + fold +
+          per-sample loop + float64 tail, inputs already in HBM.
+  e2e   : samples/s through the public host call (wrnn_generate via ctypes): host mel in, host
+          float64 waveform out, copies inside the timed region.
+  roofline : the per-sample loop kernel, algorithmic weight bytes per loop step (15 331 448 B, fp32
+          MoL model) x steps / kernel time, against measured HBM bandwidth.
+  cpu_baseline : the oracle port (torch-CPU restatement of the reference loop) on a bounded sample.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+T_FRAMES, TARGET, OVERLAP = 801, 11000, 550
+WEIGHT_BYTES_PER_STEP = 15_331_448        # 3 825 152 matrix + 7 710 bias fp32 elements
+SAMPLE_RATE = 22050
+METRIC = 'generated audio samples/sec'
+CPU_SAMPLE_STEPS = 400                    # loop steps (x20 folds) of the workload timed on the CPU
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.isfile(p):
+        try:
+            return float(json.load(open(p))['hbm_gbs']), 'measured (MEASURED_PEAKS.json)'
+        except Exception:
+            pass
+    return 6650.0, 'fallback (B200_PROFILING.md)'
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ('index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,'
+         'clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
+         'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(['nvidia-smi', f'--query-gpu={self.Q}', '--format=csv,noheader,nounits',
+                                          '-i', str(self.index), '-lms', '100'], stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(',')])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        for r in self.rows:
+            try:
+                sm.append(float(r[1]))
+                mx.append(float(r[2]))
+                for n, v in zip(names, r[5:9]):
+                    if v.lower().startswith('active'):
+                        reasons.add(n)
+            except Exception:
+                pass
+        if not sm:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': [], 'samples': 0}
+        return {'sm_mhz': float(np.median(sm)), 'sm_max_mhz': max(mx), 'reasons': sorted(reasons), 'samples': len(sm)}
+
+
+def workload(rank=0):
+    from wavernn_b200 import synth
+    from wavernn_b200.config import VocoderDims
+    dims = VocoderDims(mode='MOL')
+    sd = synth.synth_state_dict(dims, seed=0, style='init')
+    mel = synth.synth_mel(T_FRAMES, seed=1234 + rank)
+    return dims, sd, mel
+
+
+def config_dict(n_gpus):
+    return {'workload': 'fatchord WaveRNN MoL rnn512 fc512 hop275 22.05kHz, batched generate target=11000 '
+                        'overlap=550, synthetic 10 s mel T=801 (20 folds x 12100 steps), one utterance per GPU',
+            'utterances_per_gpu': 1, 'folds_per_gpu': 20, 'loop_steps': 12100, 'samples_per_utterance': 220000,
+            'weights': 'random-init seed 0 (pretrained ljspeech.wavernn.mol.800k unavailable on this box)',
+            'noise': 'in-kernel Philox', 'parallelism': f'independent utterances x{n_gpus}, no collective',
+            'l2': 'flushed between timed iterations (256 MiB write)'}
+
+
+def cpu_port_rate(dims, sd, mel, steps, threads):
+    """Oracle port of the reference loop on the host cores: -> (samples/s equivalent, seconds)."""
+    import torch
+    from oracle import fatchord as ofc
+    from wavernn_b200 import synth
+    torch.set_num_threads(threads)
+    W = ofc.to_torch(sd)
+    with torch.no_grad():
+        t0 = time.time()
+        m, aux, wave_len = ofc.conditioning(W, dims, mel, True, TARGET, OVERLAP)
+        B, S, _ = m.shape
+        noise = synth.synth_noise_mol(steps, B, 4321)
+        ofc.run_loop(W, dims, m, aux, noise, max_steps=steps)
+        dt = time.time() - t0
+    return wave_len * (steps / S) / dt, dt
+
+
+def run_reference(args):
+    rank = int(os.environ.get('RANK', '0'))
+    if rank != 0:
+        return
+    dims, sd, mel = workload(0)
+    threads = os.cpu_count() or 1
+    for _ in range(args.warmup):
+        cpu_port_rate(dims, sd, mel, 20, threads)
+    rates, total = [], 0.0
+    for _ in range(args.steps):
+        r, dt = cpu_port_rate(dims, sd, mel, CPU_SAMPLE_STEPS, threads)
+        rates.append(r)
+        total += dt
+    v = float(np.median(rates))
+    sample = (f'conditioning + first {CPU_SAMPLE_STEPS} of 12100 loop steps at 20 folds per step '
+              f'(rate scaled to whole-utterance samples/s)')
+    print(json.dumps({
+        'impl': 'reference', 'metric': METRIC, 'value': v, 'unit': 'samples/s', 'rtf': v / SAMPLE_RATE,
+        'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': 1000 * total / max(args.steps, 1),
+        'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+        'config': config_dict(args.gpus),
+        'cpu_baseline': {'value': v, 'unit': 'samples/s', 'cores': threads, 'kind': 'port', 'sample': sample},
+        'e2e': {'value': v, 'unit': 'samples/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+        'gpu_launches': 0}))
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from wavernn_b200 import binding
+
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    rank = int(os.environ.get('RANK', '0'))
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    if not torch.cuda.is_available():
+        raise SystemExit('bench.py: no CUDA device and no CPU fallback for the product path')
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
+        dist.init_process_group('nccl', device_id=torch.device('cuda', local))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    dims, sd, mel = workload(rank)
+    voc = binding.Vocoder(dims, device=local)
+    voc.load_weights(sd)
+    stream = torch.cuda.current_stream().cuda_stream
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device='cuda')
+    wave_len = (T_FRAMES - 1) * dims.hop_length
+
+    # ---------------- value: inputs resident in HBM, device time by CUDA events ----------------
+    voc.stage([mel[0]], True, TARGET, OVERLAP, False, stream=stream)
+    for i in range(args.warmup):
+        voc.run_staged(seed=100 + i, stream=stream)
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    loop_ms, launches = [], 0
+    barrier()
+    t_wall = time.time()
+    for i in range(args.steps):
+        flush.fill_(i & 0xff)                      # L2 flush between timed iterations (not timed)
+        ev[i][0].record()
+        voc.run_staged(seed=1000 + i, stream=stream)
+        ev[i][1].record()
+        ev[i][1].synchronize()
+        t = voc.last_timing()
+        loop_ms.append(t['ms_loop'])
+        launches += t['launches']
+    barrier()
+    t_wall = time.time() - t_wall
+    dev_ms = sum(a.elapsed_time(b) for a, b in ev)
+    clocks = sampler.stop() if rank == 0 else None
+    wave = voc.fetch(stream=stream)[0]
+    assert wave.shape == (wave_len,) and np.all(np.isfinite(wave))
+
+    # ---------------- e2e: host buffers in, host waveform out, through the public call ----------
+    for i in range(min(args.warmup, 2)):
+        voc.generate([mel[0]], True, TARGET, OVERLAP, False, seed=i, stream=stream)
+    barrier()
+    t0 = time.time()
+    for i in range(args.steps):
+        out = voc.generate([mel[0]], True, TARGET, OVERLAP, False, seed=2000 + i, stream=stream)[0]
+    barrier()
+    e2e_s = time.time() - t0
+
+    tt = torch.tensor([dev_ms, e2e_s * 1000.0], dtype=torch.float64, device='cuda')
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    dev_ms_max, e2e_ms_max = tt.tolist()
+    total_samples = wave_len * args.steps * world
+    value = total_samples / (dev_ms_max / 1000.0)
+    e2e = total_samples / (e2e_ms_max / 1000.0)
+    if rank == 0:
+        peak, peak_src = measured_peaks()
+        t = voc.last_timing()
+        k_ms = float(np.mean(loop_ms))
+        achieved = WEIGHT_BYTES_PER_STEP * t['steps'] / (k_ms * 1e-3) / 1e9
+        line = {
+            'metric': METRIC, 'value': value, 'unit': 'samples/s', 'rtf': value / SAMPLE_RATE / world,
+            'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': dev_ms_max / args.steps,
+            'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+            'config': config_dict(world),
+            'e2e': {'value': e2e, 'unit': 'samples/s', 'rtf_per_gpu': e2e / SAMPLE_RATE / world,
+                    'h2d_bytes_per_step': int(mel[0].nbytes), 'd2h_bytes_per_step': int(wave_len * 8),
+                    'ms_per_step': e2e_ms_max / args.steps},
+            'gpu_launches': int(launches),
+            'loop': {'kernel': voc.loop_kernel_name(t['folds']), 'ms': k_ms, 'us_per_step': 1000 * k_ms / t['steps'],
+                     'folds': t['folds'], 'steps': t['steps'], 'ms_cond': t['ms_cond'], 'ms_tail': t['ms_tail'],
+                     'fold_steps_per_s': t['folds'] * t['steps'] / (k_ms * 1e-3)},
+            'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
+                         'traffic': None, 'peak_source': peak_src,
+                         'note': 'algorithmic = fp32 weight bytes re-read once per loop step; weights are '
+                                 'SM-resident, so frac > 1 means faster than streaming them from HBM'},
+            'clocks': clocks, 'wall_s_value_leg': t_wall,
+        }
+        if world == 1 and not args.no_cpu:
+            threads = os.cpu_count() or 1
+            v, dt = cpu_port_rate(dims, sd, mel, CPU_SAMPLE_STEPS, threads)
+            line['cpu_baseline'] = {'value': v, 'unit': 'samples/s', 'cores': threads, 'kind': 'port',
+                                    'sample': f'conditioning + first {CPU_SAMPLE_STEPS} of 12100 loop steps at 20 folds '
+                                              f'({dt:.1f} s of CPU work), scaled to samples/s'}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=10)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
+    ap.add_argument('--no-cpu', action='store_true', help='skip the cpu_baseline leg')
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == 'ours' else args.warmup
+    if args.impl == 'reference':
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == '__main__':
+    main()

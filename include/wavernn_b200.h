@@ -124,6 +124,11 @@ int wrnn_unfold(wrnn_handle *h, const double *y, int64_t folds, int64_t target, 
  * as float32; out float64.  wrnn_mulaw_lut (host only, no GPU) fills the mu-entry table. */
 int wrnn_decode_mu_law(wrnn_handle *h, const float *y, int64_t n, int32_t mu, double *out);
 int wrnn_mulaw_lut(int32_t mu, double *lut);
+/* numpy's float64 `power` is a SIMD routine that differs from libm `pow` by 1 ulp on some inputs
+ * (and between CPUs), so a host that must match the reference bit-for-bit evaluates the reference's
+ * expression itself and installs the table here (mu entries, copied).  Without it the library uses
+ * wrnn_mulaw_lut (libm, within 1 ulp). */
+int wrnn_set_mulaw_lut(wrnn_handle *h, int32_t mu, const double *lut);
 /* Host tables of the cross-fade / fade-out gains (numpy linspace semantics), host only. */
 int wrnn_xfade_tables(int64_t overlap, double *fade_in, double *fade_out);
 /* Teacher-forced logits == WaveRNN.forward (fatchord_version.py:131-167): x (n_seq, S) previous

@@ -1,0 +1,418 @@
+// C ABI, part 2: stage -> run -> fetch (and wrnn_generate = the three in sequence).
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+
+#include "internal.h"
+
+namespace wrnn {
+
+struct StageOpts {
+    bool prepadded = false;        // mels already carry `pad` frames on both sides (forward_logits)
+    const float *teacher = nullptr;   // host [B][S]
+    bool want_logits = false;
+};
+
+static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+// Layout of ws_meta (device): FoldMeta[B] | TailMeta[n_utt] | int32 fold_len[B]
+struct MetaLayout { size_t off_fold, off_tail, off_len, bytes; };
+static MetaLayout meta_layout(int64_t B, int n_utt) {
+    MetaLayout m;
+    m.off_fold = 0;
+    m.off_tail = align_up(sizeof(FoldMeta) * B, 64);
+    m.off_len = m.off_tail + align_up(sizeof(TailMeta) * n_utt, 64);
+    m.bytes = m.off_len + align_up(sizeof(int32_t) * B, 64);
+    return m;
+}
+// Layout of ws_tables (device doubles): fade_in[ov] | fade_out[ov] | fo[20*hop] | lut[NC]
+struct TableLayout { size_t fin, fout, fo, lut, n; };
+static TableLayout table_layout(const wrnn_handle *h) {
+    TableLayout t;
+    t.fin = 0;
+    t.fout = t.fin + (size_t)std::max<int64_t>(h->overlap, 1);
+    t.fo = t.fout + (size_t)std::max<int64_t>(h->overlap, 1);
+    t.lut = t.fo + (size_t)20 * h->d.hop;
+    t.n = t.lut + (size_t)h->d.NC;
+    return t;
+}
+
+int do_stage(wrnn_handle *h, const float *const *mels, const int32_t *T, int32_t n_utt, int32_t batched,
+             int32_t target, int32_t overlap, int32_t mu_law, const wrnn_noise *noise, cudaStream_t st,
+             const StageOpts &o) {
+    const Dims &d = h->d;
+    h->staged = false;
+    if (!mels || !T || n_utt < 1) return fail(h, WRNN_ERR_ARG, "need at least one utterance");
+    WRNN_CUDA(h, cudaSetDevice(h->device));
+    WRNN_TRY(ensure_packed_public(h));
+    if (batched && (target < 1 || overlap < 0)) return fail(h, WRNN_ERR_ARG, "target must be >= 1 and overlap >= 0");
+    h->batched = batched ? 1 : 0;
+    h->target = target;
+    h->overlap = batched ? overlap : 0;
+    h->mu_law = (d.mode == WRNN_MODE_RAW && mu_law) ? 1 : 0;     // fatchord_version.py:174
+    h->utts.clear();
+    int64_t mel_off = 0, up_off = 0, res_off = 0, out_off = 0, fold0 = 0, Smax = 0;
+    for (int u = 0; u < n_utt; u++) {
+        wrnn_handle::Utt ut;
+        const int Tin = T[u];
+        ut.T = o.prepadded ? Tin - 2 * d.pad : Tin;
+        if (!mels[u] || ut.T < 1) return fail(h, WRNN_ERR_ARG, "utterance %d: empty mel", u);
+        ut.L = (int64_t)ut.T * d.hop;
+        ut.wave_len = (int64_t)(ut.T - 1) * d.hop;
+        // the reference's fade-out multiplies the last 20*hop samples (:256-258) and raises on
+        // shorter output; same condition, raised early
+        if (!o.want_logits && ut.wave_len < 20 * (int64_t)d.hop)
+            return fail(h, WRNN_ERR_ARG, "utterance %d: mel too short (T=%d, need T >= 21 for the 20-hop fade-out)", u, ut.T);
+        if (batched) {
+            if (ut.L <= overlap) return fail(h, WRNN_ERR_ARG, "utterance %d: shorter than the overlap", u);
+            ut.nfolds = wrnn_num_folds(ut.L, target, overlap);
+        } else {
+            ut.nfolds = 1;
+            Smax = std::max(Smax, ut.L);
+        }
+        ut.fold0 = fold0; fold0 += ut.nfolds;
+        ut.mel_off = mel_off; mel_off += (int64_t)d.F * Tin;
+        ut.up_off = up_off; up_off += ut.L;
+        ut.res_off = res_off; res_off += ut.T;
+        ut.out_off = out_off; out_off += ut.wave_len;
+        h->utts.push_back(ut);
+    }
+    h->B = fold0;
+    h->S = batched ? (int64_t)target + 2 * (int64_t)overlap : Smax;
+    h->total_out = out_off;
+    if (h->B > 0x7fffffff / 4 || h->S > 0x7fffffff) return fail(h, WRNN_ERR_ARG, "too many folds / steps");
+
+    // ---- mels: host -> pinned -> device (raw region, then a padded region filled by run) ----
+    const size_t mel_bytes = (size_t)mel_off * sizeof(float);
+    if (h->h_pinned_in_bytes < mel_bytes) {
+        if (h->h_pinned_in) cudaFreeHost(h->h_pinned_in);
+        h->h_pinned_in = nullptr;
+        WRNN_CUDA(h, cudaMallocHost((void **)&h->h_pinned_in, mel_bytes + mel_bytes / 4));
+        h->h_pinned_in_bytes = mel_bytes + mel_bytes / 4;
+    }
+    for (int u = 0; u < n_utt; u++)
+        memcpy(h->h_pinned_in + h->utts[u].mel_off, mels[u], (size_t)d.F * T[u] * sizeof(float));
+    size_t padded_floats = 0;
+    for (auto &ut : h->utts) padded_floats += (size_t)d.F * (ut.T + 2 * d.pad);
+    WRNN_TRY(ws_reserve(h, h->ws_mel, mel_bytes + padded_floats * sizeof(float) + 256));
+    WRNN_CUDA(h, cudaMemcpyAsync(h->ws_mel.p, h->h_pinned_in, mel_bytes, cudaMemcpyHostToDevice, st));
+
+    // ---- meta ----
+    const MetaLayout ml = meta_layout(h->B, n_utt);
+    std::vector<char> hm(ml.bytes, 0);
+    FoldMeta *fm = (FoldMeta *)(hm.data() + ml.off_fold);
+    TailMeta *tm = (TailMeta *)(hm.data() + ml.off_tail);
+    int32_t *fl = (int32_t *)(hm.data() + ml.off_len);
+    for (int u = 0; u < n_utt; u++) {
+        const auto &ut = h->utts[u];
+        for (int64_t i = 0; i < ut.nfolds; i++) {
+            fm[ut.fold0 + i] = FoldMeta{ut.up_off, ut.res_off, batched ? i * ((int64_t)target + overlap) : 0, ut.L};
+            fl[ut.fold0 + i] = (int32_t)(batched ? h->S : ut.L);
+        }
+        tm[u] = TailMeta{ut.fold0, ut.nfolds, ut.wave_len, ut.out_off};
+    }
+    WRNN_TRY(ws_reserve(h, h->ws_meta, ml.bytes));
+    WRNN_CUDA(h, cudaMemcpyAsync(h->ws_meta.p, hm.data(), ml.bytes, cudaMemcpyHostToDevice, st));
+
+    // ---- float64 tables ----
+    const TableLayout tl = table_layout(h);
+    std::vector<double> tab(tl.n, 0.0);
+    if (batched) wrnn_xfade_tables(overlap, tab.data() + tl.fin, tab.data() + tl.fout);
+    host_linspace(1.0, 0.0, 20 * (int64_t)d.hop, tab.data() + tl.fo);          // :256
+    if (d.mode == WRNN_MODE_RAW) {
+        if ((int)h->lut_override.size() == d.NC) memcpy(tab.data() + tl.lut, h->lut_override.data(), d.NC * sizeof(double));
+        else wrnn_mulaw_lut(d.NC, tab.data() + tl.lut);
+    }
+    WRNN_TRY(ws_reserve(h, h->ws_tables, tl.n * sizeof(double)));
+    WRNN_CUDA(h, cudaMemcpyAsync(h->ws_tables.p, tab.data(), tl.n * sizeof(double), cudaMemcpyHostToDevice, st));
+
+    // ---- injected noise ----
+    h->have_noise = false;
+    if (noise) {
+        if (noise->steps != h->S || noise->folds != h->B)
+            return fail(h, WRNN_ERR_ARG, "noise is %lld x %lld but the call runs %lld steps x %lld folds",
+                        (long long)noise->steps, (long long)noise->folds, (long long)h->S, (long long)h->B);
+        const size_t SB = (size_t)h->S * h->B;
+        if (d.mode == WRNN_MODE_MOL) {
+            if (!noise->u1 || !noise->u2) return fail(h, WRNN_ERR_ARG, "MOL noise needs u1 and u2");
+            const size_t nm = d.NC / 3;
+            WRNN_TRY(ws_reserve(h, h->ws_noise, SB * (nm + 1) * sizeof(float)));
+            WRNN_CUDA(h, cudaMemcpyAsync(h->ws_noise.p, noise->u1, SB * nm * sizeof(float), cudaMemcpyHostToDevice, st));
+            WRNN_CUDA(h, cudaMemcpyAsync((float *)h->ws_noise.p + SB * nm, noise->u2, SB * sizeof(float),
+                                         cudaMemcpyHostToDevice, st));
+        } else {
+            if (!noise->q) return fail(h, WRNN_ERR_ARG, "RAW noise needs q");
+            WRNN_TRY(ws_reserve(h, h->ws_noise, SB * d.NC * sizeof(float)));
+            WRNN_CUDA(h, cudaMemcpyAsync(h->ws_noise.p, noise->q, SB * d.NC * sizeof(float), cudaMemcpyHostToDevice, st));
+        }
+        h->have_noise = true;
+    }
+    if (o.teacher) {
+        WRNN_TRY(ws_reserve(h, h->ws_teacher, (size_t)h->B * h->S * sizeof(float)));
+        WRNN_CUDA(h, cudaMemcpyAsync(h->ws_teacher.p, o.teacher, (size_t)h->B * h->S * sizeof(float),
+                                     cudaMemcpyHostToDevice, st));
+    }
+    // ---- device workspaces for run ----
+    WRNN_TRY(ws_reserve(h, h->ws_up, (size_t)up_off * d.F * sizeof(float)));
+    WRNN_TRY(ws_reserve(h, h->ws_res, (size_t)res_off * d.R * sizeof(float)));
+    WRNN_TRY(ws_reserve(h, h->ws_cond, (size_t)h->B * h->S * (d.F + d.R) * sizeof(float)));
+    WRNN_TRY(ws_reserve(h, h->ws_samples, (size_t)h->B * h->S * sizeof(float)));
+    WRNN_TRY(ws_reserve(h, h->ws_picks, (size_t)h->B * h->S * sizeof(int32_t)));
+    WRNN_TRY(ws_reserve(h, h->ws_out, (size_t)std::max<int64_t>(h->total_out, 1) * sizeof(double)));
+    if (o.want_logits) WRNN_TRY(ws_reserve(h, h->ws_logits, (size_t)h->B * h->S * d.NC * sizeof(float)));
+    h->staged = true;
+    return 0;
+}
+
+int do_run(wrnn_handle *h, uint64_t seed, cudaStream_t st, const StageOpts &o) {
+    if (!h->staged) return fail(h, WRNN_ERR_STATE, "nothing staged: call wrnn_stage first");
+    const Dims &d = h->d;
+    WRNN_CUDA(h, cudaSetDevice(h->device));
+    h->launches = 0;
+    const int n_utt = (int)h->utts.size();
+    const MetaLayout ml = meta_layout(h->B, n_utt);
+    const TableLayout tl = table_layout(h);
+    float *mel_raw = (float *)h->ws_mel.p;
+    size_t raw_floats = 0;
+    for (auto &ut : h->utts) raw_floats += (size_t)d.F * (o.prepadded ? ut.T + 2 * d.pad : ut.T);
+    float *mel_pad = mel_raw + align_up(raw_floats, 64);
+    WRNN_CUDA(h, cudaEventRecord(h->ev[0], st));
+    // conditioning per utterance (fatchord_version.py:185-186)
+    size_t poff = 0;
+    for (auto &ut : h->utts) {
+        const int Tp = ut.T + 2 * d.pad;
+        const float *mp;
+        if (o.prepadded) {
+            mp = mel_raw + ut.mel_off;
+        } else {
+            WRNN_TRY(launch_pad_mel(h, mel_raw + ut.mel_off, ut.T, mel_pad + poff, st));
+            mp = mel_pad + poff;
+        }
+        WRNN_TRY(run_conditioning(h, mp, Tp, (float *)h->ws_up.p + (size_t)ut.up_off * d.F,
+                                  (float *)h->ws_res.p + (size_t)ut.res_off * d.R, st));
+        poff += (size_t)d.F * Tp;
+    }
+    // fold (:188-190); unbatched = one fold per utterance
+    WRNN_TRY(launch_fold_cond(h, (const float *)h->ws_up.p, (const float *)h->ws_res.p,
+                              (const FoldMeta *)((char *)h->ws_meta.p + ml.off_fold), h->B, h->S, (float *)h->ws_cond.p, st));
+    WRNN_CUDA(h, cudaEventRecord(h->ev[1], st));
+    // per-sample loop (:201-241)
+    LoopArgs a;
+    a.cond = (const float *)h->ws_cond.p;
+    a.B = h->B;
+    a.S = h->S;
+    a.fold_len = (const int32_t *)((char *)h->ws_meta.p + ml.off_len);
+    a.u1 = a.u2 = a.q = nullptr;
+    if (h->have_noise) {
+        if (d.mode == WRNN_MODE_MOL) {
+            a.u1 = (const float *)h->ws_noise.p;
+            a.u2 = a.u1 + (size_t)h->S * h->B * (d.NC / 3);
+        } else {
+            a.q = (const float *)h->ws_noise.p;
+        }
+    }
+    a.teacher = o.teacher ? (const float *)h->ws_teacher.p : nullptr;
+    a.logits_out = o.want_logits ? (float *)h->ws_logits.p : nullptr;
+    a.samples = (float *)h->ws_samples.p;
+    a.picks = (int32_t *)h->ws_picks.p;
+    a.seed = seed;
+    WRNN_TRY(fma_run(h, a, st));
+    WRNN_CUDA(h, cudaEventRecord(h->ev[2], st));
+    // float64 tail (:243-258)
+    if (!o.want_logits) {
+        int64_t max_wave = 0;
+        for (auto &ut : h->utts) max_wave = std::max(max_wave, ut.wave_len);
+        const double *tab = (const double *)h->ws_tables.p;
+        WRNN_TRY(launch_tail(h, a.samples, a.picks, (const TailMeta *)((char *)h->ws_meta.p + ml.off_tail), n_utt,
+                             max_wave, h->S, h->batched, h->target, h->overlap, tab + tl.fin, tab + tl.fout,
+                             tab + tl.fo, 20 * (int64_t)d.hop, h->mu_law ? tab + tl.lut : nullptr,
+                             (double *)h->ws_out.p, st));
+    }
+    WRNN_CUDA(h, cudaEventRecord(h->ev[3], st));
+    return 0;
+}
+
+int check_abort(wrnn_handle *h, cudaStream_t st) {
+    int flag = 0;
+    if (h->ws_sync.p) {
+        WRNN_CUDA(h, cudaMemcpyAsync(&flag, (char *)h->ws_sync.p + 16, sizeof(int), cudaMemcpyDeviceToHost, st));
+        WRNN_CUDA(h, cudaStreamSynchronize(st));
+    }
+    if (flag) return fail(h, WRNN_ERR_CUDA, "per-sample loop kernel aborted: grid barrier watchdog fired");
+    return 0;
+}
+
+}  // namespace wrnn
+
+using namespace wrnn;
+
+extern "C" {
+
+int wrnn_stage(wrnn_handle *h, const float *const *mels, const int32_t *T, int32_t n_utt, int32_t batched,
+               int32_t target, int32_t overlap, int32_t mu_law, const wrnn_noise *noise, void *cuda_stream) {
+    if (!h) return WRNN_ERR_ARG;
+    return do_stage(h, mels, T, n_utt, batched, target, overlap, mu_law, noise, (cudaStream_t)cuda_stream, StageOpts());
+}
+
+int wrnn_run_staged(wrnn_handle *h, uint64_t seed, void *cuda_stream) {
+    if (!h) return WRNN_ERR_ARG;
+    return do_run(h, seed, (cudaStream_t)cuda_stream, StageOpts());
+}
+
+int wrnn_fetch(wrnn_handle *h, double *const *out, int64_t *out_len, void *cuda_stream) {
+    if (!h || !out) return fail(h, WRNN_ERR_ARG, "null argument");
+    if (!h->staged) return fail(h, WRNN_ERR_STATE, "nothing staged");
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    const size_t bytes = (size_t)h->total_out * sizeof(double);
+    if (h->h_pinned_out_bytes < bytes) {
+        if (h->h_pinned_out) cudaFreeHost(h->h_pinned_out);
+        h->h_pinned_out = nullptr;
+        WRNN_CUDA(h, cudaMallocHost((void **)&h->h_pinned_out, bytes + bytes / 4 + 64));
+        h->h_pinned_out_bytes = bytes + bytes / 4 + 64;
+    }
+    WRNN_CUDA(h, cudaMemcpyAsync(h->h_pinned_out, h->ws_out.p, bytes, cudaMemcpyDeviceToHost, st));
+    WRNN_TRY(check_abort(h, st));      // synchronises the stream
+    WRNN_CUDA(h, cudaGetLastError());
+    for (size_t u = 0; u < h->utts.size(); u++) {
+        const auto &ut = h->utts[u];
+        memcpy(out[u], h->h_pinned_out + ut.out_off, (size_t)ut.wave_len * sizeof(double));
+        if (out_len) out_len[u] = ut.wave_len;
+    }
+    return 0;
+}
+
+int wrnn_generate(wrnn_handle *h, const float *const *mels, const int32_t *T, int32_t n_utt, int32_t batched,
+                  int32_t target, int32_t overlap, int32_t mu_law, const wrnn_noise *noise, uint64_t seed,
+                  double *const *out, int64_t *out_len, void *cuda_stream) {
+    if (!h) return WRNN_ERR_ARG;
+    WRNN_TRY(wrnn_stage(h, mels, T, n_utt, batched, target, overlap, mu_law, noise, cuda_stream));
+    WRNN_TRY(wrnn_run_staged(h, seed, cuda_stream));
+    return wrnn_fetch(h, out, out_len, cuda_stream);
+}
+
+int wrnn_last_timing(wrnn_handle *h, float *ms_cond, float *ms_loop, float *ms_tail, int64_t *steps,
+                     int64_t *folds, int64_t *kernel_launches) {
+    if (!h) return WRNN_ERR_ARG;
+    float a = 0, b = 0, c = 0;
+    WRNN_CUDA(h, cudaEventSynchronize(h->ev[3]));
+    WRNN_CUDA(h, cudaEventElapsedTime(&a, h->ev[0], h->ev[1]));
+    WRNN_CUDA(h, cudaEventElapsedTime(&b, h->ev[1], h->ev[2]));
+    WRNN_CUDA(h, cudaEventElapsedTime(&c, h->ev[2], h->ev[3]));
+    if (ms_cond) *ms_cond = a;
+    if (ms_loop) *ms_loop = b;
+    if (ms_tail) *ms_tail = c;
+    if (steps) *steps = h->S;
+    if (folds) *folds = h->B;
+    if (kernel_launches) *kernel_launches = h->launches;
+    return 0;
+}
+
+int wrnn_fetch_samples(wrnn_handle *h, float *samples, void *cuda_stream) {
+    if (!h || !samples) return fail(h, WRNN_ERR_ARG, "null argument");
+    if (!h->staged) return fail(h, WRNN_ERR_STATE, "nothing staged");
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    WRNN_CUDA(h, cudaMemcpyAsync(samples, h->ws_samples.p, (size_t)h->B * h->S * sizeof(float), cudaMemcpyDeviceToHost, st));
+    WRNN_CUDA(h, cudaStreamSynchronize(st));
+    return 0;
+}
+
+int wrnn_forward_logits(wrnn_handle *h, const float *x, const float *mels, int32_t n_seq, int64_t S, float *logits) {
+    if (!h || !x || !mels || !logits || n_seq < 1) return fail(h, WRNN_ERR_ARG, "null argument");
+    const Dims &d = h->d;
+    if (S < 1 || S % d.hop) return fail(h, WRNN_ERR_ARG, "S must be a positive multiple of hop_length");
+    const int Tp = (int)(S / d.hop) + 2 * d.pad;
+    std::vector<const float *> mp(n_seq);
+    std::vector<int32_t> Ts(n_seq, Tp);
+    for (int i = 0; i < n_seq; i++) mp[i] = mels + (size_t)i * d.F * Tp;
+    StageOpts o;
+    o.prepadded = true;
+    o.teacher = x;
+    o.want_logits = true;
+    WRNN_TRY(do_stage(h, mp.data(), Ts.data(), n_seq, 0, 0, 0, 0, nullptr, 0, o));
+    WRNN_TRY(do_run(h, 0, 0, o));
+    WRNN_CUDA(h, cudaMemcpyAsync(logits, h->ws_logits.p, (size_t)n_seq * S * d.NC * sizeof(float), cudaMemcpyDeviceToHost, 0));
+    WRNN_TRY(check_abort(h, 0));
+    h->staged = false;
+    return 0;
+}
+
+// ------------------------------------------------------------------ component entry points
+int wrnn_upsample(wrnn_handle *h, const float *mel, int32_t T, float *mels_out, float *aux_out) {
+    if (!h || !mel || !mels_out || !aux_out || T < 1) return fail(h, WRNN_ERR_ARG, "bad argument");
+    const Dims &d = h->d;
+    WRNN_CUDA(h, cudaSetDevice(h->device));
+    WRNN_TRY(ensure_packed_public(h));
+    const int Tp = T + 2 * d.pad;
+    const int64_t L = (int64_t)T * d.hop;
+    const size_t raw = align_up((size_t)d.F * T, 64), padf = (size_t)d.F * Tp;
+    WRNN_TRY(ws_reserve(h, h->ws_mel, (raw + padf) * sizeof(float)));
+    WRNN_TRY(ws_reserve(h, h->ws_up, (size_t)L * d.F * sizeof(float)));
+    WRNN_TRY(ws_reserve(h, h->ws_res, (size_t)T * d.R * sizeof(float)));
+    WRNN_TRY(ws_reserve(h, h->ws_cond, (size_t)L * d.R * sizeof(float)));
+    float *mraw = (float *)h->ws_mel.p, *mpad = mraw + raw;
+    WRNN_CUDA(h, cudaMemcpyAsync(mraw, mel, (size_t)d.F * T * sizeof(float), cudaMemcpyHostToDevice, 0));
+    WRNN_TRY(launch_pad_mel(h, mraw, T, mpad, 0));
+    WRNN_TRY(run_conditioning(h, mpad, Tp, (float *)h->ws_up.p, (float *)h->ws_res.p, 0));
+    WRNN_TRY(launch_repeat_aux(h, (const float *)h->ws_res.p, T, (float *)h->ws_cond.p, 0));
+    WRNN_CUDA(h, cudaMemcpyAsync(mels_out, h->ws_up.p, (size_t)L * d.F * sizeof(float), cudaMemcpyDeviceToHost, 0));
+    WRNN_CUDA(h, cudaMemcpyAsync(aux_out, h->ws_cond.p, (size_t)L * d.R * sizeof(float), cudaMemcpyDeviceToHost, 0));
+    WRNN_CUDA(h, cudaStreamSynchronize(0));
+    h->staged = false;
+    return 0;
+}
+
+int wrnn_fold(wrnn_handle *h, const float *x, int64_t L, int32_t F, int64_t target, int64_t overlap, float *out) {
+    if (!h || !x || !out || L < 1 || F < 1 || target < 1 || overlap < 0 || L <= overlap)
+        return fail(h, WRNN_ERR_ARG, "bad argument");
+    WRNN_CUDA(h, cudaSetDevice(h->device));
+    const int64_t folds = wrnn_num_folds(L, target, overlap), len = target + 2 * overlap;
+    WRNN_TRY(ws_reserve(h, h->ws_tmp0, (size_t)L * F * sizeof(float)));
+    WRNN_TRY(ws_reserve(h, h->ws_tmp1, (size_t)folds * len * F * sizeof(float)));
+    WRNN_CUDA(h, cudaMemcpyAsync(h->ws_tmp0.p, x, (size_t)L * F * sizeof(float), cudaMemcpyHostToDevice, 0));
+    WRNN_TRY(launch_fold(h, (const float *)h->ws_tmp0.p, L, F, target, overlap, folds, (float *)h->ws_tmp1.p, 0));
+    WRNN_CUDA(h, cudaMemcpyAsync(out, h->ws_tmp1.p, (size_t)folds * len * F * sizeof(float), cudaMemcpyDeviceToHost, 0));
+    WRNN_CUDA(h, cudaStreamSynchronize(0));
+    return 0;
+}
+
+int wrnn_unfold(wrnn_handle *h, const double *y, int64_t folds, int64_t target, int64_t overlap, double *out) {
+    if (!h || !y || !out || folds < 1 || target < 0 || overlap < 0) return fail(h, WRNN_ERR_ARG, "bad argument");
+    WRNN_CUDA(h, cudaSetDevice(h->device));
+    const int64_t len = target + 2 * overlap, total = folds * (target + overlap) + overlap;
+    const size_t ov = (size_t)std::max<int64_t>(overlap, 1);
+    std::vector<double> tab(2 * ov, 0.0);
+    wrnn_xfade_tables(overlap, tab.data(), tab.data() + ov);
+    WRNN_TRY(ws_reserve(h, h->ws_tmp0, (size_t)folds * len * sizeof(double)));
+    WRNN_TRY(ws_reserve(h, h->ws_tmp1, (size_t)total * sizeof(double)));
+    WRNN_TRY(ws_reserve(h, h->ws_tables, 2 * ov * sizeof(double)));
+    WRNN_CUDA(h, cudaMemcpyAsync(h->ws_tmp0.p, y, (size_t)folds * len * sizeof(double), cudaMemcpyHostToDevice, 0));
+    WRNN_CUDA(h, cudaMemcpyAsync(h->ws_tables.p, tab.data(), 2 * ov * sizeof(double), cudaMemcpyHostToDevice, 0));
+    WRNN_TRY(launch_unfold(h, (const double *)h->ws_tmp0.p, folds, target, overlap, (const double *)h->ws_tables.p,
+                           (const double *)h->ws_tables.p + ov, (double *)h->ws_tmp1.p, 0));
+    WRNN_CUDA(h, cudaMemcpyAsync(out, h->ws_tmp1.p, (size_t)total * sizeof(double), cudaMemcpyDeviceToHost, 0));
+    WRNN_CUDA(h, cudaStreamSynchronize(0));
+    h->staged = false;
+    return 0;
+}
+
+int wrnn_decode_mu_law(wrnn_handle *h, const float *y, int64_t n, int32_t mu, double *out) {
+    if (!h || !y || !out || n < 1 || mu < 2) return fail(h, WRNN_ERR_ARG, "bad argument");
+    WRNN_CUDA(h, cudaSetDevice(h->device));
+    std::vector<double> lut(mu);
+    if ((int)h->lut_override.size() == mu) lut = h->lut_override;
+    else wrnn_mulaw_lut(mu, lut.data());
+    WRNN_TRY(ws_reserve(h, h->ws_tmp0, (size_t)n * sizeof(float)));
+    WRNN_TRY(ws_reserve(h, h->ws_tmp1, (size_t)n * sizeof(double)));
+    WRNN_TRY(ws_reserve(h, h->ws_tables, (size_t)mu * sizeof(double)));
+    WRNN_CUDA(h, cudaMemcpyAsync(h->ws_tmp0.p, y, (size_t)n * sizeof(float), cudaMemcpyHostToDevice, 0));
+    WRNN_CUDA(h, cudaMemcpyAsync(h->ws_tables.p, lut.data(), (size_t)mu * sizeof(double), cudaMemcpyHostToDevice, 0));
+    WRNN_TRY(launch_mulaw(h, (const float *)h->ws_tmp0.p, n, mu, (const double *)h->ws_tables.p, (double *)h->ws_tmp1.p, 0));
+    WRNN_CUDA(h, cudaMemcpyAsync(out, h->ws_tmp1.p, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, 0));
+    WRNN_CUDA(h, cudaStreamSynchronize(0));
+    h->staged = false;
+    return 0;
+}
+
+}  // extern "C"

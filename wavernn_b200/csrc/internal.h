@@ -1,0 +1,146 @@
+// Internal declarations shared by the .cu files of libwavernn_b200.so (not part of the ABI).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../../include/wavernn_b200.h"
+
+namespace wrnn {
+
+struct Dims {
+    int H, FC, F, A, R, C, NC, pad, hop, nres, nup, up[8], total_scale, indent, mode, bits, ksize;
+};
+
+struct HostTensor {            // checkpoint tensor kept on the host; packers upload device images
+    std::vector<float> v;
+    std::vector<int64_t> shape;
+};
+
+// ---- packed conditioning weights (cond.cu) -------------------------------------------------
+struct CondPack {
+    // all [k][c] (input index major, output channel fastest) so thread c reads coalesced
+    float *conv_in_t = nullptr;        // [(F*ksize)][C]
+    float *bn_scale = nullptr;         // [1 + 2*nres][C]  gamma / sqrt(var + eps)
+    float *bn_shift = nullptr;         // [1 + 2*nres][C]  beta - mean * scale
+    float *res_t = nullptr;            // [2*nres][C][C]
+    float *conv_out_t = nullptr;       // [C][R]
+    float *conv_out_b = nullptr;       // [R]
+    float *fir[8] = {nullptr};         // [2*s+1] per stage
+};
+
+// ---- per-sample loop, FMA kernel (loop_fma.cu) ----------------------------------------------
+struct FmaPlan {
+    int G = 0;                 // grid (CTAs), one per SM
+    int upc = 0, rF = 0, r3 = 0;   // GRU units / fc rows / fc3 rows per CTA
+    int KI = 0, KH = 0, KHA = 0, KFA = 0, KF = 0;   // padded (multiple of 4) reduction lengths
+    int64_t img_floats = 0;    // per-CTA weight image size
+    int64_t off_I, off_r1i, off_r1h, off_r2i, off_r2h, off_f1, off_f2, off_f3, off_bias;
+    float *image = nullptr;    // device [G][img_floats]
+    size_t smem_bytes = 0;
+};
+
+struct LoopArgs {
+    const float *cond;         // [B][S][F+R]
+    int64_t B, S;
+    const int32_t *fold_len;   // [B] steps valid per fold (== S when batched)
+    const float *u1, *u2, *q;  // injected noise or null
+    const float *teacher;      // [B][S] or null
+    float *logits_out;         // [B][S][NC] or null
+    float *samples;            // [B][S]
+    int32_t *picks;            // [B][S] (RAW class index / MoL mixture index)
+    uint64_t seed;
+};
+
+struct Workspace {             // grows on demand, never shrinks
+    void *p = nullptr;
+    size_t bytes = 0;
+};
+
+}  // namespace wrnn
+
+struct wrnn_handle {
+    wrnn_config cfg;
+    wrnn::Dims d;
+    int device = 0;
+    int num_sms = 0;
+    size_t smem_optin = 0;
+    std::string err;
+    std::map<std::string, wrnn::HostTensor> w;     // raw checkpoint tensors (host copies)
+    bool packed = false;
+    wrnn::CondPack cp;
+    wrnn::FmaPlan fma;
+    int force_kernel = 0;
+    std::vector<double> lut_override;   // host-supplied mu-law table (wrnn_set_mulaw_lut)
+    bool sparse = false;
+
+    // staged call
+    struct Utt { int T; int64_t L, wave_len, fold0, nfolds, mel_off, up_off, res_off, out_off; };
+    std::vector<Utt> utts;
+    bool staged = false;
+    int batched = 0, mu_law = 0;
+    int64_t target = 0, overlap = 0, B = 0, S = 0, total_out = 0;
+    bool have_noise = false;
+
+    wrnn::Workspace ws_mel, ws_up, ws_res, ws_cond, ws_samples, ws_picks, ws_out, ws_noise,
+        ws_meta, ws_tables, ws_sync, ws_act, ws_tmp0, ws_tmp1, ws_teacher, ws_logits;
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    int64_t launches = 0;
+    double *h_pinned_out = nullptr;
+    size_t h_pinned_out_bytes = 0;
+    float *h_pinned_in = nullptr;
+    size_t h_pinned_in_bytes = 0;
+};
+
+namespace wrnn {
+
+// error plumbing: functions return 0 / negative status and fill h->err
+int fail(wrnn_handle *h, int code, const char *fmt, ...);
+#define WRNN_CUDA(h, expr)                                                                    \
+    do {                                                                                      \
+        cudaError_t e__ = (expr);                                                             \
+        if (e__ != cudaSuccess)                                                               \
+            return wrnn::fail((h), WRNN_ERR_CUDA, "%s failed: %s (%s:%d)", #expr,            \
+                              cudaGetErrorString(e__), __FILE__, __LINE__);                   \
+    } while (0)
+#define WRNN_TRY(expr)                                                                        \
+    do {                                                                                      \
+        int r__ = (expr);                                                                     \
+        if (r__ != 0) return r__;                                                             \
+    } while (0)
+
+int ws_reserve(wrnn_handle *h, Workspace &w, size_t bytes);
+int ensure_packed_public(wrnn_handle *h);   // pack weights for the kernels if not yet done
+
+// cond.cu
+int pack_cond(wrnn_handle *h);
+// mel_padded: device [F][Tp] (Tp = T + 2*pad); up_mels: device [L][F]; res_out: device [T][R]
+int run_conditioning(wrnn_handle *h, const float *mel_padded, int Tp, float *up_mels, float *res_out,
+                     cudaStream_t st);
+int launch_repeat_aux(wrnn_handle *h, const float *res_out, int T, float *aux, cudaStream_t st);
+int launch_pad_mel(wrnn_handle *h, const float *mel, int T, float *mel_padded, cudaStream_t st);
+int launch_fold(wrnn_handle *h, const float *x, int64_t L, int F, int64_t target, int64_t overlap,
+                int64_t folds, float *out, cudaStream_t st);
+struct FoldMeta { int64_t up_off, res_off, start, L; };   // per fold, element offsets (rows)
+int launch_fold_cond(wrnn_handle *h, const float *up_mels, const float *res_out, const FoldMeta *meta,
+                     int64_t B, int64_t S, float *cond, cudaStream_t st);
+struct TailMeta { int64_t fold0, nfolds, wave_len, out_off; };   // per utterance
+int launch_tail(wrnn_handle *h, const float *samples, const int32_t *picks, const TailMeta *meta,
+                int n_utt, int64_t max_wave, int64_t S, int batched, int64_t target, int64_t overlap,
+                const double *fade_in, const double *fade_out, const double *fo, int64_t fo_len,
+                const double *lut, double *out, cudaStream_t st);
+int launch_unfold(wrnn_handle *h, const double *y, int64_t folds, int64_t target, int64_t overlap,
+                  const double *fade_in, const double *fade_out, double *out, cudaStream_t st);
+int launch_mulaw(wrnn_handle *h, const float *y, int64_t n, int mu, const double *lut, double *out,
+                 cudaStream_t st);
+
+// loop_fma.cu
+int fma_plan(wrnn_handle *h);
+int fma_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st);
+
+// host tables (api.cu)
+void host_linspace(double start, double stop, int64_t n, double *out);
+
+}  // namespace wrnn

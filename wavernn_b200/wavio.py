@@ -1,0 +1,35 @@
+"""Dependency-free float32 WAV writer.
+
+Replaces `save_wav` (`utils/dsp.py:22-23`), which calls `librosa.output.write_wav` — an API that
+no longer exists in current librosa and is absent on this box.  Same output contract: float32
+samples, `sample_rate` Hz, mono (IEEE-float WAVE, format tag 3).
+"""
+import struct
+
+import numpy as np
+
+
+def save_wav(x, path, sample_rate):
+    data = np.asarray(x, dtype=np.float32).tobytes()
+    hdr = b'RIFF' + struct.pack('<I', 50 + len(data)) + b'WAVE'
+    hdr += b'fmt ' + struct.pack('<IHHIIHHH', 18, 3, 1, int(sample_rate), int(sample_rate) * 4, 4, 32, 0)
+    hdr += b'fact' + struct.pack('<II', 4, len(data) // 4)
+    hdr += b'data' + struct.pack('<I', len(data))
+    with open(str(path), 'wb') as f:
+        f.write(hdr + data)
+
+
+def load_wav(path):
+    """Read back a file written by `save_wav` -> (float32 array, sample_rate)."""
+    raw = open(str(path), 'rb').read()
+    assert raw[:4] == b'RIFF' and raw[8:12] == b'WAVE'
+    pos, rate, data = 12, None, None
+    while pos + 8 <= len(raw):
+        tag, size = raw[pos:pos + 4], struct.unpack('<I', raw[pos + 4:pos + 8])[0]
+        body = raw[pos + 8:pos + 8 + size]
+        if tag == b'fmt ':
+            rate = struct.unpack('<I', body[4:8])[0]
+        elif tag == b'data':
+            data = np.frombuffer(body, dtype=np.float32).copy()
+        pos += 8 + size + (size & 1)
+    return data, rate
