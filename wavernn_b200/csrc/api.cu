@@ -22,6 +22,7 @@ int fail(wrnn_handle *h, int code, const char *fmt, ...) {
     va_end(ap);
     if (h) h->err = buf;
     else g_create_err = buf;
+    if (code == WRNN_ERR_CUDA) cudaGetLastError();   // clear the sticky (non-fatal) error state
     return code;
 }
 

@@ -90,6 +90,46 @@ __device__ __forceinline__ float sum_q(const float *obuf, int m, int nq, int str
     return s;
 }
 
+
+// Stage one chunk of fold rows into smem: dst[f][0..ld) = [ main row (Kmain floats, written by other
+// CTAs this step -> .cg loads) | tail (ntail conditioning floats, read-only) | zero padding ].
+// One warp per fold row; all global loads of a row are issued before the first store so a fill
+// costs one L2 round trip instead of one per element.
+__device__ __forceinline__ void fill_rows(float *dst, int ld, int nb, const float *main_base, int Kmain,
+                                          const float *tail_base, int64_t tail_ld, int ntail, int warp, int lane) {
+    for (int f = warp; f < BT; f += FMA_WARPS) {
+        float *row = dst + (size_t)f * ld;
+        if (f >= nb) {
+            for (int k = lane; k < ld; k += 32) row[k] = 0.f;
+            continue;
+        }
+        const float *src = main_base + (size_t)f * Kmain;
+        if ((Kmain & 3) == 0) {
+            const float4 *s4 = reinterpret_cast<const float4 *>(src);
+            float4 *d4 = reinterpret_cast<float4 *>(row);
+            const int K4 = Kmain >> 2;
+            for (int base = 0; base < K4; base += 128) {
+                float4 v[4];
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const int i = base + j * 32 + lane;
+                    if (i < K4) v[j] = ld_cg4(s4 + i);
+                }
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const int i = base + j * 32 + lane;
+                    if (i < K4) d4[i] = v[j];
+                }
+            }
+        } else {
+            for (int k = lane; k < Kmain; k += 32) row[k] = ld_cg(src + k);
+        }
+        const float *tl = tail_base + (size_t)f * tail_ld;
+        for (int k = lane; k < ntail; k += 32) row[Kmain + k] = __ldg(tl + k);
+        for (int k = Kmain + ntail + lane; k < ld; k += 32) row[k] = 0.f;
+    }
+}
+
 __global__ void __launch_bounds__(FMA_THREADS, 1) fma_loop_kernel(const FmaParams P) {
     extern __shared__ __align__(16) float smem[];
     const Dims &d = P.d;
@@ -172,15 +212,23 @@ __global__ void __launch_bounds__(FMA_THREADS, 1) fma_loop_kernel(const FmaParam
             if (t == S) continue;     // the extra iteration only samples the last step
             __syncthreads();
             // x = [x_prev, m_t, a1_t]  (fatchord_version.py:208)
-            for (int i = tid; i < BT * P.KI; i += FMA_THREADS) {
-                const int f = i / P.KI, k = i % P.KI;
-                float v = 0.f;
-                if (f < nb) {
-                    const float *crow = P.a.cond + ((size_t)(b0 + f) * S + t) * (F + d.R);
-                    if (k == 0) v = xprev[f];
-                    else if (k <= F + A) v = __ldg(crow + k - 1);      // m_t then the first A aux channels
+            for (int f = warp; f < BT; f += FMA_WARPS) {
+                float *row = xbuf + (size_t)f * P.KI;
+                const float *crow = P.a.cond + ((size_t)(b0 + f) * S + t) * (F + d.R);
+                float v[4];
+#pragma unroll
+                for (int j = 0; j < 4; j++) {              // KI <= 128 covered in one batch, else loop below
+                    const int k = j * 32 + lane;
+                    v[j] = (f < nb && k >= 1 && k <= F + A) ? __ldg(crow + k - 1) : 0.f;
                 }
-                xbuf[i] = v;
+                if (lane == 0 && f < nb) v[0] = xprev[f];
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const int k = j * 32 + lane;
+                    if (k < P.KI) row[k] = v[j];
+                }
+                for (int k = 128 + lane; k < P.KI; k += 32)
+                    row[k] = (f < nb && k <= F + A) ? __ldg(crow + k - 1) : 0.f;
             }
             __syncthreads();
             if (nu > 0) {
@@ -215,20 +263,10 @@ __global__ void __launch_bounds__(FMA_THREADS, 1) fma_loop_kernel(const FmaParam
             for (int ch = 0; ch < nchunks; ch++) {
                 const int64_t b0 = (int64_t)ch * BT;
                 const int nb = (int)min((int64_t)BT, B - b0);
-                for (int i = tid; i < BT * Kin; i += FMA_THREADS) {
-                    const int f = i / Kin, k = i % Kin;
-                    float v = 0.f;
-                    if (f < nb) {
-                        if (k < H) v = ld_cg(xin + (size_t)(b0 + f) * H + k);
-                        else if (layer == 1 && k < H + A)
-                            v = __ldg(P.a.cond + ((size_t)(b0 + f) * S + t) * (F + d.R) + aoff + (k - H));
-                    }
-                    xbuf[i] = v;
-                }
-                for (int i = tid; i < BT * P.KH; i += FMA_THREADS) {
-                    const int f = i / P.KH, k = i % P.KH;
-                    hbuf[i] = (f < nb && k < H) ? ld_cg(hcur + (size_t)(b0 + f) * H + k) : 0.f;
-                }
+                fill_rows(xbuf, Kin, nb, xin + (size_t)b0 * H, H,
+                          P.a.cond + ((size_t)b0 * S + t) * (F + d.R) + aoff, (int64_t)S * (F + d.R),
+                          layer == 1 ? A : 0, warp, lane);
+                fill_rows(hbuf, P.KH, nb, hcur + (size_t)b0 * H, H, P.a.cond, 0, 0, warp, lane);
                 __syncthreads();
                 if (nu > 0) {
                     if (tid == 0) {
@@ -271,16 +309,8 @@ __global__ void __launch_bounds__(FMA_THREADS, 1) fma_loop_kernel(const FmaParam
             for (int ch = 0; ch < nchunks; ch++) {
                 const int64_t b0 = (int64_t)ch * BT;
                 const int nb = (int)min((int64_t)BT, B - b0);
-                for (int i = tid; i < BT * Kin; i += FMA_THREADS) {
-                    const int f = i / Kin, k = i % Kin;
-                    float v = 0.f;
-                    if (f < nb) {
-                        if (k < Kmain) v = ld_cg(xin + (size_t)(b0 + f) * Kmain + k);
-                        else if (k < Kmain + A)
-                            v = __ldg(P.a.cond + ((size_t)(b0 + f) * S + t) * (F + d.R) + aoff + (k - Kmain));
-                    }
-                    xbuf[i] = v;
-                }
+                fill_rows(xbuf, Kin, nb, xin + (size_t)b0 * Kmain, Kmain,
+                          P.a.cond + ((size_t)b0 * S + t) * (F + d.R) + aoff, (int64_t)S * (F + d.R), A, warp, lane);
                 __syncthreads();
                 if (nf1 > 0) {
                     if (tid == 0)
@@ -305,10 +335,7 @@ __global__ void __launch_bounds__(FMA_THREADS, 1) fma_loop_kernel(const FmaParam
             const int64_t b0 = (int64_t)ch * BT;
             const int nb = (int)min((int64_t)BT, B - b0);
             if (nc3 > 0) {      // CTA-uniform
-                for (int i = tid; i < BT * P.KF; i += FMA_THREADS) {
-                    const int f = i / P.KF, k = i % P.KF;
-                    xbuf[i] = (f < nb && k < FC) ? ld_cg(P.y2 + (size_t)(b0 + f) * FC + k) : 0.f;
-                }
+                fill_rows(xbuf, P.KF, nb, P.y2 + (size_t)b0 * FC, FC, P.a.cond, 0, 0, warp, lane);
                 if (tid == 0)
                     jobs[0] = MatJob{reinterpret_cast<const float4 *>(wimg + P.off_f3), reinterpret_cast<const float4 *>(xbuf),
                                      P.KF / 4, P.KF / 4, P.KF / 4, nc3};
@@ -470,6 +497,8 @@ int fma_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
     WRNN_CUDA(h, cudaMemsetAsync(h->ws_sync.p, 0, 64, st));
     P.gs.counter = (unsigned long long *)h->ws_sync.p;
     P.gs.abort_flag = (int *)((char *)h->ws_sync.p + 16);
+    // the attribute is per function, not per handle: another handle (other dims) may have changed it
+    WRNN_CUDA(h, cudaFuncSetAttribute(fma_loop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem_bytes));
     void *args[] = {(void *)&P};
     WRNN_CUDA(h, cudaLaunchCooperativeKernel((const void *)fma_loop_kernel, dim3(p.G), dim3(FMA_THREADS), args,
                                              p.smem_bytes, st));
