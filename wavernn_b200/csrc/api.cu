@@ -67,6 +67,7 @@ int ensure_packed_public(wrnn_handle *h) {
     WRNN_CUDA(h, cudaSetDevice(h->device));
     WRNN_TRY(pack_cond(h));
     WRNN_TRY(fma_plan(h));
+    WRNN_TRY(pipe_plan(h));
     h->packed = true;
     return 0;
 }
@@ -124,11 +125,11 @@ void wrnn_destroy(wrnn_handle *h) {
     cudaSetDevice(h->device);
     Workspace *all[] = {&h->ws_mel, &h->ws_up, &h->ws_res, &h->ws_cond, &h->ws_samples, &h->ws_picks, &h->ws_out,
                         &h->ws_noise, &h->ws_meta, &h->ws_tables, &h->ws_sync, &h->ws_act, &h->ws_tmp0, &h->ws_tmp1,
-                        &h->ws_teacher, &h->ws_logits};
+                        &h->ws_teacher, &h->ws_logits, &h->ws_prof};
     for (Workspace *w : all)
         if (w->p) cudaFree(w->p);
     float *ptrs[] = {h->cp.conv_in_t, h->cp.bn_scale, h->cp.bn_shift, h->cp.res_t, h->cp.conv_out_t, h->cp.conv_out_b,
-                     h->fma.image};
+                     h->fma.image, h->pipe.row_image, h->pipe.tail_image};
     for (float *p : ptrs)
         if (p) cudaFree(p);
     for (int i = 0; i < 8; i++)
@@ -205,7 +206,8 @@ int64_t wrnn_num_folds(int64_t total_len, int64_t target, int64_t overlap) {
 const char *wrnn_loop_kernel_name(wrnn_handle *h, int64_t folds) {
     (void)folds;
     if (!h) return "none";
-    return "fma";
+    if (h->force_kernel != 1 && !h->packed && !h->w.empty()) ensure_packed_public(h);
+    return (h->force_kernel != 1 && pipe_supported(h)) ? "fma-pipelined" : "fma";
 }
 
 int wrnn_set_loop_kernel(wrnn_handle *h, int32_t which) {

@@ -218,7 +218,29 @@ int do_run(wrnn_handle *h, uint64_t seed, cudaStream_t st, const StageOpts &o) {
     a.samples = (float *)h->ws_samples.p;
     a.picks = (int32_t *)h->ws_picks.p;
     a.seed = seed;
-    WRNN_TRY(fma_run(h, a, st));
+    a.Btot = h->B;
+    a.b0 = 0;
+    WRNN_TRY(ws_reserve(h, h->ws_sync, 128));
+    WRNN_CUDA(h, cudaMemsetAsync(h->ws_sync.p, 0, 128, st));      // barrier counter + abort flag
+    if (h->force_kernel != 1 && pipe_supported(h)) {
+        // the pipelined kernel takes fold groups of <= 20 (folds are independent: any grouping is exact)
+        const int64_t cap = pipe_max_folds(), ng = (h->B + cap - 1) / cap, per = (h->B + ng - 1) / ng;
+        const size_t CW = (size_t)(d.F + d.R);
+        for (int64_t b0 = 0; b0 < h->B; b0 += per) {
+            LoopArgs g = a;
+            g.B = std::min<int64_t>(per, h->B - b0);
+            g.b0 = b0;
+            g.cond = a.cond + (size_t)b0 * h->S * CW;
+            g.fold_len = a.fold_len + b0;
+            g.samples = a.samples + (size_t)b0 * h->S;
+            g.picks = a.picks + (size_t)b0 * h->S;
+            if (a.teacher) g.teacher = a.teacher + (size_t)b0 * h->S;
+            if (a.logits_out) g.logits_out = a.logits_out + (size_t)b0 * h->S * d.NC;
+            WRNN_TRY(pipe_run(h, g, st));
+        }
+    } else {
+        WRNN_TRY(fma_run(h, a, st));
+    }
     WRNN_CUDA(h, cudaEventRecord(h->ev[2], st));
     // float64 tail (:243-258)
     if (!o.want_logits) {
@@ -237,10 +259,10 @@ int do_run(wrnn_handle *h, uint64_t seed, cudaStream_t st, const StageOpts &o) {
 int check_abort(wrnn_handle *h, cudaStream_t st) {
     int flag = 0;
     if (h->ws_sync.p) {
-        WRNN_CUDA(h, cudaMemcpyAsync(&flag, (char *)h->ws_sync.p + 16, sizeof(int), cudaMemcpyDeviceToHost, st));
+        WRNN_CUDA(h, cudaMemcpyAsync(&flag, (char *)h->ws_sync.p + 64, sizeof(int), cudaMemcpyDeviceToHost, st));
         WRNN_CUDA(h, cudaStreamSynchronize(st));
     }
-    if (flag) return fail(h, WRNN_ERR_CUDA, "per-sample loop kernel aborted: grid barrier watchdog fired");
+    if (flag) return fail(h, WRNN_ERR_CUDA, "per-sample loop kernel aborted: exchange watchdog fired");
     return 0;
 }
 

@@ -42,9 +42,22 @@ struct FmaPlan {
     size_t smem_bytes = 0;
 };
 
+// ---- per-sample loop, phase-pipelined kernel (loop_pipe.cu) -----------------------------------
+struct PipePlan {
+    bool ok = false;           // dims supported and images built
+    int G = 0, NR = 0, NT = 0, upc = 0, rF = 0;
+    int Kc = 0, ldc = 0, KH = 0, ldh = 0, KX1 = 0, ldx1 = 0, KX2 = 0, ldx2 = 0, ldx = 0, KF = 0, ldf3 = 0;
+    int off_Wc = 0, off_w0 = 0, off_hh1 = 0, off_ih2 = 0, off_hh2 = 0, off_f1 = 0, off_f2 = 0, off_bias = 0;
+    int img_floats = 0, tail_floats = 0;
+    float *row_image = nullptr;    // device [NR][img_floats]
+    float *tail_image = nullptr;   // device fc3 rows + bias
+    size_t smem_bytes = 0;
+};
+
 struct LoopArgs {
     const float *cond;         // [B][S][F+R]
     int64_t B, S;
+    int64_t Btot, b0;          // fold count of the whole call and this launch's first fold (noise / Philox addressing)
     const int32_t *fold_len;   // [B] steps valid per fold (== S when batched)
     const float *u1, *u2, *q;  // injected noise or null
     const float *teacher;      // [B][S] or null
@@ -72,6 +85,7 @@ struct wrnn_handle {
     bool packed = false;
     wrnn::CondPack cp;
     wrnn::FmaPlan fma;
+    wrnn::PipePlan pipe;
     int force_kernel = 0;
     std::vector<double> lut_override;   // host-supplied mu-law table (wrnn_set_mulaw_lut)
     bool sparse = false;
@@ -85,7 +99,7 @@ struct wrnn_handle {
     bool have_noise = false;
 
     wrnn::Workspace ws_mel, ws_up, ws_res, ws_cond, ws_samples, ws_picks, ws_out, ws_noise,
-        ws_meta, ws_tables, ws_sync, ws_act, ws_tmp0, ws_tmp1, ws_teacher, ws_logits;
+        ws_meta, ws_tables, ws_sync, ws_act, ws_tmp0, ws_tmp1, ws_teacher, ws_logits, ws_prof;
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
     int64_t launches = 0;
     double *h_pinned_out = nullptr;
@@ -139,6 +153,12 @@ int launch_mulaw(wrnn_handle *h, const float *y, int64_t n, int mu, const double
 // loop_fma.cu
 int fma_plan(wrnn_handle *h);
 int fma_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st);
+
+// loop_pipe.cu
+int pipe_plan(wrnn_handle *h);
+bool pipe_supported(const wrnn_handle *h);
+int pipe_max_folds();
+int pipe_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st);
 
 // host tables (api.cu)
 void host_linspace(double start, double stop, int64_t n, double *out);

@@ -493,10 +493,10 @@ int fma_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
     P.y1 = P.x2 + BH; P.y2 = P.y1 + BF;
     P.h1 = P.y2 + BF; P.h2 = P.h1 + 2 * BH;
     P.logits = P.h2 + 2 * BH;
-    WRNN_TRY(ws_reserve(h, h->ws_sync, 64));
-    WRNN_CUDA(h, cudaMemsetAsync(h->ws_sync.p, 0, 64, st));
+    WRNN_TRY(ws_reserve(h, h->ws_sync, 128));
+    WRNN_CUDA(h, cudaMemsetAsync(h->ws_sync.p, 0, 16, st));          // the abort flag is cleared once per run
     P.gs.counter = (unsigned long long *)h->ws_sync.p;
-    P.gs.abort_flag = (int *)((char *)h->ws_sync.p + 16);
+    P.gs.abort_flag = (int *)((char *)h->ws_sync.p + 64);
     // the attribute is per function, not per handle: another handle (other dims) may have changed it
     WRNN_CUDA(h, cudaFuncSetAttribute(fma_loop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem_bytes));
     void *args[] = {(void *)&P};
