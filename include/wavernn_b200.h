@@ -135,9 +135,10 @@ int wrnn_xfade_tables(int64_t overlap, double *fade_in, double *fade_out);
  * samples, mels (n_seq, feat_dims, S/hop + 2*pad) ALREADY padded -> logits (n_seq, S, n_classes). */
 int wrnn_forward_logits(wrnn_handle *h, const float *x, const float *mels, int32_t n_seq, int64_t S,
                         float *logits);
-/* Which loop kernel the next run will use, for reports: "fma", "mma", "sparse". */
+/* Which loop kernel the next run will use, for reports: "fma", "fma-pipelined", "fma-resident". */
 const char *wrnn_loop_kernel_name(wrnn_handle *h, int64_t folds);
-/* Force a loop kernel: 0 = auto (mma when folds >= 16 and dims are the default ones), 1 = fma. */
+/* Force a loop kernel: 0 = auto (fastest kernel that supports the dims), 1 = fma (grid-barrier kernel, any dims and
+ * fold count, reference order of operations), 2 = fma-pipelined (tagged exchange, shared-memory weights). */
 int wrnn_set_loop_kernel(wrnn_handle *h, int32_t which);
 
 /* ------------------------------------------------------------------ deepmind variant */

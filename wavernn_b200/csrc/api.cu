@@ -61,6 +61,15 @@ static int64_t num_folds(int64_t total_len, int64_t target, int64_t overlap) {
     return n;
 }
 
+int loop_kernel_choice(const wrnn_handle *h) {
+    const int f = h->force_kernel;
+    if (f == 1) return 1;
+    if (f == 2) return pipe_supported(h) ? 2 : 1;
+    if (res_supported(h)) return 3;
+    if (pipe_supported(h)) return 2;
+    return 1;
+}
+
 int ensure_packed_public(wrnn_handle *h) {
     if (h->packed) return 0;
     if (h->w.empty()) return fail(h, WRNN_ERR_STATE, "weights not loaded: call wrnn_load_weights first");
@@ -68,6 +77,7 @@ int ensure_packed_public(wrnn_handle *h) {
     WRNN_TRY(pack_cond(h));
     WRNN_TRY(fma_plan(h));
     WRNN_TRY(pipe_plan(h));
+    WRNN_TRY(res_plan(h));
     h->packed = true;
     return 0;
 }
@@ -129,7 +139,7 @@ void wrnn_destroy(wrnn_handle *h) {
     for (Workspace *w : all)
         if (w->p) cudaFree(w->p);
     float *ptrs[] = {h->cp.conv_in_t, h->cp.bn_scale, h->cp.bn_shift, h->cp.res_t, h->cp.conv_out_t, h->cp.conv_out_b,
-                     h->fma.image, h->pipe.row_image, h->pipe.tail_image};
+                     h->fma.image, h->pipe.row_image, h->pipe.tail_image, h->res.img, h->res.tail_img};
     for (float *p : ptrs)
         if (p) cudaFree(p);
     for (int i = 0; i < 8; i++)
@@ -206,8 +216,9 @@ int64_t wrnn_num_folds(int64_t total_len, int64_t target, int64_t overlap) {
 const char *wrnn_loop_kernel_name(wrnn_handle *h, int64_t folds) {
     (void)folds;
     if (!h) return "none";
-    if (h->force_kernel != 1 && !h->packed && !h->w.empty()) ensure_packed_public(h);
-    return (h->force_kernel != 1 && pipe_supported(h)) ? "fma-pipelined" : "fma";
+    if (!h->packed && !h->w.empty()) ensure_packed_public(h);
+    const int k = loop_kernel_choice(h);
+    return k == 3 ? "fma-resident" : (k == 2 ? "fma-pipelined" : "fma");
 }
 
 int wrnn_set_loop_kernel(wrnn_handle *h, int32_t which) {

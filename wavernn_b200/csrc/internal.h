@@ -54,6 +54,15 @@ struct PipePlan {
     size_t smem_bytes = 0;
 };
 
+// ---- per-sample loop, register-resident warp-specialised kernel (loop_res.cu) ----------------
+struct ResPlan {
+    bool ok = false;
+    int G = 0;
+    float *img = nullptr;          // device [128][IMG_FLOATS]
+    float *tail_img = nullptr;     // device fc3 rows + bias
+    size_t smem_bytes = 0;
+};
+
 struct LoopArgs {
     const float *cond;         // [B][S][F+R]
     int64_t B, S;
@@ -86,6 +95,7 @@ struct wrnn_handle {
     wrnn::CondPack cp;
     wrnn::FmaPlan fma;
     wrnn::PipePlan pipe;
+    wrnn::ResPlan res;
     int force_kernel = 0;
     std::vector<double> lut_override;   // host-supplied mu-law table (wrnn_set_mulaw_lut)
     bool sparse = false;
@@ -159,6 +169,15 @@ int pipe_plan(wrnn_handle *h);
 bool pipe_supported(const wrnn_handle *h);
 int pipe_max_folds();
 int pipe_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st);
+
+// loop_res.cu
+int res_plan(wrnn_handle *h);
+bool res_supported(const wrnn_handle *h);
+int res_max_folds();
+int res_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st);
+// which loop kernel a run will use: 1 = fma (grid barriers, any dims, any fold count), 2 = pipelined
+// (smem weights, tagged exchange), 3 = resident (register weights, default dims)
+int loop_kernel_choice(const wrnn_handle *h);
 
 // host tables (api.cu)
 void host_linspace(double start, double stop, int64_t n, double *out);

@@ -28,6 +28,7 @@
 
 #include "internal.h"
 #include "loop_common.cuh"
+#include "exchange.cuh"
 
 namespace wrnn {
 
@@ -68,42 +69,6 @@ struct PipeParams {
         }                                                                   \
     } while (0)
 
-// ---------------------------------------------------------------------------- PTX access helpers
-__device__ __forceinline__ uint4 ld_relaxed_v4(const void *p) {
-    uint4 v;
-    asm volatile("ld.relaxed.gpu.global.v4.u32 {%0,%1,%2,%3}, [%4];"
-                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ uint32_t ld_relaxed_u32(const void *p) {
-    uint32_t v;
-    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ unsigned long long ld_relaxed_u64(const void *p) {
-    unsigned long long v;
-    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ void st_relaxed_v4(void *p, uint4 v) {
-    asm volatile("st.relaxed.gpu.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
-}
-__device__ __forceinline__ void st_relaxed_u32(void *p, uint32_t v) {
-    asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ void st_relaxed_u64(void *p, unsigned long long v) {
-    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
-
-__device__ __forceinline__ uint32_t tag_word(float v, uint32_t tag) {      // round to 22 bits, insert tag
-    return ((__float_as_uint(v) + 2u) & ~3u) | tag;
-}
-__device__ __forceinline__ float untag(uint32_t w) { return __uint_as_float(w & ~3u); }
-__device__ __forceinline__ bool tags_ok(const uint4 &v, uint32_t tag) {
-    return (((v.x ^ tag) | (v.y ^ tag) | (v.z ^ tag) | (v.w ^ tag)) & 3u) == 0u;
-}
-
-constexpr long long WATCHDOG_CLOCKS = 4000000000ll;     // ~2 s: a lost exchange becomes an error, not a hang
 
 // Gather a tagged vector src[nrow][K] (K % 4 == 0) into smem dst[row][0..K) with row stride ld.
 // Every thread owns float4 slots tid, tid + PT, ...; it probes its first slot until valid, then reads

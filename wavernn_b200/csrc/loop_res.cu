@@ -1,0 +1,821 @@
+// Per-sample loop, register-resident warp-specialised fp32 kernel ("resident"): the fast path at the
+// reference's vocoder dims (rnn 512, fc 512, aux 32 -- every hparams file of the reference uses them).
+// One persistent cooperative launch runs all S steps of `generate`'s hot loop
+// (models/fatchord_version.py:201-241) for a group of <= 20 folds.
+//
+// Weights never move: every thread keeps its share of the matrices in REGISTERS for the whole call
+// (128 row CTAs x 512 threads x <= 64 weights), so the FMA pipe only reads activations from shared
+// memory (0.67 B per FMA) and all of shared memory is free for the gathered activations.
+//
+// CTA roles: 128 "row" CTAs own 4 units of both GRUs and 4 rows of fc1/fc2; the remaining SMs are
+// "tail" CTAs that own whole folds (fc3 + sampling).  Inside a row CTA four 128-thread groups run
+// concurrently and synchronise through named barriers only where data is handed over:
+//   GA  rnn2 input product on h1(t), rnn2 gates          -> publishes h2(t), x2'(t) = h1 + h2
+//   GB  waits x_prev(t), rnn1 gates -> publishes h1(t);   then W_hh1 . h1(t) for step t+1 (shadow)
+//   GC  W_hh2 . h2(t) for step t+1 (shadow) and the conditioning part of rnn2's input side
+//   GD  fc1 on x2'(t) -> publishes y1(t); fc2 on y1(t) -> publishes y2(t)
+// The residual adds of the reference (x = x + h1, x = x + h2, :212,216) are folded into the weights:
+// with xI = W_I [x_prev; m_t; a1_t] + b_I,
+//   rnn1 input side  = (W_ih1 W_I) [x_prev; m; a1] + ...          (as in loop_pipe.cu)
+//   rnn2 input side  = W_ih2a h1 + (W_ih2a W_I) [x_prev; m; a1] + W_ih2b a2 + ...
+//   fc1              = W_f1a (h1 + h2) + (W_f1a W_I) [x_prev; m; a1] + W_f1b a3 + ...
+// so only h1, h2, h1+h2, y1, y2 are exchanged (4 x 40 KB per row CTA per step instead of 6) and every
+// product with the conditioning features is computed one step ahead.  Composed matrices are formed on
+// the host in double.  Exchange protocol: tagged words through L2, see exchange.cuh / loop_pipe.cu.
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "internal.h"
+#include "loop_common.cuh"
+#include "exchange.cuh"
+
+namespace wrnn {
+
+constexpr int RTH = 512;         // threads per CTA
+constexpr int RB = 20;           // folds per launch
+constexpr int RH = 512;          // rnn_dims == fc_dims
+constexpr int RNR = 128;         // row CTAs (4 units each)
+constexpr int RU = 4;
+constexpr int CB1 = 128, CB2 = 160, CB3 = 192;   // conditioning row strides in smem (zero padded)
+
+// per-row-CTA weight image in global memory (floats)
+constexpr int IMG_IH2 = 0;                        // [12][512]  W_ih2[:, :512]   rows gate-major (g*4 + u)
+constexpr int IMG_HH1 = IMG_IH2 + 12 * RH;        // [12][512]
+constexpr int IMG_HH2 = IMG_HH1 + 12 * RH;        // [12][512]
+constexpr int IMG_F1 = IMG_HH2 + 12 * RH;         // [4][512]   fc1[:, :512]
+constexpr int IMG_F2 = IMG_F1 + 4 * RH;           // [4][512]   fc2[:, :512]
+constexpr int IMG_C1 = IMG_F2 + 4 * RH;           // [12][128]  (W_ih1 W_I)[:, 1:]            cols (m, a1)
+constexpr int IMG_C2 = IMG_C1 + 12 * CB1;         // [12][160]  (W_ih2a W_I)[:, 1:] | W_ih2b  cols (m, a1, a2)
+constexpr int IMG_C3 = IMG_C2 + 12 * CB2;         // [4][192]   (W_f1a W_I)[:, 1:] | W_f1b | W_f2b   cols (m, a1, a3, a4)
+constexpr int IMG_W0 = IMG_C3 + 4 * CB3;          // [32] column 0 (x_prev): i1[12] i2[12] f1[4] pad[4]
+constexpr int IMG_B = IMG_W0 + 32;                // [64] biases: i1[12] i2[12] f1[4] f2[4] hh1[12] hh2[12] pad
+constexpr int IMG_FLOATS = IMG_B + 64;
+
+struct ResParams {
+    Dims d;
+    int B, FG, NT, Kc;           // folds, fold groups of 5, tail CTAs, F + A
+    int64_t S;
+    const float *img;            // [128][IMG_FLOATS]
+    const float *tail_img;       // [32][512] fc3 rows (zero padded) | bias[32]
+    LoopArgs a;
+    float *h1, *h2, *x2, *y1, *y2;           // [2][B][512] tagged words
+    unsigned long long *xprev;               // [2][RB]
+    int *abort_flag;
+    long long *prof;
+};
+
+// shared memory carve (floats)
+constexpr int SM_H1 = 0;                          // [20][512] h1(t)            (GA + GB)
+constexpr int SM_H2 = SM_H1 + RB * RH;            // [20][512] h2(t)            (GC)
+constexpr int SM_X = SM_H2 + RB * RH;             // [20][512] x2'(t) / y1(t)   (GD)
+constexpr int SM_CB1 = SM_X + RB * RH;            // [20][128]
+constexpr int SM_CB2 = SM_CB1 + RB * CB1;         // [20][160]
+constexpr int SM_CB3 = SM_CB2 + RB * CB2;         // [20][192]
+constexpr int SM_RED = SM_CB3 + RB * CB3;         // [4 groups][4 warps][4 fold groups][32]
+constexpr int SM_PRE = SM_RED + 4 * 512;          // pre_h1[12][20] pre_h2 pre_i1 pre_i2 (240 each) pre_f1[4][20] pre_f2 (80 each)
+constexpr int SM_HST = SM_PRE + 4 * 240 + 2 * 80; // hst1[4][20] hst2[4][20]
+constexpr int SM_XP = SM_HST + 160;               // xpA[32] xpB[32] xpD[32]
+constexpr int SM_WC = SM_XP + 96;                 // conditioning matrices C1 [12][128] C2 [12][160] C3 [4][192]
+constexpr int SM_WCN = 12 * CB1 + 12 * CB2 + 4 * CB3;
+constexpr int SM_PROF = SM_WC + SM_WCN;           // [4 groups][8] 64-bit clock accumulators (debug)
+constexpr int SM_FLOATS = SM_PROF + 64;
+
+// ---------------------------------------------------------------------------- polling with a sticky abort
+struct Dead {
+    bool dead;
+    const int *flag;
+    int *flag_w;
+};
+__device__ __forceinline__ bool poll_giveup(Dead &dd, long long t0, unsigned &spins) {
+    if ((++spins & 255u) != 0u) return false;
+    if (clock64() - t0 > WATCHDOG_CLOCKS) { atomicExch(dd.flag_w, 1); dd.dead = true; return true; }
+    if (ld_volatile_s32(dd.flag)) { dd.dead = true; return true; }
+    return false;
+}
+
+// Gather src[n4 float4] (tagged words) into dst (dense smem) with `nth` threads; thread `ti` owns slots
+// ti, ti + nth, ...  With 128 float4 per fold and nth a multiple of 128 every slot of a thread is the same
+// float4 column, i.e. comes from ONE producer CTA (one 16-byte store per fold).  So the thread polls its
+// first slot through registers until that producer's tag shows up, then fetches the rest with cp.async.cg
+// (L2 -> smem, no registers held, all in flight at once), and validates them from smem; a slot that lost
+// the race is re-polled through registers.  Tag bits stay in the words (see tag_word).
+__device__ __forceinline__ void cp_async16(void *smem_dst, const void *gsrc) {
+    const uint32_t s = (uint32_t)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ uint4 poll_slot(const uint4 *p, uint32_t tag, Dead &dd) {
+    uint4 v = ld_relaxed_v4(p);
+    if (!dd.dead && !tags_ok(v, tag)) {
+        const long long t0 = clock64();
+        unsigned spins = 0;
+        do {
+            v = ld_relaxed_v4(p);
+        } while (!tags_ok(v, tag) && !poll_giveup(dd, t0, spins));
+    }
+    return v;
+}
+__device__ __forceinline__ void gather_group(const float *src, int n4, float *dst, uint32_t tag, int nth, int ti, Dead &dd) {
+    if (ti >= n4) return;
+    const uint4 *s4 = reinterpret_cast<const uint4 *>(src);
+    uint4 *d4 = reinterpret_cast<uint4 *>(dst);
+    d4[ti] = poll_slot(s4 + ti, tag, dd);
+    for (int i = ti + nth; i < n4; i += nth) cp_async16(d4 + i, s4 + i);
+    asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
+    for (int i = ti + nth; i < n4; i += nth)
+        if (!tags_ok(d4[i], tag)) d4[i] = poll_slot(s4 + i, tag, dd);
+}
+
+__device__ __forceinline__ float poll_xprev(const unsigned long long *slot, uint32_t want, Dead &dd) {
+    unsigned long long v = ld_relaxed_u64(slot);
+    if (!dd.dead && (uint32_t)(v >> 32) != want) {
+        const long long t0 = clock64();
+        unsigned spins = 0;
+        do {
+            v = ld_relaxed_u64(slot);
+        } while ((uint32_t)(v >> 32) != want && !poll_giveup(dd, t0, spins));
+    }
+    return __uint_as_float((uint32_t)v);
+}
+
+// Copy conditioning columns [c0, c0 + n) of step t (n % 4 == 0) of every fold into dst[f][d0 ...].
+__device__ __forceinline__ void load_cond(const float *cond_t, int64_t fold_stride, int B, int c0, int n, float *dst,
+                                          int ld, int d0, int nth, int ti) {
+    const int n4 = n >> 2;
+    for (int i = ti; i < B * n4; i += nth) {
+        const int f = i / n4, k4 = i - f * n4;
+        const float4 v = __ldg(reinterpret_cast<const float4 *>(cond_t + (size_t)f * fold_stride + c0) + k4);
+        *reinterpret_cast<float4 *>(dst + (size_t)f * ld + d0 + 4 * k4) = v;
+    }
+}
+
+// ---------------------------------------------------------------------------- jobs on register weights
+// 12 rows x 512 over 128 threads: warp wq = (row half rg, K half kw); lane owns float4 columns
+// kw*64 + lane and kw*64 + 32 + lane of 6 rows.  Five folds at a time: 30 partial sums per lane are
+// reduce-scattered over the warp (lane l ends with the sum of index l = fold*6 + row) and stored.
+struct GruW {
+    float4 a[6], b[6];
+};
+__device__ __forceinline__ void load_gru_w(GruW &w, const float *img, int wq, int lane) {
+    const int rg = wq >> 1, kw = wq & 1;
+    const float4 *p = reinterpret_cast<const float4 *>(img);
+#pragma unroll
+    for (int i = 0; i < 6; i++) {
+        w.a[i] = __ldg(p + (size_t)(rg * 6 + i) * (RH / 4) + kw * 64 + lane);
+        w.b[i] = __ldg(p + (size_t)(rg * 6 + i) * (RH / 4) + kw * 64 + 32 + lane);
+    }
+}
+__device__ __forceinline__ void gru_job(const GruW &w, const float *buf, int FG, float *red, int wq, int lane) {
+    const int kw = wq & 1;
+    const float4 *x4 = reinterpret_cast<const float4 *>(buf) + kw * 64 + lane;
+    for (int fg = 0; fg < FG; fg++) {
+        float v[32];
+        v[30] = v[31] = 0.f;
+#pragma unroll
+        for (int fl = 0; fl < 5; fl++) {
+            const float4 xa = x4[(fg * 5 + fl) * (RH / 4)], xb = x4[(fg * 5 + fl) * (RH / 4) + 32];
+#pragma unroll
+            for (int i = 0; i < 6; i++) {
+                float s = w.a[i].x * xa.x;
+                s = fmaf(w.a[i].y, xa.y, s);
+                s = fmaf(w.a[i].z, xa.z, s);
+                s = fmaf(w.a[i].w, xa.w, s);
+                s = fmaf(w.b[i].x, xb.x, s);
+                s = fmaf(w.b[i].y, xb.y, s);
+                s = fmaf(w.b[i].z, xb.z, s);
+                s = fmaf(w.b[i].w, xb.w, s);
+                v[fl * 6 + i] = s;
+            }
+        }
+        warp_reduce_scatter<32>(v, lane);
+        red[(wq * 4 + fg) * 32 + lane] = v[0];
+    }
+}
+// sum of gate row r (0..11), fold f over the two K halves (fixed order)
+__device__ __forceinline__ float gru_out(const float *red, int r, int f) {
+    const int rg = r / 6, i = r - rg * 6, fg = f / 5, fl = f - fg * 5;
+    return red[((rg * 2 + 0) * 4 + fg) * 32 + fl * 6 + i] + red[((rg * 2 + 1) * 4 + fg) * 32 + fl * 6 + i];
+}
+
+// 4 rows x 512 over 128 threads: thread owns float4 column tg of all 4 rows.
+struct FcW {
+    float4 r[4];
+};
+__device__ __forceinline__ void load_fc_w(FcW &w, const float *img, int tg) {
+    const float4 *p = reinterpret_cast<const float4 *>(img);
+#pragma unroll
+    for (int i = 0; i < 4; i++) w.r[i] = __ldg(p + (size_t)i * (RH / 4) + tg);
+}
+__device__ __forceinline__ void fc_job(const FcW &w, const float *buf, int FG, float *red, int wq, int lane, int tg) {
+    const float4 *x4 = reinterpret_cast<const float4 *>(buf) + tg;
+    for (int fg = 0; fg < FG; fg++) {
+        float v[32];
+#pragma unroll
+        for (int i = 20; i < 32; i++) v[i] = 0.f;
+#pragma unroll
+        for (int fl = 0; fl < 5; fl++) {
+            const float4 x = x4[(fg * 5 + fl) * (RH / 4)];
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                float s = w.r[i].x * x.x;
+                s = fmaf(w.r[i].y, x.y, s);
+                s = fmaf(w.r[i].z, x.z, s);
+                s = fmaf(w.r[i].w, x.w, s);
+                v[fl * 4 + i] = s;
+            }
+        }
+        warp_reduce_scatter<32>(v, lane);
+        red[(wq * 4 + fg) * 32 + lane] = v[0];
+    }
+}
+__device__ __forceinline__ float fc_out(const float *red, int r, int f) {
+    const int fg = f / 5, fl = f - fg * 5, idx = fl * 4 + r;
+    float s = red[(0 * 4 + fg) * 32 + idx];
+    s += red[(1 * 4 + fg) * 32 + idx];
+    s += red[(2 * 4 + fg) * 32 + idx];
+    s += red[(3 * 4 + fg) * 32 + idx];
+    return s;
+}
+
+// Conditioning job: warp wq owns rows 3*wq .. 3*wq+2 of a [12][ld] matrix, lane owns columns lane + 32*j
+// (j < NJ).  pre[row][f] = sum + bias for every fold (60 partials per lane, reduce-scatter of 64).
+template <int NJ>
+struct CondW {
+    float w[3][NJ];
+};
+template <int NJ>
+__device__ __forceinline__ void cond_job(const float *wsm, const float *cb, int ld, int B, const float *bias, float *pre,
+                                         int wq, int lane) {
+    CondW<NJ> c;                                     // transient: the conditioning matrices live in smem
+#pragma unroll
+    for (int i = 0; i < 3; i++)
+#pragma unroll
+        for (int j = 0; j < NJ; j++) c.w[i][j] = wsm[(3 * wq + i) * ld + lane + 32 * j];
+#pragma unroll
+    for (int half = 0; half < 2; half++) {          // ten folds at a time: 30 partials per lane
+        float v[32];
+        v[30] = v[31] = 0.f;
+#pragma unroll
+        for (int fl = 0; fl < 10; fl++) {
+            const int f = half * 10 + fl;
+            float x[NJ];
+#pragma unroll
+            for (int j = 0; j < NJ; j++) x[j] = cb[f * ld + lane + 32 * j];
+#pragma unroll
+            for (int i = 0; i < 3; i++) {
+                float s = c.w[i][0] * x[0];
+#pragma unroll
+                for (int j = 1; j < NJ; j++) s = fmaf(c.w[i][j], x[j], s);
+                v[fl * 3 + i] = s;
+            }
+        }
+        warp_reduce_scatter<32>(v, lane);
+        const int fl = lane / 3, i = lane - 3 * fl, f = half * 10 + fl;
+        if (lane < 30 && f < B) pre[(3 * wq + i) * RB + f] = v[0] + bias[3 * wq + i];
+    }
+}
+
+// ---------------------------------------------------------------------------- tail CTA: fc3 + sampling
+__device__ __forceinline__ float mol_sample_smem2(const float *logits, int nmix, float myu1, float u2, int lane, int *pick) {
+    float t = -INFINITY;
+    if (lane < nmix) t = logits[lane] - logf(-logf(myu1));
+    int idx = lane;
+#pragma unroll
+    for (int o = 16; o >= 1; o >>= 1) {
+        const float ot = __shfl_xor_sync(0xffffffffu, t, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
+        if (ot > t || (ot == t && oi < idx)) { t = ot; idx = oi; }
+    }
+    const float mean = logits[nmix + idx];
+    const float ls = fmaxf(logits[2 * nmix + idx], -32.23619130191664f);   // log(1e-14)
+    float x = mean + expf(ls) * (logf(u2) - logf(1.f - u2));
+    x = fminf(fmaxf(x, -1.f), 1.f);
+    *pick = idx;
+    return x;
+}
+
+__device__ void res_tail_role(const ResParams &P, int j, float *smem) {
+    const Dims &d = P.d;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int NC = d.NC, B = P.B;
+    const int64_t S = P.a.S;
+    if (j >= B) return;
+    float *ybuf = smem;              // [512]
+    float *lg = smem + RH;           // [32]
+    // fc3 rows 2*warp, 2*warp + 1 (zero rows beyond NC); lane owns float4 columns lane + 32*q
+    float4 w3[2][4];
+    float b3[2];
+#pragma unroll
+    for (int r = 0; r < 2; r++) {
+        const int row = 2 * warp + r;
+#pragma unroll
+        for (int q = 0; q < 4; q++) w3[r][q] = __ldg(reinterpret_cast<const float4 *>(P.tail_img) + (size_t)row * (RH / 4) + lane + 32 * q);
+        b3[r] = __ldg(P.tail_img + 32 * RH + row);
+    }
+    const uint2 key = make_uint2((uint32_t)P.a.seed, (uint32_t)(P.a.seed >> 32));
+    const int nmix = NC / 3;
+    const int64_t Bt = P.a.Btot, b0 = P.a.b0;
+    Dead dd{false, P.abort_flag, P.abort_flag};
+    const bool prof_on = P.prof != nullptr && j == 0 && tid == 0;
+    long long pacc[4] = {0, 0, 0, 0}, pt = clock64();
+
+    for (int64_t t = 0; t <= S; t++) {
+        for (int f = j; f < B; f += P.NT) {
+            float xv = 0.f;
+            int pick = 0;
+            if (t > 0) {
+                const int64_t tp = t - 1, b = b0 + f;
+                // noise for this draw first: it does not depend on y2 (utils/distribution.py:106,118 draw order)
+                float myu1 = 0.5f, u2 = 0.5f;
+                if (warp == 0 && d.mode == WRNN_MODE_MOL) {
+                    if (P.a.u1) {
+                        if (lane < nmix) myu1 = P.a.u1[((size_t)tp * Bt + b) * nmix + lane];
+                        u2 = P.a.u2[(size_t)tp * Bt + b];
+                    } else {
+                        const uint4 r = philox4x32(make_uint4((uint32_t)tp, (uint32_t)b, (uint32_t)(lane >> 2), 1u), key);
+                        const uint32_t rr[4] = {r.x, r.y, r.z, r.w};
+                        myu1 = u_clip(rr[lane & 3]);
+                        const uint4 r2 = philox4x32(make_uint4((uint32_t)tp, (uint32_t)b, 0u, 2u), key);
+                        u2 = u_clip(r2.x);
+                    }
+                }
+                if (tid < RH / 4)
+                    gather_group(P.y2 + ((size_t)(tp & 1) * B + f) * RH, RH / 4, ybuf, (uint32_t)((tp + 1) & 3), RH / 4, tid, dd);
+                __syncthreads();
+                if (prof_on) { const long long n = clock64(); pacc[0] += n - pt; pt = n; }
+                float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+                for (int q = 0; q < 4; q++) {
+                    const float4 y = reinterpret_cast<const float4 *>(ybuf)[lane + 32 * q];
+                    s0 = fmaf(w3[0][q].x, y.x, s0); s0 = fmaf(w3[0][q].y, y.y, s0);
+                    s0 = fmaf(w3[0][q].z, y.z, s0); s0 = fmaf(w3[0][q].w, y.w, s0);
+                    s1 = fmaf(w3[1][q].x, y.x, s1); s1 = fmaf(w3[1][q].y, y.y, s1);
+                    s1 = fmaf(w3[1][q].z, y.z, s1); s1 = fmaf(w3[1][q].w, y.w, s1);
+                }
+#pragma unroll
+                for (int o = 16; o >= 1; o >>= 1) {
+                    s0 += __shfl_xor_sync(0xffffffffu, s0, o);
+                    s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+                }
+                if (lane < 2) {
+                    const int row = 2 * warp + lane;
+                    const float v = lane == 0 ? s0 + b3[0] : s1 + b3[1];
+                    if (row < NC) {
+                        lg[row] = v;
+                        if (P.a.logits_out && tp < P.a.fold_len[f]) P.a.logits_out[((size_t)f * S + tp) * NC + row] = v;
+                    }
+                }
+                __syncthreads();
+                if (prof_on) { const long long n = clock64(); pacc[1] += n - pt; pt = n; }
+                if (warp == 0) {
+                    xv = mol_sample_smem2(lg, nmix, myu1, u2, lane, &pick);
+                    if (tp >= P.a.fold_len[f]) xv = 0.f;
+                    else if (lane == 0) {
+                        P.a.samples[(size_t)f * S + tp] = xv;
+                        P.a.picks[(size_t)f * S + tp] = pick;
+                    }
+                }
+            }
+            if (warp == 0 && lane == 0 && t < S) {
+                if (P.a.teacher) xv = P.a.teacher[(size_t)f * S + t];
+                st_relaxed_u64(P.xprev + (size_t)(t & 1) * RB + f,
+                               ((unsigned long long)(uint32_t)(t + 1) << 32) | (unsigned long long)__float_as_uint(xv));
+            }
+            if (prof_on) { const long long n = clock64(); pacc[2] += n - pt; pt = n; }
+        }
+    }
+    if (prof_on)
+        for (int i = 0; i < 4; i++) P.prof[16 + i] = pacc[i];
+}
+
+// ---------------------------------------------------------------------------- row CTA
+enum { BAR_A = 1, BAR_B = 2, BAR_C = 3, BAR_D = 4, BAR_H1 = 5, BAR_GC2GA = 6, BAR_H1FREE = 7, BAR_AJOB = 8 };
+
+// Lanes 4k..4k+3 hold the tagged words of the CTA's four units (rows) of one fold: lane 4k stores them as
+// ONE 16-byte word, which is exactly one gather slot of every consumer.  All lanes of the warp call this.
+__device__ __forceinline__ void publish4(float *dst, uint32_t w, int lane, bool active) {
+    const int b = lane & ~3;
+    uint4 v;
+    v.x = __shfl_sync(0xffffffffu, w, b);
+    v.y = __shfl_sync(0xffffffffu, w, b + 1);
+    v.z = __shfl_sync(0xffffffffu, w, b + 2);
+    v.w = __shfl_sync(0xffffffffu, w, b + 3);
+    if ((lane & 3) == 0 && active) st_relaxed_v4(dst, v);
+}
+
+#define RPROF(slot)                                                   \
+    do {                                                              \
+        if (prof_on) {                                                \
+            const long long n__ = clock64();                          \
+            pacc[slot] += n__ - pt;                                   \
+            pt = n__;                                                 \
+        }                                                             \
+    } while (0)
+
+__device__ void res_row_role(const ResParams &P, int cta, float *smem) {
+    const Dims &d = P.d;
+    const int tid = threadIdx.x, gid = tid >> 7, tg = tid & 127, wq = tg >> 5, lane = tid & 31;
+    const int B = P.B, FG = P.FG, Kc = P.Kc, F = d.F;
+    const int64_t S = P.a.S;
+    const int CW = F + d.R;
+    const int64_t cstride = S * CW;
+    const int u0 = cta * RU;
+    const float *img = P.img + (size_t)cta * IMG_FLOATS;
+
+    float *bufH1 = smem + SM_H1, *bufH2 = smem + SM_H2, *bufX = smem + SM_X;
+    float *cb1 = smem + SM_CB1, *cb2 = smem + SM_CB2, *cb3 = smem + SM_CB3;
+    float *red = smem + SM_RED + gid * 512;
+    float *pre_h1 = smem + SM_PRE, *pre_h2 = pre_h1 + 240, *pre_i1 = pre_h2 + 240, *pre_i2 = pre_i1 + 240,
+          *pre_f1 = pre_i2 + 240, *pre_f2 = pre_f1 + 80;
+    float *hst1 = smem + SM_HST, *hst2 = hst1 + 80;
+    float *xpA = smem + SM_XP, *xpB = xpA + 32, *xpD = xpB + 32;
+
+    for (int i = tid; i < SM_FLOATS; i += RTH) smem[i] = 0.f;
+    __syncthreads();
+    for (int i = tid; i < SM_WCN; i += RTH) smem[SM_WC + i] = __ldg(img + IMG_C1 + i);     // C1 | C2 | C3 are contiguous
+    const float *wc1 = smem + SM_WC, *wc2 = wc1 + 12 * CB1, *wc3 = wc2 + 12 * CB2;
+    __syncthreads();
+    Dead dd{false, P.abort_flag, P.abort_flag};
+    const float *w0 = img + IMG_W0, *bias = img + IMG_B;
+    const float *b_i1 = bias, *b_i2 = bias + 12, *b_f1 = bias + 24, *b_f2 = bias + 28, *b_hh1 = bias + 32, *b_hh2 = bias + 44;
+    const bool prof_on = P.prof != nullptr && cta == 0 && tg == 0;
+    long long *pacc = reinterpret_cast<long long *>(smem + SM_PROF) + gid * 8, pt = 0;
+
+    if (gid == 0) {
+        // ======================================================================== GA: rnn2
+        GruW w;
+        load_gru_w(w, img + IMG_IH2, wq, lane);
+        float w0r[3] = {0.f, 0.f, 0.f};
+        const int gu = tg & 3, gf = tg >> 2;                      // gate thread: unit gu (< 4), fold gf
+        const bool gate = gf < B;
+        for (int g = 0; g < 3; g++) w0r[g] = __ldg(w0 + 12 + g * RU + gu);
+        __syncthreads();                                          // prologue of all groups done
+        pt = clock64();
+        for (int64_t t = 0; t < S; t++) {
+            const uint32_t tag = (uint32_t)((t + 1) & 3);
+            const size_t par = (size_t)(t & 1);
+            if (tg < B) xpA[tg] = poll_xprev(P.xprev + par * RB + tg, (uint32_t)(t + 1), dd);
+            if (t > 0) bar_sync(BAR_H1FREE, 256);                  // GB finished reading h1(t-1)
+            RPROF(0);
+            gather_group(P.h1 + par * B * RH, B * (RH / 4), bufH1, tag, 256, tid, dd);
+            bar_sync(BAR_H1, 256);
+            RPROF(1);
+            gru_job(w, bufH1, FG, red, wq, lane);
+            bar_arrive(BAR_AJOB, 256);                             // GB may start its shadow job now
+            bar_sync(BAR_A, 128);
+            if (t > 0) bar_sync(BAR_GC2GA, 256);                   // pre_h2(t), pre_i2(t) written by GC
+            RPROF(2);
+            if (tg < 96) {                                         // warps 0-2 hold the 80 gate threads
+                uint32_t hw = tag, xw = tag;
+                if (gate) {
+                    const float xp = xpA[gf];
+                    const float ir = gru_out(red, 0 * RU + gu, gf) + fmaf(w0r[0], xp, pre_i2[(0 * RU + gu) * RB + gf]);
+                    const float iz = gru_out(red, 1 * RU + gu, gf) + fmaf(w0r[1], xp, pre_i2[(1 * RU + gu) * RB + gf]);
+                    const float in_ = gru_out(red, 2 * RU + gu, gf) + fmaf(w0r[2], xp, pre_i2[(2 * RU + gu) * RB + gf]);
+                    const float hn = gru_update(ir, iz, in_, pre_h2[(0 * RU + gu) * RB + gf], pre_h2[(1 * RU + gu) * RB + gf],
+                                                pre_h2[(2 * RU + gu) * RB + gf], hst2[gu * RB + gf]);
+                    hw = tag_word(hn, tag);
+                    const float hr = __uint_as_float(hw);          // the state IS the tagged word, everywhere
+                    hst2[gu * RB + gf] = hr;
+                    xw = tag_word(bufH1[gf * RH + u0 + gu] + hr, tag);     // h1 + h2 (residuals :212,216)
+                }
+                publish4(P.h2 + (par * B + gf) * RH + u0, hw, lane, gate);
+                publish4(P.x2 + (par * B + gf) * RH + u0, xw, lane, gate);
+            }
+            bar_sync(BAR_A, 128);                                  // red / bufH1 reads done before the next job
+            RPROF(3);
+        }
+    } else if (gid == 1) {
+        // ======================================================================== GB: rnn1
+        GruW w;
+        load_gru_w(w, img + IMG_HH1, wq, lane);
+        float w0r[3] = {0.f, 0.f, 0.f};
+        const int gu = tg & 3, gf = tg >> 2;
+        const bool gate = gf < B;
+        for (int g = 0; g < 3; g++) w0r[g] = __ldg(w0 + g * RU + gu);
+        for (int i = tg; i < 12 * RB; i += 128) pre_h1[i] = __ldg(b_hh1 + i / RB);      // h = 0 at t = 0 (:194)
+        load_cond(P.a.cond, cstride, B, 0, Kc, cb1, CB1, 0, 128, tg);
+        bar_sync(BAR_B, 128);
+        cond_job<4>(wc1, cb1, CB1, B, b_i1, pre_i1, wq, lane);
+        __syncthreads();
+        pt = clock64();
+        for (int64_t t = 0; t < S; t++) {
+            const uint32_t tag = (uint32_t)((t + 1) & 3);
+            const size_t par = (size_t)(t & 1);
+            if (tg < B) xpB[tg] = poll_xprev(P.xprev + par * RB + tg, (uint32_t)(t + 1), dd);
+            bar_sync(BAR_B, 128);
+            RPROF(0);
+            if (tg < 96) {
+                uint32_t hw = tag;
+                if (gate) {
+                    const float xp = xpB[gf];
+                    const float ir = fmaf(w0r[0], xp, pre_i1[(0 * RU + gu) * RB + gf]);
+                    const float iz = fmaf(w0r[1], xp, pre_i1[(1 * RU + gu) * RB + gf]);
+                    const float in_ = fmaf(w0r[2], xp, pre_i1[(2 * RU + gu) * RB + gf]);
+                    const float hn = gru_update(ir, iz, in_, pre_h1[(0 * RU + gu) * RB + gf], pre_h1[(1 * RU + gu) * RB + gf],
+                                                pre_h1[(2 * RU + gu) * RB + gf], hst1[gu * RB + gf]);
+                    hw = tag_word(hn, tag);
+                    hst1[gu * RB + gf] = __uint_as_float(hw);
+                }
+                publish4(P.h1 + (par * B + gf) * RH + u0, hw, lane, gate);
+            }
+            RPROF(1);
+            gather_group(P.h1 + par * B * RH, B * (RH / 4), bufH1, tag, 256, tid, dd);
+            bar_sync(BAR_H1, 256);
+            bar_sync(BAR_AJOB, 256);                               // the critical rnn2 product goes first
+            RPROF(2);
+            gru_job(w, bufH1, FG, red, wq, lane);
+            if (t + 1 < S) bar_arrive(BAR_H1FREE, 256);            // h1(t) no longer needed by this thread
+            bar_sync(BAR_B, 128);
+            for (int i = tg; i < 12 * RB; i += 128) {
+                const int r = i / RB, f = i - r * RB;
+                pre_h1[i] = gru_out(red, r, f) + b_hh1[r];
+            }
+            RPROF(3);
+            if (t + 1 < S) {
+                load_cond(P.a.cond + (size_t)(t + 1) * CW, cstride, B, 0, Kc, cb1, CB1, 0, 128, tg);
+                bar_sync(BAR_B, 128);
+                cond_job<4>(wc1, cb1, CB1, B, b_i1, pre_i1, wq, lane);
+            }
+            RPROF(4);
+        }
+    } else if (gid == 2) {
+        // ======================================================================== GC: W_hh2 . h2, rnn2 conditioning
+        GruW w;
+        load_gru_w(w, img + IMG_HH2, wq, lane);
+        for (int i = tg; i < 12 * RB; i += 128) pre_h2[i] = __ldg(b_hh2 + i / RB);
+        load_cond(P.a.cond, cstride, B, 0, Kc + 32, cb2, CB2, 0, 128, tg);
+        bar_sync(BAR_C, 128);
+        cond_job<5>(wc2, cb2, CB2, B, b_i2, pre_i2, wq, lane);
+        __syncthreads();
+        pt = clock64();
+        for (int64_t t = 0; t < S; t++) {
+            const uint32_t tag = (uint32_t)((t + 1) & 3);
+            const size_t par = (size_t)(t & 1);
+            if (t + 1 < S) load_cond(P.a.cond + (size_t)(t + 1) * CW, cstride, B, 0, Kc + 32, cb2, CB2, 0, 128, tg);
+            gather_group(P.h2 + par * B * RH, B * (RH / 4), bufH2, tag, 128, tg, dd);
+            bar_sync(BAR_C, 128);
+            RPROF(0);
+            gru_job(w, bufH2, FG, red, wq, lane);
+            bar_sync(BAR_C, 128);
+            // all rnn2 gate threads of this CTA have published h2(t), so pre_h2(t) / pre_i2(t) are dead
+            for (int i = tg; i < 12 * RB; i += 128) {
+                const int r = i / RB, f = i - r * RB;
+                pre_h2[i] = gru_out(red, r, f) + b_hh2[r];
+            }
+            if (t + 1 < S) {
+                cond_job<5>(wc2, cb2, CB2, B, b_i2, pre_i2, wq, lane);
+                bar_arrive(BAR_GC2GA, 256);
+            }
+            bar_sync(BAR_C, 128);
+            RPROF(1);
+        }
+    } else {
+        // ======================================================================== GD: fc1, fc2
+        FcW w1, w2;
+        load_fc_w(w1, img + IMG_F1, tg);
+        load_fc_w(w2, img + IMG_F2, tg);
+        // conditioning of fc1 (row wq, columns lane + 32 j of (m, a1, a3)) and of fc2 (a4)
+        const int er = tg & 3, ef = tg >> 2;                       // epilogue thread: row er (< 4), fold ef
+        const bool epi = ef < B;
+        const float w0f = __ldg(w0 + 24 + er);
+        auto cond34 = [&]() {
+            float c3[5], c4;
+#pragma unroll
+            for (int jj = 0; jj < 5; jj++) c3[jj] = wc3[wq * CB3 + lane + 32 * jj];
+            c4 = wc3[wq * CB3 + 160 + lane];
+            float v[32];
+#pragma unroll
+            for (int i = 20; i < 32; i++) v[i] = 0.f;
+#pragma unroll
+            for (int f = 0; f < RB; f++) {
+                float s = c3[0] * cb3[f * CB3 + lane];
+#pragma unroll
+                for (int jj = 1; jj < 5; jj++) s = fmaf(c3[jj], cb3[f * CB3 + lane + 32 * jj], s);
+                v[f] = s;
+            }
+            warp_reduce_scatter<32>(v, lane);
+            if (lane < B) pre_f1[wq * RB + lane] = v[0] + b_f1[wq];
+#pragma unroll
+            for (int f = 0; f < RB; f++) v[f] = c4 * cb3[f * CB3 + 160 + lane];
+#pragma unroll
+            for (int i = 20; i < 32; i++) v[i] = 0.f;
+            warp_reduce_scatter<32>(v, lane);
+            if (lane < B) pre_f2[wq * RB + lane] = v[0] + b_f2[wq];
+        };
+        auto load_cb3 = [&](int64_t t) {
+            const float *ct = P.a.cond + (size_t)t * CW;
+            load_cond(ct, cstride, B, 0, Kc, cb3, CB3, 0, 128, tg);                 // m, a1
+            load_cond(ct, cstride, B, Kc + 32, 32, cb3, CB3, Kc, 128, tg);          // a3
+            load_cond(ct, cstride, B, Kc + 64, 32, cb3, CB3, 160, 128, tg);         // a4
+        };
+        load_cb3(0);
+        bar_sync(BAR_D, 128);
+        cond34();
+        __syncthreads();
+        pt = clock64();
+        for (int64_t t = 0; t < S; t++) {
+            const uint32_t tag = (uint32_t)((t + 1) & 3);
+            const size_t par = (size_t)(t & 1);
+            if (tg < B) xpD[tg] = poll_xprev(P.xprev + par * RB + tg, (uint32_t)(t + 1), dd);
+            gather_group(P.x2 + par * B * RH, B * (RH / 4), bufX, tag, 128, tg, dd);
+            bar_sync(BAR_D, 128);
+            RPROF(0);
+            fc_job(w1, bufX, FG, red, wq, lane, tg);
+            bar_sync(BAR_D, 128);
+            if (tg < 96) {
+                uint32_t yw = tag;
+                if (epi) yw = tag_word(fmaxf(fc_out(red, er, ef) + fmaf(w0f, xpD[ef], pre_f1[er * RB + ef]), 0.f), tag);
+                publish4(P.y1 + (par * B + ef) * RH + u0, yw, lane, epi);
+            }
+            RPROF(1);
+            gather_group(P.y1 + par * B * RH, B * (RH / 4), bufX, tag, 128, tg, dd);
+            bar_sync(BAR_D, 128);
+            RPROF(2);
+            fc_job(w2, bufX, FG, red, wq, lane, tg);
+            bar_sync(BAR_D, 128);
+            if (tg < 96) {
+                uint32_t yw = tag;
+                if (epi) yw = tag_word(fmaxf(fc_out(red, er, ef) + pre_f2[er * RB + ef], 0.f), tag);
+                publish4(P.y2 + (par * B + ef) * RH + u0, yw, lane, epi);
+            }
+            RPROF(3);
+            if (t + 1 < S) {
+                load_cb3(t + 1);
+                bar_sync(BAR_D, 128);                              // also: epilogue reads of pre_f1/pre_f2 done
+                cond34();
+            }
+            bar_sync(BAR_D, 128);
+            RPROF(4);
+        }
+    }
+    if (prof_on)
+        for (int i = 0; i < 8; i++) P.prof[32 + gid * 8 + i] = pacc[i];
+}
+
+__global__ void __launch_bounds__(RTH, 1) res_loop_kernel(const ResParams P) {
+    extern __shared__ __align__(16) float smem[];
+    const int cta = blockIdx.x;
+    if (cta < RNR) res_row_role(P, cta, smem);
+    else res_tail_role(P, cta - RNR, smem);
+}
+
+// ============================================================================ host: plan + launch
+bool res_supported(const wrnn_handle *h) { return h->res.ok; }
+int res_max_folds() { return RB; }
+
+int res_plan(wrnn_handle *h) {
+    const Dims &d = h->d;
+    ResPlan &p = h->res;
+    p.ok = false;
+    const int Kc = d.F + d.A;
+    if (d.mode != WRNN_MODE_MOL || d.H != RH || d.FC != RH || d.A != 32 || Kc % 4 || Kc > 128 || d.NC > 32) return 0;
+    if (h->num_sms < RNR + 1) return 0;
+    p.G = h->num_sms;
+    p.smem_bytes = (size_t)SM_FLOATS * sizeof(float);
+    if (p.smem_bytes > h->smem_optin) return 0;
+
+    auto get = [&](const char *k, std::vector<int64_t> shape) -> const HostTensor * {
+        auto it = h->w.find(k);
+        if (it == h->w.end()) { fail(h, WRNN_ERR_STATE, "checkpoint key missing: %s", k); return nullptr; }
+        if (it->second.shape != shape) { fail(h, WRNN_ERR_ARG, "checkpoint key %s has the wrong shape", k); return nullptr; }
+        return &it->second;
+    };
+    const int H = d.H, FC = d.FC, NC = d.NC, A = d.A, KinI = 1 + Kc;
+    const HostTensor *WI = get("I.weight", {H, KinI}), *BI = get("I.bias", {H});
+    const HostTensor *W1i = get("rnn1.weight_ih_l0", {3 * H, H}), *W1h = get("rnn1.weight_hh_l0", {3 * H, H});
+    const HostTensor *B1i = get("rnn1.bias_ih_l0", {3 * H}), *B1h = get("rnn1.bias_hh_l0", {3 * H});
+    const HostTensor *W2i = get("rnn2.weight_ih_l0", {3 * H, H + A}), *W2h = get("rnn2.weight_hh_l0", {3 * H, H});
+    const HostTensor *B2i = get("rnn2.bias_ih_l0", {3 * H}), *B2h = get("rnn2.bias_hh_l0", {3 * H});
+    const HostTensor *F1 = get("fc1.weight", {FC, H + A}), *F1b = get("fc1.bias", {FC});
+    const HostTensor *F2 = get("fc2.weight", {FC, FC + A}), *F2b = get("fc2.bias", {FC});
+    const HostTensor *F3 = get("fc3.weight", {NC, FC}), *F3b = get("fc3.bias", {NC});
+    if (!WI || !BI || !W1i || !W1h || !B1i || !B1h || !W2i || !W2h || !B2i || !B2h || !F1 || !F1b || !F2 || !F2b ||
+        !F3 || !F3b)
+        return WRNN_ERR_STATE;
+
+    // Composition with the I layer in double: out[r][:] = sum_k M[r][k] * W_I[k][:],  outb[r] = sum_k M[r][k] * b_I[k]
+    auto compose = [&](const HostTensor *M, int rows, int ldm, std::vector<float> &out, std::vector<double> &outb) {
+        out.assign((size_t)rows * KinI, 0.f);
+        outb.assign(rows, 0.0);
+        std::vector<double> acc(KinI);
+        for (int r = 0; r < rows; r++) {
+            std::fill(acc.begin(), acc.end(), 0.0);
+            double bacc = 0.0;
+            const float *mr = M->v.data() + (size_t)r * ldm;
+            for (int k = 0; k < H; k++) {
+                const double m = mr[k];
+                const float *ir = WI->v.data() + (size_t)k * KinI;
+                for (int c = 0; c < KinI; c++) acc[c] += m * (double)ir[c];
+                bacc += m * (double)BI->v[k];
+            }
+            for (int c = 0; c < KinI; c++) out[(size_t)r * KinI + c] = (float)acc[c];
+            outb[r] = bacc;
+        }
+    };
+    std::vector<float> P1, P2, P3;
+    std::vector<double> q1, q2, q3;
+    compose(W1i, 3 * H, H, P1, q1);          // W_ih1 W_I
+    compose(W2i, 3 * H, H + A, P2, q2);      // W_ih2[:, :H] W_I
+    compose(F1, FC, H + A, P3, q3);          // fc1[:, :H] W_I
+
+    std::vector<float> img((size_t)RNR * IMG_FLOATS, 0.f);
+    for (int c = 0; c < RNR; c++) {
+        float *im = img.data() + (size_t)c * IMG_FLOATS;
+        float *w0 = im + IMG_W0, *bias = im + IMG_B;
+        for (int u = 0; u < RU; u++) {
+            const int unit = c * RU + u;
+            for (int g = 0; g < 3; g++) {
+                const int row = g * H + unit, lr = g * RU + u;
+                memcpy(im + IMG_IH2 + (size_t)lr * RH, W2i->v.data() + (size_t)row * (H + A), (size_t)H * sizeof(float));
+                memcpy(im + IMG_HH1 + (size_t)lr * RH, W1h->v.data() + (size_t)row * H, (size_t)H * sizeof(float));
+                memcpy(im + IMG_HH2 + (size_t)lr * RH, W2h->v.data() + (size_t)row * H, (size_t)H * sizeof(float));
+                memcpy(im + IMG_C1 + (size_t)lr * CB1, P1.data() + (size_t)row * KinI + 1, (size_t)Kc * sizeof(float));
+                memcpy(im + IMG_C2 + (size_t)lr * CB2, P2.data() + (size_t)row * KinI + 1, (size_t)Kc * sizeof(float));
+                memcpy(im + IMG_C2 + (size_t)lr * CB2 + Kc, W2i->v.data() + (size_t)row * (H + A) + H, (size_t)A * sizeof(float));
+                w0[lr] = P1[(size_t)row * KinI];
+                w0[12 + lr] = P2[(size_t)row * KinI];
+                bias[lr] = (float)(q1[row] + (double)B1i->v[row]);
+                bias[12 + lr] = (float)(q2[row] + (double)B2i->v[row]);
+                bias[32 + lr] = B1h->v[row];
+                bias[44 + lr] = B2h->v[row];
+            }
+            const int row = c * RU + u;       // fc rows
+            memcpy(im + IMG_F1 + (size_t)u * RH, F1->v.data() + (size_t)row * (H + A), (size_t)H * sizeof(float));
+            memcpy(im + IMG_F2 + (size_t)u * RH, F2->v.data() + (size_t)row * (FC + A), (size_t)FC * sizeof(float));
+            memcpy(im + IMG_C3 + (size_t)u * CB3, P3.data() + (size_t)row * KinI + 1, (size_t)Kc * sizeof(float));
+            memcpy(im + IMG_C3 + (size_t)u * CB3 + Kc, F1->v.data() + (size_t)row * (H + A) + H, (size_t)A * sizeof(float));
+            memcpy(im + IMG_C3 + (size_t)u * CB3 + 160, F2->v.data() + (size_t)row * (FC + A) + FC, (size_t)A * sizeof(float));
+            w0[24 + u] = P3[(size_t)row * KinI];
+            bias[24 + u] = (float)(q3[row] + (double)F1b->v[row]);
+            bias[28 + u] = F2b->v[row];
+        }
+    }
+    std::vector<float> timg((size_t)32 * RH + 32, 0.f);
+    for (int r = 0; r < NC; r++) {
+        memcpy(timg.data() + (size_t)r * RH, F3->v.data() + (size_t)r * FC, (size_t)FC * sizeof(float));
+        timg[(size_t)32 * RH + r] = F3b->v[r];
+    }
+    if (p.img) cudaFree(p.img);
+    if (p.tail_img) cudaFree(p.tail_img);
+    p.img = p.tail_img = nullptr;
+    WRNN_CUDA(h, cudaMalloc((void **)&p.img, img.size() * sizeof(float)));
+    WRNN_CUDA(h, cudaMemcpy(p.img, img.data(), img.size() * sizeof(float), cudaMemcpyHostToDevice));
+    WRNN_CUDA(h, cudaMalloc((void **)&p.tail_img, timg.size() * sizeof(float)));
+    WRNN_CUDA(h, cudaMemcpy(p.tail_img, timg.data(), timg.size() * sizeof(float), cudaMemcpyHostToDevice));
+    WRNN_CUDA(h, cudaFuncSetAttribute(res_loop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem_bytes));
+    p.ok = true;
+    return 0;
+}
+
+int res_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
+    const Dims &d = h->d;
+    const ResPlan &p = h->res;
+    if (a.B < 1 || a.B > RB) return fail(h, WRNN_ERR_ARG, "resident loop kernel takes 1..%d folds per launch", RB);
+    ResParams P;
+    P.d = d;
+    P.B = (int)a.B;
+    P.FG = (P.B + 4) / 5;
+    P.NT = p.G - RNR;
+    P.Kc = d.F + d.A;
+    P.S = a.S;
+    P.img = p.img;
+    P.tail_img = p.tail_img;
+    P.a = a;
+    const size_t BH = (size_t)a.B * RH;
+    const size_t act_floats = 2 * 5 * BH;
+    const size_t xprev_bytes = 2 * RB * sizeof(unsigned long long);
+    WRNN_TRY(ws_reserve(h, h->ws_act, act_floats * sizeof(float) + xprev_bytes + 256));
+    WRNN_CUDA(h, cudaMemsetAsync(h->ws_act.p, 0, act_floats * sizeof(float) + xprev_bytes + 256, st));
+    float *base = (float *)h->ws_act.p;
+    P.h1 = base; P.h2 = P.h1 + 2 * BH; P.x2 = P.h2 + 2 * BH; P.y1 = P.x2 + 2 * BH; P.y2 = P.y1 + 2 * BH;
+    P.xprev = (unsigned long long *)(((uintptr_t)(P.y2 + 2 * BH) + 63) & ~(uintptr_t)63);
+    WRNN_TRY(ws_reserve(h, h->ws_sync, 128));                        // cleared by the caller once per run
+    P.abort_flag = (int *)((char *)h->ws_sync.p + 64);
+    static const bool prof_env = getenv("WRNN_PROF") != nullptr;
+    P.prof = nullptr;
+    if (prof_env) {
+        WRNN_TRY(ws_reserve(h, h->ws_prof, 64 * sizeof(long long)));
+        WRNN_CUDA(h, cudaMemsetAsync(h->ws_prof.p, 0, 64 * sizeof(long long), st));
+        P.prof = (long long *)h->ws_prof.p;
+    }
+    WRNN_CUDA(h, cudaFuncSetAttribute(res_loop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem_bytes));
+    void *args[] = {(void *)&P};
+    WRNN_CUDA(h, cudaLaunchCooperativeKernel((const void *)res_loop_kernel, dim3(p.G), dim3(RTH), args, p.smem_bytes, st));
+    h->launches++;
+    if (prof_env) {      // debugging aid: per-segment clocks of row CTA 0's groups and tail CTA 0 (synchronises!)
+        long long pr[64];
+        WRNN_CUDA(h, cudaMemcpyAsync(pr, h->ws_prof.p, sizeof pr, cudaMemcpyDeviceToHost, st));
+        WRNN_CUDA(h, cudaStreamSynchronize(st));
+        const double s = (double)a.S;
+        fprintf(stderr, "[wrnn prof] clocks/step  GA: wait=%.0f gather_h1=%.0f job+sync=%.0f gates=%.0f | GB: wait_xprev=%.0f gates1=%.0f "
+                        "gather_h1=%.0f job+pre=%.0f cond=%.0f | GC: gather_h2=%.0f job+cond=%.0f | GD: gather_x2=%.0f fc1=%.0f "
+                        "gather_y1=%.0f fc2=%.0f cond=%.0f | tail: gather_y2=%.0f fc3=%.0f sample=%.0f\n",
+                pr[32] / s, pr[33] / s, pr[34] / s, pr[35] / s, pr[40] / s, pr[41] / s, pr[42] / s, pr[43] / s, pr[44] / s,
+                pr[48] / s, pr[49] / s, pr[56] / s, pr[57] / s, pr[58] / s, pr[59] / s, pr[60] / s, pr[16] / s, pr[17] / s,
+                pr[18] / s);
+    }
+    return 0;
+}
+
+}  // namespace wrnn
