@@ -228,8 +228,49 @@ int wrnn_set_loop_kernel(wrnn_handle *h, int32_t which) {
 }
 
 int wrnn_prune_16x1(wrnn_handle *h, float keep_fraction, float *masked_out) {
-    (void)keep_fraction; (void)masked_out;
-    return fail(h, WRNN_ERR_STATE, "block-sparse path not built yet");
+    // SURVEY.md §8a row S (the reference has no block-sparse code; nearest: per-gate magnitude pruning in
+    // notebooks/Pruning - Scratchpad.ipynb:92-108).  Per matrix and per gate (H-row split), blocks of 16
+    // consecutive output rows x 1 input column; keep round(keep_fraction * nblocks) blocks of largest L1 norm
+    // (ties: lower block index wins), zero the rest.
+    if (!h) return WRNN_ERR_ARG;
+    if (!(keep_fraction > 0.f) || keep_fraction > 1.f) return fail(h, WRNN_ERR_ARG, "keep_fraction must be in (0, 1]");
+    const int H = h->d.H;
+    if (H % 16) return fail(h, WRNN_ERR_ARG, "rnn_dims must be a multiple of 16 for 16x1 block pruning");
+    const char *keys[4] = {"rnn1.weight_ih_l0", "rnn1.weight_hh_l0", "rnn2.weight_ih_l0", "rnn2.weight_hh_l0"};
+    size_t out_off = 0;
+    for (int m = 0; m < 4; m++) {
+        auto it = h->w.find(keys[m]);
+        if (it == h->w.end() || it->second.shape.size() != 2 || it->second.shape[0] != 3 * H)
+            return fail(h, WRNN_ERR_STATE, "checkpoint key missing or misshapen: %s", keys[m]);
+        HostTensor &W = it->second;
+        const int64_t K = W.shape[1], nbr = H / 16, nblocks = nbr * K;
+        const int64_t keep = std::min<int64_t>(nblocks, std::max<int64_t>(1, (int64_t)floor((double)keep_fraction * (double)nblocks + 0.5)));
+        std::vector<std::pair<double, int64_t>> norm((size_t)nblocks);
+        for (int g = 0; g < 3; g++) {
+            float *base = W.v.data() + (size_t)g * H * K;
+            for (int64_t br = 0; br < nbr; br++)
+                for (int64_t c = 0; c < K; c++) {
+                    double s = 0.0;
+                    for (int r = 0; r < 16; r++) s += fabs((double)base[(size_t)(br * 16 + r) * K + c]);
+                    norm[(size_t)(br * K + c)] = {s, br * K + c};
+                }
+            std::vector<std::pair<double, int64_t>> sorted = norm;
+            std::sort(sorted.begin(), sorted.end(), [](const std::pair<double, int64_t> &a, const std::pair<double, int64_t> &b) {
+                return a.first > b.first || (a.first == b.first && a.second < b.second);
+            });
+            std::vector<char> keepmask((size_t)nblocks, 0);
+            for (int64_t i = 0; i < keep; i++) keepmask[(size_t)sorted[(size_t)i].second] = 1;
+            for (int64_t br = 0; br < nbr; br++)
+                for (int64_t c = 0; c < K; c++)
+                    if (!keepmask[(size_t)(br * K + c)])
+                        for (int r = 0; r < 16; r++) base[(size_t)(br * 16 + r) * K + c] = 0.f;
+        }
+        if (masked_out) memcpy(masked_out + out_off, W.v.data(), W.v.size() * sizeof(float));
+        out_off += W.v.size();
+    }
+    h->packed = false;
+    h->sparse = true;
+    return 0;
 }
 
 }  // extern "C"

@@ -78,14 +78,16 @@ constexpr int SM_HST = SM_PRE + 4 * 240 + 2 * 80; // hst1[4][20] hst2[4][20]
 constexpr int SM_XP = SM_HST + 160;               // xpA[32] xpB[32] xpD[32]
 constexpr int SM_WC = SM_XP + 96;                 // conditioning matrices C1 [12][128] C2 [12][160] C3 [4][192]
 constexpr int SM_WCN = 12 * CB1 + 12 * CB2 + 4 * CB3;
-constexpr int SM_PROF = SM_WC + SM_WCN;           // [4 groups][8] 64-bit clock accumulators (debug)
-constexpr int SM_FLOATS = SM_PROF + 64;
+constexpr int SM_W0B = SM_WC + SM_WCN;            // w0[32] | biases[64] (copy of the image tail)
+constexpr int SM_PROF = SM_W0B + 96;              // [4 groups][8] 64-bit clock accumulators (debug)
+constexpr int SM_FLOATS = SM_PROF + 64 + 16;
 
 // ---------------------------------------------------------------------------- polling with a sticky abort
 struct Dead {
     bool dead;
     const int *flag;
     int *flag_w;
+    unsigned int *cnt;      // debug counters in smem (null unless WRNN_PROF): [0] probe spins, [1] fallback slots, [2] fallback spins
 };
 __device__ __forceinline__ bool poll_giveup(Dead &dd, long long t0, unsigned &spins) {
     if ((++spins & 255u) != 0u) return false;
@@ -104,7 +106,7 @@ __device__ __forceinline__ void cp_async16(void *smem_dst, const void *gsrc) {
     const uint32_t s = (uint32_t)__cvta_generic_to_shared(smem_dst);
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gsrc) : "memory");
 }
-__device__ __forceinline__ uint4 poll_slot(const uint4 *p, uint32_t tag, Dead &dd) {
+__device__ __forceinline__ uint4 poll_slot(const uint4 *p, uint32_t tag, Dead &dd, int which = 0) {
     uint4 v = ld_relaxed_v4(p);
     if (!dd.dead && !tags_ok(v, tag)) {
         const long long t0 = clock64();
@@ -112,6 +114,7 @@ __device__ __forceinline__ uint4 poll_slot(const uint4 *p, uint32_t tag, Dead &d
         do {
             v = ld_relaxed_v4(p);
         } while (!tags_ok(v, tag) && !poll_giveup(dd, t0, spins));
+        if (dd.cnt) { atomicAdd(dd.cnt + which, spins); if (which) atomicAdd(dd.cnt + 1, 1u); }
     }
     return v;
 }
@@ -123,7 +126,7 @@ __device__ __forceinline__ void gather_group(const float *src, int n4, float *ds
     for (int i = ti + nth; i < n4; i += nth) cp_async16(d4 + i, s4 + i);
     asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
     for (int i = ti + nth; i < n4; i += nth)
-        if (!tags_ok(d4[i], tag)) d4[i] = poll_slot(s4 + i, tag, dd);
+        if (!tags_ok(d4[i], tag)) d4[i] = poll_slot(s4 + i, tag, dd, 2);
 }
 
 __device__ __forceinline__ float poll_xprev(const unsigned long long *slot, uint32_t want, Dead &dd) {
@@ -149,6 +152,20 @@ __device__ __forceinline__ void load_cond(const float *cond_t, int64_t fold_stri
     }
 }
 
+// Weight loads go through volatile asm: a plain (__ldg) load is pure, so under register pressure the
+// compiler re-issues it inside the step loop instead of keeping the value, which turns "register-resident"
+// into an L2 stream.  A volatile asm result can only be kept (or spilled; ptxas -v must show 0 spills).
+__device__ __forceinline__ float4 ld_keep4(const float4 *p) {
+    float4 v;
+    asm volatile("ld.global.nc.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ float ld_keep(const float *p) {
+    float v;
+    asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(v) : "l"(p));
+    return v;
+}
+
 // ---------------------------------------------------------------------------- jobs on register weights
 // 12 rows x 512 over 128 threads: warp wq = (row half rg, K half kw); lane owns float4 columns
 // kw*64 + lane and kw*64 + 32 + lane of 6 rows.  Five folds at a time: 30 partial sums per lane are
@@ -161,8 +178,8 @@ __device__ __forceinline__ void load_gru_w(GruW &w, const float *img, int wq, in
     const float4 *p = reinterpret_cast<const float4 *>(img);
 #pragma unroll
     for (int i = 0; i < 6; i++) {
-        w.a[i] = __ldg(p + (size_t)(rg * 6 + i) * (RH / 4) + kw * 64 + lane);
-        w.b[i] = __ldg(p + (size_t)(rg * 6 + i) * (RH / 4) + kw * 64 + 32 + lane);
+        w.a[i] = ld_keep4(p + (size_t)(rg * 6 + i) * (RH / 4) + kw * 64 + lane);
+        w.b[i] = ld_keep4(p + (size_t)(rg * 6 + i) * (RH / 4) + kw * 64 + 32 + lane);
     }
 }
 __device__ __forceinline__ void gru_job(const GruW &w, const float *buf, int FG, float *red, int wq, int lane) {
@@ -204,7 +221,7 @@ struct FcW {
 __device__ __forceinline__ void load_fc_w(FcW &w, const float *img, int tg) {
     const float4 *p = reinterpret_cast<const float4 *>(img);
 #pragma unroll
-    for (int i = 0; i < 4; i++) w.r[i] = __ldg(p + (size_t)i * (RH / 4) + tg);
+    for (int i = 0; i < 4; i++) w.r[i] = ld_keep4(p + (size_t)i * (RH / 4) + tg);
 }
 __device__ __forceinline__ void fc_job(const FcW &w, const float *buf, int FG, float *red, int wq, int lane, int tg) {
     const float4 *x4 = reinterpret_cast<const float4 *>(buf) + tg;
@@ -309,13 +326,13 @@ __device__ void res_tail_role(const ResParams &P, int j, float *smem) {
     for (int r = 0; r < 2; r++) {
         const int row = 2 * warp + r;
 #pragma unroll
-        for (int q = 0; q < 4; q++) w3[r][q] = __ldg(reinterpret_cast<const float4 *>(P.tail_img) + (size_t)row * (RH / 4) + lane + 32 * q);
-        b3[r] = __ldg(P.tail_img + 32 * RH + row);
+        for (int q = 0; q < 4; q++) w3[r][q] = ld_keep4(reinterpret_cast<const float4 *>(P.tail_img) + (size_t)row * (RH / 4) + lane + 32 * q);
+        b3[r] = ld_keep(P.tail_img + 32 * RH + row);
     }
     const uint2 key = make_uint2((uint32_t)P.a.seed, (uint32_t)(P.a.seed >> 32));
     const int nmix = NC / 3;
     const int64_t Bt = P.a.Btot, b0 = P.a.b0;
-    Dead dd{false, P.abort_flag, P.abort_flag};
+    Dead dd{false, P.abort_flag, P.abort_flag, nullptr};
     const bool prof_on = P.prof != nullptr && j == 0 && tid == 0;
     long long pacc[4] = {0, 0, 0, 0}, pt = clock64();
 
@@ -432,11 +449,11 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
 
     for (int i = tid; i < SM_FLOATS; i += RTH) smem[i] = 0.f;
     __syncthreads();
-    for (int i = tid; i < SM_WCN; i += RTH) smem[SM_WC + i] = __ldg(img + IMG_C1 + i);     // C1 | C2 | C3 are contiguous
+    for (int i = tid; i < SM_WCN + 96; i += RTH) smem[SM_WC + i] = __ldg(img + IMG_C1 + i);     // C1 | C2 | C3 | w0 | biases are contiguous
     const float *wc1 = smem + SM_WC, *wc2 = wc1 + 12 * CB1, *wc3 = wc2 + 12 * CB2;
     __syncthreads();
-    Dead dd{false, P.abort_flag, P.abort_flag};
-    const float *w0 = img + IMG_W0, *bias = img + IMG_B;
+    Dead dd{false, P.abort_flag, P.abort_flag, (P.prof != nullptr && cta == 0) ? reinterpret_cast<unsigned int *>(smem + SM_PROF + 64) + gid * 4 : nullptr};
+    const float *w0 = smem + SM_W0B, *bias = w0 + 32;
     const float *b_i1 = bias, *b_i2 = bias + 12, *b_f1 = bias + 24, *b_f2 = bias + 28, *b_hh1 = bias + 32, *b_hh2 = bias + 44;
     const bool prof_on = P.prof != nullptr && cta == 0 && tg == 0;
     long long *pacc = reinterpret_cast<long long *>(smem + SM_PROF) + gid * 8, pt = 0;
@@ -448,7 +465,7 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
         float w0r[3] = {0.f, 0.f, 0.f};
         const int gu = tg & 3, gf = tg >> 2;                      // gate thread: unit gu (< 4), fold gf
         const bool gate = gf < B;
-        for (int g = 0; g < 3; g++) w0r[g] = __ldg(w0 + 12 + g * RU + gu);
+        for (int g = 0; g < 3; g++) w0r[g] = w0[12 + g * RU + gu];
         __syncthreads();                                          // prologue of all groups done
         pt = clock64();
         for (int64_t t = 0; t < S; t++) {
@@ -461,8 +478,10 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
             bar_sync(BAR_H1, 256);
             RPROF(1);
             gru_job(w, bufH1, FG, red, wq, lane);
+            RPROF(4);
             bar_arrive(BAR_AJOB, 256);                             // GB may start its shadow job now
             bar_sync(BAR_A, 128);
+            RPROF(5);
             if (t > 0) bar_sync(BAR_GC2GA, 256);                   // pre_h2(t), pre_i2(t) written by GC
             RPROF(2);
             if (tg < 96) {                                         // warps 0-2 hold the 80 gate threads
@@ -492,8 +511,8 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
         float w0r[3] = {0.f, 0.f, 0.f};
         const int gu = tg & 3, gf = tg >> 2;
         const bool gate = gf < B;
-        for (int g = 0; g < 3; g++) w0r[g] = __ldg(w0 + g * RU + gu);
-        for (int i = tg; i < 12 * RB; i += 128) pre_h1[i] = __ldg(b_hh1 + i / RB);      // h = 0 at t = 0 (:194)
+        for (int g = 0; g < 3; g++) w0r[g] = w0[g * RU + gu];
+        for (int i = tg; i < 12 * RB; i += 128) pre_h1[i] = b_hh1[i / RB];      // h = 0 at t = 0 (:194)
         load_cond(P.a.cond, cstride, B, 0, Kc, cb1, CB1, 0, 128, tg);
         bar_sync(BAR_B, 128);
         cond_job<4>(wc1, cb1, CB1, B, b_i1, pre_i1, wq, lane);
@@ -543,7 +562,7 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
         // ======================================================================== GC: W_hh2 . h2, rnn2 conditioning
         GruW w;
         load_gru_w(w, img + IMG_HH2, wq, lane);
-        for (int i = tg; i < 12 * RB; i += 128) pre_h2[i] = __ldg(b_hh2 + i / RB);
+        for (int i = tg; i < 12 * RB; i += 128) pre_h2[i] = b_hh2[i / RB];
         load_cond(P.a.cond, cstride, B, 0, Kc + 32, cb2, CB2, 0, 128, tg);
         bar_sync(BAR_C, 128);
         cond_job<5>(wc2, cb2, CB2, B, b_i2, pre_i2, wq, lane);
@@ -578,7 +597,7 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
         // conditioning of fc1 (row wq, columns lane + 32 j of (m, a1, a3)) and of fc2 (a4)
         const int er = tg & 3, ef = tg >> 2;                       // epilogue thread: row er (< 4), fold ef
         const bool epi = ef < B;
-        const float w0f = __ldg(w0 + 24 + er);
+        const float w0f = w0[24 + er];
         auto cond34 = [&]() {
             float c3[5], c4;
 #pragma unroll
@@ -649,8 +668,10 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
             RPROF(4);
         }
     }
-    if (prof_on)
+    if (prof_on) {
         for (int i = 0; i < 8; i++) P.prof[32 + gid * 8 + i] = pacc[i];
+        for (int i = 0; i < 3; i++) P.prof[20 + gid * 3 + i] = dd.cnt[i];
+    }
 }
 
 __global__ void __launch_bounds__(RTH, 1) res_loop_kernel(const ResParams P) {
@@ -808,12 +829,14 @@ int res_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
         WRNN_CUDA(h, cudaMemcpyAsync(pr, h->ws_prof.p, sizeof pr, cudaMemcpyDeviceToHost, st));
         WRNN_CUDA(h, cudaStreamSynchronize(st));
         const double s = (double)a.S;
-        fprintf(stderr, "[wrnn prof] clocks/step  GA: wait=%.0f gather_h1=%.0f job+sync=%.0f gates=%.0f | GB: wait_xprev=%.0f gates1=%.0f "
+        fprintf(stderr, "[wrnn prof] clocks/step  GA: wait=%.0f gather_h1=%.0f (job=%.0f barA=%.0f) gc2ga=%.0f gates=%.0f | GB: wait_xprev=%.0f gates1=%.0f "
                         "gather_h1=%.0f job+pre=%.0f cond=%.0f | GC: gather_h2=%.0f job+cond=%.0f | GD: gather_x2=%.0f fc1=%.0f "
                         "gather_y1=%.0f fc2=%.0f cond=%.0f | tail: gather_y2=%.0f fc3=%.0f sample=%.0f\n",
-                pr[32] / s, pr[33] / s, pr[34] / s, pr[35] / s, pr[40] / s, pr[41] / s, pr[42] / s, pr[43] / s, pr[44] / s,
+                pr[32] / s, pr[33] / s, pr[36] / s, pr[37] / s, pr[34] / s, pr[35] / s, pr[40] / s, pr[41] / s, pr[42] / s, pr[43] / s, pr[44] / s,
                 pr[48] / s, pr[49] / s, pr[56] / s, pr[57] / s, pr[58] / s, pr[59] / s, pr[60] / s, pr[16] / s, pr[17] / s,
                 pr[18] / s);
+        fprintf(stderr, "[wrnn prof] per step, CTA 0 (probe spins, fallback slots, fallback spins): GA %.1f %.2f %.1f | GB %.1f %.2f %.1f | GC %.1f %.2f %.1f | GD %.1f %.2f %.1f\n",
+                pr[20] / s, pr[21] / s, pr[22] / s, pr[23] / s, pr[24] / s, pr[25] / s, pr[26] / s, pr[27] / s, pr[28] / s, pr[29] / s, pr[30] / s, pr[31] / s);
     }
     return 0;
 }
