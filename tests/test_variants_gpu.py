@@ -1,0 +1,114 @@
+"""GPU: the deepmind coarse/fine variant and the 16x1 block-pruned GRU against the oracle / golden fixtures.
+
+Integer outputs (coarse, fine, combined) are compared bit-exact under identical injected Exp(1) noise.
+The pruned model's oracle is the dense reference run on the masked weights.
+"""
+import numpy as np
+import pytest
+import torch
+
+from oracle import deepmind as odm
+from oracle import fatchord as ofc
+from wavernn_b200 import binding, synth
+from wavernn_b200.config import VocoderDims
+from wavernn_b200.deepmind_version import WaveRNN as DeepmindWaveRNN
+
+from common import CASES, case_inputs, golden
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize('name,hs,S', [('dm_small', 64, 300), ('dm_full', 896, 400)])
+def test_deepmind_vs_reference_fixture(name, hs, S):
+    sd = synth.synth_dm_state_dict(hs, 256, seed=0)
+    qc = synth.synth_noise_exp(S, 1, 256, seed=4321)
+    qf = synth.synth_noise_exp(S, 1, 256, seed=4322)
+    v = binding.DeepmindVocoder(hs, 256, device=0)
+    v.load_weights(sd)
+    out, c, f = v.generate(S, 1, qc, qf)
+    g = golden('deepmind')
+    assert out.dtype == np.int64 and out.shape == (1, S)
+    assert np.array_equal(c[0], g[name + '_coarse'])
+    assert np.array_equal(f[0], g[name + '_fine'])
+    assert np.array_equal(out[0], g[name + '_output'])
+    assert np.array_equal(out[0], c[0] * 256 + f[0] - 2 ** 15)          # combine_signal, utils/dsp.py:33-34
+
+
+def test_deepmind_many_sequences_vs_oracle():
+    hs, S, N = 64, 120, 11                      # 11 sequences: two launches (8 + 3)
+    sd = synth.synth_dm_state_dict(hs, 256, seed=3)
+    qc = synth.synth_noise_exp(S, N, 256, seed=11)
+    qf = synth.synth_noise_exp(S, N, 256, seed=12)
+    v = binding.DeepmindVocoder(hs, 256, device=0)
+    v.load_weights(sd)
+    out, c, f = v.generate(S, N, qc, qf)
+    o_out, o_c, o_f = odm.generate(ofc.to_torch(sd), S, qc, qf, n_seq=N)
+    assert np.array_equal(c, o_c) and np.array_equal(f, o_f) and np.array_equal(out, o_out)
+    # every sequence equals a single-sequence run with its own noise column
+    out1, c1, f1 = v.generate(S, 1, qc[:, 4:5], qf[:, 4:5])
+    assert np.array_equal(c1[0], c[4]) and np.array_equal(f1[0], f[4])
+
+
+def test_deepmind_module_contract_and_philox():
+    model = DeepmindWaveRNN(hidden_size=64, quantisation=256).cuda()
+    a = model.generate(200, seed=5)
+    b = model.generate(200, seed=5)
+    c = model.generate(200, seed=6)
+    assert len(a) == 3 and all(x.dtype == np.int64 and x.shape == (200,) for x in a)
+    assert all(np.array_equal(x, y) for x, y in zip(a, b)) and not np.array_equal(a[0], c[0])
+    assert a[1].min() >= 0 and a[1].max() <= 255 and a[2].min() >= 0 and a[2].max() <= 255
+    with pytest.raises(RuntimeError):
+        DeepmindWaveRNN(hidden_size=64).generate(10)                   # CPU module: no fallback
+
+
+def _mask_16x1(w, H, keep):
+    """numpy statement of SURVEY.md row S: per gate, 16x1 blocks, keep the top `keep` fraction by L1 norm."""
+    w = w.copy()
+    K = w.shape[1]
+    for g in range(3):
+        blk = w[g * H:(g + 1) * H].reshape(H // 16, 16, K)
+        norm = np.abs(blk.astype(np.float64)).sum(axis=1).reshape(-1)           # [block_row * K + col]
+        n_keep = min(norm.size, max(1, int(np.floor(keep * norm.size + 0.5))))
+        order = np.lexsort((np.arange(norm.size), -norm))
+        m = np.zeros(norm.size, dtype=bool)
+        m[order[:n_keep]] = True
+        blk *= m.reshape(H // 16, 1, K)
+    return w
+
+
+@pytest.mark.parametrize('name', ['tiny_mol_batched', 'full_mol_batched'])
+def test_pruned_16x1_vs_dense_oracle_on_masked_weights(name):
+    dims, sd, mel, noise, (T, batched, target, overlap, mu_law, B, S) = case_inputs(name)
+    v = binding.Vocoder(dims, device=0)
+    v.load_weights(sd)
+    masked = v.prune_16x1(0.1, want_masked=True)
+    H = dims.rnn_dims
+    sd2 = dict(sd)
+    for k, w in masked.items():
+        ref = _mask_16x1(sd[k], H, 0.1)
+        assert np.array_equal(w, ref), k
+        kept = (np.abs(w.reshape(3, H // 16, 16, -1)).sum(axis=2) > 0).mean()
+        assert abs(kept - 0.1) < 2e-3
+        sd2[k] = w
+    wave = v.generate([mel[0]], batched, target, overlap, mu_law, noise=noise)[0]
+    ref = ofc.generate(ofc.to_torch(sd2), dims, mel, batched, target, overlap, mu_law, noise)
+    assert wave.shape == ref.shape and np.abs(wave - ref).max() <= 2e-4
+    # loading weights again restores the dense model
+    v.load_weights(sd)
+    dense = v.generate([mel[0]], batched, target, overlap, mu_law, noise=noise)[0]
+    assert np.abs(dense - golden(name)['wave']).max() <= 2e-4
+
+
+@pytest.mark.parametrize('kernel', [1, 2])
+def test_all_loop_kernels_agree_with_fixture(kernel):
+    """The default kernel is covered by test_gpu_parity; force the grid-barrier and the pipelined kernels."""
+    name = 'full_mol_batched'
+    dims, sd, mel, noise, (T, batched, target, overlap, mu_law, B, S) = case_inputs(name)
+    v = binding.Vocoder(dims, device=0)
+    v.load_weights(sd)
+    v.set_loop_kernel(kernel)
+    assert v.loop_kernel_name(B) == {1: 'fma', 2: 'fma-pipelined'}[kernel]
+    wave = v.generate([mel[0]], batched, target, overlap, mu_law, noise=noise)[0]
+    assert np.abs(wave - golden(name)['wave']).max() <= 2e-4
+    v.set_loop_kernel(0)
+    assert v.loop_kernel_name(B) == 'fma-resident'

@@ -1,19 +1,477 @@
-// deepmind coarse/fine variant (models/deepmind_version.py:75-165) — placeholder until the kernel lands.
-#include "internal.h"
+// deepmind coarse/fine dual-softmax WaveRNN generation (models/deepmind_version.py:75-165) as one
+// persistent cooperative kernel: every SM keeps its rows of R, O1..O4 in shared memory for all steps;
+// the layers exchange through small L2-resident buffers separated by grid barriers (6 per step).
+//   A  R.hidden for the units this CTA owns (all three gates), coarse gates -> hidden_coarse       (:116-125)
+//   B  O1 + ReLU      C  O2 -> coarse logits                                                        (:128-129)
+//   D  softmax + Categorical sample of the coarse value (every CTA, redundantly), fine gates       (:130-145)
+//   E  O3 + ReLU      F  O4 -> fine logits; the fine sample is drawn at the start of the next step (:148-152)
+// The reference runs one sequence; `n_seq` independent sequences (<= 8 per launch) share the weights.
+#include <stdio.h>
+#include <string.h>
 
-struct wrnn_dm_handle { std::string err; };
+#include <map>
+#include <string>
+#include <vector>
+
+#include "internal.h"
+#include "loop_common.cuh"
+
+namespace wrnn {
+
+constexpr int DM_THREADS = 256, DM_WARPS = DM_THREADS / 32, DM_MAXN = 8;
+
+struct DmParams {
+    int H, S2, Q, N;             // hidden, hidden/2, quantisation, sequences in this launch
+    int upc, r1, r2;             // hidden units / O1,O3 rows / O2,O4 rows per CTA
+    int64_t T;                   // steps
+    int img_floats;
+    int off_R, off_O1, off_O2, off_O3, off_O4, off_I, off_b;
+    const float *image;          // [G][img_floats]
+    float *hidden;               // [2][N][H]
+    float *o1, *o3;              // [N][S2]
+    float *lc, *lf;              // [N][Q] coarse / fine logits
+    const float *qc, *qf;        // injected Exp(1) noise [T][Ntot][Q] or null
+    int64_t Ntot, n0;
+    int32_t *coarse, *fine;      // [N][T]
+    uint64_t seed;
+    GridSync gs;
+};
+
+// dot products of `nrows` smem rows (stride ld) with N smem vectors (stride ldx), one warp per row, K % 4 == 0
+template <int NMAX>
+__device__ __forceinline__ void warp_rows(const float *W, int ld, int K, const float *X, int ldx, int N, int lane, float (&out)[NMAX]) {
+    float acc[NMAX];
+#pragma unroll
+    for (int n = 0; n < NMAX; n++) acc[n] = 0.f;
+    const float4 *w4 = reinterpret_cast<const float4 *>(W);
+    for (int k4 = lane; k4 < (K >> 2); k4 += 32) {
+        const float4 w = w4[k4];
+#pragma unroll
+        for (int n = 0; n < NMAX; n++)
+            if (n < N) {
+                const float4 x = reinterpret_cast<const float4 *>(X + (size_t)n * ldx)[k4];
+                acc[n] = fmaf(w.x, x.x, acc[n]);
+                acc[n] = fmaf(w.y, x.y, acc[n]);
+                acc[n] = fmaf(w.z, x.z, acc[n]);
+                acc[n] = fmaf(w.w, x.w, acc[n]);
+            }
+    }
+#pragma unroll
+    for (int n = 0; n < NMAX; n++) {
+#pragma unroll
+        for (int o = 16; o >= 1; o >>= 1) acc[n] += __shfl_xor_sync(0xffffffffu, acc[n], o);
+        out[n] = acc[n];
+    }
+    (void)ld;
+}
+
+__device__ __forceinline__ void stage_cg(float *dst, const float *src, int n, int tid) {     // written by other CTAs
+    for (int i = tid; i < (n >> 2); i += DM_THREADS) reinterpret_cast<float4 *>(dst)[i] = __ldcg(reinterpret_cast<const float4 *>(src) + i);
+}
+
+__global__ void __launch_bounds__(DM_THREADS, 1) dm_loop_kernel(const DmParams P) {
+    extern __shared__ __align__(16) float smem[];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, cta = blockIdx.x;
+    const int H = P.H, S2 = P.S2, Q = P.Q, N = P.N;
+    float *wimg = smem;
+    float *xbuf = wimg + P.img_floats;               // [N][H] staged inputs
+    float *rsum = xbuf + (size_t)DM_MAXN * H;        // [upc][3][N] R.hidden of the owned units
+    float *lrow = rsum + (size_t)P.upc * 3 * DM_MAXN;   // [N][Q] staged logits
+    __shared__ int prev_c[DM_MAXN], prev_f[DM_MAXN], cur_c[DM_MAXN];
+    for (int i = tid; i < P.img_floats / 4; i += DM_THREADS)
+        reinterpret_cast<float4 *>(wimg)[i] = reinterpret_cast<const float4 *>(P.image + (size_t)cta * P.img_floats)[i];
+    if (tid < DM_MAXN) prev_c[tid] = prev_f[tid] = cur_c[tid] = 0;
+    __syncthreads();
+    const float *R = wimg + P.off_R, *O1 = wimg + P.off_O1, *O2 = wimg + P.off_O2, *O3 = wimg + P.off_O3, *O4 = wimg + P.off_O4;
+    const float *Iw = wimg + P.off_I;      // per unit: 3 gates x 3 input weights (coarse units use 2)
+    const float *bb = wimg + P.off_b;      // per unit: b_u, b_r, b_e | then O1 bias[r1] O2[r2] O3[r1] O4[r2]
+    const float *bO1 = bb + 3 * P.upc, *bO2 = bO1 + P.r1, *bO3 = bO2 + P.r2, *bO4 = bO3 + P.r1;
+    const int u0 = cta * P.upc, nu = max(0, min(P.upc, H - u0));
+    const int a0 = cta * P.r1, na = max(0, min(P.r1, S2 - a0));
+    const int c0 = cta * P.r2, nc = max(0, min(P.r2, Q - c0));
+    const uint2 key = make_uint2((uint32_t)P.seed, (uint32_t)(P.seed >> 32));
+    unsigned long long gen = 0;
+    float o[DM_MAXN];
+
+    for (int64_t t = 0; t <= P.T; t++) {
+        const float *hcur = P.hidden + (size_t)(t & 1) * N * H;
+        float *hnxt = P.hidden + (size_t)((t + 1) & 1) * N * H;
+        // ---- fine sample of step t-1 (every CTA draws the same value; CTA 0 records it)
+        if (t > 0) {
+            stage_cg(lrow, P.lf, N * Q, tid);
+            __syncthreads();
+            for (int n = warp; n < N; n += DM_WARPS) {
+                const float *qs = P.qf ? P.qf + ((size_t)(t - 1) * P.Ntot + P.n0 + n) * Q : nullptr;
+                const int k = categorical_warp(lrow + (size_t)n * Q, Q, qs, key, (uint32_t)(t - 1), (uint32_t)(P.n0 + n), 5u, lane);
+                if (lane == 0) {
+                    prev_f[n] = k;
+                    prev_c[n] = cur_c[n];
+                    if (cta == 0) P.fine[(size_t)n * P.T + t - 1] = k;
+                }
+            }
+            __syncthreads();
+        }
+        if (t == P.T) break;
+        // ---- A: R.hidden for owned units; coarse units update now
+        stage_cg(xbuf, hcur, N * H, tid);
+        __syncthreads();
+        for (int j = warp; j < 3 * nu; j += DM_WARPS) {
+            warp_rows<DM_MAXN>(R + (size_t)j * H, H, H, xbuf, H, N, lane, o);
+            if (lane == 0)
+                {
+#pragma unroll
+                for (int n = 0; n < DM_MAXN; n++) if (n < N) rsum[j * DM_MAXN + n] = o[n];
+            }        // j = u*3 + gate
+        }
+        __syncthreads();
+        for (int i = tid; i < nu * N; i += DM_THREADS) {
+            const int u = i / N, n = i - u * N, unit = u0 + u;
+            if (unit < S2) {
+                const float pc = (float)prev_c[n] / 127.5f - 1.f, pf = (float)prev_f[n] / 127.5f - 1.f;      // :106-108
+                const float *iw = Iw + u * 9;
+                const float Iu = iw[0] * pc + iw[1] * pf, Ir = iw[3] * pc + iw[4] * pf, Ie = iw[6] * pc + iw[7] * pf;
+                const float uu = sigmoidf_acc(rsum[(u * 3 + 0) * DM_MAXN + n] + Iu + bb[u * 3 + 0]);
+                const float rr = sigmoidf_acc(rsum[(u * 3 + 1) * DM_MAXN + n] + Ir + bb[u * 3 + 1]);
+                const float ee = tanhf(rr * rsum[(u * 3 + 2) * DM_MAXN + n] + Ie + bb[u * 3 + 2]);
+                hnxt[(size_t)n * H + unit] = uu * xbuf[n * H + unit] + (1.f - uu) * ee;                    // :125
+            }
+        }
+        grid_barrier(P.gs, gen);
+        // ---- B: O1 + ReLU on hidden_coarse
+        stage_cg(xbuf, hnxt, N * H, tid);          // only [:, :S2] is new; the rest is ignored
+        __syncthreads();
+        for (int j = warp; j < na; j += DM_WARPS) {
+            warp_rows<DM_MAXN>(O1 + (size_t)j * S2, S2, S2, xbuf, H, N, lane, o);
+            if (lane == 0)
+                {
+#pragma unroll
+                for (int n = 0; n < DM_MAXN; n++) if (n < N) P.o1[(size_t)n * S2 + a0 + j] = fmaxf(o[n] + bO1[j], 0.f);
+            }
+        }
+        grid_barrier(P.gs, gen);
+        // ---- C: O2 -> coarse logits
+        stage_cg(xbuf, P.o1, N * S2, tid);
+        __syncthreads();
+        for (int j = warp; j < nc; j += DM_WARPS) {
+            warp_rows<DM_MAXN>(O2 + (size_t)j * S2, S2, S2, xbuf, S2, N, lane, o);
+            if (lane == 0)
+                {
+#pragma unroll
+                for (int n = 0; n < DM_MAXN; n++) if (n < N) P.lc[(size_t)n * Q + c0 + j] = o[n] + bO2[j];
+            }
+        }
+        grid_barrier(P.gs, gen);
+        // ---- D: coarse sample (redundant), fine gates
+        stage_cg(lrow, P.lc, N * Q, tid);
+        stage_cg(xbuf, hcur, N * H, tid);          // previous hidden_fine for the fine update
+        __syncthreads();
+        for (int n = warp; n < N; n += DM_WARPS) {
+            const float *qs = P.qc ? P.qc + ((size_t)t * P.Ntot + P.n0 + n) * Q : nullptr;
+            const int k = categorical_warp(lrow + (size_t)n * Q, Q, qs, key, (uint32_t)t, (uint32_t)(P.n0 + n), 4u, lane);
+            if (lane == 0) {
+                cur_c[n] = k;
+                if (cta == 0) P.coarse[(size_t)n * P.T + t] = k;
+            }
+        }
+        __syncthreads();
+        for (int i = tid; i < nu * N; i += DM_THREADS) {
+            const int u = i / N, n = i - u * N, unit = u0 + u;
+            if (unit >= S2) {
+                const float pc = (float)prev_c[n] / 127.5f - 1.f, pf = (float)prev_f[n] / 127.5f - 1.f;
+                const float cc = (float)cur_c[n] / 127.5f - 1.f;                                          // :135
+                const float *iw = Iw + u * 9;
+                const float Iu = iw[0] * pc + iw[1] * pf + iw[2] * cc, Ir = iw[3] * pc + iw[4] * pf + iw[5] * cc,
+                            Ie = iw[6] * pc + iw[7] * pf + iw[8] * cc;
+                const float uu = sigmoidf_acc(rsum[(u * 3 + 0) * DM_MAXN + n] + Iu + bb[u * 3 + 0]);
+                const float rr = sigmoidf_acc(rsum[(u * 3 + 1) * DM_MAXN + n] + Ir + bb[u * 3 + 1]);
+                const float ee = tanhf(rr * rsum[(u * 3 + 2) * DM_MAXN + n] + Ie + bb[u * 3 + 2]);
+                hnxt[(size_t)n * H + unit] = uu * xbuf[n * H + unit] + (1.f - uu) * ee;                    // :145
+            }
+        }
+        grid_barrier(P.gs, gen);
+        // ---- E: O3 + ReLU on hidden_fine
+        stage_cg(xbuf, hnxt, N * H, tid);
+        __syncthreads();
+        for (int j = warp; j < na; j += DM_WARPS) {
+            warp_rows<DM_MAXN>(O3 + (size_t)j * S2, S2, S2, xbuf + S2, H, N, lane, o);
+            if (lane == 0)
+                {
+#pragma unroll
+                for (int n = 0; n < DM_MAXN; n++) if (n < N) P.o3[(size_t)n * S2 + a0 + j] = fmaxf(o[n] + bO3[j], 0.f);
+            }
+        }
+        grid_barrier(P.gs, gen);
+        // ---- F: O4 -> fine logits
+        stage_cg(xbuf, P.o3, N * S2, tid);
+        __syncthreads();
+        for (int j = warp; j < nc; j += DM_WARPS) {
+            warp_rows<DM_MAXN>(O4 + (size_t)j * S2, S2, S2, xbuf, S2, N, lane, o);
+            if (lane == 0)
+                {
+#pragma unroll
+                for (int n = 0; n < DM_MAXN; n++) if (n < N) P.lf[(size_t)n * Q + c0 + j] = o[n] + bO4[j];
+            }
+        }
+        grid_barrier(P.gs, gen);
+    }
+}
+
+}  // namespace wrnn
+
+// ============================================================================ host
+struct wrnn_dm_handle {
+    int hidden = 0, quant = 0, device = 0, num_sms = 0;
+    size_t smem_optin = 0;
+    std::string err;
+    std::map<std::string, wrnn::HostTensor> w;
+    bool packed = false;
+    wrnn::DmParams plan;         // layout fields only
+    float *image = nullptr;
+    size_t smem_bytes = 0;
+    void *ws = nullptr;
+    size_t ws_bytes = 0;
+    cudaEvent_t ev[2] = {nullptr, nullptr};
+    int64_t launches = 0;
+};
+
 static thread_local std::string g_dm_err;
 
+namespace wrnn {
+
+static int dm_fail(wrnn_dm_handle *h, int code, const char *msg) {
+    if (h) h->err = msg;
+    else g_dm_err = msg;
+    if (code == WRNN_ERR_CUDA) cudaGetLastError();
+    return code;
+}
+#define DM_CUDA(h, expr)                                                                          \
+    do {                                                                                          \
+        cudaError_t e__ = (expr);                                                                 \
+        if (e__ != cudaSuccess) {                                                                 \
+            char b__[512];                                                                        \
+            snprintf(b__, sizeof b__, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e__), __FILE__, __LINE__); \
+            return wrnn::dm_fail((h), WRNN_ERR_CUDA, b__);                                        \
+        }                                                                                         \
+    } while (0)
+
+static int dm_pack(wrnn_dm_handle *h) {
+    const int H = h->hidden, S2 = H / 2, Q = h->quant, G = h->num_sms;
+    auto get = [&](const char *k, std::vector<int64_t> shape) -> const HostTensor * {
+        auto it = h->w.find(k);
+        if (it == h->w.end() || it->second.shape != shape) {
+            h->err = std::string("checkpoint key missing or misshapen: ") + k;
+            return nullptr;
+        }
+        return &it->second;
+    };
+    const HostTensor *R = get("R.weight", {3 * H, H}), *O1 = get("O1.weight", {S2, S2}), *O1b = get("O1.bias", {S2}),
+                     *O2 = get("O2.weight", {Q, S2}), *O2b = get("O2.bias", {Q}), *O3 = get("O3.weight", {S2, S2}),
+                     *O3b = get("O3.bias", {S2}), *O4 = get("O4.weight", {Q, S2}), *O4b = get("O4.bias", {Q}),
+                     *Ic = get("I_coarse.weight", {3 * S2, 2}), *If = get("I_fine.weight", {3 * S2, 3}),
+                     *bu = get("bias_u", {H}), *br = get("bias_r", {H}), *be = get("bias_e", {H});
+    if (!R || !O1 || !O1b || !O2 || !O2b || !O3 || !O3b || !O4 || !O4b || !Ic || !If || !bu || !br || !be) return WRNN_ERR_STATE;
+    DmParams &p = h->plan;
+    p.H = H; p.S2 = S2; p.Q = Q;
+    p.upc = (H + G - 1) / G;
+    p.r1 = (S2 + G - 1) / G;
+    p.r2 = (Q + G - 1) / G;
+    int o = 0;
+    p.off_R = o;  o += p.upc * 3 * H;
+    p.off_O1 = o; o += p.r1 * S2;
+    p.off_O2 = o; o += p.r2 * S2;
+    p.off_O3 = o; o += p.r1 * S2;
+    p.off_O4 = o; o += p.r2 * S2;
+    p.off_I = o;  o += p.upc * 9;
+    p.off_b = o;  o += p.upc * 3 + 2 * p.r1 + 2 * p.r2;
+    p.img_floats = (o + 3) & ~3;
+    h->smem_bytes = ((size_t)p.img_floats + (size_t)DM_MAXN * H + (size_t)p.upc * 3 * DM_MAXN + (size_t)DM_MAXN * Q) * sizeof(float);
+    if (h->smem_bytes > h->smem_optin) return dm_fail(h, WRNN_ERR_ARG, "deepmind model too large for the shared-memory resident kernel");
+    std::vector<float> img((size_t)G * p.img_floats, 0.f);
+    for (int c = 0; c < G; c++) {
+        float *im = img.data() + (size_t)c * p.img_floats;
+        float *bb = im + p.off_b, *bO1 = bb + 3 * p.upc, *bO2 = bO1 + p.r1, *bO3 = bO2 + p.r2, *bO4 = bO3 + p.r1;
+        for (int u = 0; u < p.upc; u++) {
+            const int unit = c * p.upc + u;
+            if (unit >= H) break;
+            for (int g = 0; g < 3; g++) {
+                // R.hidden splits into [u_c, u_f, r_c, r_f, e_c, e_f] (:117-119): gate g of unit j is row g*H + j
+                memcpy(im + p.off_R + (size_t)(u * 3 + g) * H, R->v.data() + (size_t)(g * H + unit) * H, (size_t)H * sizeof(float));
+                float *iw = im + p.off_I + u * 9 + g * 3;
+                if (unit < S2) { iw[0] = Ic->v[(size_t)(g * S2 + unit) * 2]; iw[1] = Ic->v[(size_t)(g * S2 + unit) * 2 + 1]; }
+                else for (int k = 0; k < 3; k++) iw[k] = If->v[(size_t)(g * S2 + unit - S2) * 3 + k];
+            }
+            bb[u * 3 + 0] = bu->v[unit]; bb[u * 3 + 1] = br->v[unit]; bb[u * 3 + 2] = be->v[unit];
+        }
+        for (int r = 0; r < p.r1; r++) {
+            const int row = c * p.r1 + r;
+            if (row >= S2) break;
+            memcpy(im + p.off_O1 + (size_t)r * S2, O1->v.data() + (size_t)row * S2, (size_t)S2 * sizeof(float));
+            memcpy(im + p.off_O3 + (size_t)r * S2, O3->v.data() + (size_t)row * S2, (size_t)S2 * sizeof(float));
+            bO1[r] = O1b->v[row]; bO3[r] = O3b->v[row];
+        }
+        for (int r = 0; r < p.r2; r++) {
+            const int row = c * p.r2 + r;
+            if (row >= Q) break;
+            memcpy(im + p.off_O2 + (size_t)r * S2, O2->v.data() + (size_t)row * S2, (size_t)S2 * sizeof(float));
+            memcpy(im + p.off_O4 + (size_t)r * S2, O4->v.data() + (size_t)row * S2, (size_t)S2 * sizeof(float));
+            bO2[r] = O2b->v[row]; bO4[r] = O4b->v[row];
+        }
+    }
+    if (h->image) cudaFree(h->image);
+    h->image = nullptr;
+    DM_CUDA(h, cudaMalloc((void **)&h->image, img.size() * sizeof(float)));
+    DM_CUDA(h, cudaMemcpy(h->image, img.data(), img.size() * sizeof(float), cudaMemcpyHostToDevice));
+    h->packed = true;
+    return 0;
+}
+
+}  // namespace wrnn
+
+using namespace wrnn;
+
 extern "C" {
-int wrnn_dm_create(int32_t, int32_t, int, wrnn_dm_handle **out) {
-    if (out) *out = nullptr;
-    g_dm_err = "deepmind variant not built yet";
-    return WRNN_ERR_STATE;
+
+int wrnn_dm_create(int32_t hidden_size, int32_t quantisation, int device, wrnn_dm_handle **out) {
+    if (!out) return dm_fail(nullptr, WRNN_ERR_ARG, "null argument");
+    *out = nullptr;
+    if (hidden_size < 8 || hidden_size % 8 || quantisation < 4 || quantisation % 4)
+        return dm_fail(nullptr, WRNN_ERR_ARG, "hidden_size must be a multiple of 8 and quantisation a multiple of 4");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) return dm_fail(nullptr, WRNN_ERR_CUDA, "no CUDA device: this library has no CPU fallback");
+    if (device < 0 || device >= ndev) return dm_fail(nullptr, WRNN_ERR_ARG, "device out of range");
+    cudaDeviceProp prop;
+    if (cudaSetDevice(device) != cudaSuccess || cudaGetDeviceProperties(&prop, device) != cudaSuccess)
+        return dm_fail(nullptr, WRNN_ERR_CUDA, "cannot open device");
+    wrnn_dm_handle *h = new wrnn_dm_handle();
+    h->hidden = hidden_size; h->quant = quantisation; h->device = device;
+    h->num_sms = prop.multiProcessorCount;
+    h->smem_optin = prop.sharedMemPerBlockOptin;
+    cudaEventCreate(&h->ev[0]);
+    cudaEventCreate(&h->ev[1]);
+    *out = h;
+    return 0;
 }
-void wrnn_dm_destroy(wrnn_dm_handle *h) { delete h; }
+
+void wrnn_dm_destroy(wrnn_dm_handle *h) {
+    if (!h) return;
+    cudaSetDevice(h->device);
+    if (h->image) cudaFree(h->image);
+    if (h->ws) cudaFree(h->ws);
+    for (int i = 0; i < 2; i++)
+        if (h->ev[i]) cudaEventDestroy(h->ev[i]);
+    delete h;
+}
+
 const char *wrnn_dm_last_error(const wrnn_dm_handle *h) { return h ? h->err.c_str() : g_dm_err.c_str(); }
-int wrnn_dm_load_weights(wrnn_dm_handle *, const wrnn_tensor *, int32_t) { return WRNN_ERR_STATE; }
-int wrnn_dm_generate(wrnn_dm_handle *, int64_t, int32_t, const float *, const float *, uint64_t, int64_t *, int64_t *,
-                     int64_t *, void *) { return WRNN_ERR_STATE; }
-int wrnn_dm_last_timing(wrnn_dm_handle *, float *, int64_t *) { return WRNN_ERR_STATE; }
+
+int wrnn_dm_load_weights(wrnn_dm_handle *h, const wrnn_tensor *tensors, int32_t n) {
+    if (!h || (!tensors && n > 0)) return dm_fail(h, WRNN_ERR_ARG, "null argument");
+    for (int i = 0; i < n; i++) {
+        const wrnn_tensor &t = tensors[i];
+        if (!t.name || !t.data || t.ndim < 0 || t.ndim > 4) return dm_fail(h, WRNN_ERR_ARG, "bad tensor");
+        if (t.dtype != 0) continue;
+        HostTensor ht;
+        int64_t numel = 1;
+        for (int k = 0; k < t.ndim; k++) { ht.shape.push_back(t.shape[k]); numel *= t.shape[k]; }
+        ht.v.assign((const float *)t.data, (const float *)t.data + numel);
+        h->w[t.name] = std::move(ht);
+    }
+    h->packed = false;
+    return 0;
 }
+
+}  // extern "C"
+
+extern "C" {
+
+int wrnn_dm_generate(wrnn_dm_handle *h, int64_t seq_len, int32_t n_seq, const float *q_coarse, const float *q_fine,
+                     uint64_t seed, int64_t *output, int64_t *coarse, int64_t *fine, void *cuda_stream) {
+    if (!h || !output || !coarse || !fine || seq_len < 1 || n_seq < 1) return dm_fail(h, WRNN_ERR_ARG, "bad argument");
+    if ((q_coarse == nullptr) != (q_fine == nullptr)) return dm_fail(h, WRNN_ERR_ARG, "give both noise tensors or none");
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    DM_CUDA(h, cudaSetDevice(h->device));
+    if (!h->packed) {
+        if (h->w.empty()) return dm_fail(h, WRNN_ERR_STATE, "weights not loaded: call wrnn_dm_load_weights first");
+        const int rc = dm_pack(h);
+        if (rc) return rc;
+    }
+    const int H = h->hidden, S2 = H / 2, Q = h->quant;
+    const size_t nq = q_coarse ? (size_t)seq_len * n_seq * Q : 0;
+    // workspace: sync[128 B] | hidden[2][8][H] | o1, o3 [8][S2] | lc, lf [8][Q] | coarse, fine int32 [n_seq][T] | noise
+    size_t off = 128;
+    const size_t o_hidden = off; off += (size_t)2 * DM_MAXN * H * 4;
+    const size_t o_o1 = off; off += (size_t)DM_MAXN * S2 * 4;
+    const size_t o_o3 = off; off += (size_t)DM_MAXN * S2 * 4;
+    const size_t o_lc = off; off += (size_t)DM_MAXN * Q * 4;
+    const size_t o_lf = off; off += (size_t)DM_MAXN * Q * 4;
+    const size_t act_end = off;
+    const size_t o_c = off; off += (size_t)n_seq * seq_len * 4;
+    const size_t o_f = off; off += (size_t)n_seq * seq_len * 4;
+    off = (off + 255) & ~(size_t)255;
+    const size_t o_qc = off; off += nq * 4;
+    const size_t o_qf = off; off += nq * 4;
+    if (off > h->ws_bytes) {
+        if (h->ws) cudaFree(h->ws);
+        h->ws = nullptr; h->ws_bytes = 0;
+        DM_CUDA(h, cudaMalloc(&h->ws, off + off / 8));
+        h->ws_bytes = off + off / 8;
+    }
+    char *ws = (char *)h->ws;
+    if (nq) {
+        DM_CUDA(h, cudaMemcpyAsync(ws + o_qc, q_coarse, nq * 4, cudaMemcpyHostToDevice, st));
+        DM_CUDA(h, cudaMemcpyAsync(ws + o_qf, q_fine, nq * 4, cudaMemcpyHostToDevice, st));
+    }
+    DM_CUDA(h, cudaFuncSetAttribute(dm_loop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_bytes));
+    h->launches = 0;
+    DM_CUDA(h, cudaEventRecord(h->ev[0], st));
+    for (int n0 = 0; n0 < n_seq; n0 += DM_MAXN) {          // sequences are independent: groups of <= 8 per launch
+        DmParams P = h->plan;
+        P.N = std::min(DM_MAXN, n_seq - n0);
+        P.T = seq_len;
+        P.image = h->image;
+        DM_CUDA(h, cudaMemsetAsync(ws, 0, act_end, st));     // barrier counter, abort flag, hidden = 0 (:167-169)
+        P.gs.counter = (unsigned long long *)ws;
+        P.gs.abort_flag = (int *)(ws + 64);
+        P.hidden = (float *)(ws + o_hidden);
+        P.o1 = (float *)(ws + o_o1); P.o3 = (float *)(ws + o_o3);
+        P.lc = (float *)(ws + o_lc); P.lf = (float *)(ws + o_lf);
+        P.qc = nq ? (const float *)(ws + o_qc) : nullptr;
+        P.qf = nq ? (const float *)(ws + o_qf) : nullptr;
+        P.Ntot = n_seq; P.n0 = n0;
+        P.coarse = (int32_t *)(ws + o_c) + (size_t)n0 * seq_len;
+        P.fine = (int32_t *)(ws + o_f) + (size_t)n0 * seq_len;
+        P.seed = seed;
+        void *args[] = {(void *)&P};
+        DM_CUDA(h, cudaLaunchCooperativeKernel((const void *)dm_loop_kernel, dim3(h->num_sms), dim3(DM_THREADS), args, h->smem_bytes, st));
+        h->launches++;
+        int flag = 0;
+        DM_CUDA(h, cudaMemcpyAsync(&flag, ws + 64, sizeof(int), cudaMemcpyDeviceToHost, st));
+        DM_CUDA(h, cudaStreamSynchronize(st));
+        if (flag) return dm_fail(h, WRNN_ERR_CUDA, "deepmind loop kernel aborted: grid barrier watchdog fired");
+    }
+    DM_CUDA(h, cudaEventRecord(h->ev[1], st));
+    std::vector<int32_t> hc((size_t)n_seq * seq_len), hf((size_t)n_seq * seq_len);
+    DM_CUDA(h, cudaMemcpyAsync(hc.data(), ws + o_c, hc.size() * 4, cudaMemcpyDeviceToHost, st));
+    DM_CUDA(h, cudaMemcpyAsync(hf.data(), ws + o_f, hf.size() * 4, cudaMemcpyDeviceToHost, st));
+    DM_CUDA(h, cudaStreamSynchronize(st));
+    DM_CUDA(h, cudaGetLastError());
+    for (size_t i = 0; i < hc.size(); i++) {
+        coarse[i] = hc[i];
+        fine[i] = hf[i];
+        output[i] = (int64_t)hc[i] * 256 + hf[i] - 32768;      // combine_signal (utils/dsp.py:33-34)
+    }
+    return 0;
+}
+
+int wrnn_dm_last_timing(wrnn_dm_handle *h, float *ms_loop, int64_t *kernel_launches) {
+    if (!h) return WRNN_ERR_ARG;
+    float ms = 0;
+    DM_CUDA(h, cudaEventSynchronize(h->ev[1]));
+    DM_CUDA(h, cudaEventElapsedTime(&ms, h->ev[0], h->ev[1]));
+    if (ms_loop) *ms_loop = ms;
+    if (kernel_launches) *kernel_launches = h->launches;
+    return 0;
+}
+
+}  // extern "C"
