@@ -63,6 +63,7 @@ struct ResParams {
     unsigned long long *xprev;               // [2][RB]
     int *abort_flag;
     long long *prof;
+    int exp;                                 // WRNN_EXP bit set: schedule experiments (debug)
 };
 
 // shared memory carve (floats)
@@ -80,13 +81,15 @@ constexpr int SM_WC = SM_XP + 96;                 // conditioning matrices C1 [1
 constexpr int SM_WCN = 12 * CB1 + 12 * CB2 + 4 * CB3;
 constexpr int SM_W0B = SM_WC + SM_WCN;            // w0[32] | biases[64] (copy of the image tail)
 constexpr int SM_PROF = SM_W0B + 96;              // [4 groups][8] 64-bit clock accumulators (debug)
-constexpr int SM_FLOATS = SM_PROF + 64 + 16;
+constexpr int SM_HIST = SM_PROF + 64 + 16 + 32;   // [8 phases][32 buckets of 512 clk] per-step duration histogram (debug)
+constexpr int SM_FLOATS = SM_HIST + 256;    // + per-group poll counters + 16 gather-phase accumulators (debug)
 
 // ---------------------------------------------------------------------------- polling with a sticky abort
 struct Dead {
     bool dead;
     const int *flag;
     int *flag_w;
+    unsigned long long *gacc;   // debug, CTA 0 only: per gather [first slot valid, cp.async landed, validated] thread-clock sums
     unsigned int *cnt;      // debug counters in smem (null unless WRNN_PROF): [0] probe spins, [1] fallback slots, [2] fallback spins
 };
 __device__ __forceinline__ bool poll_giveup(Dead &dd, long long t0, unsigned &spins) {
@@ -123,8 +126,10 @@ __device__ __forceinline__ void gather_group(const float *src, int n4, float *ds
     const uint4 *s4 = reinterpret_cast<const uint4 *>(src);
     uint4 *d4 = reinterpret_cast<uint4 *>(dst);
     d4[ti] = poll_slot(s4 + ti, tag, dd);
+#pragma unroll 1
     for (int i = ti + nth; i < n4; i += nth) cp_async16(d4 + i, s4 + i);
     asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
+#pragma unroll 1
     for (int i = ti + nth; i < n4; i += nth)
         if (!tags_ok(d4[i], tag)) d4[i] = poll_slot(s4 + i, tag, dd, 2);
 }
@@ -145,6 +150,7 @@ __device__ __forceinline__ float poll_xprev(const unsigned long long *slot, uint
 __device__ __forceinline__ void load_cond(const float *cond_t, int64_t fold_stride, int B, int c0, int n, float *dst,
                                           int ld, int d0, int nth, int ti) {
     const int n4 = n >> 2;
+#pragma unroll 1
     for (int i = ti; i < B * n4; i += nth) {
         const int f = i / n4, k4 = i - f * n4;
         const float4 v = __ldg(reinterpret_cast<const float4 *>(cond_t + (size_t)f * fold_stride + c0) + k4);
@@ -183,6 +189,7 @@ __device__ __forceinline__ void load_gru_w(GruW &w, const float *img, int wq, in
     }
 }
 __device__ __forceinline__ void gru_job(const GruW &w, const float *buf, int FG, float *red, int wq, int lane) {
+    __syncwarp();
     const int kw = wq & 1;
     const float4 *x4 = reinterpret_cast<const float4 *>(buf) + kw * 64 + lane;
     for (int fg = 0; fg < FG; fg++) {
@@ -223,7 +230,10 @@ __device__ __forceinline__ void load_fc_w(FcW &w, const float *img, int tg) {
 #pragma unroll
     for (int i = 0; i < 4; i++) w.r[i] = ld_keep4(p + (size_t)i * (RH / 4) + tg);
 }
-__device__ __forceinline__ void fc_job(const FcW &w, const float *buf, int FG, float *red, int wq, int lane, int tg) {
+__device__ __forceinline__ void fc_job(const float4 &r0, const float4 &r1, const float4 &r2, const float4 &r3, const float *buf, int FG,
+                                       float *red, int wq, int lane, int tg) {
+    __syncwarp();
+    const float4 wr[4] = {r0, r1, r2, r3};
     const float4 *x4 = reinterpret_cast<const float4 *>(buf) + tg;
     for (int fg = 0; fg < FG; fg++) {
         float v[32];
@@ -234,10 +244,10 @@ __device__ __forceinline__ void fc_job(const FcW &w, const float *buf, int FG, f
             const float4 x = x4[(fg * 5 + fl) * (RH / 4)];
 #pragma unroll
             for (int i = 0; i < 4; i++) {
-                float s = w.r[i].x * x.x;
-                s = fmaf(w.r[i].y, x.y, s);
-                s = fmaf(w.r[i].z, x.z, s);
-                s = fmaf(w.r[i].w, x.w, s);
+                float s = wr[i].x * x.x;
+                s = fmaf(wr[i].y, x.y, s);
+                s = fmaf(wr[i].z, x.z, s);
+                s = fmaf(wr[i].w, x.w, s);
                 v[fl * 4 + i] = s;
             }
         }
@@ -263,12 +273,13 @@ struct CondW {
 template <int NJ>
 __device__ __forceinline__ void cond_job(const float *wsm, const float *cb, int ld, int B, const float *bias, float *pre,
                                          int wq, int lane) {
+    __syncwarp();
     CondW<NJ> c;                                     // transient: the conditioning matrices live in smem
 #pragma unroll
     for (int i = 0; i < 3; i++)
 #pragma unroll
         for (int j = 0; j < NJ; j++) c.w[i][j] = wsm[(3 * wq + i) * ld + lane + 32 * j];
-#pragma unroll
+#pragma unroll 1
     for (int half = 0; half < 2; half++) {          // ten folds at a time: 30 partials per lane
         float v[32];
         v[30] = v[31] = 0.f;
@@ -332,7 +343,7 @@ __device__ void res_tail_role(const ResParams &P, int j, float *smem) {
     const uint2 key = make_uint2((uint32_t)P.a.seed, (uint32_t)(P.a.seed >> 32));
     const int nmix = NC / 3;
     const int64_t Bt = P.a.Btot, b0 = P.a.b0;
-    Dead dd{false, P.abort_flag, P.abort_flag, nullptr};
+    Dead dd{false, P.abort_flag, P.abort_flag, nullptr, nullptr};
     const bool prof_on = P.prof != nullptr && j == 0 && tid == 0;
     long long pacc[4] = {0, 0, 0, 0}, pt = clock64();
 
@@ -420,15 +431,72 @@ __device__ __forceinline__ void publish4(float *dst, uint32_t w, int lane, bool 
     if ((lane & 3) == 0 && active) st_relaxed_v4(dst, v);
 }
 
+__device__ __forceinline__ long long clock_fenced() {       // the "memory" clobber keeps it on its side of barriers
+    long long c;
+    asm volatile("mov.u64 %0, %%clock64;" : "=l"(c)::"memory");
+    return c;
+}
 #define RPROF(slot)                                                   \
     do {                                                              \
         if (prof_on) {                                                \
-            const long long n__ = clock64();                          \
-            pacc[slot] += n__ - pt;                                   \
+            const long long n__ = clock_fenced();                     \
+            const long long d__ = n__ - pt;                           \
+            pacc[slot] += d__;                                        \
+            if (d__ > pacc[8 + slot]) pacc[8 + slot] = d__;           \
+            { const long long b__ = d__ >> 9; reinterpret_cast<int *>(smem + SM_HIST)[slot * 32 + (b__ > 31 ? 31 : (int)b__)]++; } \
+            if (d__ < pacc[16 + slot] || pacc[16 + slot] == 0) pacc[16 + slot] = d__; \
             pt = n__;                                                 \
         }                                                             \
+        __syncwarp();   /* the timing lane must rejoin its warp: a warp that stays split runs every shuffle on the slow path */ \
     } while (0)
 
+// CTA-wide gather of a tagged vector (n4 float4) into dense smem: every thread requests all its slots
+// (tid, tid + 512, ...: 5 at 20 folds) at once and re-polls the ones whose tag is not there yet.
+// CTA-wide gather of 40 KB of tagged words: every slot by cp.async.cg (L2 -> smem, no registers), all of a
+// thread's slots in flight at once, re-issued until the slot's four tags match.
+__device__ __forceinline__ void gather_cta(const float *src, int n4, float *dst, uint32_t tag, int tid, Dead &dd, int delay = 0) {
+    const uint4 *s4 = reinterpret_cast<const uint4 *>(src);
+    uint4 *d4 = reinterpret_cast<uint4 *>(dst);
+    unsigned todo = 0;
+#pragma unroll
+    for (int j = 0; j < 5; j++)
+        if (tid + j * RTH < n4) todo |= 1u << j;
+    unsigned spins = 0;
+    long long t0 = 0;
+    if (delay) {
+        const long long c0 = clock64();
+        while (clock64() - c0 < delay) {}
+    }
+    for (;;) {
+#pragma unroll
+        for (int j = 0; j < 5; j++)
+            if (todo & (1u << j)) cp_async16(d4 + tid + j * RTH, s4 + tid + j * RTH);
+        asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
+#pragma unroll
+        for (int j = 0; j < 5; j++)
+            if ((todo & (1u << j)) && tags_ok(d4[tid + j * RTH], tag)) todo &= ~(1u << j);
+        if (todo == 0 || dd.dead) break;
+        if (spins == 0) t0 = clock64();
+        if (poll_giveup(dd, t0, spins)) break;
+    }
+    if (dd.cnt) atomicAdd(dd.cnt, spins);
+}
+
+// Row CTA, bulk-synchronous schedule.  Per step (S* = __syncthreads):
+//   P  shadow  GB: W_hh1 . h1(t-1), rnn1 conditioning;  GC: W_hh2 . h2(t-1), rnn2 conditioning;  GD: fc conditioning
+//              -- nothing here needs sample t-1, so for t > 0 it runs while the tail CTAs do fc3 + sampling   S5
+//   T0 all     wait x_prev(t)                                   S0
+//   T1 GB      rnn1 gates -> publish h1(t)
+//   T2 all     gather h1(t)                                     S1
+//   T3 GA      W_ih2a . h1 (alone on the SM), rnn2 gates -> publish x2'(t) = h1 + h2      S1b
+//   T4 all     gather x2'(t)                                    S2
+//   T5 GD      fc1 -> publish y1(t);   GC: h2 = x2' - h1 (saves exchanging h2)      S3
+//   T6 all     gather y1(t)                                     S4
+//   T7 GD      fc2 -> publish y2(t)
+// The measured cost of one all-to-all round through L2 is 3-4.5 k clk whatever its size, so the schedule keeps
+// the SM free for the layer on the chain and pushes everything else into the tail window.  The loop body is
+// kept small on purpose (one call site per job, bounded unrolling): at > 128 KB of SASS the four groups'
+// instruction streams evict each other and every phase slows down.
 __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
     const Dims &d = P.d;
     const int tid = threadIdx.x, gid = tid >> 7, tg = tid & 127, wq = tg >> 5, lane = tid & 31;
@@ -445,233 +513,207 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
     float *pre_h1 = smem + SM_PRE, *pre_h2 = pre_h1 + 240, *pre_i1 = pre_h2 + 240, *pre_i2 = pre_i1 + 240,
           *pre_f1 = pre_i2 + 240, *pre_f2 = pre_f1 + 80;
     float *hst1 = smem + SM_HST, *hst2 = hst1 + 80;
-    float *xpA = smem + SM_XP, *xpB = xpA + 32, *xpD = xpB + 32;
+    float *xp = smem + SM_XP;
 
     for (int i = tid; i < SM_FLOATS; i += RTH) smem[i] = 0.f;
     __syncthreads();
     for (int i = tid; i < SM_WCN + 96; i += RTH) smem[SM_WC + i] = __ldg(img + IMG_C1 + i);     // C1 | C2 | C3 | w0 | biases are contiguous
     const float *wc1 = smem + SM_WC, *wc2 = wc1 + 12 * CB1, *wc3 = wc2 + 12 * CB2;
     __syncthreads();
-    Dead dd{false, P.abort_flag, P.abort_flag, (P.prof != nullptr && cta == 0) ? reinterpret_cast<unsigned int *>(smem + SM_PROF + 64) + gid * 4 : nullptr};
+    Dead dd{false, P.abort_flag, P.abort_flag, nullptr,
+            (P.prof != nullptr && cta == 0) ? reinterpret_cast<unsigned int *>(smem + SM_PROF + 64) + gid * 4 : nullptr};
     const float *w0 = smem + SM_W0B, *bias = w0 + 32;
     const float *b_i1 = bias, *b_i2 = bias + 12, *b_f1 = bias + 24, *b_f2 = bias + 28, *b_hh1 = bias + 32, *b_hh2 = bias + 44;
-    const bool prof_on = P.prof != nullptr && cta == 0 && tg == 0;
-    long long *pacc = reinterpret_cast<long long *>(smem + SM_PROF) + gid * 8, pt = 0;
+    const bool prof_on = P.prof != nullptr && tid == 0;          // every row CTA times its own phases
+    long long *pacc = reinterpret_cast<long long *>(smem + SM_PROF), pt = 0;
 
-    if (gid == 0) {
-        // ======================================================================== GA: rnn2
-        GruW w;
-        load_gru_w(w, img + IMG_IH2, wq, lane);
-        float w0r[3] = {0.f, 0.f, 0.f};
-        const int gu = tg & 3, gf = tg >> 2;                      // gate thread: unit gu (< 4), fold gf
-        const bool gate = gf < B;
-        for (int g = 0; g < 3; g++) w0r[g] = w0[12 + g * RU + gu];
-        __syncthreads();                                          // prologue of all groups done
-        pt = clock64();
-        for (int64_t t = 0; t < S; t++) {
-            const uint32_t tag = (uint32_t)((t + 1) & 3);
-            const size_t par = (size_t)(t & 1);
-            if (tg < B) xpA[tg] = poll_xprev(P.xprev + par * RB + tg, (uint32_t)(t + 1), dd);
-            if (t > 0) bar_sync(BAR_H1FREE, 256);                  // GB finished reading h1(t-1)
-            RPROF(0);
-            gather_group(P.h1 + par * B * RH, B * (RH / 4), bufH1, tag, 256, tid, dd);
-            bar_sync(BAR_H1, 256);
-            RPROF(1);
-            gru_job(w, bufH1, FG, red, wq, lane);
-            RPROF(4);
-            bar_arrive(BAR_AJOB, 256);                             // GB may start its shadow job now
+    // ---- per-group register state: the weights live here for the whole call
+    GruW w;                                   // GA: W_ih2a   GB: W_hh1   GC: W_hh2   GD: fc1 rows in a[0..3], fc2 rows in a[4], a[5], b[0], b[1]
+    if (gid < 3) load_gru_w(w, img + (gid == 0 ? IMG_IH2 : gid == 1 ? IMG_HH1 : IMG_HH2), wq, lane);
+    else {
+        const float4 *p1 = reinterpret_cast<const float4 *>(img + IMG_F1), *p2 = reinterpret_cast<const float4 *>(img + IMG_F2);
+#pragma unroll
+        for (int i = 0; i < 4; i++) w.a[i] = ld_keep4(p1 + (size_t)i * (RH / 4) + tg);
+        w.a[4] = ld_keep4(p2 + tg);
+        w.a[5] = ld_keep4(p2 + (RH / 4) + tg);
+        w.b[0] = ld_keep4(p2 + 2 * (RH / 4) + tg);
+        w.b[1] = ld_keep4(p2 + 3 * (RH / 4) + tg);
+#pragma unroll
+        for (int i = 2; i < 6; i++) w.b[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    const int gu = tg & 3, gf = tg >> 2;      // gate / epilogue thread: unit (row) gu of fold gf
+    const bool gate = gf < B;
+    float w0r[3] = {0.f, 0.f, 0.f};
+    if (gid == 0) for (int g = 0; g < 3; g++) w0r[g] = w0[12 + g * RU + gu];
+    if (gid == 1) for (int g = 0; g < 3; g++) w0r[g] = w0[g * RU + gu];
+    if (gid == 3) w0r[0] = w0[24 + gu];
+
+    auto cond34 = [&]() {                     // GD: conditioning part of fc1 (m, a1, a3) and fc2 (a4), row wq
+        __syncwarp();
+        float c3[5], c4;
+#pragma unroll
+        for (int jj = 0; jj < 5; jj++) c3[jj] = wc3[wq * CB3 + lane + 32 * jj];
+        c4 = wc3[wq * CB3 + 160 + lane];
+        float v[32];
+#pragma unroll
+        for (int i = 20; i < 32; i++) v[i] = 0.f;
+#pragma unroll
+        for (int f = 0; f < RB; f++) {
+            float s = c3[0] * cb3[f * CB3 + lane];
+#pragma unroll
+            for (int jj = 1; jj < 5; jj++) s = fmaf(c3[jj], cb3[f * CB3 + lane + 32 * jj], s);
+            v[f] = s;
+        }
+        warp_reduce_scatter<32>(v, lane);
+        if (lane < B) pre_f1[wq * RB + lane] = v[0] + b_f1[wq];
+#pragma unroll
+        for (int f = 0; f < RB; f++) v[f] = c4 * cb3[f * CB3 + 160 + lane];
+#pragma unroll
+        for (int i = 20; i < 32; i++) v[i] = 0.f;
+        warp_reduce_scatter<32>(v, lane);
+        if (lane < B) pre_f2[wq * RB + lane] = v[0] + b_f2[wq];
+    };
+    auto load_cb3 = [&](int64_t t) {
+        const float *ct = P.a.cond + (size_t)t * CW;
+        load_cond(ct, cstride, B, 0, Kc, cb3, CB3, 0, 128, tg);                 // m, a1
+        load_cond(ct, cstride, B, Kc + 32, 32, cb3, CB3, Kc, 128, tg);          // a3
+        load_cond(ct, cstride, B, Kc + 64, 32, cb3, CB3, 160, 128, tg);         // a4
+    };
+
+    // bufH1 / bufH2 are zero here (h = 0 at t = 0, :194-195), so the first shadow pass yields pre_h = b_hh.
+    __syncthreads();
+    pt = clock64();
+
+    // Clocks between a CTA's own publish and its first look at the others' data.  A bulk fetch that arrives before
+    // the stores fails its tag check AND queues 5 MB of reads in front of those stores chip-wide; measured on B200:
+    // no delay 6.1 k clk per exchange, 500: 2.7 k, 700: 2.4 k, 900: 2.6 k (the fetch itself is ~1.7 k).
+    const int gdelay = (P.exp >> 4) ? (P.exp >> 4) * 100 : 700;
+    for (int64_t t = 0; t < S; t++) {
+        const uint32_t tag = (uint32_t)((t + 1) & 3);
+        const size_t par = (size_t)(t & 1);
+        // ---- P: everything step t needs that does not depend on sample t-1; for t > 0 this runs while the
+        //         tail CTAs turn y2(t-1) into that sample
+        if (gid == 1 || gid == 2) {
+            const bool g1 = gid == 1;
+            if (!(P.exp & 8)) gru_job(w, g1 ? bufH1 : bufH2, FG, red, wq, lane);
+            float *cb = g1 ? cb1 : cb2;
+            const int ldc = g1 ? CB1 : CB2;
+            load_cond(P.a.cond + (size_t)t * CW, cstride, B, 0, g1 ? Kc : Kc + 32, cb, ldc, 0, 128, tg);
+            bar_sync(g1 ? BAR_B : BAR_C, 128);
+            float *pre_h = g1 ? pre_h1 : pre_h2;
+            const float *b_hh = g1 ? b_hh1 : b_hh2;
+#pragma unroll 1
+            for (int i = tg; i < 12 * RB; i += 128) {
+                const int r = i / RB, f = i - r * RB;
+                pre_h[i] = gru_out(red, r, f) + b_hh[r];
+            }
+            if (!(P.exp & 8)) {
+                if (g1) cond_job<4>(wc1, cb1, CB1, B, b_i1, pre_i1, wq, lane);
+                else cond_job<5>(wc2, cb2, CB2, B, b_i2, pre_i2, wq, lane);
+            }
+        } else if (gid == 3) {
+            load_cb3(t);
+            bar_sync(BAR_D, 128);
+            if (!(P.exp & 8)) cond34();
+        }
+        __syncthreads();                                                         // S5
+        RPROF(0);
+        // ---- T0: previous sample
+        if (tid < B) xp[tid] = poll_xprev(P.xprev + par * RB + tid, (uint32_t)(t + 1), dd);
+        __syncthreads();                                                         // S0
+        RPROF(1);
+        // ---- T1: rnn1 gates (GB)
+        if (gid == 1 && tg < 96) {
+            uint32_t hw = tag;
+            if (gate) {
+                const float xpv = xp[gf];
+                const float ir = fmaf(w0r[0], xpv, pre_i1[(0 * RU + gu) * RB + gf]);
+                const float iz = fmaf(w0r[1], xpv, pre_i1[(1 * RU + gu) * RB + gf]);
+                const float in_ = fmaf(w0r[2], xpv, pre_i1[(2 * RU + gu) * RB + gf]);
+                const float hn = gru_update(ir, iz, in_, pre_h1[(0 * RU + gu) * RB + gf], pre_h1[(1 * RU + gu) * RB + gf],
+                                            pre_h1[(2 * RU + gu) * RB + gf], hst1[gu * RB + gf]);
+                hw = tag_word(hn, tag);
+                hst1[gu * RB + gf] = __uint_as_float(hw);          // the state IS the tagged word, everywhere
+            }
+            publish4(P.h1 + (par * B + gf) * RH + u0, hw, lane, gate);
+        }
+        __syncthreads();                                    // S0b: as S1b
+        // ---- T2: gather h1(t)
+        gather_cta(P.h1 + par * B * RH, B * (RH / 4), bufH1, tag, tid, dd, gdelay);
+        __syncthreads();                                                         // S1
+        RPROF(2);
+        // ---- T3: rnn2 (GA, alone on the SM)
+        if (gid == 0) {
+            if (!(P.exp & 4)) gru_job(w, bufH1, FG, red, wq, lane);
             bar_sync(BAR_A, 128);
-            RPROF(5);
-            if (t > 0) bar_sync(BAR_GC2GA, 256);                   // pre_h2(t), pre_i2(t) written by GC
-            RPROF(2);
-            if (tg < 96) {                                         // warps 0-2 hold the 80 gate threads
-                uint32_t hw = tag, xw = tag;
+            if (tg < 96) {
+                uint32_t xw = tag;
                 if (gate) {
-                    const float xp = xpA[gf];
-                    const float ir = gru_out(red, 0 * RU + gu, gf) + fmaf(w0r[0], xp, pre_i2[(0 * RU + gu) * RB + gf]);
-                    const float iz = gru_out(red, 1 * RU + gu, gf) + fmaf(w0r[1], xp, pre_i2[(1 * RU + gu) * RB + gf]);
-                    const float in_ = gru_out(red, 2 * RU + gu, gf) + fmaf(w0r[2], xp, pre_i2[(2 * RU + gu) * RB + gf]);
+                    const float xpv = xp[gf];
+                    const float ir = gru_out(red, 0 * RU + gu, gf) + fmaf(w0r[0], xpv, pre_i2[(0 * RU + gu) * RB + gf]);
+                    const float iz = gru_out(red, 1 * RU + gu, gf) + fmaf(w0r[1], xpv, pre_i2[(1 * RU + gu) * RB + gf]);
+                    const float in_ = gru_out(red, 2 * RU + gu, gf) + fmaf(w0r[2], xpv, pre_i2[(2 * RU + gu) * RB + gf]);
                     const float hn = gru_update(ir, iz, in_, pre_h2[(0 * RU + gu) * RB + gf], pre_h2[(1 * RU + gu) * RB + gf],
                                                 pre_h2[(2 * RU + gu) * RB + gf], hst2[gu * RB + gf]);
-                    hw = tag_word(hn, tag);
-                    const float hr = __uint_as_float(hw);          // the state IS the tagged word, everywhere
-                    hst2[gu * RB + gf] = hr;
-                    xw = tag_word(bufH1[gf * RH + u0 + gu] + hr, tag);     // h1 + h2 (residuals :212,216)
+                    hst2[gu * RB + gf] = hn;                                   // own state, never exchanged: exact
+                    xw = tag_word(bufH1[gf * RH + u0 + gu] + hn, tag);         // h1 + h2 (residuals :212,216)
                 }
-                publish4(P.h2 + (par * B + gf) * RH + u0, hw, lane, gate);
                 publish4(P.x2 + (par * B + gf) * RH + u0, xw, lane, gate);
             }
-            bar_sync(BAR_A, 128);                                  // red / bufH1 reads done before the next job
-            RPROF(3);
         }
-    } else if (gid == 1) {
-        // ======================================================================== GB: rnn1
-        GruW w;
-        load_gru_w(w, img + IMG_HH1, wq, lane);
-        float w0r[3] = {0.f, 0.f, 0.f};
-        const int gu = tg & 3, gf = tg >> 2;
-        const bool gate = gf < B;
-        for (int g = 0; g < 3; g++) w0r[g] = w0[g * RU + gu];
-        for (int i = tg; i < 12 * RB; i += 128) pre_h1[i] = b_hh1[i / RB];      // h = 0 at t = 0 (:194)
-        load_cond(P.a.cond, cstride, B, 0, Kc, cb1, CB1, 0, 128, tg);
-        bar_sync(BAR_B, 128);
-        cond_job<4>(wc1, cb1, CB1, B, b_i1, pre_i1, wq, lane);
-        __syncthreads();
-        pt = clock64();
-        for (int64_t t = 0; t < S; t++) {
-            const uint32_t tag = (uint32_t)((t + 1) & 3);
-            const size_t par = (size_t)(t & 1);
-            if (tg < B) xpB[tg] = poll_xprev(P.xprev + par * RB + tg, (uint32_t)(t + 1), dd);
-            bar_sync(BAR_B, 128);
-            RPROF(0);
-            if (tg < 96) {
-                uint32_t hw = tag;
-                if (gate) {
-                    const float xp = xpB[gf];
-                    const float ir = fmaf(w0r[0], xp, pre_i1[(0 * RU + gu) * RB + gf]);
-                    const float iz = fmaf(w0r[1], xp, pre_i1[(1 * RU + gu) * RB + gf]);
-                    const float in_ = fmaf(w0r[2], xp, pre_i1[(2 * RU + gu) * RB + gf]);
-                    const float hn = gru_update(ir, iz, in_, pre_h1[(0 * RU + gu) * RB + gf], pre_h1[(1 * RU + gu) * RB + gf],
-                                                pre_h1[(2 * RU + gu) * RB + gf], hst1[gu * RB + gf]);
-                    hw = tag_word(hn, tag);
-                    hst1[gu * RB + gf] = __uint_as_float(hw);
-                }
-                publish4(P.h1 + (par * B + gf) * RH + u0, hw, lane, gate);
-            }
-            RPROF(1);
-            gather_group(P.h1 + par * B * RH, B * (RH / 4), bufH1, tag, 256, tid, dd);
-            bar_sync(BAR_H1, 256);
-            bar_sync(BAR_AJOB, 256);                               // the critical rnn2 product goes first
-            RPROF(2);
-            gru_job(w, bufH1, FG, red, wq, lane);
-            if (t + 1 < S) bar_arrive(BAR_H1FREE, 256);            // h1(t) no longer needed by this thread
-            bar_sync(BAR_B, 128);
-            for (int i = tg; i < 12 * RB; i += 128) {
-                const int r = i / RB, f = i - r * RB;
-                pre_h1[i] = gru_out(red, r, f) + b_hh1[r];
-            }
-            RPROF(3);
-            if (t + 1 < S) {
-                load_cond(P.a.cond + (size_t)(t + 1) * CW, cstride, B, 0, Kc, cb1, CB1, 0, 128, tg);
-                bar_sync(BAR_B, 128);
-                cond_job<4>(wc1, cb1, CB1, B, b_i1, pre_i1, wq, lane);
-            }
-            RPROF(4);
-        }
-    } else if (gid == 2) {
-        // ======================================================================== GC: W_hh2 . h2, rnn2 conditioning
-        GruW w;
-        load_gru_w(w, img + IMG_HH2, wq, lane);
-        for (int i = tg; i < 12 * RB; i += 128) pre_h2[i] = b_hh2[i / RB];
-        load_cond(P.a.cond, cstride, B, 0, Kc + 32, cb2, CB2, 0, 128, tg);
-        bar_sync(BAR_C, 128);
-        cond_job<5>(wc2, cb2, CB2, B, b_i2, pre_i2, wq, lane);
-        __syncthreads();
-        pt = clock64();
-        for (int64_t t = 0; t < S; t++) {
-            const uint32_t tag = (uint32_t)((t + 1) & 3);
-            const size_t par = (size_t)(t & 1);
-            if (t + 1 < S) load_cond(P.a.cond + (size_t)(t + 1) * CW, cstride, B, 0, Kc + 32, cb2, CB2, 0, 128, tg);
-            gather_group(P.h2 + par * B * RH, B * (RH / 4), bufH2, tag, 128, tg, dd);
-            bar_sync(BAR_C, 128);
-            RPROF(0);
-            gru_job(w, bufH2, FG, red, wq, lane);
-            bar_sync(BAR_C, 128);
-            // all rnn2 gate threads of this CTA have published h2(t), so pre_h2(t) / pre_i2(t) are dead
-            for (int i = tg; i < 12 * RB; i += 128) {
-                const int r = i / RB, f = i - r * RB;
-                pre_h2[i] = gru_out(red, r, f) + b_hh2[r];
-            }
-            if (t + 1 < S) {
-                cond_job<5>(wc2, cb2, CB2, B, b_i2, pre_i2, wq, lane);
-                bar_arrive(BAR_GC2GA, 256);
-            }
-            bar_sync(BAR_C, 128);
-            RPROF(1);
-        }
-    } else {
-        // ======================================================================== GD: fc1, fc2
-        FcW w1, w2;
-        load_fc_w(w1, img + IMG_F1, tg);
-        load_fc_w(w2, img + IMG_F2, tg);
-        // conditioning of fc1 (row wq, columns lane + 32 j of (m, a1, a3)) and of fc2 (a4)
-        const int er = tg & 3, ef = tg >> 2;                       // epilogue thread: row er (< 4), fold ef
-        const bool epi = ef < B;
-        const float w0f = w0[24 + er];
-        auto cond34 = [&]() {
-            float c3[5], c4;
-#pragma unroll
-            for (int jj = 0; jj < 5; jj++) c3[jj] = wc3[wq * CB3 + lane + 32 * jj];
-            c4 = wc3[wq * CB3 + 160 + lane];
-            float v[32];
-#pragma unroll
-            for (int i = 20; i < 32; i++) v[i] = 0.f;
-#pragma unroll
-            for (int f = 0; f < RB; f++) {
-                float s = c3[0] * cb3[f * CB3 + lane];
-#pragma unroll
-                for (int jj = 1; jj < 5; jj++) s = fmaf(c3[jj], cb3[f * CB3 + lane + 32 * jj], s);
-                v[f] = s;
-            }
-            warp_reduce_scatter<32>(v, lane);
-            if (lane < B) pre_f1[wq * RB + lane] = v[0] + b_f1[wq];
-#pragma unroll
-            for (int f = 0; f < RB; f++) v[f] = c4 * cb3[f * CB3 + 160 + lane];
-#pragma unroll
-            for (int i = 20; i < 32; i++) v[i] = 0.f;
-            warp_reduce_scatter<32>(v, lane);
-            if (lane < B) pre_f2[wq * RB + lane] = v[0] + b_f2[wq];
-        };
-        auto load_cb3 = [&](int64_t t) {
-            const float *ct = P.a.cond + (size_t)t * CW;
-            load_cond(ct, cstride, B, 0, Kc, cb3, CB3, 0, 128, tg);                 // m, a1
-            load_cond(ct, cstride, B, Kc + 32, 32, cb3, CB3, Kc, 128, tg);          // a3
-            load_cond(ct, cstride, B, Kc + 64, 32, cb3, CB3, 160, 128, tg);         // a4
-        };
-        load_cb3(0);
-        bar_sync(BAR_D, 128);
-        cond34();
-        __syncthreads();
-        pt = clock64();
-        for (int64_t t = 0; t < S; t++) {
-            const uint32_t tag = (uint32_t)((t + 1) & 3);
-            const size_t par = (size_t)(t & 1);
-            if (tg < B) xpD[tg] = poll_xprev(P.xprev + par * RB + tg, (uint32_t)(t + 1), dd);
-            gather_group(P.x2 + par * B * RH, B * (RH / 4), bufX, tag, 128, tg, dd);
-            bar_sync(BAR_D, 128);
-            RPROF(0);
-            fc_job(w1, bufX, FG, red, wq, lane, tg);
+        __syncthreads();                                    // S1b: nobody polls x2' while it is still being computed
+        RPROF(3);
+        // ---- T4: gather x2'(t)
+        gather_cta(P.x2 + par * B * RH, B * (RH / 4), bufX, tag, tid, dd, gdelay);
+        __syncthreads();                                                         // S2
+        RPROF(4);
+        // ---- T5: fc1 (GD); h2 = x2' - h1 for the next shadow product (GC)
+        if (gid == 3) {
+            if (!(P.exp & 4)) fc_job(w.a[0], w.a[1], w.a[2], w.a[3], bufX, FG, red, wq, lane, tg);
             bar_sync(BAR_D, 128);
             if (tg < 96) {
                 uint32_t yw = tag;
-                if (epi) yw = tag_word(fmaxf(fc_out(red, er, ef) + fmaf(w0f, xpD[ef], pre_f1[er * RB + ef]), 0.f), tag);
-                publish4(P.y1 + (par * B + ef) * RH + u0, yw, lane, epi);
+                if (gate) yw = tag_word(fmaxf(fc_out(red, gu, gf) + fmaf(w0r[0], xp[gf], pre_f1[gu * RB + gf]), 0.f), tag);
+                publish4(P.y1 + (par * B + gf) * RH + u0, yw, lane, gate);
             }
-            RPROF(1);
-            gather_group(P.y1 + par * B * RH, B * (RH / 4), bufX, tag, 128, tg, dd);
-            bar_sync(BAR_D, 128);
-            RPROF(2);
-            fc_job(w2, bufX, FG, red, wq, lane, tg);
+        } else if (gid == 2) {
+            const float4 *a4 = reinterpret_cast<const float4 *>(bufX), *b4 = reinterpret_cast<const float4 *>(bufH1);
+            float4 *c4 = reinterpret_cast<float4 *>(bufH2);
+#pragma unroll 2
+            for (int i = tg; i < B * (RH / 4); i += 128) {
+                const float4 a = a4[i], b = b4[i];
+                c4[i] = make_float4(a.x - b.x, a.y - b.y, a.z - b.z, a.w - b.w);
+            }
+        }
+        __syncthreads();                                                         // S3: bufX may be overwritten
+        RPROF(5);
+        // ---- T6: gather y1(t)
+        gather_cta(P.y1 + par * B * RH, B * (RH / 4), bufX, tag, tid, dd, gdelay);
+        __syncthreads();                                                         // S4
+        RPROF(6);
+        // ---- T7: fc2 (GD)
+        if (gid == 3) {
+            if (!(P.exp & 4)) fc_job(w.a[4], w.a[5], w.b[0], w.b[1], bufX, FG, red, wq, lane, tg);
             bar_sync(BAR_D, 128);
             if (tg < 96) {
                 uint32_t yw = tag;
-                if (epi) yw = tag_word(fmaxf(fc_out(red, er, ef) + pre_f2[er * RB + ef], 0.f), tag);
-                publish4(P.y2 + (par * B + ef) * RH + u0, yw, lane, epi);
+                if (gate) yw = tag_word(fmaxf(fc_out(red, gu, gf) + pre_f2[gu * RB + gf], 0.f), tag);
+                publish4(P.y2 + (par * B + gf) * RH + u0, yw, lane, gate);
             }
-            RPROF(3);
-            if (t + 1 < S) {
-                load_cb3(t + 1);
-                bar_sync(BAR_D, 128);                              // also: epilogue reads of pre_f1/pre_f2 done
-                cond34();
-            }
-            bar_sync(BAR_D, 128);
-            RPROF(4);
+        }
+        if (P.prof != nullptr) {                                                 // debug only: time fc2 by itself
+            __syncthreads();
+            RPROF(7);
         }
     }
-    if (prof_on) {
-        for (int i = 0; i < 8; i++) P.prof[32 + gid * 8 + i] = pacc[i];
+    if (prof_on)
+        for (int i = 0; i < 8; i++) P.prof[64 + cta * 8 + i] = pacc[i];
+    if (prof_on)
+        for (int i = 0; i < 256; i++) reinterpret_cast<int *>(P.prof + 64 + RNR * 8)[cta * 256 + i] = reinterpret_cast<int *>(smem + SM_HIST)[i];
+    if (prof_on && cta == 5)
+        for (int i = 0; i < 16; i++) P.prof[40 + i] = pacc[8 + i];
+    if (P.prof != nullptr && cta == 0 && tg == 0)
         for (int i = 0; i < 3; i++) P.prof[20 + gid * 3 + i] = dd.cnt[i];
-    }
 }
 
 __global__ void __launch_bounds__(RTH, 1) res_loop_kernel(const ResParams P) {
@@ -814,10 +856,12 @@ int res_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
     WRNN_TRY(ws_reserve(h, h->ws_sync, 128));                        // cleared by the caller once per run
     P.abort_flag = (int *)((char *)h->ws_sync.p + 64);
     static const bool prof_env = getenv("WRNN_PROF") != nullptr;
+    static const int exp_env = getenv("WRNN_EXP") ? atoi(getenv("WRNN_EXP")) : 0;
+    P.exp = exp_env;
     P.prof = nullptr;
     if (prof_env) {
-        WRNN_TRY(ws_reserve(h, h->ws_prof, 64 * sizeof(long long)));
-        WRNN_CUDA(h, cudaMemsetAsync(h->ws_prof.p, 0, 64 * sizeof(long long), st));
+        WRNN_TRY(ws_reserve(h, h->ws_prof, (64 + RNR * 8 + RNR * 128) * sizeof(long long)));
+        WRNN_CUDA(h, cudaMemsetAsync(h->ws_prof.p, 0, (64 + RNR * 8 + RNR * 128) * sizeof(long long), st));
         P.prof = (long long *)h->ws_prof.p;
     }
     WRNN_CUDA(h, cudaFuncSetAttribute(res_loop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem_bytes));
@@ -825,18 +869,44 @@ int res_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
     WRNN_CUDA(h, cudaLaunchCooperativeKernel((const void *)res_loop_kernel, dim3(p.G), dim3(RTH), args, p.smem_bytes, st));
     h->launches++;
     if (prof_env) {      // debugging aid: per-segment clocks of row CTA 0's groups and tail CTA 0 (synchronises!)
-        long long pr[64];
+        static long long pr[64 + RNR * 8 + RNR * 128];
         WRNN_CUDA(h, cudaMemcpyAsync(pr, h->ws_prof.p, sizeof pr, cudaMemcpyDeviceToHost, st));
         WRNN_CUDA(h, cudaStreamSynchronize(st));
         const double s = (double)a.S;
-        fprintf(stderr, "[wrnn prof] clocks/step  GA: wait=%.0f gather_h1=%.0f (job=%.0f barA=%.0f) gc2ga=%.0f gates=%.0f | GB: wait_xprev=%.0f gates1=%.0f "
-                        "gather_h1=%.0f job+pre=%.0f cond=%.0f | GC: gather_h2=%.0f job+cond=%.0f | GD: gather_x2=%.0f fc1=%.0f "
-                        "gather_y1=%.0f fc2=%.0f cond=%.0f | tail: gather_y2=%.0f fc3=%.0f sample=%.0f\n",
-                pr[32] / s, pr[33] / s, pr[36] / s, pr[37] / s, pr[34] / s, pr[35] / s, pr[40] / s, pr[41] / s, pr[42] / s, pr[43] / s, pr[44] / s,
-                pr[48] / s, pr[49] / s, pr[56] / s, pr[57] / s, pr[58] / s, pr[59] / s, pr[60] / s, pr[16] / s, pr[17] / s,
-                pr[18] / s);
-        fprintf(stderr, "[wrnn prof] per step, CTA 0 (probe spins, fallback slots, fallback spins): GA %.1f %.2f %.1f | GB %.1f %.2f %.1f | GC %.1f %.2f %.1f | GD %.1f %.2f %.1f\n",
-                pr[20] / s, pr[21] / s, pr[22] / s, pr[23] / s, pr[24] / s, pr[25] / s, pr[26] / s, pr[27] / s, pr[28] / s, pr[29] / s, pr[30] / s, pr[31] / s);
+        static const char *names[8] = {"shadow", "wait_xprev", "gates1+exch_h1", "rnn2", "exch_x2", "fc1", "exch_y1", "fc2"};
+        fprintf(stderr, "[wrnn prof] row CTA clocks/step, min/mean/max over %d CTAs:", RNR);
+        for (int i = 0; i < 8; i++) {
+            double mn = 1e30, mx = 0, sum = 0;
+            for (int c = 0; c < RNR; c++) {
+                const double v = pr[64 + c * 8 + i] / s;
+                mn = v < mn ? v : mn;
+                mx = v > mx ? v : mx;
+                sum += v;
+            }
+            fprintf(stderr, " %s=%.0f/%.0f/%.0f", names[i], mn, sum / RNR, mx);
+        }
+        fprintf(stderr, " | CTA 5 per-step min..max:");
+        for (int i = 0; i < 8; i++) fprintf(stderr, " %s=%lld..%lld", names[i], pr[48 + i], pr[40 + i]);
+        fprintf(stderr, " | tail 0: gather_y2=%.0f fc3=%.0f sample=%.0f\n", pr[16] / s, pr[17] / s, pr[18] / s);
+        if (getenv("WRNN_PROF_HIST")) {
+            const int *hist = reinterpret_cast<const int *>(pr + 64 + RNR * 8);
+            for (int i = 0; i < 8; i++) {
+                fprintf(stderr, "[wrnn prof] hist %-15s (512-clk buckets, %% of CTA-steps):", names[i]);
+                for (int b = 0; b < 32; b++) {
+                    double n = 0;
+                    for (int c = 0; c < RNR; c++) n += hist[c * 256 + i * 32 + b];
+                    fprintf(stderr, " %.1f", 100.0 * n / (s * RNR));
+                }
+                fprintf(stderr, "\n");
+            }
+        }
+        if (getenv("WRNN_PROF_CTAS")) {
+            for (int c = 0; c < RNR; c++) {
+                fprintf(stderr, "[wrnn prof] cta %3d:", c);
+                for (int i = 0; i < 8; i++) fprintf(stderr, " %6.0f", pr[64 + c * 8 + i] / s);
+                fprintf(stderr, "\n");
+            }
+        }
     }
     return 0;
 }
