@@ -59,30 +59,33 @@ struct ResParams {
     const float *img;            // [128][IMG_FLOATS]
     const float *tail_img;       // [32][512] fc3 rows (zero padded) | bias[32]
     LoopArgs a;
-    float *h1, *h2, *x2, *y1, *y2;           // [2][B][512] tagged words
+    float *h1, *h2, *x2, *y1, *y2;           // [2][B][512] tagged words (h2: unused since h2 = x2' - h1 is formed locally)
     unsigned long long *xprev;               // [2][RB]
     int *abort_flag;
     long long *prof;
     int exp;                                 // WRNN_EXP bit set: schedule experiments (debug)
+    int d1, d2;                              // WRNN_D1 / WRNN_D2: override the gather delays (debug)
 };
 
 // shared memory carve (floats)
 constexpr int SM_H1 = 0;                          // [20][512] h1(t)            (GA + GB)
 constexpr int SM_H2 = SM_H1 + RB * RH;            // [20][512] h2(t)            (GC)
 constexpr int SM_X = SM_H2 + RB * RH;             // [20][512] x2'(t) / y1(t)   (GD)
-constexpr int SM_CB1 = SM_X + RB * RH;            // [20][128]
-constexpr int SM_CB2 = SM_CB1 + RB * CB1;         // [20][160]
-constexpr int SM_CB3 = SM_CB2 + RB * CB2;         // [20][192]
-constexpr int SM_RED = SM_CB3 + RB * CB3;         // [4 groups][4 warps][4 fold groups][32]
-constexpr int SM_PRE = SM_RED + 4 * 512;          // pre_h1[12][20] pre_h2 pre_i1 pre_i2 (240 each) pre_f1[4][20] pre_f2 (80 each)
-constexpr int SM_HST = SM_PRE + 4 * 240 + 2 * 80; // hst1[4][20] hst2[4][20]
+constexpr int GATHER_DELAY_H1 = 700, GATHER_DELAY = 700, GATHER_RETRY_PAUSE = 0;   // clocks, see gather_cta
+constexpr int CBL = 224;                          // conditioning row stride in smem: F + 4 A <= 96 + 128 floats
+constexpr int SM_CB = SM_X + RB * RH;             // [2][20][224] whole conditioning rows of steps t, t+1 (TMA bulk copies)
+constexpr int SM_MBAR = SM_CB + 2 * RB * CBL;     // two mbarriers (8 bytes each), one per conditioning buffer
+constexpr int SM_RED = SM_MBAR + 8;               // (+ one more mbarrier for the TMA gathers)  [4 groups][4 warps][4 fold groups][32]
+constexpr int SM_PRE = SM_RED + 4 * 512;          // pre_h1[12][20] pre_h2 | by step parity: pre_i1[2][12][20] pre_i2[2][..] pre_f1[2][4][20] pre_f2[2][..]
+constexpr int SM_HST = SM_PRE + 6 * 240 + 4 * 80; // hst1[4][20] hst2[4][20]
 constexpr int SM_XP = SM_HST + 160;               // xpA[32] xpB[32] xpD[32]
 constexpr int SM_WC = SM_XP + 96;                 // conditioning matrices C1 [12][128] C2 [12][160] C3 [4][192]
 constexpr int SM_WCN = 12 * CB1 + 12 * CB2 + 4 * CB3;
 constexpr int SM_W0B = SM_WC + SM_WCN;            // w0[32] | biases[64] (copy of the image tail)
 constexpr int SM_PROF = SM_W0B + 96;              // [4 groups][8] 64-bit clock accumulators (debug)
 constexpr int SM_HIST = SM_PROF + 64 + 16 + 32;   // [8 phases][32 buckets of 512 clk] per-step duration histogram (debug)
-constexpr int SM_FLOATS = SM_HIST + 256;    // + per-group poll counters + 16 gather-phase accumulators (debug)
+constexpr int SM_GP = SM_HIST + 256;               // [4 groups][16 marks] 64-bit clock accumulators of the group leaders (debug)
+constexpr int SM_FLOATS = SM_GP + 128;    // + per-group poll counters + 16 gather-phase accumulators (debug)
 
 // ---------------------------------------------------------------------------- polling with a sticky abort
 struct Dead {
@@ -109,6 +112,26 @@ __device__ __forceinline__ void cp_async16(void *smem_dst, const void *gsrc) {
     const uint32_t s = (uint32_t)__cvta_generic_to_shared(smem_dst);
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gsrc) : "memory");
 }
+// TMA bulk copy global -> smem, completion counted in bytes on an mbarrier (async proxy: no registers, no
+// cp.async group, so it does not get in the way of the gathers' wait_group).
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(void *b, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(b)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(void *b, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(b)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(void *b, uint32_t parity) {
+    uint32_t ok;
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(ok) : "r"(smem_u32(b)), "r"(parity) : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t bytes, void *b) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(b)) : "memory");
+}
+
 __device__ __forceinline__ uint4 poll_slot(const uint4 *p, uint32_t tag, Dead &dd, int which = 0) {
     uint4 v = ld_relaxed_v4(p);
     if (!dd.dead && !tags_ok(v, tag)) {
@@ -271,7 +294,7 @@ struct CondW {
     float w[3][NJ];
 };
 template <int NJ>
-__device__ __forceinline__ void cond_job(const float *wsm, const float *cb, int ld, int B, const float *bias, float *pre,
+__device__ __forceinline__ void cond_job(const float *wsm, int ld, const float *cb, int B, const float *bias, float *pre,
                                          int wq, int lane) {
     __syncwarp();
     CondW<NJ> c;                                     // transient: the conditioning matrices live in smem
@@ -288,7 +311,7 @@ __device__ __forceinline__ void cond_job(const float *wsm, const float *cb, int 
             const int f = half * 10 + fl;
             float x[NJ];
 #pragma unroll
-            for (int j = 0; j < NJ; j++) x[j] = cb[f * ld + lane + 32 * j];
+            for (int j = 0; j < NJ; j++) x[j] = cb[f * CBL + lane + 32 * j];
 #pragma unroll
             for (int i = 0; i < 3; i++) {
                 float s = c.w[i][0] * x[0];
@@ -452,30 +475,77 @@ __device__ __forceinline__ long long clock_fenced() {       // the "memory" clob
 
 // CTA-wide gather of a tagged vector (n4 float4) into dense smem: every thread requests all its slots
 // (tid, tid + 512, ...: 5 at 20 folds) at once and re-polls the ones whose tag is not there yet.
+#define GMARK(k)                                                      \
+    do {                                                              \
+        if (gprof_on) {                                               \
+            const long long n__ = clock_fenced();                     \
+            gacc[k] += n__ - gpt;                                     \
+            gpt = n__;                                                \
+        }                                                             \
+        __syncwarp();                                                 \
+    } while (0)
+
 // CTA-wide gather of 40 KB of tagged words: every slot by cp.async.cg (L2 -> smem, no registers), all of a
-// thread's slots in flight at once, re-issued until the slot's four tags match.
-__device__ __forceinline__ void gather_cta(const float *src, int n4, float *dst, uint32_t tag, int tid, Dead &dd, int delay = 0) {
+// thread's slots in flight at once, re-issued (after a pause) until the slot's four tags match.
+// `delay` = clocks between the CTA's own publish and its first look at the others' data.  A bulk fetch that
+// arrives before the stores fails its tag check AND queues 5 MB of reads chip-wide in front of the stores it is
+// waiting for.  Measured on B200 per exchange: no delay 6.1 k clk, 500: 2.7 k, 700: 2.4 k, 900: 2.6 k (the fetch
+// itself is ~1.7 k); a publish counter polled by one thread per CTA instead of the delay: 3.4 k.
+__device__ __forceinline__ void spin_clocks(int n) {
+    const long long c0 = clock64();
+    while (clock64() - c0 < n) {}
+}
+__device__ __forceinline__ void gather_cta(const float *src, int n4, float *dst, uint32_t tag, int rank, int nth, int delay, Dead &dd) {
     const uint4 *s4 = reinterpret_cast<const uint4 *>(src);
     uint4 *d4 = reinterpret_cast<uint4 *>(dst);
-    unsigned todo = 0;
-#pragma unroll
-    for (int j = 0; j < 5; j++)
-        if (tid + j * RTH < n4) todo |= 1u << j;
     unsigned spins = 0;
     long long t0 = 0;
-    if (delay) {
-        const long long c0 = clock64();
-        while (clock64() - c0 < delay) {}
-    }
+    bool first = true;
+    spin_clocks(delay);
     for (;;) {
-#pragma unroll
-        for (int j = 0; j < 5; j++)
-            if (todo & (1u << j)) cp_async16(d4 + tid + j * RTH, s4 + tid + j * RTH);
+        bool any = false;
+#pragma unroll 2
+        for (int i = rank; i < n4; i += nth)
+            if (first || !tags_ok(d4[i], tag)) {
+                cp_async16(d4 + i, s4 + i);
+                any = true;
+            }
+        if (!any || dd.dead) break;
         asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
-#pragma unroll
-        for (int j = 0; j < 5; j++)
-            if ((todo & (1u << j)) && tags_ok(d4[tid + j * RTH], tag)) todo &= ~(1u << j);
-        if (todo == 0 || dd.dead) break;
+        if (!first) {
+            if (spins == 0) t0 = clock64();
+            if (poll_giveup(dd, t0, spins)) break;
+        }
+        first = false;
+    }
+    if (dd.cnt) atomicAdd(dd.cnt, spins);
+}
+
+// The same gather through the TMA unit: thread 0 issues ONE bulk copy of the whole vector (after the start-up
+// delay), everybody waits on the mbarrier, checks the tags of its own slots in smem and re-fetches the few
+// that lost the race with cp.async.  No thread is busy while the copy is in flight.
+__device__ __forceinline__ void gather_tma(const float *src, int n4, float *dst, uint32_t tag, int tid, int delay, void *mb, uint32_t parity,
+                                           Dead &dd) {
+    if (tid == 0) {
+        spin_clocks(delay);
+        mbar_expect_tx(mb, (uint32_t)n4 * 16u);
+        bulk_g2s(dst, src, (uint32_t)n4 * 16u, mb);
+    }
+    while (!mbar_try_wait(mb, parity)) {}
+    const uint4 *s4 = reinterpret_cast<const uint4 *>(src);
+    uint4 *d4 = reinterpret_cast<uint4 *>(dst);
+    unsigned spins = 0;
+    long long t0 = 0;
+    for (;;) {
+        bool any = false;
+#pragma unroll 5
+        for (int i = tid; i < n4; i += RTH)
+            if (!tags_ok(d4[i], tag)) {
+                cp_async16(d4 + i, s4 + i);
+                any = true;
+            }
+        if (!any || dd.dead) break;
+        asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
         if (spins == 0) t0 = clock64();
         if (poll_giveup(dd, t0, spins)) break;
     }
@@ -507,11 +577,12 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
     const int u0 = cta * RU;
     const float *img = P.img + (size_t)cta * IMG_FLOATS;
 
-    float *bufH1 = smem + SM_H1, *bufH2 = smem + SM_H2, *bufX = smem + SM_X;
-    float *cb1 = smem + SM_CB1, *cb2 = smem + SM_CB2, *cb3 = smem + SM_CB3;
+    float *bufH1 = smem + SM_H1, *bufY = smem + SM_H2, *bufX = smem + SM_X;     // h1 | y1 | x2' (turned into h2 in place)
+    float *cbuf = smem + SM_CB;
+    unsigned long long *mbar = reinterpret_cast<unsigned long long *>(smem + SM_MBAR);
     float *red = smem + SM_RED + gid * 512;
-    float *pre_h1 = smem + SM_PRE, *pre_h2 = pre_h1 + 240, *pre_i1 = pre_h2 + 240, *pre_i2 = pre_i1 + 240,
-          *pre_f1 = pre_i2 + 240, *pre_f2 = pre_f1 + 80;
+    float *pre_h1 = smem + SM_PRE, *pre_h2 = pre_h1 + 240, *pre_i1b = pre_h2 + 240, *pre_i2b = pre_i1b + 480,
+          *pre_f1b = pre_i2b + 480, *pre_f2b = pre_f1b + 160;
     float *hst1 = smem + SM_HST, *hst2 = hst1 + 80;
     float *xp = smem + SM_XP;
 
@@ -526,6 +597,8 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
     const float *b_i1 = bias, *b_i2 = bias + 12, *b_f1 = bias + 24, *b_f2 = bias + 28, *b_hh1 = bias + 32, *b_hh2 = bias + 44;
     const bool prof_on = P.prof != nullptr && tid == 0;          // every row CTA times its own phases
     long long *pacc = reinterpret_cast<long long *>(smem + SM_PROF), pt = 0;
+    const bool gprof_on = P.prof != nullptr && cta == 5 && tg == 0;      // group leaders of one CTA: finer marks
+    long long *gacc = reinterpret_cast<long long *>(smem + SM_GP) + gid * 16, gpt = 0;
 
     // ---- per-group register state: the weights live here for the whole call
     GruW w;                                   // GA: W_ih2a   GB: W_hh1   GC: W_hh2   GD: fc1 rows in a[0..3], fc2 rows in a[4], a[5], b[0], b[1]
@@ -548,57 +621,89 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
     if (gid == 1) for (int g = 0; g < 3; g++) w0r[g] = w0[g * RU + gu];
     if (gid == 3) w0r[0] = w0[24 + gu];
 
-    auto cond34 = [&]() {                     // GD: conditioning part of fc1 (m, a1, a3) and fc2 (a4), row wq
+    // GD: conditioning part of fc1 (m, a1, a3) and fc2 (a4), row wq.  The matrix image packs its columns as
+    // (m, a1, a3 | pad | a4 at 160); the row in smem is the whole (m, a1, a2, a3, a4), so a3 sits 32 further on.
+    auto cond34 = [&](const float *cb, float *pre_f1, float *pre_f2) {
         __syncwarp();
         float c3[5], c4;
+        int o3[5];
 #pragma unroll
-        for (int jj = 0; jj < 5; jj++) c3[jj] = wc3[wq * CB3 + lane + 32 * jj];
+        for (int jj = 0; jj < 5; jj++) {
+            c3[jj] = wc3[wq * CB3 + lane + 32 * jj];
+            o3[jj] = lane + 32 * jj + (lane + 32 * jj < Kc ? 0 : 32);
+        }
         c4 = wc3[wq * CB3 + 160 + lane];
+        const int o4 = Kc + 64 + lane;
         float v[32];
 #pragma unroll
         for (int i = 20; i < 32; i++) v[i] = 0.f;
 #pragma unroll
         for (int f = 0; f < RB; f++) {
-            float s = c3[0] * cb3[f * CB3 + lane];
+            float s = c3[0] * cb[f * CBL + o3[0]];
 #pragma unroll
-            for (int jj = 1; jj < 5; jj++) s = fmaf(c3[jj], cb3[f * CB3 + lane + 32 * jj], s);
+            for (int jj = 1; jj < 5; jj++) s = fmaf(c3[jj], cb[f * CBL + o3[jj]], s);
             v[f] = s;
         }
         warp_reduce_scatter<32>(v, lane);
         if (lane < B) pre_f1[wq * RB + lane] = v[0] + b_f1[wq];
 #pragma unroll
-        for (int f = 0; f < RB; f++) v[f] = c4 * cb3[f * CB3 + 160 + lane];
+        for (int f = 0; f < RB; f++) v[f] = c4 * cb[f * CBL + o4];
 #pragma unroll
         for (int i = 20; i < 32; i++) v[i] = 0.f;
         warp_reduce_scatter<32>(v, lane);
         if (lane < B) pre_f2[wq * RB + lane] = v[0] + b_f2[wq];
     };
-    auto load_cb3 = [&](int64_t t) {
-        const float *ct = P.a.cond + (size_t)t * CW;
-        load_cond(ct, cstride, B, 0, Kc, cb3, CB3, 0, 128, tg);                 // m, a1
-        load_cond(ct, cstride, B, Kc + 32, 32, cb3, CB3, Kc, 128, tg);          // a3
-        load_cond(ct, cstride, B, Kc + 64, 32, cb3, CB3, 160, 128, tg);         // a4
+    // Conditioning rows of step t (all folds, whole row) -> buffer t & 1, by warp 0: one bulk copy per fold.
+    auto fetch_cond = [&](int64_t t) {
+        if (tid < 32) {
+            unsigned long long *mb = mbar + (t & 1);
+            if (lane == 0) mbar_expect_tx(mb, (uint32_t)(B * CW * sizeof(float)));
+            __syncwarp();
+            if (lane < B) bulk_g2s(cbuf + ((size_t)(t & 1) * RB + lane) * CBL, P.a.cond + (size_t)lane * cstride + (size_t)t * CW,
+                                   (uint32_t)(CW * sizeof(float)), mb);
+        }
     };
+    if (tid == 0) {
+        mbar_init(mbar, 1);
+        mbar_init(mbar + 1, 1);
+        mbar_init(mbar + 2, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // the zero fill above, before the first bulk copy lands
+    __syncthreads();
+    fetch_cond(0);
 
+    // Conditioning terms of step t -> pre_*[t & 1]; GB, GC and GD each do theirs (needs cond(t) in smem).
+    auto cond_step = [&](int64_t t, bool gb, bool gc, bool gd) {
+        const float *cb = cbuf + (size_t)(t & 1) * RB * CBL;
+        const int pp = (int)(t & 1);
+        if ((gid == 1 && gb) || (gid == 2 && gc) || (gid == 3 && gd))
+            while (!mbar_try_wait(mbar + pp, (uint32_t)((t >> 1) & 1))) {}
+        GMARK(15);
+        if (gid == 1 && gb) cond_job<4>(wc1, CB1, cb, B, b_i1, pre_i1b + pp * 240, wq, lane);
+        else if (gid == 2 && gc) cond_job<5>(wc2, CB2, cb, B, b_i2, pre_i2b + pp * 240, wq, lane);
+        else if (gid == 3 && gd) cond34(cb, pre_f1b + pp * 80, pre_f2b + pp * 80);
+    };
+    cond_step(0, true, true, true);
     // bufH1 / bufH2 are zero here (h = 0 at t = 0, :194-195), so the first shadow pass yields pre_h = b_hh.
     __syncthreads();
     pt = clock64();
+    gpt = pt;
 
-    // Clocks between a CTA's own publish and its first look at the others' data.  A bulk fetch that arrives before
-    // the stores fails its tag check AND queues 5 MB of reads in front of those stores chip-wide; measured on B200:
-    // no delay 6.1 k clk per exchange, 500: 2.7 k, 700: 2.4 k, 900: 2.6 k (the fetch itself is ~1.7 k).
-    const int gdelay = (P.exp >> 4) ? (P.exp >> 4) * 100 : 700;
+    const int d1 = P.d1 ? P.d1 : GATHER_DELAY_H1, d2 = P.d2 ? P.d2 : GATHER_DELAY;
+    uint32_t gpar = 0;                                   // phase parity of the gather mbarrier
+    const bool use_tma = !(P.exp & 2);
     for (int64_t t = 0; t < S; t++) {
         const uint32_t tag = (uint32_t)((t + 1) & 3);
         const size_t par = (size_t)(t & 1);
         // ---- P: everything step t needs that does not depend on sample t-1; for t > 0 this runs while the
         //         tail CTAs turn y2(t-1) into that sample
+        const float *pre_i1 = pre_i1b + (t & 1) * 240, *pre_i2 = pre_i2b + (t & 1) * 240, *pre_f1 = pre_f1b + (t & 1) * 80,
+                    *pre_f2 = pre_f2b + (t & 1) * 80;
+        if (t + 1 < S) fetch_cond(t + 1);                  // its buffer was last read two steps ago
         if (gid == 1 || gid == 2) {
             const bool g1 = gid == 1;
-            if (!(P.exp & 8)) gru_job(w, g1 ? bufH1 : bufH2, FG, red, wq, lane);
-            float *cb = g1 ? cb1 : cb2;
-            const int ldc = g1 ? CB1 : CB2;
-            load_cond(P.a.cond + (size_t)t * CW, cstride, B, 0, g1 ? Kc : Kc + 32, cb, ldc, 0, 128, tg);
+            if (!(P.exp & 8)) gru_job(w, g1 ? bufH1 : bufX, FG, red, wq, lane);
             bar_sync(g1 ? BAR_B : BAR_C, 128);
             float *pre_h = g1 ? pre_h1 : pre_h2;
             const float *b_hh = g1 ? b_hh1 : b_hh2;
@@ -607,21 +712,15 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
                 const int r = i / RB, f = i - r * RB;
                 pre_h[i] = gru_out(red, r, f) + b_hh[r];
             }
-            if (!(P.exp & 8)) {
-                if (g1) cond_job<4>(wc1, cb1, CB1, B, b_i1, pre_i1, wq, lane);
-                else cond_job<5>(wc2, cb2, CB2, B, b_i2, pre_i2, wq, lane);
-            }
-        } else if (gid == 3) {
-            load_cb3(t);
-            bar_sync(BAR_D, 128);
-            if (!(P.exp & 8)) cond34();
         }
         __syncthreads();                                                         // S5
         RPROF(0);
+        GMARK(0);
         // ---- T0: previous sample
         if (tid < B) xp[tid] = poll_xprev(P.xprev + par * RB + tid, (uint32_t)(t + 1), dd);
         __syncthreads();                                                         // S0
         RPROF(1);
+        GMARK(1);
         // ---- T1: rnn1 gates (GB)
         if (gid == 1 && tg < 96) {
             uint32_t hw = tag;
@@ -638,10 +737,19 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
             publish4(P.h1 + (par * B + gf) * RH + u0, hw, lane, gate);
         }
         __syncthreads();                                    // S0b: as S1b
-        // ---- T2: gather h1(t)
-        gather_cta(P.h1 + par * B * RH, B * (RH / 4), bufH1, tag, tid, dd, gdelay);
+        GMARK(2);
+        // ---- T2: gather h1(t).  The start-up delay of each gather is where the conditioning terms of step t+1 are
+        //         formed: GB's and GD's here, GC's in the next one.
+        const bool more = t + 1 < S && !(P.exp & 8);
+        if (more) cond_step(t + 1, true, false, true);
+        GMARK(3);
+        if (use_tma) { gather_tma(P.h1 + par * B * RH, B * (RH / 4), bufH1, tag, tid, d1, mbar + 2, gpar, dd); gpar ^= 1; }
+        else if (!more) gather_cta(P.h1 + par * B * RH, B * (RH / 4), bufH1, tag, tid, RTH, d1, dd);
+        else if (gid == 0 || gid == 2) gather_cta(P.h1 + par * B * RH, B * (RH / 4), bufH1, tag, (gid >> 1) * 128 + tg, 256, d1, dd);
+        GMARK(4);
         __syncthreads();                                                         // S1
         RPROF(2);
+        GMARK(5);
         // ---- T3: rnn2 (GA, alone on the SM)
         if (gid == 0) {
             if (!(P.exp & 4)) gru_job(w, bufH1, FG, red, wq, lane);
@@ -661,13 +769,20 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
                 publish4(P.x2 + (par * B + gf) * RH + u0, xw, lane, gate);
             }
         }
-        __syncthreads();                                    // S1b: nobody polls x2' while it is still being computed
+        __syncthreads();                                    // S1b: nobody looks at x2' while it is still being computed
         RPROF(3);
+        GMARK(6);
         // ---- T4: gather x2'(t)
-        gather_cta(P.x2 + par * B * RH, B * (RH / 4), bufX, tag, tid, dd, gdelay);
+        if (more) cond_step(t + 1, false, true, false);
+        GMARK(7);
+        if (use_tma) { gather_tma(P.x2 + par * B * RH, B * (RH / 4), bufX, tag, tid, d2, mbar + 2, gpar, dd); gpar ^= 1; }
+        else if (!more) gather_cta(P.x2 + par * B * RH, B * (RH / 4), bufX, tag, tid, RTH, d2, dd);
+        else if (gid != 2) gather_cta(P.x2 + par * B * RH, B * (RH / 4), bufX, tag, (gid == 3 ? 256 : gid * 128) + tg, 384, d2, dd);
+        GMARK(8);
         __syncthreads();                                                         // S2
         RPROF(4);
-        // ---- T5: fc1 (GD); h2 = x2' - h1 for the next shadow product (GC)
+        GMARK(9);
+        // ---- T5: fc1 (GD)
         if (gid == 3) {
             if (!(P.exp & 4)) fc_job(w.a[0], w.a[1], w.a[2], w.a[3], bufX, FG, red, wq, lane, tg);
             bar_sync(BAR_D, 128);
@@ -676,24 +791,31 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
                 if (gate) yw = tag_word(fmaxf(fc_out(red, gu, gf) + fmaf(w0r[0], xp[gf], pre_f1[gu * RB + gf]), 0.f), tag);
                 publish4(P.y1 + (par * B + gf) * RH + u0, yw, lane, gate);
             }
-        } else if (gid == 2) {
-            const float4 *a4 = reinterpret_cast<const float4 *>(bufX), *b4 = reinterpret_cast<const float4 *>(bufH1);
-            float4 *c4 = reinterpret_cast<float4 *>(bufH2);
-#pragma unroll 2
+        }
+        __syncthreads();                                                         // S3: fc1 has read x2'
+        RPROF(5);
+        GMARK(10);
+        // ---- T6: gather y1(t); meanwhile GC turns x2' into h2 = x2' - h1 in place for the next shadow product
+        //         (saves exchanging h2)
+        if (gid == 2) {
+            float4 *a4 = reinterpret_cast<float4 *>(bufX);
+            const float4 *b4 = reinterpret_cast<const float4 *>(bufH1);
+#pragma unroll 4
             for (int i = tg; i < B * (RH / 4); i += 128) {
                 const float4 a = a4[i], b = b4[i];
-                c4[i] = make_float4(a.x - b.x, a.y - b.y, a.z - b.z, a.w - b.w);
+                a4[i] = make_float4(a.x - b.x, a.y - b.y, a.z - b.z, a.w - b.w);
             }
         }
-        __syncthreads();                                                         // S3: bufX may be overwritten
-        RPROF(5);
-        // ---- T6: gather y1(t)
-        gather_cta(P.y1 + par * B * RH, B * (RH / 4), bufX, tag, tid, dd, gdelay);
+        GMARK(11);
+        if (use_tma) { gather_tma(P.y1 + par * B * RH, B * (RH / 4), bufY, tag, tid, d2, mbar + 2, gpar, dd); gpar ^= 1; }
+        else if (gid != 2) gather_cta(P.y1 + par * B * RH, B * (RH / 4), bufY, tag, (gid == 3 ? 256 : gid * 128) + tg, 384, d2, dd);
+        GMARK(12);
         __syncthreads();                                                         // S4
         RPROF(6);
+        GMARK(13);
         // ---- T7: fc2 (GD)
         if (gid == 3) {
-            if (!(P.exp & 4)) fc_job(w.a[4], w.a[5], w.b[0], w.b[1], bufX, FG, red, wq, lane, tg);
+            if (!(P.exp & 4)) fc_job(w.a[4], w.a[5], w.b[0], w.b[1], bufY, FG, red, wq, lane, tg);
             bar_sync(BAR_D, 128);
             if (tg < 96) {
                 uint32_t yw = tag;
@@ -701,15 +823,18 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
                 publish4(P.y2 + (par * B + gf) * RH + u0, yw, lane, gate);
             }
         }
-        if (P.prof != nullptr) {                                                 // debug only: time fc2 by itself
-            __syncthreads();
-            RPROF(7);
-        }
+        GMARK(14);
+        // S4b: fc2 is on the chain, the shadow products are not.  Without this barrier GB and GC start them while
+        // GD is still in fc2, sharing its FMA and LDS bandwidth (measured: 17.1 us per step without, 13.6 with).
+        if (!(P.exp & 64)) __syncthreads();
+        RPROF(7);
     }
     if (prof_on)
         for (int i = 0; i < 8; i++) P.prof[64 + cta * 8 + i] = pacc[i];
     if (prof_on)
         for (int i = 0; i < 256; i++) reinterpret_cast<int *>(P.prof + 64 + RNR * 8)[cta * 256 + i] = reinterpret_cast<int *>(smem + SM_HIST)[i];
+    if (gprof_on)
+        for (int i = 0; i < 16; i++) P.prof[64 + RNR * 8 + RNR * 128 + gid * 16 + i] = gacc[i];
     if (prof_on && cta == 5)
         for (int i = 0; i < 16; i++) P.prof[40 + i] = pacc[8 + i];
     if (P.prof != nullptr && cta == 0 && tg == 0)
@@ -858,10 +983,13 @@ int res_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
     static const bool prof_env = getenv("WRNN_PROF") != nullptr;
     static const int exp_env = getenv("WRNN_EXP") ? atoi(getenv("WRNN_EXP")) : 0;
     P.exp = exp_env;
+    static const int d1_env = getenv("WRNN_D1") ? atoi(getenv("WRNN_D1")) : 0, d2_env = getenv("WRNN_D2") ? atoi(getenv("WRNN_D2")) : 0;
+    P.d1 = d1_env;
+    P.d2 = d2_env;
     P.prof = nullptr;
     if (prof_env) {
-        WRNN_TRY(ws_reserve(h, h->ws_prof, (64 + RNR * 8 + RNR * 128) * sizeof(long long)));
-        WRNN_CUDA(h, cudaMemsetAsync(h->ws_prof.p, 0, (64 + RNR * 8 + RNR * 128) * sizeof(long long), st));
+        WRNN_TRY(ws_reserve(h, h->ws_prof, (128 + RNR * 8 + RNR * 128) * sizeof(long long)));
+        WRNN_CUDA(h, cudaMemsetAsync(h->ws_prof.p, 0, (128 + RNR * 8 + RNR * 128) * sizeof(long long), st));
         P.prof = (long long *)h->ws_prof.p;
     }
     WRNN_CUDA(h, cudaFuncSetAttribute(res_loop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem_bytes));
@@ -869,7 +997,7 @@ int res_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
     WRNN_CUDA(h, cudaLaunchCooperativeKernel((const void *)res_loop_kernel, dim3(p.G), dim3(RTH), args, p.smem_bytes, st));
     h->launches++;
     if (prof_env) {      // debugging aid: per-segment clocks of row CTA 0's groups and tail CTA 0 (synchronises!)
-        static long long pr[64 + RNR * 8 + RNR * 128];
+        static long long pr[128 + RNR * 8 + RNR * 128];
         WRNN_CUDA(h, cudaMemcpyAsync(pr, h->ws_prof.p, sizeof pr, cudaMemcpyDeviceToHost, st));
         WRNN_CUDA(h, cudaStreamSynchronize(st));
         const double s = (double)a.S;
@@ -888,6 +1016,16 @@ int res_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
         fprintf(stderr, " | CTA 5 per-step min..max:");
         for (int i = 0; i < 8; i++) fprintf(stderr, " %s=%lld..%lld", names[i], pr[48 + i], pr[40 + i]);
         fprintf(stderr, " | tail 0: gather_y2=%.0f fc3=%.0f sample=%.0f\n", pr[16] / s, pr[17] / s, pr[18] / s);
+        if (getenv("WRNN_PROF_GROUPS")) {
+            static const char *marks[15] = {"S5", "S0", "S0b", "work_h1", "fetch_h1", "S1", "S1b", "work_x2", "fetch_x2", "S2", "S3", "work_y1",
+                                            "fetch_y1", "S4", "end"};
+            for (int g = 0; g < 4; g++) {
+                fprintf(stderr, "[wrnn prof] CTA 5 group %c leader, clocks since its previous mark:", "ABCD"[g]);
+                for (int k = 0; k < 15; k++) fprintf(stderr, " %s=%.0f", marks[k], pr[64 + RNR * 8 + RNR * 128 + g * 16 + k] / s);
+                fprintf(stderr, " (cond wait=%.0f)", pr[64 + RNR * 8 + RNR * 128 + g * 16 + 15] / s);
+                fprintf(stderr, "\n");
+            }
+        }
         if (getenv("WRNN_PROF_HIST")) {
             const int *hist = reinterpret_cast<const int *>(pr + 64 + RNR * 8);
             for (int i = 0; i < 8; i++) {
