@@ -37,7 +37,7 @@ constexpr int RB = 20;           // folds per launch
 constexpr int RH = 512;          // rnn_dims == fc_dims
 constexpr int RNR = 128;         // row CTAs (4 units each)
 constexpr int RU = 4;
-constexpr int CB1 = 128, CB2 = 160, CB3 = 192;   // conditioning row strides in smem (zero padded)
+constexpr int WCL = 224;                          // row stride of the conditioning matrix: F + 4 A <= 96 + 128 floats
 
 // per-row-CTA weight image in global memory (floats)
 constexpr int IMG_IH2 = 0;                        // [12][512]  W_ih2[:, :512]   rows gate-major (g*4 + u)
@@ -45,10 +45,13 @@ constexpr int IMG_HH1 = IMG_IH2 + 12 * RH;        // [12][512]
 constexpr int IMG_HH2 = IMG_HH1 + 12 * RH;        // [12][512]
 constexpr int IMG_F1 = IMG_HH2 + 12 * RH;         // [4][512]   fc1[:, :512]
 constexpr int IMG_F2 = IMG_F1 + 4 * RH;           // [4][512]   fc2[:, :512]
-constexpr int IMG_C1 = IMG_F2 + 4 * RH;           // [12][128]  (W_ih1 W_I)[:, 1:]            cols (m, a1)
-constexpr int IMG_C2 = IMG_C1 + 12 * CB1;         // [12][160]  (W_ih2a W_I)[:, 1:] | W_ih2b  cols (m, a1, a2)
-constexpr int IMG_C3 = IMG_C2 + 12 * CB2;         // [4][192]   (W_f1a W_I)[:, 1:] | W_f1b | W_f2b   cols (m, a1, a3, a4)
-constexpr int IMG_W0 = IMG_C3 + 4 * CB3;          // [32] column 0 (x_prev): i1[12] i2[12] f1[4] pad[4]
+// Conditioning matrix over the whole row (m, a1, a2, a3, a4) of a step, zero where a layer does not read:
+//   rows  0..11  (W_ih1 W_I)[:, 1:]                       cols (m, a1)
+//   rows 12..23  (W_ih2a W_I)[:, 1:] | W_ih2b             cols (m, a1, a2)
+//   rows 24..27  (W_f1a W_I)[:, 1:]  | W_f1b              cols (m, a1, a3)
+//   rows 28..31  W_f2b                                    cols (a4)
+constexpr int IMG_CU = IMG_F2 + 4 * RH;           // [32][WCL]
+constexpr int IMG_W0 = IMG_CU + 32 * WCL;         // [32] column 0 (x_prev): i1[12] i2[12] f1[4] pad[4]
 constexpr int IMG_B = IMG_W0 + 32;                // [64] biases: i1[12] i2[12] f1[4] f2[4] hh1[12] hh2[12] pad
 constexpr int IMG_FLOATS = IMG_B + 64;
 
@@ -63,36 +66,35 @@ struct ResParams {
     unsigned long long *xprev;               // [2][RB]
     int *abort_flag;
     long long *prof;
-    int exp;                                 // WRNN_EXP bit set: schedule experiments (debug)
-    int d1, d2;                              // WRNN_D1 / WRNN_D2: override the gather delays (debug)
+    int d1, d2, d3;                          // WRNN_D1 / _D2 / _D3: override the gather delays of h1, x2', y1 (debug)
 };
 
 // shared memory carve (floats)
-constexpr int SM_H1 = 0;                          // [20][512] h1(t)            (GA + GB)
-constexpr int SM_H2 = SM_H1 + RB * RH;            // [20][512] h2(t)            (GC)
-constexpr int SM_X = SM_H2 + RB * RH;             // [20][512] x2'(t) / y1(t)   (GD)
-constexpr int GATHER_DELAY_H1 = 700, GATHER_DELAY = 700, GATHER_RETRY_PAUSE = 0;   // clocks, see gather_cta
-constexpr int CBL = 224;                          // conditioning row stride in smem: F + 4 A <= 96 + 128 floats
-constexpr int SM_CB = SM_X + RB * RH;             // [2][20][224] whole conditioning rows of steps t, t+1 (TMA bulk copies)
-constexpr int SM_MBAR = SM_CB + 2 * RB * CBL;     // two mbarriers (8 bytes each), one per conditioning buffer
-constexpr int SM_RED = SM_MBAR + 8;               // (+ one more mbarrier for the TMA gathers)  [4 groups][4 warps][4 fold groups][32]
-constexpr int SM_PRE = SM_RED + 4 * 512;          // pre_h1[12][20] pre_h2 | by step parity: pre_i1[2][12][20] pre_i2[2][..] pre_f1[2][4][20] pre_f2[2][..]
-constexpr int SM_HST = SM_PRE + 6 * 240 + 4 * 80; // hst1[4][20] hst2[4][20]
-constexpr int SM_XP = SM_HST + 160;               // xpA[32] xpB[32] xpD[32]
-constexpr int SM_WC = SM_XP + 96;                 // conditioning matrices C1 [12][128] C2 [12][160] C3 [4][192]
-constexpr int SM_WCN = 12 * CB1 + 12 * CB2 + 4 * CB3;
+constexpr int SM_H1 = 0;                          // [20][512] h1(t)                                  (GA, GB)
+constexpr int SM_H2 = SM_H1 + RB * RH;            // [20][512] y1(t)                                  (GD)
+constexpr int SM_X = SM_H2 + RB * RH;             // [20][512] x2'(t), turned into h2(t) in place     (GD, GC)
+constexpr int GATHER_DELAY_H1 = 1700, GATHER_DELAY_X2 = 1200, GATHER_DELAY_Y1 = 700;   // clocks, see gather_issue
+constexpr int CBL = 228;                          // conditioning row stride in smem: >= 224, and 4 banks apart per fold (float4 reads by 8 lanes)
+constexpr int SM_CB = SM_X + RB * RH;             // [2][20][228] whole conditioning rows of steps t, t+1 (TMA bulk copies)
+constexpr int SM_MBAR = SM_CB + 2 * RB * CBL;     // three mbarriers (8 bytes each): conditioning buffer 0, 1, the gathers
+constexpr int SM_RED = SM_MBAR + 8;               // [4 groups][4 warps][4 fold groups][32]
+constexpr int SM_PRE = SM_RED + 4 * 512;          // pre_h1[12][20] pre_h2 | by step parity: [2][2 column halves][32 rows: i1 i2 f1 f2][20]
+constexpr int SM_HST = SM_PRE + 2 * 240 + 4 * 640; // hst1[4][20] hst2[4][20]
+constexpr int SM_XP = SM_HST + 160;               // x_prev[20] of the step
+constexpr int SM_WC = SM_XP + 96;                 // conditioning matrix [32][WCL]
+constexpr int SM_WCN = 32 * WCL;
 constexpr int SM_W0B = SM_WC + SM_WCN;            // w0[32] | biases[64] (copy of the image tail)
-constexpr int SM_PROF = SM_W0B + 96;              // [4 groups][8] 64-bit clock accumulators (debug)
+constexpr int SM_PROF = SM_W0B + 96;              // 64-bit clock accumulators: [8] sum, [8] max, [8] min per phase; poll counters (debug)
 constexpr int SM_HIST = SM_PROF + 64 + 16 + 32;   // [8 phases][32 buckets of 512 clk] per-step duration histogram (debug)
 constexpr int SM_GP = SM_HIST + 256;               // [4 groups][16 marks] 64-bit clock accumulators of the group leaders (debug)
-constexpr int SM_FLOATS = SM_GP + 128;    // + per-group poll counters + 16 gather-phase accumulators (debug)
+constexpr int SM_FLOATS = SM_GP + 128;
 
 // ---------------------------------------------------------------------------- polling with a sticky abort
 struct Dead {
     bool dead;
     const int *flag;
     int *flag_w;
-    unsigned long long *gacc;   // debug, CTA 0 only: per gather [first slot valid, cp.async landed, validated] thread-clock sums
+    unsigned long long *gacc;   // unused
     unsigned int *cnt;      // debug counters in smem (null unless WRNN_PROF): [0] probe spins, [1] fallback slots, [2] fallback spins
 };
 __device__ __forceinline__ bool poll_giveup(Dead &dd, long long t0, unsigned &spins) {
@@ -287,44 +289,46 @@ __device__ __forceinline__ float fc_out(const float *red, int r, int f) {
     return s;
 }
 
-// Conditioning job: warp wq owns rows 3*wq .. 3*wq+2 of a [12][ld] matrix, lane owns columns lane + 32*j
-// (j < NJ).  pre[row][f] = sum + bias for every fold (60 partials per lane, reduce-scatter of 64).
-template <int NJ>
-struct CondW {
-    float w[3][NJ];
-};
-template <int NJ>
-__device__ __forceinline__ void cond_job(const float *wsm, int ld, const float *cb, int B, const float *bias, float *pre,
-                                         int wq, int lane) {
-    __syncwarp();
-    CondW<NJ> c;                                     // transient: the conditioning matrices live in smem
+// Conditioning terms of one step for all 32 rows and all folds, by the whole CTA.  K is ~128 here, so splitting it
+// over lanes would spend more on the cross-lane reduction than on the FMAs; instead a thread owns whole outputs:
+// lane f < 20 takes fold f, warp w takes four rows of one layer (block w >> 1: i1 rows 0-3 / 4-7 / 8-11, i2 rows
+// 12-15 / 16-19 / 20-23, f1 rows 24-27, f2 rows 28-31) over one half (w & 1) of that layer's columns.  The job is
+// bound by shared-memory bandwidth (128 B/clk): per float4 column a warp reads four matrix words (broadcast, one
+// wavefront each) and one activation word (20 lanes 4 banks apart, three wavefronts), i.e. 1.75 wavefronts per
+// row-word; with one or two rows per pass it was 4 and 2.5 and took 4-5 k clk.
+// part[half][row][f]: the two halves are added by the consumer (pre2), bias is folded into half 0.
+// It is done in two portions, each inside the idle time of one exchange: `second` = false does i1, f1 and f2 (warps
+// 0-9), true does i2 (warps 0-5).
+__device__ __forceinline__ void cond_all(const float *wcu, const float *cb, const float *bias, float *part, int B, int Kc, int warp,
+                                         int lane, bool second) {
+    if (lane >= B || warp >= (second ? 6 : 10)) return;
+    const int task = warp >> 1, half = warp & 1;
+    const int blk = second ? 3 + task : (task < 3 ? task : task + 3), r0 = 4 * blk;
+    // column range the layer reads, in float4: i1 (m,a1)  i2 (m,a1,a2)  f1 (m,a1,[a2 = 0],a3)  f2 (a4)
+    const int c0 = blk < 7 ? 0 : (Kc + 64) >> 2;
+    const int c1 = blk < 3 ? Kc >> 2 : blk < 6 ? (Kc + 32) >> 2 : blk < 7 ? (Kc + 64) >> 2 : (Kc + 96) >> 2;
+    const int len = (c1 - c0) >> 1, ca = c0 + half * len, cb_ = half ? c1 : ca + len;
+    const float4 *x4 = reinterpret_cast<const float4 *>(cb + lane * CBL);
+    const float4 *w4 = reinterpret_cast<const float4 *>(wcu + r0 * WCL);
+    float s[4];
 #pragma unroll
-    for (int i = 0; i < 3; i++)
+    for (int i = 0; i < 4; i++) s[i] = half ? 0.f : bias[r0 + i];
+#pragma unroll 2
+    for (int c = ca; c < cb_; c++) {
+        const float4 x = x4[c];
 #pragma unroll
-        for (int j = 0; j < NJ; j++) c.w[i][j] = wsm[(3 * wq + i) * ld + lane + 32 * j];
-#pragma unroll 1
-    for (int half = 0; half < 2; half++) {          // ten folds at a time: 30 partials per lane
-        float v[32];
-        v[30] = v[31] = 0.f;
-#pragma unroll
-        for (int fl = 0; fl < 10; fl++) {
-            const int f = half * 10 + fl;
-            float x[NJ];
-#pragma unroll
-            for (int j = 0; j < NJ; j++) x[j] = cb[f * CBL + lane + 32 * j];
-#pragma unroll
-            for (int i = 0; i < 3; i++) {
-                float s = c.w[i][0] * x[0];
-#pragma unroll
-                for (int j = 1; j < NJ; j++) s = fmaf(c.w[i][j], x[j], s);
-                v[fl * 3 + i] = s;
-            }
+        for (int i = 0; i < 4; i++) {
+            const float4 w = w4[i * (WCL / 4) + c];
+            s[i] = fmaf(w.x, x.x, s[i]);
+            s[i] = fmaf(w.y, x.y, s[i]);
+            s[i] = fmaf(w.z, x.z, s[i]);
+            s[i] = fmaf(w.w, x.w, s[i]);
         }
-        warp_reduce_scatter<32>(v, lane);
-        const int fl = lane / 3, i = lane - 3 * fl, f = half * 10 + fl;
-        if (lane < 30 && f < B) pre[(3 * wq + i) * RB + f] = v[0] + bias[3 * wq + i];
     }
+#pragma unroll
+    for (int i = 0; i < 4; i++) part[half * 640 + (r0 + i) * RB + lane] = s[i];
 }
+__device__ __forceinline__ float pre2(const float *part, int idx) { return part[idx] + part[640 + idx]; }
 
 // ---------------------------------------------------------------------------- tail CTA: fc3 + sampling
 __device__ __forceinline__ float mol_sample_smem2(const float *logits, int nmix, float myu1, float u2, int lane, int *pick) {
@@ -485,52 +489,22 @@ __device__ __forceinline__ long long clock_fenced() {       // the "memory" clob
         __syncwarp();                                                 \
     } while (0)
 
-// CTA-wide gather of 40 KB of tagged words: every slot by cp.async.cg (L2 -> smem, no registers), all of a
-// thread's slots in flight at once, re-issued (after a pause) until the slot's four tags match.
-// `delay` = clocks between the CTA's own publish and its first look at the others' data.  A bulk fetch that
-// arrives before the stores fails its tag check AND queues 5 MB of reads chip-wide in front of the stores it is
-// waiting for.  Measured on B200 per exchange: no delay 6.1 k clk, 500: 2.7 k, 700: 2.4 k, 900: 2.6 k (the fetch
-// itself is ~1.7 k); a publish counter polled by one thread per CTA instead of the delay: 3.4 k.
+// CTA-wide gather of a 40 KB vector of tagged words through the TMA unit: one thread issues ONE bulk copy of the
+// whole vector `delay` clocks after the CTA's own publish, everybody else is free until it needs the data; then
+// each thread checks the tags of its own slots in smem and re-fetches the few that lost the race with cp.async.
+// Why the delay: a fetch that arrives before the stores fails its tag check AND queues 5 MB of reads chip-wide in
+// front of the stores it is waiting for.  Measured on B200 per exchange (cp.async version): no delay 6.1 k clk,
+// 500: 2.7 k, 700: 2.4 k, 900: 2.6 k; a publish counter polled by one thread per CTA instead of the delay: 3.4 k.
 __device__ __forceinline__ void spin_clocks(int n) {
     const long long c0 = clock64();
     while (clock64() - c0 < n) {}
 }
-__device__ __forceinline__ void gather_cta(const float *src, int n4, float *dst, uint32_t tag, int rank, int nth, int delay, Dead &dd) {
-    const uint4 *s4 = reinterpret_cast<const uint4 *>(src);
-    uint4 *d4 = reinterpret_cast<uint4 *>(dst);
-    unsigned spins = 0;
-    long long t0 = 0;
-    bool first = true;
+__device__ __forceinline__ void gather_issue(const float *src, int n4, float *dst, int delay, void *mb) {
     spin_clocks(delay);
-    for (;;) {
-        bool any = false;
-#pragma unroll 2
-        for (int i = rank; i < n4; i += nth)
-            if (first || !tags_ok(d4[i], tag)) {
-                cp_async16(d4 + i, s4 + i);
-                any = true;
-            }
-        if (!any || dd.dead) break;
-        asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
-        if (!first) {
-            if (spins == 0) t0 = clock64();
-            if (poll_giveup(dd, t0, spins)) break;
-        }
-        first = false;
-    }
-    if (dd.cnt) atomicAdd(dd.cnt, spins);
+    mbar_expect_tx(mb, (uint32_t)n4 * 16u);
+    bulk_g2s(dst, src, (uint32_t)n4 * 16u, mb);
 }
-
-// The same gather through the TMA unit: thread 0 issues ONE bulk copy of the whole vector (after the start-up
-// delay), everybody waits on the mbarrier, checks the tags of its own slots in smem and re-fetches the few
-// that lost the race with cp.async.  No thread is busy while the copy is in flight.
-__device__ __forceinline__ void gather_tma(const float *src, int n4, float *dst, uint32_t tag, int tid, int delay, void *mb, uint32_t parity,
-                                           Dead &dd) {
-    if (tid == 0) {
-        spin_clocks(delay);
-        mbar_expect_tx(mb, (uint32_t)n4 * 16u);
-        bulk_g2s(dst, src, (uint32_t)n4 * 16u, mb);
-    }
+__device__ __forceinline__ void gather_wait(const float *src, int n4, float *dst, uint32_t tag, int tid, void *mb, uint32_t parity, Dead &dd) {
     while (!mbar_try_wait(mb, parity)) {}
     const uint4 *s4 = reinterpret_cast<const uint4 *>(src);
     uint4 *d4 = reinterpret_cast<uint4 *>(dst);
@@ -552,21 +526,23 @@ __device__ __forceinline__ void gather_tma(const float *src, int n4, float *dst,
     if (dd.cnt) atomicAdd(dd.cnt, spins);
 }
 
-// Row CTA, bulk-synchronous schedule.  Per step (S* = __syncthreads):
-//   P  shadow  GB: W_hh1 . h1(t-1), rnn1 conditioning;  GC: W_hh2 . h2(t-1), rnn2 conditioning;  GD: fc conditioning
-//              -- nothing here needs sample t-1, so for t > 0 it runs while the tail CTAs do fc3 + sampling   S5
-//   T0 all     wait x_prev(t)                                   S0
-//   T1 GB      rnn1 gates -> publish h1(t)
-//   T2 all     gather h1(t)                                     S1
-//   T3 GA      W_ih2a . h1 (alone on the SM), rnn2 gates -> publish x2'(t) = h1 + h2      S1b
-//   T4 all     gather x2'(t)                                    S2
-//   T5 GD      fc1 -> publish y1(t);   GC: h2 = x2' - h1 (saves exchanging h2)      S3
-//   T6 all     gather y1(t)                                     S4
-//   T7 GD      fc2 -> publish y2(t)
-// The measured cost of one all-to-all round through L2 is 3-4.5 k clk whatever its size, so the schedule keeps
-// the SM free for the layer on the chain and pushes everything else into the tail window.  The loop body is
-// kept small on purpose (one call site per job, bounded unrolling): at > 128 KB of SASS the four groups'
-// instruction streams evict each other and every phase slows down.
+// Row CTA, bulk-synchronous schedule.  One layer is on the chain at a time and has the SM to itself; everything that
+// does not depend on the newest sample is moved off the chain.  Per step t (S* = __syncthreads):
+//   P   shadow   GB: W_hh1 . h1(t-1)   GC: W_hh2 . h2(t-1)   warp 0: TMA prefetch of the conditioning rows of t+1
+//                -- nothing here needs sample t-1, so for t > 0 it runs while the tail CTAs do fc3 + sampling     S5
+//   T0  all      wait x_prev(t)                                                                                   S0
+//   T1  GB       rnn1 gates -> publish h1(t)                                                                      S0b
+//   T2  all      exchange h1(t): one TMA bulk copy, issued GATHER_DELAY_H1 clocks after the publish; while it is
+//                in flight the CTA forms the conditioning terms i1, f1, f2 of step t+1 (cond_all)                 S1
+//   T3  GA       W_ih2a . h1, rnn2 gates -> publish x2'(t) = h1 + h2                                              S1b
+//   T4  all      exchange x2'(t); meanwhile conditioning terms i2 of step t+1                                     S2
+//   T5  GD       fc1 -> publish y1(t)                                                                             S3
+//   T6  all      exchange y1(t); meanwhile GC turns x2' into h2 = x2' - h1 in place (h2 is never exchanged)       S4
+//   T7  GD       fc2 -> publish y2(t) (the tail CTAs pick it up)                                                  S4b
+// Measured on B200 (clocks per step, 20 folds): P 5.4 k (two concurrent products), T0 0.9 k, T1+T2 4.7 k, T3 3.9 k,
+// T4 3.7 k, T5 2.5 k, T6 3.3 k, T7 2.6 k = 27 k = 13.7 us.  The products are bound by the LSU pipe (LDS + SHFL
+// wavefronts: 36 % of peak over the whole step, two products side by side take twice as long as one), the
+// exchanges by L2 round trips; see DESIGN.md section 4.
 __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
     const Dims &d = P.d;
     const int tid = threadIdx.x, gid = tid >> 7, tg = tid & 127, wq = tg >> 5, lane = tid & 31;
@@ -581,15 +557,14 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
     float *cbuf = smem + SM_CB;
     unsigned long long *mbar = reinterpret_cast<unsigned long long *>(smem + SM_MBAR);
     float *red = smem + SM_RED + gid * 512;
-    float *pre_h1 = smem + SM_PRE, *pre_h2 = pre_h1 + 240, *pre_i1b = pre_h2 + 240, *pre_i2b = pre_i1b + 480,
-          *pre_f1b = pre_i2b + 480, *pre_f2b = pre_f1b + 160;
+    float *pre_h1 = smem + SM_PRE, *pre_h2 = pre_h1 + 240, *pre_cb = pre_h2 + 240;      // pre_cb[2][2][32][20]
     float *hst1 = smem + SM_HST, *hst2 = hst1 + 80;
     float *xp = smem + SM_XP;
 
     for (int i = tid; i < SM_FLOATS; i += RTH) smem[i] = 0.f;
     __syncthreads();
-    for (int i = tid; i < SM_WCN + 96; i += RTH) smem[SM_WC + i] = __ldg(img + IMG_C1 + i);     // C1 | C2 | C3 | w0 | biases are contiguous
-    const float *wc1 = smem + SM_WC, *wc2 = wc1 + 12 * CB1, *wc3 = wc2 + 12 * CB2;
+    for (int i = tid; i < SM_WCN + 96; i += RTH) smem[SM_WC + i] = __ldg(img + IMG_CU + i);     // matrix | w0 | biases are contiguous
+    const float *wcu = smem + SM_WC;
     __syncthreads();
     Dead dd{false, P.abort_flag, P.abort_flag, nullptr,
             (P.prof != nullptr && cta == 0) ? reinterpret_cast<unsigned int *>(smem + SM_PROF + 64) + gid * 4 : nullptr};
@@ -621,38 +596,6 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
     if (gid == 1) for (int g = 0; g < 3; g++) w0r[g] = w0[g * RU + gu];
     if (gid == 3) w0r[0] = w0[24 + gu];
 
-    // GD: conditioning part of fc1 (m, a1, a3) and fc2 (a4), row wq.  The matrix image packs its columns as
-    // (m, a1, a3 | pad | a4 at 160); the row in smem is the whole (m, a1, a2, a3, a4), so a3 sits 32 further on.
-    auto cond34 = [&](const float *cb, float *pre_f1, float *pre_f2) {
-        __syncwarp();
-        float c3[5], c4;
-        int o3[5];
-#pragma unroll
-        for (int jj = 0; jj < 5; jj++) {
-            c3[jj] = wc3[wq * CB3 + lane + 32 * jj];
-            o3[jj] = lane + 32 * jj + (lane + 32 * jj < Kc ? 0 : 32);
-        }
-        c4 = wc3[wq * CB3 + 160 + lane];
-        const int o4 = Kc + 64 + lane;
-        float v[32];
-#pragma unroll
-        for (int i = 20; i < 32; i++) v[i] = 0.f;
-#pragma unroll
-        for (int f = 0; f < RB; f++) {
-            float s = c3[0] * cb[f * CBL + o3[0]];
-#pragma unroll
-            for (int jj = 1; jj < 5; jj++) s = fmaf(c3[jj], cb[f * CBL + o3[jj]], s);
-            v[f] = s;
-        }
-        warp_reduce_scatter<32>(v, lane);
-        if (lane < B) pre_f1[wq * RB + lane] = v[0] + b_f1[wq];
-#pragma unroll
-        for (int f = 0; f < RB; f++) v[f] = c4 * cb[f * CBL + o4];
-#pragma unroll
-        for (int i = 20; i < 32; i++) v[i] = 0.f;
-        warp_reduce_scatter<32>(v, lane);
-        if (lane < B) pre_f2[wq * RB + lane] = v[0] + b_f2[wq];
-    };
     // Conditioning rows of step t (all folds, whole row) -> buffer t & 1, by warp 0: one bulk copy per fold.
     auto fetch_cond = [&](int64_t t) {
         if (tid < 32) {
@@ -673,37 +616,31 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
     __syncthreads();
     fetch_cond(0);
 
-    // Conditioning terms of step t -> pre_*[t & 1]; GB, GC and GD each do theirs (needs cond(t) in smem).
-    auto cond_step = [&](int64_t t, bool gb, bool gc, bool gd) {
-        const float *cb = cbuf + (size_t)(t & 1) * RB * CBL;
+    // Conditioning terms of step t -> pre_cb[t & 1], by all 16 warps (needs cond(t) in smem).
+    auto cond_step = [&](int64_t t, bool second) {
         const int pp = (int)(t & 1);
-        if ((gid == 1 && gb) || (gid == 2 && gc) || (gid == 3 && gd))
-            while (!mbar_try_wait(mbar + pp, (uint32_t)((t >> 1) & 1))) {}
-        GMARK(15);
-        if (gid == 1 && gb) cond_job<4>(wc1, CB1, cb, B, b_i1, pre_i1b + pp * 240, wq, lane);
-        else if (gid == 2 && gc) cond_job<5>(wc2, CB2, cb, B, b_i2, pre_i2b + pp * 240, wq, lane);
-        else if (gid == 3 && gd) cond34(cb, pre_f1b + pp * 80, pre_f2b + pp * 80);
+        while (!mbar_try_wait(mbar + pp, (uint32_t)((t >> 1) & 1))) {}
+        cond_all(wcu, cbuf + (size_t)pp * RB * CBL, bias, pre_cb + pp * 1280, B, Kc, tid >> 5, lane, second);
     };
-    cond_step(0, true, true, true);
+    cond_step(0, false);
+    cond_step(0, true);
     // bufH1 / bufH2 are zero here (h = 0 at t = 0, :194-195), so the first shadow pass yields pre_h = b_hh.
     __syncthreads();
     pt = clock64();
     gpt = pt;
 
-    const int d1 = P.d1 ? P.d1 : GATHER_DELAY_H1, d2 = P.d2 ? P.d2 : GATHER_DELAY;
+    const int d1 = P.d1 ? P.d1 : GATHER_DELAY_H1, d2 = P.d2 ? P.d2 : GATHER_DELAY_X2, d3 = P.d3 ? P.d3 : GATHER_DELAY_Y1;
     uint32_t gpar = 0;                                   // phase parity of the gather mbarrier
-    const bool use_tma = !(P.exp & 2);
     for (int64_t t = 0; t < S; t++) {
         const uint32_t tag = (uint32_t)((t + 1) & 3);
         const size_t par = (size_t)(t & 1);
         // ---- P: everything step t needs that does not depend on sample t-1; for t > 0 this runs while the
         //         tail CTAs turn y2(t-1) into that sample
-        const float *pre_i1 = pre_i1b + (t & 1) * 240, *pre_i2 = pre_i2b + (t & 1) * 240, *pre_f1 = pre_f1b + (t & 1) * 80,
-                    *pre_f2 = pre_f2b + (t & 1) * 80;
+        const float *pre_i1 = pre_cb + (t & 1) * 1280, *pre_i2 = pre_i1 + 240, *pre_f1 = pre_i1 + 480, *pre_f2 = pre_i1 + 560;
         if (t + 1 < S) fetch_cond(t + 1);                  // its buffer was last read two steps ago
         if (gid == 1 || gid == 2) {
             const bool g1 = gid == 1;
-            if (!(P.exp & 8)) gru_job(w, g1 ? bufH1 : bufX, FG, red, wq, lane);
+            gru_job(w, g1 ? bufH1 : bufX, FG, red, wq, lane);
             bar_sync(g1 ? BAR_B : BAR_C, 128);
             float *pre_h = g1 ? pre_h1 : pre_h2;
             const float *b_hh = g1 ? b_hh1 : b_hh2;
@@ -726,9 +663,9 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
             uint32_t hw = tag;
             if (gate) {
                 const float xpv = xp[gf];
-                const float ir = fmaf(w0r[0], xpv, pre_i1[(0 * RU + gu) * RB + gf]);
-                const float iz = fmaf(w0r[1], xpv, pre_i1[(1 * RU + gu) * RB + gf]);
-                const float in_ = fmaf(w0r[2], xpv, pre_i1[(2 * RU + gu) * RB + gf]);
+                const float ir = fmaf(w0r[0], xpv, pre2(pre_i1, (0 * RU + gu) * RB + gf));
+                const float iz = fmaf(w0r[1], xpv, pre2(pre_i1, (1 * RU + gu) * RB + gf));
+                const float in_ = fmaf(w0r[2], xpv, pre2(pre_i1, (2 * RU + gu) * RB + gf));
                 const float hn = gru_update(ir, iz, in_, pre_h1[(0 * RU + gu) * RB + gf], pre_h1[(1 * RU + gu) * RB + gf],
                                             pre_h1[(2 * RU + gu) * RB + gf], hst1[gu * RB + gf]);
                 hw = tag_word(hn, tag);
@@ -738,29 +675,30 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
         }
         __syncthreads();                                    // S0b: as S1b
         GMARK(2);
-        // ---- T2: gather h1(t).  The start-up delay of each gather is where the conditioning terms of step t+1 are
-        //         formed: GB's and GD's here, GC's in the next one.
-        const bool more = t + 1 < S && !(P.exp & 8);
-        if (more) cond_step(t + 1, true, false, true);
+        // ---- T2: gather h1(t).  Its start-up delay and flight time is where the whole CTA forms the conditioning
+        //         terms of step t+1 (thread 0 issues the bulk copy first).
+        const bool more = t + 1 < S;
         GMARK(3);
-        if (use_tma) { gather_tma(P.h1 + par * B * RH, B * (RH / 4), bufH1, tag, tid, d1, mbar + 2, gpar, dd); gpar ^= 1; }
-        else if (!more) gather_cta(P.h1 + par * B * RH, B * (RH / 4), bufH1, tag, tid, RTH, d1, dd);
-        else if (gid == 0 || gid == 2) gather_cta(P.h1 + par * B * RH, B * (RH / 4), bufH1, tag, (gid >> 1) * 128 + tg, 256, d1, dd);
+        if (tid == RTH - 1) gather_issue(P.h1 + par * B * RH, B * (RH / 4), bufH1, d1, mbar + 2);      // an idle lane (>= B)
+        if (more) cond_step(t + 1, false);
+        GMARK(15);
+        gather_wait(P.h1 + par * B * RH, B * (RH / 4), bufH1, tag, tid, mbar + 2, gpar, dd);
+        gpar ^= 1;
         GMARK(4);
         __syncthreads();                                                         // S1
         RPROF(2);
         GMARK(5);
         // ---- T3: rnn2 (GA, alone on the SM)
         if (gid == 0) {
-            if (!(P.exp & 4)) gru_job(w, bufH1, FG, red, wq, lane);
+            gru_job(w, bufH1, FG, red, wq, lane);
             bar_sync(BAR_A, 128);
             if (tg < 96) {
                 uint32_t xw = tag;
                 if (gate) {
                     const float xpv = xp[gf];
-                    const float ir = gru_out(red, 0 * RU + gu, gf) + fmaf(w0r[0], xpv, pre_i2[(0 * RU + gu) * RB + gf]);
-                    const float iz = gru_out(red, 1 * RU + gu, gf) + fmaf(w0r[1], xpv, pre_i2[(1 * RU + gu) * RB + gf]);
-                    const float in_ = gru_out(red, 2 * RU + gu, gf) + fmaf(w0r[2], xpv, pre_i2[(2 * RU + gu) * RB + gf]);
+                    const float ir = gru_out(red, 0 * RU + gu, gf) + fmaf(w0r[0], xpv, pre2(pre_i2, (0 * RU + gu) * RB + gf));
+                    const float iz = gru_out(red, 1 * RU + gu, gf) + fmaf(w0r[1], xpv, pre2(pre_i2, (1 * RU + gu) * RB + gf));
+                    const float in_ = gru_out(red, 2 * RU + gu, gf) + fmaf(w0r[2], xpv, pre2(pre_i2, (2 * RU + gu) * RB + gf));
                     const float hn = gru_update(ir, iz, in_, pre_h2[(0 * RU + gu) * RB + gf], pre_h2[(1 * RU + gu) * RB + gf],
                                                 pre_h2[(2 * RU + gu) * RB + gf], hst2[gu * RB + gf]);
                     hst2[gu * RB + gf] = hn;                                   // own state, never exchanged: exact
@@ -773,22 +711,22 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
         RPROF(3);
         GMARK(6);
         // ---- T4: gather x2'(t)
-        if (more) cond_step(t + 1, false, true, false);
         GMARK(7);
-        if (use_tma) { gather_tma(P.x2 + par * B * RH, B * (RH / 4), bufX, tag, tid, d2, mbar + 2, gpar, dd); gpar ^= 1; }
-        else if (!more) gather_cta(P.x2 + par * B * RH, B * (RH / 4), bufX, tag, tid, RTH, d2, dd);
-        else if (gid != 2) gather_cta(P.x2 + par * B * RH, B * (RH / 4), bufX, tag, (gid == 3 ? 256 : gid * 128) + tg, 384, d2, dd);
+        if (tid == RTH - 1) gather_issue(P.x2 + par * B * RH, B * (RH / 4), bufX, d2, mbar + 2);
+        if (more) cond_step(t + 1, true);
+        gather_wait(P.x2 + par * B * RH, B * (RH / 4), bufX, tag, tid, mbar + 2, gpar, dd);
+        gpar ^= 1;
         GMARK(8);
         __syncthreads();                                                         // S2
         RPROF(4);
         GMARK(9);
         // ---- T5: fc1 (GD)
         if (gid == 3) {
-            if (!(P.exp & 4)) fc_job(w.a[0], w.a[1], w.a[2], w.a[3], bufX, FG, red, wq, lane, tg);
+            fc_job(w.a[0], w.a[1], w.a[2], w.a[3], bufX, FG, red, wq, lane, tg);
             bar_sync(BAR_D, 128);
             if (tg < 96) {
                 uint32_t yw = tag;
-                if (gate) yw = tag_word(fmaxf(fc_out(red, gu, gf) + fmaf(w0r[0], xp[gf], pre_f1[gu * RB + gf]), 0.f), tag);
+                if (gate) yw = tag_word(fmaxf(fc_out(red, gu, gf) + fmaf(w0r[0], xp[gf], pre2(pre_f1, gu * RB + gf)), 0.f), tag);
                 publish4(P.y1 + (par * B + gf) * RH + u0, yw, lane, gate);
             }
         }
@@ -797,6 +735,7 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
         GMARK(10);
         // ---- T6: gather y1(t); meanwhile GC turns x2' into h2 = x2' - h1 in place for the next shadow product
         //         (saves exchanging h2)
+        if (tid == RTH - 1) gather_issue(P.y1 + par * B * RH, B * (RH / 4), bufY, d3, mbar + 2);
         if (gid == 2) {
             float4 *a4 = reinterpret_cast<float4 *>(bufX);
             const float4 *b4 = reinterpret_cast<const float4 *>(bufH1);
@@ -807,26 +746,26 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
             }
         }
         GMARK(11);
-        if (use_tma) { gather_tma(P.y1 + par * B * RH, B * (RH / 4), bufY, tag, tid, d2, mbar + 2, gpar, dd); gpar ^= 1; }
-        else if (gid != 2) gather_cta(P.y1 + par * B * RH, B * (RH / 4), bufY, tag, (gid == 3 ? 256 : gid * 128) + tg, 384, d2, dd);
+        gather_wait(P.y1 + par * B * RH, B * (RH / 4), bufY, tag, tid, mbar + 2, gpar, dd);
+        gpar ^= 1;
         GMARK(12);
         __syncthreads();                                                         // S4
         RPROF(6);
         GMARK(13);
         // ---- T7: fc2 (GD)
         if (gid == 3) {
-            if (!(P.exp & 4)) fc_job(w.a[4], w.a[5], w.b[0], w.b[1], bufY, FG, red, wq, lane, tg);
+            fc_job(w.a[4], w.a[5], w.b[0], w.b[1], bufY, FG, red, wq, lane, tg);
             bar_sync(BAR_D, 128);
             if (tg < 96) {
                 uint32_t yw = tag;
-                if (gate) yw = tag_word(fmaxf(fc_out(red, gu, gf) + pre_f2[gu * RB + gf], 0.f), tag);
+                if (gate) yw = tag_word(fmaxf(fc_out(red, gu, gf) + pre2(pre_f2, gu * RB + gf), 0.f), tag);
                 publish4(P.y2 + (par * B + gf) * RH + u0, yw, lane, gate);
             }
         }
         GMARK(14);
         // S4b: fc2 is on the chain, the shadow products are not.  Without this barrier GB and GC start them while
         // GD is still in fc2, sharing its FMA and LDS bandwidth (measured: 17.1 us per step without, 13.6 with).
-        if (!(P.exp & 64)) __syncthreads();
+        __syncthreads();
         RPROF(7);
     }
     if (prof_on)
@@ -857,7 +796,7 @@ int res_plan(wrnn_handle *h) {
     ResPlan &p = h->res;
     p.ok = false;
     const int Kc = d.F + d.A;
-    if (d.mode != WRNN_MODE_MOL || d.H != RH || d.FC != RH || d.A != 32 || Kc % 4 || Kc > 128 || d.NC > 32) return 0;
+    if (d.mode != WRNN_MODE_MOL || d.H != RH || d.FC != RH || d.A != 32 || Kc % 8 || Kc > 128 || d.NC > 32) return 0;
     if (h->num_sms < RNR + 1) return 0;
     p.G = h->num_sms;
     p.smem_bytes = (size_t)SM_FLOATS * sizeof(float);
@@ -918,9 +857,9 @@ int res_plan(wrnn_handle *h) {
                 memcpy(im + IMG_IH2 + (size_t)lr * RH, W2i->v.data() + (size_t)row * (H + A), (size_t)H * sizeof(float));
                 memcpy(im + IMG_HH1 + (size_t)lr * RH, W1h->v.data() + (size_t)row * H, (size_t)H * sizeof(float));
                 memcpy(im + IMG_HH2 + (size_t)lr * RH, W2h->v.data() + (size_t)row * H, (size_t)H * sizeof(float));
-                memcpy(im + IMG_C1 + (size_t)lr * CB1, P1.data() + (size_t)row * KinI + 1, (size_t)Kc * sizeof(float));
-                memcpy(im + IMG_C2 + (size_t)lr * CB2, P2.data() + (size_t)row * KinI + 1, (size_t)Kc * sizeof(float));
-                memcpy(im + IMG_C2 + (size_t)lr * CB2 + Kc, W2i->v.data() + (size_t)row * (H + A) + H, (size_t)A * sizeof(float));
+                memcpy(im + IMG_CU + (size_t)lr * WCL, P1.data() + (size_t)row * KinI + 1, (size_t)Kc * sizeof(float));
+                memcpy(im + IMG_CU + (size_t)(12 + lr) * WCL, P2.data() + (size_t)row * KinI + 1, (size_t)Kc * sizeof(float));
+                memcpy(im + IMG_CU + (size_t)(12 + lr) * WCL + Kc, W2i->v.data() + (size_t)row * (H + A) + H, (size_t)A * sizeof(float));
                 w0[lr] = P1[(size_t)row * KinI];
                 w0[12 + lr] = P2[(size_t)row * KinI];
                 bias[lr] = (float)(q1[row] + (double)B1i->v[row]);
@@ -931,9 +870,9 @@ int res_plan(wrnn_handle *h) {
             const int row = c * RU + u;       // fc rows
             memcpy(im + IMG_F1 + (size_t)u * RH, F1->v.data() + (size_t)row * (H + A), (size_t)H * sizeof(float));
             memcpy(im + IMG_F2 + (size_t)u * RH, F2->v.data() + (size_t)row * (FC + A), (size_t)FC * sizeof(float));
-            memcpy(im + IMG_C3 + (size_t)u * CB3, P3.data() + (size_t)row * KinI + 1, (size_t)Kc * sizeof(float));
-            memcpy(im + IMG_C3 + (size_t)u * CB3 + Kc, F1->v.data() + (size_t)row * (H + A) + H, (size_t)A * sizeof(float));
-            memcpy(im + IMG_C3 + (size_t)u * CB3 + 160, F2->v.data() + (size_t)row * (FC + A) + FC, (size_t)A * sizeof(float));
+            memcpy(im + IMG_CU + (size_t)(24 + u) * WCL, P3.data() + (size_t)row * KinI + 1, (size_t)Kc * sizeof(float));
+            memcpy(im + IMG_CU + (size_t)(24 + u) * WCL + Kc + 32, F1->v.data() + (size_t)row * (H + A) + H, (size_t)A * sizeof(float));       // a3
+            memcpy(im + IMG_CU + (size_t)(28 + u) * WCL + Kc + 64, F2->v.data() + (size_t)row * (FC + A) + FC, (size_t)A * sizeof(float));      // a4
             w0[24 + u] = P3[(size_t)row * KinI];
             bias[24 + u] = (float)(q3[row] + (double)F1b->v[row]);
             bias[28 + u] = F2b->v[row];
@@ -981,11 +920,11 @@ int res_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
     WRNN_TRY(ws_reserve(h, h->ws_sync, 128));                        // cleared by the caller once per run
     P.abort_flag = (int *)((char *)h->ws_sync.p + 64);
     static const bool prof_env = getenv("WRNN_PROF") != nullptr;
-    static const int exp_env = getenv("WRNN_EXP") ? atoi(getenv("WRNN_EXP")) : 0;
-    P.exp = exp_env;
     static const int d1_env = getenv("WRNN_D1") ? atoi(getenv("WRNN_D1")) : 0, d2_env = getenv("WRNN_D2") ? atoi(getenv("WRNN_D2")) : 0;
     P.d1 = d1_env;
     P.d2 = d2_env;
+    static const int d3_env = getenv("WRNN_D3") ? atoi(getenv("WRNN_D3")) : 0;
+    P.d3 = d3_env;
     P.prof = nullptr;
     if (prof_env) {
         WRNN_TRY(ws_reserve(h, h->ws_prof, (128 + RNR * 8 + RNR * 128) * sizeof(long long)));
@@ -1022,7 +961,7 @@ int res_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
             for (int g = 0; g < 4; g++) {
                 fprintf(stderr, "[wrnn prof] CTA 5 group %c leader, clocks since its previous mark:", "ABCD"[g]);
                 for (int k = 0; k < 15; k++) fprintf(stderr, " %s=%.0f", marks[k], pr[64 + RNR * 8 + RNR * 128 + g * 16 + k] / s);
-                fprintf(stderr, " (cond wait=%.0f)", pr[64 + RNR * 8 + RNR * 128 + g * 16 + 15] / s);
+                fprintf(stderr, " (of fetch_h1, conditioning job=%.0f)", pr[64 + RNR * 8 + RNR * 128 + g * 16 + 15] / s);
                 fprintf(stderr, "\n");
             }
         }
