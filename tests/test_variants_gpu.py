@@ -112,3 +112,23 @@ def test_all_loop_kernels_agree_with_fixture(kernel):
     assert np.abs(wave - golden(name)['wave']).max() <= 2e-4
     v.set_loop_kernel(0)
     assert v.loop_kernel_name(B) == 'fma-resident'
+
+
+def test_raw_default_dims_run_on_the_resident_kernel_and_agree_with_the_barrier_kernel():
+    """RAW 9-bit at default dims: fc3 (512 rows) is a fifth layer of the row CTAs in the resident kernel."""
+    name = 'full_raw_batched_mulaw'
+    dims, sd, mel, noise, (T, batched, target, overlap, mu_law, B, S) = case_inputs(name)
+    v = binding.Vocoder(dims, device=0)
+    v.load_weights(sd)
+    assert v.loop_kernel_name(B) == 'fma-resident'
+    wave = v.generate([mel[0]], batched, target, overlap, mu_law, noise=noise)[0]
+    labels = v.fetch_samples()
+    assert np.abs(wave - golden(name)['wave']).max() <= 2e-4
+    v.set_loop_kernel(1)
+    assert v.loop_kernel_name(B) == 'fma'
+    wave1 = v.generate([mel[0]], batched, target, overlap, mu_law, noise=noise)[0]
+    labels1 = v.fetch_samples()
+    # identical class draws under identical injected noise (the two kernels differ in summation order only)
+    same = np.mean(np.asarray(labels) == np.asarray(labels1))
+    assert same >= 0.999, same
+    assert np.abs(wave1 - golden(name)['wave']).max() <= 2e-4

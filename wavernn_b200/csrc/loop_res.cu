@@ -50,9 +50,10 @@ constexpr int IMG_F2 = IMG_F1 + 4 * RH;           // [4][512]   fc2[:, :512]
 //   rows 12..23  (W_ih2a W_I)[:, 1:] | W_ih2b             cols (m, a1, a2)
 //   rows 24..27  (W_f1a W_I)[:, 1:]  | W_f1b              cols (m, a1, a3)
 //   rows 28..31  W_f2b                                    cols (a4)
-constexpr int IMG_CU = IMG_F2 + 4 * RH;           // [32][WCL]
+constexpr int IMG_F3 = IMG_F2 + 4 * RH;           // [4][512]   fc3 (RAW mode, 512 classes: 4 rows per CTA; zero in MoL mode)
+constexpr int IMG_CU = IMG_F3 + 4 * RH;           // [32][WCL]
 constexpr int IMG_W0 = IMG_CU + 32 * WCL;         // [32] column 0 (x_prev): i1[12] i2[12] f1[4] pad[4]
-constexpr int IMG_B = IMG_W0 + 32;                // [64] biases: i1[12] i2[12] f1[4] f2[4] hh1[12] hh2[12] pad
+constexpr int IMG_B = IMG_W0 + 32;                // [64] biases: i1[12] i2[12] f1[4] f2[4] hh1[12] hh2[12] f3[4] pad
 constexpr int IMG_FLOATS = IMG_B + 64;
 
 struct ResParams {
@@ -63,6 +64,7 @@ struct ResParams {
     const float *tail_img;       // [32][512] fc3 rows (zero padded) | bias[32]
     LoopArgs a;
     float *h1, *h2, *x2, *y1, *y2;           // [2][B][512] tagged words (h2: unused since h2 = x2' - h1 is formed locally)
+    float *y3;                               // [2][B][512] RAW mode: the 512 logits (fc3 rows live in the row CTAs)
     unsigned long long *xprev;               // [2][RB]
     int *abort_flag;
     long long *prof;
@@ -73,7 +75,7 @@ struct ResParams {
 constexpr int SM_H1 = 0;                          // [20][512] h1(t)                                  (GA, GB)
 constexpr int SM_H2 = SM_H1 + RB * RH;            // [20][512] y1(t)                                  (GD)
 constexpr int SM_X = SM_H2 + RB * RH;             // [20][512] x2'(t), turned into h2(t) in place     (GD, GC)
-constexpr int GATHER_DELAY_H1 = 1700, GATHER_DELAY_X2 = 1200, GATHER_DELAY_Y1 = 700;   // clocks, see gather_issue
+constexpr int GATHER_DELAY_H1 = 1700, GATHER_DELAY_X2 = 1200, GATHER_DELAY_Y1 = 700, GATHER_DELAY_Y2 = 700;   // clocks, see gather_issue
 constexpr int CBL = 228;                          // conditioning row stride in smem: >= 224, and 4 banks apart per fold (float4 reads by 8 lanes)
 constexpr int SM_CB = SM_X + RB * RH;             // [2][20][228] whole conditioning rows of steps t, t+1 (TMA bulk copies)
 constexpr int SM_MBAR = SM_CB + 2 * RB * CBL;     // three mbarriers (8 bytes each): conditioning buffer 0, 1, the gathers
@@ -349,6 +351,7 @@ __device__ __forceinline__ float mol_sample_smem2(const float *logits, int nmix,
     return x;
 }
 
+template <bool RAW>
 __device__ void res_tail_role(const ResParams &P, int j, float *smem) {
     const Dims &d = P.d;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -364,8 +367,10 @@ __device__ void res_tail_role(const ResParams &P, int j, float *smem) {
     for (int r = 0; r < 2; r++) {
         const int row = 2 * warp + r;
 #pragma unroll
-        for (int q = 0; q < 4; q++) w3[r][q] = ld_keep4(reinterpret_cast<const float4 *>(P.tail_img) + (size_t)row * (RH / 4) + lane + 32 * q);
-        b3[r] = ld_keep(P.tail_img + 32 * RH + row);
+        for (int q = 0; q < 4; q++)
+            w3[r][q] = RAW ? make_float4(0.f, 0.f, 0.f, 0.f)
+                           : ld_keep4(reinterpret_cast<const float4 *>(P.tail_img) + (size_t)row * (RH / 4) + lane + 32 * q);
+        b3[r] = RAW ? 0.f : ld_keep(P.tail_img + 32 * RH + row);
     }
     const uint2 key = make_uint2((uint32_t)P.a.seed, (uint32_t)(P.a.seed >> 32));
     const int nmix = NC / 3;
@@ -395,9 +400,26 @@ __device__ void res_tail_role(const ResParams &P, int j, float *smem) {
                     }
                 }
                 if (tid < RH / 4)
-                    gather_group(P.y2 + ((size_t)(tp & 1) * B + f) * RH, RH / 4, ybuf, (uint32_t)((tp + 1) & 3), RH / 4, tid, dd);
+                    gather_group((RAW ? P.y3 : P.y2) + ((size_t)(tp & 1) * B + f) * RH, RH / 4, ybuf, (uint32_t)((tp + 1) & 3), RH / 4, tid, dd);
                 __syncthreads();
                 if (prof_on) { const long long n = clock64(); pacc[0] += n - pt; pt = n; }
+                if (RAW) {
+                    // RAW branch (fatchord_version.py:231-237): ybuf holds the 512 logits of this fold (fc3 ran in the
+                    // row CTAs); softmax -> Categorical.sample == argmax(p / q), q ~ Exp(1) -> 2k/(C-1) - 1.
+                    if (P.a.logits_out && tp < P.a.fold_len[f])
+                        for (int i = tid; i < NC; i += RTH) P.a.logits_out[((size_t)f * S + tp) * NC + i] = ybuf[i];
+                    if (warp == 0) {
+                        const float *qsrc = P.a.q ? P.a.q + ((size_t)tp * Bt + b) * NC : nullptr;
+                        pick = categorical_warp(ybuf, NC, qsrc, key, (uint32_t)tp, (uint32_t)b, 3u, lane);
+                        xv = raw_value(pick, NC);
+                        if (tp >= P.a.fold_len[f]) xv = 0.f;
+                        else if (lane == 0) {
+                            P.a.samples[(size_t)f * S + tp] = xv;
+                            P.a.picks[(size_t)f * S + tp] = pick;
+                        }
+                    }
+                    __syncthreads();                       // ybuf is rewritten by the next gather
+                } else {
                 float s0 = 0.f, s1 = 0.f;
 #pragma unroll
                 for (int q = 0; q < 4; q++) {
@@ -429,6 +451,7 @@ __device__ void res_tail_role(const ResParams &P, int j, float *smem) {
                         P.a.samples[(size_t)f * S + tp] = xv;
                         P.a.picks[(size_t)f * S + tp] = pick;
                     }
+                }
                 }
             }
             if (warp == 0 && lane == 0 && t < S) {
@@ -504,17 +527,21 @@ __device__ __forceinline__ void gather_issue(const float *src, int n4, float *ds
     mbar_expect_tx(mb, (uint32_t)n4 * 16u);
     bulk_g2s(dst, src, (uint32_t)n4 * 16u, mb);
 }
-__device__ __forceinline__ void gather_wait(const float *src, int n4, float *dst, uint32_t tag, int tid, void *mb, uint32_t parity, Dead &dd) {
+__device__ __forceinline__ void gather_wait(const float *src, int n4, float *dst, uint32_t tag, int rank, int nth, void *mb, uint32_t parity,
+                                            Dead &dd) {
     while (!mbar_try_wait(mb, parity)) {}
     const uint4 *s4 = reinterpret_cast<const uint4 *>(src);
     uint4 *d4 = reinterpret_cast<uint4 *>(dst);
     unsigned spins = 0;
     long long t0 = 0;
+    // A slot is one aligned 16-byte store of its producer, so one word stands for the slot; lane l looks at word
+    // (l >> 3) & 3 of its slot, which spreads a warp's 32 reads over all 32 banks (one wavefront instead of four).
+    const uint32_t *dw = reinterpret_cast<const uint32_t *>(dst) + ((rank >> 3) & 3);
     for (;;) {
         bool any = false;
 #pragma unroll 5
-        for (int i = tid; i < n4; i += RTH)
-            if (!tags_ok(d4[i], tag)) {
+        for (int i = rank; i < n4; i += nth)
+            if (((dw[4 * i] ^ tag) & 3u) != 0u) {
                 cp_async16(d4 + i, s4 + i);
                 any = true;
             }
@@ -543,6 +570,7 @@ __device__ __forceinline__ void gather_wait(const float *src, int n4, float *dst
 // T4 3.7 k, T5 2.5 k, T6 3.3 k, T7 2.6 k = 27 k = 13.7 us.  The products are bound by the LSU pipe (LDS + SHFL
 // wavefronts: 36 % of peak over the whole step, two products side by side take twice as long as one), the
 // exchanges by L2 round trips; see DESIGN.md section 4.
+template <bool RAW>
 __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
     const Dims &d = P.d;
     const int tid = threadIdx.x, gid = tid >> 7, tg = tid & 127, wq = tg >> 5, lane = tid & 31;
@@ -586,8 +614,9 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
         w.a[5] = ld_keep4(p2 + (RH / 4) + tg);
         w.b[0] = ld_keep4(p2 + 2 * (RH / 4) + tg);
         w.b[1] = ld_keep4(p2 + 3 * (RH / 4) + tg);
+        const float4 *p3 = reinterpret_cast<const float4 *>(img + IMG_F3);       // RAW mode: fc3 rows; zeros in MoL mode
 #pragma unroll
-        for (int i = 2; i < 6; i++) w.b[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int i = 0; i < 4; i++) w.b[2 + i] = RAW ? ld_keep4(p3 + (size_t)i * (RH / 4) + tg) : make_float4(0.f, 0.f, 0.f, 0.f);
     }
     const int gu = tg & 3, gf = tg >> 2;      // gate / epilogue thread: unit (row) gu of fold gf
     const bool gate = gf < B;
@@ -631,6 +660,26 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
 
     const int d1 = P.d1 ? P.d1 : GATHER_DELAY_H1, d2 = P.d2 ? P.d2 : GATHER_DELAY_X2, d3 = P.d3 ? P.d3 : GATHER_DELAY_Y1;
     uint32_t gpar = 0;                                   // phase parity of the gather mbarrier
+    // RAW mode: fc3 has 512 rows, four per row CTA like fc1 / fc2, so the chain goes on here: y2(tp) is exchanged
+    // among the row CTAs, GD forms its four logits per fold and publishes them for the tail CTAs (softmax +
+    // categorical draw there).  Runs beside the shadow products of GB and GC.
+    auto raw_fc3 = [&](int64_t tp) {
+        const uint32_t tg3 = (uint32_t)((tp + 1) & 3);
+        const size_t pp = (size_t)(tp & 1);
+        if (tid == 0) gather_issue(P.y2 + pp * B * RH, B * (RH / 4), bufY, GATHER_DELAY_Y2, mbar + 2);
+        if (gid == 3) {
+            gather_wait(P.y2 + pp * B * RH, B * (RH / 4), bufY, tg3, tg, 128, mbar + 2, gpar, dd);
+            bar_sync(BAR_D, 128);
+            fc_job(w.b[2], w.b[3], w.b[4], w.b[5], bufY, FG, red, wq, lane, tg);
+            bar_sync(BAR_D, 128);
+            if (tg < 96) {
+                uint32_t lw = tg3;
+                if (gate) lw = tag_word(fc_out(red, gu, gf) + bias[56 + gu], tg3);
+                publish4(P.y3 + (pp * B + gf) * RH + u0, lw, lane, gate);
+            }
+        }
+        gpar ^= 1;
+    };
     for (int64_t t = 0; t < S; t++) {
         const uint32_t tag = (uint32_t)((t + 1) & 3);
         const size_t par = (size_t)(t & 1);
@@ -638,6 +687,7 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
         //         tail CTAs turn y2(t-1) into that sample
         const float *pre_i1 = pre_cb + (t & 1) * 1280, *pre_i2 = pre_i1 + 240, *pre_f1 = pre_i1 + 480, *pre_f2 = pre_i1 + 560;
         if (t + 1 < S) fetch_cond(t + 1);                  // its buffer was last read two steps ago
+        if (RAW && t > 0) raw_fc3(t - 1);
         if (gid == 1 || gid == 2) {
             const bool g1 = gid == 1;
             gru_job(w, g1 ? bufH1 : bufX, FG, red, wq, lane);
@@ -682,7 +732,7 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
         if (tid == RTH - 1) gather_issue(P.h1 + par * B * RH, B * (RH / 4), bufH1, d1, mbar + 2);      // an idle lane (>= B)
         if (more) cond_step(t + 1, false);
         GMARK(15);
-        gather_wait(P.h1 + par * B * RH, B * (RH / 4), bufH1, tag, tid, mbar + 2, gpar, dd);
+        gather_wait(P.h1 + par * B * RH, B * (RH / 4), bufH1, tag, tid, RTH, mbar + 2, gpar, dd);
         gpar ^= 1;
         GMARK(4);
         __syncthreads();                                                         // S1
@@ -714,7 +764,7 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
         GMARK(7);
         if (tid == RTH - 1) gather_issue(P.x2 + par * B * RH, B * (RH / 4), bufX, d2, mbar + 2);
         if (more) cond_step(t + 1, true);
-        gather_wait(P.x2 + par * B * RH, B * (RH / 4), bufX, tag, tid, mbar + 2, gpar, dd);
+        gather_wait(P.x2 + par * B * RH, B * (RH / 4), bufX, tag, tid, RTH, mbar + 2, gpar, dd);
         gpar ^= 1;
         GMARK(8);
         __syncthreads();                                                         // S2
@@ -746,7 +796,7 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
             }
         }
         GMARK(11);
-        gather_wait(P.y1 + par * B * RH, B * (RH / 4), bufY, tag, tid, mbar + 2, gpar, dd);
+        gather_wait(P.y1 + par * B * RH, B * (RH / 4), bufY, tag, tid, RTH, mbar + 2, gpar, dd);
         gpar ^= 1;
         GMARK(12);
         __syncthreads();                                                         // S4
@@ -768,6 +818,7 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
         __syncthreads();
         RPROF(7);
     }
+    if (RAW && S > 0) raw_fc3(S - 1);
     if (prof_on)
         for (int i = 0; i < 8; i++) P.prof[64 + cta * 8 + i] = pacc[i];
     if (prof_on)
@@ -780,11 +831,12 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
         for (int i = 0; i < 3; i++) P.prof[20 + gid * 3 + i] = dd.cnt[i];
 }
 
+template <bool RAW>
 __global__ void __launch_bounds__(RTH, 1) res_loop_kernel(const ResParams P) {
     extern __shared__ __align__(16) float smem[];
     const int cta = blockIdx.x;
-    if (cta < RNR) res_row_role(P, cta, smem);
-    else res_tail_role(P, cta - RNR, smem);
+    if (cta < RNR) res_row_role<RAW>(P, cta, smem);
+    else res_tail_role<RAW>(P, cta - RNR, smem);
 }
 
 // ============================================================================ host: plan + launch
@@ -796,7 +848,9 @@ int res_plan(wrnn_handle *h) {
     ResPlan &p = h->res;
     p.ok = false;
     const int Kc = d.F + d.A;
-    if (d.mode != WRNN_MODE_MOL || d.H != RH || d.FC != RH || d.A != 32 || Kc % 8 || Kc > 128 || d.NC > 32) return 0;
+    if (d.H != RH || d.FC != RH || d.A != 32 || Kc % 8 || Kc > 128) return 0;
+    if (d.mode == WRNN_MODE_MOL ? d.NC > 32 : d.NC != 4 * RNR) return 0;       // RAW: 512 classes = 4 fc3 rows per row CTA
+    const bool raw = d.mode != WRNN_MODE_MOL;
     if (h->num_sms < RNR + 1) return 0;
     p.G = h->num_sms;
     p.smem_bytes = (size_t)SM_FLOATS * sizeof(float);
@@ -876,10 +930,14 @@ int res_plan(wrnn_handle *h) {
             w0[24 + u] = P3[(size_t)row * KinI];
             bias[24 + u] = (float)(q3[row] + (double)F1b->v[row]);
             bias[28 + u] = F2b->v[row];
+            if (raw) {
+                memcpy(im + IMG_F3 + (size_t)u * RH, F3->v.data() + (size_t)row * FC, (size_t)FC * sizeof(float));
+                bias[56 + u] = F3b->v[row];
+            }
         }
     }
     std::vector<float> timg((size_t)32 * RH + 32, 0.f);
-    for (int r = 0; r < NC; r++) {
+    for (int r = 0; r < NC && !raw; r++) {
         memcpy(timg.data() + (size_t)r * RH, F3->v.data() + (size_t)r * FC, (size_t)FC * sizeof(float));
         timg[(size_t)32 * RH + r] = F3b->v[r];
     }
@@ -890,7 +948,8 @@ int res_plan(wrnn_handle *h) {
     WRNN_CUDA(h, cudaMemcpy(p.img, img.data(), img.size() * sizeof(float), cudaMemcpyHostToDevice));
     WRNN_CUDA(h, cudaMalloc((void **)&p.tail_img, timg.size() * sizeof(float)));
     WRNN_CUDA(h, cudaMemcpy(p.tail_img, timg.data(), timg.size() * sizeof(float), cudaMemcpyHostToDevice));
-    WRNN_CUDA(h, cudaFuncSetAttribute(res_loop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem_bytes));
+    WRNN_CUDA(h, cudaFuncSetAttribute(res_loop_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem_bytes));
+    WRNN_CUDA(h, cudaFuncSetAttribute(res_loop_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem_bytes));
     p.ok = true;
     return 0;
 }
@@ -910,13 +969,13 @@ int res_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
     P.tail_img = p.tail_img;
     P.a = a;
     const size_t BH = (size_t)a.B * RH;
-    const size_t act_floats = 2 * 5 * BH;
+    const size_t act_floats = 2 * 6 * BH;
     const size_t xprev_bytes = 2 * RB * sizeof(unsigned long long);
     WRNN_TRY(ws_reserve(h, h->ws_act, act_floats * sizeof(float) + xprev_bytes + 256));
     WRNN_CUDA(h, cudaMemsetAsync(h->ws_act.p, 0, act_floats * sizeof(float) + xprev_bytes + 256, st));
     float *base = (float *)h->ws_act.p;
-    P.h1 = base; P.h2 = P.h1 + 2 * BH; P.x2 = P.h2 + 2 * BH; P.y1 = P.x2 + 2 * BH; P.y2 = P.y1 + 2 * BH;
-    P.xprev = (unsigned long long *)(((uintptr_t)(P.y2 + 2 * BH) + 63) & ~(uintptr_t)63);
+    P.h1 = base; P.h2 = P.h1 + 2 * BH; P.x2 = P.h2 + 2 * BH; P.y1 = P.x2 + 2 * BH; P.y2 = P.y1 + 2 * BH; P.y3 = P.y2 + 2 * BH;
+    P.xprev = (unsigned long long *)(((uintptr_t)(P.y3 + 2 * BH) + 63) & ~(uintptr_t)63);
     WRNN_TRY(ws_reserve(h, h->ws_sync, 128));                        // cleared by the caller once per run
     P.abort_flag = (int *)((char *)h->ws_sync.p + 64);
     static const bool prof_env = getenv("WRNN_PROF") != nullptr;
@@ -931,9 +990,9 @@ int res_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
         WRNN_CUDA(h, cudaMemsetAsync(h->ws_prof.p, 0, (128 + RNR * 8 + RNR * 128) * sizeof(long long), st));
         P.prof = (long long *)h->ws_prof.p;
     }
-    WRNN_CUDA(h, cudaFuncSetAttribute(res_loop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem_bytes));
+    const void *kern = d.mode == WRNN_MODE_MOL ? (const void *)res_loop_kernel<false> : (const void *)res_loop_kernel<true>;
     void *args[] = {(void *)&P};
-    WRNN_CUDA(h, cudaLaunchCooperativeKernel((const void *)res_loop_kernel, dim3(p.G), dim3(RTH), args, p.smem_bytes, st));
+    WRNN_CUDA(h, cudaLaunchCooperativeKernel(kern, dim3(p.G), dim3(RTH), args, p.smem_bytes, st));
     h->launches++;
     if (prof_env) {      // debugging aid: per-segment clocks of row CTA 0's groups and tail CTA 0 (synchronises!)
         static long long pr[128 + RNR * 8 + RNR * 128];
