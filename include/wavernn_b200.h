@@ -135,7 +135,9 @@ int wrnn_xfade_tables(int64_t overlap, double *fade_in, double *fade_out);
  * samples, mels (n_seq, feat_dims, S/hop + 2*pad) ALREADY padded -> logits (n_seq, S, n_classes). */
 int wrnn_forward_logits(wrnn_handle *h, const float *x, const float *mels, int32_t n_seq, int64_t S,
                         float *logits);
-/* Which loop kernel the next run will use, for reports: "fma", "fma-pipelined", "fma-resident". */
+/* Which loop kernel the next run will use, for reports: "fma", "fma-pipelined", "fma-resident".
+ * "fma-resident" (register-resident weights, TMA exchanges; csrc/loop_res.cu) takes rnn_dims = fc_dims = 512,
+ * aux 32, feat_dims a multiple of 8 up to 96, MoL or RAW with 512 classes, on a GPU with >= 129 SMs. */
 const char *wrnn_loop_kernel_name(wrnn_handle *h, int64_t folds);
 /* Force a loop kernel: 0 = auto (fastest kernel that supports the dims), 1 = fma (grid-barrier kernel, any dims and
  * fold count, reference order of operations), 2 = fma-pipelined (tagged exchange, shared-memory weights). */
