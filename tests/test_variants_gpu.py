@@ -132,3 +132,25 @@ def test_raw_default_dims_run_on_the_resident_kernel_and_agree_with_the_barrier_
     same = np.mean(np.asarray(labels) == np.asarray(labels1))
     assert same >= 0.999, same
     assert np.abs(wave1 - golden(name)['wave']).max() <= 2e-4
+
+
+@pytest.mark.parametrize('mode,T,target,overlap', [('MOL', 64, 300, 50), ('MOL', 26, 300, 40), ('RAW', 40, 300, 50)])
+def test_default_dims_fold_groups_vs_oracle(mode, T, target, overlap):
+    """More than 20 folds: the resident kernel takes them in balanced groups of <= 20, each group with its own
+    launch; noise and Philox addressing stay per (step, global fold).  21 folds is the smallest split (11 + 10)."""
+    dims = VocoderDims(mode=mode)
+    sd = synth.synth_state_dict(dims, seed=0, style='init')
+    mel = synth.synth_mel(T, seed=77, feat_dims=dims.feat_dims)
+    v = binding.Vocoder(dims, device=0)
+    v.load_weights(sd)
+    W = ofc.to_torch(sd)
+    with torch.no_grad():
+        m, aux, wave_len = ofc.conditioning(W, dims, mel, True, target, overlap)
+    B, S = int(m.shape[0]), int(m.shape[1])
+    assert B > 20 and S == target + 2 * overlap                    # 51, 21 and 32 folds
+    noise = synth.synth_noise_mol(S, B, 9) if mode == 'MOL' else synth.synth_noise_exp(S, B, dims.n_classes, 9)
+    wave = v.generate([mel[0]], True, target, overlap, mode == 'RAW', noise=noise)[0]
+    assert v.loop_kernel_name(20) == 'fma-resident' and v.last_timing()['folds'] == B
+    ref = ofc.generate(W, dims, mel, True, target, overlap, mode == 'RAW', noise)
+    assert wave.shape == ref.shape == (wave_len,)
+    assert np.abs(wave - ref).max() <= 2e-4
