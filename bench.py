@@ -30,11 +30,12 @@ sys.path.insert(0, ROOT)
 T_FRAMES, TARGET, OVERLAP = 801, 11000, 550
 WEIGHT_BYTES_PER_STEP = 15_331_448        # 3 825 152 matrix + 7 710 bias fp32 elements
 # dram__bytes_read.sum + dram__bytes_write.sum of one res_loop_kernel launch (12100 steps), ncu --set full
-NCU_DRAM_BYTES_PER_LAUNCH = 221_816_832 + 5_805_056
-NCU_SOURCE = 'profiles/r01b_resident_loop_ncu.txt'
+NCU_DRAM_BYTES_PER_LAUNCH = 224_634_624 + 5_766_912
+NCU_SOURCE = 'profiles/r01c_resident_loop_ncu.txt'
 SAMPLE_RATE = 22050
 METRIC = 'generated audio samples/sec'
-CPU_SAMPLE_STEPS = 400                    # loop steps (x20 folds) of the workload timed on the CPU
+CPU_SAMPLE_STEPS = 2000                   # --impl reference: loop steps (x20 folds) per timed step (~2.5 s of CPU work each)
+CPU_BASELINE_STEPS = 12100                # cpu_baseline leg of our arm: up to the whole utterance, sized for ~15 s of CPU work
 
 
 def measured_peaks():
@@ -128,15 +129,18 @@ def run_reference(args):
         return
     dims, sd, mel = workload(0)
     threads = os.cpu_count() or 1
-    for _ in range(args.warmup):
-        cpu_port_rate(dims, sd, mel, 20, threads)
+    dt0 = 1.0
+    for _ in range(max(args.warmup, 1)):
+        _, dt0 = cpu_port_rate(dims, sd, mel, 20, threads)
+    # bounded sample: about 2.5 s of CPU work per timed step, at most CPU_SAMPLE_STEPS loop steps
+    n_steps = int(min(CPU_SAMPLE_STEPS, max(50, 20 * 2.5 / max(dt0, 1e-3))))
     rates, total = [], 0.0
     for _ in range(args.steps):
-        r, dt = cpu_port_rate(dims, sd, mel, CPU_SAMPLE_STEPS, threads)
+        r, dt = cpu_port_rate(dims, sd, mel, n_steps, threads)
         rates.append(r)
         total += dt
     v = float(np.median(rates))
-    sample = (f'conditioning + first {CPU_SAMPLE_STEPS} of 12100 loop steps at 20 folds per step '
+    sample = (f'conditioning + first {n_steps} of 12100 loop steps at 20 folds per step '
               f'(rate scaled to whole-utterance samples/s)')
     print(json.dumps({
         'impl': 'reference', 'metric': METRIC, 'value': v, 'unit': 'samples/s', 'rtf': v / SAMPLE_RATE,
@@ -246,9 +250,11 @@ def run_ours(args):
         }
         if world == 1 and not args.no_cpu:
             threads = os.cpu_count() or 1
-            v, dt = cpu_port_rate(dims, sd, mel, CPU_SAMPLE_STEPS, threads)
+            _, dt0 = cpu_port_rate(dims, sd, mel, 100, threads)                 # probe, then size the sample for ~15 s
+            n_cpu = int(min(CPU_BASELINE_STEPS, max(200, 100 * 15.0 / max(dt0, 1e-3))))
+            v, dt = cpu_port_rate(dims, sd, mel, n_cpu, threads)
             line['cpu_baseline'] = {'value': v, 'unit': 'samples/s', 'cores': threads, 'kind': 'port',
-                                    'sample': f'conditioning + first {CPU_SAMPLE_STEPS} of 12100 loop steps at 20 folds '
+                                    'sample': f'conditioning + first {n_cpu} of 12100 loop steps at 20 folds '
                                               f'({dt:.1f} s of CPU work), scaled to samples/s'}
         print(json.dumps(line))
     if world > 1:
