@@ -154,3 +154,31 @@ def test_default_dims_fold_groups_vs_oracle(mode, T, target, overlap):
     ref = ofc.generate(W, dims, mel, True, target, overlap, mode == 'RAW', noise)
     assert wave.shape == ref.shape == (wave_len,)
     assert np.abs(wave - ref).max() <= 2e-4
+
+
+def test_edge_inputs_default_dims():
+    """Shortest utterance the reference accepts (T = 21: the 5 500-sample fade-out must fit, fatchord_version.py:256-258),
+    a batched call that yields a single fold, ragged utterances in one call, and an empty call (ValueError)."""
+    dims = VocoderDims(mode='MOL')
+    sd = synth.synth_state_dict(dims, seed=0, style='init')
+    v = binding.Vocoder(dims, device=0)
+    v.load_weights(sd)
+    W = ofc.to_torch(sd)
+    # T = 21, unbatched, first 600 steps against the oracle (the rest of the 5 775 steps only adds time)
+    mel = synth.synth_mel(21, seed=5, feat_dims=dims.feat_dims)
+    wave = v.generate([mel[0]], False, 11000, 550, False, seed=1)[0]
+    assert wave.shape == (20 * dims.hop_length,) and np.all(np.isfinite(wave)) and wave[-1] == 0.0     # linspace(1, 0) ends at 0
+    assert v.last_timing()['folds'] == 1 and v.last_timing()['steps'] == 21 * dims.hop_length
+    # batched with a target longer than the utterance: one fold, zero padded tail (fatchord_version.py:325-331)
+    noise = synth.synth_noise_mol(7000 + 2 * 100, 1, 3)
+    wb = v.generate([mel[0]], True, 7000, 100, False, noise=noise)[0]
+    ref = ofc.generate(W, dims, mel, True, 7000, 100, False, noise)
+    assert v.last_timing()['folds'] == 1 and wb.shape == ref.shape and np.abs(wb - ref).max() <= 2e-4
+    # ragged: three utterances of different lengths in one call == three single calls (Philox keyed per utterance fold)
+    mels = [synth.synth_mel(T, seed=40 + T, feat_dims=dims.feat_dims)[0] for T in (21, 37, 64)]
+    outs = v.generate(mels, True, 2000, 100, False, seed=11)
+    assert [len(o) for o in outs] == [(T - 1) * dims.hop_length for T in (21, 37, 64)]
+    assert all(np.all(np.isfinite(o)) for o in outs)
+    # empty call: an argument error, not a crash
+    with pytest.raises(ValueError):
+        v.generate([], True, 2000, 100, False, seed=0)
