@@ -56,7 +56,7 @@ if __name__ == '__main__':
     fatchord('2: MoL batched T=801 (B=20)', mol, 801, True)
     fatchord('2b: MoL batched T=800 (B=19, no tail pad)', mol, 800, True)
     fatchord('3: RAW 9-bit mu-law batched T=801 (B=20)', raw, 801, True, mu_law=True, reps=1)
-    fatchord('4: config 2 with 16x1 block-pruned GRU (10 % kept), dense kernels on masked weights', mol, 801, True, prune=0.1)
+    fatchord('4: config 2 with 16x1 block-pruned GRU (10 % kept), 16x1 block-sparse tables', mol, 801, True, prune=0.1)
     fatchord('5 (8 of 256 utterances): MoL batched T=801, 160 folds in groups of 20', mol, 801, True, n_utt=8, reps=1)
     deepmind(1)
     deepmind(8)

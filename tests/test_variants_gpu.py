@@ -93,10 +93,39 @@ def test_pruned_16x1_vs_dense_oracle_on_masked_weights(name):
     wave = v.generate([mel[0]], batched, target, overlap, mu_law, noise=noise)[0]
     ref = ofc.generate(ofc.to_torch(sd2), dims, mel, batched, target, overlap, mu_law, noise)
     assert wave.shape == ref.shape and np.abs(wave - ref).max() <= 2e-4
+    if name.startswith('full'):
+        assert v.loop_kernel_name(B) == 'fma-resident-sparse16x1'       # the dedicated 16x1 block-sparse products
     # loading weights again restores the dense model
     v.load_weights(sd)
+    if name.startswith('full'):
+        assert v.loop_kernel_name(B) == 'fma-resident'
     dense = v.generate([mel[0]], batched, target, overlap, mu_law, noise=noise)[0]
     assert np.abs(dense - golden(name)['wave']).max() <= 2e-4
+
+
+@pytest.mark.parametrize('mode,keep', [('RAW', 0.1), ('MOL', 0.03), ('MOL', 0.14)])
+def test_pruned_checkpoint_is_detected_and_runs_on_the_sparse_tables(mode, keep):
+    """A checkpoint that was pruned elsewhere (the masked weights arrive through load_weights) takes the 16x1
+    block-sparse tables when every (CTA, gate) keeps <= 80 columns, else the dense products; both against the dense
+    oracle on the same masked weights.  RAW mode: sparse products beside the in-row fc3.  21 folds: two groups."""
+    dims = VocoderDims(mode=mode)
+    H = dims.rnn_dims
+    sd = dict(synth.synth_state_dict(dims, seed=2, style='init'))
+    for k in ('rnn1.weight_ih_l0', 'rnn1.weight_hh_l0', 'rnn2.weight_ih_l0', 'rnn2.weight_hh_l0'):
+        sd[k] = _mask_16x1(sd[k], H, keep)
+    mel = synth.synth_mel(26, seed=8, feat_dims=dims.feat_dims)
+    v = binding.Vocoder(dims, device=0)
+    v.load_weights(sd)
+    assert v.loop_kernel_name(20) == ('fma-resident' if keep > 0.12 else 'fma-resident-sparse16x1')
+    W = ofc.to_torch(sd)
+    target, overlap = 300, 40
+    with torch.no_grad():
+        m, aux, wave_len = ofc.conditioning(W, dims, mel, True, target, overlap)
+    B, S = int(m.shape[0]), int(m.shape[1])
+    noise = synth.synth_noise_mol(S, B, 9) if mode == 'MOL' else synth.synth_noise_exp(S, B, dims.n_classes, 9)
+    wave = v.generate([mel[0]], True, target, overlap, mode == 'RAW', noise=noise)[0]
+    ref = ofc.generate(W, dims, mel, True, target, overlap, mode == 'RAW', noise)
+    assert wave.shape == ref.shape and np.abs(wave - ref).max() <= 2e-4
 
 
 @pytest.mark.parametrize('kernel', [1, 2])

@@ -218,7 +218,7 @@ const char *wrnn_loop_kernel_name(wrnn_handle *h, int64_t folds) {
     if (!h) return "none";
     if (!h->packed && !h->w.empty()) ensure_packed_public(h);
     const int k = loop_kernel_choice(h);
-    return k == 3 ? "fma-resident" : (k == 2 ? "fma-pipelined" : "fma");
+    return k == 3 ? (h->res.sparse ? "fma-resident-sparse16x1" : "fma-resident") : (k == 2 ? "fma-pipelined" : "fma");
 }
 
 int wrnn_set_loop_kernel(wrnn_handle *h, int32_t which) {

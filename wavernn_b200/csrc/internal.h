@@ -57,6 +57,7 @@ struct PipePlan {
 // ---- per-sample loop, register-resident warp-specialised kernel (loop_res.cu) ----------------
 struct ResPlan {
     bool ok = false;
+    bool sparse = false;           // every (CTA, gate) of the three GRU matrices keeps <= 80 columns: 16x1 block-sparse tables in use
     int G = 0;
     float *img = nullptr;          // device [128][IMG_FLOATS]
     float *tail_img = nullptr;     // device fc3 rows + bias

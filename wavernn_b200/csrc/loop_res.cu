@@ -54,7 +54,13 @@ constexpr int IMG_F3 = IMG_F2 + 4 * RH;           // [4][512]   fc3 (RAW mode, 5
 constexpr int IMG_CU = IMG_F3 + 4 * RH;           // [32][WCL]
 constexpr int IMG_W0 = IMG_CU + 32 * WCL;         // [32] column 0 (x_prev): i1[12] i2[12] f1[4] pad[4]
 constexpr int IMG_B = IMG_W0 + 32;                // [64] biases: i1[12] i2[12] f1[4] f2[4] hh1[12] hh2[12] f3[4] pad
-constexpr int IMG_FLOATS = IMG_B + 64;
+// 16x1 block-sparse tables (pruned GRU matrices, SURVEY.md row S / utils/prune.py of the north star): the four rows a
+// CTA owns of one gate lie inside one 16-row block, so they share their kept columns.  Per matrix (W_ih2a, W_hh1,
+// W_hh2) and gate: { n8 (chunks of 8 kept columns), pad[3], cols[SPC] (int), vals[SPC][4 units] }.
+constexpr int SPC = 80;                           // kept columns per (CTA, gate) the tables hold; more -> dense path
+constexpr int SPG = 4 + SPC + 4 * SPC;            // floats per gate table
+constexpr int IMG_SP = IMG_B + 64;                // [3 matrices][3 gates][SPG]
+constexpr int IMG_FLOATS = IMG_SP + 9 * SPG;
 
 struct ResParams {
     Dims d;
@@ -69,6 +75,7 @@ struct ResParams {
     int *abort_flag;
     long long *prof;
     int d1, d2, d3;                          // WRNN_D1 / _D2 / _D3: override the gather delays of h1, x2', y1 (debug)
+    int sparse;                              // the GRU matrices are 16x1 block-sparse: GA / GB / GC walk the kept-column tables
 };
 
 // shared memory carve (floats)
@@ -89,7 +96,9 @@ constexpr int SM_W0B = SM_WC + SM_WCN;            // w0[32] | biases[64] (copy o
 constexpr int SM_PROF = SM_W0B + 96;              // 64-bit clock accumulators: [8] sum, [8] max, [8] min per phase; poll counters (debug)
 constexpr int SM_HIST = SM_PROF + 64 + 16 + 32;   // [8 phases][32 buckets of 512 clk] per-step duration histogram (debug)
 constexpr int SM_GP = SM_HIST + 256;               // [4 groups][16 marks] 64-bit clock accumulators of the group leaders (debug)
-constexpr int SM_FLOATS = SM_GP + 128;
+constexpr int SM_SP = SM_GP + 128;                // 16x1 block-sparse tables [3][3][SPG] (copy of the image tail; sparse models only)
+constexpr int SM_FLOATS = SM_SP + 9 * SPG;
+static_assert(SM_FLOATS * 4 <= 232448, "over the 227 KB a CTA can opt in to on sm_100");
 
 // ---------------------------------------------------------------------------- polling with a sticky abort
 struct Dead {
@@ -243,6 +252,45 @@ __device__ __forceinline__ void gru_job(const GruW &w, const float *buf, int FG,
     }
 }
 // sum of gate row r (0..11), fold f over the two K halves (fixed order)
+// 16x1 block-sparse version of gru_job, one warp pass of the 15 a matrix takes (tab: [3 gates][SPG]): pass p is one
+// gate and four folds, lane = (fold, one of eight kept columns of a chunk); the eight column partials are added by
+// shuffles and land in the slot gru_out reads for K half 0 (the slot of half 1 stays zero: the dense job never runs on
+// a sparse model).  A pass is a short latency-bound chain, so the passes of a job go to as many warps as are idle.
+__device__ __forceinline__ void sparse_pass(const float *tab, const float *buf, int p, int B, float *red, int lane) {
+    const int fq = p / 3, g = p - fq * 3;
+    if (fq * 4 >= B) return;
+    const int j = lane & 7, f = fq * 4 + (lane >> 3);
+    const float *tg_ = tab + g * SPG;
+    const int n8 = __float_as_int(tg_[0]);
+    const int *cols = reinterpret_cast<const int *>(tg_ + 4) + j;
+    const float4 *vals = reinterpret_cast<const float4 *>(tg_ + 4 + SPC) + j;
+    const float *x = buf + f * RH;
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll 4
+    for (int c = 0; c < n8; c++) {
+        const float xv = x[cols[c * 8]];
+        const float4 wv = vals[c * 8];
+        a0 = fmaf(wv.x, xv, a0);
+        a1 = fmaf(wv.y, xv, a1);
+        a2 = fmaf(wv.z, xv, a2);
+        a3 = fmaf(wv.w, xv, a3);
+    }
+#pragma unroll
+    for (int o = 4; o; o >>= 1) {
+        a0 += __shfl_xor_sync(0xffffffffu, a0, o);
+        a1 += __shfl_xor_sync(0xffffffffu, a1, o);
+        a2 += __shfl_xor_sync(0xffffffffu, a2, o);
+        a3 += __shfl_xor_sync(0xffffffffu, a3, o);
+    }
+    if (j == 0) {
+        const int fg = f / 5, fl = f - fg * 5, r0 = g * RU, base = fg * 32 + fl * 6;
+        red[((r0 / 6) * 2) * 128 + base + r0 % 6] = a0;
+        red[(((r0 + 1) / 6) * 2) * 128 + base + (r0 + 1) % 6] = a1;
+        red[(((r0 + 2) / 6) * 2) * 128 + base + (r0 + 2) % 6] = a2;
+        red[(((r0 + 3) / 6) * 2) * 128 + base + (r0 + 3) % 6] = a3;
+    }
+    __syncwarp();
+}
 __device__ __forceinline__ float gru_out(const float *red, int r, int f) {
     const int rg = r / 6, i = r - rg * 6, fg = f / 5, fl = f - fg * 5;
     return red[((rg * 2 + 0) * 4 + fg) * 32 + fl * 6 + i] + red[((rg * 2 + 1) * 4 + fg) * 32 + fl * 6 + i];
@@ -570,7 +618,7 @@ __device__ __forceinline__ void gather_wait(const float *src, int n4, float *dst
 // T4 3.7 k, T5 2.5 k, T6 3.3 k, T7 2.6 k = 27 k = 13.7 us.  The products are bound by the LSU pipe (LDS + SHFL
 // wavefronts: 36 % of peak over the whole step, two products side by side take twice as long as one), the
 // exchanges by L2 round trips; see DESIGN.md section 4.
-template <bool RAW>
+template <bool RAW, bool SP>
 __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
     const Dims &d = P.d;
     const int tid = threadIdx.x, gid = tid >> 7, tg = tid & 127, wq = tg >> 5, lane = tid & 31;
@@ -593,6 +641,9 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
     __syncthreads();
     for (int i = tid; i < SM_WCN + 96; i += RTH) smem[SM_WC + i] = __ldg(img + IMG_CU + i);     // matrix | w0 | biases are contiguous
     const float *wcu = smem + SM_WC;
+    constexpr bool sp = SP;                   // 16x1 block-sparse GRU matrices: own instantiation, the dense kernels stay as they were
+    const float *sptab = smem + SM_SP;
+    if (sp) for (int i = tid; i < 9 * SPG; i += RTH) smem[SM_SP + i] = __ldg(img + IMG_SP + i);
     __syncthreads();
     Dead dd{false, P.abort_flag, P.abort_flag, nullptr,
             (P.prof != nullptr && cta == 0) ? reinterpret_cast<unsigned int *>(smem + SM_PROF + 64) + gid * 4 : nullptr};
@@ -605,8 +656,12 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
 
     // ---- per-group register state: the weights live here for the whole call
     GruW w;                                   // GA: W_ih2a   GB: W_hh1   GC: W_hh2   GD: fc1 rows in a[0..3], fc2 rows in a[4], a[5], b[0], b[1]
-    if (gid < 3) load_gru_w(w, img + (gid == 0 ? IMG_IH2 : gid == 1 ? IMG_HH1 : IMG_HH2), wq, lane);
-    else {
+    if (gid < 3) {
+        if (!SP) load_gru_w(w, img + (gid == 0 ? IMG_IH2 : gid == 1 ? IMG_HH1 : IMG_HH2), wq, lane);
+        else
+#pragma unroll
+            for (int i = 0; i < 6; i++) w.a[i] = w.b[i] = make_float4(0.f, 0.f, 0.f, 0.f);      // sparse model: the tables in smem are the weights
+    } else {
         const float4 *p1 = reinterpret_cast<const float4 *>(img + IMG_F1), *p2 = reinterpret_cast<const float4 *>(img + IMG_F2);
 #pragma unroll
         for (int i = 0; i < 4; i++) w.a[i] = ld_keep4(p1 + (size_t)i * (RH / 4) + tg);
@@ -688,7 +743,18 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
         const float *pre_i1 = pre_cb + (t & 1) * 1280, *pre_i2 = pre_i1 + 240, *pre_f1 = pre_i1 + 480, *pre_f2 = pre_i1 + 560;
         if (t + 1 < S) fetch_cond(t + 1);                  // its buffer was last read two steps ago
         if (RAW && t > 0) raw_fc3(t - 1);
-        if (gid == 1 || gid == 2) {
+        if (sp) {
+            // sparse model: 2 x 15 short passes, spread over every warp that is idle here (RAW: warp 0 issues the y2
+            // gather and GD runs fc3); the products are complete at S5 and pre_h is formed beside the x_prev poll
+            constexpr int W0 = RAW ? 1 : 0, NW = RAW ? 11 : 16;
+            const int wi = tid >> 5;
+            __syncwarp();
+            if (wi >= W0 && wi < W0 + NW)
+                for (int p = wi - W0; p < 30; p += NW) {
+                    const bool g1 = p < 15;
+                    sparse_pass(sptab + (g1 ? 3 : 6) * SPG, g1 ? bufH1 : bufX, g1 ? p : p - 15, B, smem + SM_RED + (g1 ? 512 : 1024), lane);
+                }
+        } else if (gid == 1 || gid == 2) {
             const bool g1 = gid == 1;
             gru_job(w, g1 ? bufH1 : bufX, FG, red, wq, lane);
             bar_sync(g1 ? BAR_B : BAR_C, 128);
@@ -705,6 +771,15 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
         GMARK(0);
         // ---- T0: previous sample
         if (tid < B) xp[tid] = poll_xprev(P.xprev + par * RB + tid, (uint32_t)(t + 1), dd);
+        if (sp && (gid == 1 || gid == 2)) {
+            float *pre_h = gid == 1 ? pre_h1 : pre_h2;
+            const float *b_hh = gid == 1 ? b_hh1 : b_hh2;
+#pragma unroll 1
+            for (int i = tg; i < 12 * RB; i += 128) {
+                const int r = i / RB, f = i - r * RB;
+                pre_h[i] = gru_out(red, r, f) + b_hh[r];
+            }
+        }
         __syncthreads();                                                         // S0
         RPROF(1);
         GMARK(1);
@@ -739,9 +814,16 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
         RPROF(2);
         GMARK(5);
         // ---- T3: rnn2 (GA, alone on the SM)
+        if (sp) {                                           // sparse model: one pass per warp, all 16 warps
+            __syncwarp();
+            if ((tid >> 5) < 15) sparse_pass(sptab, bufH1, tid >> 5, B, smem + SM_RED, lane);
+            __syncthreads();
+        }
         if (gid == 0) {
-            gru_job(w, bufH1, FG, red, wq, lane);
-            bar_sync(BAR_A, 128);
+            if (!sp) {
+                gru_job(w, bufH1, FG, red, wq, lane);
+                bar_sync(BAR_A, 128);
+            }
             if (tg < 96) {
                 uint32_t xw = tag;
                 if (gate) {
@@ -831,11 +913,11 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
         for (int i = 0; i < 3; i++) P.prof[20 + gid * 3 + i] = dd.cnt[i];
 }
 
-template <bool RAW>
+template <bool RAW, bool SP>
 __global__ void __launch_bounds__(RTH, 1) res_loop_kernel(const ResParams P) {
     extern __shared__ __align__(16) float smem[];
     const int cta = blockIdx.x;
-    if (cta < RNR) res_row_role<RAW>(P, cta, smem);
+    if (cta < RNR) res_row_role<RAW, SP>(P, cta, smem);
     else res_tail_role<RAW>(P, cta - RNR, smem);
 }
 
@@ -936,6 +1018,37 @@ int res_plan(wrnn_handle *h) {
             }
         }
     }
+    // 16x1 block-sparse tables: a column of (CTA, gate) is kept when any of the four unit rows holds a non-zero there
+    // (the mask of utils/prune.py is constant over a 16-row block, so this finds the block structure of any pruned
+    // checkpoint, not only of one pruned through wrnn_prune_16x1).  One (CTA, gate) over SPC columns -> dense path.
+    bool sparse = true;
+    for (int c = 0; c < RNR && sparse; c++) {
+        float *im = img.data() + (size_t)c * IMG_FLOATS;
+        const int moff[3] = {IMG_IH2, IMG_HH1, IMG_HH2};
+        for (int m = 0; m < 3 && sparse; m++)
+            for (int g = 0; g < 3 && sparse; g++) {
+                float *tab = im + IMG_SP + (size_t)(m * 3 + g) * SPG;
+                int *cols = reinterpret_cast<int *>(tab + 4);
+                float *vals = tab + 4 + SPC;
+                int n = 0;
+                for (int k = 0; k < RH && sparse; k++) {
+                    float v[RU];
+                    bool any = false;
+                    for (int u = 0; u < RU; u++) {
+                        v[u] = im[moff[m] + (size_t)(g * RU + u) * RH + k];
+                        any = any || v[u] != 0.f;
+                    }
+                    if (!any) continue;
+                    if (n == SPC) { sparse = false; break; }
+                    cols[n] = k;
+                    for (int u = 0; u < RU; u++) vals[(size_t)n * 4 + u] = v[u];
+                    n++;
+                }
+                const int n8 = (n + 7) / 8;
+                memcpy(tab, &n8, sizeof(int));              // slots n .. 8 n8 - 1 stay {column 0, weights 0}
+            }
+    }
+    p.sparse = sparse;
     std::vector<float> timg((size_t)32 * RH + 32, 0.f);
     for (int r = 0; r < NC && !raw; r++) {
         memcpy(timg.data() + (size_t)r * RH, F3->v.data() + (size_t)r * FC, (size_t)FC * sizeof(float));
@@ -948,8 +1061,10 @@ int res_plan(wrnn_handle *h) {
     WRNN_CUDA(h, cudaMemcpy(p.img, img.data(), img.size() * sizeof(float), cudaMemcpyHostToDevice));
     WRNN_CUDA(h, cudaMalloc((void **)&p.tail_img, timg.size() * sizeof(float)));
     WRNN_CUDA(h, cudaMemcpy(p.tail_img, timg.data(), timg.size() * sizeof(float), cudaMemcpyHostToDevice));
-    WRNN_CUDA(h, cudaFuncSetAttribute(res_loop_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem_bytes));
-    WRNN_CUDA(h, cudaFuncSetAttribute(res_loop_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem_bytes));
+    WRNN_CUDA(h, cudaFuncSetAttribute(res_loop_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem_bytes));
+    WRNN_CUDA(h, cudaFuncSetAttribute(res_loop_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem_bytes));
+    WRNN_CUDA(h, cudaFuncSetAttribute(res_loop_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem_bytes));
+    WRNN_CUDA(h, cudaFuncSetAttribute(res_loop_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem_bytes));
     p.ok = true;
     return 0;
 }
@@ -984,13 +1099,17 @@ int res_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
     P.d2 = d2_env;
     static const int d3_env = getenv("WRNN_D3") ? atoi(getenv("WRNN_D3")) : 0;
     P.d3 = d3_env;
+    static const bool force_dense = getenv("WRNN_DENSE") != nullptr;       // A/B measurement: dense job on the masked weights
+    P.sparse = (p.sparse && !force_dense) ? 1 : 0;
     P.prof = nullptr;
     if (prof_env) {
         WRNN_TRY(ws_reserve(h, h->ws_prof, (128 + RNR * 8 + RNR * 128) * sizeof(long long)));
         WRNN_CUDA(h, cudaMemsetAsync(h->ws_prof.p, 0, (128 + RNR * 8 + RNR * 128) * sizeof(long long), st));
         P.prof = (long long *)h->ws_prof.p;
     }
-    const void *kern = d.mode == WRNN_MODE_MOL ? (const void *)res_loop_kernel<false> : (const void *)res_loop_kernel<true>;
+    const bool rawm = d.mode != WRNN_MODE_MOL;
+    const void *kern = P.sparse ? (rawm ? (const void *)res_loop_kernel<true, true> : (const void *)res_loop_kernel<false, true>)
+                                : (rawm ? (const void *)res_loop_kernel<true, false> : (const void *)res_loop_kernel<false, false>);
     void *args[] = {(void *)&P};
     WRNN_CUDA(h, cudaLaunchCooperativeKernel(kern, dim3(p.G), dim3(RTH), args, p.smem_bytes, st));
     h->launches++;
