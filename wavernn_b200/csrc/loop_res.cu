@@ -71,10 +71,10 @@ struct ResParams {
     LoopArgs a;
     float *h1, *h2, *x2, *y1, *y2;           // [2][B][512] tagged words (h2: unused since h2 = x2' - h1 is formed locally)
     float *y3;                               // [2][B][512] RAW mode: the 512 logits (fc3 rows live in the row CTAs)
-    unsigned long long *xprev;               // [2][RB]
+    unsigned long long *xprev;               // [128 row CTAs][2][RB]: {fp32 sample, step + 1}, one copy per row CTA
     int *abort_flag;
     long long *prof;
-    int d1, d2, d3;                          // WRNN_D1 / _D2 / _D3: override the gather delays of h1, x2', y1 (debug)
+    int d1, d2, d3, d4;                      // WRNN_D1 .. _D4: override the gather delays of h1, x2', y1, y2 (debug)
     int sparse;                              // the GRU matrices are 16x1 block-sparse: GA / GB / GC walk the kept-column tables
 };
 
@@ -224,11 +224,11 @@ __device__ __forceinline__ void load_gru_w(GruW &w, const float *img, int wq, in
         w.b[i] = ld_keep4(p + (size_t)(rg * 6 + i) * (RH / 4) + kw * 64 + 32 + lane);
     }
 }
-__device__ __forceinline__ void gru_job(const GruW &w, const float *buf, int FG, float *red, int wq, int lane) {
+__device__ __forceinline__ void gru_job(const GruW &w, const float *buf, int fg0, int fg1, float *red, int wq, int lane) {
     __syncwarp();
     const int kw = wq & 1;
     const float4 *x4 = reinterpret_cast<const float4 *>(buf) + kw * 64 + lane;
-    for (int fg = 0; fg < FG; fg++) {
+    for (int fg = fg0; fg < fg1; fg++) {
         float v[32];
         v[30] = v[31] = 0.f;
 #pragma unroll
@@ -399,6 +399,75 @@ __device__ __forceinline__ float mol_sample_smem2(const float *logits, int nmix,
     return x;
 }
 
+// -DWRNN_EVPROF: sums of %globaltimer (ns, common to all SMs) at five events of the sample chain, for one row CTA and
+// one tail CTA; differences of the sums / (S - 1) are the mean latencies between the events (printed with WRNN_PROF).
+#ifdef WRNN_EVPROF
+#define EV(var)                                                           \
+    do {                                                                  \
+        unsigned long long g_;                                            \
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g_));           \
+        var += (long long)(g_ & 0xFFFFFFFFFFull);                         \
+    } while (0)
+#else
+#define EV(var) do { } while (0)
+#endif
+// Block-wide form of categorical_warp (loop_common.cuh) for the tail CTAs of the resident kernel: C == RTH == 512, one
+// class per thread, the same arithmetic per class (softmax, Categorical's renormalisation, p / q, first maximum);
+// only the order of the two sums differs.  l: this thread's logit, q: its Exp(1) draw.  scr: 80 floats.  Returns the
+// class on every thread of warp 0.
+__device__ __forceinline__ int categorical_block(float l, float q, float *scr, int tid) {
+    const int warp = tid >> 5, lane = tid & 31;
+    float m = l;
+#pragma unroll
+    for (int o = 16; o >= 1; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if (lane == 0) scr[warp] = m;
+    __syncthreads();
+    m = scr[lane & 15];
+#pragma unroll
+    for (int o = 8; o >= 1; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    const float e = expf(l - m);
+    float s = e;
+#pragma unroll
+    for (int o = 16; o >= 1; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (lane == 0) scr[16 + warp] = s;
+    __syncthreads();
+    s = scr[16 + (lane & 15)];
+#pragma unroll
+    for (int o = 8; o >= 1; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    const float pn = e / s;
+    float ps = pn;                               // Categorical renormalises: probs / probs.sum(-1)
+#pragma unroll
+    for (int o = 16; o >= 1; o >>= 1) ps += __shfl_xor_sync(0xffffffffu, ps, o);
+    if (lane == 0) scr[32 + warp] = ps;
+    __syncthreads();
+    ps = scr[32 + (lane & 15)];
+#pragma unroll
+    for (int o = 8; o >= 1; o >>= 1) ps += __shfl_xor_sync(0xffffffffu, ps, o);
+    float best = (pn / ps) / q;
+    int bi = tid;
+    if (!(best > -INFINITY)) { best = -INFINITY; bi = 0x7fffffff; }       // as the warp form: a class that never wins a comparison
+#pragma unroll
+    for (int o = 16; o >= 1; o >>= 1) {
+        const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+        if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
+    }
+    if (lane == 0) {
+        scr[48 + warp] = best;
+        scr[64 + warp] = __int_as_float(bi);
+    }
+    __syncthreads();
+    best = scr[48 + (lane & 15)];
+    bi = __float_as_int(scr[64 + (lane & 15)]);
+#pragma unroll
+    for (int o = 8; o >= 1; o >>= 1) {
+        const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+        if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
+    }
+    return bi;
+}
+
 template <bool RAW>
 __device__ void res_tail_role(const ResParams &P, int j, float *smem) {
     const Dims &d = P.d;
@@ -425,7 +494,10 @@ __device__ void res_tail_role(const ResParams &P, int j, float *smem) {
     const int64_t Bt = P.a.Btot, b0 = P.a.b0;
     Dead dd{false, P.abort_flag, P.abort_flag, nullptr, nullptr};
     const bool prof_on = P.prof != nullptr && j == 0 && tid == 0;
-    long long pacc[4] = {0, 0, 0, 0}, pt = clock64();
+    const bool ev_t = P.prof != nullptr && tid == 0 && (j % 5 == 0 || j == 19);      // WRNN_EVPROF: x_prev publish time of tails 0, 5, 10, 15, 19
+    long long evj = 0;
+    (void)ev_t; (void)evj;
+    long long pacc[4] = {0, 0, 0, 0}, pt = clock64(), ev2 = 0, ev3 = 0;
 
     for (int64_t t = 0; t <= S; t++) {
         for (int f = j; f < B; f += P.NT) {
@@ -447,18 +519,27 @@ __device__ void res_tail_role(const ResParams &P, int j, float *smem) {
                         u2 = u_clip(r2.x);
                     }
                 }
+                float myq = 1.f;                           // RAW: this thread's class draw q ~ Exp(1), addressed as categorical_warp does
+                if (RAW) {
+                    if (P.a.q) myq = P.a.q[((size_t)tp * Bt + b) * NC + tid];
+                    else {
+                        const uint4 r = philox4x32(make_uint4((uint32_t)tp, (uint32_t)b, (uint32_t)((tid >> 7) * 32 + lane), 3u), key);
+                        const uint32_t rr[4] = {r.x, r.y, r.z, r.w};
+                        myq = exp1(rr[(tid >> 5) & 3]);
+                    }
+                }
                 if (tid < RH / 4)
                     gather_group((RAW ? P.y3 : P.y2) + ((size_t)(tp & 1) * B + f) * RH, RH / 4, ybuf, (uint32_t)((tp + 1) & 3), RH / 4, tid, dd);
                 __syncthreads();
+                if (prof_on && t < S) EV(ev2);
                 if (prof_on) { const long long n = clock64(); pacc[0] += n - pt; pt = n; }
                 if (RAW) {
                     // RAW branch (fatchord_version.py:231-237): ybuf holds the 512 logits of this fold (fc3 ran in the
                     // row CTAs); softmax -> Categorical.sample == argmax(p / q), q ~ Exp(1) -> 2k/(C-1) - 1.
                     if (P.a.logits_out && tp < P.a.fold_len[f])
                         for (int i = tid; i < NC; i += RTH) P.a.logits_out[((size_t)f * S + tp) * NC + i] = ybuf[i];
+                    pick = categorical_block(ybuf[tid], myq, lg + 32, tid);
                     if (warp == 0) {
-                        const float *qsrc = P.a.q ? P.a.q + ((size_t)tp * Bt + b) * NC : nullptr;
-                        pick = categorical_warp(ybuf, NC, qsrc, key, (uint32_t)tp, (uint32_t)b, 3u, lane);
                         xv = raw_value(pick, NC);
                         if (tp >= P.a.fold_len[f]) xv = 0.f;
                         else if (lane == 0) {
@@ -502,20 +583,29 @@ __device__ void res_tail_role(const ResParams &P, int j, float *smem) {
                 }
                 }
             }
-            if (warp == 0 && lane == 0 && t < S) {
+            if (warp == 0 && t < S) {
+                // one copy per row CTA: 2 560 pollers on the same two L2 lines saw the sample 1.6 us (MoL) to 4 us (RAW)
+                // after this store (measured with %globaltimer); with its own line a row CTA sees it after one round trip
                 if (P.a.teacher) xv = P.a.teacher[(size_t)f * S + t];
-                st_relaxed_u64(P.xprev + (size_t)(t & 1) * RB + f,
-                               ((unsigned long long)(uint32_t)(t + 1) << 32) | (unsigned long long)__float_as_uint(xv));
+                if (prof_on && t > 0) EV(ev3);
+                if (ev_t && t > 0) EV(evj);
+                const unsigned long long word = ((unsigned long long)(uint32_t)(t + 1) << 32) | (unsigned long long)__float_as_uint(xv);
+#pragma unroll
+                for (int c = 0; c < RNR / 32; c++) st_relaxed_u64(P.xprev + ((size_t)(c * 32 + lane) * 2 + (size_t)(t & 1)) * RB + f, word);
             }
             if (prof_on) { const long long n = clock64(); pacc[2] += n - pt; pt = n; }
         }
     }
     if (prof_on)
         for (int i = 0; i < 4; i++) P.prof[16 + i] = pacc[i];
+    if (prof_on) { P.prof[2] = ev2; P.prof[3] = ev3; }
+#ifdef WRNN_EVPROF
+    if (ev_t) P.prof[56 + (j == 19 ? 4 : j / 5)] = evj;
+#endif
 }
 
 // ---------------------------------------------------------------------------- row CTA
-enum { BAR_A = 1, BAR_B = 2, BAR_C = 3, BAR_D = 4, BAR_H1 = 5, BAR_GC2GA = 6, BAR_H1FREE = 7, BAR_AJOB = 8 };
+enum { BAR_A = 1, BAR_B = 2, BAR_C = 3, BAR_D = 4, BAR_H1 = 5, BAR_GC2GA = 6, BAR_H1FREE = 7, BAR_AJOB = 8, BAR_RAW = 9 };
 
 // Lanes 4k..4k+3 hold the tagged words of the CTA's four units (rows) of one fold: lane 4k stores them as
 // ONE 16-byte word, which is exactly one gather slot of every consumer.  All lanes of the warp call this.
@@ -713,6 +803,9 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
     pt = clock64();
     gpt = pt;
 
+    const bool ev_d = P.prof != nullptr && cta == 5 && tid == 384, ev_0 = P.prof != nullptr && cta == 5 && tid == 0;
+    long long ev0 = 0, ev1 = 0, ev4 = 0;
+    (void)ev_d; (void)ev_0; (void)ev0; (void)ev1; (void)ev4;
     const int d1 = P.d1 ? P.d1 : GATHER_DELAY_H1, d2 = P.d2 ? P.d2 : GATHER_DELAY_X2, d3 = P.d3 ? P.d3 : GATHER_DELAY_Y1;
     uint32_t gpar = 0;                                   // phase parity of the gather mbarrier
     // RAW mode: fc3 has 512 rows, four per row CTA like fc1 / fc2, so the chain goes on here: y2(tp) is exchanged
@@ -721,17 +814,20 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
     auto raw_fc3 = [&](int64_t tp) {
         const uint32_t tg3 = (uint32_t)((tp + 1) & 3);
         const size_t pp = (size_t)(tp & 1);
-        if (tid == 0) gather_issue(P.y2 + pp * B * RH, B * (RH / 4), bufY, GATHER_DELAY_Y2, mbar + 2);
+        if (tid == 0) gather_issue(P.y2 + pp * B * RH, B * (RH / 4), bufY, P.d4 ? P.d4 : GATHER_DELAY_Y2, mbar + 2);
         if (gid == 3) {
             gather_wait(P.y2 + pp * B * RH, B * (RH / 4), bufY, tg3, tg, 128, mbar + 2, gpar, dd);
+            if (ev_d && tp + 1 < S) EV(ev0);
             bar_sync(BAR_D, 128);
             fc_job(w.b[2], w.b[3], w.b[4], w.b[5], bufY, FG, red, wq, lane, tg);
+            if (!SP && tp + 1 < S) bar_arrive(BAR_RAW, 384);       // releases the second half of the shadow products (dense model)
             bar_sync(BAR_D, 128);
             if (tg < 96) {
                 uint32_t lw = tg3;
                 if (gate) lw = tag_word(fc_out(red, gu, gf) + bias[56 + gu], tg3);
                 publish4(P.y3 + (pp * B + gf) * RH + u0, lw, lane, gate);
             }
+            if (ev_d && tp + 1 < S) EV(ev1);
         }
         gpar ^= 1;
     };
@@ -741,8 +837,9 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
         // ---- P: everything step t needs that does not depend on sample t-1; for t > 0 this runs while the
         //         tail CTAs turn y2(t-1) into that sample
         const float *pre_i1 = pre_cb + (t & 1) * 1280, *pre_i2 = pre_i1 + 240, *pre_f1 = pre_i1 + 480, *pre_f2 = pre_i1 + 560;
-        if (t + 1 < S) fetch_cond(t + 1);                  // its buffer was last read two steps ago
+        if (!RAW && t + 1 < S) fetch_cond(t + 1);          // its buffer was last read two steps ago
         if (RAW && t > 0) raw_fc3(t - 1);
+        if (RAW && t + 1 < S) fetch_cond(t + 1);           // RAW: behind the y2 gather, which is on the chain to the next sample
         if (sp) {
             // sparse model: 2 x 15 short passes, spread over every warp that is idle here (RAW: warp 0 issues the y2
             // gather and GD runs fc3); the products are complete at S5 and pre_h is formed beside the x_prev poll
@@ -756,7 +853,17 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
                 }
         } else if (gid == 1 || gid == 2) {
             const bool g1 = gid == 1;
-            gru_job(w, g1 ? bufH1 : bufX, FG, red, wq, lane);
+            if (RAW && t > 0) {
+                // RAW: fc3(t-1) in GD is on the chain to the next sample, these products are not (needed after the
+                // sample is back).  First half while GD waits for y2, second half once its fc3 product is done.
+                const int fsplit = P.d3 == 7 ? 0 : (P.d3 == 8 ? 1 : FG / 2);
+                gru_job(w, g1 ? bufH1 : bufX, 0, fsplit, red, wq, lane);
+                bar_sync(BAR_RAW, 384);
+                GMARK(2);
+                gru_job(w, g1 ? bufH1 : bufX, fsplit, FG, red, wq, lane);
+                GMARK(3);
+            } else
+                gru_job(w, g1 ? bufH1 : bufX, 0, FG, red, wq, lane);
             bar_sync(g1 ? BAR_B : BAR_C, 128);
             float *pre_h = g1 ? pre_h1 : pre_h2;
             const float *b_hh = g1 ? b_hh1 : b_hh2;
@@ -766,21 +873,27 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
                 pre_h[i] = gru_out(red, r, f) + b_hh[r];
             }
         }
+        // x_prev(t): warp 0 polls for it inside P (after its bulk-copy issues / passes), so a sample that is back
+        // before the shadow products are done costs no L2 round trip after them
+        if (!sp && tid < B) xp[tid] = poll_xprev(P.xprev + ((size_t)cta * 2 + par) * RB + tid, (uint32_t)(t + 1), dd);
+        if (ev_0 && t > 0) EV(ev0);
         __syncthreads();                                                         // S5
         RPROF(0);
         GMARK(0);
-        // ---- T0: previous sample
-        if (tid < B) xp[tid] = poll_xprev(P.xprev + par * RB + tid, (uint32_t)(t + 1), dd);
-        if (sp && (gid == 1 || gid == 2)) {
-            float *pre_h = gid == 1 ? pre_h1 : pre_h2;
-            const float *b_hh = gid == 1 ? b_hh1 : b_hh2;
+        if (sp) {                                           // sparse model: the passes of all warps are complete only here
+            if (tid < B) xp[tid] = poll_xprev(P.xprev + ((size_t)cta * 2 + par) * RB + tid, (uint32_t)(t + 1), dd);
+            if (gid == 1 || gid == 2) {
+                float *pre_h = gid == 1 ? pre_h1 : pre_h2;
+                const float *b_hh = gid == 1 ? b_hh1 : b_hh2;
 #pragma unroll 1
-            for (int i = tg; i < 12 * RB; i += 128) {
-                const int r = i / RB, f = i - r * RB;
-                pre_h[i] = gru_out(red, r, f) + b_hh[r];
+                for (int i = tg; i < 12 * RB; i += 128) {
+                    const int r = i / RB, f = i - r * RB;
+                    pre_h[i] = gru_out(red, r, f) + b_hh[r];
+                }
             }
+            __syncthreads();                                                     // S0
         }
-        __syncthreads();                                                         // S0
+        if (ev_0 && t > 0) EV(ev4);
         RPROF(1);
         GMARK(1);
         // ---- T1: rnn1 gates (GB)
@@ -821,7 +934,7 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
         }
         if (gid == 0) {
             if (!sp) {
-                gru_job(w, bufH1, FG, red, wq, lane);
+                gru_job(w, bufH1, 0, FG, red, wq, lane);
                 bar_sync(BAR_A, 128);
             }
             if (tg < 96) {
@@ -893,6 +1006,7 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
                 if (gate) yw = tag_word(fmaxf(fc_out(red, gu, gf) + pre2(pre_f2, gu * RB + gf), 0.f), tag);
                 publish4(P.y2 + (par * B + gf) * RH + u0, yw, lane, gate);
             }
+            if (!RAW && ev_d && t + 1 < S) EV(ev1);
         }
         GMARK(14);
         // S4b: fc2 is on the chain, the shadow products are not.  Without this barrier GB and GC start them while
@@ -901,6 +1015,10 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
         RPROF(7);
     }
     if (RAW && S > 0) raw_fc3(S - 1);
+#ifdef WRNN_EVPROF
+    if (ev_d) { P.prof[0] = ev0; P.prof[1] = ev1; }
+    if (ev_0) { P.prof[4] = ev4; P.prof[5] = ev0; }
+#endif
     if (prof_on)
         for (int i = 0; i < 8; i++) P.prof[64 + cta * 8 + i] = pacc[i];
     if (prof_on)
@@ -1085,7 +1203,7 @@ int res_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
     P.a = a;
     const size_t BH = (size_t)a.B * RH;
     const size_t act_floats = 2 * 6 * BH;
-    const size_t xprev_bytes = 2 * RB * sizeof(unsigned long long);
+    const size_t xprev_bytes = (size_t)RNR * 2 * RB * sizeof(unsigned long long);
     WRNN_TRY(ws_reserve(h, h->ws_act, act_floats * sizeof(float) + xprev_bytes + 256));
     WRNN_CUDA(h, cudaMemsetAsync(h->ws_act.p, 0, act_floats * sizeof(float) + xprev_bytes + 256, st));
     float *base = (float *)h->ws_act.p;
@@ -1099,6 +1217,8 @@ int res_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
     P.d2 = d2_env;
     static const int d3_env = getenv("WRNN_D3") ? atoi(getenv("WRNN_D3")) : 0;
     P.d3 = d3_env;
+    static const int d4_env = getenv("WRNN_D4") ? atoi(getenv("WRNN_D4")) : 0;
+    P.d4 = d4_env;
     static const bool force_dense = getenv("WRNN_DENSE") != nullptr;       // A/B measurement: dense job on the masked weights
     P.sparse = (p.sparse && !force_dense) ? 1 : 0;
     P.prof = nullptr;
@@ -1133,6 +1253,19 @@ int res_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
         fprintf(stderr, " | CTA 5 per-step min..max:");
         for (int i = 0; i < 8; i++) fprintf(stderr, " %s=%lld..%lld", names[i], pr[48 + i], pr[40 + i]);
         fprintf(stderr, " | tail 0: gather_y2=%.0f fc3=%.0f sample=%.0f\n", pr[16] / s, pr[17] / s, pr[18] / s);
+        fprintf(stderr, "[wrnn prof] row CTA 0, slot re-fetch rounds per step summed over the threads of group A / B / C / D: %.2f %.2f %.2f %.2f\n",
+                pr[20] / s, pr[23] / s, pr[26] / s, pr[29] / s);
+#ifdef WRNN_EVPROF
+        {
+            const double n = s - 1.0;
+            fprintf(stderr, "[wrnn prof] sample chain, mean ns (row CTA 5, tail CTA 0): rows' y2 gather -> logits published=%.0f | published -> tail has them=%.0f | "
+                            "tail sampling -> x_prev published=%.0f | published -> row CTA past S0=%.0f\n",
+                    pr[0] ? (pr[1] - pr[0]) / n : 0.0, (pr[2] - pr[1]) / n, (pr[3] - pr[2]) / n, (pr[4] - pr[3]) / n);
+            fprintf(stderr, "[wrnn prof] x_prev published by tail 0 -> seen by thread 0 of row CTA 5: %.0f ns\n", (pr[5] - pr[3]) / n);
+            fprintf(stderr, "[wrnn prof] x_prev publish of tails 5, 10, 15, 19 after tail 0, mean ns: %.0f %.0f %.0f %.0f\n", (pr[57] - pr[56]) / n,
+                    (pr[58] - pr[56]) / n, (pr[59] - pr[56]) / n, (pr[60] - pr[56]) / n);
+        }
+#endif
         if (getenv("WRNN_PROF_GROUPS")) {
             static const char *marks[15] = {"S5", "S0", "S0b", "work_h1", "fetch_h1", "S1", "S1b", "work_x2", "fetch_x2", "S2", "S3", "work_y1",
                                             "fetch_y1", "S4", "end"};
