@@ -263,7 +263,7 @@ int check_abort(wrnn_handle *h, cudaStream_t st) {
         WRNN_CUDA(h, cudaMemcpyAsync(&flag, (char *)h->ws_sync.p + 64, sizeof(int), cudaMemcpyDeviceToHost, st));
         WRNN_CUDA(h, cudaStreamSynchronize(st));
     }
-    if (flag) return fail(h, WRNN_ERR_CUDA, "per-sample loop kernel aborted: exchange watchdog fired");
+    if (flag) return fail(h, WRNN_ERR_CUDA, "per-sample loop kernel aborted: exchange watchdog fired (code %d)", flag);
     return 0;
 }
 

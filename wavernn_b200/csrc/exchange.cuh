@@ -44,10 +44,13 @@ constexpr long long WATCHDOG_CLOCKS = 4000000000ll;     // ~2 s: a lost exchange
 
 // named barriers (sub-CTA thread groups)
 __device__ __forceinline__ void bar_sync(int id, int nthreads) {
-    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+    // barrier.sync, not its .aligned form bar.sync: lanes leave poll loops at different times, and a warp that arrives
+    // in two fragments is counted twice by the aligned barrier (seen as a hang when the lane that issues a gather
+    // sits in the group that then synchronises on a named barrier)
+    asm volatile("barrier.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
 __device__ __forceinline__ void bar_arrive(int id, int nthreads) {
-    asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+    asm volatile("barrier.arrive %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
 
 }  // namespace wrnn
