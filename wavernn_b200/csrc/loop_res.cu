@@ -296,46 +296,57 @@ __device__ __forceinline__ float gru_out(const float *red, int r, int f) {
     return red[((rg * 2 + 0) * 4 + fg) * 32 + fl * 6 + i] + red[((rg * 2 + 1) * 4 + fg) * 32 + fl * 6 + i];
 }
 
-// 4 rows x 512 over 128 threads: thread owns float4 column tg of all 4 rows.
-struct FcW {
-    float4 r[4];
-};
-__device__ __forceinline__ void load_fc_w(FcW &w, const float *img, int tg) {
-    const float4 *p = reinterpret_cast<const float4 *>(img);
-#pragma unroll
-    for (int i = 0; i < 4; i++) w.r[i] = ld_keep4(p + (size_t)i * (RH / 4) + tg);
+// 4 rows x 512 over 128 threads: thread owns float4 column tg of all 4 rows.  Eight folds at a time: 32 partial sums
+// per lane, reduce-scattered over the warp WITHOUT the two selects per element of warp_reduce_scatter: lane L forms in
+// register j the partial of output j ^ L (fold (j >> 2) ^ (L >> 2) of the chunk, row (j & 3) ^ (L & 3)), so that at
+// every level the half a lane keeps is in its low registers and the half it sends in its high ones.  The fold part of
+// the permutation is an address, the row part is baked into the weight registers when they are loaded
+// (load_fc_rows: slot i of lane L holds row i ^ (L & 3)).  Lane L ends with output L = fold (L >> 2), row L & 3.
+// The source-level profile had the reduce-scatter at ~45 % of a job (profiles/r01e_schedule_experiments.txt).
+__device__ __forceinline__ void load_fc_rows(float4 &s0, float4 &s1, float4 &s2, float4 &s3, const float *rows, int tg, int lane) {
+    const float4 *p = reinterpret_cast<const float4 *>(rows);
+    const int x = lane & 3;
+    s0 = ld_keep4(p + (size_t)(0 ^ x) * (RH / 4) + tg);
+    s1 = ld_keep4(p + (size_t)(1 ^ x) * (RH / 4) + tg);
+    s2 = ld_keep4(p + (size_t)(2 ^ x) * (RH / 4) + tg);
+    s3 = ld_keep4(p + (size_t)(3 ^ x) * (RH / 4) + tg);
 }
-__device__ __forceinline__ void fc_job(const float4 &r0, const float4 &r1, const float4 &r2, const float4 &r3, const float *buf, int FG,
+__device__ __forceinline__ void fc_job(const float4 &r0, const float4 &r1, const float4 &r2, const float4 &r3, const float *buf, int B,
                                        float *red, int wq, int lane, int tg) {
     __syncwarp();
     const float4 wr[4] = {r0, r1, r2, r3};
     const float4 *x4 = reinterpret_cast<const float4 *>(buf) + tg;
-    for (int fg = 0; fg < FG; fg++) {
+    const int lf = lane >> 2;
+    for (int c = 0; c * 8 < B; c++) {
         float v[32];
 #pragma unroll
-        for (int i = 20; i < 32; i++) v[i] = 0.f;
-#pragma unroll
-        for (int fl = 0; fl < 5; fl++) {
-            const float4 x = x4[(fg * 5 + fl) * (RH / 4)];
+        for (int jf = 0; jf < 8; jf++) {
+            const int f = min(c * 8 + (jf ^ lf), RB - 1);         // folds >= B: stale rows inside the buffer, outputs never read
+            const float4 x = x4[f * (RH / 4)];
 #pragma unroll
             for (int i = 0; i < 4; i++) {
                 float s = wr[i].x * x.x;
                 s = fmaf(wr[i].y, x.y, s);
                 s = fmaf(wr[i].z, x.z, s);
                 s = fmaf(wr[i].w, x.w, s);
-                v[fl * 4 + i] = s;
+                v[jf * 4 + i] = s;
             }
         }
-        warp_reduce_scatter<32>(v, lane);
-        red[(wq * 4 + fg) * 32 + lane] = v[0];
+#pragma unroll
+        for (int lvl = 0; lvl < 5; lvl++) {
+            const int half = 16 >> lvl;
+#pragma unroll
+            for (int i = 0; i < half; i++) v[i] += __shfl_xor_sync(0xffffffffu, v[i + half], half);
+        }
+        red[(wq * 3 + c) * 32 + lane] = v[0];
     }
 }
 __device__ __forceinline__ float fc_out(const float *red, int r, int f) {
-    const int fg = f / 5, fl = f - fg * 5, idx = fl * 4 + r;
-    float s = red[(0 * 4 + fg) * 32 + idx];
-    s += red[(1 * 4 + fg) * 32 + idx];
-    s += red[(2 * 4 + fg) * 32 + idx];
-    s += red[(3 * 4 + fg) * 32 + idx];
+    const int c = f >> 3, idx = (f & 7) * 4 + r;
+    float s = red[(0 * 3 + c) * 32 + idx];
+    s += red[(1 * 3 + c) * 32 + idx];
+    s += red[(2 * 3 + c) * 32 + idx];
+    s += red[(3 * 3 + c) * 32 + idx];
     return s;
 }
 
@@ -752,16 +763,11 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
 #pragma unroll
             for (int i = 0; i < 6; i++) w.a[i] = w.b[i] = make_float4(0.f, 0.f, 0.f, 0.f);      // sparse model: the tables in smem are the weights
     } else {
-        const float4 *p1 = reinterpret_cast<const float4 *>(img + IMG_F1), *p2 = reinterpret_cast<const float4 *>(img + IMG_F2);
+        load_fc_rows(w.a[0], w.a[1], w.a[2], w.a[3], img + IMG_F1, tg, lane);         // rows permuted per lane, see fc_job
+        load_fc_rows(w.a[4], w.a[5], w.b[0], w.b[1], img + IMG_F2, tg, lane);
 #pragma unroll
-        for (int i = 0; i < 4; i++) w.a[i] = ld_keep4(p1 + (size_t)i * (RH / 4) + tg);
-        w.a[4] = ld_keep4(p2 + tg);
-        w.a[5] = ld_keep4(p2 + (RH / 4) + tg);
-        w.b[0] = ld_keep4(p2 + 2 * (RH / 4) + tg);
-        w.b[1] = ld_keep4(p2 + 3 * (RH / 4) + tg);
-        const float4 *p3 = reinterpret_cast<const float4 *>(img + IMG_F3);       // RAW mode: fc3 rows; zeros in MoL mode
-#pragma unroll
-        for (int i = 0; i < 4; i++) w.b[2 + i] = RAW ? ld_keep4(p3 + (size_t)i * (RH / 4) + tg) : make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int i = 0; i < 4; i++) w.b[2 + i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (RAW) load_fc_rows(w.b[2], w.b[3], w.b[4], w.b[5], img + IMG_F3, tg, lane);      // RAW mode: fc3 rows
     }
     const int gu = tg & 3, gf = tg >> 2;      // gate / epilogue thread: unit (row) gu of fold gf
     const bool gate = gf < B;
@@ -819,7 +825,7 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
             gather_wait(P.y2 + pp * B * RH, B * (RH / 4), bufY, tg3, tg, 128, mbar + 2, gpar, dd);
             if (ev_d && tp + 1 < S) EV(ev0);
             bar_sync(BAR_D, 128);
-            fc_job(w.b[2], w.b[3], w.b[4], w.b[5], bufY, FG, red, wq, lane, tg);
+            fc_job(w.b[2], w.b[3], w.b[4], w.b[5], bufY, B, red, wq, lane, tg);
             if (!SP && tp + 1 < S) bar_arrive(BAR_RAW, 384);       // releases the second half of the shadow products (dense model)
             bar_sync(BAR_D, 128);
             if (tg < 96) {
@@ -967,7 +973,7 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
         GMARK(9);
         // ---- T5: fc1 (GD)
         if (gid == 3) {
-            fc_job(w.a[0], w.a[1], w.a[2], w.a[3], bufX, FG, red, wq, lane, tg);
+            fc_job(w.a[0], w.a[1], w.a[2], w.a[3], bufX, B, red, wq, lane, tg);
             bar_sync(BAR_D, 128);
             if (tg < 96) {
                 uint32_t yw = tag;
@@ -999,7 +1005,7 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
         GMARK(13);
         // ---- T7: fc2 (GD)
         if (gid == 3) {
-            fc_job(w.a[4], w.a[5], w.b[0], w.b[1], bufY, FG, red, wq, lane, tg);
+            fc_job(w.a[4], w.a[5], w.b[0], w.b[1], bufY, B, red, wq, lane, tg);
             bar_sync(BAR_D, 128);
             if (tg < 96) {
                 uint32_t yw = tag;
