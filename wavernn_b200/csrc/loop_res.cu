@@ -82,7 +82,7 @@ struct ResParams {
 constexpr int SM_H1 = 0;                          // [20][512] h1(t)                                  (GA, GB)
 constexpr int SM_H2 = SM_H1 + RB * RH;            // [20][512] y1(t)                                  (GD)
 constexpr int SM_X = SM_H2 + RB * RH;             // [20][512] x2'(t), turned into h2(t) in place     (GD, GC)
-constexpr int GATHER_DELAY_H1 = 1700, GATHER_DELAY_X2 = 1200, GATHER_DELAY_Y1 = 700, GATHER_DELAY_Y2 = 700;   // clocks, see gather_issue
+constexpr int GATHER_DELAY_H1 = 1700, GATHER_DELAY_X2 = 1500, GATHER_DELAY_Y1 = 1000, GATHER_DELAY_Y2 = 700;   // clocks, see gather_issue
 constexpr int CBL = 228;                          // conditioning row stride in smem: >= 224, and 4 banks apart per fold (float4 reads by 8 lanes)
 constexpr int SM_CB = SM_X + RB * RH;             // [2][20][228] whole conditioning rows of steps t, t+1 (TMA bulk copies)
 constexpr int SM_MBAR = SM_CB + 2 * RB * CBL;     // three mbarriers (8 bytes each): conditioning buffer 0, 1, the gathers
