@@ -1,3 +1,5 @@
+"""Loop time of one variant of config 2 on one GPU: `python scripts/time_variant.py raw|sp|mol` (RAW 9-bit mu-law,
+16x1 block-sparse GRU, dense MoL).  scripts/time_config2.py times the dense MoL kernel with a fold count argument."""
 import sys, os, time, json
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from wavernn_b200 import binding, synth
