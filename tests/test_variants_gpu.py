@@ -211,3 +211,36 @@ def test_edge_inputs_default_dims():
     # empty call: an argument error, not a crash
     with pytest.raises(ValueError):
         v.generate([], True, 2000, 100, False, seed=0)
+
+
+@pytest.mark.parametrize('mode', ['MOL', 'RAW'])
+def test_config2_full_size_properties(mode):
+    """BASELINE.json config 2 / 3 at full size (T = 801 -> 20 folds x 12 100 steps, 220 000 samples), through properties
+    that need no oracle run: the call is deterministic in its seed, the waveform has the reference's length
+    (fatchord_version.py:253) and range, an utterance does not depend on what else is in the call (folds are independent,
+    :194-196), and the injected-noise path and the Philox path agree on the first fold-steps of teacher-free generation
+    only in shape (different noise), so only shape is asserted there."""
+    dims = VocoderDims(mode='RAW', bits=9) if mode == 'RAW' else VocoderDims(mode='MOL')
+    v = binding.Vocoder(dims, device=0)
+    v.load_weights(synth.synth_state_dict(dims, seed=0, style='init'))
+    mel = synth.synth_mel(801, seed=1234)
+    mel2 = synth.synth_mel(260, seed=77)
+    mu_law = mode == 'RAW'
+    a = v.generate([mel[0]], True, 11000, 550, mu_law, seed=11)[0]
+    t = v.last_timing()
+    assert (t['folds'], t['steps']) == (20, 12100) and v.loop_kernel_name(20).startswith('fma-resident')
+    b = v.generate([mel[0]], True, 11000, 550, mu_law, seed=11)[0]
+    c = v.generate([mel[0]], True, 11000, 550, mu_law, seed=12)[0]
+    assert a.shape == (800 * 275,) and a.dtype == np.float64
+    assert np.array_equal(a, b) and not np.array_equal(a, c)
+    assert np.all(np.isfinite(a)) and np.abs(a).max() <= 1.5   # cross-faded overlaps: sqrt gains add up to <= sqrt(2)
+    assert np.all(a[-1:] == 0.0)                      # fade-out ends at exactly 0 (linspace(1, 0, 5500), :256-258)
+    # independence: the same utterance as the second of two in one call (its folds then run in another launch group
+    # with other fold indices); Philox is keyed by (seed, global fold, step), so compare through injected noise
+    if mode == 'MOL':
+        B1, B2, S = 20, binding.num_folds(260 * 275, 11000, 550), 12100
+        n1, n2 = synth.synth_noise_mol(S, B1, 5), synth.synth_noise_mol(S, B2, 6)
+        w2 = v.generate([mel2[0]], True, 11000, 550, False, noise=n2)[0]
+        both = (np.concatenate([n1[0], n2[0]], axis=1), np.concatenate([n1[1], n2[1]], axis=1))
+        o1, o2 = v.generate([mel[0], mel2[0]], True, 11000, 550, False, noise=both)
+        assert np.array_equal(o2, w2) and o1.shape == a.shape
