@@ -75,6 +75,21 @@ __device__ __forceinline__ float gru_update(float ir, float iz, float in_, float
     return (h - n) * z + n;
 }
 
+// The same cell with the special-function unit (ex2.approx through __expf, rcp through __fdividef): |error| ~ 2e-7
+// per gate, below the 3.6e-7 the tagged exchange words already carry.  For the resident kernel, where the 80 gate
+// threads of a CTA sit on the sample-to-sample chain twice per step; the exact-order kernels keep gru_update.
+__device__ __forceinline__ float sigmoidf_fast(float x) { return __fdividef(1.0f, 1.0f + __expf(-x)); }
+__device__ __forceinline__ float tanhf_fast(float x) {
+    const float e = __expf(-2.0f * fabsf(x));                 // in (0, 1]: no overflow
+    return copysignf(__fdividef(1.0f - e, 1.0f + e), x);
+}
+__device__ __forceinline__ float gru_update_fast(float ir, float iz, float in_, float hr, float hz, float hn, float h) {
+    const float r = sigmoidf_fast(hr + ir);
+    const float z = sigmoidf_fast(hz + iz);
+    const float n = tanhf_fast(in_ + hn * r);
+    return (h - n) * z + n;
+}
+
 // ---------------------------------------------------------------------------- samplers (one warp per fold)
 // sample_from_discretized_mix_logistic (utils/distribution.py:87-123) for one fold.  `logits` (3*nmix,
 // possibly written by another CTA: .cg loads), lane < nmix holds its own u1.  Returns the sample on

@@ -392,9 +392,11 @@ __device__ __forceinline__ void cond_all(const float *wcu, const float *cb, cons
 __device__ __forceinline__ float pre2(const float *part, int idx) { return part[idx] + part[640 + idx]; }
 
 // ---------------------------------------------------------------------------- tail CTA: fc3 + sampling
-__device__ __forceinline__ float mol_sample_smem2(const float *logits, int nmix, float myu1, float u2, int lane, int *pick) {
+// g1 = log(-log(u1)) of this lane's mixture and lg2 = log(u2) - log(1 - u2) do not depend on the logits: the caller
+// forms them while y2 is still on its way (same expressions, same results; ~300 clk off the sample-to-sample chain).
+__device__ __forceinline__ float mol_sample_smem2(const float *logits, int nmix, float g1, float lg2, int lane, int *pick) {
     float t = -INFINITY;
-    if (lane < nmix) t = logits[lane] - logf(-logf(myu1));
+    if (lane < nmix) t = logits[lane] - g1;
     int idx = lane;
 #pragma unroll
     for (int o = 16; o >= 1; o >>= 1) {
@@ -404,7 +406,7 @@ __device__ __forceinline__ float mol_sample_smem2(const float *logits, int nmix,
     }
     const float mean = logits[nmix + idx];
     const float ls = fmaxf(logits[2 * nmix + idx], -32.23619130191664f);   // log(1e-14)
-    float x = mean + expf(ls) * (logf(u2) - logf(1.f - u2));
+    float x = mean + expf(ls) * lg2;
     x = fminf(fmaxf(x, -1.f), 1.f);
     *pick = idx;
     return x;
@@ -530,6 +532,7 @@ __device__ void res_tail_role(const ResParams &P, int j, float *smem) {
                         u2 = u_clip(r2.x);
                     }
                 }
+                const float g1 = logf(-logf(myu1)), lg2 = logf(u2) - logf(1.f - u2);      // off the chain, see mol_sample_smem2
                 float myq = 1.f;                           // RAW: this thread's class draw q ~ Exp(1), addressed as categorical_warp does
                 if (RAW) {
                     if (P.a.q) myq = P.a.q[((size_t)tp * Bt + b) * NC + tid];
@@ -585,7 +588,7 @@ __device__ void res_tail_role(const ResParams &P, int j, float *smem) {
                 __syncthreads();
                 if (prof_on) { const long long n = clock64(); pacc[1] += n - pt; pt = n; }
                 if (warp == 0) {
-                    xv = mol_sample_smem2(lg, nmix, myu1, u2, lane, &pick);
+                    xv = mol_sample_smem2(lg, nmix, g1, lg2, lane, &pick);
                     if (tp >= P.a.fold_len[f]) xv = 0.f;
                     else if (lane == 0) {
                         P.a.samples[(size_t)f * S + tp] = xv;
@@ -910,7 +913,7 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
                 const float ir = fmaf(w0r[0], xpv, pre2(pre_i1, (0 * RU + gu) * RB + gf));
                 const float iz = fmaf(w0r[1], xpv, pre2(pre_i1, (1 * RU + gu) * RB + gf));
                 const float in_ = fmaf(w0r[2], xpv, pre2(pre_i1, (2 * RU + gu) * RB + gf));
-                const float hn = gru_update(ir, iz, in_, pre_h1[(0 * RU + gu) * RB + gf], pre_h1[(1 * RU + gu) * RB + gf],
+                const float hn = gru_update_fast(ir, iz, in_, pre_h1[(0 * RU + gu) * RB + gf], pre_h1[(1 * RU + gu) * RB + gf],
                                             pre_h1[(2 * RU + gu) * RB + gf], hst1[gu * RB + gf]);
                 hw = tag_word(hn, tag);
                 hst1[gu * RB + gf] = __uint_as_float(hw);          // the state IS the tagged word, everywhere
@@ -950,7 +953,7 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
                     const float ir = gru_out(red, 0 * RU + gu, gf) + fmaf(w0r[0], xpv, pre2(pre_i2, (0 * RU + gu) * RB + gf));
                     const float iz = gru_out(red, 1 * RU + gu, gf) + fmaf(w0r[1], xpv, pre2(pre_i2, (1 * RU + gu) * RB + gf));
                     const float in_ = gru_out(red, 2 * RU + gu, gf) + fmaf(w0r[2], xpv, pre2(pre_i2, (2 * RU + gu) * RB + gf));
-                    const float hn = gru_update(ir, iz, in_, pre_h2[(0 * RU + gu) * RB + gf], pre_h2[(1 * RU + gu) * RB + gf],
+                    const float hn = gru_update_fast(ir, iz, in_, pre_h2[(0 * RU + gu) * RB + gf], pre_h2[(1 * RU + gu) * RB + gf],
                                                 pre_h2[(2 * RU + gu) * RB + gf], hst2[gu * RB + gf]);
                     hst2[gu * RB + gf] = hn;                                   // own state, never exchanged: exact
                     xw = tag_word(bufH1[gf * RH + u0 + gu] + hn, tag);         // h1 + h2 (residuals :212,216)
