@@ -481,7 +481,7 @@ __device__ __forceinline__ int categorical_block(float l, float q, float *scr, i
     return bi;
 }
 
-template <bool RAW>
+template <bool RAW, bool PROF>
 __device__ void res_tail_role(const ResParams &P, int j, float *smem) {
     const Dims &d = P.d;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -506,8 +506,8 @@ __device__ void res_tail_role(const ResParams &P, int j, float *smem) {
     const int nmix = NC / 3;
     const int64_t Bt = P.a.Btot, b0 = P.a.b0;
     Dead dd{false, P.abort_flag, P.abort_flag, nullptr, nullptr};
-    const bool prof_on = P.prof != nullptr && j == 0 && tid == 0;
-    const bool ev_t = P.prof != nullptr && tid == 0 && (j % 5 == 0 || j == 19);      // WRNN_EVPROF: x_prev publish time of tails 0, 5, 10, 15, 19
+    const bool prof_on = PROF && P.prof != nullptr && j == 0 && tid == 0;
+    const bool ev_t = PROF && P.prof != nullptr && tid == 0 && (j % 5 == 0 || j == 19);      // WRNN_EVPROF: x_prev publish time of tails 0, 5, 10, 15, 19
     long long evj = 0;
     (void)ev_t; (void)evj;
     long long pacc[4] = {0, 0, 0, 0}, pt = clock64(), ev2 = 0, ev3 = 0;
@@ -638,6 +638,9 @@ __device__ __forceinline__ long long clock_fenced() {       // the "memory" clob
     asm volatile("mov.u64 %0, %%clock64;" : "=l"(c)::"memory");
     return c;
 }
+// The phase profiler is a template parameter of the kernel: with the hooks compiled in but switched off (a predicate and a
+// __syncwarp per mark, ~25 marks per step) the step took 12.44 us instead of 11.82 (measured, config 2).
+#define WRNN_PROF_REJOIN() do { if (PROF) __syncwarp(); } while (0)
 #define RPROF(slot)                                                   \
     do {                                                              \
         if (prof_on) {                                                \
@@ -649,7 +652,7 @@ __device__ __forceinline__ long long clock_fenced() {       // the "memory" clob
             if (d__ < pacc[16 + slot] || pacc[16 + slot] == 0) pacc[16 + slot] = d__; \
             pt = n__;                                                 \
         }                                                             \
-        __syncwarp();   /* the timing lane must rejoin its warp: a warp that stays split runs every shuffle on the slow path */ \
+        WRNN_PROF_REJOIN();   /* the timing lane must rejoin its warp: a warp that stays split runs every shuffle on the slow path */ \
     } while (0)
 
 // CTA-wide gather of a tagged vector (n4 float4) into dense smem: every thread requests all its slots
@@ -661,7 +664,7 @@ __device__ __forceinline__ long long clock_fenced() {       // the "memory" clob
             gacc[k] += n__ - gpt;                                     \
             gpt = n__;                                                \
         }                                                             \
-        __syncwarp();                                                 \
+        WRNN_PROF_REJOIN();                                           \
     } while (0)
 
 // CTA-wide gather of a 40 KB vector of tagged words through the TMA unit: one thread issues ONE bulk copy of the
@@ -722,7 +725,7 @@ __device__ __forceinline__ void gather_wait(const float *src, int n4, float *dst
 // T4 3.7 k, T5 2.5 k, T6 3.3 k, T7 2.6 k = 27 k = 13.7 us.  The products are bound by the LSU pipe (LDS + SHFL
 // wavefronts: 36 % of peak over the whole step, two products side by side take twice as long as one), the
 // exchanges by L2 round trips; see DESIGN.md section 4.
-template <bool RAW, bool SP>
+template <bool RAW, bool SP, bool PROF>
 __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
     const Dims &d = P.d;
     const int tid = threadIdx.x, gid = tid >> 7, tg = tid & 127, wq = tg >> 5, lane = tid & 31;
@@ -750,12 +753,12 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
     if (sp) for (int i = tid; i < 9 * SPG; i += RTH) smem[SM_SP + i] = __ldg(img + IMG_SP + i);
     __syncthreads();
     Dead dd{false, P.abort_flag, P.abort_flag, nullptr,
-            (P.prof != nullptr && cta == 0) ? reinterpret_cast<unsigned int *>(smem + SM_PROF + 64) + gid * 4 : nullptr};
+            (PROF && P.prof != nullptr && cta == 0) ? reinterpret_cast<unsigned int *>(smem + SM_PROF + 64) + gid * 4 : nullptr};
     const float *w0 = smem + SM_W0B, *bias = w0 + 32;
     const float *b_i1 = bias, *b_i2 = bias + 12, *b_f1 = bias + 24, *b_f2 = bias + 28, *b_hh1 = bias + 32, *b_hh2 = bias + 44;
-    const bool prof_on = P.prof != nullptr && tid == 0;          // every row CTA times its own phases
+    const bool prof_on = PROF && P.prof != nullptr && tid == 0;          // every row CTA times its own phases
     long long *pacc = reinterpret_cast<long long *>(smem + SM_PROF), pt = 0;
-    const bool gprof_on = P.prof != nullptr && cta == 5 && tg == 0;      // group leaders of one CTA: finer marks
+    const bool gprof_on = PROF && P.prof != nullptr && cta == 5 && tg == 0;      // group leaders of one CTA: finer marks
     long long *gacc = reinterpret_cast<long long *>(smem + SM_GP) + gid * 16, gpt = 0;
 
     // ---- per-group register state: the weights live here for the whole call
@@ -812,7 +815,7 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
     pt = clock64();
     gpt = pt;
 
-    const bool ev_d = P.prof != nullptr && cta == 5 && tid == 384, ev_0 = P.prof != nullptr && cta == 5 && tid == 0;
+    const bool ev_d = PROF && P.prof != nullptr && cta == 5 && tid == 384, ev_0 = PROF && P.prof != nullptr && cta == 5 && tid == 0;
     long long ev0 = 0, ev1 = 0, ev4 = 0;
     (void)ev_d; (void)ev_0; (void)ev0; (void)ev1; (void)ev4;
     const int d1 = P.d1 ? P.d1 : GATHER_DELAY_H1, d2 = P.d2 ? P.d2 : GATHER_DELAY_X2, d3 = P.d3 ? P.d3 : GATHER_DELAY_Y1;
@@ -1036,16 +1039,21 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
         for (int i = 0; i < 16; i++) P.prof[64 + RNR * 8 + RNR * 128 + gid * 16 + i] = gacc[i];
     if (prof_on && cta == 5)
         for (int i = 0; i < 16; i++) P.prof[40 + i] = pacc[8 + i];
-    if (P.prof != nullptr && cta == 0 && tg == 0)
+    if (PROF && P.prof != nullptr && cta == 0 && tg == 0)
         for (int i = 0; i < 3; i++) P.prof[20 + gid * 3 + i] = dd.cnt[i];
 }
 
-template <bool RAW, bool SP>
+template <bool RAW, bool SP, bool PROF>
 __global__ void __launch_bounds__(RTH, 1) res_loop_kernel(const ResParams P) {
     extern __shared__ __align__(16) float smem[];
     const int cta = blockIdx.x;
-    if (cta < RNR) res_row_role<RAW, SP>(P, cta, smem);
-    else res_tail_role<RAW>(P, cta - RNR, smem);
+    if (cta < RNR) res_row_role<RAW, SP, PROF>(P, cta, smem);
+    else res_tail_role<RAW, PROF>(P, cta - RNR, smem);
+}
+template <bool PROF>
+static const void *res_kernel_ptr(bool raw, bool sparse) {
+    return sparse ? (raw ? (const void *)res_loop_kernel<true, true, PROF> : (const void *)res_loop_kernel<false, true, PROF>)
+                  : (raw ? (const void *)res_loop_kernel<true, false, PROF> : (const void *)res_loop_kernel<false, false, PROF>);
 }
 
 // ============================================================================ host: plan + launch
@@ -1188,10 +1196,10 @@ int res_plan(wrnn_handle *h) {
     WRNN_CUDA(h, cudaMemcpy(p.img, img.data(), img.size() * sizeof(float), cudaMemcpyHostToDevice));
     WRNN_CUDA(h, cudaMalloc((void **)&p.tail_img, timg.size() * sizeof(float)));
     WRNN_CUDA(h, cudaMemcpy(p.tail_img, timg.data(), timg.size() * sizeof(float), cudaMemcpyHostToDevice));
-    WRNN_CUDA(h, cudaFuncSetAttribute(res_loop_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem_bytes));
-    WRNN_CUDA(h, cudaFuncSetAttribute(res_loop_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem_bytes));
-    WRNN_CUDA(h, cudaFuncSetAttribute(res_loop_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem_bytes));
-    WRNN_CUDA(h, cudaFuncSetAttribute(res_loop_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem_bytes));
+    for (int k = 0; k < 8; k++) {
+        const void *f = (k & 4) ? res_kernel_ptr<true>(k & 1, k & 2) : res_kernel_ptr<false>(k & 1, k & 2);
+        WRNN_CUDA(h, cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem_bytes));
+    }
     p.ok = true;
     return 0;
 }
@@ -1237,8 +1245,7 @@ int res_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
         P.prof = (long long *)h->ws_prof.p;
     }
     const bool rawm = d.mode != WRNN_MODE_MOL;
-    const void *kern = P.sparse ? (rawm ? (const void *)res_loop_kernel<true, true> : (const void *)res_loop_kernel<false, true>)
-                                : (rawm ? (const void *)res_loop_kernel<true, false> : (const void *)res_loop_kernel<false, false>);
+    const void *kern = prof_env ? res_kernel_ptr<true>(rawm, P.sparse != 0) : res_kernel_ptr<false>(rawm, P.sparse != 0);
     void *args[] = {(void *)&P};
     WRNN_CUDA(h, cudaLaunchCooperativeKernel(kern, dim3(p.G), dim3(RTH), args, p.smem_bytes, st));
     h->launches++;
