@@ -30,8 +30,8 @@ sys.path.insert(0, ROOT)
 T_FRAMES, TARGET, OVERLAP = 801, 11000, 550
 WEIGHT_BYTES_PER_STEP = 15_331_448        # 3 825 152 matrix + 7 710 bias fp32 elements
 # dram__bytes_read.sum + dram__bytes_write.sum of one res_loop_kernel launch (12100 steps), ncu --set full
-NCU_DRAM_BYTES_PER_LAUNCH = 223_736_832 + 6_335_232
-NCU_SOURCE = 'profiles/r01f_resident_loop_ncu.txt'
+NCU_DRAM_BYTES_PER_LAUNCH = 223_707_136 + 6_333_440
+NCU_SOURCE = 'profiles/r01h_resident_loop_ncu.txt'
 SAMPLE_RATE = 22050
 METRIC = 'generated audio samples/sec'
 CPU_SAMPLE_STEPS = 2000                   # --impl reference: loop steps (x20 folds) per timed step (~2.5 s of CPU work each)
