@@ -713,7 +713,7 @@ __device__ __forceinline__ void gather_wait(const float *src, int n4, float *dst
 //   P   shadow   GB: W_hh1 . h1(t-1)   GC: W_hh2 . h2(t-1)   warp 0: TMA prefetch of the conditioning rows of t+1
 //                -- nothing here needs sample t-1, so for t > 0 it runs while the tail CTAs do fc3 + sampling     S5
 //   T0  all      wait x_prev(t)                                                                                   S0
-//   T1  GB       rnn1 gates -> publish h1(t)                                                                      S0b
+//   T1  GB       rnn1 gates -> publish h1(t)                                               (no barrier: T2 starts beside it)
 //   T2  all      exchange h1(t): one TMA bulk copy, issued GATHER_DELAY_H1 clocks after the publish; while it is
 //                in flight the CTA forms the conditioning terms i1, f1, f2 of step t+1 (cond_all)                 S1
 //   T3  GA       W_ih2a . h1, rnn2 gates -> publish x2'(t) = h1 + h2                                              S1b
@@ -721,10 +721,12 @@ __device__ __forceinline__ void gather_wait(const float *src, int n4, float *dst
 //   T5  GD       fc1 -> publish y1(t)                                                                             S3
 //   T6  all      exchange y1(t); meanwhile GC turns x2' into h2 = x2' - h1 in place (h2 is never exchanged)       S4
 //   T7  GD       fc2 -> publish y2(t) (the tail CTAs pick it up)                                                  S4b
-// Measured on B200 (clocks per step, 20 folds): P 5.4 k (two concurrent products), T0 0.9 k, T1+T2 4.7 k, T3 3.9 k,
-// T4 3.7 k, T5 2.5 k, T6 3.3 k, T7 2.6 k = 27 k = 13.7 us.  The products are bound by the LSU pipe (LDS + SHFL
-// wavefronts: 36 % of peak over the whole step, two products side by side take twice as long as one), the
-// exchanges by L2 round trips; see DESIGN.md section 4.
+// Measured on B200 with the PROF instantiation (clocks per step, 20 folds, end of round 1): P 5.4 k (two concurrent
+// products; the tail chain behind it is 4.6 k), T0 0.3 k, T1+T2 4.0 k, T3 3.8 k, T4 3.6 k, T5 1.9 k, T6 3.1 k, T7 2.1 k;
+// the product kernel (PROF = false) runs the step in 22.5 k = 11.4 us (first version of this schedule: 27 k).  The
+// products are bound by issue slots and LSU wavefronts (LDS + SHFL: 40 % of peak over the whole step, two products
+// side by side take as long as one after the other), the exchanges by L2 round trips; see DESIGN.md section 4 and
+// profiles/r01e_schedule_experiments.txt.
 template <bool RAW, bool SP, bool PROF>
 __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
     const Dims &d = P.d;
