@@ -139,9 +139,13 @@ int wrnn_forward_logits(wrnn_handle *h, const float *x, const float *mels, int32
  * "fma-resident" (register-resident weights, TMA exchanges; csrc/loop_res.cu) takes rnn_dims = fc_dims = 512,
  * aux 32, feat_dims a multiple of 8 up to 96, MoL or RAW with 512 classes, on a GPU with >= 129 SMs. */
 const char *wrnn_loop_kernel_name(wrnn_handle *h, int64_t folds);
-/* Force a loop kernel: 0 = auto (fastest kernel that supports the dims), 1 = fma (grid-barrier kernel, any dims and
- * fold count, reference order of operations), 2 = fma-pipelined (tagged exchange, shared-memory weights). */
+/* Force a loop kernel: 0 = auto (fastest kernel that supports the dims and the fold count), 1 = fma (grid-barrier
+ * kernel, any dims and fold count, reference order of operations), 2 = fma-pipelined (tagged exchange, shared-memory
+ * weights), 4 = "tcgen05-bf16x3" (csrc/loop_mma.cu: the contractions of fatchord_version.py:208-221 on the tensor
+ * cores with bf16 hi/lo split operands and fp32 TMEM accumulators; default dims, MoL; auto from 48 folds up). */
 int wrnn_set_loop_kernel(wrnn_handle *h, int32_t which);
+/* Fold-tile width N of the tensor-core kernel's (128 rows x N folds) jobs: 0 = auto, else a multiple of 16 <= 128. */
+int wrnn_set_mma_fold_tile(wrnn_handle *h, int32_t nt);
 
 /* ------------------------------------------------------------------ deepmind variant */
 typedef struct wrnn_dm_handle wrnn_dm_handle;

@@ -1,6 +1,8 @@
 """Import the real reference (build container only) to pin the oracle.  TEST INFRASTRUCTURE.
 
-`/root/reference` is read-only and exists only in the build container; nothing on the GPU
+`/root/reference` is read-only and exists only in the build container; on the GPU box the
+un-modified copies staged by `oracle/stage_ref.py` into git-ignored `oracle/_ref/reference/` are
+used instead (timed CPU baseline and call-compatibility test only).  Nothing on the product
 path may call this.  The shims are the ones listed in SURVEY.md F4/F6 and touch no arithmetic:
   * stub `matplotlib` / `librosa` modules (`utils/display.py:1-3`, `utils/dsp.py:3`);
   * `np.cumproduct = np.cumprod` (`models/fatchord_version.py:68`; removed in NumPy 2);
@@ -12,7 +14,18 @@ import os
 import sys
 import types
 
-REF_ROOT = os.environ.get('WAVERNN_REFERENCE', '/root/reference')
+_STAGED = os.path.join(os.path.dirname(os.path.abspath(__file__)), '_ref', 'reference')
+
+
+def _find_root():
+    # the build container has the tree itself; the GPU box has the copies `oracle/stage_ref.py` made at build time
+    for cand in (os.environ.get('WAVERNN_REFERENCE'), '/root/reference', _STAGED):
+        if cand and os.path.isfile(os.path.join(cand, 'models', 'fatchord_version.py')):
+            return cand
+    return '/root/reference'
+
+
+REF_ROOT = _find_root()
 
 
 def available() -> bool:

@@ -62,6 +62,7 @@ _SIGS = {
     'wrnn_forward_logits': (C.c_int, [_P, _P, _P, C.c_int32, C.c_int64, _P]),
     'wrnn_loop_kernel_name': (C.c_char_p, [_P, C.c_int64]),
     'wrnn_set_loop_kernel': (C.c_int, [_P, C.c_int32]),
+    'wrnn_set_mma_fold_tile': (C.c_int, [_P, C.c_int32]),
     'wrnn_dm_create': (C.c_int, [C.c_int32, C.c_int32, C.c_int, C.POINTER(_P)]),
     'wrnn_dm_destroy': (None, [_P]),
     'wrnn_dm_last_error': (C.c_char_p, [_P]),
@@ -249,7 +250,11 @@ class Vocoder:
         return lib().wrnn_loop_kernel_name(self._h, int(folds)).decode()
 
     def set_loop_kernel(self, which):
+        """0 auto, 1 fma, 2 fma-pipelined, 4 tcgen05-bf16x3 (tensor cores; auto from 48 folds up)."""
         self._ck(lib().wrnn_set_loop_kernel(self._h, int(which)))
+
+    def set_mma_fold_tile(self, nt):
+        self._ck(lib().wrnn_set_mma_fold_tile(self._h, int(nt)))
 
     def prune_16x1(self, keep_fraction, want_masked=False):
         d = self.dims

@@ -61,8 +61,10 @@ static int64_t num_folds(int64_t total_len, int64_t target, int64_t overlap) {
     return n;
 }
 
-int loop_kernel_choice(const wrnn_handle *h) {
+int loop_kernel_choice(const wrnn_handle *h, int64_t folds) {
     const int f = h->force_kernel;
+    if (f == 4 && mma_supported(h)) return 4;
+    if (f == 0 && mma_supported(h) && folds >= mma_min_folds()) return 4;
     if (f == 1) return 1;
     if (f == 2) return pipe_supported(h) ? 2 : 1;
     if (res_supported(h)) return 3;
@@ -73,11 +75,12 @@ int loop_kernel_choice(const wrnn_handle *h) {
 int ensure_packed_public(wrnn_handle *h) {
     if (h->packed) return 0;
     if (h->w.empty()) return fail(h, WRNN_ERR_STATE, "weights not loaded: call wrnn_load_weights first");
-    WRNN_CUDA(h, cudaSetDevice(h->device));
+    WRNN_DEVICE(h);
     WRNN_TRY(pack_cond(h));
     WRNN_TRY(fma_plan(h));
     WRNN_TRY(pipe_plan(h));
     WRNN_TRY(res_plan(h));
+    WRNN_TRY(mma_plan(h));
     h->packed = true;
     return 0;
 }
@@ -119,7 +122,8 @@ int wrnn_create(const wrnn_config *cfg, int device, wrnn_handle **out) {
         return fail(nullptr, WRNN_ERR_ARG, "upsample_factors must multiply to hop_length");
     }
     cudaDeviceProp prop;
-    if (cudaSetDevice(device) != cudaSuccess || cudaGetDeviceProperties(&prop, device) != cudaSuccess) {
+    DeviceGuard guard(device);
+    if (guard.err != cudaSuccess || cudaGetDeviceProperties(&prop, device) != cudaSuccess) {
         delete h;
         return fail(nullptr, WRNN_ERR_CUDA, "cannot open device %d", device);
     }
@@ -132,14 +136,15 @@ int wrnn_create(const wrnn_config *cfg, int device, wrnn_handle **out) {
 
 void wrnn_destroy(wrnn_handle *h) {
     if (!h) return;
-    cudaSetDevice(h->device);
+    DeviceGuard guard(h->device);
     Workspace *all[] = {&h->ws_mel, &h->ws_up, &h->ws_res, &h->ws_cond, &h->ws_samples, &h->ws_picks, &h->ws_out,
                         &h->ws_noise, &h->ws_meta, &h->ws_tables, &h->ws_sync, &h->ws_act, &h->ws_tmp0, &h->ws_tmp1,
                         &h->ws_teacher, &h->ws_logits, &h->ws_prof};
     for (Workspace *w : all)
         if (w->p) cudaFree(w->p);
     float *ptrs[] = {h->cp.conv_in_t, h->cp.bn_scale, h->cp.bn_shift, h->cp.res_t, h->cp.conv_out_t, h->cp.conv_out_b,
-                     h->fma.image, h->pipe.row_image, h->pipe.tail_image, h->res.img, h->res.tail_img};
+                     h->fma.image, h->pipe.row_image, h->pipe.tail_image, h->res.img, h->res.tail_img,
+                     (float *)h->mma.Aimg, h->mma.bias, h->mma.wf3};
     for (float *p : ptrs)
         if (p) cudaFree(p);
     for (int i = 0; i < 8; i++)
@@ -214,16 +219,23 @@ int64_t wrnn_num_folds(int64_t total_len, int64_t target, int64_t overlap) {
 }
 
 const char *wrnn_loop_kernel_name(wrnn_handle *h, int64_t folds) {
-    (void)folds;
     if (!h) return "none";
     if (!h->packed && !h->w.empty()) ensure_packed_public(h);
-    const int k = loop_kernel_choice(h);
+    const int k = loop_kernel_choice(h, folds);
+    if (k == 4) return "tcgen05-bf16x3";
     return k == 3 ? (h->res.sparse ? "fma-resident-sparse16x1" : "fma-resident") : (k == 2 ? "fma-pipelined" : "fma");
 }
 
 int wrnn_set_loop_kernel(wrnn_handle *h, int32_t which) {
     if (!h) return WRNN_ERR_ARG;
     h->force_kernel = which;
+    return 0;
+}
+
+int wrnn_set_mma_fold_tile(wrnn_handle *h, int32_t nt) {
+    if (!h) return WRNN_ERR_ARG;
+    if (nt != 0 && (nt < 16 || nt > 128 || nt % 16)) return fail(h, WRNN_ERR_ARG, "fold tile must be 0 (auto) or a multiple of 16 in [16, 128]");
+    h->mma_force_nt = nt;
     return 0;
 }
 

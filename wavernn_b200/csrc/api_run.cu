@@ -45,7 +45,7 @@ int do_stage(wrnn_handle *h, const float *const *mels, const int32_t *T, int32_t
     const Dims &d = h->d;
     h->staged = false;
     if (!mels || !T || n_utt < 1) return fail(h, WRNN_ERR_ARG, "need at least one utterance");
-    WRNN_CUDA(h, cudaSetDevice(h->device));
+    WRNN_DEVICE(h);
     WRNN_TRY(ensure_packed_public(h));
     if (batched && (target < 1 || overlap < 0)) return fail(h, WRNN_ERR_ARG, "target must be >= 1 and overlap >= 0");
     h->batched = batched ? 1 : 0;
@@ -169,7 +169,7 @@ int do_stage(wrnn_handle *h, const float *const *mels, const int32_t *T, int32_t
 int do_run(wrnn_handle *h, uint64_t seed, cudaStream_t st, const StageOpts &o) {
     if (!h->staged) return fail(h, WRNN_ERR_STATE, "nothing staged: call wrnn_stage first");
     const Dims &d = h->d;
-    WRNN_CUDA(h, cudaSetDevice(h->device));
+    WRNN_DEVICE(h);
     h->launches = 0;
     const int n_utt = (int)h->utts.size();
     const MetaLayout ml = meta_layout(h->B, n_utt);
@@ -220,10 +220,16 @@ int do_run(wrnn_handle *h, uint64_t seed, cudaStream_t st, const StageOpts &o) {
     a.seed = seed;
     a.Btot = h->B;
     a.b0 = 0;
+    // barrier counter (bytes 0..63) is cleared per run; the abort flag (byte 64) is STICKY: it stays set across runs
+    // until a fetch has reported it (check_abort), so a benchmark that runs N times and fetches once cannot count an
+    // aborted (early-exited) iteration as throughput
+    const bool fresh_sync = h->ws_sync.p == nullptr;
     WRNN_TRY(ws_reserve(h, h->ws_sync, 128));
-    WRNN_CUDA(h, cudaMemsetAsync(h->ws_sync.p, 0, 128, st));      // barrier counter + abort flag
-    const int kernel = loop_kernel_choice(h);
-    if (kernel != 1) {
+    WRNN_CUDA(h, cudaMemsetAsync(h->ws_sync.p, 0, fresh_sync ? 128 : 64, st));
+    const int kernel = loop_kernel_choice(h, h->B);
+    if (kernel == 4) {
+        WRNN_TRY(mma_run(h, a, st));       // all folds of the call in one launch
+    } else if (kernel != 1) {
         // these kernels take fold groups of <= 20 (folds are independent: any grouping is exact)
         const int64_t cap = kernel == 3 ? res_max_folds() : pipe_max_folds(), ng = (h->B + cap - 1) / cap, per = (h->B + ng - 1) / ng;
         const size_t CW = (size_t)(d.F + d.R);
@@ -263,7 +269,10 @@ int check_abort(wrnn_handle *h, cudaStream_t st) {
         WRNN_CUDA(h, cudaMemcpyAsync(&flag, (char *)h->ws_sync.p + 64, sizeof(int), cudaMemcpyDeviceToHost, st));
         WRNN_CUDA(h, cudaStreamSynchronize(st));
     }
-    if (flag) return fail(h, WRNN_ERR_CUDA, "per-sample loop kernel aborted: exchange watchdog fired (code %d)", flag);
+    if (flag) {
+        cudaMemsetAsync((char *)h->ws_sync.p + 64, 0, 4, st);      // reported once, then re-armed
+        return fail(h, WRNN_ERR_CUDA, "per-sample loop kernel aborted: exchange watchdog fired (code %d)", flag);
+    }
     return 0;
 }
 
@@ -287,6 +296,7 @@ int wrnn_run_staged(wrnn_handle *h, uint64_t seed, void *cuda_stream) {
 int wrnn_fetch(wrnn_handle *h, double *const *out, int64_t *out_len, void *cuda_stream) {
     if (!h || !out) return fail(h, WRNN_ERR_ARG, "null argument");
     if (!h->staged) return fail(h, WRNN_ERR_STATE, "nothing staged");
+    WRNN_DEVICE(h);
     cudaStream_t st = (cudaStream_t)cuda_stream;
     const size_t bytes = (size_t)h->total_out * sizeof(double);
     if (h->h_pinned_out_bytes < bytes) {
@@ -318,6 +328,7 @@ int wrnn_generate(wrnn_handle *h, const float *const *mels, const int32_t *T, in
 int wrnn_last_timing(wrnn_handle *h, float *ms_cond, float *ms_loop, float *ms_tail, int64_t *steps,
                      int64_t *folds, int64_t *kernel_launches) {
     if (!h) return WRNN_ERR_ARG;
+    WRNN_DEVICE(h);
     float a = 0, b = 0, c = 0;
     WRNN_CUDA(h, cudaEventSynchronize(h->ev[3]));
     WRNN_CUDA(h, cudaEventElapsedTime(&a, h->ev[0], h->ev[1]));
@@ -335,6 +346,7 @@ int wrnn_last_timing(wrnn_handle *h, float *ms_cond, float *ms_loop, float *ms_t
 int wrnn_fetch_samples(wrnn_handle *h, float *samples, void *cuda_stream) {
     if (!h || !samples) return fail(h, WRNN_ERR_ARG, "null argument");
     if (!h->staged) return fail(h, WRNN_ERR_STATE, "nothing staged");
+    WRNN_DEVICE(h);
     cudaStream_t st = (cudaStream_t)cuda_stream;
     WRNN_CUDA(h, cudaMemcpyAsync(samples, h->ws_samples.p, (size_t)h->B * h->S * sizeof(float), cudaMemcpyDeviceToHost, st));
     WRNN_CUDA(h, cudaStreamSynchronize(st));
@@ -344,6 +356,7 @@ int wrnn_fetch_samples(wrnn_handle *h, float *samples, void *cuda_stream) {
 int wrnn_forward_logits(wrnn_handle *h, const float *x, const float *mels, int32_t n_seq, int64_t S, float *logits) {
     if (!h || !x || !mels || !logits || n_seq < 1) return fail(h, WRNN_ERR_ARG, "null argument");
     const Dims &d = h->d;
+    WRNN_DEVICE(h);
     if (S < 1 || S % d.hop) return fail(h, WRNN_ERR_ARG, "S must be a positive multiple of hop_length");
     const int Tp = (int)(S / d.hop) + 2 * d.pad;
     std::vector<const float *> mp(n_seq);
@@ -365,7 +378,7 @@ int wrnn_forward_logits(wrnn_handle *h, const float *x, const float *mels, int32
 int wrnn_upsample(wrnn_handle *h, const float *mel, int32_t T, float *mels_out, float *aux_out) {
     if (!h || !mel || !mels_out || !aux_out || T < 1) return fail(h, WRNN_ERR_ARG, "bad argument");
     const Dims &d = h->d;
-    WRNN_CUDA(h, cudaSetDevice(h->device));
+    WRNN_DEVICE(h);
     WRNN_TRY(ensure_packed_public(h));
     const int Tp = T + 2 * d.pad;
     const int64_t L = (int64_t)T * d.hop;
@@ -389,7 +402,7 @@ int wrnn_upsample(wrnn_handle *h, const float *mel, int32_t T, float *mels_out, 
 int wrnn_fold(wrnn_handle *h, const float *x, int64_t L, int32_t F, int64_t target, int64_t overlap, float *out) {
     if (!h || !x || !out || L < 1 || F < 1 || target < 1 || overlap < 0 || L <= overlap)
         return fail(h, WRNN_ERR_ARG, "bad argument");
-    WRNN_CUDA(h, cudaSetDevice(h->device));
+    WRNN_DEVICE(h);
     const int64_t folds = wrnn_num_folds(L, target, overlap), len = target + 2 * overlap;
     WRNN_TRY(ws_reserve(h, h->ws_tmp0, (size_t)L * F * sizeof(float)));
     WRNN_TRY(ws_reserve(h, h->ws_tmp1, (size_t)folds * len * F * sizeof(float)));
@@ -402,7 +415,7 @@ int wrnn_fold(wrnn_handle *h, const float *x, int64_t L, int32_t F, int64_t targ
 
 int wrnn_unfold(wrnn_handle *h, const double *y, int64_t folds, int64_t target, int64_t overlap, double *out) {
     if (!h || !y || !out || folds < 1 || target < 0 || overlap < 0) return fail(h, WRNN_ERR_ARG, "bad argument");
-    WRNN_CUDA(h, cudaSetDevice(h->device));
+    WRNN_DEVICE(h);
     const int64_t len = target + 2 * overlap, total = folds * (target + overlap) + overlap;
     const size_t ov = (size_t)std::max<int64_t>(overlap, 1);
     std::vector<double> tab(2 * ov, 0.0);
@@ -422,7 +435,7 @@ int wrnn_unfold(wrnn_handle *h, const double *y, int64_t folds, int64_t target, 
 
 int wrnn_decode_mu_law(wrnn_handle *h, const float *y, int64_t n, int32_t mu, double *out) {
     if (!h || !y || !out || n < 1 || mu < 2) return fail(h, WRNN_ERR_ARG, "bad argument");
-    WRNN_CUDA(h, cudaSetDevice(h->device));
+    WRNN_DEVICE(h);
     std::vector<double> lut(mu);
     if ((int)h->lut_override.size() == mu) lut = h->lut_override;
     else wrnn_mulaw_lut(mu, lut.data());

@@ -341,7 +341,8 @@ int wrnn_dm_create(int32_t hidden_size, int32_t quantisation, int device, wrnn_d
     if (e != cudaSuccess || ndev == 0) return dm_fail(nullptr, WRNN_ERR_CUDA, "no CUDA device: this library has no CPU fallback");
     if (device < 0 || device >= ndev) return dm_fail(nullptr, WRNN_ERR_ARG, "device out of range");
     cudaDeviceProp prop;
-    if (cudaSetDevice(device) != cudaSuccess || cudaGetDeviceProperties(&prop, device) != cudaSuccess)
+    wrnn::DeviceGuard guard(device);
+    if (guard.err != cudaSuccess || cudaGetDeviceProperties(&prop, device) != cudaSuccess)
         return dm_fail(nullptr, WRNN_ERR_CUDA, "cannot open device");
     wrnn_dm_handle *h = new wrnn_dm_handle();
     h->hidden = hidden_size; h->quant = quantisation; h->device = device;
@@ -355,7 +356,7 @@ int wrnn_dm_create(int32_t hidden_size, int32_t quantisation, int device, wrnn_d
 
 void wrnn_dm_destroy(wrnn_dm_handle *h) {
     if (!h) return;
-    cudaSetDevice(h->device);
+    wrnn::DeviceGuard guard(h->device);
     if (h->image) cudaFree(h->image);
     if (h->ws) cudaFree(h->ws);
     for (int i = 0; i < 2; i++)
@@ -390,7 +391,8 @@ int wrnn_dm_generate(wrnn_dm_handle *h, int64_t seq_len, int32_t n_seq, const fl
     if (!h || !output || !coarse || !fine || seq_len < 1 || n_seq < 1) return dm_fail(h, WRNN_ERR_ARG, "bad argument");
     if ((q_coarse == nullptr) != (q_fine == nullptr)) return dm_fail(h, WRNN_ERR_ARG, "give both noise tensors or none");
     cudaStream_t st = (cudaStream_t)cuda_stream;
-    DM_CUDA(h, cudaSetDevice(h->device));
+    wrnn::DeviceGuard guard(h->device);
+    DM_CUDA(h, guard.err);
     if (!h->packed) {
         if (h->w.empty()) return dm_fail(h, WRNN_ERR_STATE, "weights not loaded: call wrnn_dm_load_weights first");
         const int rc = dm_pack(h);

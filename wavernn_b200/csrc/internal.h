@@ -64,6 +64,16 @@ struct ResPlan {
     size_t smem_bytes = 0;
 };
 
+// ---- per-sample loop, tensor-core kernel for large fold batches (loop_mma.cu) ------------------
+struct MmaPlan {
+    bool ok = false;
+    uint8_t *Aimg = nullptr;       // device: bf16 hi/lo weight images of the four MMA phases
+    int64_t offA[4] = {0, 0, 0, 0};
+    float *bias = nullptr;         // device: composed biases
+    float *wf3 = nullptr;          // device: fc3 rows (fp32) + bias
+    size_t img_bytes = 0, smem_bytes = 0;
+};
+
 struct LoopArgs {
     const float *cond;         // [B][S][F+R]
     int64_t B, S;
@@ -97,6 +107,8 @@ struct wrnn_handle {
     wrnn::FmaPlan fma;
     wrnn::PipePlan pipe;
     wrnn::ResPlan res;
+    wrnn::MmaPlan mma;
+    int mma_force_nt = 0;              // debug / tests: fold-tile width of the tensor-core kernel (0 = auto)
     int force_kernel = 0;
     std::vector<double> lut_override;   // host-supplied mu-law table (wrnn_set_mulaw_lut)
     bool sparse = false;
@@ -135,6 +147,27 @@ int fail(wrnn_handle *h, int code, const char *fmt, ...);
         int r__ = (expr);                                                                     \
         if (r__ != 0) return r__;                                                             \
     } while (0)
+
+// The current CUDA device is thread-global state shared with the host process (PyTorch): every entry point selects the
+// handle's device for the duration of the call and puts the caller's device back on every exit path.
+struct DeviceGuard {
+    int prev = -1;
+    cudaError_t err = cudaSuccess;
+    explicit DeviceGuard(int dev) {
+        if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+        if (prev != dev) err = cudaSetDevice(dev);
+        else prev = -1;                 // nothing to restore
+    }
+    ~DeviceGuard() {
+        if (prev >= 0) cudaSetDevice(prev);
+    }
+    DeviceGuard(const DeviceGuard &) = delete;
+    DeviceGuard &operator=(const DeviceGuard &) = delete;
+};
+#define WRNN_DEVICE(h)                                                                          \
+    wrnn::DeviceGuard dev_guard__((h)->device);                                                 \
+    if (dev_guard__.err != cudaSuccess)                                                         \
+        return wrnn::fail((h), WRNN_ERR_CUDA, "cudaSetDevice(%d) failed: %s", (h)->device, cudaGetErrorString(dev_guard__.err))
 
 int ws_reserve(wrnn_handle *h, Workspace &w, size_t bytes);
 int ensure_packed_public(wrnn_handle *h);   // pack weights for the kernels if not yet done
@@ -176,9 +209,15 @@ int res_plan(wrnn_handle *h);
 bool res_supported(const wrnn_handle *h);
 int res_max_folds();
 int res_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st);
+// loop_mma.cu
+int mma_plan(wrnn_handle *h);
+bool mma_supported(const wrnn_handle *h);
+int mma_min_folds();               // fold count from which the tensor-core kernel beats groups of the resident kernel
+int mma_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st);
 // which loop kernel a run will use: 1 = fma (grid barriers, any dims, any fold count), 2 = pipelined
-// (smem weights, tagged exchange), 3 = resident (register weights, default dims)
-int loop_kernel_choice(const wrnn_handle *h);
+// (smem weights, tagged exchange), 3 = resident (register weights, default dims), 4 = tensor-core (tcgen05, bf16 hi/lo
+// operands, default dims, MoL; chosen from mma_min_folds() folds up)
+int loop_kernel_choice(const wrnn_handle *h, int64_t folds);
 
 // host tables (api.cu)
 void host_linspace(double start, double stop, int64_t n, double *out);

@@ -1,0 +1,757 @@
+// Per-sample loop, tensor-core kernel for large fold batches (config 5: hundreds of folds per GPU).
+//
+// `generate`'s hot loop (models/fatchord_version.py:201-241) for B folds at once is, per step, a chain of skinny
+// GEMMs  out[rows x B] = W[rows x K] . act[K x B]:  rnn1 (:210), rnn2 (:213-214), fc1 (:217-218), fc2 (:220-221),
+// fc3 (:223).  The FMA kernels (loop_res.cu ...) spend the same time per fold whatever B is; here the four big
+// layers run on the 5th-generation tensor cores:
+//
+//   * swap-AB: weights are the M operand (128-row tiles), folds are N (NT = 16..128 per tile), `tcgen05.mma`
+//     cta_group::1 kind::f16 issued by one thread, accumulators in TMEM, read back with `tcgen05.ld` into the fused
+//     GRU-gate / ReLU epilogue;
+//   * precision: every operand is a bf16 hi + bf16 lo pair (x = hi + lo to ~2^-17), three MMAs per k-step
+//     (hi.hi + hi.lo + lo.hi) accumulated in fp32: products carry ~1e-5 relative error, far inside the 1e-3 bound
+//     on teacher-forced logits that plain bf16 breaks after a few thousand recurrent steps;
+//   * operands live in global memory (L2-resident) already in the K-major, no-swizzle shared-memory image the MMA
+//     descriptors address, "[k-chunk of 8][row][8 elements]", so a pipeline stage is two plain `cp.async.bulk`
+//     copies (one weight block, one activation block) completing on an mbarrier: no tensor maps, no swizzle;
+//   * one persistent cooperative launch for all S steps; per step four MMA phases (rnn1, rnn2, fc1, fc2) and one
+//     fp32 FFMA phase (fc3 + MoL sampling + next step's conditioning operand), separated by split-phase grid
+//     barriers (epilogue warps arrive, the TMA producer waits); every phase is spread over all SMs as
+//     (row tile, fold tile) jobs;
+//   * algebra: the I layer and both residual adds are folded into composed matrices formed on the host in double
+//     (W_ih1 W_I etc., as in loop_res.cu), so the conditioning features and the previous sample enter every layer as
+//     extra K columns of the same MMA chain.
+//
+// Warp roles in a CTA (320 threads): warp 0 = TMA producer, warp 1 = MMA issuer (owns TMEM), warps 2..9 = epilogue
+// (TMEM -> registers -> shared staging -> gates -> global operands) and the FFMA phase.
+#include <cuda_bf16.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <vector>
+
+#include "internal.h"
+#include "loop_common.cuh"
+#include "exchange.cuh"
+
+namespace wrnn {
+
+namespace mma {
+
+constexpr int H = 512, FCD = 512, AUX = 32, FEAT = 80;
+constexpr int UT = 32;                     // GRU units per row tile: rows [r(32) | z(32) | n(32)] = 96 of the MMA's 128
+constexpr int GRU_ROWS = 3 * UT, FC_ROWS = 128;
+constexpr int MT_GRU = H / UT, MT_FC = FCD / FC_ROWS;     // 16, 4 row tiles
+constexpr int KC = 4;                      // k-chunks (of 8 elements) per pipeline stage: K = 32 = two MMA k-steps
+constexpr int NSTAGE = 4;
+constexpr int A_STAGE = 2 * KC * FC_ROWS * 16;            // 16384 B: hi + lo, room for the 128-row image
+constexpr int B_STAGE = 2 * KC * 128 * 16;                // 16384 B at NT = 128
+constexpr int STAGE_BYTES = A_STAGE + B_STAGE;
+constexpr int CGROUPS = 7;                 // conditioning operand: 28 chunks = 224 elements per fold
+constexpr int HGROUPS = H / 32;            // 16 stage groups in a 512-wide operand
+constexpr int THREADS = 320, EPI_THREADS = 256, EPI_WARPS = 8;
+constexpr int STG_FLOATS = 2 * 3 * UT * 33;               // epilogue staging (GRU: two accumulators x three gates)
+constexpr int NCP = 32;                    // fc3 rows padded (MoL: 30)
+constexpr int TMEM_COLS = 512;
+// conditioning operand element order (which features each layer concatenates):
+//   [a4 (32) | a2 (32) | x_prev (1) | m (80) | a1 (32) | a3 (32) | zero (15)]
+// so that rnn1 reads chunks 8..23, rnn2 chunks 4..23, fc1 chunks 8..27, fc2 chunks 0..3.
+constexpr int C_A4 = 0, C_A2 = 32, C_X = 64, C_M = 65, C_A1 = 145, C_A3 = 177, C_END = 209;
+constexpr int NST_P1 = 4 + 16, NST_P2 = 16 + 5 + 16, NST_P3 = 16 + 5, NST_P4 = 16 + 1;
+
+enum { ARR_C = 0, ARR_H1CUR, ARR_H1NEW, ARR_H2CUR, ARR_S12, ARR_Y1 };
+
+struct StageInfo { int arr, g, acc, first; };
+__host__ __device__ inline int phase_stages(int p) { return p == 0 ? NST_P1 : p == 1 ? NST_P2 : p == 2 ? NST_P3 : NST_P4; }
+__host__ __device__ inline StageInfo stage_info(int p, int s) {
+    if (p == 0) return s < 4 ? StageInfo{ARR_C, 2 + s, 0, s == 0} : StageInfo{ARR_H1CUR, s - 4, 1, s == 4};
+    if (p == 1) {
+        if (s < 16) return StageInfo{ARR_H1NEW, s, 0, s == 0};
+        if (s < 21) return StageInfo{ARR_C, 1 + (s - 16), 0, 0};
+        return StageInfo{ARR_H2CUR, s - 21, 1, s == 21};
+    }
+    if (p == 2) return s < 16 ? StageInfo{ARR_S12, s, 0, s == 0} : StageInfo{ARR_C, 2 + (s - 16), 0, 0};
+    return s < 16 ? StageInfo{ARR_Y1, s, 0, s == 0} : StageInfo{ARR_C, 0, 0, 0};
+}
+
+struct Params {
+    LoopArgs a;
+    int NT, NTILES, G, NC;
+    const uint8_t *Aimg;           // packed weights: phase p at offA[p], [row tile][stage][hi|lo][KC][rows][8] bf16
+    int64_t offA[4];
+    const float *bias;             // P1: [16][2][96] | P2: [16][2][96] | P3: [512] | P4: [512]
+    const float *Wf3, *bf3;        // [NCP][512], [NCP] fp32
+    uint8_t *H1[2], *H2[2], *S12, *Y1, *C;      // B operands, [fold tile][group][hi|lo][KC][NT][8] bf16
+    float *h1f, *h2f, *y2f;        // [NTILES*NT][512] fp32 state / fc2 output
+    GridSync gs;
+};
+
+// ---------------------------------------------------------------------------- PTX
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(void *b, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(b)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(void *b, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(b)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(void *b) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(b)) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(void *b, uint32_t parity) {
+    uint32_t ok;
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(ok) : "r"(smem_u32(b)), "r"(parity) : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t bytes, void *b) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(b)) : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async_global() { asm volatile("fence.proxy.async.global;" ::: "memory"); }
+__device__ __forceinline__ void tmem_alloc(uint32_t *dst_smem, uint32_t ncols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "r"(ncols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accum) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                 ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum) : "memory");
+}
+__device__ __forceinline__ void umma_commit(void *bar) {     // arrives on `bar` when every MMA issued so far has completed
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {   // 32 lanes x 32 columns: thread i <- lane i
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
+          "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]),
+          "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]),
+          "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr) : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+// Shared-memory matrix descriptor, K-major, no swizzle: element (row r, k) of the operand sits at
+//   start + (r % 8) * 16 + (r / 8) * SBO + (k / 8) * LBO + (k % 8) * 2   bytes.
+// With the image [k-chunk][rows][8]: SBO = 128 (eight 16-byte rows), LBO = rows * 16.
+__device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo, uint32_t sbo) {
+    return (uint64_t)((saddr >> 4) & 0x3fff) | ((uint64_t)((lbo >> 4) & 0x3fff) << 16) | ((uint64_t)((sbo >> 4) & 0x3fff) << 32) |
+           ((uint64_t)1 << 46);
+}
+// instruction descriptor: fp32 accumulate, A = B = bf16, both K-major, N >> 3 at bit 17, M >> 4 at bit 24
+__device__ __forceinline__ uint32_t make_idesc(int M, int N) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+// ---------------------------------------------------------------------------- small helpers
+struct Watch {                  // a lost arrival becomes an error flag, not a hung GPU box
+    int *abort_flag;
+    bool dead;
+};
+__device__ __forceinline__ bool give_up(Watch &w, long long t0, unsigned &spins) {
+    if ((++spins & 1023u) == 0u) {
+        if (clock64() - t0 > WATCHDOG_CLOCKS) { atomicExch(w.abort_flag, 3); w.dead = true; }
+        else if (ld_volatile_s32(w.abort_flag)) w.dead = true;
+    }
+    return w.dead;
+}
+__device__ __forceinline__ void mbar_wait(void *b, uint32_t parity, Watch &w) {
+    if (w.dead || mbar_try_wait(b, parity)) return;
+    const long long t0 = clock64();
+    unsigned spins = 0;
+    while (!mbar_try_wait(b, parity))
+        if (give_up(w, t0, spins)) return;
+}
+__device__ __forceinline__ void grid_wait(const GridSync &gs, unsigned long long want, Watch &w) {
+    if (w.dead) return;
+    const long long t0 = clock64();
+    unsigned spins = 0;
+    while (ld_acquire_u64(gs.counter) < want)
+        if (give_up(w, t0, spins)) return;
+}
+__device__ __forceinline__ void epi_bar() { bar_sync(1, EPI_THREADS); }
+
+// bf16 hi / lo split of four floats, packed: .x/.y = hi pairs, .z/.w = lo pairs
+__device__ __forceinline__ void split4(const float (&v)[4], uint2 &hi, uint2 &lo) {
+    __nv_bfloat16 h[4], l[4];
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        h[i] = __float2bfloat16_rn(v[i]);
+        l[i] = __float2bfloat16_rn(v[i] - __bfloat162float(h[i]));
+    }
+    hi.x = (uint32_t)__bfloat16_as_ushort(h[0]) | ((uint32_t)__bfloat16_as_ushort(h[1]) << 16);
+    hi.y = (uint32_t)__bfloat16_as_ushort(h[2]) | ((uint32_t)__bfloat16_as_ushort(h[3]) << 16);
+    lo.x = (uint32_t)__bfloat16_as_ushort(l[0]) | ((uint32_t)__bfloat16_as_ushort(l[1]) << 16);
+    lo.y = (uint32_t)__bfloat16_as_ushort(l[2]) | ((uint32_t)__bfloat16_as_ushort(l[3]) << 16);
+}
+// byte offset of the 16-byte slot (fold fi of tile nt, feature chunk `chunk`) in a B operand with NG stage groups
+__device__ __forceinline__ size_t b_slot(int NT, int NG, int nt, int chunk, int fi, int hl) {
+    return ((size_t)(nt * NG + (chunk >> 2)) * 2 + hl) * (size_t)(KC * NT * 16) + (size_t)((chunk & 3) * NT + fi) * 16;
+}
+
+// MoL draw for one fold by one warp from 3*nmix logits in shared memory: same arithmetic as mol_sample_warp
+__device__ __forceinline__ float mol_sample_smem(const float *lg, int nmix, float myu1, float u2, int lane, int *pick) {
+    float t = -INFINITY;
+    if (lane < nmix) t = lg[lane] - logf(-logf(myu1));
+    int idx = lane;
+#pragma unroll
+    for (int o = 16; o >= 1; o >>= 1) {
+        const float ot = __shfl_xor_sync(0xffffffffu, t, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
+        if (ot > t || (ot == t && oi < idx)) { t = ot; idx = oi; }
+    }
+    const float mean = lg[nmix + idx];
+    const float ls = fmaxf(lg[2 * nmix + idx], -32.23619130191664f);
+    float x = mean + expf(ls) * (logf(u2) - logf(1.f - u2));
+    x = fminf(fmaxf(x, -1.f), 1.f);
+    *pick = idx;
+    return x;
+}
+
+// conditioning operand of step `t` for fold b (one warp): gather the 208-float row, reorder, split, store 28 chunks
+__device__ __forceinline__ void write_cond_operand(const Params &P, int64_t b, int64_t t, float xprev, float *scr, int lane) {
+    const int64_t S = P.a.S;
+    const int RW = FEAT + 4 * AUX;
+    if (t < S) {
+        const float *row = P.a.cond + ((size_t)b * S + t) * RW;
+#pragma unroll
+        for (int i = 0; i < 7; i++) {
+            const int e = lane + 32 * i;
+            if (e < RW) scr[e] = __ldg(row + e);
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < 7; i++) {
+            const int e = lane + 32 * i;
+            if (e < RW) scr[e] = 0.f;
+        }
+    }
+    __syncwarp();
+    if (lane < 4 * CGROUPS) {
+        float v[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            const int e = lane * 8 + i;
+            float x;
+            if (e < C_A2) x = scr[FEAT + 3 * AUX + (e - C_A4)];
+            else if (e < C_X) x = scr[FEAT + AUX + (e - C_A2)];
+            else if (e == C_X) x = xprev;
+            else if (e < C_A1) x = scr[e - C_M];
+            else if (e < C_A3) x = scr[FEAT + (e - C_A1)];
+            else if (e < C_END) x = scr[FEAT + 2 * AUX + (e - C_A3)];
+            else x = 0.f;
+            v[i] = x;
+        }
+        const float v0[4] = {v[0], v[1], v[2], v[3]}, v1[4] = {v[4], v[5], v[6], v[7]};
+        uint2 h0, l0, h1, l1;
+        split4(v0, h0, l0);
+        split4(v1, h1, l1);
+        const int nt = (int)(b / P.NT), fi = (int)(b % P.NT);
+        *reinterpret_cast<uint4 *>(P.C + b_slot(P.NT, CGROUPS, nt, lane, fi, 0)) = make_uint4(h0.x, h0.y, h1.x, h1.y);
+        *reinterpret_cast<uint4 *>(P.C + b_slot(P.NT, CGROUPS, nt, lane, fi, 1)) = make_uint4(l0.x, l0.y, l1.x, l1.y);
+    }
+    __syncwarp();
+}
+
+__device__ __forceinline__ const uint8_t *b_array(const Params &P, int arr, int64_t t) {
+    switch (arr) {
+        case ARR_C: return P.C;
+        case ARR_H1CUR: return P.H1[t & 1];
+        case ARR_H1NEW: return P.H1[(t + 1) & 1];
+        case ARR_H2CUR: return P.H2[t & 1];
+        case ARR_S12: return P.S12;
+        default: return P.Y1;
+    }
+}
+
+// first job of CTA `cta` in phase p, and the job stride: GRU phases fill CTAs from 0 up, fc phases from G-1 down
+__device__ __forceinline__ int phase_tiles(const Params &P, int p) { return (p < 2 ? MT_GRU : MT_FC) * P.NTILES; }
+__device__ __forceinline__ int first_job(const Params &P, int p, int cta) { return p < 2 ? cta : P.G - 1 - cta; }
+
+__global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    __shared__ __align__(8) uint64_t bar_full[NSTAGE], bar_empty[NSTAGE], bar_tfull[2], bar_tempty[2];
+    __shared__ uint32_t tmem_base_s;
+    uint8_t *stages = smem;
+    float *stg = reinterpret_cast<float *>(smem + NSTAGE * STAGE_BYTES);
+    float *wf3 = stg + STG_FLOATS;                          // [NCP][512]
+    float *scr = wf3 + NCP * FCD;                           // per epilogue warp: 256 floats
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, cta = blockIdx.x;
+    const int NT = P.NT, G = P.G;
+    const int64_t S = P.a.S, B = P.a.B;
+    Watch w{P.gs.abort_flag, false};
+
+    if (tid == 0) {
+        for (int i = 0; i < NSTAGE; i++) { mbar_init(&bar_full[i], 1); mbar_init(&bar_empty[i], 1); }
+        for (int i = 0; i < 2; i++) { mbar_init(&bar_tfull[i], 1); mbar_init(&bar_tempty[i], 1); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) tmem_alloc(&tmem_base_s, TMEM_COLS);
+    for (int i = tid; i < NCP * FCD; i += THREADS) wf3[i] = P.Wf3[i];
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tb = tmem_base_s;
+
+    if (warp == 0) {
+        // ======================================================================= TMA producer
+        if (lane == 0) {
+            uint32_t it = 0;
+            for (int64_t t = 0; t < S && !w.dead; t++) {
+                for (int p = 0; p < 4; p++) {
+                    const int ntiles = phase_tiles(P, p), nst = phase_stages(p);
+                    const uint32_t abytes = 2u * KC * (p < 2 ? GRU_ROWS : FC_ROWS) * 16u, bbytes = 2u * KC * NT * 16u;
+                    bool waited = false;
+                    for (int id = first_job(P, p, cta); id < ntiles; id += G) {
+                        if (!waited) {     // this phase's operands were written by phase q-1 of every CTA
+                            grid_wait(P.gs, (unsigned long long)G * (unsigned long long)(1 + 5 * t + p), w);
+                            fence_proxy_async_global();
+                            waited = true;
+                        }
+                        const int mt = id % (p < 2 ? MT_GRU : MT_FC), nt = id / (p < 2 ? MT_GRU : MT_FC);
+                        const uint8_t *Abase = P.Aimg + P.offA[p] + (size_t)mt * nst * abytes;
+                        for (int s = 0; s < nst; s++, it++) {
+                            const int slot = it % NSTAGE;
+                            mbar_wait(&bar_empty[slot], ((it / NSTAGE) & 1) ^ 1, w);
+                            const StageInfo si = stage_info(p, s);
+                            const int NG = si.arr == ARR_C ? CGROUPS : HGROUPS;
+                            const uint8_t *Bsrc = b_array(P, si.arr, t) + (size_t)(nt * NG + si.g) * bbytes;
+                            uint8_t *dst = stages + (size_t)slot * STAGE_BYTES;
+                            mbar_expect_tx(&bar_full[slot], abytes + bbytes);
+                            bulk_g2s(dst, Abase + (size_t)s * abytes, abytes, &bar_full[slot]);
+                            bulk_g2s(dst + A_STAGE, Bsrc, bbytes, &bar_full[slot]);
+                        }
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ======================================================================= MMA issuer
+        if (lane == 0) {
+            uint32_t it = 0, j = 0;
+            const uint32_t idesc = make_idesc(128, NT);
+            for (int64_t t = 0; t < S && !w.dead; t++) {
+                for (int p = 0; p < 4; p++) {
+                    const int ntiles = phase_tiles(P, p), nst = phase_stages(p);
+                    const uint32_t rows = p < 2 ? GRU_ROWS : FC_ROWS;
+                    const uint32_t lboA = rows * 16u, lboB = (uint32_t)NT * 16u;
+                    for (int id = first_job(P, p, cta); id < ntiles; id += G, j++) {
+                        const uint32_t buf = j & 1;
+                        mbar_wait(&bar_tempty[buf], ((j >> 1) & 1) ^ 1, w);
+                        tc_fence_after();
+                        for (int s = 0; s < nst; s++, it++) {
+                            const int slot = it % NSTAGE;
+                            mbar_wait(&bar_full[slot], (it / NSTAGE) & 1, w);
+                            tc_fence_after();
+                            const StageInfo si = stage_info(p, s);
+                            const uint32_t d = tb + buf * 256u + (uint32_t)si.acc * (uint32_t)NT;
+                            const uint32_t sA = smem_u32(stages + (size_t)slot * STAGE_BYTES), sB = sA + A_STAGE;
+#pragma unroll
+                            for (int ks = 0; ks < KC / 2; ks++) {
+                                const uint64_t ah = make_desc(sA + ks * 2 * lboA, lboA, 128);
+                                const uint64_t al = make_desc(sA + KC * lboA + ks * 2 * lboA, lboA, 128);
+                                const uint64_t bh = make_desc(sB + ks * 2 * lboB, lboB, 128);
+                                const uint64_t bl = make_desc(sB + KC * lboB + ks * 2 * lboB, lboB, 128);
+                                umma_bf16(d, ah, bh, idesc, (si.first && ks == 0) ? 0u : 1u);
+                                umma_bf16(d, ah, bl, idesc, 1u);
+                                umma_bf16(d, al, bh, idesc, 1u);
+                            }
+                            umma_commit(&bar_empty[slot]);          // the stage is free once these MMAs have read it
+                        }
+                        umma_commit(&bar_tfull[buf]);               // accumulators complete
+                    }
+                }
+            }
+        }
+        __syncwarp();
+    } else {
+        // ======================================================================= epilogue warps + FFMA phase
+        const int etid = tid - 64, ewarp = warp - 2;
+        const int q = warp & 3, half = ewarp >> 2;          // TMEM lane quarter this warp may read; column half
+        float *myscr = scr + ewarp * 256;
+        const uint2 key = make_uint2((uint32_t)P.a.seed, (uint32_t)(P.a.seed >> 32));
+        const int nmix = P.NC / 3;
+        // ---- phase 0: conditioning operand of step 0 (x_prev = 0 or the teacher's first sample)
+        for (int64_t b = cta + (int64_t)G * ewarp; b < B; b += (int64_t)G * EPI_WARPS) {
+            const float x0 = P.a.teacher ? P.a.teacher[(size_t)b * S] : 0.f;
+            write_cond_operand(P, b, 0, x0, myscr, lane);
+        }
+        epi_bar();
+        if (etid == 0) { fence_proxy_async_global(); red_release_add_u64(P.gs.counter, 1ull); }
+
+        uint32_t j = 0;
+        for (int64_t t = 0; t < S; t++) {
+            if (w.dead) break;                               // uniform: set below from a flag read after a barrier
+            for (int p = 0; p < 4; p++) {
+                const int ntiles = phase_tiles(P, p);
+                for (int id = first_job(P, p, cta); id < ntiles; id += G, j++) {
+                    const uint32_t buf = j & 1;
+                    const int mt = id % (p < 2 ? MT_GRU : MT_FC), nt = id / (p < 2 ? MT_GRU : MT_FC);
+                    mbar_wait(&bar_tfull[buf], (j >> 1) & 1, w);
+                    __syncwarp();       // lanes leave the spin loop one by one; tcgen05.ld is .sync.aligned: converge first
+                    tc_fence_after();
+                    if (p < 2) {
+                        // ---------------- GRU gates (fatchord_version.py:210-216): rows [r | z | n] x 32 units
+                        const float *bi = P.bias + (size_t)(p * MT_GRU + mt) * 2 * GRU_ROWS, *bh = bi + GRU_ROWS;
+                        float *hf = p == 0 ? P.h1f : P.h2f;
+                        uint8_t *Hn = p == 0 ? P.H1[(t + 1) & 1] : P.H2[(t + 1) & 1];
+                        for (int c0 = 0; c0 < NT; c0 += 32) {
+                            if (q < 3) {
+                                uint32_t r[32];
+                                tmem_ld32(tb + ((uint32_t)(q * 32) << 16) + buf * 256u + (uint32_t)(half * NT + c0), r);
+                                float *dst = stg + ((half * 3 + q) * UT + lane) * 33;
+#pragma unroll
+                                for (int i = 0; i < 32; i++) dst[i] = __uint_as_float(r[i]);
+                            }
+                            epi_bar();
+                            const int f = etid & 31, quad = etid >> 5, fi = c0 + f;
+                            if (fi < NT) {
+                                const int u0 = quad * 4, gu = mt * UT + u0;
+                                const size_t fold = (size_t)nt * NT + fi;
+                                const float4 hp4 = __ldcg(reinterpret_cast<const float4 *>(hf + fold * H + gu));
+                                const float hp[4] = {hp4.x, hp4.y, hp4.z, hp4.w};
+                                float hn[4];
+#pragma unroll
+                                for (int i = 0; i < 4; i++) {
+                                    const int u = u0 + i;
+                                    const float ir = stg[((0 * 3 + 0) * UT + u) * 33 + f] + __ldg(bi + 0 * UT + u);
+                                    const float iz = stg[((0 * 3 + 1) * UT + u) * 33 + f] + __ldg(bi + 1 * UT + u);
+                                    const float in_ = stg[((0 * 3 + 2) * UT + u) * 33 + f] + __ldg(bi + 2 * UT + u);
+                                    const float hr = stg[((1 * 3 + 0) * UT + u) * 33 + f] + __ldg(bh + 0 * UT + u);
+                                    const float hz = stg[((1 * 3 + 1) * UT + u) * 33 + f] + __ldg(bh + 1 * UT + u);
+                                    const float hnn = stg[((1 * 3 + 2) * UT + u) * 33 + f] + __ldg(bh + 2 * UT + u);
+                                    hn[i] = gru_update(ir, iz, in_, hr, hz, hnn, hp[i]);
+                                }
+                                *reinterpret_cast<float4 *>(hf + fold * H + gu) = make_float4(hn[0], hn[1], hn[2], hn[3]);
+                                uint2 hi, lo;
+                                split4(hn, hi, lo);
+                                const int sub = (gu & 7) * 2;       // 0 or 8 bytes inside the 16-byte chunk
+                                *reinterpret_cast<uint2 *>(Hn + b_slot(NT, HGROUPS, nt, gu >> 3, fi, 0) + sub) = hi;
+                                *reinterpret_cast<uint2 *>(Hn + b_slot(NT, HGROUPS, nt, gu >> 3, fi, 1) + sub) = lo;
+                                if (p == 1) {                       // fc1 reads x + h1 + h2; x is folded into its weights
+                                    const float4 a4 = __ldcg(reinterpret_cast<const float4 *>(P.h1f + fold * H + gu));
+                                    const float s[4] = {a4.x + hn[0], a4.y + hn[1], a4.z + hn[2], a4.w + hn[3]};
+                                    split4(s, hi, lo);
+                                    *reinterpret_cast<uint2 *>(P.S12 + b_slot(NT, HGROUPS, nt, gu >> 3, fi, 0) + sub) = hi;
+                                    *reinterpret_cast<uint2 *>(P.S12 + b_slot(NT, HGROUPS, nt, gu >> 3, fi, 1) + sub) = lo;
+                                }
+                            }
+                            epi_bar();
+                        }
+                    } else {
+                        // ---------------- fc1 / fc2 + ReLU (:217-221): 128 rows
+                        const float *bb = P.bias + (size_t)2 * MT_GRU * 2 * GRU_ROWS + (size_t)(p - 2) * FCD + mt * FC_ROWS;
+                        for (int c0 = 0; c0 < NT; c0 += 32) {
+                            if (half == 0) {
+                                uint32_t r[32];
+                                tmem_ld32(tb + ((uint32_t)(q * 32) << 16) + buf * 256u + (uint32_t)c0, r);
+                                float *dst = stg + (q * 32 + lane) * 33;
+#pragma unroll
+                                for (int i = 0; i < 32; i++) dst[i] = __uint_as_float(r[i]);
+                            }
+                            epi_bar();
+                            const int f = etid & 31, rg = etid >> 5, fi = c0 + f;
+                            if (fi < NT) {
+                                const size_t fold = (size_t)nt * NT + fi;
+                                float v[16];
+#pragma unroll
+                                for (int i = 0; i < 16; i++)
+                                    v[i] = fmaxf(stg[(rg * 16 + i) * 33 + f] + __ldg(bb + rg * 16 + i), 0.f);
+                                const int gr = mt * FC_ROWS + rg * 16;
+                                if (p == 2) {
+#pragma unroll
+                                    for (int c = 0; c < 2; c++) {
+                                        const float v0[4] = {v[8 * c], v[8 * c + 1], v[8 * c + 2], v[8 * c + 3]};
+                                        const float v1[4] = {v[8 * c + 4], v[8 * c + 5], v[8 * c + 6], v[8 * c + 7]};
+                                        uint2 h0, l0, h1, l1;
+                                        split4(v0, h0, l0);
+                                        split4(v1, h1, l1);
+                                        *reinterpret_cast<uint4 *>(P.Y1 + b_slot(NT, HGROUPS, nt, (gr >> 3) + c, fi, 0)) =
+                                            make_uint4(h0.x, h0.y, h1.x, h1.y);
+                                        *reinterpret_cast<uint4 *>(P.Y1 + b_slot(NT, HGROUPS, nt, (gr >> 3) + c, fi, 1)) =
+                                            make_uint4(l0.x, l0.y, l1.x, l1.y);
+                                    }
+                                } else {
+                                    float4 *dst = reinterpret_cast<float4 *>(P.y2f + fold * FCD + gr);
+#pragma unroll
+                                    for (int c = 0; c < 4; c++) dst[c] = make_float4(v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
+                                }
+                            }
+                            epi_bar();
+                        }
+                    }
+                    tc_fence_before();
+                    epi_bar();
+                    if (etid == 0) mbar_arrive(&bar_tempty[buf]);        // TMEM buffer drained
+                }
+                // phase q = 1 + 5t + p finished by this CTA: publish
+                epi_bar();
+                if (etid == 0) { fence_proxy_async_global(); red_release_add_u64(P.gs.counter, 1ull); }
+            }
+            // ---------------- fc3 (:223) in fp32 + MoL draw (utils/distribution.py:87-123) + next conditioning operand
+            if (etid == 0) grid_wait(P.gs, (unsigned long long)G * (unsigned long long)(1 + 5 * t + 4), w);
+            epi_bar();
+            for (int64_t b = cta + (int64_t)G * ewarp; b < B; b += (int64_t)G * EPI_WARPS) {
+                float4 y[4];
+#pragma unroll
+                for (int jj = 0; jj < 4; jj++) y[jj] = __ldcg(reinterpret_cast<const float4 *>(P.y2f + (size_t)b * FCD + 128 * jj + lane * 4));
+                float acc[NCP];
+#pragma unroll
+                for (int r = 0; r < NCP; r++) {
+                    float a = 0.f;
+#pragma unroll
+                    for (int jj = 0; jj < 4; jj++) {
+                        const float4 wv = *reinterpret_cast<const float4 *>(wf3 + r * FCD + 128 * jj + lane * 4);
+                        a = fmaf(wv.x, y[jj].x, a);
+                        a = fmaf(wv.y, y[jj].y, a);
+                        a = fmaf(wv.z, y[jj].z, a);
+                        a = fmaf(wv.w, y[jj].w, a);
+                    }
+                    acc[r] = a;
+                }
+                warp_reduce_scatter<NCP>(acc, lane);
+                const int row = reduce_scatter_base<NCP>(lane);
+                const float lg = acc[0] + __ldg(P.bf3 + row);
+                __syncwarp();
+                myscr[224 + row] = lg;
+                __syncwarp();
+                const bool live = t < P.a.fold_len[b];
+                if (P.a.logits_out && live && lane < P.NC)
+                    P.a.logits_out[((size_t)b * S + t) * P.NC + lane] = myscr[224 + lane];
+                float myu1 = 0.5f, u2;
+                if (P.a.u1) {
+                    if (lane < nmix) myu1 = P.a.u1[((size_t)t * P.a.Btot + P.a.b0 + b) * nmix + lane];
+                    u2 = P.a.u2[(size_t)t * P.a.Btot + P.a.b0 + b];
+                } else {
+                    const uint4 r4 = philox4x32(make_uint4((uint32_t)t, (uint32_t)(P.a.b0 + b), (uint32_t)(lane >> 2), 1u), key);
+                    const uint32_t rr[4] = {r4.x, r4.y, r4.z, r4.w};
+                    myu1 = u_clip(rr[lane & 3]);
+                    const uint4 r2 = philox4x32(make_uint4((uint32_t)t, (uint32_t)(P.a.b0 + b), 0u, 2u), key);
+                    u2 = u_clip(r2.x);
+                }
+                int pick = 0;
+                float xv = mol_sample_smem(myscr + 224, nmix, myu1, u2, lane, &pick);
+                if (!live) xv = 0.f;
+                if (lane == 0 && live) {
+                    P.a.samples[(size_t)b * S + t] = xv;
+                    P.a.picks[(size_t)b * S + t] = pick;
+                }
+                if (P.a.teacher) xv = t + 1 < S ? P.a.teacher[(size_t)b * S + t + 1] : 0.f;
+                write_cond_operand(P, b, t + 1, xv, myscr, lane);
+            }
+            epi_bar();
+            if (etid == 0) { fence_proxy_async_global(); red_release_add_u64(P.gs.counter, 1ull); }
+            // uniform exit on a fired watchdog
+            if (etid == 0) stg[0] = (w.dead || ld_volatile_s32(P.gs.abort_flag)) ? 1.f : 0.f;
+            epi_bar();
+            w.dead = stg[0] != 0.f;
+            epi_bar();
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tb, TMEM_COLS);
+}
+
+}  // namespace mma
+
+// ============================================================================ host: pack + launch
+static inline uint16_t f2bf(float x) {       // round to nearest even
+    uint32_t u;
+    memcpy(&u, &x, 4);
+    if ((u & 0x7f800000u) == 0x7f800000u) return (uint16_t)(u >> 16);
+    u += 0x7fffu + ((u >> 16) & 1u);
+    return (uint16_t)(u >> 16);
+}
+static inline float bf2f(uint16_t b) {
+    uint32_t u = (uint32_t)b << 16;
+    float x;
+    memcpy(&x, &u, 4);
+    return x;
+}
+
+bool mma_supported(const wrnn_handle *h) {
+    const Dims &d = h->d;
+    return h->mma.ok && d.mode == WRNN_MODE_MOL && d.H == mma::H && d.FC == mma::FCD && d.A == mma::AUX && d.F == mma::FEAT &&
+           d.NC <= mma::NCP;
+}
+int mma_min_folds() { return 48; }
+
+int mma_plan(wrnn_handle *h) {
+    using namespace mma;
+    const Dims &d = h->d;
+    MmaPlan &pl = h->mma;
+    pl.ok = false;
+    if (!(d.mode == WRNN_MODE_MOL && d.H == H && d.FC == FCD && d.A == AUX && d.F == FEAT && d.NC <= NCP)) return 0;
+    if (h->num_sms < 16) return 0;
+    auto get = [&](const char *k) -> const HostTensor * {
+        auto it = h->w.find(k);
+        return it == h->w.end() ? nullptr : &it->second;
+    };
+    const HostTensor *WI = get("I.weight"), *BI = get("I.bias");
+    const HostTensor *W1i = get("rnn1.weight_ih_l0"), *W1h = get("rnn1.weight_hh_l0"), *B1i = get("rnn1.bias_ih_l0"),
+                     *B1h = get("rnn1.bias_hh_l0");
+    const HostTensor *W2i = get("rnn2.weight_ih_l0"), *W2h = get("rnn2.weight_hh_l0"), *B2i = get("rnn2.bias_ih_l0"),
+                     *B2h = get("rnn2.bias_hh_l0");
+    const HostTensor *F1 = get("fc1.weight"), *F1b = get("fc1.bias"), *F2 = get("fc2.weight"), *F2b = get("fc2.bias"),
+                     *F3 = get("fc3.weight"), *F3b = get("fc3.bias");
+    if (!WI || !BI || !W1i || !W1h || !B1i || !B1h || !W2i || !W2h || !B2i || !B2h || !F1 || !F1b || !F2 || !F2b || !F3 || !F3b)
+        return 0;      // fma_plan reports missing keys
+    const int KI = 1 + FEAT + AUX;     // 113: [x_prev, m, a1]
+    // composed matrices in double (fatchord_version.py:208-218): W . W_I and W . b_I for the three consumers of x
+    auto compose = [&](const HostTensor *W, int rows, int ldw, std::vector<double> &Wc, std::vector<double> &bc) {
+        Wc.assign((size_t)rows * KI, 0.0);
+        bc.assign(rows, 0.0);
+        for (int r = 0; r < rows; r++) {
+            const float *wr = W->v.data() + (size_t)r * ldw;
+            double *o = Wc.data() + (size_t)r * KI;
+            double bsum = 0.0;
+            for (int k = 0; k < H; k++) {
+                const double wk = wr[k];
+                const float *ir = WI->v.data() + (size_t)k * KI;
+                for (int c = 0; c < KI; c++) o[c] += wk * ir[c];
+                bsum += wk * BI->v[k];
+            }
+            bc[r] = bsum;
+        }
+    };
+    std::vector<double> Wc1, bc1, Wc2, bc2, Wc3, bc3;
+    compose(W1i, 3 * H, H, Wc1, bc1);
+    compose(W2i, 3 * H, H + AUX, Wc2, bc2);
+    compose(F1, FCD, H + AUX, Wc3, bc3);
+    // value of weight element (phase p, global row, conditioning element e of the operand order) / (512-wide operand, k)
+    auto cond_w = [&](int p, int grow, int e) -> double {
+        const bool in_x = e >= C_X && e < C_A3;        // x_prev, m, a1: column e - 64 of the composed matrix
+        if (p == 0) return in_x ? Wc1[(size_t)grow * KI + (e - C_X)] : 0.0;
+        if (p == 1) {
+            if (e >= C_A2 && e < C_X) return W2i->v[(size_t)grow * (H + AUX) + H + (e - C_A2)];
+            return in_x ? Wc2[(size_t)grow * KI + (e - C_X)] : 0.0;
+        }
+        if (p == 2) {
+            if (e >= C_A3 && e < C_END) return F1->v[(size_t)grow * (H + AUX) + H + (e - C_A3)];
+            return in_x ? Wc3[(size_t)grow * KI + (e - C_X)] : 0.0;
+        }
+        return (e >= C_A4 && e < C_A2) ? F2->v[(size_t)grow * (FCD + AUX) + FCD + (e - C_A4)] : 0.0;
+    };
+    auto main_w = [&](int p, int arr, int grow, int k) -> double {
+        switch (arr) {
+            case ARR_H1CUR: return W1h->v[(size_t)grow * H + k];
+            case ARR_H1NEW: return W2i->v[(size_t)grow * (H + AUX) + k];
+            case ARR_H2CUR: return W2h->v[(size_t)grow * H + k];
+            case ARR_S12: return F1->v[(size_t)grow * (H + AUX) + k];
+            default: return F2->v[(size_t)grow * (FCD + AUX) + k];
+        }
+        (void)p;
+    };
+    size_t total = 0;
+    for (int p = 0; p < 4; p++) {
+        pl.offA[p] = (int64_t)total;
+        const int rows = p < 2 ? GRU_ROWS : FC_ROWS, mts = p < 2 ? MT_GRU : MT_FC;
+        total += (size_t)mts * phase_stages(p) * 2 * KC * rows * 16;
+    }
+    std::vector<uint16_t> img(total / 2 + 2048, 0);       // + slack: the 96-row image is addressed as 128 rows
+    for (int p = 0; p < 4; p++) {
+        const int rows = p < 2 ? GRU_ROWS : FC_ROWS, mts = p < 2 ? MT_GRU : MT_FC, nst = phase_stages(p);
+        for (int mt = 0; mt < mts; mt++)
+            for (int s = 0; s < nst; s++) {
+                const StageInfo si = stage_info(p, s);
+                uint16_t *blk = img.data() + (size_t)pl.offA[p] / 2 + ((size_t)mt * nst + s) * (2 * KC * rows * 8);
+                for (int r = 0; r < rows; r++) {
+                    const int grow = p < 2 ? (r / UT) * H + mt * UT + (r % UT) : mt * FC_ROWS + r;
+                    for (int kl = 0; kl < KC * 8; kl++) {
+                        const int feat = si.g * 32 + kl;
+                        const double wv = si.arr == ARR_C ? cond_w(p, grow, feat) : main_w(p, si.arr, grow, feat);
+                        const float wf = (float)wv;
+                        const uint16_t hi = f2bf(wf), lo = f2bf((float)(wv - (double)bf2f(hi)));
+                        const size_t o = ((size_t)(kl / 8) * rows + r) * 8 + kl % 8;
+                        blk[o] = hi;
+                        blk[(size_t)KC * rows * 8 + o] = lo;
+                    }
+                }
+            }
+    }
+    std::vector<float> bias((size_t)2 * MT_GRU * 2 * GRU_ROWS + 2 * FCD, 0.f);
+    for (int p = 0; p < 2; p++)
+        for (int mt = 0; mt < MT_GRU; mt++)
+            for (int r = 0; r < GRU_ROWS; r++) {
+                const int grow = (r / UT) * H + mt * UT + (r % UT);
+                float *b = bias.data() + (size_t)(p * MT_GRU + mt) * 2 * GRU_ROWS;
+                b[r] = (float)((p == 0 ? bc1[grow] : bc2[grow]) + (double)(p == 0 ? B1i : B2i)->v[grow]);
+                b[GRU_ROWS + r] = (p == 0 ? B1h : B2h)->v[grow];
+            }
+    for (int r = 0; r < FCD; r++) {
+        bias[(size_t)2 * MT_GRU * 2 * GRU_ROWS + r] = (float)(bc3[r] + (double)F1b->v[r]);
+        bias[(size_t)2 * MT_GRU * 2 * GRU_ROWS + FCD + r] = F2b->v[r];
+    }
+    std::vector<float> wf3((size_t)NCP * FCD + NCP, 0.f);
+    for (int r = 0; r < d.NC; r++) {
+        memcpy(wf3.data() + (size_t)r * FCD, F3->v.data() + (size_t)r * FCD, FCD * sizeof(float));
+        wf3[(size_t)NCP * FCD + r] = F3b->v[r];
+    }
+    if (pl.Aimg) cudaFree(pl.Aimg);
+    if (pl.bias) cudaFree(pl.bias);
+    if (pl.wf3) cudaFree(pl.wf3);
+    pl.Aimg = nullptr; pl.bias = nullptr; pl.wf3 = nullptr;
+    WRNN_CUDA(h, cudaMalloc((void **)&pl.Aimg, img.size() * 2));
+    WRNN_CUDA(h, cudaMemcpy(pl.Aimg, img.data(), img.size() * 2, cudaMemcpyHostToDevice));
+    WRNN_CUDA(h, cudaMalloc((void **)&pl.bias, bias.size() * 4));
+    WRNN_CUDA(h, cudaMemcpy(pl.bias, bias.data(), bias.size() * 4, cudaMemcpyHostToDevice));
+    WRNN_CUDA(h, cudaMalloc((void **)&pl.wf3, wf3.size() * 4));
+    WRNN_CUDA(h, cudaMemcpy(pl.wf3, wf3.data(), wf3.size() * 4, cudaMemcpyHostToDevice));
+    pl.img_bytes = total;
+    pl.smem_bytes = (size_t)NSTAGE * STAGE_BYTES + (size_t)(STG_FLOATS + NCP * FCD + EPI_WARPS * 256) * sizeof(float);
+    if (pl.smem_bytes + 1024 > h->smem_optin) return 0;
+    WRNN_CUDA(h, cudaFuncSetAttribute(mma::mma_loop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes));
+    pl.ok = true;
+    return 0;
+}
+
+// fold-tile width: the smallest multiple of 16 that puts the 16 x NTILES GRU jobs of a phase on distinct SMs
+int mma_pick_nt(int64_t B, int G) {
+    for (int nt = 16; nt <= 128; nt += 16)
+        if ((int64_t)mma::MT_GRU * ((B + nt - 1) / nt) <= G) return nt;
+    return 128;
+}
+
+int mma_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
+    using namespace mma;
+    const MmaPlan &pl = h->mma;
+    Params P;
+    P.a = a;
+    P.G = h->num_sms;
+    P.NT = h->mma_force_nt > 0 ? h->mma_force_nt : mma_pick_nt(a.B, P.G);
+    P.NTILES = (int)((a.B + P.NT - 1) / P.NT);
+    P.NC = h->d.NC;
+    P.Aimg = pl.Aimg;
+    for (int p = 0; p < 4; p++) P.offA[p] = pl.offA[p];
+    P.bias = pl.bias;
+    P.Wf3 = pl.wf3;
+    P.bf3 = pl.wf3 + (size_t)NCP * FCD;
+    const size_t NF = (size_t)P.NTILES * P.NT;
+    const size_t bH = NF * H * 4, bC = NF * CGROUPS * 128, bF = NF * H * sizeof(float);     // hi + lo bf16 = 4 B per element
+    const size_t total = 6 * bH + bC + 3 * bF + 4096;
+    WRNN_TRY(ws_reserve(h, h->ws_act, total));
+    WRNN_CUDA(h, cudaMemsetAsync(h->ws_act.p, 0, total, st));       // h1 = h2 = 0 (:194-195), padded folds stay zero
+    uint8_t *p8 = (uint8_t *)h->ws_act.p;
+    P.H1[0] = p8; p8 += bH; P.H1[1] = p8; p8 += bH;
+    P.H2[0] = p8; p8 += bH; P.H2[1] = p8; p8 += bH;
+    P.S12 = p8; p8 += bH; P.Y1 = p8; p8 += bH;
+    P.C = p8; p8 += (bC + 1023) / 1024 * 1024;
+    P.h1f = (float *)p8; p8 += bF; P.h2f = (float *)p8; p8 += bF; P.y2f = (float *)p8;
+    WRNN_TRY(ws_reserve(h, h->ws_sync, 128));
+    WRNN_CUDA(h, cudaMemsetAsync(h->ws_sync.p, 0, 16, st));
+    P.gs.counter = (unsigned long long *)h->ws_sync.p;
+    P.gs.abort_flag = (int *)((char *)h->ws_sync.p + 64);
+    WRNN_CUDA(h, cudaFuncSetAttribute(mma_loop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes));
+    void *args[] = {(void *)&P};
+    WRNN_CUDA(h, cudaLaunchCooperativeKernel((const void *)mma_loop_kernel, dim3(P.G), dim3(THREADS), args, pl.smem_bytes, st));
+    h->launches++;
+    return 0;
+}
+
+}  // namespace wrnn

@@ -145,6 +145,15 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t by
                  ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(b)) : "memory");
 }
 
+// mbarrier wait with the exchange watchdog: a bulk copy that never completes becomes an error, not a hang
+__device__ __forceinline__ void mbar_wait_wd(void *b, uint32_t parity, Dead &dd) {
+    if (mbar_try_wait(b, parity) || dd.dead) return;
+    const long long t0 = clock64();
+    unsigned spins = 0;
+    while (!mbar_try_wait(b, parity))
+        if (poll_giveup(dd, t0, spins)) return;
+}
+
 __device__ __forceinline__ uint4 poll_slot(const uint4 *p, uint32_t tag, Dead &dd, int which = 0) {
     uint4 v = ld_relaxed_v4(p);
     if (!dd.dead && !tags_ok(v, tag)) {
@@ -684,19 +693,19 @@ __device__ __forceinline__ void gather_issue(const float *src, int n4, float *ds
 }
 __device__ __forceinline__ void gather_wait(const float *src, int n4, float *dst, uint32_t tag, int rank, int nth, void *mb, uint32_t parity,
                                             Dead &dd) {
-    while (!mbar_try_wait(mb, parity)) {}
+    mbar_wait_wd(mb, parity, dd);
     const uint4 *s4 = reinterpret_cast<const uint4 *>(src);
     uint4 *d4 = reinterpret_cast<uint4 *>(dst);
     unsigned spins = 0;
     long long t0 = 0;
-    // A slot is one aligned 16-byte store of its producer, so one word stands for the slot; lane l looks at word
-    // (l >> 3) & 3 of its slot, which spreads a warp's 32 reads over all 32 banks (one wavefront instead of four).
-    const uint32_t *dw = reinterpret_cast<const uint32_t *>(dst) + ((rank >> 3) & 3);
+    // Every word of a slot carries the tag and all four are checked (one LDS.128 per slot, conflict-free: consecutive
+    // lanes read consecutive 16-byte slots).  PTX models the producer's st.relaxed.gpu.v4 as four scalar stores, so a
+    // slot whose words were not all replaced yet must fail the check, not pass on the strength of one word.
     for (;;) {
         bool any = false;
 #pragma unroll 5
         for (int i = rank; i < n4; i += nth)
-            if (((dw[4 * i] ^ tag) & 3u) != 0u) {
+            if (!tags_ok(d4[i], tag)) {
                 cp_async16(d4 + i, s4 + i);
                 any = true;
             }
@@ -807,7 +816,7 @@ __device__ void res_row_role(const ResParams &P, int cta, float *smem) {
     // Conditioning terms of step t -> pre_cb[t & 1], by all 16 warps (needs cond(t) in smem).
     auto cond_step = [&](int64_t t, bool second) {
         const int pp = (int)(t & 1);
-        while (!mbar_try_wait(mbar + pp, (uint32_t)((t >> 1) & 1))) {}
+        mbar_wait_wd(mbar + pp, (uint32_t)((t >> 1) & 1), dd);
         cond_all(wcu, cbuf + (size_t)pp * RB * CBL, bias, pre_cb + pp * 1280, B, Kc, tid >> 5, lane, second);
     };
     cond_step(0, false);
