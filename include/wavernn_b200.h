@@ -141,11 +141,16 @@ int wrnn_forward_logits(wrnn_handle *h, const float *x, const float *mels, int32
 const char *wrnn_loop_kernel_name(wrnn_handle *h, int64_t folds);
 /* Force a loop kernel: 0 = auto (fastest kernel that supports the dims and the fold count), 1 = fma (grid-barrier
  * kernel, any dims and fold count, reference order of operations), 2 = fma-pipelined (tagged exchange, shared-memory
- * weights), 4 = "tcgen05-bf16x3" (csrc/loop_mma.cu: the contractions of fatchord_version.py:208-221 on the tensor
+ * weights), 3 = fma-resident (register-resident weights, groups of <= 20 folds, whatever the fold count),
+ * 4 = "tcgen05-bf16x3" (csrc/loop_mma.cu: the contractions of fatchord_version.py:208-221 on the tensor
  * cores with bf16 hi/lo split operands and fp32 TMEM accumulators; default dims, MoL; auto from 48 folds up). */
 int wrnn_set_loop_kernel(wrnn_handle *h, int32_t which);
 /* Fold-tile width N of the tensor-core kernel's (128 rows x N folds) jobs: 0 = auto, else a multiple of 16 <= 128. */
 int wrnn_set_mma_fold_tile(wrnn_handle *h, int32_t nt);
+/* Bring-up aid: recurrent state of the last tensor-core run, (folds, 512) float32: which = 0 h1, 1 h2, 2 fc2 output.
+ * With the environment variable WRNN_MMA_STEPS=n the kernel stops after n loop steps so the state can be compared
+ * with the oracle's after the same steps. */
+int wrnn_debug_mma_state(wrnn_handle *h, int32_t which, int64_t folds, float *out);
 
 /* ------------------------------------------------------------------ deepmind variant */
 typedef struct wrnn_dm_handle wrnn_dm_handle;

@@ -101,11 +101,12 @@ struct TestArgs {
     long long *clk;                                 // [2]: mma clocks, status
 };
 
-// one CTA: warp 0 loads, warp 1 issues, warps 2..5 read TMEM
+// one CTA, staged with CTA barriers (load -> MMA chain -> TMEM read): warp 0 loads, warp 1 issues, warps 2..5 read TMEM
 __global__ void __launch_bounds__(192, 1) umma_test(TestArgs a) {
     extern __shared__ __align__(128) uint8_t sm[];
     __shared__ __align__(8) uint64_t bar_load, bar_mma;
     __shared__ uint32_t tmem_base;
+    __shared__ int s_ok;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t bytesA = (uint32_t)a.nchunks * a.rowsA * 16, bytesB = (uint32_t)a.nchunks * a.N * 16;
     uint8_t *sAhi = sm, *sAlo = sAhi + bytesA, *sBhi = sAlo + bytesA, *sBlo = sBhi + bytesB;   // + 1 KB slack behind for the aliased rows
@@ -113,7 +114,9 @@ __global__ void __launch_bounds__(192, 1) umma_test(TestArgs a) {
         mbar_init(&bar_load, 1);
         mbar_init(&bar_mma, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        s_ok = 1;
     }
+    __syncthreads();
     if (warp == 1) tmem_alloc(&tmem_base, 512);
     tc_fence_before();
     __syncthreads();
@@ -125,9 +128,10 @@ __global__ void __launch_bounds__(192, 1) umma_test(TestArgs a) {
         bulk_g2s(sAlo, a.Alo, bytesA, &bar_load);
         bulk_g2s(sBhi, a.Bhi, bytesB, &bar_load);
         bulk_g2s(sBlo, a.Blo, bytesB, &bar_load);
-    } else if (warp == 1) {
-        bool ok = mbar_wait(&bar_load, 0);
-        __syncwarp();
+        if (!mbar_wait(&bar_load, 0)) s_ok = 0;
+    }
+    __syncthreads();
+    if (warp == 1) {
         tc_fence_after();
         if (lane == 0) {
             const uint32_t idesc = make_idesc(128, a.N);
@@ -152,29 +156,29 @@ __global__ void __launch_bounds__(192, 1) umma_test(TestArgs a) {
                 }
             }
             umma_commit(&bar_mma);
-            ok = mbar_wait(&bar_mma, 0) && ok;
+            if (!mbar_wait(&bar_mma, 0)) s_ok = 0;
             const long long t1 = clock64();
             a.clk[0] = t1 - t0;
-            a.clk[1] = ok ? 1 : -1;
         }
         __syncwarp();
-    } else {
-        const bool ok = mbar_wait(&bar_mma, 0);
-        __syncwarp();          // lanes leave the spin loop one by one; tcgen05.ld is .sync.aligned and needs the warp converged
-        tc_fence_after();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    if (threadIdx.x == 0) a.clk[1] = s_ok ? 1 : -1;
+    if (warp >= 2) {
         const int q = warp & 3, row = q * 32 + lane;
         for (int c0 = 0; c0 < a.N; c0 += 32) {
             uint32_t r[32];
             tmem_ld32(tb + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, r);
             for (int j = 0; j < 32; j++)
-                if (c0 + j < a.N) a.D[(size_t)row * a.N + c0 + j] = ok ? __uint_as_float(r[j]) : NAN;
+                if (c0 + j < a.N) a.D[(size_t)row * a.N + c0 + j] = __uint_as_float(r[j]);
         }
     }
     tc_fence_before();
     __syncthreads();
     if (warp == 1) tmem_dealloc(tb, 512);
 }
-
 
 // Staged probe with progress markers in mapped host memory: which tcgen05 step does not come back?
 //   mode bit 0: TMEM alloc / dealloc, bit 1: bulk copies, bit 2: one MMA + commit, bit 3: tcgen05.ld
@@ -286,6 +290,65 @@ __global__ void __launch_bounds__(64, 1) l2_stream(const uint8_t *buf, size_t bu
     }
 }
 
+
+// Streaming with `nissue` issuing warps (lane 0 of each), each its own ring: is the per-copy cost in the issuing thread or in the TMA unit?
+// Also measures the issue cost of one UBLKCP (clock around the instruction) and the latency of an isolated copy.
+__global__ void __launch_bounds__(256, 1) l2_stream2(const uint8_t *buf, size_t buf_bytes, uint32_t chunk, int nring, int per_warp, int nissue,
+                                                     long long *out) {
+    extern __shared__ __align__(128) uint8_t sm[];
+    __shared__ __align__(8) uint64_t bars[8][8];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) {
+        for (int w = 0; w < 8; w++)
+            for (int i = 0; i < 8; i++) mbar_init(&bars[w][i], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if (warp < nissue && lane == 0) {
+        uint8_t *ring = sm + (size_t)warp * nring * chunk;
+        const size_t per = buf_bytes / chunk;
+        size_t pos = ((size_t)blockIdx.x * 37 + warp * 101) % per;
+        // isolated copy latency and issue cost
+        long long c0 = clock64();
+        mbar_expect_tx(&bars[warp][0], chunk);
+        bulk_g2s(ring, buf + pos * chunk, chunk, &bars[warp][0]);
+        long long c1 = clock64();
+        bool ok = mbar_wait(&bars[warp][0], 0);
+        long long c2 = clock64();
+        long long issue_sum = 0;
+        const long long t0 = clock64();
+        int issued = 0, done = 0;
+        for (; issued < nring && issued < per_warp; issued++) {
+            mbar_expect_tx(&bars[warp][issued], chunk);
+            bulk_g2s(ring + (size_t)issued * chunk, buf + pos * chunk, chunk, &bars[warp][issued]);
+            pos = (pos + 1) % per;
+        }
+        while (done < per_warp && ok) {
+            const int slot = done % nring;
+            // slot 0 has already completed one phase (the isolated copy)
+            const uint32_t par = (uint32_t)(((done / nring) + (slot == 0 ? 1 : 0)) & 1);
+            ok = mbar_wait(&bars[warp][slot], par);
+            done++;
+            if (issued < per_warp) {
+                const long long i0 = clock64();
+                mbar_expect_tx(&bars[warp][slot], chunk);
+                bulk_g2s(ring + (size_t)slot * chunk, buf + pos * chunk, chunk, &bars[warp][slot]);
+                issue_sum += clock64() - i0;
+                pos = (pos + 1) % per;
+                issued++;
+            }
+        }
+        const long long t1 = clock64();
+        if (blockIdx.x == 0 || warp == 0) {
+            long long *o = out + ((size_t)blockIdx.x * 8 + warp) * 4;
+            o[0] = ok ? t1 - t0 : -1;
+            o[1] = c1 - c0;
+            o[2] = c2 - c1;
+            o[3] = issue_sum / (per_warp > nring ? per_warp - nring : 1);
+        }
+    }
+}
+
 static float bf16_round(float x) { return __bfloat162float(__float2bfloat16(x)); }
 
 int main(int argc, char **argv) {
@@ -341,11 +404,12 @@ int main(int argc, char **argv) {
 
     struct Case { int rowsA, N, K, passes, swap, split; };
     const Case cases[] = {
-        {128, 128, 128, 1, 0, 0}, {128, 128, 128, 1, 1, 0},      // descriptor reading
-        {128, 80, 256, 1, 0, 0},  {128, 80, 256, 1, 1, 0},
+        {128, 64, 64, 1, 0, 0},   {128, 64, 64, 1, 1, 0},        // descriptor reading
+        {128, 128, 128, 1, 0, 0}, {128, 128, 128, 1, 1, 0},
+        {128, 80, 128, 1, 0, 0},
         {96, 80, 256, 1, 0, 0},                                   // aliased rows
-        {128, 16, 128, 1, 0, 0},  {128, 32, 512, 1, 0, 0},  {128, 256, 64, 1, 0, 0},
-        {128, 128, 256, 3, 0, 1}, {96, 80, 512, 3, 0, 1},         // hi/lo split
+        {128, 16, 128, 1, 0, 0},  {128, 32, 256, 1, 0, 0},  {128, 256, 64, 1, 0, 0},
+        {128, 128, 64, 3, 0, 1}, {96, 80, 128, 3, 0, 1},         // hi/lo split
     };
     srand(1234);
     for (const Case &c : cases) {
@@ -380,6 +444,7 @@ int main(int argc, char **argv) {
         CK(cudaMemset(dD, 0xff, (size_t)128 * c.N * 4));
         TestArgs ta{dAhi, dAlo, dBhi, dBlo, dD, c.rowsA, c.N, nch, c.passes, c.swap, 1, dclk};
         const size_t smem = 2 * (size_t)nch * c.rowsA * 16 + 2 * (size_t)nch * c.N * 16 + 1024;
+        printf("launch rowsA=%d N=%d K=%d passes=%d swap=%d smem=%zu\n", c.rowsA, c.N, c.K, c.passes, c.swap, smem);
         umma_test<<<1, 192, smem>>>(ta);
         CK(cudaDeviceSynchronize());
         std::vector<float> D((size_t)128 * c.N);
@@ -406,7 +471,7 @@ int main(int argc, char **argv) {
 
     // ---- MMA issue rate: reps x (K = 256 -> 16 k-steps) x passes on resident operands
     {
-        const int K = 256, nch = K / 8;
+        const int K = 128, nch = K / 8;
         for (int N : {16, 32, 64, 80, 128, 256}) {
             for (int passes : {1, 3}) {
                 std::vector<__nv_bfloat16> Z((size_t)nch * 256 * 8 + 4096, __float2bfloat16(0.f));
@@ -453,6 +518,40 @@ int main(int argc, char **argv) {
             }
         }
         cudaFree(buf);
+    }
+
+    // ---- streaming, several issuing warps
+    {
+        CK(cudaFuncSetAttribute(l2_stream2, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        const size_t bytes = 16u << 20;
+        uint8_t *buf;
+        long long *dout;
+        CK(cudaMalloc(&buf, bytes));
+        CK(cudaMemset(buf, 1, bytes));
+        CK(cudaMalloc(&dout, 148 * 8 * 4 * sizeof(long long)));
+        struct Cfg { uint32_t chunk; int nring, nissue; };
+        const Cfg cfgs[] = {{2048, 8, 1}, {2048, 8, 4}, {2048, 8, 8}, {4096, 4, 1}, {4096, 8, 4}, {8192, 2, 1}, {8192, 4, 1}, {8192, 8, 1}, {8192, 4, 4},
+                            {16384, 2, 1}, {16384, 4, 1}, {16384, 4, 2}, {16384, 2, 4}, {32768, 2, 1}, {32768, 4, 1}, {32768, 2, 2}, {49152, 4, 1}, {65536, 3, 1}};
+        for (int grid : {1, 148}) {
+            for (const Cfg &c : cfgs) {
+                const int per_warp = (int)((4u << 20) / c.chunk / c.nissue);
+                const size_t smem = (size_t)c.nring * c.chunk * c.nissue;
+                if (smem > 200 * 1024) continue;
+                for (int rep = 0; rep < 2; rep++) {
+                    CK(cudaMemset(dout, 0, 148 * 8 * 4 * sizeof(long long)));
+                    l2_stream2<<<grid, 256, smem>>>(buf, bytes, c.chunk, c.nring, per_warp, c.nissue, dout);
+                    CK(cudaDeviceSynchronize());
+                }
+                std::vector<long long> o((size_t)grid * 8 * 4);
+                CK(cudaMemcpy(o.data(), dout, o.size() * sizeof(long long), cudaMemcpyDeviceToHost));
+                long long mx = 0;
+                for (int b = 0; b < grid; b++) mx = o[(size_t)b * 32] > mx ? o[(size_t)b * 32] : mx;
+                printf("l2 stream2 grid=%3d chunk=%5u ring=%d issuers=%d: %.1f B/clk/SM, %.0f clk per copy per issuer; isolated copy: issue %lld clk, latency %lld clk; steady issue %lld clk\n",
+                       grid, c.chunk, c.nring, c.nissue, (double)per_warp * c.nissue * c.chunk / mx, (double)mx / per_warp, o[1], o[2], o[3]);
+            }
+        }
+        cudaFree(buf);
+        cudaFree(dout);
     }
     printf("done\n");
     return 0;

@@ -10,6 +10,7 @@ if ROOT not in sys.path:
 
 def pytest_configure(config):
     config.addinivalue_line('markers', 'gpu: needs a CUDA device (run on the B200 box)')
+    config.addinivalue_line('markers', 'slow: full-size parity cases that run the CPU oracle for seconds to minutes')
 
 
 def _have_gpu():

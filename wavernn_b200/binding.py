@@ -63,6 +63,7 @@ _SIGS = {
     'wrnn_loop_kernel_name': (C.c_char_p, [_P, C.c_int64]),
     'wrnn_set_loop_kernel': (C.c_int, [_P, C.c_int32]),
     'wrnn_set_mma_fold_tile': (C.c_int, [_P, C.c_int32]),
+    'wrnn_debug_mma_state': (C.c_int, [_P, C.c_int32, C.c_int64, _P]),
     'wrnn_dm_create': (C.c_int, [C.c_int32, C.c_int32, C.c_int, C.POINTER(_P)]),
     'wrnn_dm_destroy': (None, [_P]),
     'wrnn_dm_last_error': (C.c_char_p, [_P]),
@@ -252,6 +253,11 @@ class Vocoder:
     def set_loop_kernel(self, which):
         """0 auto, 1 fma, 2 fma-pipelined, 4 tcgen05-bf16x3 (tensor cores; auto from 48 folds up)."""
         self._ck(lib().wrnn_set_loop_kernel(self._h, int(which)))
+
+    def debug_mma_state(self, which, folds):
+        out = np.empty((folds, 512), dtype=np.float32)
+        self._ck(lib().wrnn_debug_mma_state(self._h, int(which), int(folds), _ptr(out)))
+        return out
 
     def set_mma_fold_tile(self, nt):
         self._ck(lib().wrnn_set_mma_fold_tile(self._h, int(nt)))

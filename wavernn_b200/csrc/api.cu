@@ -67,6 +67,7 @@ int loop_kernel_choice(const wrnn_handle *h, int64_t folds) {
     if (f == 0 && mma_supported(h) && folds >= mma_min_folds()) return 4;
     if (f == 1) return 1;
     if (f == 2) return pipe_supported(h) ? 2 : 1;
+    if (f == 3 && res_supported(h)) return 3;
     if (res_supported(h)) return 3;
     if (pipe_supported(h)) return 2;
     return 1;
@@ -138,7 +139,7 @@ void wrnn_destroy(wrnn_handle *h) {
     if (!h) return;
     DeviceGuard guard(h->device);
     Workspace *all[] = {&h->ws_mel, &h->ws_up, &h->ws_res, &h->ws_cond, &h->ws_samples, &h->ws_picks, &h->ws_out,
-                        &h->ws_noise, &h->ws_meta, &h->ws_tables, &h->ws_sync, &h->ws_act, &h->ws_tmp0, &h->ws_tmp1,
+                        &h->ws_noise, &h->ws_meta, &h->ws_tables, &h->ws_sync, &h->ws_mma_sync, &h->ws_act, &h->ws_tmp0, &h->ws_tmp1,
                         &h->ws_teacher, &h->ws_logits, &h->ws_prof};
     for (Workspace *w : all)
         if (w->p) cudaFree(w->p);
@@ -229,6 +230,15 @@ const char *wrnn_loop_kernel_name(wrnn_handle *h, int64_t folds) {
 int wrnn_set_loop_kernel(wrnn_handle *h, int32_t which) {
     if (!h) return WRNN_ERR_ARG;
     h->force_kernel = which;
+    return 0;
+}
+
+int wrnn_debug_mma_state(wrnn_handle *h, int32_t which, int64_t folds, float *out) {
+    if (!h || !out || which < 0 || which > 2 || folds < 1) return fail(h, WRNN_ERR_ARG, "bad argument");
+    if (!h->mma_dbg[which]) return fail(h, WRNN_ERR_STATE, "no tensor-core run yet");
+    WRNN_DEVICE(h);
+    WRNN_CUDA(h, cudaDeviceSynchronize());
+    WRNN_CUDA(h, cudaMemcpy(out, h->mma_dbg[which], (size_t)folds * 512 * sizeof(float), cudaMemcpyDeviceToHost));
     return 0;
 }
 

@@ -108,6 +108,7 @@ struct wrnn_handle {
     wrnn::PipePlan pipe;
     wrnn::ResPlan res;
     wrnn::MmaPlan mma;
+    float *mma_dbg[3] = {nullptr, nullptr, nullptr};   // h1, h2, fc2 output [folds][512] fp32 of the last tensor-core run
     int mma_force_nt = 0;              // debug / tests: fold-tile width of the tensor-core kernel (0 = auto)
     int force_kernel = 0;
     std::vector<double> lut_override;   // host-supplied mu-law table (wrnn_set_mulaw_lut)
@@ -122,7 +123,7 @@ struct wrnn_handle {
     bool have_noise = false;
 
     wrnn::Workspace ws_mel, ws_up, ws_res, ws_cond, ws_samples, ws_picks, ws_out, ws_noise,
-        ws_meta, ws_tables, ws_sync, ws_act, ws_tmp0, ws_tmp1, ws_teacher, ws_logits, ws_prof;
+        ws_meta, ws_tables, ws_sync, ws_mma_sync, ws_act, ws_tmp0, ws_tmp1, ws_teacher, ws_logits, ws_prof;
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
     int64_t launches = 0;
     double *h_pinned_out = nullptr;

@@ -26,8 +26,10 @@
 // (TMEM -> registers -> shared staging -> gates -> global operands) and the FFMA phase.
 #include <cuda_bf16.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
+#include <algorithm>
 #include <vector>
 
 #include "internal.h"
@@ -77,6 +79,7 @@ __host__ __device__ inline StageInfo stage_info(int p, int s) {
 struct Params {
     LoopArgs a;
     int NT, NTILES, G, NC;
+    int64_t steps_run;             // == a.S except under WRNN_MMA_STEPS (bring-up: stop after n steps and inspect the state)
     const uint8_t *Aimg;           // packed weights: phase p at offA[p], [row tile][stage][hi|lo][KC][rows][8] bf16
     int64_t offA[4];
     const float *bias;             // P1: [16][2][96] | P2: [16][2][96] | P3: [512] | P4: [512]
@@ -107,7 +110,10 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t by
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(b)) : "memory");
 }
-__device__ __forceinline__ void fence_proxy_async_global() { asm volatile("fence.proxy.async.global;" ::: "memory"); }
+// generic-proxy writes (st.global by the epilogue threads) are read by the TMA unit (async proxy) of other SMs: EVERY writing
+// thread orders its own stores against the async proxy before the CTA publishes the phase, and the producer thread does the
+// same after it has acquired the grid counter (the pattern of a TMA store after generic smem writes, applied to global)
+__device__ __forceinline__ void fence_proxy_async_global() { asm volatile("fence.proxy.async;" ::: "memory"); }
 __device__ __forceinline__ void tmem_alloc(uint32_t *dst_smem, uint32_t ncols) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "r"(ncols) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
@@ -166,11 +172,18 @@ __device__ __forceinline__ void mbar_wait(void *b, uint32_t parity, Watch &w) {
     while (!mbar_try_wait(b, parity))
         if (give_up(w, t0, spins)) return;
 }
-__device__ __forceinline__ void grid_wait(const GridSync &gs, unsigned long long want, Watch &w) {
+// Split-phase grid barrier, ONE MONOTONIC COUNTER PER PHASE of the step (five, each on its own 128-byte line): a CTA
+// that has no job in a phase publishes it at once and runs ahead to the next thing it has to wait for, so a single
+// counter summed over phases would reach "G arrivals" before every CTA has finished the phase in question.  Per phase,
+// counter[p] >= G * (t + 1) does mean that every CTA has published phase p of step t: no CTA can publish phase p of
+// step t + 1 before it has passed the fc3 phase of step t, which waits for everybody's fc2 phase of step t.
+__device__ __forceinline__ unsigned long long *phase_counter(const GridSync &gs, int p) { return gs.counter + 16 * (p + 1); }
+__device__ __forceinline__ void grid_wait(const GridSync &gs, int p, unsigned long long want, Watch &w) {
     if (w.dead) return;
     const long long t0 = clock64();
     unsigned spins = 0;
-    while (ld_acquire_u64(gs.counter) < want)
+    const unsigned long long *c = phase_counter(gs, p);
+    while (ld_acquire_u64(c) < want)
         if (give_up(w, t0, spins)) return;
 }
 __device__ __forceinline__ void epi_bar() { bar_sync(1, EPI_THREADS); }
@@ -302,14 +315,16 @@ __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
         // ======================================================================= TMA producer
         if (lane == 0) {
             uint32_t it = 0;
-            for (int64_t t = 0; t < S && !w.dead; t++) {
+            for (int64_t t = 0; t < P.steps_run && !w.dead; t++) {
                 for (int p = 0; p < 4; p++) {
                     const int ntiles = phase_tiles(P, p), nst = phase_stages(p);
                     const uint32_t abytes = 2u * KC * (p < 2 ? GRU_ROWS : FC_ROWS) * 16u, bbytes = 2u * KC * NT * 16u;
                     bool waited = false;
                     for (int id = first_job(P, p, cta); id < ntiles; id += G) {
                         if (!waited) {     // this phase's operands were written by phase q-1 of every CTA
-                            grid_wait(P.gs, (unsigned long long)G * (unsigned long long)(1 + 5 * t + p), w);
+                            // phase p reads what phase p - 1 of this step wrote (rnn1: what the fc3 phase of the step before,
+                            // or the prologue, wrote: both publish on counter 4)
+                            grid_wait(P.gs, p == 0 ? 4 : p - 1, (unsigned long long)G * (unsigned long long)(t + 1), w);
                             fence_proxy_async_global();
                             waited = true;
                         }
@@ -335,11 +350,16 @@ __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
         if (lane == 0) {
             uint32_t it = 0, j = 0;
             const uint32_t idesc = make_idesc(128, NT);
-            for (int64_t t = 0; t < S && !w.dead; t++) {
+            const uint32_t stage0 = smem_u32(stages);
+            for (int64_t t = 0; t < P.steps_run && !w.dead; t++) {
                 for (int p = 0; p < 4; p++) {
                     const int ntiles = phase_tiles(P, p), nst = phase_stages(p);
                     const uint32_t rows = p < 2 ? GRU_ROWS : FC_ROWS;
-                    const uint32_t lboA = rows * 16u, lboB = (uint32_t)NT * 16u;
+                    // descriptors differ only in the 14-bit start-address field (16-byte units): build the constant part once
+                    // per phase and add slot / k-step offsets, so that issuing a k-step is a handful of integer instructions
+                    const uint64_t dA0 = make_desc(0, rows * 16u, 128), dB0 = make_desc(0, (uint32_t)NT * 16u, 128);
+                    const uint32_t stepA = 2u * rows, stepB = 2u * (uint32_t)NT;          // two k-chunks, in 16-byte units
+                    const uint32_t loA = KC * rows, loB = KC * (uint32_t)NT;               // hi -> lo image
                     for (int id = first_job(P, p, cta); id < ntiles; id += G, j++) {
                         const uint32_t buf = j & 1;
                         mbar_wait(&bar_tempty[buf], ((j >> 1) & 1) ^ 1, w);
@@ -350,13 +370,11 @@ __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
                             tc_fence_after();
                             const StageInfo si = stage_info(p, s);
                             const uint32_t d = tb + buf * 256u + (uint32_t)si.acc * (uint32_t)NT;
-                            const uint32_t sA = smem_u32(stages + (size_t)slot * STAGE_BYTES), sB = sA + A_STAGE;
+                            const uint32_t aA = (stage0 + (uint32_t)slot * STAGE_BYTES) >> 4, aB = aA + (A_STAGE >> 4);
 #pragma unroll
                             for (int ks = 0; ks < KC / 2; ks++) {
-                                const uint64_t ah = make_desc(sA + ks * 2 * lboA, lboA, 128);
-                                const uint64_t al = make_desc(sA + KC * lboA + ks * 2 * lboA, lboA, 128);
-                                const uint64_t bh = make_desc(sB + ks * 2 * lboB, lboB, 128);
-                                const uint64_t bl = make_desc(sB + KC * lboB + ks * 2 * lboB, lboB, 128);
+                                const uint64_t ah = dA0 + (aA + ks * stepA), al = dA0 + (aA + loA + ks * stepA);
+                                const uint64_t bh = dB0 + (aB + ks * stepB), bl = dB0 + (aB + loB + ks * stepB);
                                 umma_bf16(d, ah, bh, idesc, (si.first && ks == 0) ? 0u : 1u);
                                 umma_bf16(d, ah, bl, idesc, 1u);
                                 umma_bf16(d, al, bh, idesc, 1u);
@@ -381,11 +399,12 @@ __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
             const float x0 = P.a.teacher ? P.a.teacher[(size_t)b * S] : 0.f;
             write_cond_operand(P, b, 0, x0, myscr, lane);
         }
+        fence_proxy_async_global();
         epi_bar();
-        if (etid == 0) { fence_proxy_async_global(); red_release_add_u64(P.gs.counter, 1ull); }
+        if (etid == 0) { fence_proxy_async_global(); red_release_add_u64(phase_counter(P.gs, 4), 1ull); }
 
         uint32_t j = 0;
-        for (int64_t t = 0; t < S; t++) {
+        for (int64_t t = 0; t < P.steps_run; t++) {
             if (w.dead) break;                               // uniform: set below from a flag read after a barrier
             for (int p = 0; p < 4; p++) {
                 const int ntiles = phase_tiles(P, p);
@@ -489,12 +508,13 @@ __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
                     epi_bar();
                     if (etid == 0) mbar_arrive(&bar_tempty[buf]);        // TMEM buffer drained
                 }
-                // phase q = 1 + 5t + p finished by this CTA: publish
+                // phase p of step t finished by this CTA: publish
+                fence_proxy_async_global();
                 epi_bar();
-                if (etid == 0) { fence_proxy_async_global(); red_release_add_u64(P.gs.counter, 1ull); }
+                if (etid == 0) { fence_proxy_async_global(); red_release_add_u64(phase_counter(P.gs, p), 1ull); }
             }
             // ---------------- fc3 (:223) in fp32 + MoL draw (utils/distribution.py:87-123) + next conditioning operand
-            if (etid == 0) grid_wait(P.gs, (unsigned long long)G * (unsigned long long)(1 + 5 * t + 4), w);
+            if (etid == 0) grid_wait(P.gs, 3, (unsigned long long)G * (unsigned long long)(t + 1), w);
             epi_bar();
             for (int64_t b = cta + (int64_t)G * ewarp; b < B; b += (int64_t)G * EPI_WARPS) {
                 float4 y[4];
@@ -544,8 +564,9 @@ __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
                 if (P.a.teacher) xv = t + 1 < S ? P.a.teacher[(size_t)b * S + t + 1] : 0.f;
                 write_cond_operand(P, b, t + 1, xv, myscr, lane);
             }
+            fence_proxy_async_global();
             epi_bar();
-            if (etid == 0) { fence_proxy_async_global(); red_release_add_u64(P.gs.counter, 1ull); }
+            if (etid == 0) { fence_proxy_async_global(); red_release_add_u64(phase_counter(P.gs, 4), 1ull); }
             // uniform exit on a fired watchdog
             if (etid == 0) stg[0] = (w.dead || ld_volatile_s32(P.gs.abort_flag)) ? 1.f : 0.f;
             epi_bar();
@@ -727,6 +748,8 @@ int mma_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
     P.NT = h->mma_force_nt > 0 ? h->mma_force_nt : mma_pick_nt(a.B, P.G);
     P.NTILES = (int)((a.B + P.NT - 1) / P.NT);
     P.NC = h->d.NC;
+    P.steps_run = a.S;
+    if (const char *e = getenv("WRNN_MMA_STEPS")) P.steps_run = std::min<int64_t>(a.S, std::max(1, atoi(e)));
     P.Aimg = pl.Aimg;
     for (int p = 0; p < 4; p++) P.offA[p] = pl.offA[p];
     P.bias = pl.bias;
@@ -743,10 +766,11 @@ int mma_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
     P.S12 = p8; p8 += bH; P.Y1 = p8; p8 += bH;
     P.C = p8; p8 += (bC + 1023) / 1024 * 1024;
     P.h1f = (float *)p8; p8 += bF; P.h2f = (float *)p8; p8 += bF; P.y2f = (float *)p8;
-    WRNN_TRY(ws_reserve(h, h->ws_sync, 128));
-    WRNN_CUDA(h, cudaMemsetAsync(h->ws_sync.p, 0, 16, st));
-    P.gs.counter = (unsigned long long *)h->ws_sync.p;
-    P.gs.abort_flag = (int *)((char *)h->ws_sync.p + 64);
+    h->mma_dbg[0] = P.h1f; h->mma_dbg[1] = P.h2f; h->mma_dbg[2] = P.y2f;
+    WRNN_TRY(ws_reserve(h, h->ws_mma_sync, 1024));                    // five phase counters, 128 bytes apart, from +128
+    WRNN_CUDA(h, cudaMemsetAsync(h->ws_mma_sync.p, 0, 1024, st));
+    P.gs.counter = (unsigned long long *)h->ws_mma_sync.p;
+    P.gs.abort_flag = (int *)((char *)h->ws_sync.p + 64);             // the call's sticky abort flag (api_run.cu)
     WRNN_CUDA(h, cudaFuncSetAttribute(mma_loop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes));
     void *args[] = {(void *)&P};
     WRNN_CUDA(h, cudaLaunchCooperativeKernel((const void *)mma_loop_kernel, dim3(P.G), dim3(THREADS), args, pl.smem_bytes, st));
