@@ -1,20 +1,25 @@
 #!/usr/bin/env python
-"""Benchmark of the WaveRNN batched generation path (BASELINE.json configs[1]).
+"""Benchmark of the WaveRNN batched generation path (BASELINE.json: generated audio samples/s per B200 and whole box).
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
 
-A "step" is one full `generate` of the workload: fatchord WaveRNN MoL (rnn 512, fc 512, hop 275),
-batched target=11000 overlap=550 on a synthetic 10 s mel (T=801 -> 20 folds x 12100 loop steps ->
-220 000 samples), one utterance per GPU (weak scaling, no collective on the path).
-  value : samples/s, device time (CUDA events) of stage-resident runs: conditioning + fold +
-          per-sample loop + float64 tail, inputs already in HBM.
-  e2e   : samples/s through the public host call (wrnn_generate via ctypes): host mel in, host
-          float64 waveform out, copies inside the timed region.
-  roofline : the per-sample loop kernel, algorithmic weight bytes per loop step (15 331 448 B, fp32
-          MoL model) x steps / kernel time, against measured HBM bandwidth.
-  cpu_baseline : the oracle port (torch-CPU restatement of the reference loop) on a bounded sample.
+A "step" is one full `generate` of the workload.  The headline workload (`value`, `e2e`) is BASELINE.json configs[1]:
+fatchord WaveRNN MoL (rnn 512, fc 512, hop 275), batched target=11000 overlap=550 on a synthetic 10 s mel
+(T=801 -> 20 folds x 12100 loop steps -> 220 000 samples), one utterance per GPU (weak scaling, no collective on the path).
+  value : samples/s, device time (CUDA events) of stage-resident runs: conditioning + fold + per-sample loop + float64
+          tail, inputs already in HBM.
+  e2e   : samples/s through the public host call (wrnn_generate via ctypes): host mel in, host float64 waveform out,
+          copies inside the timed region.
+  roofline : the per-sample loop kernel of that workload: algorithmic weight bytes per loop step (15 331 448 B, fp32 MoL
+          model) x steps / kernel time against measured HBM bandwidth, PLUS what actually binds
+          the register-resident kernel: the exchange-latency floor and the fraction of it reached.
+  config5 : the same line carries a second record, BASELINE.json configs[4] per GPU: 32 utterances of T=801 in ONE
+          call (640 folds x 12100 steps; 256 utterances on 8 GPUs), through the tensor-core loop kernel (tcgen05, bf16
+          hi/lo operands), with its own value / e2e / roofline (bound: tensor, against the measured sustained bf16 rate).
+  cpu_baseline : the reference's own un-patched generate() (staged copy, oracle/_ref) on the host cores, whole utterance.
 """
 import argparse
+import glob
 import json
 import os
 import subprocess
@@ -28,24 +33,42 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 T_FRAMES, TARGET, OVERLAP = 801, 11000, 550
-WEIGHT_BYTES_PER_STEP = 15_331_448        # SURVEY.md §8(d): 3 825 152 matrix + 7 710 bias fp32 elements
-# dram__bytes_read.sum + dram__bytes_write.sum of one res_loop_kernel launch (12100 steps), ncu --set full
-NCU_DRAM_BYTES_PER_LAUNCH = 223_707_136 + 6_333_440
-NCU_SOURCE = 'profiles/r01h_resident_loop_ncu.txt'
+WEIGHT_BYTES_PER_STEP = 15_331_448        # SURVEY.md section 8(d): 3 825 152 matrix + 7 710 bias fp32 elements
+FLOP_PER_FOLD_STEP = 7_650_304            # 2 x matrix elements (MoL)
+CONFIG5_UTTERANCES = 32                   # per GPU: 256 utterances on the 8-GPU box
 SAMPLE_RATE = 22050
 METRIC = 'generated audio samples/sec'
-CPU_SAMPLE_STEPS = 2000                   # --impl reference: loop steps (x20 folds) per timed step (~2.5 s of CPU work each)
-CPU_BASELINE_STEPS = 12100                # cpu_baseline leg of our arm: up to the whole utterance, sized for ~15 s of CPU work
+# Exchange-latency floor of the resident kernel (measured with scripts/microbench*.cu on B200,
+# profiles/r01_microbench_b200.txt): a step is five dependent L2 exchanges of ~2 400 clocks each (including the delayed
+# first look) plus the fp32 FMA floor of the four products on the chain (153 MFLOP at 20 folds on 128 SMs = 3 900 clocks).
+EXCHANGE_CLOCKS, EXCHANGES_PER_STEP, FMA_FLOOR_CLOCKS = 2400, 5, 3900
+
+
+def loop_traffic(kernel):
+    """DRAM bytes per launch of the loop kernel that ran, from the newest ncu capture summary under profiles/
+    (`profiles/*_traffic.json`: {"kernel name": {"dram_bytes_per_launch": ..., "source": ...}}); None when that kernel
+    has no capture at this HEAD."""
+    best = None
+    for path in sorted(glob.glob(os.path.join(ROOT, 'profiles', '*_traffic.json'))):
+        try:
+            d = json.load(open(path))
+        except Exception:
+            continue
+        if kernel in d:
+            best = dict(d[kernel], file=os.path.relpath(path, ROOT))
+    return best
 
 
 def measured_peaks():
+    """-> (hbm GB/s, bf16 sustained TFLOP/s, source)."""
     p = os.path.join(ROOT, 'MEASURED_PEAKS.json')
     if os.path.isfile(p):
         try:
-            return float(json.load(open(p))['hbm_gbs']), 'measured (MEASURED_PEAKS.json)'
+            d = json.load(open(p))
+            return float(d['hbm_gbs']), float(d.get('bf16_tflops_sustained', d['bf16_tflops'])), 'measured (MEASURED_PEAKS.json)'
         except Exception:
             pass
-    return 6650.0, 'fallback (B200_PROFILING.md)'
+    return 6650.0, 1400.0, 'fallback (B200_PROFILING.md)'
 
 
 class ClockSampler:
@@ -177,6 +200,71 @@ def run_reference(args):
         'gpu_launches': 0}))
 
 
+def run_config5(args, voc, dims, rank, world, stream, flush, barrier):
+    """BASELINE.json configs[4], one GPU's share: 32 utterances of T=801 (seed 1234 + global utterance index) in ONE
+    generate call = 640 folds x 12100 steps through the tensor-core loop kernel.  Same protocol as the headline record:
+    device-timed runs with inputs resident, then end-to-end calls with host buffers."""
+    import torch
+    from wavernn_b200 import synth
+    from wavernn_b200.shard import whole_job_rate
+    n_utt = CONFIG5_UTTERANCES
+    mels = [synth.synth_mel(T_FRAMES, seed=1234 + rank * n_utt + u)[0] for u in range(n_utt)]
+    wave_len = (T_FRAMES - 1) * dims.hop_length
+    k = max(1, min(args.steps, 3))
+    voc.stage(mels, True, TARGET, OVERLAP, False, stream=stream)
+    voc.run_staged(seed=50, stream=stream)                       # warm-up (weights / workspaces already packed)
+    torch.cuda.synchronize()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(k)]
+    loop_ms, launches = [], 0
+    barrier()
+    for i in range(k):
+        flush.fill_(i & 0xff)
+        ev[i][0].record()
+        voc.run_staged(seed=500 + i, stream=stream)
+        ev[i][1].record()
+        ev[i][1].synchronize()
+        t = voc.last_timing()
+        loop_ms.append(t['ms_loop'])
+        launches += t['launches']
+    barrier()
+    dev_ms = sum(a.elapsed_time(b) for a, b in ev)
+    waves = voc.fetch(stream=stream)
+    assert len(waves) == n_utt and all(w.shape == (wave_len,) and np.all(np.isfinite(w)) for w in waves)
+    voc.generate(mels, True, TARGET, OVERLAP, False, seed=3, stream=stream)
+    barrier()
+    t0 = time.time()
+    for i in range(k):
+        voc.generate(mels, True, TARGET, OVERLAP, False, seed=600 + i, stream=stream)
+    barrier()
+    e2e_s = time.time() - t0
+    value, (dev_ms_max, e2e_ms_max) = whole_job_rate(n_utt * wave_len * k, [dev_ms, e2e_s * 1000.0], device='cuda')
+    if rank != 0:
+        return None
+    k_ms = float(np.mean(loop_ms))
+    fold_steps = t['folds'] * t['steps'] / (k_ms * 1e-3)
+    kernel = voc.loop_kernel_name(t['folds'])
+    traffic = loop_traffic(kernel)
+    return {
+        'workload': f'{n_utt} utterances per GPU (= {n_utt * world} in the job), each a synthetic 10 s mel T=801, one batched '
+                    f'generate call: {t["folds"]} folds x {t["steps"]} steps per GPU',
+        'value': value, 'unit': 'samples/s', 'rtf': value / SAMPLE_RATE, 'steps': k, 'ms_per_step': dev_ms_max / k,
+        'e2e': {'value': n_utt * wave_len * k * world / (e2e_ms_max / 1000.0), 'unit': 'samples/s',
+                'h2d_bytes_per_step': int(sum(m.nbytes for m in mels)), 'd2h_bytes_per_step': int(n_utt * wave_len * 8),
+                'ms_per_step': e2e_ms_max / k},
+        'loop': {'kernel': kernel, 'ms': k_ms, 'us_per_step': 1000 * k_ms / t['steps'], 'folds': t['folds'], 'steps': t['steps'],
+                 'ms_cond': t['ms_cond'], 'ms_tail': t['ms_tail'], 'fold_steps_per_s': fold_steps,
+                 'fold_steps_per_s_resident_groups_r01': 1.75e6},
+        'dtype': 'bf16 hi+lo split operands (3 MMAs per product), fp32 accumulate in TMEM; fc3 + sampling fp32',
+        'roofline': {'bound': 'tensor', 'achieved': FLOP_PER_FOLD_STEP * fold_steps / 1e12, 'unit': 'TFLOP/s',
+                     'algorithmic_flop_per_fold_step': FLOP_PER_FOLD_STEP,
+                     'executed_flop_factor': 'x3 for the hi/lo split, x1.33 for the 96-of-128-row GRU tiles',
+                     'traffic': traffic['dram_bytes_per_launch'] if traffic else None,
+                     'traffic_source': (traffic['source'] + ' via ' + traffic['file']) if traffic else
+                     'no ncu capture of this kernel under profiles/ at this HEAD'},
+        'launches': launches,
+    }
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -228,6 +316,8 @@ def run_ours(args):
         launches += t['launches']
     barrier()
     t_wall = time.time() - t_wall
+    folds_loop, steps_loop = t['folds'], t['steps']
+    loop_kernel = voc.loop_kernel_name(folds_loop)
     dev_ms = sum(a.elapsed_time(b) for a, b in ev)
     clocks = sampler.stop() if rank == 0 else None
     wave = voc.fetch(stream=stream)[0]
@@ -243,15 +333,25 @@ def run_ours(args):
     barrier()
     e2e_s = time.time() - t0
 
+    # ---------------- config 5 per GPU: 32 utterances in one call, tensor-core loop kernel ----------------
+    c5 = None
+    if not args.no_config5:
+        c5 = run_config5(args, voc, dims, rank, world, stream, flush, barrier)
+
     # whole-job rate: samples of all ranks over the slowest rank's time (wavernn_b200/shard.py, gloo-tested on CPU)
     value, (dev_ms_max, e2e_ms_max) = whole_job_rate(wave_len * args.steps, [dev_ms, e2e_s * 1000.0], device='cuda')
     total_samples = wave_len * args.steps * world
     e2e = total_samples / (e2e_ms_max / 1000.0)
     if rank == 0:
-        peak, peak_src = measured_peaks()
-        t = voc.last_timing()
+        hbm, bf16, peak_src = measured_peaks()
+        t_last = t
         k_ms = float(np.mean(loop_ms))
-        achieved = WEIGHT_BYTES_PER_STEP * t['steps'] / (k_ms * 1e-3) / 1e9
+        kernel = loop_kernel
+        us_step = 1000 * k_ms / steps_loop
+        achieved = WEIGHT_BYTES_PER_STEP * steps_loop / (k_ms * 1e-3) / 1e9
+        sm_mhz = (clocks or {}).get('sm_mhz') or 1965.0
+        floor_us = (EXCHANGES_PER_STEP * EXCHANGE_CLOCKS + FMA_FLOOR_CLOCKS) / sm_mhz
+        traffic = loop_traffic(kernel)
         line = {
             'metric': METRIC, 'value': value, 'unit': 'samples/s', 'rtf': value / SAMPLE_RATE / world,
             'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': dev_ms_max / args.steps,
@@ -260,27 +360,40 @@ def run_ours(args):
             'e2e': {'value': e2e, 'unit': 'samples/s', 'rtf_per_gpu': e2e / SAMPLE_RATE / world,
                     'h2d_bytes_per_step': int(mel[0].nbytes), 'd2h_bytes_per_step': int(wave_len * 8),
                     'ms_per_step': e2e_ms_max / args.steps},
-            'gpu_launches': int(launches),
-            'loop': {'kernel': voc.loop_kernel_name(t['folds']), 'ms': k_ms, 'us_per_step': 1000 * k_ms / t['steps'],
-                     'folds': t['folds'], 'steps': t['steps'], 'ms_cond': t['ms_cond'], 'ms_tail': t['ms_tail'],
-                     'fold_steps_per_s': t['folds'] * t['steps'] / (k_ms * 1e-3)},
-            'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
-                         'traffic': NCU_DRAM_BYTES_PER_LAUNCH, 'traffic_unit': 'bytes per launch of the loop kernel',
-                         'traffic_source': NCU_SOURCE,
-                         'algorithmic_bytes_per_launch': WEIGHT_BYTES_PER_STEP * t['steps'], 'peak_source': peak_src,
-                         'note': 'algorithmic = fp32 weight bytes re-read once per loop step; the weights are '
-                                 'register-resident, so measured DRAM traffic is ~0.2 % of that (conditioning rows) and '
-                                 'the loop is bound by L2 round trips and the LSU pipe, not HBM'},
+            'gpu_launches': int(launches) + (c5['launches'] if c5 else 0),
+            'loop': {'kernel': kernel, 'ms': k_ms, 'us_per_step': us_step,
+                     'folds': folds_loop, 'steps': steps_loop, 'ms_cond': t_last['ms_cond'], 'ms_tail': t_last['ms_tail'],
+                     'fold_steps_per_s': folds_loop * steps_loop / (k_ms * 1e-3)},
+            'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': hbm, 'unit': 'GB/s', 'frac': achieved / hbm,
+                         'traffic': traffic['dram_bytes_per_launch'] if traffic else None,
+                         'traffic_source': (traffic['source'] + ' via ' + traffic['file']) if traffic else
+                         'no ncu capture of this kernel under profiles/ at this HEAD',
+                         'algorithmic_bytes_per_launch': WEIGHT_BYTES_PER_STEP * steps_loop, 'peak_source': peak_src,
+                         'binding_limit': 'exchange latency (five dependent L2 exchanges per step), then the LSU pipe',
+                         'latency_floor_us': floor_us, 'frac_of_floor': floor_us / us_step,
+                         'latency_floor': f'{EXCHANGES_PER_STEP} exchanges x {EXCHANGE_CLOCKS} clk + {FMA_FLOOR_CLOCKS} clk fp32 FMA '
+                                          f'floor at {sm_mhz:.0f} MHz (DESIGN.md 4.1, profiles/r01_microbench_b200.txt)',
+                         'fp32_fma_frac': folds_loop * FLOP_PER_FOLD_STEP / (us_step * 1e-6) / (148 * 128 * 2 * sm_mhz * 1e6),
+                         'note': 'algorithmic = fp32 weight bytes re-read once per loop step; the weights are register-resident, '
+                                 'so DRAM traffic is the conditioning rows only and HBM does not bind: frac_of_floor is the '
+                                 'figure that says how close the kernel is to what bounds it'},
             'clocks': clocks, 'wall_s_value_leg': t_wall,
         }
+        if c5:
+            c5.pop('launches', None)
+            c5['roofline']['peak'] = bf16
+            c5['roofline']['frac'] = c5['roofline']['achieved'] / bf16
+            c5['roofline']['peak_source'] = peak_src + ' bf16_tflops_sustained'
+            line['config5'] = c5
         if world == 1 and not args.no_cpu:
             threads = os.cpu_count() or 1
-            _, dt0 = cpu_port_rate(dims, sd, mel, 100, threads)                 # probe, then size the sample for ~15 s
-            n_cpu = int(min(CPU_BASELINE_STEPS, max(200, 100 * 15.0 / max(dt0, 1e-3))))
-            v, dt = cpu_port_rate(dims, sd, mel, n_cpu, threads)
-            line['cpu_baseline'] = {'value': v, 'unit': 'samples/s', 'cores': threads, 'kind': 'port',
-                                    'sample': f'conditioning + first {n_cpu} of 12100 loop steps at 20 folds '
-                                              f'({dt:.1f} s of CPU work), scaled to samples/s'}
+            from wavernn_b200 import synth
+            cpu_generate(dims, sd, synth.synth_mel(41, seed=7), threads, target=1100, overlap=550)     # warm-up
+            runs = [cpu_generate(dims, sd, mel, threads) for _ in range(2)]
+            v = float(np.median([r[0] for r in runs]))
+            line['cpu_baseline'] = {'value': v, 'unit': 'samples/s', 'cores': threads, 'kind': runs[0][2],
+                                    'sample': 'whole utterance, twice (median): conditioning + 12100 of 12100 loop steps at 20 '
+                                              f'folds + unfold ({sum(r[1] for r in runs):.1f} s of CPU work)'}
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
@@ -293,6 +406,7 @@ def main():
     ap.add_argument('--warmup', type=int, default=3)
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
     ap.add_argument('--no-cpu', action='store_true', help='skip the cpu_baseline leg')
+    ap.add_argument('--no-config5', action='store_true', help='skip the 32-utterance record')
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == 'ours' else args.warmup
     if args.impl == 'reference':

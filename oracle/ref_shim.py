@@ -73,6 +73,29 @@ def load():
     return _loaded
 
 
+def load_gen_wavernn():
+    """The reference's CLI module `gen_wavernn.py` (its `gen_from_file` / `gen_testset` are the callers of the
+    drop-in boundary), imported un-modified; its `save_wav` for the target file is a no-op."""
+    load()
+    # gen_wavernn imports utils.dataset -> utils.text (Tacotron's text front end, not on the path), which wants
+    # `unidecode` and `inflect`: absent here, stubbed like matplotlib / librosa
+    if 'unidecode' not in sys.modules:
+        m = types.ModuleType('unidecode')
+        m.unidecode = lambda s: s
+        sys.modules['unidecode'] = m
+    if 'inflect' not in sys.modules:
+        m = types.ModuleType('inflect')
+        m.engine = lambda: types.SimpleNamespace(number_to_words=lambda *a, **k: '')
+        sys.modules['inflect'] = m
+    sys.path.insert(0, REF_ROOT)
+    try:
+        import gen_wavernn as gw
+    finally:
+        sys.path.remove(REF_ROOT)
+    gw.save_wav = lambda x, path: None
+    return gw
+
+
 def build_fatchord(dims, state_dict_np):
     """Reference `WaveRNN(**dims)` on CPU with the given checkpoint loaded (strict)."""
     import contextlib

@@ -23,6 +23,9 @@ FILES = [
     'models/__init__.py', 'models/fatchord_version.py', 'models/deepmind_version.py',
     'utils/__init__.py', 'utils/distribution.py', 'utils/dsp.py', 'utils/display.py', 'utils/dataset.py',
     'utils/paths.py', 'utils/files.py',
+    # imported by utils/dataset.py (text front end; only its import has to succeed)
+    'utils/text/__init__.py', 'utils/text/cleaners.py', 'utils/text/cmudict.py', 'utils/text/numbers.py',
+    'utils/text/symbols.py', 'utils/text/recipes.py', 'utils/text/LICENSE',
 ]
 
 

@@ -349,6 +349,49 @@ __global__ void __launch_bounds__(256, 1) l2_stream2(const uint8_t *buf, size_t 
     }
 }
 
+// MMA chain timing with a minimal issue loop: `nacc` independent accumulators used round-robin (1 = one dependent chain),
+// `nmma` MMAs in total on resident operands.  Separates issue overhead, dependent-accumulate latency and the tensor floor.
+__global__ void __launch_bounds__(64, 1) mma_chain(int N, int nacc, int nmma, long long *out) {
+    extern __shared__ __align__(128) uint8_t sm[];
+    __shared__ __align__(8) uint64_t bar;
+    __shared__ uint32_t tmem_base;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int i = threadIdx.x; i < 16384; i += 64) reinterpret_cast<uint32_t *>(sm)[i] = 0;     // 64 KB of zero operands
+    if (threadIdx.x == 0) {
+        mbar_init(&bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncthreads();
+    if (warp == 1) tmem_alloc(&tmem_base, 512);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tb = tmem_base;
+    if (warp == 1 && lane == 0) {
+        const uint32_t idesc = make_idesc(128, N);
+        const uint64_t dA = make_desc(smem_u32(sm), 128 * 16, 128), dB = make_desc(smem_u32(sm) + 8192, (uint32_t)N * 16, 128);
+        const long long t0 = clock64();
+        int acc = 0;
+        for (int i = 0; i < nmma; i += 4) {
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                umma_bf16(tb + (uint32_t)(acc * N), dA + (uint64_t)(j * 2), dB, idesc, 1u);
+                acc = acc + 1 == nacc ? 0 : acc + 1;
+            }
+        }
+        const long long t1 = clock64();
+        umma_commit(&bar);
+        const bool ok = mbar_wait(&bar, 0);
+        const long long t2 = clock64();
+        out[0] = ok ? t2 - t0 : -1;
+        out[1] = t1 - t0;
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tb, 512);
+}
+
 static float bf16_round(float x) { return __bfloat162float(__float2bfloat16(x)); }
 
 int main(int argc, char **argv) {
@@ -520,6 +563,26 @@ int main(int argc, char **argv) {
         cudaFree(buf);
     }
 
+
+    // ---- MMA chains: dependent vs independent accumulators
+    {
+        CK(cudaFuncSetAttribute(mma_chain, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+        long long *dout;
+        CK(cudaMalloc(&dout, 2 * sizeof(long long)));
+        for (int N : {16, 32, 64, 80, 128}) {
+            for (int nacc : {1, 2, 3, 4}) {
+                if (nacc * N > 512) continue;
+                const int nmma = 4096;
+                mma_chain<<<1, 64, 64 * 1024>>>(N, nacc, nmma, dout);
+                CK(cudaDeviceSynchronize());
+                long long o[2];
+                CK(cudaMemcpy(o, dout, sizeof(o), cudaMemcpyDeviceToHost));
+                printf("mma chain N=%3d accumulators=%d: %.1f clk/MMA to completion, %.1f clk/MMA issue only (floor %.1f)\n", N, nacc,
+                       (double)o[0] / nmma, (double)o[1] / nmma, 128.0 * N / 256);
+            }
+        }
+        cudaFree(dout);
+    }
     // ---- streaming, several issuing warps
     {
         CK(cudaFuncSetAttribute(l2_stream2, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));

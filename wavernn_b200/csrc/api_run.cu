@@ -227,11 +227,11 @@ int do_run(wrnn_handle *h, uint64_t seed, cudaStream_t st, const StageOpts &o) {
     WRNN_TRY(ws_reserve(h, h->ws_sync, 128));
     WRNN_CUDA(h, cudaMemsetAsync(h->ws_sync.p, 0, fresh_sync ? 128 : 64, st));
     const int kernel = loop_kernel_choice(h, h->B);
-    if (kernel == 4) {
-        WRNN_TRY(mma_run(h, a, st));       // all folds of the call in one launch
-    } else if (kernel != 1) {
+    if (kernel != 1) {
         // these kernels take fold groups of <= 20 (folds are independent: any grouping is exact)
-        const int64_t cap = kernel == 3 ? res_max_folds() : pipe_max_folds(), ng = (h->B + cap - 1) / cap, per = (h->B + ng - 1) / ng;
+        // (the tensor-core kernel takes up to 1 152 folds per launch: one (row tile, fold tile) job per CTA)
+        const int64_t cap = kernel == 4 ? mma_max_folds(h) : kernel == 3 ? res_max_folds() : pipe_max_folds(),
+                      ng = (h->B + cap - 1) / cap, per = (h->B + ng - 1) / ng;
         const size_t CW = (size_t)(d.F + d.R);
         for (int64_t b0 = 0; b0 < h->B; b0 += per) {
             LoopArgs g = a;
@@ -243,7 +243,7 @@ int do_run(wrnn_handle *h, uint64_t seed, cudaStream_t st, const StageOpts &o) {
             g.picks = a.picks + (size_t)b0 * h->S;
             if (a.teacher) g.teacher = a.teacher + (size_t)b0 * h->S;
             if (a.logits_out) g.logits_out = a.logits_out + (size_t)b0 * h->S * d.NC;
-            WRNN_TRY(kernel == 3 ? res_run(h, g, st) : pipe_run(h, g, st));
+            WRNN_TRY(kernel == 4 ? mma_run(h, g, st) : kernel == 3 ? res_run(h, g, st) : pipe_run(h, g, st));
         }
     } else {
         WRNN_TRY(fma_run(h, a, st));

@@ -68,7 +68,7 @@ struct ResPlan {
 struct MmaPlan {
     bool ok = false;
     uint8_t *Aimg = nullptr;       // device: bf16 hi/lo weight images of the four MMA phases
-    int64_t offA[4] = {0, 0, 0, 0};
+    int64_t offA[6] = {0, 0, 0, 0, 0, 0};      // one image per job type (rnn1, rnn2, recurrent 1, recurrent 2, fc1, fc2)
     float *bias = nullptr;         // device: composed biases
     float *wf3 = nullptr;          // device: fc3 rows (fp32) + bias
     size_t img_bytes = 0, smem_bytes = 0;
@@ -215,6 +215,7 @@ int mma_plan(wrnn_handle *h);
 bool mma_supported(const wrnn_handle *h);
 int mma_min_folds();               // fold count from which the tensor-core kernel beats groups of the resident kernel
 int mma_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st);
+int64_t mma_max_folds(const wrnn_handle *h);   // folds one launch takes (one GRU job per CTA): larger calls run in groups
 // which loop kernel a run will use: 1 = fma (grid barriers, any dims, any fold count), 2 = pipelined
 // (smem weights, tagged exchange), 3 = resident (register weights, default dims), 4 = tensor-core (tcgen05, bf16 hi/lo
 // operands, default dims, MoL; chosen from mma_min_folds() folds up)

@@ -45,49 +45,65 @@ constexpr int UT = 32;                     // GRU units per row tile: rows [r(32
 constexpr int GRU_ROWS = 3 * UT, FC_ROWS = 128;
 constexpr int MT_GRU = H / UT, MT_FC = FCD / FC_ROWS;     // 16, 4 row tiles
 constexpr int KC = 4;                      // k-chunks (of 8 elements) per pipeline stage: K = 32 = two MMA k-steps
-constexpr int NSTAGE = 4;
-constexpr int A_STAGE = 2 * KC * FC_ROWS * 16;            // 16384 B: hi + lo, room for the 128-row image
-constexpr int B_STAGE = 2 * KC * 128 * 16;                // 16384 B at NT = 128
-constexpr int STAGE_BYTES = A_STAGE + B_STAGE;
+constexpr int MAXSTAGE = 8;                // ring depth is chosen at launch: as many stages as shared memory holds, up to 8
+constexpr int A_GRU = 2 * KC * GRU_ROWS * 16, A_FC = 2 * KC * FC_ROWS * 16;     // 12288 / 16384 B per stage: hi + lo
 constexpr int CGROUPS = 7;                 // conditioning operand: 28 chunks = 224 elements per fold
 constexpr int HGROUPS = H / 32;            // 16 stage groups in a 512-wide operand
 constexpr int THREADS = 320, EPI_THREADS = 256, EPI_WARPS = 8;
 constexpr int STG_FLOATS = 2 * 3 * UT * 33;               // epilogue staging (GRU: two accumulators x three gates)
 constexpr int NCP = 32;                    // fc3 rows padded (MoL: 30)
 constexpr int TMEM_COLS = 512;
-// conditioning operand element order (SURVEY.md §8a rows a7-a9: which features each layer concatenates):
+constexpr int FIXED_SMEM = (STG_FLOATS + NCP * FCD + EPI_WARPS * 256) * 4;       // staging + fc3 rows + per-warp scratch
+// conditioning operand element order (SURVEY.md section 8a rows a7-a9: which features each layer concatenates):
 //   [a4 (32) | a2 (32) | x_prev (1) | m (80) | a1 (32) | a3 (32) | zero (15)]
 // so that rnn1 reads chunks 8..23, rnn2 chunks 4..23, fc1 chunks 8..27, fc2 chunks 0..3.
 constexpr int C_A4 = 0, C_A2 = 32, C_X = 64, C_M = 65, C_A1 = 145, C_A3 = 177, C_END = 209;
-constexpr int NST_P1 = 4 + 16, NST_P2 = 16 + 5 + 16, NST_P3 = 16 + 5, NST_P4 = 16 + 1;
 
-enum { ARR_C = 0, ARR_H1CUR, ARR_H1NEW, ARR_H2CUR, ARR_S12, ARR_Y1 };
-
-struct StageInfo { int arr, g, acc, first; };
-__host__ __device__ inline int phase_stages(int p) { return p == 0 ? NST_P1 : p == 1 ? NST_P2 : p == 2 ? NST_P3 : NST_P4; }
-__host__ __device__ inline StageInfo stage_info(int p, int s) {
-    if (p == 0) return s < 4 ? StageInfo{ARR_C, 2 + s, 0, s == 0} : StageInfo{ARR_H1CUR, s - 4, 1, s == 4};
-    if (p == 1) {
-        if (s < 16) return StageInfo{ARR_H1NEW, s, 0, s == 0};
-        if (s < 21) return StageInfo{ARR_C, 1 + (s - 16), 0, 0};
-        return StageInfo{ARR_H2CUR, s - 21, 1, s == 21};
+// Job types.  A job = one (row tile, fold tile) MMA chain into one TMEM accumulator.  Per step a GRU CTA runs
+//   J_R1 (rnn1, conditioning columns only)  -> gates -> J_R2 (rnn2: W_ih2a . h1' + conditioning columns) -> gates,
+// then, OFF the sample-to-sample chain while the fc CTAs work, the two recurrent products of the NEXT step,
+//   J_S1 (W_hh1 . h1') and J_S2 (W_hh2 . h2'), whose accumulators stay in TMEM until the next step's gates read them;
+// an fc CTA runs J_F1 (fc1) -> ReLU -> J_F2 (fc2) -> ReLU.  (loop_res.cu's "shadow products", on tensor cores.)
+enum { J_R1 = 0, J_R2, J_S1, J_S2, J_F1, J_F2, NJOB };
+enum { ARR_C = 0, ARR_H1NEW, ARR_H2NEW, ARR_S12, ARR_Y1 };
+// TMEM accumulator of each job, in units of NT columns: rnn1 reads X1 + H1, rnn2 reads X2 + H2; fc reuses X1's columns
+__host__ __device__ inline int job_acc(int jt) { return jt == J_R1 ? 0 : jt == J_S1 ? 1 : jt == J_R2 ? 2 : jt == J_S2 ? 3 : 0; }
+__host__ __device__ inline int job_stages(int jt) { return jt == J_R1 ? 4 : jt == J_R2 ? 21 : jt == J_F1 ? 21 : jt == J_F2 ? 17 : 16; }
+__host__ __device__ inline int job_rows(int jt) { return jt >= J_F1 ? FC_ROWS : GRU_ROWS; }
+// grid counter a job's loads wait for (value G * (t + 1)), -1 = ordered behind the previous job of the same CTA
+__host__ __device__ inline int job_gate(int jt) { return jt == J_R1 ? 4 : jt == J_R2 ? 0 : jt == J_S1 ? -1 : jt == J_F2 ? 2 : 1; }
+struct StageInfo { int arr, g; };
+__host__ __device__ inline StageInfo stage_info(int jt, int s) {
+    switch (jt) {
+        case J_R1: return StageInfo{ARR_C, 2 + s};
+        case J_R2: return s < 16 ? StageInfo{ARR_H1NEW, s} : StageInfo{ARR_C, 1 + (s - 16)};
+        case J_S1: return StageInfo{ARR_H1NEW, s};
+        case J_S2: return StageInfo{ARR_H2NEW, s};
+        case J_F1: return s < 16 ? StageInfo{ARR_S12, s} : StageInfo{ARR_C, 2 + (s - 16)};
+        default: return s < 16 ? StageInfo{ARR_Y1, s} : StageInfo{ARR_C, 0};
     }
-    if (p == 2) return s < 16 ? StageInfo{ARR_S12, s, 0, s == 0} : StageInfo{ARR_C, 2 + (s - 16), 0, 0};
-    return s < 16 ? StageInfo{ARR_Y1, s, 0, s == 0} : StageInfo{ARR_C, 0, 0, 0};
 }
 
 struct Params {
     LoopArgs a;
     int NT, NTILES, G, NC;
     int64_t steps_run;             // == a.S except under WRNN_MMA_STEPS (bring-up: stop after n steps and inspect the state)
-    const uint8_t *Aimg;           // packed weights: phase p at offA[p], [row tile][stage][hi|lo][KC][rows][8] bf16
-    int64_t offA[4];
+    int ring_bytes;                // shared memory of the stage ring (the staging / fc3 / scratch region follows it)
+    const uint8_t *Aimg;           // packed weights: job type j at offA[j], [row tile][stage][hi|lo][KC][rows][8] bf16
+    int64_t offA[NJOB];
     const float *bias;             // P1: [16][2][96] | P2: [16][2][96] | P3: [512] | P4: [512]
     const float *Wf3, *bf3;        // [NCP][512], [NCP] fp32
     uint8_t *H1[2], *H2[2], *S12, *Y1, *C;      // B operands, [fold tile][group][hi|lo][KC][NT][8] bf16
     float *h1f, *h2f, *y2f;        // [NTILES*NT][512] fp32 state / fc2 output
     GridSync gs;
+    long long *prof;               // debug (WRNN_MMA_PROF=step): clock64 timeline of that step from CTA 0 and CTA G-1, else null
+    int64_t prof_step;
 };
+
+#define PROF_MARK(slot)                                                                              \
+    do {                                                                                             \
+        if (P.prof && t == P.prof_step && (cta == 0 || cta == G - 1)) P.prof[(cta == 0 ? 0 : 64) + (slot)] = clock64(); \
+    } while (0)
 
 // ---------------------------------------------------------------------------- PTX
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -225,24 +241,20 @@ __device__ __forceinline__ float mol_sample_smem(const float *lg, int nmix, floa
     return x;
 }
 
-// conditioning operand of step `t` for fold b (one warp): gather the 208-float row, reorder, split, store 28 chunks
-__device__ __forceinline__ void write_cond_operand(const Params &P, int64_t b, int64_t t, float xprev, float *scr, int lane) {
+// conditioning operand of step `t` for fold b (one warp), in two halves so that the 832-byte row (HBM, cold) can be
+// fetched before the warp has to wait for anything: load_cond_row -> scr[0..207], build_cond_operand reorders, splits
+// into bf16 hi/lo and stores the 28 chunks.
+__device__ __forceinline__ void load_cond_row(const Params &P, int64_t b, int64_t t, float *scr, int lane) {
     const int64_t S = P.a.S;
     const int RW = FEAT + 4 * AUX;
-    if (t < S) {
-        const float *row = P.a.cond + ((size_t)b * S + t) * RW;
+    const float *row = P.a.cond + ((size_t)b * S + (t < S ? t : 0)) * RW;
 #pragma unroll
-        for (int i = 0; i < 7; i++) {
-            const int e = lane + 32 * i;
-            if (e < RW) scr[e] = __ldg(row + e);
-        }
-    } else {
-#pragma unroll
-        for (int i = 0; i < 7; i++) {
-            const int e = lane + 32 * i;
-            if (e < RW) scr[e] = 0.f;
-        }
+    for (int i = 0; i < 7; i++) {
+        const int e = lane + 32 * i;
+        if (e < RW) scr[e] = t < S ? __ldg(row + e) : 0.f;
     }
+}
+__device__ __forceinline__ void build_cond_operand(const Params &P, int64_t b, float xprev, const float *scr, int lane) {
     __syncwarp();
     if (lane < 4 * CGROUPS) {
         float v[8];
@@ -270,27 +282,203 @@ __device__ __forceinline__ void write_cond_operand(const Params &P, int64_t b, i
     __syncwarp();
 }
 
+// operand array a job reads at step t (t = -1: the prologue's recurrent products on the zero state)
 __device__ __forceinline__ const uint8_t *b_array(const Params &P, int arr, int64_t t) {
     switch (arr) {
         case ARR_C: return P.C;
-        case ARR_H1CUR: return P.H1[t & 1];
         case ARR_H1NEW: return P.H1[(t + 1) & 1];
-        case ARR_H2CUR: return P.H2[t & 1];
+        case ARR_H2NEW: return P.H2[(t + 1) & 1];
         case ARR_S12: return P.S12;
         default: return P.Y1;
     }
 }
 
-// first job of CTA `cta` in phase p, and the job stride: GRU phases fill CTAs from 0 up, fc phases from G-1 down
-__device__ __forceinline__ int phase_tiles(const Params &P, int p) { return (p < 2 ? MT_GRU : MT_FC) * P.NTILES; }
-__device__ __forceinline__ int first_job(const Params &P, int p, int cta) { return p < 2 ? cta : P.G - 1 - cta; }
+struct Ring {                   // the stage ring of this CTA and a position in it (producer and MMA issuer keep one each)
+    uint32_t nstage, a_slot, stage_bytes;       // depth, bytes reserved for the weight block of a stage, bytes per stage
+    uint32_t slot, par;
+    __device__ __forceinline__ void advance() {
+        if (++slot == nstage) { slot = 0; par ^= 1u; }
+    }
+};
+// A CTA that only ever runs GRU jobs (96-row weight blocks) packs its stages tighter than one that also has an fc job;
+// the ring is as deep as its share of shared memory allows (4 stages at 128 folds per tile, 7 at 16).
+__device__ __forceinline__ Ring make_ring(const Params &P, bool has_fc) {
+    Ring r;
+    r.a_slot = has_fc ? A_FC : A_GRU;
+    r.stage_bytes = r.a_slot + 2u * KC * (uint32_t)P.NT * 16u;
+    r.nstage = min((uint32_t)MAXSTAGE, (uint32_t)P.ring_bytes / r.stage_bytes);
+    r.slot = 0;
+    r.par = 0;
+    return r;
+}
+
+// One job of the TMA producer thread: (wait for the grid counter,) stream the stages of (job type, row tile, fold tile).
+__device__ __forceinline__ void produce_job(const Params &P, int jt, int mt, int nt, int64_t t, Ring &r, uint8_t *stages,
+                                            uint64_t *bar_full, uint64_t *bar_empty, Watch &w) {
+    const int nst = job_stages(jt), gate = job_gate(jt);
+    const uint32_t abytes = 2u * KC * (uint32_t)job_rows(jt) * 16u, bbytes = 2u * KC * (uint32_t)P.NT * 16u;
+    if (gate >= 0) {            // this job's operands were written by that phase of every CTA
+        grid_wait(P.gs, gate, (unsigned long long)P.G * (unsigned long long)(t + 1), w);
+        fence_proxy_async_global();
+    }
+    const uint8_t *Abase = P.Aimg + P.offA[jt] + (size_t)mt * nst * abytes;
+    for (int s = 0; s < nst; s++) {
+        mbar_wait(&bar_empty[r.slot], r.par ^ 1u, w);
+        const StageInfo si = stage_info(jt, s);
+        const int NG = si.arr == ARR_C ? CGROUPS : HGROUPS;
+        const uint8_t *Bsrc = b_array(P, si.arr, t) + (size_t)(nt * NG + si.g) * bbytes;
+        uint8_t *dst = stages + (size_t)r.slot * r.stage_bytes;
+        mbar_expect_tx(&bar_full[r.slot], abytes + bbytes);
+        bulk_g2s(dst, Abase + (size_t)s * abytes, abytes, &bar_full[r.slot]);
+        bulk_g2s(dst + r.a_slot, Bsrc, bbytes, &bar_full[r.slot]);
+        r.advance();
+    }
+}
+
+// One job of the MMA issuer thread: three MMAs (hi.hi, hi.lo, lo.hi) per k-step into the job's accumulator.
+__device__ __forceinline__ void issue_job(const Params &P, int jt, Ring &r, uint32_t stage0, uint32_t tb, uint32_t idesc,
+                                          uint64_t *bar_full, uint64_t *bar_empty, uint64_t *bar_tfull, Watch &w) {
+    const int nst = job_stages(jt);
+    const uint32_t rows = job_rows(jt), NT = P.NT;
+    // descriptors differ only in the 14-bit start-address field (16-byte units): constant part once per job
+    const uint64_t dA0 = make_desc(0, rows * 16u, 128), dB0 = make_desc(0, NT * 16u, 128);
+    const uint32_t stepA = 2u * rows, stepB = 2u * NT;          // two k-chunks, in 16-byte units
+    const uint32_t loA = KC * rows, loB = KC * NT;               // hi -> lo image
+    const uint32_t d = tb + (uint32_t)job_acc(jt) * NT;
+    for (int s = 0; s < nst; s++) {
+        mbar_wait(&bar_full[r.slot], r.par, w);
+        tc_fence_after();
+        const uint32_t aA = (stage0 + r.slot * r.stage_bytes) >> 4, aB = aA + (r.a_slot >> 4);
+#pragma unroll
+        for (int ks = 0; ks < KC / 2; ks++) {
+            const uint64_t ah = dA0 + (aA + ks * stepA), al = dA0 + (aA + loA + ks * stepA);
+            const uint64_t bh = dB0 + (aB + ks * stepB), bl = dB0 + (aB + loB + ks * stepB);
+            umma_bf16(d, ah, bh, idesc, (s == 0 && ks == 0) ? 0u : 1u);
+            umma_bf16(d, ah, bl, idesc, 1u);
+            umma_bf16(d, al, bh, idesc, 1u);
+        }
+        umma_commit(&bar_empty[r.slot]);          // the stage is free once these MMAs have read it
+        r.advance();
+    }
+    if (jt != J_S1 && jt != J_S2) umma_commit(bar_tfull);       // accumulator (and every earlier MMA) complete
+}
+
+// ---------------------------------------------------------------------------- epilogues (256 threads, warps 2..9)
+// GRU gates (fatchord_version.py:210-216) of one (32 units x NT folds) tile: accumulators X (input side) and H (recurrent
+// side, formed one step ahead) hold rows [r | z | n]; h' goes out as fp32 state and as the bf16 hi/lo operand of the
+// next products; rnn2 also emits s12 = h1' + h2' (fc1 reads x + h1 + h2, x is folded into fc1's weights).
+__device__ __forceinline__ void epi_gru(const Params &P, int layer, int mt, int nt, int64_t t, uint32_t tb, float *stg, int etid,
+                                        int q, int half, int lane) {
+    const int NT = P.NT;
+    const float *bi = P.bias + (size_t)(layer * MT_GRU + mt) * 2 * GRU_ROWS, *bh = bi + GRU_ROWS;
+    float *hf = layer == 0 ? P.h1f : P.h2f;
+    uint8_t *Hn = layer == 0 ? P.H1[(t + 1) & 1] : P.H2[(t + 1) & 1];
+    const uint32_t colX = (uint32_t)job_acc(layer == 0 ? J_R1 : J_R2) * NT, colH = (uint32_t)job_acc(layer == 0 ? J_S1 : J_S2) * NT;
+    const int f = etid & 31, quad = etid >> 5, u0 = quad * 4, gu = mt * UT + u0;
+    float bir[4], biz[4], bin[4], bhr[4], bhz[4], bhn[4];
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        bir[i] = __ldg(bi + 0 * UT + u0 + i); biz[i] = __ldg(bi + 1 * UT + u0 + i); bin[i] = __ldg(bi + 2 * UT + u0 + i);
+        bhr[i] = __ldg(bh + 0 * UT + u0 + i); bhz[i] = __ldg(bh + 1 * UT + u0 + i); bhn[i] = __ldg(bh + 2 * UT + u0 + i);
+    }
+    for (int c0 = 0; c0 < NT; c0 += 32) {
+        const int fi = c0 + f;
+        const size_t fold = (size_t)nt * NT + fi;
+        float4 hp4 = make_float4(0.f, 0.f, 0.f, 0.f), a4 = hp4;
+        if (fi < NT) {                          // own state of the step before / rnn1's new state: in flight under the TMEM read
+            hp4 = __ldcg(reinterpret_cast<const float4 *>(hf + fold * H + gu));
+            if (layer == 1) a4 = __ldcg(reinterpret_cast<const float4 *>(P.h1f + fold * H + gu));
+        }
+        if (q < 3) {
+            uint32_t r[32];
+            tmem_ld32(tb + ((uint32_t)(q * 32) << 16) + (half ? colH : colX) + (uint32_t)c0, r);
+            float *dst = stg + ((half * 3 + q) * UT + lane) * 33;
+#pragma unroll
+            for (int i = 0; i < 32; i++) dst[i] = __uint_as_float(r[i]);
+        }
+        epi_bar();
+        if (fi < NT) {
+            const float hp[4] = {hp4.x, hp4.y, hp4.z, hp4.w};
+            float hn[4];
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                const int u = u0 + i;
+                const float ir = stg[((0 * 3 + 0) * UT + u) * 33 + f] + bir[i];
+                const float iz = stg[((0 * 3 + 1) * UT + u) * 33 + f] + biz[i];
+                const float in_ = stg[((0 * 3 + 2) * UT + u) * 33 + f] + bin[i];
+                const float hr = stg[((1 * 3 + 0) * UT + u) * 33 + f] + bhr[i];
+                const float hz = stg[((1 * 3 + 1) * UT + u) * 33 + f] + bhz[i];
+                const float hnn = stg[((1 * 3 + 2) * UT + u) * 33 + f] + bhn[i];
+                hn[i] = gru_update_fast(ir, iz, in_, hr, hz, hnn, hp[i]);
+            }
+            *reinterpret_cast<float4 *>(hf + fold * H + gu) = make_float4(hn[0], hn[1], hn[2], hn[3]);
+            uint2 hi, lo;
+            split4(hn, hi, lo);
+            const int sub = (gu & 7) * 2;       // 0 or 8 bytes inside the 16-byte chunk
+            *reinterpret_cast<uint2 *>(Hn + b_slot(NT, HGROUPS, nt, gu >> 3, fi, 0) + sub) = hi;
+            *reinterpret_cast<uint2 *>(Hn + b_slot(NT, HGROUPS, nt, gu >> 3, fi, 1) + sub) = lo;
+            if (layer == 1) {
+                const float sm[4] = {a4.x + hn[0], a4.y + hn[1], a4.z + hn[2], a4.w + hn[3]};
+                split4(sm, hi, lo);
+                *reinterpret_cast<uint2 *>(P.S12 + b_slot(NT, HGROUPS, nt, gu >> 3, fi, 0) + sub) = hi;
+                *reinterpret_cast<uint2 *>(P.S12 + b_slot(NT, HGROUPS, nt, gu >> 3, fi, 1) + sub) = lo;
+            }
+        }
+        epi_bar();
+    }
+}
+
+// fc1 / fc2 + ReLU (:217-221) of one (128 rows x NT folds) tile: fc1 -> bf16 hi/lo operand of fc2, fc2 -> fp32 rows for fc3
+__device__ __forceinline__ void epi_fc(const Params &P, int layer, int mt, int nt, uint32_t tb, float *stg, int etid, int q, int half,
+                                       int lane) {
+    const int NT = P.NT;
+    const float *bb = P.bias + (size_t)2 * MT_GRU * 2 * GRU_ROWS + (size_t)layer * FCD + mt * FC_ROWS;
+    const int f = etid & 31, rg = etid >> 5, gr = mt * FC_ROWS + rg * 16;
+    float bv[16];
+#pragma unroll
+    for (int i = 0; i < 16; i++) bv[i] = __ldg(bb + rg * 16 + i);
+    for (int c0 = 0; c0 < NT; c0 += 32) {
+        if (half == 0) {
+            uint32_t r[32];
+            tmem_ld32(tb + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, r);
+            float *dst = stg + (q * 32 + lane) * 33;
+#pragma unroll
+            for (int i = 0; i < 32; i++) dst[i] = __uint_as_float(r[i]);
+        }
+        epi_bar();
+        const int fi = c0 + f;
+        if (fi < NT) {
+            const size_t fold = (size_t)nt * NT + fi;
+            float v[16];
+#pragma unroll
+            for (int i = 0; i < 16; i++) v[i] = fmaxf(stg[(rg * 16 + i) * 33 + f] + bv[i], 0.f);
+            if (layer == 0) {
+#pragma unroll
+                for (int c = 0; c < 2; c++) {
+                    const float v0[4] = {v[8 * c], v[8 * c + 1], v[8 * c + 2], v[8 * c + 3]};
+                    const float v1[4] = {v[8 * c + 4], v[8 * c + 5], v[8 * c + 6], v[8 * c + 7]};
+                    uint2 h0, l0, h1, l1;
+                    split4(v0, h0, l0);
+                    split4(v1, h1, l1);
+                    *reinterpret_cast<uint4 *>(P.Y1 + b_slot(NT, HGROUPS, nt, (gr >> 3) + c, fi, 0)) = make_uint4(h0.x, h0.y, h1.x, h1.y);
+                    *reinterpret_cast<uint4 *>(P.Y1 + b_slot(NT, HGROUPS, nt, (gr >> 3) + c, fi, 1)) = make_uint4(l0.x, l0.y, l1.x, l1.y);
+                }
+            } else {
+                float4 *dst = reinterpret_cast<float4 *>(P.y2f + fold * FCD + gr);
+#pragma unroll
+                for (int c = 0; c < 4; c++) dst[c] = make_float4(v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
+            }
+        }
+        epi_bar();
+    }
+}
 
 __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
     extern __shared__ __align__(1024) uint8_t smem[];
-    __shared__ __align__(8) uint64_t bar_full[NSTAGE], bar_empty[NSTAGE], bar_tfull[2], bar_tempty[2];
+    __shared__ __align__(8) uint64_t bar_full[MAXSTAGE], bar_empty[MAXSTAGE], bar_tfull;
     __shared__ uint32_t tmem_base_s;
     uint8_t *stages = smem;
-    float *stg = reinterpret_cast<float *>(smem + NSTAGE * STAGE_BYTES);
+    float *stg = reinterpret_cast<float *>(smem + P.ring_bytes);
     float *wf3 = stg + STG_FLOATS;                          // [NCP][512]
     float *scr = wf3 + NCP * FCD;                           // per epilogue warp: 256 floats
 
@@ -298,10 +486,13 @@ __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
     const int NT = P.NT, G = P.G;
     const int64_t S = P.a.S, B = P.a.B;
     Watch w{P.gs.abort_flag, false};
+    // static roles: GRU (row tile, fold tile) jobs fill CTAs from 0 up, fc jobs from G - 1 down; at most one of each per CTA
+    const bool has_gru = cta < MT_GRU * P.NTILES, has_fc = G - 1 - cta < MT_FC * P.NTILES;
+    const int mt_g = cta % MT_GRU, nt_g = cta / MT_GRU, mt_f = (G - 1 - cta) % MT_FC, nt_f = (G - 1 - cta) / MT_FC;
 
     if (tid == 0) {
-        for (int i = 0; i < NSTAGE; i++) { mbar_init(&bar_full[i], 1); mbar_init(&bar_empty[i], 1); }
-        for (int i = 0; i < 2; i++) { mbar_init(&bar_tfull[i], 1); mbar_init(&bar_tempty[i], 1); }
+        for (int i = 0; i < MAXSTAGE; i++) { mbar_init(&bar_full[i], 1); mbar_init(&bar_empty[i], 1); }
+        mbar_init(&bar_tfull, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) tmem_alloc(&tmem_base_s, TMEM_COLS);
@@ -314,209 +505,154 @@ __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
     if (warp == 0) {
         // ======================================================================= TMA producer
         if (lane == 0) {
-            uint32_t it = 0;
+            Ring r = make_ring(P, has_fc);
+            if (has_gru) {      // step "-1": recurrent products of step 0 on the zero state (h = 0, :194-195)
+                produce_job(P, J_S1, mt_g, nt_g, -1, r, stages, bar_full, bar_empty, w);
+                produce_job(P, J_S2, mt_g, nt_g, -1, r, stages, bar_full, bar_empty, w);
+            }
             for (int64_t t = 0; t < P.steps_run && !w.dead; t++) {
-                for (int p = 0; p < 4; p++) {
-                    const int ntiles = phase_tiles(P, p), nst = phase_stages(p);
-                    const uint32_t abytes = 2u * KC * (p < 2 ? GRU_ROWS : FC_ROWS) * 16u, bbytes = 2u * KC * NT * 16u;
-                    bool waited = false;
-                    for (int id = first_job(P, p, cta); id < ntiles; id += G) {
-                        if (!waited) {     // this phase's operands were written by phase q-1 of every CTA
-                            // phase p reads what phase p - 1 of this step wrote (rnn1: what the fc3 phase of the step before,
-                            // or the prologue, wrote: both publish on counter 4)
-                            grid_wait(P.gs, p == 0 ? 4 : p - 1, (unsigned long long)G * (unsigned long long)(t + 1), w);
-                            fence_proxy_async_global();
-                            waited = true;
-                        }
-                        const int mt = id % (p < 2 ? MT_GRU : MT_FC), nt = id / (p < 2 ? MT_GRU : MT_FC);
-                        const uint8_t *Abase = P.Aimg + P.offA[p] + (size_t)mt * nst * abytes;
-                        for (int s = 0; s < nst; s++, it++) {
-                            const int slot = it % NSTAGE;
-                            mbar_wait(&bar_empty[slot], ((it / NSTAGE) & 1) ^ 1, w);
-                            const StageInfo si = stage_info(p, s);
-                            const int NG = si.arr == ARR_C ? CGROUPS : HGROUPS;
-                            const uint8_t *Bsrc = b_array(P, si.arr, t) + (size_t)(nt * NG + si.g) * bbytes;
-                            uint8_t *dst = stages + (size_t)slot * STAGE_BYTES;
-                            mbar_expect_tx(&bar_full[slot], abytes + bbytes);
-                            bulk_g2s(dst, Abase + (size_t)s * abytes, abytes, &bar_full[slot]);
-                            bulk_g2s(dst + A_STAGE, Bsrc, bbytes, &bar_full[slot]);
-                        }
-                    }
+                if (has_gru) {
+                    PROF_MARK(0);
+                    produce_job(P, J_R1, mt_g, nt_g, t, r, stages, bar_full, bar_empty, w);
+                    PROF_MARK(1);
+                    produce_job(P, J_R2, mt_g, nt_g, t, r, stages, bar_full, bar_empty, w);
+                    PROF_MARK(2);
+                    produce_job(P, J_S1, mt_g, nt_g, t, r, stages, bar_full, bar_empty, w);
+                    PROF_MARK(3);
+                }
+                if (has_fc) {
+                    PROF_MARK(4);
+                    produce_job(P, J_F1, mt_f, nt_f, t, r, stages, bar_full, bar_empty, w);
+                    PROF_MARK(5);
+                    produce_job(P, J_F2, mt_f, nt_f, t, r, stages, bar_full, bar_empty, w);
+                    PROF_MARK(6);
+                }
+                if (has_gru) {
+                    produce_job(P, J_S2, mt_g, nt_g, t, r, stages, bar_full, bar_empty, w);
+                    PROF_MARK(7);
                 }
             }
         }
     } else if (warp == 1) {
         // ======================================================================= MMA issuer
         if (lane == 0) {
-            uint32_t it = 0, j = 0;
-            const uint32_t idesc = make_idesc(128, NT);
-            const uint32_t stage0 = smem_u32(stages);
+            Ring r = make_ring(P, has_fc);
+            const uint32_t idesc = make_idesc(128, NT), stage0 = smem_u32(stages);
+            if (has_gru) {
+                issue_job(P, J_S1, r, stage0, tb, idesc, bar_full, bar_empty, &bar_tfull, w);
+                issue_job(P, J_S2, r, stage0, tb, idesc, bar_full, bar_empty, &bar_tfull, w);
+            }
             for (int64_t t = 0; t < P.steps_run && !w.dead; t++) {
-                for (int p = 0; p < 4; p++) {
-                    const int ntiles = phase_tiles(P, p), nst = phase_stages(p);
-                    const uint32_t rows = p < 2 ? GRU_ROWS : FC_ROWS;
-                    // descriptors differ only in the 14-bit start-address field (16-byte units): build the constant part once
-                    // per phase and add slot / k-step offsets, so that issuing a k-step is a handful of integer instructions
-                    const uint64_t dA0 = make_desc(0, rows * 16u, 128), dB0 = make_desc(0, (uint32_t)NT * 16u, 128);
-                    const uint32_t stepA = 2u * rows, stepB = 2u * (uint32_t)NT;          // two k-chunks, in 16-byte units
-                    const uint32_t loA = KC * rows, loB = KC * (uint32_t)NT;               // hi -> lo image
-                    for (int id = first_job(P, p, cta); id < ntiles; id += G, j++) {
-                        const uint32_t buf = j & 1;
-                        mbar_wait(&bar_tempty[buf], ((j >> 1) & 1) ^ 1, w);
-                        tc_fence_after();
-                        for (int s = 0; s < nst; s++, it++) {
-                            const int slot = it % NSTAGE;
-                            mbar_wait(&bar_full[slot], (it / NSTAGE) & 1, w);
-                            tc_fence_after();
-                            const StageInfo si = stage_info(p, s);
-                            const uint32_t d = tb + buf * 256u + (uint32_t)si.acc * (uint32_t)NT;
-                            const uint32_t aA = (stage0 + (uint32_t)slot * STAGE_BYTES) >> 4, aB = aA + (A_STAGE >> 4);
-#pragma unroll
-                            for (int ks = 0; ks < KC / 2; ks++) {
-                                const uint64_t ah = dA0 + (aA + ks * stepA), al = dA0 + (aA + loA + ks * stepA);
-                                const uint64_t bh = dB0 + (aB + ks * stepB), bl = dB0 + (aB + loB + ks * stepB);
-                                umma_bf16(d, ah, bh, idesc, (si.first && ks == 0) ? 0u : 1u);
-                                umma_bf16(d, ah, bl, idesc, 1u);
-                                umma_bf16(d, al, bh, idesc, 1u);
-                            }
-                            umma_commit(&bar_empty[slot]);          // the stage is free once these MMAs have read it
-                        }
-                        umma_commit(&bar_tfull[buf]);               // accumulators complete
-                    }
+                if (has_gru) {
+                    issue_job(P, J_R1, r, stage0, tb, idesc, bar_full, bar_empty, &bar_tfull, w);
+                    PROF_MARK(10);
+                    issue_job(P, J_R2, r, stage0, tb, idesc, bar_full, bar_empty, &bar_tfull, w);
+                    PROF_MARK(11);
+                    issue_job(P, J_S1, r, stage0, tb, idesc, bar_full, bar_empty, &bar_tfull, w);
+                    PROF_MARK(12);
+                }
+                if (has_fc) {
+                    issue_job(P, J_F1, r, stage0, tb, idesc, bar_full, bar_empty, &bar_tfull, w);
+                    PROF_MARK(13);
+                    issue_job(P, J_F2, r, stage0, tb, idesc, bar_full, bar_empty, &bar_tfull, w);
+                    PROF_MARK(14);
+                }
+                if (has_gru) {
+                    issue_job(P, J_S2, r, stage0, tb, idesc, bar_full, bar_empty, &bar_tfull, w);
+                    PROF_MARK(15);
                 }
             }
         }
         __syncwarp();
     } else {
-        // ======================================================================= epilogue warps + FFMA phase
+        // ======================================================================= epilogue warps + fc3 / sampling phase
         const int etid = tid - 64, ewarp = warp - 2;
-        const int q = warp & 3, half = ewarp >> 2;          // TMEM lane quarter this warp may read; column half
+        const int q = warp & 3, half = ewarp >> 2;          // TMEM lane quarter this warp may read; which accumulator / idle
         float *myscr = scr + ewarp * 256;
         const uint2 key = make_uint2((uint32_t)P.a.seed, (uint32_t)(P.a.seed >> 32));
         const int nmix = P.NC / 3;
-        // ---- phase 0: conditioning operand of step 0 (x_prev = 0 or the teacher's first sample)
+        uint32_t tpar = 0;                                   // parity of bar_tfull: one completion per job with an epilogue
+        auto publish = [&](int p) {                          // every writing thread fences, one thread releases the counter
+            fence_proxy_async_global();
+            epi_bar();
+            if (etid == 0) red_release_add_u64(phase_counter(P.gs, p), 1ull);
+        };
+        auto wait_acc = [&]() {
+            mbar_wait(&bar_tfull, tpar, w);
+            tpar ^= 1u;
+            __syncwarp();       // lanes leave the spin loop one by one; tcgen05.ld is .sync.aligned: converge first
+            tc_fence_after();
+        };
+        // ---- step "-1": conditioning operand of step 0 (x_prev = 0 or the teacher's first sample)
         for (int64_t b = cta + (int64_t)G * ewarp; b < B; b += (int64_t)G * EPI_WARPS) {
             const float x0 = P.a.teacher ? P.a.teacher[(size_t)b * S] : 0.f;
-            write_cond_operand(P, b, 0, x0, myscr, lane);
+            load_cond_row(P, b, 0, myscr, lane);
+            build_cond_operand(P, b, x0, myscr, lane);
         }
-        fence_proxy_async_global();
-        epi_bar();
-        if (etid == 0) { fence_proxy_async_global(); red_release_add_u64(phase_counter(P.gs, 4), 1ull); }
+        publish(4);
 
-        uint32_t j = 0;
         for (int64_t t = 0; t < P.steps_run; t++) {
             if (w.dead) break;                               // uniform: set below from a flag read after a barrier
-            for (int p = 0; p < 4; p++) {
-                const int ntiles = phase_tiles(P, p);
-                for (int id = first_job(P, p, cta); id < ntiles; id += G, j++) {
-                    const uint32_t buf = j & 1;
-                    const int mt = id % (p < 2 ? MT_GRU : MT_FC), nt = id / (p < 2 ? MT_GRU : MT_FC);
-                    mbar_wait(&bar_tfull[buf], (j >> 1) & 1, w);
-                    __syncwarp();       // lanes leave the spin loop one by one; tcgen05.ld is .sync.aligned: converge first
-                    tc_fence_after();
-                    if (p < 2) {
-                        // ---------------- GRU gates (fatchord_version.py:210-216): rows [r | z | n] x 32 units
-                        const float *bi = P.bias + (size_t)(p * MT_GRU + mt) * 2 * GRU_ROWS, *bh = bi + GRU_ROWS;
-                        float *hf = p == 0 ? P.h1f : P.h2f;
-                        uint8_t *Hn = p == 0 ? P.H1[(t + 1) & 1] : P.H2[(t + 1) & 1];
-                        for (int c0 = 0; c0 < NT; c0 += 32) {
-                            if (q < 3) {
-                                uint32_t r[32];
-                                tmem_ld32(tb + ((uint32_t)(q * 32) << 16) + buf * 256u + (uint32_t)(half * NT + c0), r);
-                                float *dst = stg + ((half * 3 + q) * UT + lane) * 33;
-#pragma unroll
-                                for (int i = 0; i < 32; i++) dst[i] = __uint_as_float(r[i]);
-                            }
-                            epi_bar();
-                            const int f = etid & 31, quad = etid >> 5, fi = c0 + f;
-                            if (fi < NT) {
-                                const int u0 = quad * 4, gu = mt * UT + u0;
-                                const size_t fold = (size_t)nt * NT + fi;
-                                const float4 hp4 = __ldcg(reinterpret_cast<const float4 *>(hf + fold * H + gu));
-                                const float hp[4] = {hp4.x, hp4.y, hp4.z, hp4.w};
-                                float hn[4];
-#pragma unroll
-                                for (int i = 0; i < 4; i++) {
-                                    const int u = u0 + i;
-                                    const float ir = stg[((0 * 3 + 0) * UT + u) * 33 + f] + __ldg(bi + 0 * UT + u);
-                                    const float iz = stg[((0 * 3 + 1) * UT + u) * 33 + f] + __ldg(bi + 1 * UT + u);
-                                    const float in_ = stg[((0 * 3 + 2) * UT + u) * 33 + f] + __ldg(bi + 2 * UT + u);
-                                    const float hr = stg[((1 * 3 + 0) * UT + u) * 33 + f] + __ldg(bh + 0 * UT + u);
-                                    const float hz = stg[((1 * 3 + 1) * UT + u) * 33 + f] + __ldg(bh + 1 * UT + u);
-                                    const float hnn = stg[((1 * 3 + 2) * UT + u) * 33 + f] + __ldg(bh + 2 * UT + u);
-                                    hn[i] = gru_update(ir, iz, in_, hr, hz, hnn, hp[i]);
-                                }
-                                *reinterpret_cast<float4 *>(hf + fold * H + gu) = make_float4(hn[0], hn[1], hn[2], hn[3]);
-                                uint2 hi, lo;
-                                split4(hn, hi, lo);
-                                const int sub = (gu & 7) * 2;       // 0 or 8 bytes inside the 16-byte chunk
-                                *reinterpret_cast<uint2 *>(Hn + b_slot(NT, HGROUPS, nt, gu >> 3, fi, 0) + sub) = hi;
-                                *reinterpret_cast<uint2 *>(Hn + b_slot(NT, HGROUPS, nt, gu >> 3, fi, 1) + sub) = lo;
-                                if (p == 1) {                       // fc1 reads x + h1 + h2; x is folded into its weights
-                                    const float4 a4 = __ldcg(reinterpret_cast<const float4 *>(P.h1f + fold * H + gu));
-                                    const float s[4] = {a4.x + hn[0], a4.y + hn[1], a4.z + hn[2], a4.w + hn[3]};
-                                    split4(s, hi, lo);
-                                    *reinterpret_cast<uint2 *>(P.S12 + b_slot(NT, HGROUPS, nt, gu >> 3, fi, 0) + sub) = hi;
-                                    *reinterpret_cast<uint2 *>(P.S12 + b_slot(NT, HGROUPS, nt, gu >> 3, fi, 1) + sub) = lo;
-                                }
-                            }
-                            epi_bar();
-                        }
-                    } else {
-                        // ---------------- fc1 / fc2 + ReLU (:217-221): 128 rows
-                        const float *bb = P.bias + (size_t)2 * MT_GRU * 2 * GRU_ROWS + (size_t)(p - 2) * FCD + mt * FC_ROWS;
-                        for (int c0 = 0; c0 < NT; c0 += 32) {
-                            if (half == 0) {
-                                uint32_t r[32];
-                                tmem_ld32(tb + ((uint32_t)(q * 32) << 16) + buf * 256u + (uint32_t)c0, r);
-                                float *dst = stg + (q * 32 + lane) * 33;
-#pragma unroll
-                                for (int i = 0; i < 32; i++) dst[i] = __uint_as_float(r[i]);
-                            }
-                            epi_bar();
-                            const int f = etid & 31, rg = etid >> 5, fi = c0 + f;
-                            if (fi < NT) {
-                                const size_t fold = (size_t)nt * NT + fi;
-                                float v[16];
-#pragma unroll
-                                for (int i = 0; i < 16; i++)
-                                    v[i] = fmaxf(stg[(rg * 16 + i) * 33 + f] + __ldg(bb + rg * 16 + i), 0.f);
-                                const int gr = mt * FC_ROWS + rg * 16;
-                                if (p == 2) {
-#pragma unroll
-                                    for (int c = 0; c < 2; c++) {
-                                        const float v0[4] = {v[8 * c], v[8 * c + 1], v[8 * c + 2], v[8 * c + 3]};
-                                        const float v1[4] = {v[8 * c + 4], v[8 * c + 5], v[8 * c + 6], v[8 * c + 7]};
-                                        uint2 h0, l0, h1, l1;
-                                        split4(v0, h0, l0);
-                                        split4(v1, h1, l1);
-                                        *reinterpret_cast<uint4 *>(P.Y1 + b_slot(NT, HGROUPS, nt, (gr >> 3) + c, fi, 0)) =
-                                            make_uint4(h0.x, h0.y, h1.x, h1.y);
-                                        *reinterpret_cast<uint4 *>(P.Y1 + b_slot(NT, HGROUPS, nt, (gr >> 3) + c, fi, 1)) =
-                                            make_uint4(l0.x, l0.y, l1.x, l1.y);
-                                    }
-                                } else {
-                                    float4 *dst = reinterpret_cast<float4 *>(P.y2f + fold * FCD + gr);
-#pragma unroll
-                                    for (int c = 0; c < 4; c++) dst[c] = make_float4(v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
-                                }
-                            }
-                            epi_bar();
-                        }
-                    }
-                    tc_fence_before();
-                    epi_bar();
-                    if (etid == 0) mbar_arrive(&bar_tempty[buf]);        // TMEM buffer drained
-                }
-                // phase p of step t finished by this CTA: publish
-                fence_proxy_async_global();
-                epi_bar();
-                if (etid == 0) { fence_proxy_async_global(); red_release_add_u64(phase_counter(P.gs, p), 1ull); }
+            if (has_gru) {
+                wait_acc();
+                if (etid == 0) PROF_MARK(20);
+                epi_gru(P, 0, mt_g, nt_g, t, tb, stg, etid, q, half, lane);
+                tc_fence_before();
             }
-            // ---------------- fc3 (:223) in fp32 + MoL draw (utils/distribution.py:87-123) + next conditioning operand
+            publish(0);
+            if (etid == 0) PROF_MARK(21);
+            if (has_gru) {
+                wait_acc();
+                if (etid == 0) PROF_MARK(22);
+                epi_gru(P, 1, mt_g, nt_g, t, tb, stg, etid, q, half, lane);
+                tc_fence_before();
+            }
+            publish(1);
+            if (etid == 0) PROF_MARK(23);
+            if (has_fc) {
+                wait_acc();
+                if (etid == 0) PROF_MARK(24);
+                epi_fc(P, 0, mt_f, nt_f, tb, stg, etid, q, half, lane);
+                tc_fence_before();
+            }
+            publish(2);
+            if (etid == 0) PROF_MARK(25);
+            if (has_fc) {
+                wait_acc();
+                if (etid == 0) PROF_MARK(26);
+                epi_fc(P, 1, mt_f, nt_f, tb, stg, etid, q, half, lane);
+                tc_fence_before();
+            }
+            publish(3);
+            if (etid == 0) PROF_MARK(27);
+            // ---------------- fc3 (:223) in fp32 + MoL draw (utils/distribution.py:87-123) + next conditioning operand.
+            // What does not depend on fc2 is done before the wait: next step's conditioning row (HBM) and the noise.
+            const int64_t bfirst = cta + (int64_t)G * ewarp;
+            float myu1 = 0.5f, u2 = 0.5f;
+            auto draw_noise = [&](int64_t b) {
+                if (P.a.u1) {
+                    if (lane < nmix) myu1 = P.a.u1[((size_t)t * P.a.Btot + P.a.b0 + b) * nmix + lane];
+                    u2 = P.a.u2[(size_t)t * P.a.Btot + P.a.b0 + b];
+                } else {
+                    const uint4 r4 = philox4x32(make_uint4((uint32_t)t, (uint32_t)(P.a.b0 + b), (uint32_t)(lane >> 2), 1u), key);
+                    const uint32_t rr[4] = {r4.x, r4.y, r4.z, r4.w};
+                    myu1 = u_clip(rr[lane & 3]);
+                    const uint4 r2 = philox4x32(make_uint4((uint32_t)t, (uint32_t)(P.a.b0 + b), 0u, 2u), key);
+                    u2 = u_clip(r2.x);
+                }
+            };
+            if (bfirst < B) {
+                load_cond_row(P, bfirst, t + 1, myscr, lane);
+                draw_noise(bfirst);
+            }
             if (etid == 0) grid_wait(P.gs, 3, (unsigned long long)G * (unsigned long long)(t + 1), w);
             epi_bar();
-            for (int64_t b = cta + (int64_t)G * ewarp; b < B; b += (int64_t)G * EPI_WARPS) {
+            if (etid == 0) PROF_MARK(28);
+            for (int64_t b = bfirst; b < B; b += (int64_t)G * EPI_WARPS) {
+                if (b != bfirst) {
+                    load_cond_row(P, b, t + 1, myscr, lane);
+                    draw_noise(b);
+                }
                 float4 y[4];
 #pragma unroll
                 for (int jj = 0; jj < 4; jj++) y[jj] = __ldcg(reinterpret_cast<const float4 *>(P.y2f + (size_t)b * FCD + 128 * jj + lane * 4));
@@ -541,19 +677,7 @@ __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
                 myscr[224 + row] = lg;
                 __syncwarp();
                 const bool live = t < P.a.fold_len[b];
-                if (P.a.logits_out && live && lane < P.NC)
-                    P.a.logits_out[((size_t)b * S + t) * P.NC + lane] = myscr[224 + lane];
-                float myu1 = 0.5f, u2;
-                if (P.a.u1) {
-                    if (lane < nmix) myu1 = P.a.u1[((size_t)t * P.a.Btot + P.a.b0 + b) * nmix + lane];
-                    u2 = P.a.u2[(size_t)t * P.a.Btot + P.a.b0 + b];
-                } else {
-                    const uint4 r4 = philox4x32(make_uint4((uint32_t)t, (uint32_t)(P.a.b0 + b), (uint32_t)(lane >> 2), 1u), key);
-                    const uint32_t rr[4] = {r4.x, r4.y, r4.z, r4.w};
-                    myu1 = u_clip(rr[lane & 3]);
-                    const uint4 r2 = philox4x32(make_uint4((uint32_t)t, (uint32_t)(P.a.b0 + b), 0u, 2u), key);
-                    u2 = u_clip(r2.x);
-                }
+                if (P.a.logits_out && live && lane < P.NC) P.a.logits_out[((size_t)b * S + t) * P.NC + lane] = myscr[224 + lane];
                 int pick = 0;
                 float xv = mol_sample_smem(myscr + 224, nmix, myu1, u2, lane, &pick);
                 if (!live) xv = 0.f;
@@ -562,11 +686,11 @@ __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
                     P.a.picks[(size_t)b * S + t] = pick;
                 }
                 if (P.a.teacher) xv = t + 1 < S ? P.a.teacher[(size_t)b * S + t + 1] : 0.f;
-                write_cond_operand(P, b, t + 1, xv, myscr, lane);
+                build_cond_operand(P, b, xv, myscr, lane);
             }
-            fence_proxy_async_global();
-            epi_bar();
-            if (etid == 0) { fence_proxy_async_global(); red_release_add_u64(phase_counter(P.gs, 4), 1ull); }
+            if (etid == 0) PROF_MARK(29);
+            publish(4);
+            if (etid == 0) PROF_MARK(30);
             // uniform exit on a fired watchdog
             if (etid == 0) stg[0] = (w.dead || ld_volatile_s32(P.gs.abort_flag)) ? 1.f : 0.f;
             epi_bar();
@@ -659,34 +783,34 @@ int mma_plan(wrnn_handle *h) {
         }
         return (e >= C_A4 && e < C_A2) ? F2->v[(size_t)grow * (FCD + AUX) + FCD + (e - C_A4)] : 0.0;
     };
-    auto main_w = [&](int p, int arr, int grow, int k) -> double {
-        switch (arr) {
-            case ARR_H1CUR: return W1h->v[(size_t)grow * H + k];
-            case ARR_H1NEW: return W2i->v[(size_t)grow * (H + AUX) + k];
-            case ARR_H2CUR: return W2h->v[(size_t)grow * H + k];
-            case ARR_S12: return F1->v[(size_t)grow * (H + AUX) + k];
+    // weight on a 512-wide operand column k for job type jt
+    auto main_w = [&](int jt, int grow, int k) -> double {
+        switch (jt) {
+            case J_R2: return W2i->v[(size_t)grow * (H + AUX) + k];
+            case J_S1: return W1h->v[(size_t)grow * H + k];
+            case J_S2: return W2h->v[(size_t)grow * H + k];
+            case J_F1: return F1->v[(size_t)grow * (H + AUX) + k];
             default: return F2->v[(size_t)grow * (FCD + AUX) + k];
         }
-        (void)p;
     };
+    const int cond_phase[NJOB] = {0, 1, -1, -1, 2, 3};     // which layer's conditioning columns a job carries
     size_t total = 0;
-    for (int p = 0; p < 4; p++) {
-        pl.offA[p] = (int64_t)total;
-        const int rows = p < 2 ? GRU_ROWS : FC_ROWS, mts = p < 2 ? MT_GRU : MT_FC;
-        total += (size_t)mts * phase_stages(p) * 2 * KC * rows * 16;
+    for (int jt = 0; jt < NJOB; jt++) {
+        pl.offA[jt] = (int64_t)total;
+        total += (size_t)(jt >= J_F1 ? MT_FC : MT_GRU) * job_stages(jt) * 2 * KC * job_rows(jt) * 16;
     }
     std::vector<uint16_t> img(total / 2 + 2048, 0);       // + slack: the 96-row image is addressed as 128 rows
-    for (int p = 0; p < 4; p++) {
-        const int rows = p < 2 ? GRU_ROWS : FC_ROWS, mts = p < 2 ? MT_GRU : MT_FC, nst = phase_stages(p);
+    for (int jt = 0; jt < NJOB; jt++) {
+        const int rows = job_rows(jt), mts = jt >= J_F1 ? MT_FC : MT_GRU, nst = job_stages(jt);
         for (int mt = 0; mt < mts; mt++)
             for (int s = 0; s < nst; s++) {
-                const StageInfo si = stage_info(p, s);
-                uint16_t *blk = img.data() + (size_t)pl.offA[p] / 2 + ((size_t)mt * nst + s) * (2 * KC * rows * 8);
+                const StageInfo si = stage_info(jt, s);
+                uint16_t *blk = img.data() + (size_t)pl.offA[jt] / 2 + ((size_t)mt * nst + s) * (2 * KC * rows * 8);
                 for (int r = 0; r < rows; r++) {
-                    const int grow = p < 2 ? (r / UT) * H + mt * UT + (r % UT) : mt * FC_ROWS + r;
+                    const int grow = jt < J_F1 ? (r / UT) * H + mt * UT + (r % UT) : mt * FC_ROWS + r;
                     for (int kl = 0; kl < KC * 8; kl++) {
                         const int feat = si.g * 32 + kl;
-                        const double wv = si.arr == ARR_C ? cond_w(p, grow, feat) : main_w(p, si.arr, grow, feat);
+                        const double wv = si.arr == ARR_C ? cond_w(cond_phase[jt], grow, feat) : main_w(jt, grow, feat);
                         const float wf = (float)wv;
                         const uint16_t hi = f2bf(wf), lo = f2bf((float)(wv - (double)bf2f(hi)));
                         const size_t o = ((size_t)(kl / 8) * rows + r) * 8 + kl % 8;
@@ -725,19 +849,27 @@ int mma_plan(wrnn_handle *h) {
     WRNN_CUDA(h, cudaMalloc((void **)&pl.wf3, wf3.size() * 4));
     WRNN_CUDA(h, cudaMemcpy(pl.wf3, wf3.data(), wf3.size() * 4, cudaMemcpyHostToDevice));
     pl.img_bytes = total;
-    pl.smem_bytes = (size_t)NSTAGE * STAGE_BYTES + (size_t)(STG_FLOATS + NCP * FCD + EPI_WARPS * 256) * sizeof(float);
-    if (pl.smem_bytes + 1024 > h->smem_optin) return 0;
+    // everything the device offers minus the static part (barriers): the stage ring takes what staging / fc3 rows leave
+    pl.smem_bytes = (h->smem_optin - 1024) / 1024 * 1024;
+    if (pl.smem_bytes < (size_t)FIXED_SMEM + 2 * (A_FC + 2 * KC * 128 * 16)) return 0;
     WRNN_CUDA(h, cudaFuncSetAttribute(mma::mma_loop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes));
     pl.ok = true;
     return 0;
 }
 
 // fold-tile width: the smallest multiple of 16 that puts the 16 x NTILES GRU jobs of a phase on distinct SMs
+// Fold-tile width N (a multiple of 16, <= 128): every CTA gets at most one GRU job and one fc job per step.  A tcgen05
+// MMA costs max(56, N / 2) clocks whatever N is below 112 (measured, scripts/mb_umma.cu), so narrow tiles are not
+// cheaper per instruction; they only shorten the operand copies and the epilogues.  Preferred: the narrowest tile that
+// gives GRU and fc jobs their own CTAs (20 jobs per fold tile), else the narrowest that fits the 16 GRU jobs per tile.
 int mma_pick_nt(int64_t B, int G) {
+    for (int nt = 16; nt <= 128; nt += 16)
+        if ((int64_t)(mma::MT_GRU + mma::MT_FC) * ((B + nt - 1) / nt) <= G) return nt;
     for (int nt = 16; nt <= 128; nt += 16)
         if ((int64_t)mma::MT_GRU * ((B + nt - 1) / nt) <= G) return nt;
     return 128;
 }
+int64_t mma_max_folds(const wrnn_handle *h) { return (int64_t)128 * (h->num_sms / mma::MT_GRU); }
 
 int mma_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
     using namespace mma;
@@ -747,11 +879,15 @@ int mma_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
     P.G = h->num_sms;
     P.NT = h->mma_force_nt > 0 ? h->mma_force_nt : mma_pick_nt(a.B, P.G);
     P.NTILES = (int)((a.B + P.NT - 1) / P.NT);
+    if (MT_GRU * P.NTILES > P.G)
+        return fail(h, WRNN_ERR_ARG, "tensor-core loop kernel: %lld folds in tiles of %d need %d CTAs, the device has %d",
+                    (long long)a.B, P.NT, MT_GRU * P.NTILES, P.G);
+    P.ring_bytes = (int)(pl.smem_bytes - FIXED_SMEM) / 1024 * 1024;
     P.NC = h->d.NC;
     P.steps_run = a.S;
     if (const char *e = getenv("WRNN_MMA_STEPS")) P.steps_run = std::min<int64_t>(a.S, std::max(1, atoi(e)));
     P.Aimg = pl.Aimg;
-    for (int p = 0; p < 4; p++) P.offA[p] = pl.offA[p];
+    for (int j = 0; j < NJOB; j++) P.offA[j] = pl.offA[j];
     P.bias = pl.bias;
     P.Wf3 = pl.wf3;
     P.bf3 = pl.wf3 + (size_t)NCP * FCD;
@@ -772,9 +908,44 @@ int mma_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
     P.gs.counter = (unsigned long long *)h->ws_mma_sync.p;
     P.gs.abort_flag = (int *)((char *)h->ws_sync.p + 64);             // the call's sticky abort flag (api_run.cu)
     WRNN_CUDA(h, cudaFuncSetAttribute(mma_loop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes));
+    P.prof = nullptr;
+    P.prof_step = -1;
+    const char *pe = getenv("WRNN_MMA_PROF");
+    if (pe) {
+        WRNN_TRY(ws_reserve(h, h->ws_prof, 128 * sizeof(long long)));
+        WRNN_CUDA(h, cudaMemsetAsync(h->ws_prof.p, 0, 128 * sizeof(long long), st));
+        P.prof = (long long *)h->ws_prof.p;
+        P.prof_step = std::min<int64_t>(atoi(pe), P.steps_run - 1);
+    }
     void *args[] = {(void *)&P};
     WRNN_CUDA(h, cudaLaunchCooperativeKernel((const void *)mma_loop_kernel, dim3(P.G), dim3(THREADS), args, pl.smem_bytes, st));
     h->launches++;
+    if (pe) {     // debug: print the timeline of the profiled step (clocks relative to the CTA's first event of the step)
+        std::vector<long long> pr(128);
+        WRNN_CUDA(h, cudaStreamSynchronize(st));
+        WRNN_CUDA(h, cudaMemcpy(pr.data(), P.prof, 128 * sizeof(long long), cudaMemcpyDeviceToHost));
+        static const char *names[32] = {
+            "producer: step begin", "producer: rnn1 issued", "producer: rnn2 issued", "producer: recurrent-1 issued", "producer: fc begin",
+            "producer: fc1 issued", "producer: fc2 issued", "producer: recurrent-2 issued", "", "",
+            "mma: rnn1 issued", "mma: rnn2 issued", "mma: recurrent-1 issued", "mma: fc1 issued", "mma: fc2 issued", "mma: recurrent-2 issued",
+            "", "", "", "",
+            "epilogue: rnn1 accumulators ready", "epilogue: rnn1 published", "epilogue: rnn2 accumulators ready", "epilogue: rnn2 published",
+            "epilogue: fc1 accumulator ready", "epilogue: fc1 published", "epilogue: fc2 accumulator ready", "epilogue: fc2 published",
+            "fc3 phase: fc2 of all CTAs seen", "fc3 phase: folds done", "fc3 phase: published", ""};
+        for (int c = 0; c < 2; c++) {
+            const long long *q = pr.data() + 64 * c;
+            long long t0 = 0;
+            for (int i = 0; i < 32; i++)
+                if (q[i] && (!t0 || q[i] < t0)) t0 = q[i];
+            fprintf(stderr, "[mma prof] CTA %s, step %lld, folds %lld, fold tile %d\n", c == 0 ? "0" : "G-1", (long long)P.prof_step,
+                    (long long)a.B, P.NT);
+            std::vector<std::pair<long long, int>> ev;
+            for (int i = 0; i < 32; i++)
+                if (q[i]) ev.push_back({q[i] - t0, i});
+            std::sort(ev.begin(), ev.end());
+            for (auto &e : ev) fprintf(stderr, "[mma prof]   %8lld  %s\n", e.first, names[e.second]);
+        }
+    }
     return 0;
 }
 
