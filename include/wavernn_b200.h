@@ -120,6 +120,19 @@ int wrnn_fold(wrnn_handle *h, const float *x, int64_t L, int32_t F, int64_t targ
  * out (folds*(target+overlap)+overlap) float64. */
 int wrnn_unfold(wrnn_handle *h, const double *y, int64_t folds, int64_t target, int64_t overlap,
                 double *out);
+/* wrnn_unfold without any allocation.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  Same
+ * arguments, arithmetic and result as wrnn_unfold (xfade_and_unfold, fatchord_version.py:342-405); the device scratch
+ * (device copy of y, fade tables, device output) is a file-scope static __device__ array of WRNN_NOALLOC_MAX_DOUBLES
+ * doubles (4 MiB, held by every GPU that loads the library until exit), so the call performs no cudaMalloc / cudaFree /
+ * host allocation.  Needs folds*(target+2*overlap) + folds*(target+overlap)+overlap + 2*overlap <= WRNN_NOALLOC_MAX_DOUBLES
+ * and overlap <= WRNN_NOALLOC_MAX_OVERLAP, else WRNN_ERR_ARG with a message.  All calls on a device share the array, which
+ * keeps the last call's contents (nothing in it must start at zero); calls that overlap on the GPU race: serialise them.
+ * `cuda_stream` as in wrnn_generate; returns after the result is on the host. */
+#define WRNN_NOALLOC_MAX_DOUBLES 524288
+#define WRNN_NOALLOC_MAX_OVERLAP 4096
+int wrnn_unfold_noalloc(wrnn_handle *h, const double *y, int64_t folds, int64_t target, int64_t overlap, double *out,
+                        void *cuda_stream);
 /* decode_mu_law(y, mu, from_labels=False) (utils/dsp.py:98-103) for samples y = 2k/(mu-1)-1 given
  * as float32; out float64.  wrnn_mulaw_lut (host only, no GPU) fills the mu-entry table. */
 int wrnn_decode_mu_law(wrnn_handle *h, const float *y, int64_t n, int32_t mu, double *out);

@@ -55,6 +55,7 @@ _SIGS = {
     'wrnn_num_folds': (C.c_int64, [C.c_int64, C.c_int64, C.c_int64]),
     'wrnn_fold': (C.c_int, [_P, _P, C.c_int64, C.c_int32, C.c_int64, C.c_int64, _P]),
     'wrnn_unfold': (C.c_int, [_P, _P, C.c_int64, C.c_int64, C.c_int64, _P]),
+    'wrnn_unfold_noalloc': (C.c_int, [_P, _P, C.c_int64, C.c_int64, C.c_int64, _P, _P]),
     'wrnn_decode_mu_law': (C.c_int, [_P, _P, C.c_int64, C.c_int32, _P]),
     'wrnn_mulaw_lut': (C.c_int, [C.c_int32, _P]),
     'wrnn_set_mulaw_lut': (C.c_int, [_P, C.c_int32, _P]),
@@ -303,6 +304,17 @@ class Vocoder:
         target = length - 2 * overlap          # recomputed like fatchord_version.py:375
         out = np.empty(folds * (target + overlap) + overlap, dtype=np.float64)
         self._ck(lib().wrnn_unfold(self._h, _ptr(y), folds, target, overlap, _ptr(out)))
+        return out
+
+    def unfold_noalloc(self, y, target, overlap, out=None, stream=None):
+        """wrnn_unfold_noalloc: same result as `unfold`, device scratch in a static array (no cudaMalloc); `out` may be
+        a caller-owned float64 array so that the call allocates nothing on the host side either."""
+        y = np.ascontiguousarray(y, dtype=np.float64)
+        folds, length = y.shape
+        target = length - 2 * overlap
+        if out is None:
+            out = np.empty(folds * (target + overlap) + overlap, dtype=np.float64)
+        self._ck(lib().wrnn_unfold_noalloc(self._h, _ptr(y), folds, target, overlap, _ptr(out), stream))
         return out
 
     def decode_mu_law(self, y, mu):
