@@ -392,6 +392,61 @@ __global__ void __launch_bounds__(64, 1) mma_chain(int N, int nacc, int nmma, lo
     if (warp == 1) tmem_dealloc(tb, 512);
 }
 
+// Same streaming test with the issuers as LANES OF ONE WARP (mode 0) or with mbarrier.test_wait polling instead of try_wait
+// (mode 1, issuers = warps): what is the ~680 clk per copy per issuing thread made of?
+__device__ __forceinline__ bool mbar_test_wait(void *b, uint32_t parity) {
+    uint32_t ok;
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(ok) : "r"(smem_u32(b)), "r"(parity) : "memory");
+    return ok != 0;
+}
+__global__ void __launch_bounds__(256, 1) l2_stream3(const uint8_t *buf, size_t buf_bytes, uint32_t chunk, int nring, int per_issuer, int nissue,
+                                                     int mode, long long *out) {
+    extern __shared__ __align__(128) uint8_t sm[];
+    __shared__ __align__(8) uint64_t bars[8][8];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) {
+        for (int w = 0; w < 8; w++)
+            for (int i = 0; i < 8; i++) mbar_init(&bars[w][i], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    const int me = mode == 0 ? lane : warp;
+    const bool active = mode == 0 ? (warp == 0 && lane < nissue) : (warp < nissue && lane == 0);
+    if (active) {
+        uint8_t *ring = sm + (size_t)me * nring * chunk;
+        const size_t per = buf_bytes / chunk;
+        size_t pos = ((size_t)blockIdx.x * 37 + me * 101) % per;
+        const long long t0 = clock64();
+        int issued = 0, done = 0;
+        bool ok = true;
+        for (; issued < nring && issued < per_issuer; issued++) {
+            mbar_expect_tx(&bars[me][issued], chunk);
+            bulk_g2s(ring + (size_t)issued * chunk, buf + pos * chunk, chunk, &bars[me][issued]);
+            pos = (pos + 1) % per;
+        }
+        while (done < per_issuer && ok) {
+            const int slot = done % nring;
+            const uint32_t par = (uint32_t)((done / nring) & 1);
+            if (mode == 1) {
+                const long long w0 = clock64();
+                while (!mbar_test_wait(&bars[me][slot], par))
+                    if (clock64() - w0 > 200000000ll) { ok = false; break; }
+            } else {
+                ok = mbar_wait(&bars[me][slot], par);
+            }
+            done++;
+            if (issued < per_issuer) {
+                mbar_expect_tx(&bars[me][slot], chunk);
+                bulk_g2s(ring + (size_t)slot * chunk, buf + pos * chunk, chunk, &bars[me][slot]);
+                pos = (pos + 1) % per;
+                issued++;
+            }
+        }
+        if (me == 0) out[blockIdx.x] = ok ? clock64() - t0 : -1;
+    }
+}
+
 static float bf16_round(float x) { return __bfloat162float(__float2bfloat16(x)); }
 
 int main(int argc, char **argv) {
@@ -440,6 +495,38 @@ int main(int argc, char **argv) {
     cudaDeviceProp prop;
     CK(cudaGetDeviceProperties(&prop, dev));
     printf("device %s, %d SMs, cc %d.%d\n", prop.name, prop.multiProcessorCount, prop.major, prop.minor);
+
+    // ---- streaming: issuers as lanes of one warp / test_wait polling
+    if (argc > 1 && !strcmp(argv[1], "stream3")) {
+        CK(cudaFuncSetAttribute(l2_stream3, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        const size_t bytes = 16u << 20;
+        uint8_t *buf;
+        long long *dout;
+        CK(cudaMalloc(&buf, bytes));
+        CK(cudaMemset(buf, 1, bytes));
+        CK(cudaMalloc(&dout, 148 * sizeof(long long)));
+        struct Cfg { uint32_t chunk; int nring, nissue, mode; };
+        const Cfg cfgs[] = {{12288, 4, 1, 0}, {12288, 4, 2, 0}, {12288, 4, 4, 0}, {12288, 2, 8, 0}, {12288, 4, 1, 1}, {12288, 4, 4, 1},
+                            {24576, 2, 4, 0}, {24576, 4, 2, 0}, {24576, 2, 4, 1}, {4096, 4, 4, 0}, {4096, 4, 8, 0}};
+        for (int grid : {1, 148})
+            for (const Cfg &c : cfgs) {
+                const int per = (int)((4u << 20) / c.chunk / c.nissue);
+                const size_t smem = (size_t)c.nring * c.chunk * c.nissue;
+                if (smem > 200 * 1024) continue;
+                for (int rep = 0; rep < 2; rep++) {
+                    l2_stream3<<<grid, 256, smem>>>(buf, bytes, c.chunk, c.nring, per, c.nissue, c.mode, dout);
+                    CK(cudaDeviceSynchronize());
+                }
+                std::vector<long long> o(grid);
+                CK(cudaMemcpy(o.data(), dout, grid * sizeof(long long), cudaMemcpyDeviceToHost));
+                long long mx = 0;
+                for (auto v : o) mx = v > mx ? v : mx;
+                printf("l2 stream3 grid=%3d chunk=%5u ring=%d issuers=%d (%s): %.1f B/clk/SM, %.0f clk per copy per issuer\n", grid, c.chunk,
+                       c.nring, c.nissue, c.mode == 0 ? "lanes of one warp, try_wait" : "warps, test_wait poll",
+                       (double)per * c.nissue * c.chunk / mx, (double)mx / per);
+            }
+        return 0;
+    }
     CK(cudaFuncSetAttribute(umma_test, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     CK(cudaFuncSetAttribute(l2_stream, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     long long *dclk;

@@ -143,7 +143,7 @@ void wrnn_destroy(wrnn_handle *h) {
                         &h->ws_teacher, &h->ws_logits, &h->ws_prof};
     for (Workspace *w : all)
         if (w->p) cudaFree(w->p);
-    float *ptrs[] = {h->cp.conv_in_t, h->cp.bn_scale, h->cp.bn_shift, h->cp.res_t, h->cp.conv_out_t, h->cp.conv_out_b,
+    float *ptrs[] = {h->cp.poly, h->cp.conv_in_t, h->cp.bn_scale, h->cp.bn_shift, h->cp.res_t, h->cp.conv_out_t, h->cp.conv_out_b,
                      h->fma.image, h->pipe.row_image, h->pipe.tail_image, h->res.img, h->res.tail_img,
                      (float *)h->mma.Aimg, h->mma.bias, h->mma.wf3};
     for (float *p : ptrs)

@@ -17,15 +17,22 @@ struct StageOpts {
 
 static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
-// Layout of ws_meta (device): FoldMeta[B] | TailMeta[n_utt] | int32 fold_len[B]
-struct MetaLayout { size_t off_fold, off_tail, off_len, bytes; };
-static MetaLayout meta_layout(int64_t B, int n_utt) {
+// Layout of ws_meta (device): FoldMeta[B] | TailMeta[n_utt] | int32 fold_len[B] | UttMeta[n_utt] | ResTile[n_tiles]
+struct MetaLayout { size_t off_fold, off_tail, off_len, off_utt, off_tile, bytes; };
+static MetaLayout meta_layout(int64_t B, int n_utt, int64_t n_tiles) {
     MetaLayout m;
     m.off_fold = 0;
     m.off_tail = align_up(sizeof(FoldMeta) * B, 64);
     m.off_len = m.off_tail + align_up(sizeof(TailMeta) * n_utt, 64);
-    m.bytes = m.off_len + align_up(sizeof(int32_t) * B, 64);
+    m.off_utt = m.off_len + align_up(sizeof(int32_t) * B, 64);
+    m.off_tile = m.off_utt + align_up(sizeof(UttMeta) * n_utt, 64);
+    m.bytes = m.off_tile + align_up(sizeof(ResTile) * (size_t)n_tiles, 64);
     return m;
+}
+static int64_t count_res_tiles(const wrnn_handle *h) {
+    int64_t n = 0;
+    for (auto &ut : h->utts) n += (ut.T + resnet_tile_frames() - 1) / resnet_tile_frames();
+    return n;
 }
 // Layout of ws_tables (device doubles): fade_in[ov] | fade_out[ov] | fo[20*hop] | lut[NC]
 struct TableLayout { size_t fin, fout, fo, lut, n; };
@@ -53,7 +60,7 @@ int do_stage(wrnn_handle *h, const float *const *mels, const int32_t *T, int32_t
     h->overlap = batched ? overlap : 0;
     h->mu_law = (d.mode == WRNN_MODE_RAW && mu_law) ? 1 : 0;     // fatchord_version.py:174
     h->utts.clear();
-    int64_t mel_off = 0, up_off = 0, res_off = 0, out_off = 0, fold0 = 0, Smax = 0;
+    int64_t mel_off = 0, up_off = 0, res_off = 0, out_off = 0, fold0 = 0, Smax = 0, pm_off = 0;
     for (int u = 0; u < n_utt; u++) {
         wrnn_handle::Utt ut;
         const int Tin = T[u];
@@ -74,6 +81,7 @@ int do_stage(wrnn_handle *h, const float *const *mels, const int32_t *T, int32_t
         }
         ut.fold0 = fold0; fold0 += ut.nfolds;
         ut.mel_off = mel_off; mel_off += (int64_t)d.F * Tin;
+        ut.Tin = Tin; ut.Tp = ut.T + 2 * d.pad; ut.pm_off = pm_off; pm_off += ut.Tp;
         ut.up_off = up_off; up_off += ut.L;
         ut.res_off = res_off; res_off += ut.T;
         ut.out_off = out_off; out_off += ut.wave_len;
@@ -94,24 +102,31 @@ int do_stage(wrnn_handle *h, const float *const *mels, const int32_t *T, int32_t
     }
     for (int u = 0; u < n_utt; u++)
         memcpy(h->h_pinned_in + h->utts[u].mel_off, mels[u], (size_t)d.F * T[u] * sizeof(float));
-    size_t padded_floats = 0;
-    for (auto &ut : h->utts) padded_floats += (size_t)d.F * (ut.T + 2 * d.pad);
-    WRNN_TRY(ws_reserve(h, h->ws_mel, mel_bytes + padded_floats * sizeof(float) + 256));
+    h->total_frames = pm_off;
+    const size_t padded_floats = (size_t)pm_off * d.F;       // frame-major padded mels, filled by run
+    WRNN_TRY(ws_reserve(h, h->ws_mel, mel_bytes + padded_floats * sizeof(float) + 512));
     WRNN_CUDA(h, cudaMemcpyAsync(h->ws_mel.p, h->h_pinned_in, mel_bytes, cudaMemcpyHostToDevice, st));
 
     // ---- meta ----
-    const MetaLayout ml = meta_layout(h->B, n_utt);
+    const int64_t n_tiles = count_res_tiles(h);
+    const MetaLayout ml = meta_layout(h->B, n_utt, n_tiles);
     std::vector<char> hm(ml.bytes, 0);
     FoldMeta *fm = (FoldMeta *)(hm.data() + ml.off_fold);
     TailMeta *tm = (TailMeta *)(hm.data() + ml.off_tail);
     int32_t *fl = (int32_t *)(hm.data() + ml.off_len);
+    UttMeta *um = (UttMeta *)(hm.data() + ml.off_utt);
+    ResTile *rt = (ResTile *)(hm.data() + ml.off_tile);
+    int64_t ti = 0;
     for (int u = 0; u < n_utt; u++) {
         const auto &ut = h->utts[u];
         for (int64_t i = 0; i < ut.nfolds; i++) {
-            fm[ut.fold0 + i] = FoldMeta{ut.up_off, ut.res_off, batched ? i * ((int64_t)target + overlap) : 0, ut.L};
+            fm[ut.fold0 + i] = FoldMeta{ut.pm_off, ut.res_off, batched ? i * ((int64_t)target + overlap) : 0, ut.L, ut.Tp, d.pad};
             fl[ut.fold0 + i] = (int32_t)(batched ? h->S : ut.L);
         }
         tm[u] = TailMeta{ut.fold0, ut.nfolds, ut.wave_len, ut.out_off};
+        // already-padded input (forward_logits): all Tp frames come from the caller, no zero frames added
+        um[u] = UttMeta{ut.mel_off, ut.pm_off, ut.res_off, ut.T, ut.Tp, ut.Tin, o.prepadded ? 0 : d.pad};
+        for (int t0 = 0; t0 < ut.T; t0 += resnet_tile_frames()) rt[ti++] = ResTile{u, t0};
     }
     WRNN_TRY(ws_reserve(h, h->ws_meta, ml.bytes));
     WRNN_CUDA(h, cudaMemcpyAsync(h->ws_meta.p, hm.data(), ml.bytes, cudaMemcpyHostToDevice, st));
@@ -155,7 +170,6 @@ int do_stage(wrnn_handle *h, const float *const *mels, const int32_t *T, int32_t
                                      cudaMemcpyHostToDevice, st));
     }
     // ---- device workspaces for run ----
-    WRNN_TRY(ws_reserve(h, h->ws_up, (size_t)up_off * d.F * sizeof(float)));
     WRNN_TRY(ws_reserve(h, h->ws_res, (size_t)res_off * d.R * sizeof(float)));
     WRNN_TRY(ws_reserve(h, h->ws_cond, (size_t)h->B * h->S * (d.F + d.R) * sizeof(float)));
     WRNN_TRY(ws_reserve(h, h->ws_samples, (size_t)h->B * h->S * sizeof(float)));
@@ -172,31 +186,22 @@ int do_run(wrnn_handle *h, uint64_t seed, cudaStream_t st, const StageOpts &o) {
     WRNN_DEVICE(h);
     h->launches = 0;
     const int n_utt = (int)h->utts.size();
-    const MetaLayout ml = meta_layout(h->B, n_utt);
+    const int64_t n_tiles = count_res_tiles(h);
+    const MetaLayout ml = meta_layout(h->B, n_utt, n_tiles);
     const TableLayout tl = table_layout(h);
     float *mel_raw = (float *)h->ws_mel.p;
     size_t raw_floats = 0;
-    for (auto &ut : h->utts) raw_floats += (size_t)d.F * (o.prepadded ? ut.T + 2 * d.pad : ut.T);
-    float *mel_pad = mel_raw + align_up(raw_floats, 64);
+    for (auto &ut : h->utts) raw_floats += (size_t)d.F * ut.Tin;
+    float *melT = mel_raw + align_up(raw_floats, 64);
+    const UttMeta *d_utt = (const UttMeta *)((char *)h->ws_meta.p + ml.off_utt);
     WRNN_CUDA(h, cudaEventRecord(h->ev[0], st));
-    // conditioning per utterance (fatchord_version.py:185-186)
-    size_t poff = 0;
-    for (auto &ut : h->utts) {
-        const int Tp = ut.T + 2 * d.pad;
-        const float *mp;
-        if (o.prepadded) {
-            mp = mel_raw + ut.mel_off;
-        } else {
-            WRNN_TRY(launch_pad_mel(h, mel_raw + ut.mel_off, ut.T, mel_pad + poff, st));
-            mp = mel_pad + poff;
-        }
-        WRNN_TRY(run_conditioning(h, mp, Tp, (float *)h->ws_up.p + (size_t)ut.up_off * d.F,
-                                  (float *)h->ws_res.p + (size_t)ut.res_off * d.R, st));
-        poff += (size_t)d.F * Tp;
-    }
-    // fold (:188-190); unbatched = one fold per utterance
-    WRNN_TRY(launch_fold_cond(h, (const float *)h->ws_up.p, (const float *)h->ws_res.p,
-                              (const FoldMeta *)((char *)h->ws_meta.p + ml.off_fold), h->B, h->S, (float *)h->ws_cond.p, st));
+    // conditioning of every utterance of the call (fatchord_version.py:185-190) in three launches: pad + transpose,
+    // MelResNet, and the fold rows [mel (polyphase upsampling) | aux (x hop repeat by index)]
+    WRNN_TRY(launch_pad_mel_batch(h, mel_raw, d_utt, n_utt, h->total_frames, melT, st));
+    WRNN_TRY(launch_resnet_batch(h, melT, d_utt, (const ResTile *)((char *)h->ws_meta.p + ml.off_tile), (int)n_tiles,
+                                 (float *)h->ws_res.p, st));
+    WRNN_TRY(launch_fold_cond(h, melT, (const float *)h->ws_res.p, (const FoldMeta *)((char *)h->ws_meta.p + ml.off_fold), h->B,
+                              h->S, (float *)h->ws_cond.p, st));
     WRNN_CUDA(h, cudaEventRecord(h->ev[1], st));
     // per-sample loop (:201-241)
     LoopArgs a;
@@ -382,15 +387,24 @@ int wrnn_upsample(wrnn_handle *h, const float *mel, int32_t T, float *mels_out, 
     WRNN_TRY(ensure_packed_public(h));
     const int Tp = T + 2 * d.pad;
     const int64_t L = (int64_t)T * d.hop;
+    const int n_tiles = (T + resnet_tile_frames() - 1) / resnet_tile_frames();
     const size_t raw = align_up((size_t)d.F * T, 64), padf = (size_t)d.F * Tp;
-    WRNN_TRY(ws_reserve(h, h->ws_mel, (raw + padf) * sizeof(float)));
+    WRNN_TRY(ws_reserve(h, h->ws_mel, (raw + padf) * sizeof(float) + 512));
     WRNN_TRY(ws_reserve(h, h->ws_up, (size_t)L * d.F * sizeof(float)));
     WRNN_TRY(ws_reserve(h, h->ws_res, (size_t)T * d.R * sizeof(float)));
     WRNN_TRY(ws_reserve(h, h->ws_cond, (size_t)L * d.R * sizeof(float)));
-    float *mraw = (float *)h->ws_mel.p, *mpad = mraw + raw;
+    const MetaLayout ml = meta_layout(1, 1, n_tiles);
+    std::vector<char> hm(ml.bytes, 0);
+    *(UttMeta *)(hm.data() + ml.off_utt) = UttMeta{0, 0, 0, T, Tp, T, d.pad};
+    for (int i = 0; i < n_tiles; i++) ((ResTile *)(hm.data() + ml.off_tile))[i] = ResTile{0, i * resnet_tile_frames()};
+    WRNN_TRY(ws_reserve(h, h->ws_meta, ml.bytes));
+    WRNN_CUDA(h, cudaMemcpyAsync(h->ws_meta.p, hm.data(), ml.bytes, cudaMemcpyHostToDevice, 0));
+    float *mraw = (float *)h->ws_mel.p, *melT = mraw + raw;
+    const UttMeta *d_utt = (const UttMeta *)((char *)h->ws_meta.p + ml.off_utt);
     WRNN_CUDA(h, cudaMemcpyAsync(mraw, mel, (size_t)d.F * T * sizeof(float), cudaMemcpyHostToDevice, 0));
-    WRNN_TRY(launch_pad_mel(h, mraw, T, mpad, 0));
-    WRNN_TRY(run_conditioning(h, mpad, Tp, (float *)h->ws_up.p, (float *)h->ws_res.p, 0));
+    WRNN_TRY(launch_pad_mel_batch(h, mraw, d_utt, 1, Tp, melT, 0));
+    WRNN_TRY(launch_resnet_batch(h, melT, d_utt, (const ResTile *)((char *)h->ws_meta.p + ml.off_tile), n_tiles, (float *)h->ws_res.p, 0));
+    WRNN_TRY(launch_upsample_flat(h, melT, Tp, L, (float *)h->ws_up.p, 0));
     WRNN_TRY(launch_repeat_aux(h, (const float *)h->ws_res.p, T, (float *)h->ws_cond.p, 0));
     WRNN_CUDA(h, cudaMemcpyAsync(mels_out, h->ws_up.p, (size_t)L * d.F * sizeof(float), cudaMemcpyDeviceToHost, 0));
     WRNN_CUDA(h, cudaMemcpyAsync(aux_out, h->ws_cond.p, (size_t)L * d.R * sizeof(float), cudaMemcpyDeviceToHost, 0));

@@ -87,138 +87,244 @@ int pack_cond(wrnn_handle *h) {
         if (!fw) return WRNN_ERR_STATE;
         WRNN_TRY(upload(h, &h->cp.fir[j], fw->v));
     }
+    // ---- the mel branch as one polyphase filter -------------------------------------------------
+    // UpsampleNetwork.forward (fatchord_version.py:86-88) is, per stage, nearest-repeat by s and a (2s+1)-tap FIR with
+    // zero padding.  Repeat + FIR is linear and shift-invariant in whole frames, so the composition of all stages maps
+    // padded mel frames to upsampled samples as  up[i] = sum_j g(i - j * hop) * mel[j].  g is the response to a unit
+    // impulse, formed here once in double by running the stages on an impulse; it is non-zero for a few frames around
+    // i / hop only, which gives a [hop][taps] table.  Zero padding per stage equals extending the padded mel with zeros:
+    // a stage reaches one input element to each side, and outside the signal both read zero.
+    {
+        const int hop = d.total_scale, Tn = 2 * d.nup + 5, c = Tn / 2;
+        std::vector<double> x(Tn, 0.0);
+        x[c] = 1.0;
+        for (int j = 0; j < d.nup; j++) {
+            const int sc_ = d.up[j];
+            const HostTensor *fw = need(h, "upsample.up_layers." + std::to_string(2 * j + 1) + ".weight", {1, 1, 1, 2 * sc_ + 1});
+            if (!fw) return WRNN_ERR_STATE;
+            const int64_t n_out = (int64_t)x.size() * sc_;
+            std::vector<double> y((size_t)n_out, 0.0);
+            for (int64_t i = 0; i < n_out; i++) {
+                double acc = 0.0;
+                for (int t2 = 0; t2 <= 2 * sc_; t2++) {
+                    const int64_t pidx = i + t2 - sc_;
+                    if (pidx >= 0 && pidx < n_out) acc += (double)fw->v[t2] * x[(size_t)(pidx / sc_)];
+                }
+                y[(size_t)i] = acc;
+            }
+            x.swap(y);
+        }
+        // x[i] = g(i - c * hop); tap k of phase p is g(p - k * hop) = x[(c - k) * hop + p]
+        int kmin = 0, kmax = 0;
+        for (int k = -(Tn - 1 - c); k <= c; k++)
+            for (int ph = 0; ph < hop; ph++)
+                if (x[(size_t)((c - k) * hop + ph)] != 0.0) { kmin = k < kmin ? k : kmin; kmax = k > kmax ? k : kmax; }
+        if (kmin <= -(Tn - 1 - c) || kmax >= c) return fail(h, WRNN_ERR_ARG, "upsample network reaches further than expected");
+        const int taps = kmax - kmin + 1;
+        std::vector<float> tab((size_t)hop * taps);
+        for (int ph = 0; ph < hop; ph++)
+            for (int k = kmin; k <= kmax; k++) tab[(size_t)ph * taps + (k - kmin)] = (float)x[(size_t)((c - k) * hop + ph)];
+        WRNN_TRY(upload(h, &h->cp.poly, tab));
+        h->cp.poly_taps = taps;
+        h->cp.poly_kmin = kmin;
+    }
+    return 0;
+}
+
+// ============================================================================ pad + transpose
+// pad_tensor (fatchord_version.py:281-291) for every utterance of the call, written frame-major: melT[frame][f], so the
+// kernels below read whole frames with 16-byte loads.  Raw mels are (F, Tin) row-major; `pad_` zero frames each side.
+__global__ void pad_mel_batch_kernel(const float *__restrict__ mel_raw, const UttMeta *__restrict__ utts, int n_utt, int F,
+                                     int64_t total, float *__restrict__ melT) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= total * F) return;
+    const int64_t fr = i / F;
+    const int f = (int)(i % F);
+    int lo = 0, hi = n_utt - 1;                    // utterance of this frame: pm_off is ascending
+    while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (utts[mid].pm_off <= fr) lo = mid;
+        else hi = mid - 1;
+    }
+    const UttMeta m = utts[lo];
+    const int t = (int)(fr - m.pm_off) - m.pad_;
+    melT[i] = (t >= 0 && t < m.Tin) ? mel_raw[m.raw_off + (size_t)f * m.Tin + t] : 0.f;
+}
+
+int launch_pad_mel_batch(wrnn_handle *h, const float *mel_raw, const UttMeta *utts, int n_utt, int64_t total_frames,
+                         float *melT, cudaStream_t st) {
+    const int64_t n = total_frames * h->d.F;
+    pad_mel_batch_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(mel_raw, utts, n_utt, h->d.F, total_frames, melT);
+    h->launches++;
+    WRNN_CUDA(h, cudaGetLastError());
     return 0;
 }
 
 // ============================================================================ MelResNet
-// One CTA owns RES_TT consecutive frames and carries them through every layer: after conv_in all
-// layers are 1x1 in time, so tiles are independent.  Thread c owns output channel c; weights are
-// pre-transposed [k][c] so a warp reads 128 contiguous bytes per k; activations are smem broadcasts.
-constexpr int RES_TT = 8;
+// MelResNet (fatchord_version.py:31-48) for every utterance of the call in one launch.  One CTA carries RES_TT
+// consecutive frames of one utterance through every layer (after conv_in all layers are 1x1 in time, so tiles are
+// independent).  Each layer is a [Cout x K] . [K x RES_TT] product: the weights stream from L2 through a double-buffered
+// 2 x 64 KB shared-memory stage (cp.async, next chunk in flight while this one is used: the first version read them with
+// dependent __ldg loads and was latency-bound at 0.8 TFLOP/s), activations are shared-memory broadcasts, thread
+// (c, half) owns channel c for four frames.  BatchNorm is folded to scale/shift (eval mode, eps 1e-5).
+constexpr int RES_TT = 8, RES_THREADS = 256, RES_WBUF = 16384, RES_MAXCI = 4;
+int resnet_tile_frames() { return RES_TT; }
 
-__device__ __forceinline__ void res_matvec(const float *__restrict__ Wt, int K, int ldw, int c,
-                                           const float *act, float (&acc)[RES_TT]) {
-#pragma unroll
-    for (int t = 0; t < RES_TT; t++) acc[t] = 0.f;
-    for (int k = 0; k < K; k++) {
-        const float w = __ldg(Wt + (size_t)k * ldw + c);
-        const float *a = act + k * RES_TT;
-#pragma unroll
-        for (int t = 0; t < RES_TT; t++) acc[t] = fmaf(w, a[t], acc[t]);
-    }
+struct ResPass { const float *W; int K, Cout; };
+__device__ __forceinline__ ResPass res_pass(const Dims &d, const CondPack &p, int i) {
+    if (i == 0) return ResPass{p.conv_in_t, d.F * d.ksize, d.C};
+    if (i <= 2 * d.nres) return ResPass{p.res_t + (size_t)(i - 1) * d.C * d.C, d.C, d.C};
+    return ResPass{p.conv_out_t, d.C, d.R};
+}
+__device__ __forceinline__ void res_stage(float *buf, const ResPass &ps, int ch, int tid) {
+    const int KR = RES_WBUF / ps.Cout, k0 = ch * KR, rows = min(KR, ps.K - k0);
+    const float4 *src = reinterpret_cast<const float4 *>(ps.W + (size_t)k0 * ps.Cout);
+    const uint32_t dst = (uint32_t)__cvta_generic_to_shared(buf);
+    for (int i = tid; i < rows * ps.Cout / 4; i += RES_THREADS)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + 16u * i), "l"(src + i) : "memory");
+    asm volatile("cp.async.commit_group;" ::: "memory");
 }
 
-__global__ void __launch_bounds__(128) resnet_kernel(const float *__restrict__ mel_padded, int Tp, int T,
-                                                      Dims d, CondPack p, float *__restrict__ res_out) {
-    extern __shared__ float sm[];
-    const int C = d.C, F = d.F, ks = d.ksize, R = d.R;
-    float *in = sm;                              // [F*ks][RES_TT]   im2col of the mel tile
-    float *a0 = in + (size_t)F * ks * RES_TT;    // [C][RES_TT]
-    float *a1 = a0 + (size_t)C * RES_TT;         // [C][RES_TT]
-    const int t0 = blockIdx.x * RES_TT;
-    for (int i = threadIdx.x; i < F * ks * RES_TT; i += blockDim.x) {
+__global__ void __launch_bounds__(RES_THREADS) resnet_batch_kernel(const float *__restrict__ melT, const UttMeta *__restrict__ utts,
+                                                                    const ResTile *__restrict__ tiles, Dims d, CondPack p,
+                                                                    float *__restrict__ res_out) {
+    extern __shared__ __align__(16) float sm[];
+    const int C = d.C, F = d.F, ks = d.ksize, R = d.R, tid = threadIdx.x;
+    float *wbuf = sm;                                    // [2][RES_WBUF]
+    float *in = wbuf + 2 * RES_WBUF;                     // [F*ks][RES_TT]   im2col of the mel tile
+    float *a0 = in + (size_t)F * ks * RES_TT;            // [C][RES_TT]
+    float *a1 = a0 + (size_t)C * RES_TT;                 // [C][RES_TT]
+    const ResTile tl = tiles[blockIdx.x];
+    const UttMeta um = utts[tl.utt];
+    const int t0 = tl.t0, T = um.T, Tp = um.Tp;
+    const int npass = 2 * d.nres + 2;
+    ResPass ps = res_pass(d, p, 0);
+    res_stage(wbuf, ps, 0, tid);                         // first weights in flight while the tile is gathered
+    for (int i = tid; i < F * ks * RES_TT; i += RES_THREADS) {
         const int t = i % RES_TT, fj = i / RES_TT, f = fj / ks, j = fj % ks;
-        const int tt = t0 + t + j;               // valid conv over the padded mel
-        in[i] = (t0 + t < T && tt < Tp) ? mel_padded[(size_t)f * Tp + tt] : 0.f;
+        const int tt = t0 + t + j;                       // valid conv over the padded mel
+        in[i] = (t0 + t < T && tt < Tp) ? melT[(size_t)(um.pm_off + tt) * F + f] : 0.f;
     }
-    __syncthreads();
-    float acc[RES_TT];
-    for (int c = threadIdx.x; c < C; c += blockDim.x) {
-        res_matvec(p.conv_in_t, F * ks, C, c, in, acc);
-        const float s = p.bn_scale[c], b = p.bn_shift[c];
+    const int cl = tid & 127, fh = tid >> 7;
+    float acc[RES_MAXCI][4];
+    int g = 0;
+    for (int pi = 0; pi < npass; pi++) {
+        const int KR = RES_WBUF / ps.Cout, nch = (ps.K + KR - 1) / KR, nci = (ps.Cout + 127) / 128;
+        const float *act = pi == 0 ? in : ((pi & 1) ? a0 : a1);          // odd passes (conv1, conv_out) read a0, even read a1
 #pragma unroll
-        for (int t = 0; t < RES_TT; t++) a0[c * RES_TT + t] = fmaxf(fmaf(acc[t], s, b), 0.f);
-    }
-    __syncthreads();
-    for (int i = 0; i < d.nres; i++) {
-        const float *W1 = p.res_t + (size_t)(2 * i) * C * C, *W2 = W1 + (size_t)C * C;
-        const float *s1 = p.bn_scale + (size_t)(1 + 2 * i) * C, *b1 = p.bn_shift + (size_t)(1 + 2 * i) * C;
-        const float *s2 = s1 + C, *b2 = b1 + C;
-        for (int c = threadIdx.x; c < C; c += blockDim.x) {
-            res_matvec(W1, C, C, c, a0, acc);
+        for (int ci = 0; ci < RES_MAXCI; ci++)
 #pragma unroll
-            for (int t = 0; t < RES_TT; t++) a1[c * RES_TT + t] = fmaxf(fmaf(acc[t], s1[c], b1[c]), 0.f);
+            for (int t = 0; t < 4; t++) acc[ci][t] = 0.f;
+        for (int ch = 0; ch < nch; ch++, g++) {
+            // next chunk (of this pass or the first of the next) into the other buffer
+            const bool more = ch + 1 < nch || pi + 1 < npass;
+            if (more) {
+                const ResPass nx = ch + 1 < nch ? ps : res_pass(d, p, pi + 1);
+                res_stage(wbuf + ((g + 1) & 1) * RES_WBUF, nx, ch + 1 < nch ? ch + 1 : 0, tid);
+                asm volatile("cp.async.wait_group 1;" ::: "memory");
+            } else {
+                asm volatile("cp.async.wait_group 0;" ::: "memory");
+            }
+            __syncthreads();
+            const float *wb = wbuf + (g & 1) * RES_WBUF;
+            const int k0 = ch * KR, rows = min(KR, ps.K - k0);
+            for (int k = 0; k < rows; k++) {
+                const float4 a = *reinterpret_cast<const float4 *>(act + (size_t)(k0 + k) * RES_TT + 4 * fh);
+#pragma unroll
+                for (int ci = 0; ci < RES_MAXCI; ci++) {
+                    const int c = cl + 128 * ci;
+                    if (ci < nci && c < ps.Cout) {
+                        const float wv = wb[k * ps.Cout + c];
+                        acc[ci][0] = fmaf(wv, a.x, acc[ci][0]);
+                        acc[ci][1] = fmaf(wv, a.y, acc[ci][1]);
+                        acc[ci][2] = fmaf(wv, a.z, acc[ci][2]);
+                        acc[ci][3] = fmaf(wv, a.w, acc[ci][3]);
+                    }
+                }
+            }
+            __syncthreads();
         }
-        __syncthreads();
-        float nxt[RES_TT];   // C <= blockDim handled in registers; larger C loops (values written after sync)
-        for (int c0 = 0; c0 < C; c0 += blockDim.x) {
-            const int c = c0 + threadIdx.x;
-            if (c < C) {
-                res_matvec(W2, C, C, c, a1, acc);
+        // ---- epilogue of the pass
 #pragma unroll
-                for (int t = 0; t < RES_TT; t++) nxt[t] = fmaf(acc[t], s2[c], b2[c]) + a0[c * RES_TT + t];
+        for (int ci = 0; ci < RES_MAXCI; ci++) {
+            const int c = cl + 128 * ci;
+            if (ci >= nci || c >= ps.Cout) continue;
+            if (pi == npass - 1) {                       // conv_out (+ bias) -> res_out
+                const float b = p.conv_out_b[c];
 #pragma unroll
-                for (int t = 0; t < RES_TT; t++) a0[c * RES_TT + t] = nxt[t];   // a0[c] is only read by its owner here
+                for (int t = 0; t < 4; t++)
+                    if (t0 + 4 * fh + t < T) res_out[(size_t)(um.res_off + t0 + 4 * fh + t) * R + c] = acc[ci][t] + b;
+            } else if (pi == 0 || (pi & 1)) {            // conv_in / conv1: BN + ReLU -> a0 / a1
+                const float s = p.bn_scale[(size_t)pi * C + c], b = p.bn_shift[(size_t)pi * C + c];
+                float *dst = pi == 0 ? a0 : a1;
+#pragma unroll
+                for (int t = 0; t < 4; t++) dst[c * RES_TT + 4 * fh + t] = fmaxf(fmaf(acc[ci][t], s, b), 0.f);
+            } else {                                     // conv2: BN + residual -> a0 (each element read and written by its owner)
+                const float s = p.bn_scale[(size_t)pi * C + c], b = p.bn_shift[(size_t)pi * C + c];
+#pragma unroll
+                for (int t = 0; t < 4; t++) a0[c * RES_TT + 4 * fh + t] = fmaf(acc[ci][t], s, b) + a0[c * RES_TT + 4 * fh + t];
             }
         }
-        __syncthreads();
-    }
-    for (int r = threadIdx.x; r < R; r += blockDim.x) {
-        res_matvec(p.conv_out_t, C, R, r, a0, acc);
-        const float b = p.conv_out_b[r];
-#pragma unroll
-        for (int t = 0; t < RES_TT; t++)
-            if (t0 + t < T) res_out[(size_t)(t0 + t) * R + r] = acc[t] + b;
+        if (pi + 1 < npass) ps = res_pass(d, p, pi + 1);
+        // the next pass's first __syncthreads (after its cp.async wait) orders these writes before its reads
     }
 }
 
-// ============================================================================ mel upsampling
-// One stage of UpsampleNetwork's mel branch (fatchord_version.py:73-80,86-87): nearest-repeat by s
-// along time, then a (2s+1)-tap FIR with ZERO padding of s at both ends of the repeated signal.
-// in [F][n_in] -> out [F][n_in*s], channel-major.
-__global__ void fir_stage_kernel(const float *__restrict__ in, int64_t n_in, int s,
-                                 const float *__restrict__ w, float *__restrict__ out) {
-    const int f = blockIdx.y;
-    const int64_t n_out = n_in * s;
+int launch_resnet_batch(wrnn_handle *h, const float *melT, const UttMeta *utts, const ResTile *tiles, int n_tiles,
+                        float *res_out, cudaStream_t st) {
+    const Dims &d = h->d;
+    if (d.C % 4 || d.R % 4 || d.C > 128 * RES_MAXCI || d.R > 128 * RES_MAXCI)
+        return fail(h, WRNN_ERR_ARG, "compute_dims / res_out_dims must be multiples of 4 and <= %d", 128 * RES_MAXCI);
+    const size_t smem = (2 * (size_t)RES_WBUF + ((size_t)d.F * d.ksize + 2 * (size_t)d.C) * RES_TT) * sizeof(float);
+    if (smem > h->smem_optin) return fail(h, WRNN_ERR_ARG, "MelResNet tile needs %zu B of shared memory", smem);
+    WRNN_CUDA(h, cudaFuncSetAttribute(resnet_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    resnet_batch_kernel<<<n_tiles, RES_THREADS, smem, st>>>(melT, utts, tiles, d, h->cp, res_out);
+    h->launches++;
+    WRNN_CUDA(h, cudaGetLastError());
+    return 0;
+}
+
+// ============================================================================ mel upsampling (polyphase) + repeat
+// Four consecutive features of upsampled sample i (stage coordinates: i = l + indent) of one utterance:
+//   up[i][f] = sum_k poly[i % hop][k] * melT[i / hop + kmin + k][f]      (zero outside the padded mel)
+// which is UpsampleNetwork's mel branch (fatchord_version.py:86-88), all stages at once (see pack_cond).
+__device__ __forceinline__ float4 upsample4(const float *__restrict__ melT, int64_t pm_off, int Tp, int F, const float *__restrict__ poly,
+                                            int taps, int kmin, int hop, int64_t i, int f) {
+    const int fr = (int)(i / hop), ph = (int)(i - (int64_t)fr * hop);
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int k = 0; k < taps; k++) {
+        const int j = fr + kmin + k;
+        if (j < 0 || j >= Tp) continue;
+        const float wv = __ldg(poly + ph * taps + k);
+        const float4 m = __ldg(reinterpret_cast<const float4 *>(melT + (size_t)(pm_off + j) * F + f));
+        acc.x = fmaf(wv, m.x, acc.x);
+        acc.y = fmaf(wv, m.y, acc.y);
+        acc.z = fmaf(wv, m.z, acc.z);
+        acc.w = fmaf(wv, m.w, acc.w);
+    }
+    return acc;
+}
+
+// component entry (wrnn_upsample): the upsampled mel of one utterance, time-major [L][F]
+__global__ void upsample_flat_kernel(const float *__restrict__ melT, int Tp, int F, const float *__restrict__ poly, int taps, int kmin,
+                                     int hop, int64_t indent, int64_t L, float *__restrict__ out) {
+    const int W = F / 4;
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n_out) return;
-    const float *row = in + (size_t)f * n_in;
-    float acc = 0.f;
-    for (int j = 0; j <= 2 * s; j++) {
-        const int64_t pidx = i + j - s;
-        if (pidx >= 0 && pidx < n_out) acc = fmaf(w[j], row[pidx / s], acc);
-    }
-    out[(size_t)f * n_out + i] = acc;
+    if (i >= L * W) return;
+    const int64_t l = i / W;
+    const int f = (int)(i % W) * 4;
+    *reinterpret_cast<float4 *>(out + (size_t)l * F + f) = upsample4(melT, 0, Tp, F, poly, taps, kmin, hop, l + indent, f);
 }
 
-// Last stage: same FIR, but crop `indent` at both ends and write time-major [L][F]
-// (the `.transpose(1, 2)` at fatchord_version.py:88-89) through a smem tile so the global stores
-// are full contiguous rows.
-constexpr int FIR_TI = 128;
-__global__ void __launch_bounds__(256) fir_last_kernel(const float *__restrict__ in, int64_t n_in, int s,
-                                                        const float *__restrict__ w, int F, int64_t indent,
-                                                        int64_t L, float *__restrict__ out) {
-    extern __shared__ float tile[];              // [FIR_TI][F + 1]
-    const int64_t n_out = n_in * s;
-    const int64_t l0 = (int64_t)blockIdx.x * FIR_TI;
-    const int ldt = F + 1;
-    for (int e = threadIdx.x; e < FIR_TI * F; e += blockDim.x) {
-        const int f = e / FIR_TI, tl = e % FIR_TI;   // consecutive threads walk time: reads hit one row
-        const int64_t l = l0 + tl;
-        float acc = 0.f;
-        if (l < L) {
-            const int64_t i = l + indent;
-            const float *row = in + (size_t)f * n_in;
-            for (int j = 0; j <= 2 * s; j++) {
-                const int64_t pidx = i + j - s;
-                if (pidx >= 0 && pidx < n_out) acc = fmaf(w[j], row[pidx / s], acc);
-            }
-        }
-        tile[tl * ldt + f] = acc;
-    }
-    __syncthreads();
-    for (int e = threadIdx.x; e < FIR_TI * F; e += blockDim.x) {
-        const int tl = e / F, f = e % F;
-        if (l0 + tl < L) out[(size_t)(l0 + tl) * F + f] = tile[tl * ldt + f];
-    }
-}
-
-__global__ void pad_mel_kernel(const float *__restrict__ mel, int T, int pad, int F, float *__restrict__ out) {
-    const int Tp = T + 2 * pad;
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= (int64_t)F * Tp) return;
-    const int f = i / Tp, t = i % Tp - pad;
-    out[i] = (t >= 0 && t < T) ? mel[(size_t)f * T + t] : 0.f;
+int launch_upsample_flat(wrnn_handle *h, const float *melT, int Tp, int64_t L, float *up_mels, cudaStream_t st) {
+    const Dims &d = h->d;
+    if (d.F % 4) return fail(h, WRNN_ERR_ARG, "feat_dims must be a multiple of 4");
+    const int64_t n = L * (d.F / 4);
+    upsample_flat_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(melT, Tp, d.F, h->cp.poly, h->cp.poly_taps, h->cp.poly_kmin,
+                                                                   d.total_scale, d.indent, L, up_mels);
+    h->launches++;
+    WRNN_CUDA(h, cudaGetLastError());
+    return 0;
 }
 
 __global__ void repeat_aux_kernel(const float *__restrict__ res_out, int64_t L, int hop, int R,
@@ -229,66 +335,11 @@ __global__ void repeat_aux_kernel(const float *__restrict__ res_out, int64_t L, 
     aux[i] = res_out[(size_t)(l / hop) * R + (i % R)];
 }
 
-int launch_pad_mel(wrnn_handle *h, const float *mel, int T, float *mel_padded, cudaStream_t st) {
-    const int64_t n = (int64_t)h->d.F * (T + 2 * h->d.pad);
-    pad_mel_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(mel, T, h->d.pad, h->d.F, mel_padded);
-    h->launches++;
-    WRNN_CUDA(h, cudaGetLastError());
-    return 0;
-}
-
 int launch_repeat_aux(wrnn_handle *h, const float *res_out, int T, float *aux, cudaStream_t st) {
     const int64_t L = (int64_t)T * h->d.total_scale, n = L * h->d.R;
     repeat_aux_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(res_out, L, h->d.total_scale, h->d.R, aux);
     h->launches++;
     WRNN_CUDA(h, cudaGetLastError());
-    return 0;
-}
-
-int run_conditioning(wrnn_handle *h, const float *mel_padded, int Tp, float *up_mels, float *res_out,
-                     cudaStream_t st) {
-    const Dims &d = h->d;
-    const int T = Tp - 2 * d.pad;
-    if (T < 1) return fail(h, WRNN_ERR_ARG, "mel too short: T=%d", T);
-    // MelResNet
-    const size_t smem = ((size_t)d.F * d.ksize + 2 * (size_t)d.C) * RES_TT * sizeof(float);
-    if (smem > 48 * 1024)
-        WRNN_CUDA(h, cudaFuncSetAttribute(resnet_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    resnet_kernel<<<(T + RES_TT - 1) / RES_TT, 128, smem, st>>>(mel_padded, Tp, T, d, h->cp, res_out);
-    h->launches++;
-    WRNN_CUDA(h, cudaGetLastError());
-    // mel branch: nup stages; intermediates live in two scratch buffers
-    int64_t n_in = Tp;
-    const float *cur = mel_padded;
-    size_t max_mid = 0;
-    {
-        int64_t n = Tp;
-        for (int j = 0; j + 1 < d.nup; j++) { n *= d.up[j]; max_mid = (size_t)n > max_mid ? (size_t)n : max_mid; }
-    }
-    if (d.nup > 1) {
-        WRNN_TRY(ws_reserve(h, h->ws_tmp0, max_mid * d.F * sizeof(float)));
-        WRNN_TRY(ws_reserve(h, h->ws_tmp1, max_mid * d.F * sizeof(float)));
-    }
-    for (int j = 0; j < d.nup; j++) {
-        const int s = d.up[j];
-        const int64_t n_out = n_in * s;
-        if (j + 1 < d.nup) {
-            float *dst = (float *)((j & 1) ? h->ws_tmp1.p : h->ws_tmp0.p);
-            dim3 grid((unsigned)((n_out + 255) / 256), d.F);
-            fir_stage_kernel<<<grid, 256, 0, st>>>(cur, n_in, s, h->cp.fir[j], dst);
-            cur = dst;
-        } else {
-            const int64_t L = (int64_t)T * d.total_scale;
-            const size_t sm = (size_t)FIR_TI * (d.F + 1) * sizeof(float);
-            if (sm > 48 * 1024)
-                WRNN_CUDA(h, cudaFuncSetAttribute(fir_last_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-            fir_last_kernel<<<(unsigned)((L + FIR_TI - 1) / FIR_TI), 256, sm, st>>>(cur, n_in, s, h->cp.fir[j], d.F,
-                                                                                 d.indent, L, up_mels);
-        }
-        h->launches++;
-        WRNN_CUDA(h, cudaGetLastError());
-        n_in = n_out;
-    }
     return 0;
 }
 
@@ -313,50 +364,36 @@ int launch_fold(wrnn_handle *h, const float *x, int64_t L, int F, int64_t target
     return 0;
 }
 
-// The fold the loop consumes: mel features and the (frame-rate) aux features of fold b, step s,
-// gathered into one [B][S][F+R] row so the loop reads 832 contiguous bytes per fold-step.  The
-// x275 nearest-repeat of aux (Stretch2d, :83-85) is done here by index, never materialised.
-template <int VEC>
-__global__ void fold_cond_kernel(const float *__restrict__ up_mels, const float *__restrict__ res_out,
-                                 const FoldMeta *__restrict__ meta, int64_t B, int64_t S, int F, int R, int hop,
-                                 float *__restrict__ cond) {
-    const int W = (F + R) / VEC;
+// The fold the loop consumes: mel features and the (frame-rate) aux features of fold b, step s, as one [B][S][F+R] row,
+// so the loop reads 832 contiguous bytes per fold-step.  Nothing upsampled is materialised in between: the mel part is
+// formed here from the padded frames by the polyphase table (UpsampleNetwork's three repeat + FIR stages and the crop,
+// fatchord_version.py:86-88), the x275 nearest-repeat of aux (Stretch2d, :83-85) is an index.  One launch for all
+// folds of all utterances of the call; HBM-bound on the row writes (float4 stores, a warp covers whole rows).
+__global__ void fold_cond_kernel(const float *__restrict__ melT, const float *__restrict__ res_out,
+                                 const FoldMeta *__restrict__ meta, int64_t B, int64_t S, int F, int R, int hop, int64_t indent,
+                                 const float *__restrict__ poly, int taps, int kmin, float *__restrict__ cond) {
+    const int W = (F + R) / 4;
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= B * S * W) return;
-    const int e = (int)(i % W) * VEC;
-    const int64_t s = (i / W) % S, b = i / ((int64_t)W * S);
+    const int e = (int)(i % W) * 4;
+    const int64_t row = i / W, s = row % S, b = row / S;
     const FoldMeta m = meta[b];
     const int64_t l = m.start + s;
-    float v[VEC];
-#pragma unroll
-    for (int k = 0; k < VEC; k++) v[k] = 0.f;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
     if (l < m.L) {
-        const float *src = e < F ? up_mels + (size_t)(m.up_off + l) * F + e
-                                 : res_out + (size_t)(m.res_off + l / hop) * R + (e - F);
-        if (VEC == 4) {
-            const float4 q = *reinterpret_cast<const float4 *>(src);
-            v[0] = q.x; v[1] = q.y; v[2] = q.z; v[3] = q.w;
-        } else {
-            v[0] = src[0];
-        }
+        if (e < F) v = upsample4(melT, m.pm_off, m.Tp, F, poly, taps, kmin, hop, l + indent, e);
+        else v = __ldg(reinterpret_cast<const float4 *>(res_out + (size_t)(m.res_off + l / hop) * R + (e - F)));
     }
-    float *dst = cond + (size_t)i * VEC;
-    if (VEC == 4) *reinterpret_cast<float4 *>(dst) = make_float4(v[0], v[1], v[2], v[3]);
-    else dst[0] = v[0];
+    *reinterpret_cast<float4 *>(cond + (size_t)i * 4) = v;
 }
 
-int launch_fold_cond(wrnn_handle *h, const float *up_mels, const float *res_out, const FoldMeta *meta,
+int launch_fold_cond(wrnn_handle *h, const float *melT, const float *res_out, const FoldMeta *meta,
                      int64_t B, int64_t S, float *cond, cudaStream_t st) {
     const Dims &d = h->d;
-    if (d.F % 4 == 0 && d.R % 4 == 0) {
-        const int64_t n = B * S * ((d.F + d.R) / 4);
-        fold_cond_kernel<4><<<(unsigned)((n + 255) / 256), 256, 0, st>>>(up_mels, res_out, meta, B, S, d.F, d.R,
-                                                                      d.total_scale, cond);
-    } else {
-        const int64_t n = B * S * (d.F + d.R);
-        fold_cond_kernel<1><<<(unsigned)((n + 255) / 256), 256, 0, st>>>(up_mels, res_out, meta, B, S, d.F, d.R,
-                                                                      d.total_scale, cond);
-    }
+    if (d.F % 4 || d.R % 4) return fail(h, WRNN_ERR_ARG, "feat_dims and res_out_dims must be multiples of 4");
+    const int64_t n = B * S * ((d.F + d.R) / 4);
+    fold_cond_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(melT, res_out, meta, B, S, d.F, d.R, d.total_scale, d.indent,
+                                                                h->cp.poly, h->cp.poly_taps, h->cp.poly_kmin, cond);
     h->launches++;
     WRNN_CUDA(h, cudaGetLastError());
     return 0;

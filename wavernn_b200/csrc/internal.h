@@ -29,6 +29,10 @@ struct CondPack {
     float *conv_out_t = nullptr;       // [C][R]
     float *conv_out_b = nullptr;       // [R]
     float *fir[8] = {nullptr};         // [2*s+1] per stage
+    // the whole mel branch of UpsampleNetwork as ONE polyphase filter over frames (cond.cu, pack_cond):
+    // up[i] = sum_k poly[i % hop][k] * mel_padded[i / hop + poly_kmin + k]
+    float *poly = nullptr;             // [hop][poly_taps]
+    int poly_taps = 0, poly_kmin = 0;
 };
 
 // ---- per-sample loop, FMA kernel (loop_fma.cu) ----------------------------------------------
@@ -115,7 +119,8 @@ struct wrnn_handle {
     bool sparse = false;
 
     // staged call
-    struct Utt { int T; int64_t L, wave_len, fold0, nfolds, mel_off, up_off, res_off, out_off; };
+    struct Utt { int T, Tin, Tp; int64_t L, wave_len, fold0, nfolds, mel_off, up_off, res_off, out_off, pm_off; };
+    int64_t total_frames = 0;          // padded frames of all staged utterances
     std::vector<Utt> utts;
     bool staged = false;
     int batched = 0, mu_law = 0;
@@ -176,14 +181,22 @@ int ensure_packed_public(wrnn_handle *h);   // pack weights for the kernels if n
 // cond.cu
 int pack_cond(wrnn_handle *h);
 // mel_padded: device [F][Tp] (Tp = T + 2*pad); up_mels: device [L][F]; res_out: device [T][R]
-int run_conditioning(wrnn_handle *h, const float *mel_padded, int Tp, float *up_mels, float *res_out,
-                     cudaStream_t st);
+// Conditioning of ALL utterances of a call in three launches (pad + transpose, MelResNet, conditioning rows).
+struct UttMeta { int64_t raw_off, pm_off, res_off; int T, Tp, Tin, pad_; };   // raw mel floats / padded-frame / res-row offsets
+struct ResTile { int utt, t0; };                                              // one MelResNet CTA: RES_TT frames of one utterance
+int resnet_tile_frames();
+// mel_raw: utterance u at raw_off, (F, Tin) row-major; melT: [sum Tp][F] frame-major, zero frames where the pad is
+int launch_pad_mel_batch(wrnn_handle *h, const float *mel_raw, const UttMeta *utts, int n_utt, int64_t total_frames,
+                         float *melT, cudaStream_t st);
+int launch_resnet_batch(wrnn_handle *h, const float *melT, const UttMeta *utts, const ResTile *tiles, int n_tiles,
+                        float *res_out, cudaStream_t st);
+// component entry: up_mels [L][F] of one utterance (melT at frame offset 0, Tp frames)
+int launch_upsample_flat(wrnn_handle *h, const float *melT, int Tp, int64_t L, float *up_mels, cudaStream_t st);
 int launch_repeat_aux(wrnn_handle *h, const float *res_out, int T, float *aux, cudaStream_t st);
-int launch_pad_mel(wrnn_handle *h, const float *mel, int T, float *mel_padded, cudaStream_t st);
 int launch_fold(wrnn_handle *h, const float *x, int64_t L, int F, int64_t target, int64_t overlap,
                 int64_t folds, float *out, cudaStream_t st);
-struct FoldMeta { int64_t up_off, res_off, start, L; };   // per fold, element offsets (rows)
-int launch_fold_cond(wrnn_handle *h, const float *up_mels, const float *res_out, const FoldMeta *meta,
+struct FoldMeta { int64_t pm_off, res_off, start, L; int Tp, pad_; };   // per fold: padded-frame / res-row offsets of its utterance
+int launch_fold_cond(wrnn_handle *h, const float *melT, const float *res_out, const FoldMeta *meta,
                      int64_t B, int64_t S, float *cond, cudaStream_t st);
 struct TailMeta { int64_t fold0, nfolds, wave_len, out_off; };   // per utterance
 int launch_tail(wrnn_handle *h, const float *samples, const int32_t *picks, const TailMeta *meta,

@@ -312,9 +312,16 @@ __device__ __forceinline__ Ring make_ring(const Params &P, bool has_fc) {
     return r;
 }
 
-// One job of the TMA producer thread: (wait for the grid counter,) stream the stages of (job type, row tile, fold tile).
-__device__ __forceinline__ void produce_job(const Params &P, int jt, int mt, int nt, int64_t t, Ring &r, uint8_t *stages,
-                                            uint64_t *bar_full, uint64_t *bar_empty, Watch &w) {
+// One job of the TMA producer lanes: (wait for the grid counter,) stream the stages of (job type, row tile, fold tile).
+// A thread completes only about one bulk copy per 700 clocks whatever its size (scripts/mb_umma.cu: 16 B/clk/SM from one
+// issuing thread, 52 from four lanes, ~67 = the L2 limit from eight), so the copies are spread over NPROD = 8 lanes of
+// the producer warp: stage k of the running count belongs to lane pair (k & 3), the even lane arms the barrier with the
+// byte count of both copies and brings the weight block, the odd lane brings the activation block.  Every lane keeps
+// the same ring position; a copy may complete its bytes on the barrier before the other lane has armed it (the phase
+// cannot end before the arrive).
+constexpr int NPROD = 8;
+__device__ __forceinline__ void produce_job(const Params &P, int jt, int mt, int nt, int64_t t, Ring &r, uint32_t &count, int lane,
+                                            uint8_t *stages, uint64_t *bar_full, uint64_t *bar_empty, Watch &w, long long *pacc = nullptr) {
     const int nst = job_stages(jt), gate = job_gate(jt);
     const uint32_t abytes = 2u * KC * (uint32_t)job_rows(jt) * 16u, bbytes = 2u * KC * (uint32_t)P.NT * 16u;
     if (gate >= 0) {            // this job's operands were written by that phase of every CTA
@@ -322,22 +329,28 @@ __device__ __forceinline__ void produce_job(const Params &P, int jt, int mt, int
         fence_proxy_async_global();
     }
     const uint8_t *Abase = P.Aimg + P.offA[jt] + (size_t)mt * nst * abytes;
-    for (int s = 0; s < nst; s++) {
-        mbar_wait(&bar_empty[r.slot], r.par ^ 1u, w);
-        const StageInfo si = stage_info(jt, s);
-        const int NG = si.arr == ARR_C ? CGROUPS : HGROUPS;
-        const uint8_t *Bsrc = b_array(P, si.arr, t) + (size_t)(nt * NG + si.g) * bbytes;
-        uint8_t *dst = stages + (size_t)r.slot * r.stage_bytes;
-        mbar_expect_tx(&bar_full[r.slot], abytes + bbytes);
-        bulk_g2s(dst, Abase + (size_t)s * abytes, abytes, &bar_full[r.slot]);
-        bulk_g2s(dst + r.a_slot, Bsrc, bbytes, &bar_full[r.slot]);
+    for (int s = 0; s < nst; s++, count++) {
+        if ((count & 3u) == (uint32_t)(lane >> 1)) {
+            const long long c0 = pacc ? clock64() : 0;
+            mbar_wait(&bar_empty[r.slot], r.par ^ 1u, w);
+            if (pacc && lane == 0) *pacc += clock64() - c0;
+            uint8_t *dst = stages + (size_t)r.slot * r.stage_bytes;
+            if ((lane & 1) == 0) {
+                mbar_expect_tx(&bar_full[r.slot], abytes + bbytes);
+                bulk_g2s(dst, Abase + (size_t)s * abytes, abytes, &bar_full[r.slot]);
+            } else {
+                const StageInfo si = stage_info(jt, s);
+                const int NG = si.arr == ARR_C ? CGROUPS : HGROUPS;
+                bulk_g2s(dst + r.a_slot, b_array(P, si.arr, t) + (size_t)(nt * NG + si.g) * bbytes, bbytes, &bar_full[r.slot]);
+            }
+        }
         r.advance();
     }
 }
 
 // One job of the MMA issuer thread: three MMAs (hi.hi, hi.lo, lo.hi) per k-step into the job's accumulator.
 __device__ __forceinline__ void issue_job(const Params &P, int jt, Ring &r, uint32_t stage0, uint32_t tb, uint32_t idesc,
-                                          uint64_t *bar_full, uint64_t *bar_empty, uint64_t *bar_tfull, Watch &w) {
+                                          uint64_t *bar_full, uint64_t *bar_empty, uint64_t *bar_tfull, Watch &w, long long *macc = nullptr) {
     const int nst = job_stages(jt);
     const uint32_t rows = job_rows(jt), NT = P.NT;
     // descriptors differ only in the 14-bit start-address field (16-byte units): constant part once per job
@@ -346,8 +359,10 @@ __device__ __forceinline__ void issue_job(const Params &P, int jt, Ring &r, uint
     const uint32_t loA = KC * rows, loB = KC * NT;               // hi -> lo image
     const uint32_t d = tb + (uint32_t)job_acc(jt) * NT;
     for (int s = 0; s < nst; s++) {
+        const long long c0 = macc ? clock64() : 0;
         mbar_wait(&bar_full[r.slot], r.par, w);
         tc_fence_after();
+        const long long c1 = macc ? clock64() : 0;
         const uint32_t aA = (stage0 + r.slot * r.stage_bytes) >> 4, aB = aA + (r.a_slot >> 4);
 #pragma unroll
         for (int ks = 0; ks < KC / 2; ks++) {
@@ -357,7 +372,9 @@ __device__ __forceinline__ void issue_job(const Params &P, int jt, Ring &r, uint
             umma_bf16(d, ah, bl, idesc, 1u);
             umma_bf16(d, al, bh, idesc, 1u);
         }
+        const long long c2 = macc ? clock64() : 0;
         umma_commit(&bar_empty[r.slot]);          // the stage is free once these MMAs have read it
+        if (macc) { const long long c3 = clock64(); macc[0] += c1 - c0; macc[1] += c2 - c1; macc[2] += c3 - c2; }
         r.advance();
     }
     if (jt != J_S1 && jt != J_S2) umma_commit(bar_tfull);       // accumulator (and every earlier MMA) complete
@@ -504,31 +521,33 @@ __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
 
     if (warp == 0) {
         // ======================================================================= TMA producer
-        if (lane == 0) {
+        if (lane < NPROD) {
             Ring r = make_ring(P, has_fc);
+            uint32_t count = 0;
             if (has_gru) {      // step "-1": recurrent products of step 0 on the zero state (h = 0, :194-195)
-                produce_job(P, J_S1, mt_g, nt_g, -1, r, stages, bar_full, bar_empty, w);
-                produce_job(P, J_S2, mt_g, nt_g, -1, r, stages, bar_full, bar_empty, w);
+                produce_job(P, J_S1, mt_g, nt_g, -1, r, count, lane, stages, bar_full, bar_empty, w);
+                produce_job(P, J_S2, mt_g, nt_g, -1, r, count, lane, stages, bar_full, bar_empty, w);
             }
             for (int64_t t = 0; t < P.steps_run && !w.dead; t++) {
+                long long *pa = (P.prof && t == P.prof_step && (cta == 0 || cta == G - 1)) ? P.prof + (cta == 0 ? 0 : 64) + 32 : nullptr;
                 if (has_gru) {
                     PROF_MARK(0);
-                    produce_job(P, J_R1, mt_g, nt_g, t, r, stages, bar_full, bar_empty, w);
+                    produce_job(P, J_R1, mt_g, nt_g, t, r, count, lane, stages, bar_full, bar_empty, w, pa ? pa + 0 : nullptr);
                     PROF_MARK(1);
-                    produce_job(P, J_R2, mt_g, nt_g, t, r, stages, bar_full, bar_empty, w);
+                    produce_job(P, J_R2, mt_g, nt_g, t, r, count, lane, stages, bar_full, bar_empty, w, pa ? pa + 1 : nullptr);
                     PROF_MARK(2);
-                    produce_job(P, J_S1, mt_g, nt_g, t, r, stages, bar_full, bar_empty, w);
+                    produce_job(P, J_S1, mt_g, nt_g, t, r, count, lane, stages, bar_full, bar_empty, w, pa ? pa + 2 : nullptr);
                     PROF_MARK(3);
                 }
                 if (has_fc) {
                     PROF_MARK(4);
-                    produce_job(P, J_F1, mt_f, nt_f, t, r, stages, bar_full, bar_empty, w);
+                    produce_job(P, J_F1, mt_f, nt_f, t, r, count, lane, stages, bar_full, bar_empty, w, pa ? pa + 4 : nullptr);
                     PROF_MARK(5);
-                    produce_job(P, J_F2, mt_f, nt_f, t, r, stages, bar_full, bar_empty, w);
+                    produce_job(P, J_F2, mt_f, nt_f, t, r, count, lane, stages, bar_full, bar_empty, w, pa ? pa + 5 : nullptr);
                     PROF_MARK(6);
                 }
                 if (has_gru) {
-                    produce_job(P, J_S2, mt_g, nt_g, t, r, stages, bar_full, bar_empty, w);
+                    produce_job(P, J_S2, mt_g, nt_g, t, r, count, lane, stages, bar_full, bar_empty, w, pa ? pa + 3 : nullptr);
                     PROF_MARK(7);
                 }
             }
@@ -543,22 +562,23 @@ __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
                 issue_job(P, J_S2, r, stage0, tb, idesc, bar_full, bar_empty, &bar_tfull, w);
             }
             for (int64_t t = 0; t < P.steps_run && !w.dead; t++) {
+                long long *ma = (P.prof && t == P.prof_step && (cta == 0 || cta == G - 1)) ? P.prof + (cta == 0 ? 0 : 64) + 40 : nullptr;
                 if (has_gru) {
-                    issue_job(P, J_R1, r, stage0, tb, idesc, bar_full, bar_empty, &bar_tfull, w);
+                    issue_job(P, J_R1, r, stage0, tb, idesc, bar_full, bar_empty, &bar_tfull, w, ma ? ma + 0 : nullptr);
                     PROF_MARK(10);
-                    issue_job(P, J_R2, r, stage0, tb, idesc, bar_full, bar_empty, &bar_tfull, w);
+                    issue_job(P, J_R2, r, stage0, tb, idesc, bar_full, bar_empty, &bar_tfull, w, ma ? ma + 3 : nullptr);
                     PROF_MARK(11);
-                    issue_job(P, J_S1, r, stage0, tb, idesc, bar_full, bar_empty, &bar_tfull, w);
+                    issue_job(P, J_S1, r, stage0, tb, idesc, bar_full, bar_empty, &bar_tfull, w, ma ? ma + 6 : nullptr);
                     PROF_MARK(12);
                 }
                 if (has_fc) {
-                    issue_job(P, J_F1, r, stage0, tb, idesc, bar_full, bar_empty, &bar_tfull, w);
+                    issue_job(P, J_F1, r, stage0, tb, idesc, bar_full, bar_empty, &bar_tfull, w, ma ? ma + 12 : nullptr);
                     PROF_MARK(13);
-                    issue_job(P, J_F2, r, stage0, tb, idesc, bar_full, bar_empty, &bar_tfull, w);
+                    issue_job(P, J_F2, r, stage0, tb, idesc, bar_full, bar_empty, &bar_tfull, w, ma ? ma + 15 : nullptr);
                     PROF_MARK(14);
                 }
                 if (has_gru) {
-                    issue_job(P, J_S2, r, stage0, tb, idesc, bar_full, bar_empty, &bar_tfull, w);
+                    issue_job(P, J_S2, r, stage0, tb, idesc, bar_full, bar_empty, &bar_tfull, w, ma ? ma + 9 : nullptr);
                     PROF_MARK(15);
                 }
             }
@@ -944,6 +964,11 @@ int mma_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
                 if (q[i]) ev.push_back({q[i] - t0, i});
             std::sort(ev.begin(), ev.end());
             for (auto &e : ev) fprintf(stderr, "[mma prof]   %8lld  %s\n", e.first, names[e.second]);
+            static const char *jn[6] = {"rnn1", "rnn2", "recurrent-1", "recurrent-2", "fc1", "fc2"};
+            for (int jt = 0; jt < 6; jt++)
+                if (q[40 + 3 * jt + 1])
+                    fprintf(stderr, "[mma prof]   %-12s %2d stages: MMA thread full-wait %6lld, issue %6lld, commit %5lld; producer lane 0 empty-wait %6lld\n",
+                            jn[jt], job_stages(jt), q[40 + 3 * jt], q[40 + 3 * jt + 1], q[40 + 3 * jt + 2], q[32 + jt]);
         }
     }
     return 0;
