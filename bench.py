@@ -44,10 +44,12 @@ METRIC = 'generated audio samples/sec'
 EXCHANGE_CLOCKS, EXCHANGES_PER_STEP, FMA_FLOOR_CLOCKS = 2400, 5, 3900
 
 
-def loop_traffic(kernel):
+def loop_traffic(kernel, folds=None, steps=None):
     """DRAM bytes per launch of the loop kernel that ran, from the newest ncu capture summary under profiles/
-    (`profiles/*_traffic.json`: {"kernel name": {"dram_bytes_per_launch": ..., "source": ...}}); None when that kernel
-    has no capture at this HEAD."""
+    (`profiles/*_traffic.json`, written from `ncu --set full` captures by hand at the HEAD they name).  The captures
+    run fewer steps than the benchmark (ncu replays a kernel ~40 times); DRAM traffic of these kernels is the
+    conditioning rows, i.e. proportional to fold-steps, so the file holds bytes per fold-step and the per-launch figure
+    is that times the folds x steps of the launch that was timed.  None when the kernel has no capture."""
     best = None
     for path in sorted(glob.glob(os.path.join(ROOT, 'profiles', '*_traffic.json'))):
         try:
@@ -56,6 +58,10 @@ def loop_traffic(kernel):
             continue
         if kernel in d:
             best = dict(d[kernel], file=os.path.relpath(path, ROOT))
+    if best and folds and steps:
+        best['dram_bytes_per_launch'] = int(best['dram_bytes_per_fold_step'] * folds * steps)
+        best['source'] = (f"{best['dram_bytes_per_fold_step']} B per fold-step x {folds} folds x {steps} steps; capture: "
+                          f"{best['capture']}, {best['source']}")
     return best
 
 
@@ -243,7 +249,7 @@ def run_config5(args, voc, dims, rank, world, stream, flush, barrier):
     k_ms = float(np.mean(loop_ms))
     fold_steps = t['folds'] * t['steps'] / (k_ms * 1e-3)
     kernel = voc.loop_kernel_name(t['folds'])
-    traffic = loop_traffic(kernel)
+    traffic = loop_traffic(kernel, t['folds'], t['steps'])
     return {
         'workload': f'{n_utt} utterances per GPU (= {n_utt * world} in the job), each a synthetic 10 s mel T=801, one batched '
                     f'generate call: {t["folds"]} folds x {t["steps"]} steps per GPU',
@@ -351,7 +357,7 @@ def run_ours(args):
         achieved = WEIGHT_BYTES_PER_STEP * steps_loop / (k_ms * 1e-3) / 1e9
         sm_mhz = (clocks or {}).get('sm_mhz') or 1965.0
         floor_us = (EXCHANGES_PER_STEP * EXCHANGE_CLOCKS + FMA_FLOOR_CLOCKS) / sm_mhz
-        traffic = loop_traffic(kernel)
+        traffic = loop_traffic(kernel, folds_loop, steps_loop)
         line = {
             'metric': METRIC, 'value': value, 'unit': 'samples/s', 'rtf': value / SAMPLE_RATE / world,
             'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': dev_ms_max / args.steps,

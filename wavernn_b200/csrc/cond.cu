@@ -370,31 +370,54 @@ int launch_fold(wrnn_handle *h, const float *x, int64_t L, int F, int64_t target
 // fatchord_version.py:86-88), the x275 nearest-repeat of aux (Stretch2d, :83-85) is an index.  One launch for all
 // folds of all utterances of the call; HBM-bound on the row writes (float4 stores, a warp covers whole rows).
 __global__ void fold_cond_kernel(const float *__restrict__ melT, const float *__restrict__ res_out,
-                                 const FoldMeta *__restrict__ meta, int64_t B, int64_t S, int F, int R, int hop, int64_t indent,
+                                 const FoldMeta *__restrict__ meta, int S, int F, int R, int hop, int indent,
                                  const float *__restrict__ poly, int taps, int kmin, float *__restrict__ cond) {
+    // grid = (ceil(S * W / 256), B): the fold is the block row, everything inside a fold is 32-bit arithmetic
     const int W = (F + R) / 4;
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= B * S * W) return;
-    const int e = (int)(i % W) * 4;
-    const int64_t row = i / W, s = row % S, b = row / S;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= S * W) return;
+    const int s = i / W, e = (i - s * W) * 4;
+    const int64_t b = blockIdx.y;
     const FoldMeta m = meta[b];
     const int64_t l = m.start + s;
     float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
     if (l < m.L) {
-        if (e < F) v = upsample4(melT, m.pm_off, m.Tp, F, poly, taps, kmin, hop, l + indent, e);
-        else v = __ldg(reinterpret_cast<const float4 *>(res_out + (size_t)(m.res_off + l / hop) * R + (e - F)));
+        const int li = (int)l;                     // launch_fold_cond checks that L + indent fits 31 bits
+        if (e < F) {
+            const int ii = li + indent, fr = ii / hop, ph = ii - fr * hop;
+            for (int k = 0; k < taps; k++) {
+                const int j = fr + kmin + k;
+                if (j < 0 || j >= m.Tp) continue;
+                const float wv = __ldg(poly + ph * taps + k);
+                const float4 q = __ldg(reinterpret_cast<const float4 *>(melT + (size_t)(m.pm_off + j) * F + e));
+                v.x = fmaf(wv, q.x, v.x);
+                v.y = fmaf(wv, q.y, v.y);
+                v.z = fmaf(wv, q.z, v.z);
+                v.w = fmaf(wv, q.w, v.w);
+            }
+        } else {
+            v = __ldg(reinterpret_cast<const float4 *>(res_out + (size_t)(m.res_off + li / hop) * R + (e - F)));
+        }
     }
-    *reinterpret_cast<float4 *>(cond + (size_t)i * 4) = v;
+    __stcs(reinterpret_cast<float4 *>(cond + ((size_t)b * S * W + i) * 4), v);     // streamed: the loop reads each row once, later
 }
 
 int launch_fold_cond(wrnn_handle *h, const float *melT, const float *res_out, const FoldMeta *meta,
                      int64_t B, int64_t S, float *cond, cudaStream_t st) {
     const Dims &d = h->d;
     if (d.F % 4 || d.R % 4) return fail(h, WRNN_ERR_ARG, "feat_dims and res_out_dims must be multiples of 4");
-    const int64_t n = B * S * ((d.F + d.R) / 4);
-    fold_cond_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(melT, res_out, meta, B, S, d.F, d.R, d.total_scale, d.indent,
-                                                                h->cp.poly, h->cp.poly_taps, h->cp.poly_kmin, cond);
-    h->launches++;
+    const int W = (d.F + d.R) / 4;
+    int64_t Lmax = 0;
+    for (auto &ut : h->utts) Lmax = ut.L > Lmax ? ut.L : Lmax;
+    if (Lmax + d.indent + S >= 0x7fffffff || S * W >= 0x7fffffff || B > 65535 * 32768ll)
+        return fail(h, WRNN_ERR_ARG, "utterance too long for the conditioning kernel");
+    for (int64_t b0 = 0; b0 < B; b0 += 65535) {           // gridDim.y limit
+        const int64_t nb = B - b0 < 65535 ? B - b0 : 65535;
+        dim3 grid((unsigned)((S * W + 255) / 256), (unsigned)nb);
+        fold_cond_kernel<<<grid, 256, 0, st>>>(melT, res_out, meta + b0, (int)S, d.F, d.R, d.total_scale, (int)d.indent, h->cp.poly,
+                                               h->cp.poly_taps, h->cp.poly_kmin, cond + (size_t)b0 * S * (d.F + d.R));
+        h->launches++;
+    }
     WRNN_CUDA(h, cudaGetLastError());
     return 0;
 }
