@@ -106,6 +106,14 @@ int wrnn_last_timing(wrnn_handle *h, float *ms_cond, float *ms_loop, float *ms_t
                      int64_t *steps, int64_t *folds, int64_t *kernel_launches);
 /* Raw per-fold samples of the last run: (folds, steps) float32 (RAW mode: 2k/(C-1)-1). */
 int wrnn_fetch_samples(wrnn_handle *h, float *samples, void *cuda_stream);
+/* Fold-range sharding of ONE long utterance over several GPUs (folds never communicate: cold-start state per fold,
+ * fatchord_version.py:194-196).  After wrnn_set_fold_range(h, lo, hi) the next batched
+ * single-utterance wrnn_stage / wrnn_run_staged computes conditioning only for the frames folds [lo, hi) cover and runs
+ * the loop for those folds only; injected noise and Philox stay addressed by the GLOBAL fold index, so the samples equal
+ * those of an unsharded call.  The result is read with wrnn_fetch_samples ((hi - lo, steps) float32); wrnn_fetch fails,
+ * because the float64 cross-fade / unfold / fade-out (:243-258) needs every shard: the gathering host does it
+ * (wavernn_b200/shard.py: combine_fold_samples).  lo = hi = 0 switches the range off. */
+int wrnn_set_fold_range(wrnn_handle *h, int64_t lo, int64_t hi);
 
 /* ------------------------------------------------------------------ components (parity tests) */
 /* UpsampleNetwork.forward on the zero-padded mel (fatchord_version.py:82-89,185-186).

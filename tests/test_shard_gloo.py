@@ -71,3 +71,91 @@ def test_single_process_needs_no_group():
     rate, ms = whole_job_rate(1000, [500.0])
     assert rate == pytest.approx(2000.0) and ms == [500.0]
     assert not dist.is_initialized()
+
+
+# ------------------------------------------------------------------ fold-range sharding of one utterance (section 8e)
+def test_shard_folds_partitions_exactly():
+    from wavernn_b200.shard import shard_folds
+    for n in (1, 5, 20, 160):
+        for world in (1, 2, 3, 8):
+            rng = [shard_folds(n, world, r) for r in range(world)]
+            assert [i for lo, hi in rng for i in range(lo, hi)] == list(range(n))
+            assert max(hi - lo for lo, hi in rng) - min(hi - lo for lo, hi in rng) <= 1
+
+
+def _sharded_case(mode):
+    import numpy as np
+    from oracle import fatchord as ofc
+    from wavernn_b200 import synth
+    from wavernn_b200.config import VocoderDims
+    from common import TINY
+    dims = VocoderDims(mode=mode, **TINY)
+    sd = synth.synth_state_dict(dims, seed=0, style='trained')
+    mel = synth.synth_mel(61, seed=1234, feat_dims=dims.feat_dims)
+    target, overlap, mu_law = 100, 20, mode == 'RAW'
+    W = ofc.to_torch(sd)
+    with torch.no_grad():
+        m, aux, wave_len = ofc.conditioning(W, dims, mel, True, target, overlap)
+        B, S = int(m.shape[0]), int(m.shape[1])
+        noise = synth.synth_noise_mol(S, B, 4321) if mode == 'MOL' else synth.synth_noise_exp(S, B, dims.n_classes, 4321)
+        samples = ofc.run_loop(W, dims, m, aux, noise)['samples']
+    want = ofc.finish(dims, samples, wave_len, True, target, overlap, mu_law)
+    return dims, mel, target, overlap, mu_law, samples.numpy(), want
+
+
+class _NoGpuVocoder:
+    """binding.Vocoder stand-in: dims and host-only helpers; the per-shard GPU call is replaced by run_shard."""
+
+    def __init__(self, dims):
+        self.dims = dims
+
+    @staticmethod
+    def num_folds(total_len, target, overlap):
+        from oracle.fatchord import num_folds_for
+        return num_folds_for(total_len, target, overlap)
+
+
+def _fold_worker(rank, world, port, mode, q):
+    os.environ['MASTER_ADDR'] = '127.0.0.1'
+    os.environ['MASTER_PORT'] = str(port)
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    try:
+        import numpy as np
+        from wavernn_b200.shard import generate_sharded
+        dims, mel, target, overlap, mu_law, samples, want = _sharded_case(mode)
+        # the kernel is stubbed by the oracle's samples of the rank's own fold range
+        out = generate_sharded(_NoGpuVocoder(dims), mel[0], target, overlap, mu_law,
+                               run_shard=lambda lo, hi: samples[lo:hi])
+        if rank == 0:
+            q.put((out.dtype == np.float64, out.shape == want.shape, bool(np.array_equal(out, want))))
+        else:
+            q.put((out is None,))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize('mode', ['MOL', 'RAW'])
+def test_world_size_2_gloo_fold_sharded_utterance_is_bit_exact(mode):
+    """Two ranks each hold half of the folds (the oracle's samples stand in for the kernel); rank 0 gathers and applies
+    the float64 cross-fade / unfold / fade-out, incl. the <= overlap samples that straddle the shard edge: equal, bit
+    for bit, to the reference-order tail of the unsharded utterance (oracle.finish, pinned against the reference)."""
+    world, port = 2, _free_port()
+    ctx = mp.get_context('spawn')
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_fold_worker, args=(r, world, port, mode, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    out = [q.get(timeout=180) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert sorted(out, key=len) == [(True,), (True, True, True)]
+
+
+def test_combine_fold_samples_single_process_equals_oracle_tail():
+    import numpy as np
+    from wavernn_b200.shard import combine_fold_samples
+    for mode in ('MOL', 'RAW'):
+        dims, mel, target, overlap, mu_law, samples, want = _sharded_case(mode)
+        got = combine_fold_samples(samples, want.shape[0], target, overlap, dims.hop_length, dims.n_classes if mu_law else None)
+        assert np.array_equal(got, want)

@@ -51,6 +51,7 @@ _SIGS = {
     'wrnn_last_timing': (C.c_int, [_P, C.POINTER(C.c_float), C.POINTER(C.c_float), C.POINTER(C.c_float),
                                    C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     'wrnn_fetch_samples': (C.c_int, [_P, _P, _P]),
+    'wrnn_set_fold_range': (C.c_int, [_P, C.c_int64, C.c_int64]),
     'wrnn_upsample': (C.c_int, [_P, _P, C.c_int32, _P, _P]),
     'wrnn_num_folds': (C.c_int64, [C.c_int64, C.c_int64, C.c_int64]),
     'wrnn_fold': (C.c_int, [_P, _P, C.c_int64, C.c_int32, C.c_int64, C.c_int64, _P]),
@@ -166,14 +167,22 @@ class Vocoder:
         if rc != 0:
             _raise(rc, lib().wrnn_last_error(self._h))
 
-    def set_mulaw_lut(self, mu):
-        """Install the mu-law table evaluated with the reference's own numpy expression
-        (`utils/dsp.py:98-103` at y = float32(2k/(mu-1)-1)), so decode is bit-equal on this host."""
+    @staticmethod
+    def mulaw_table(mu):
+        """decode_mu_law(y, mu, from_labels=False) (`utils/dsp.py:98-103`) at the mu sample values y = float32(2k/(mu-1)-1),
+        evaluated with the reference's own numpy expression."""
         k = np.arange(mu, dtype=np.float32)
         y = (np.float32(2) * k / np.float32(mu - 1.) - np.float32(1)).astype(np.float64)
         m = mu - 1
-        lut = np.ascontiguousarray(np.sign(y) / m * ((1 + m) ** np.abs(y) - 1), dtype=np.float64)
-        self._ck(lib().wrnn_set_mulaw_lut(self._h, int(mu), _ptr(lut)))
+        return np.ascontiguousarray(np.sign(y) / m * ((1 + m) ** np.abs(y) - 1), dtype=np.float64)
+
+    @staticmethod
+    def num_folds(total_len, target, overlap):
+        return num_folds(total_len, target, overlap)
+
+    def set_mulaw_lut(self, mu):
+        """Install that table, so decode is bit-equal on this host."""
+        self._ck(lib().wrnn_set_mulaw_lut(self._h, int(mu), _ptr(self.mulaw_table(mu))))
 
     def load_weights(self, state):
         arr, keep = _tensors(state)
@@ -241,6 +250,10 @@ class Vocoder:
         self._ck(lib().wrnn_last_timing(self._h, C.byref(a), C.byref(b), C.byref(c), C.byref(s), C.byref(f), C.byref(k)))
         return dict(ms_cond=a.value, ms_loop=b.value, ms_tail=c.value, steps=s.value, folds=f.value,
                     launches=k.value)
+
+    def set_fold_range(self, lo, hi):
+        """Run only folds [lo, hi) of the next single-utterance batched stage (0, 0 = all): see shard.py."""
+        self._ck(lib().wrnn_set_fold_range(self._h, int(lo), int(hi)))
 
     def fetch_samples(self, stream=None):
         t = self.last_timing()

@@ -29,9 +29,24 @@ static MetaLayout meta_layout(int64_t B, int n_utt, int64_t n_tiles) {
     m.bytes = m.off_tile + align_up(sizeof(ResTile) * (size_t)n_tiles, 64);
     return m;
 }
+// MelResNet tiles an utterance needs: all frames, or, under a fold range, only the frames its folds cover
+static void res_tile_span(const wrnn_handle *h, const wrnn_handle::Utt &ut, int *t_first, int *t_end) {
+    const int TT = resnet_tile_frames();
+    *t_first = 0;
+    *t_end = ut.T;
+    if (h->Btot != h->B && h->batched) {
+        const int64_t stride = h->target + h->overlap, s0 = h->fold_lo * stride, s1 = (h->fold_lo + h->B - 1) * stride + h->S;
+        *t_first = (int)(s0 / h->d.hop / TT * TT);
+        *t_end = (int)std::min<int64_t>(ut.T, s1 / h->d.hop + 1);
+    }
+}
 static int64_t count_res_tiles(const wrnn_handle *h) {
     int64_t n = 0;
-    for (auto &ut : h->utts) n += (ut.T + resnet_tile_frames() - 1) / resnet_tile_frames();
+    for (auto &ut : h->utts) {
+        int a, b;
+        res_tile_span(h, ut, &a, &b);
+        n += (b - a + resnet_tile_frames() - 1) / resnet_tile_frames();
+    }
     return n;
 }
 // Layout of ws_tables (device doubles): fade_in[ov] | fade_out[ov] | fo[20*hop] | lut[NC]
@@ -60,7 +75,7 @@ int do_stage(wrnn_handle *h, const float *const *mels, const int32_t *T, int32_t
     h->overlap = batched ? overlap : 0;
     h->mu_law = (d.mode == WRNN_MODE_RAW && mu_law) ? 1 : 0;     // fatchord_version.py:174
     h->utts.clear();
-    int64_t mel_off = 0, up_off = 0, res_off = 0, out_off = 0, fold0 = 0, Smax = 0, pm_off = 0;
+    int64_t mel_off = 0, up_off = 0, res_off = 0, out_off = 0, fold0 = 0, Smax = 0, pm_off = 0, range_total = -1, range_first = 0;
     for (int u = 0; u < n_utt; u++) {
         wrnn_handle::Utt ut;
         const int Tin = T[u];
@@ -79,6 +94,15 @@ int do_stage(wrnn_handle *h, const float *const *mels, const int32_t *T, int32_t
             ut.nfolds = 1;
             Smax = std::max(Smax, ut.L);
         }
+        if (h->range_hi > h->range_lo && !o.want_logits) {
+            // fold-range sharding: this handle runs folds [lo, hi) of the one utterance
+            if (n_utt != 1 || !batched) return fail(h, WRNN_ERR_ARG, "a fold range needs one utterance and batched generation");
+            range_total = ut.nfolds;
+            range_first = std::min(h->range_lo, ut.nfolds);
+            ut.nfolds = std::min(h->range_hi, range_total) - range_first;
+            if (ut.nfolds < 1) return fail(h, WRNN_ERR_ARG, "fold range [%lld, %lld) is empty: the utterance has %lld folds",
+                                           (long long)h->range_lo, (long long)h->range_hi, (long long)range_total);
+        }
         ut.fold0 = fold0; fold0 += ut.nfolds;
         ut.mel_off = mel_off; mel_off += (int64_t)d.F * Tin;
         ut.Tin = Tin; ut.Tp = ut.T + 2 * d.pad; ut.pm_off = pm_off; pm_off += ut.Tp;
@@ -88,6 +112,8 @@ int do_stage(wrnn_handle *h, const float *const *mels, const int32_t *T, int32_t
         h->utts.push_back(ut);
     }
     h->B = fold0;
+    h->fold_lo = range_total >= 0 ? range_first : 0;
+    h->Btot = range_total >= 0 ? range_total : fold0;
     h->S = batched ? (int64_t)target + 2 * (int64_t)overlap : Smax;
     h->total_out = out_off;
     if (h->B > 0x7fffffff / 4 || h->S > 0x7fffffff) return fail(h, WRNN_ERR_ARG, "too many folds / steps");
@@ -120,13 +146,15 @@ int do_stage(wrnn_handle *h, const float *const *mels, const int32_t *T, int32_t
     for (int u = 0; u < n_utt; u++) {
         const auto &ut = h->utts[u];
         for (int64_t i = 0; i < ut.nfolds; i++) {
-            fm[ut.fold0 + i] = FoldMeta{ut.pm_off, ut.res_off, batched ? i * ((int64_t)target + overlap) : 0, ut.L, ut.Tp, d.pad};
+            fm[ut.fold0 + i] = FoldMeta{ut.pm_off, ut.res_off, batched ? (h->fold_lo + i) * ((int64_t)target + overlap) : 0, ut.L, ut.Tp, d.pad};
             fl[ut.fold0 + i] = (int32_t)(batched ? h->S : ut.L);
         }
         tm[u] = TailMeta{ut.fold0, ut.nfolds, ut.wave_len, ut.out_off};
         // already-padded input (forward_logits): all Tp frames come from the caller, no zero frames added
         um[u] = UttMeta{ut.mel_off, ut.pm_off, ut.res_off, ut.T, ut.Tp, ut.Tin, o.prepadded ? 0 : d.pad};
-        for (int t0 = 0; t0 < ut.T; t0 += resnet_tile_frames()) rt[ti++] = ResTile{u, t0};
+        int tf, te;
+        res_tile_span(h, ut, &tf, &te);
+        for (int t0 = tf; t0 < te; t0 += resnet_tile_frames()) rt[ti++] = ResTile{u, t0};
     }
     WRNN_TRY(ws_reserve(h, h->ws_meta, ml.bytes));
     WRNN_CUDA(h, cudaMemcpyAsync(h->ws_meta.p, hm.data(), ml.bytes, cudaMemcpyHostToDevice, st));
@@ -146,10 +174,10 @@ int do_stage(wrnn_handle *h, const float *const *mels, const int32_t *T, int32_t
     // ---- injected noise ----
     h->have_noise = false;
     if (noise) {
-        if (noise->steps != h->S || noise->folds != h->B)
+        if (noise->steps != h->S || noise->folds != h->Btot)       // under a fold range the noise is that of the whole utterance
             return fail(h, WRNN_ERR_ARG, "noise is %lld x %lld but the call runs %lld steps x %lld folds",
-                        (long long)noise->steps, (long long)noise->folds, (long long)h->S, (long long)h->B);
-        const size_t SB = (size_t)h->S * h->B;
+                        (long long)noise->steps, (long long)noise->folds, (long long)h->S, (long long)h->Btot);
+        const size_t SB = (size_t)h->S * h->Btot;
         if (d.mode == WRNN_MODE_MOL) {
             if (!noise->u1 || !noise->u2) return fail(h, WRNN_ERR_ARG, "MOL noise needs u1 and u2");
             const size_t nm = d.NC / 3;
@@ -213,7 +241,7 @@ int do_run(wrnn_handle *h, uint64_t seed, cudaStream_t st, const StageOpts &o) {
     if (h->have_noise) {
         if (d.mode == WRNN_MODE_MOL) {
             a.u1 = (const float *)h->ws_noise.p;
-            a.u2 = a.u1 + (size_t)h->S * h->B * (d.NC / 3);
+            a.u2 = a.u1 + (size_t)h->S * h->Btot * (d.NC / 3);
         } else {
             a.q = (const float *)h->ws_noise.p;
         }
@@ -223,8 +251,8 @@ int do_run(wrnn_handle *h, uint64_t seed, cudaStream_t st, const StageOpts &o) {
     a.samples = (float *)h->ws_samples.p;
     a.picks = (int32_t *)h->ws_picks.p;
     a.seed = seed;
-    a.Btot = h->B;
-    a.b0 = 0;
+    a.Btot = h->Btot;
+    a.b0 = h->fold_lo;
     // barrier counter (bytes 0..63) is cleared per run; the abort flag (byte 64) is STICKY: it stays set across runs
     // until a fetch has reported it (check_abort), so a benchmark that runs N times and fetches once cannot count an
     // aborted (early-exited) iteration as throughput
@@ -241,7 +269,7 @@ int do_run(wrnn_handle *h, uint64_t seed, cudaStream_t st, const StageOpts &o) {
         for (int64_t b0 = 0; b0 < h->B; b0 += per) {
             LoopArgs g = a;
             g.B = std::min<int64_t>(per, h->B - b0);
-            g.b0 = b0;
+            g.b0 = h->fold_lo + b0;
             g.cond = a.cond + (size_t)b0 * h->S * CW;
             g.fold_len = a.fold_len + b0;
             g.samples = a.samples + (size_t)b0 * h->S;
@@ -255,7 +283,7 @@ int do_run(wrnn_handle *h, uint64_t seed, cudaStream_t st, const StageOpts &o) {
     }
     WRNN_CUDA(h, cudaEventRecord(h->ev[2], st));
     // float64 tail (:243-258)
-    if (!o.want_logits) {
+    if (!o.want_logits && h->Btot == h->B) {      // under a fold range the float64 tail belongs to whoever gathers the shards
         int64_t max_wave = 0;
         for (auto &ut : h->utts) max_wave = std::max(max_wave, ut.wave_len);
         const double *tab = (const double *)h->ws_tables.p;
@@ -301,6 +329,9 @@ int wrnn_run_staged(wrnn_handle *h, uint64_t seed, void *cuda_stream) {
 int wrnn_fetch(wrnn_handle *h, double *const *out, int64_t *out_len, void *cuda_stream) {
     if (!h || !out) return fail(h, WRNN_ERR_ARG, "null argument");
     if (!h->staged) return fail(h, WRNN_ERR_STATE, "nothing staged");
+    if (h->Btot != h->B)
+        return fail(h, WRNN_ERR_STATE, "a fold range is staged: the waveform exists only after the shards are gathered "
+                                       "(wrnn_fetch_samples, then the host cross-fade: wavernn_b200/shard.py)");
     WRNN_DEVICE(h);
     cudaStream_t st = (cudaStream_t)cuda_stream;
     const size_t bytes = (size_t)h->total_out * sizeof(double);
@@ -348,13 +379,22 @@ int wrnn_last_timing(wrnn_handle *h, float *ms_cond, float *ms_loop, float *ms_t
     return 0;
 }
 
+int wrnn_set_fold_range(wrnn_handle *h, int64_t lo, int64_t hi) {
+    if (!h) return WRNN_ERR_ARG;
+    if (lo < 0 || hi < lo) return fail(h, WRNN_ERR_ARG, "bad fold range");
+    h->range_lo = lo;
+    h->range_hi = hi;
+    h->staged = false;
+    return 0;
+}
+
 int wrnn_fetch_samples(wrnn_handle *h, float *samples, void *cuda_stream) {
     if (!h || !samples) return fail(h, WRNN_ERR_ARG, "null argument");
     if (!h->staged) return fail(h, WRNN_ERR_STATE, "nothing staged");
     WRNN_DEVICE(h);
     cudaStream_t st = (cudaStream_t)cuda_stream;
     WRNN_CUDA(h, cudaMemcpyAsync(samples, h->ws_samples.p, (size_t)h->B * h->S * sizeof(float), cudaMemcpyDeviceToHost, st));
-    WRNN_CUDA(h, cudaStreamSynchronize(st));
+    WRNN_TRY(check_abort(h, st));      // synchronises the stream; a shard must not hand on samples of an aborted loop
     return 0;
 }
 

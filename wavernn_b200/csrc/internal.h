@@ -121,6 +121,8 @@ struct wrnn_handle {
     // staged call
     struct Utt { int T, Tin, Tp; int64_t L, wave_len, fold0, nfolds, mel_off, up_off, res_off, out_off, pm_off; };
     int64_t total_frames = 0;          // padded frames of all staged utterances
+    int64_t range_lo = 0, range_hi = 0;    // wrnn_set_fold_range: [lo, hi) of the next single-utterance batched stage, 0/0 = all
+    int64_t fold_lo = 0, Btot = 0;         // staged: first global fold of this call, fold count of the whole utterance(s)
     std::vector<Utt> utts;
     bool staged = false;
     int batched = 0, mu_law = 0;

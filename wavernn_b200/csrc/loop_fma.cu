@@ -178,13 +178,13 @@ __global__ void __launch_bounds__(FMA_THREADS, 1) fma_loop_kernel(const FmaParam
                     if (d.mode == WRNN_MODE_MOL) {
                         float myu1 = 0.5f, u2;
                         if (P.a.u1) {
-                            if (lane < nmix) myu1 = P.a.u1[((size_t)tp * B + b) * nmix + lane];
-                            u2 = P.a.u2[(size_t)tp * B + b];
+                            if (lane < nmix) myu1 = P.a.u1[((size_t)tp * P.a.Btot + P.a.b0 + b) * nmix + lane];
+                            u2 = P.a.u2[(size_t)tp * P.a.Btot + P.a.b0 + b];
                         } else {
-                            const uint4 r = philox4x32(make_uint4((uint32_t)tp, (uint32_t)b, (uint32_t)(lane >> 2), 1u), key);
+                            const uint4 r = philox4x32(make_uint4((uint32_t)tp, (uint32_t)(P.a.b0 + b), (uint32_t)(lane >> 2), 1u), key);
                             const uint32_t rr[4] = {r.x, r.y, r.z, r.w};
                             myu1 = u_clip(rr[lane & 3]);
-                            const uint4 r2 = philox4x32(make_uint4((uint32_t)tp, (uint32_t)b, 0u, 2u), key);
+                            const uint4 r2 = philox4x32(make_uint4((uint32_t)tp, (uint32_t)(P.a.b0 + b), 0u, 2u), key);
                             u2 = u_clip(r2.x);
                         }
                         xv = mol_sample_warp(lg, nmix, myu1, u2, lane, &pick);
@@ -194,8 +194,8 @@ __global__ void __launch_bounds__(FMA_THREADS, 1) fma_loop_kernel(const FmaParam
                         float *lrow = obuf + (size_t)warp * NC;     // obuf is free during P0's sampling
                         for (int i = lane; i < NC; i += 32) lrow[i] = ld_cg(lg + i);
                         __syncwarp();
-                        const float *qsrc = P.a.q ? P.a.q + ((size_t)tp * B + b) * NC : nullptr;
-                        pick = categorical_warp(lrow, NC, qsrc, key, (uint32_t)tp, (uint32_t)b, 3u, lane);
+                        const float *qsrc = P.a.q ? P.a.q + ((size_t)tp * P.a.Btot + P.a.b0 + b) * NC : nullptr;
+                        pick = categorical_warp(lrow, NC, qsrc, key, (uint32_t)tp, (uint32_t)(P.a.b0 + b), 3u, lane);
                         xv = raw_value(pick, NC);
                         __syncwarp();
                     }
