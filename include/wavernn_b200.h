@@ -166,7 +166,8 @@ const char *wrnn_loop_kernel_name(wrnn_handle *h, int64_t folds);
  * 4 = "tcgen05-bf16x3" (csrc/loop_mma.cu: the contractions of fatchord_version.py:208-221 on the tensor
  * cores with bf16 hi/lo split operands and fp32 TMEM accumulators; default dims, MoL; auto from 48 folds up). */
 int wrnn_set_loop_kernel(wrnn_handle *h, int32_t which);
-/* Fold-tile width N of the tensor-core kernel's (128 rows x N folds) jobs: 0 = auto, else a multiple of 16 <= 128. */
+/* Kept for callers of earlier builds: the tensor-core kernel's fold tile is the M of its MMAs (128 folds = the 128 TMEM
+ * lanes) and no longer a choice.  The argument is validated (0, or a multiple of 16 <= 128) and otherwise ignored. */
 int wrnn_set_mma_fold_tile(wrnn_handle *h, int32_t nt);
 /* Bring-up aid: recurrent state of the last tensor-core run, (folds, 512) float32: which = 0 h1, 1 h2, 2 fc2 output.
  * With the environment variable WRNN_MMA_STEPS=n the kernel stops after n loop steps so the state can be compared

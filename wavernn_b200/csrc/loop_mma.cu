@@ -41,19 +41,21 @@ namespace wrnn {
 namespace mma {
 
 constexpr int H = 512, FCD = 512, AUX = 32, FEAT = 80;
-constexpr int UT = 32;                     // GRU units per row tile: rows [r(32) | z(32) | n(32)] = 96 of the MMA's 128
+constexpr int UT = 32;                     // GRU units per row tile: weight rows [r(32) | z(32) | n(32)] = N = 96 of an MMA
 constexpr int GRU_ROWS = 3 * UT, FC_ROWS = 128;
+constexpr int FT = 128;                    // folds per tile = M of the MMA = TMEM lanes: lane i of the accumulators is fold i
 constexpr int MT_GRU = H / UT, MT_FC = FCD / FC_ROWS;     // 16, 4 row tiles
 constexpr int KC = 4;                      // k-chunks (of 8 elements) per pipeline stage: K = 32 = two MMA k-steps
 constexpr int MAXSTAGE = 8;                // ring depth is chosen at launch: as many stages as shared memory holds, up to 8
-constexpr int A_GRU = 2 * KC * GRU_ROWS * 16, A_FC = 2 * KC * FC_ROWS * 16;     // 12288 / 16384 B per stage: hi + lo
+constexpr int W_GRU = 2 * KC * GRU_ROWS * 16, W_FC = 2 * KC * FC_ROWS * 16;     // weight block of a stage, hi + lo: 12288 / 16384 B
+constexpr int ACT_STAGE = 2 * KC * FT * 16;                                      // activation block of a stage, hi + lo: 16384 B
 constexpr int CGROUPS = 7;                 // conditioning operand: 28 chunks = 224 elements per fold
 constexpr int HGROUPS = H / 32;            // 16 stage groups in a 512-wide operand
 constexpr int THREADS = 320, EPI_THREADS = 256, EPI_WARPS = 8;
-constexpr int STG_FLOATS = 2 * 3 * UT * 33;               // epilogue staging (GRU: two accumulators x three gates)
+constexpr int SBIAS = 2 * 2 * GRU_ROWS + 2 * FC_ROWS;     // this CTA's biases in shared memory: rnn1 / rnn2 (input, recurrent), fc1 / fc2
 constexpr int NCP = 32;                    // fc3 rows padded (MoL: 30)
 constexpr int TMEM_COLS = 512;
-constexpr int FIXED_SMEM = (STG_FLOATS + NCP * FCD + EPI_WARPS * 256) * 4;       // staging + fc3 rows + per-warp scratch
+constexpr int FIXED_SMEM = (SBIAS + NCP * FCD + EPI_WARPS * 256) * 4;            // biases + fc3 rows + per-warp scratch
 // conditioning operand element order (which features each layer concatenates):
 //   [a4 (32) | a2 (32) | x_prev (1) | m (80) | a1 (32) | a3 (32) | zero (15)]
 // so that rnn1 reads chunks 8..23, rnn2 chunks 4..23, fc1 chunks 8..27, fc2 chunks 0..3.
@@ -66,8 +68,9 @@ constexpr int C_A4 = 0, C_A2 = 32, C_X = 64, C_M = 65, C_A1 = 145, C_A3 = 177, C
 // an fc CTA runs J_F1 (fc1) -> ReLU -> J_F2 (fc2) -> ReLU.  (loop_res.cu's "shadow products", on tensor cores.)
 enum { J_R1 = 0, J_R2, J_S1, J_S2, J_F1, J_F2, NJOB };
 enum { ARR_C = 0, ARR_H1NEW, ARR_H2NEW, ARR_S12, ARR_Y1 };
-// TMEM accumulator of each job, in units of NT columns: rnn1 reads X1 + H1, rnn2 reads X2 + H2; fc reuses X1's columns
-__host__ __device__ inline int job_acc(int jt) { return jt == J_R1 ? 0 : jt == J_S1 ? 1 : jt == J_R2 ? 2 : jt == J_S2 ? 3 : 0; }
+// TMEM accumulator (first column) of each job: 128 lanes = folds, columns = weight rows.  rnn1's gates read X1 + H1,
+// rnn2's X2 + H2 (96 columns each: [r | z | n] x 32 units), the fc jobs share the last 128 columns.
+__host__ __device__ inline int job_acc(int jt) { return jt == J_R1 ? 0 : jt == J_S1 ? 96 : jt == J_R2 ? 192 : jt == J_S2 ? 288 : 384; }
 __host__ __device__ inline int job_stages(int jt) { return jt == J_R1 ? 4 : jt == J_R2 ? 21 : jt == J_F1 ? 21 : jt == J_F2 ? 17 : 16; }
 __host__ __device__ inline int job_rows(int jt) { return jt >= J_F1 ? FC_ROWS : GRU_ROWS; }
 // grid counter a job's loads wait for (value G * (t + 1)), -1 = ordered behind the previous job of the same CTA
@@ -87,6 +90,7 @@ __host__ __device__ inline StageInfo stage_info(int jt, int s) {
 struct Params {
     LoopArgs a;
     int NT, NTILES, G, NC;
+    int dbg_state;                 // WRNN_MMA_STEPS set: also store the fp32 recurrent state (wrnn_debug_mma_state)
     int64_t steps_run;             // == a.S except under WRNN_MMA_STEPS (bring-up: stop after n steps and inspect the state)
     int ring_bytes;                // shared memory of the stage ring (the staging / fc3 / scratch region follows it)
     const uint8_t *Aimg;           // packed weights: job type j at offA[j], [row tile][stage][hi|lo][KC][rows][8] bf16
@@ -157,6 +161,11 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {  
         : "r"(taddr) : "memory");
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
+__device__ __forceinline__ void tmem_ld8_nowait(uint32_t taddr, uint32_t (&r)[8]) {    // thread i <- lane i, 8 consecutive columns
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]) : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 // Shared-memory matrix descriptor, K-major, no swizzle: element (row r, k) of the operand sits at
 //   start + (r % 8) * 16 + (r / 8) * SBO + (k / 8) * LBO + (k % 8) * 2   bytes.
 // With the image [k-chunk][rows][8]: SBO = 128 (eight 16-byte rows), LBO = rows * 16.
@@ -216,6 +225,15 @@ __device__ __forceinline__ void split4(const float (&v)[4], uint2 &hi, uint2 &lo
     hi.y = (uint32_t)__bfloat16_as_ushort(h[2]) | ((uint32_t)__bfloat16_as_ushort(h[3]) << 16);
     lo.x = (uint32_t)__bfloat16_as_ushort(l[0]) | ((uint32_t)__bfloat16_as_ushort(l[1]) << 16);
     lo.y = (uint32_t)__bfloat16_as_ushort(l[2]) | ((uint32_t)__bfloat16_as_ushort(l[3]) << 16);
+}
+// eight floats -> one 16-byte chunk of the hi image and one of the lo image
+__device__ __forceinline__ void split8(const float (&v)[8], uint4 &hi, uint4 &lo) {
+    const float a[4] = {v[0], v[1], v[2], v[3]}, b[4] = {v[4], v[5], v[6], v[7]};
+    uint2 h0, l0, h1, l1;
+    split4(a, h0, l0);
+    split4(b, h1, l1);
+    hi = make_uint4(h0.x, h0.y, h1.x, h1.y);
+    lo = make_uint4(l0.x, l0.y, l1.x, l1.y);
 }
 // byte offset of the 16-byte slot (fold fi of tile nt, feature chunk `chunk`) in a B operand with NG stage groups
 __device__ __forceinline__ size_t b_slot(int NT, int NG, int nt, int chunk, int fi, int hl) {
@@ -294,18 +312,18 @@ __device__ __forceinline__ const uint8_t *b_array(const Params &P, int arr, int6
 }
 
 struct Ring {                   // the stage ring of this CTA and a position in it (producer and MMA issuer keep one each)
-    uint32_t nstage, a_slot, stage_bytes;       // depth, bytes reserved for the weight block of a stage, bytes per stage
+    uint32_t nstage, w_slot, stage_bytes;       // depth, bytes reserved for the weight block of a stage, bytes per stage
     uint32_t slot, par;
     __device__ __forceinline__ void advance() {
         if (++slot == nstage) { slot = 0; par ^= 1u; }
     }
 };
 // A CTA that only ever runs GRU jobs (96-row weight blocks) packs its stages tighter than one that also has an fc job;
-// the ring is as deep as its share of shared memory allows (4 stages at 128 folds per tile, 7 at 16).
+// the ring is as deep as its share of shared memory allows (5 stages of 28 KB for a GRU CTA).
 __device__ __forceinline__ Ring make_ring(const Params &P, bool has_fc) {
     Ring r;
-    r.a_slot = has_fc ? A_FC : A_GRU;
-    r.stage_bytes = r.a_slot + 2u * KC * (uint32_t)P.NT * 16u;
+    r.w_slot = has_fc ? W_FC : W_GRU;
+    r.stage_bytes = r.w_slot + ACT_STAGE;
     r.nstage = min((uint32_t)MAXSTAGE, (uint32_t)P.ring_bytes / r.stage_bytes);
     r.slot = 0;
     r.par = 0;
@@ -323,7 +341,7 @@ constexpr int NPROD = 8;
 __device__ __forceinline__ void produce_job(const Params &P, int jt, int mt, int nt, int64_t t, Ring &r, uint32_t &count, int lane,
                                             uint8_t *stages, uint64_t *bar_full, uint64_t *bar_empty, Watch &w, long long *pacc = nullptr) {
     const int nst = job_stages(jt), gate = job_gate(jt);
-    const uint32_t abytes = 2u * KC * (uint32_t)job_rows(jt) * 16u, bbytes = 2u * KC * (uint32_t)P.NT * 16u;
+    const uint32_t abytes = 2u * KC * (uint32_t)job_rows(jt) * 16u, bbytes = ACT_STAGE;       // weight block, activation block
     if (gate >= 0) {            // this job's operands were written by that phase of every CTA
         grid_wait(P.gs, gate, (unsigned long long)P.G * (unsigned long long)(t + 1), w);
         fence_proxy_async_global();
@@ -341,7 +359,7 @@ __device__ __forceinline__ void produce_job(const Params &P, int jt, int mt, int
             } else {
                 const StageInfo si = stage_info(jt, s);
                 const int NG = si.arr == ARR_C ? CGROUPS : HGROUPS;
-                bulk_g2s(dst + r.a_slot, b_array(P, si.arr, t) + (size_t)(nt * NG + si.g) * bbytes, bbytes, &bar_full[r.slot]);
+                bulk_g2s(dst + r.w_slot, b_array(P, si.arr, t) + (size_t)(nt * NG + si.g) * bbytes, bbytes, &bar_full[r.slot]);
             }
         }
         r.advance();
@@ -349,28 +367,30 @@ __device__ __forceinline__ void produce_job(const Params &P, int jt, int mt, int
 }
 
 // One job of the MMA issuer thread: three MMAs (hi.hi, hi.lo, lo.hi) per k-step into the job's accumulator.
-__device__ __forceinline__ void issue_job(const Params &P, int jt, Ring &r, uint32_t stage0, uint32_t tb, uint32_t idesc,
+__device__ __forceinline__ void issue_job(const Params &P, int jt, Ring &r, uint32_t stage0, uint32_t tb,
                                           uint64_t *bar_full, uint64_t *bar_empty, uint64_t *bar_tfull, Watch &w, long long *macc = nullptr) {
     const int nst = job_stages(jt);
-    const uint32_t rows = job_rows(jt), NT = P.NT;
-    // descriptors differ only in the 14-bit start-address field (16-byte units): constant part once per job
-    const uint64_t dA0 = make_desc(0, rows * 16u, 128), dB0 = make_desc(0, NT * 16u, 128);
-    const uint32_t stepA = 2u * rows, stepB = 2u * NT;          // two k-chunks, in 16-byte units
-    const uint32_t loA = KC * rows, loB = KC * NT;               // hi -> lo image
-    const uint32_t d = tb + (uint32_t)job_acc(jt) * NT;
+    const uint32_t rows = job_rows(jt);
+    // A = activations (M = 128 folds), B = weights (N = rows); both K-major, no swizzle, [k-chunk][row][8].  Descriptors
+    // differ only in the 14-bit start-address field (16-byte units): constant part once per job.
+    const uint64_t dW0 = make_desc(0, rows * 16u, 128), dX0 = make_desc(0, FT * 16u, 128);
+    const uint32_t stepW = 2u * rows, stepX = 2u * FT;          // two k-chunks, in 16-byte units
+    const uint32_t loW = KC * rows, loX = KC * FT;               // hi -> lo image
+    const uint32_t d = tb + (uint32_t)job_acc(jt);
+    const uint32_t idesc = make_idesc(FT, (int)rows);
     for (int s = 0; s < nst; s++) {
         const long long c0 = macc ? clock64() : 0;
         mbar_wait(&bar_full[r.slot], r.par, w);
         tc_fence_after();
         const long long c1 = macc ? clock64() : 0;
-        const uint32_t aA = (stage0 + r.slot * r.stage_bytes) >> 4, aB = aA + (r.a_slot >> 4);
+        const uint32_t aW = (stage0 + r.slot * r.stage_bytes) >> 4, aX = aW + (r.w_slot >> 4);
 #pragma unroll
         for (int ks = 0; ks < KC / 2; ks++) {
-            const uint64_t ah = dA0 + (aA + ks * stepA), al = dA0 + (aA + loA + ks * stepA);
-            const uint64_t bh = dB0 + (aB + ks * stepB), bl = dB0 + (aB + loB + ks * stepB);
-            umma_bf16(d, ah, bh, idesc, (s == 0 && ks == 0) ? 0u : 1u);
-            umma_bf16(d, ah, bl, idesc, 1u);
-            umma_bf16(d, al, bh, idesc, 1u);
+            const uint64_t wh = dW0 + (aW + ks * stepW), wl = dW0 + (aW + loW + ks * stepW);
+            const uint64_t xh = dX0 + (aX + ks * stepX), xl = dX0 + (aX + loX + ks * stepX);
+            umma_bf16(d, xh, wh, idesc, (s == 0 && ks == 0) ? 0u : 1u);
+            umma_bf16(d, xh, wl, idesc, 1u);
+            umma_bf16(d, xl, wh, idesc, 1u);
         }
         const long long c2 = macc ? clock64() : 0;
         umma_commit(&bar_empty[r.slot]);          // the stage is free once these MMAs have read it
@@ -381,112 +401,101 @@ __device__ __forceinline__ void issue_job(const Params &P, int jt, Ring &r, uint
 }
 
 // ---------------------------------------------------------------------------- epilogues (256 threads, warps 2..9)
-// GRU gates (fatchord_version.py:210-216) of one (32 units x NT folds) tile: accumulators X (input side) and H (recurrent
-// side, formed one step ahead) hold rows [r | z | n]; h' goes out as fp32 state and as the bf16 hi/lo operand of the
-// next products; rnn2 also emits s12 = h1' + h2' (fc1 reads x + h1 + h2, x is folded into fc1's weights).
-__device__ __forceinline__ void epi_gru(const Params &P, int layer, int mt, int nt, int64_t t, uint32_t tb, float *stg, int etid,
-                                        int q, int half, int lane) {
-    const int NT = P.NT;
-    const float *bi = P.bias + (size_t)(layer * MT_GRU + mt) * 2 * GRU_ROWS, *bh = bi + GRU_ROWS;
-    float *hf = layer == 0 ? P.h1f : P.h2f;
-    uint8_t *Hn = layer == 0 ? P.H1[(t + 1) & 1] : P.H2[(t + 1) & 1];
-    const uint32_t colX = (uint32_t)job_acc(layer == 0 ? J_R1 : J_R2) * NT, colH = (uint32_t)job_acc(layer == 0 ? J_S1 : J_S2) * NT;
-    const int f = etid & 31, quad = etid >> 5, u0 = quad * 4, gu = mt * UT + u0;
-    float bir[4], biz[4], bin[4], bhr[4], bhz[4], bhn[4];
+// Accumulators are [128 folds (TMEM lanes)] x [weight rows (columns)], so a thread owns ONE fold (lane 32 q + lane of the
+// warp's lane quarter q = warp % 4) and reads the r, z, n columns of a unit straight from its own lane: no shared-memory
+// staging, no barrier inside an epilogue; the two warps of a quarter split the columns (`half`).  Operand stores are one
+// 16-byte chunk (8 units) per image per thread, consecutive lanes = consecutive folds = consecutive addresses.
+//
+// GRU gates (fatchord_version.py:210-216): X (input side) and H (recurrent side, formed one step ahead) hold columns
+// [r | z | n] x 32 units; the thread keeps the state of its (fold, 16 units) in registers for the whole run (`hst`).
+// rnn2 also emits s12 = h1' + h2' (fc1 reads x + h1 + h2; x is folded into fc1's weights).
+template <int LAYER>
+__device__ __forceinline__ void epi_gru(const Params &P, int mt, int nt, int64_t t, uint32_t tb, const float *sb, float (&hst)[16],
+                                        float (&h1new)[16], int q, int half, int lane) {
+    const int fi = q * 32 + lane, u0 = half * 16, gu = mt * UT + u0;
+    const size_t fold = (size_t)nt * FT + fi;
+    const float *bi = sb + LAYER * 2 * GRU_ROWS, *bh = bi + GRU_ROWS;
+    float *hf = LAYER == 0 ? P.h1f : P.h2f;
+    uint8_t *Hn = LAYER == 0 ? P.H1[(t + 1) & 1] : P.H2[(t + 1) & 1];
+    const uint32_t base = tb + ((uint32_t)(q * 32) << 16), colX = base + (uint32_t)job_acc(LAYER == 0 ? J_R1 : J_R2) + u0,
+                   colH = base + (uint32_t)job_acc(LAYER == 0 ? J_S1 : J_S2) + u0;
 #pragma unroll
-    for (int i = 0; i < 4; i++) {
-        bir[i] = __ldg(bi + 0 * UT + u0 + i); biz[i] = __ldg(bi + 1 * UT + u0 + i); bin[i] = __ldg(bi + 2 * UT + u0 + i);
-        bhr[i] = __ldg(bh + 0 * UT + u0 + i); bhz[i] = __ldg(bh + 1 * UT + u0 + i); bhn[i] = __ldg(bh + 2 * UT + u0 + i);
-    }
-    for (int c0 = 0; c0 < NT; c0 += 32) {
-        const int fi = c0 + f;
-        const size_t fold = (size_t)nt * NT + fi;
-        float4 hp4 = make_float4(0.f, 0.f, 0.f, 0.f), a4 = hp4;
-        if (fi < NT) {                          // own state of the step before / rnn1's new state: in flight under the TMEM read
-            hp4 = __ldcg(reinterpret_cast<const float4 *>(hf + fold * H + gu));
-            if (layer == 1) a4 = __ldcg(reinterpret_cast<const float4 *>(P.h1f + fold * H + gu));
-        }
-        if (q < 3) {
-            uint32_t r[32];
-            tmem_ld32(tb + ((uint32_t)(q * 32) << 16) + (half ? colH : colX) + (uint32_t)c0, r);
-            float *dst = stg + ((half * 3 + q) * UT + lane) * 33;
+    for (int g = 0; g < 2; g++) {
+        uint32_t xr[8], xz[8], xn[8], hr[8], hz[8], hn_[8];
+        tmem_ld8_nowait(colX + 8 * g, xr);
+        tmem_ld8_nowait(colX + UT + 8 * g, xz);
+        tmem_ld8_nowait(colX + 2 * UT + 8 * g, xn);
+        tmem_ld8_nowait(colH + 8 * g, hr);
+        tmem_ld8_nowait(colH + UT + 8 * g, hz);
+        tmem_ld8_nowait(colH + 2 * UT + 8 * g, hn_);
+        tmem_ld_wait();
+        float hn[8];
 #pragma unroll
-            for (int i = 0; i < 32; i++) dst[i] = __uint_as_float(r[i]);
+        for (int i = 0; i < 8; i++) {
+            const int u = u0 + 8 * g + i;
+            hn[i] = gru_update_fast(__uint_as_float(xr[i]) + bi[u], __uint_as_float(xz[i]) + bi[UT + u], __uint_as_float(xn[i]) + bi[2 * UT + u],
+                                    __uint_as_float(hr[i]) + bh[u], __uint_as_float(hz[i]) + bh[UT + u], __uint_as_float(hn_[i]) + bh[2 * UT + u],
+                                    hst[8 * g + i]);
+            hst[8 * g + i] = hn[i];
         }
-        epi_bar();
-        if (fi < NT) {
-            const float hp[4] = {hp4.x, hp4.y, hp4.z, hp4.w};
-            float hn[4];
+        if (P.dbg_state) {                  // fp32 copy of the state for wrnn_debug_mma_state only
+            float4 *dst = reinterpret_cast<float4 *>(hf + fold * H + gu + 8 * g);
+            dst[0] = make_float4(hn[0], hn[1], hn[2], hn[3]);
+            dst[1] = make_float4(hn[4], hn[5], hn[6], hn[7]);
+        }
+        uint4 hi, lo;
+        split8(hn, hi, lo);
+        const int chunk = (gu >> 3) + g;
+        *reinterpret_cast<uint4 *>(Hn + b_slot(FT, HGROUPS, nt, chunk, fi, 0)) = hi;
+        *reinterpret_cast<uint4 *>(Hn + b_slot(FT, HGROUPS, nt, chunk, fi, 1)) = lo;
+        if (LAYER == 1) {
+            float sm[8];
 #pragma unroll
-            for (int i = 0; i < 4; i++) {
-                const int u = u0 + i;
-                const float ir = stg[((0 * 3 + 0) * UT + u) * 33 + f] + bir[i];
-                const float iz = stg[((0 * 3 + 1) * UT + u) * 33 + f] + biz[i];
-                const float in_ = stg[((0 * 3 + 2) * UT + u) * 33 + f] + bin[i];
-                const float hr = stg[((1 * 3 + 0) * UT + u) * 33 + f] + bhr[i];
-                const float hz = stg[((1 * 3 + 1) * UT + u) * 33 + f] + bhz[i];
-                const float hnn = stg[((1 * 3 + 2) * UT + u) * 33 + f] + bhn[i];
-                hn[i] = gru_update_fast(ir, iz, in_, hr, hz, hnn, hp[i]);
-            }
-            *reinterpret_cast<float4 *>(hf + fold * H + gu) = make_float4(hn[0], hn[1], hn[2], hn[3]);
-            uint2 hi, lo;
-            split4(hn, hi, lo);
-            const int sub = (gu & 7) * 2;       // 0 or 8 bytes inside the 16-byte chunk
-            *reinterpret_cast<uint2 *>(Hn + b_slot(NT, HGROUPS, nt, gu >> 3, fi, 0) + sub) = hi;
-            *reinterpret_cast<uint2 *>(Hn + b_slot(NT, HGROUPS, nt, gu >> 3, fi, 1) + sub) = lo;
-            if (layer == 1) {
-                const float sm[4] = {a4.x + hn[0], a4.y + hn[1], a4.z + hn[2], a4.w + hn[3]};
-                split4(sm, hi, lo);
-                *reinterpret_cast<uint2 *>(P.S12 + b_slot(NT, HGROUPS, nt, gu >> 3, fi, 0) + sub) = hi;
-                *reinterpret_cast<uint2 *>(P.S12 + b_slot(NT, HGROUPS, nt, gu >> 3, fi, 1) + sub) = lo;
-            }
+            for (int i = 0; i < 8; i++) sm[i] = h1new[8 * g + i] + hn[i];
+            split8(sm, hi, lo);
+            *reinterpret_cast<uint4 *>(P.S12 + b_slot(FT, HGROUPS, nt, chunk, fi, 0)) = hi;
+            *reinterpret_cast<uint4 *>(P.S12 + b_slot(FT, HGROUPS, nt, chunk, fi, 1)) = lo;
+        } else {
+#pragma unroll
+            for (int i = 0; i < 8; i++) h1new[8 * g + i] = hn[i];
         }
-        epi_bar();
     }
 }
 
-// fc1 / fc2 + ReLU (:217-221) of one (128 rows x NT folds) tile: fc1 -> bf16 hi/lo operand of fc2, fc2 -> fp32 rows for fc3
-__device__ __forceinline__ void epi_fc(const Params &P, int layer, int mt, int nt, uint32_t tb, float *stg, int etid, int q, int half,
-                                       int lane) {
-    const int NT = P.NT;
-    const float *bb = P.bias + (size_t)2 * MT_GRU * 2 * GRU_ROWS + (size_t)layer * FCD + mt * FC_ROWS;
-    const int f = etid & 31, rg = etid >> 5, gr = mt * FC_ROWS + rg * 16;
-    float bv[16];
+// fc1 / fc2 + ReLU (:217-221): 128 rows = 128 columns, 64 per thread.  fc1 -> bf16 hi/lo operand of fc2, fc2 -> fp32 rows for fc3
+template <int LAYER>
+__device__ __forceinline__ void epi_fc(const Params &P, int mt, int nt, uint32_t tb, const float *sb, int q, int half, int lane) {
+    const int fi = q * 32 + lane, r0 = half * 64, gr = mt * FC_ROWS + r0;
+    const size_t fold = (size_t)nt * FT + fi;
+    const float *bb = sb + 4 * GRU_ROWS + LAYER * FC_ROWS + r0;
+    const uint32_t col = tb + ((uint32_t)(q * 32) << 16) + (uint32_t)job_acc(J_F1) + r0;
+#pragma unroll 2
+    for (int g = 0; g < 8; g += 2) {
+        uint32_t a[8], b[8];
+        tmem_ld8_nowait(col + 8 * g, a);
+        tmem_ld8_nowait(col + 8 * g + 8, b);
+        tmem_ld_wait();
+        float va[8], vb[8];
 #pragma unroll
-    for (int i = 0; i < 16; i++) bv[i] = __ldg(bb + rg * 16 + i);
-    for (int c0 = 0; c0 < NT; c0 += 32) {
-        if (half == 0) {
-            uint32_t r[32];
-            tmem_ld32(tb + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, r);
-            float *dst = stg + (q * 32 + lane) * 33;
-#pragma unroll
-            for (int i = 0; i < 32; i++) dst[i] = __uint_as_float(r[i]);
+        for (int i = 0; i < 8; i++) {
+            va[i] = fmaxf(__uint_as_float(a[i]) + bb[8 * g + i], 0.f);
+            vb[i] = fmaxf(__uint_as_float(b[i]) + bb[8 * g + 8 + i], 0.f);
         }
-        epi_bar();
-        const int fi = c0 + f;
-        if (fi < NT) {
-            const size_t fold = (size_t)nt * NT + fi;
-            float v[16];
-#pragma unroll
-            for (int i = 0; i < 16; i++) v[i] = fmaxf(stg[(rg * 16 + i) * 33 + f] + bv[i], 0.f);
-            if (layer == 0) {
-#pragma unroll
-                for (int c = 0; c < 2; c++) {
-                    const float v0[4] = {v[8 * c], v[8 * c + 1], v[8 * c + 2], v[8 * c + 3]};
-                    const float v1[4] = {v[8 * c + 4], v[8 * c + 5], v[8 * c + 6], v[8 * c + 7]};
-                    uint2 h0, l0, h1, l1;
-                    split4(v0, h0, l0);
-                    split4(v1, h1, l1);
-                    *reinterpret_cast<uint4 *>(P.Y1 + b_slot(NT, HGROUPS, nt, (gr >> 3) + c, fi, 0)) = make_uint4(h0.x, h0.y, h1.x, h1.y);
-                    *reinterpret_cast<uint4 *>(P.Y1 + b_slot(NT, HGROUPS, nt, (gr >> 3) + c, fi, 1)) = make_uint4(l0.x, l0.y, l1.x, l1.y);
-                }
-            } else {
-                float4 *dst = reinterpret_cast<float4 *>(P.y2f + fold * FCD + gr);
-#pragma unroll
-                for (int c = 0; c < 4; c++) dst[c] = make_float4(v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
-            }
+        if (LAYER == 0) {
+            uint4 hi, lo;
+            split8(va, hi, lo);
+            *reinterpret_cast<uint4 *>(P.Y1 + b_slot(FT, HGROUPS, nt, (gr >> 3) + g, fi, 0)) = hi;
+            *reinterpret_cast<uint4 *>(P.Y1 + b_slot(FT, HGROUPS, nt, (gr >> 3) + g, fi, 1)) = lo;
+            split8(vb, hi, lo);
+            *reinterpret_cast<uint4 *>(P.Y1 + b_slot(FT, HGROUPS, nt, (gr >> 3) + g + 1, fi, 0)) = hi;
+            *reinterpret_cast<uint4 *>(P.Y1 + b_slot(FT, HGROUPS, nt, (gr >> 3) + g + 1, fi, 1)) = lo;
+        } else {
+            float4 *dst = reinterpret_cast<float4 *>(P.y2f + fold * FCD + gr + 8 * g);
+            dst[0] = make_float4(va[0], va[1], va[2], va[3]);
+            dst[1] = make_float4(va[4], va[5], va[6], va[7]);
+            dst[2] = make_float4(vb[0], vb[1], vb[2], vb[3]);
+            dst[3] = make_float4(vb[4], vb[5], vb[6], vb[7]);
         }
-        epi_bar();
     }
 }
 
@@ -494,13 +503,14 @@ __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ __align__(8) uint64_t bar_full[MAXSTAGE], bar_empty[MAXSTAGE], bar_tfull;
     __shared__ uint32_t tmem_base_s;
+    __shared__ int dead_s;
     uint8_t *stages = smem;
-    float *stg = reinterpret_cast<float *>(smem + P.ring_bytes);
-    float *wf3 = stg + STG_FLOATS;                          // [NCP][512]
+    float *sbias = reinterpret_cast<float *>(smem + P.ring_bytes);      // this CTA's bias rows, layout of SBIAS
+    float *wf3 = sbias + SBIAS;                             // [NCP][512]
     float *scr = wf3 + NCP * FCD;                           // per epilogue warp: 256 floats
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, cta = blockIdx.x;
-    const int NT = P.NT, G = P.G;
+    const int G = P.G;
     const int64_t S = P.a.S, B = P.a.B;
     Watch w{P.gs.abort_flag, false};
     // static roles: GRU (row tile, fold tile) jobs fill CTAs from 0 up, fc jobs from G - 1 down; at most one of each per CTA
@@ -514,6 +524,16 @@ __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
     }
     if (warp == 1) tmem_alloc(&tmem_base_s, TMEM_COLS);
     for (int i = tid; i < NCP * FCD; i += THREADS) wf3[i] = P.Wf3[i];
+    for (int i = tid; i < SBIAS; i += THREADS) {            // P.bias: rnn1 [16][2][96] | rnn2 [16][2][96] | fc1 [512] | fc2 [512]
+        float v = 0.f;
+        if (i < 4 * GRU_ROWS) {
+            if (has_gru) v = P.bias[(size_t)((i / (2 * GRU_ROWS)) * MT_GRU + mt_g) * 2 * GRU_ROWS + i % (2 * GRU_ROWS)];
+        } else if (has_fc) {
+            const int j = i - 4 * GRU_ROWS;
+            v = P.bias[(size_t)2 * MT_GRU * 2 * GRU_ROWS + (size_t)(j / FC_ROWS) * FCD + mt_f * FC_ROWS + j % FC_ROWS];
+        }
+        sbias[i] = v;
+    }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -556,29 +576,29 @@ __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
         // ======================================================================= MMA issuer
         if (lane == 0) {
             Ring r = make_ring(P, has_fc);
-            const uint32_t idesc = make_idesc(128, NT), stage0 = smem_u32(stages);
+            const uint32_t stage0 = smem_u32(stages);
             if (has_gru) {
-                issue_job(P, J_S1, r, stage0, tb, idesc, bar_full, bar_empty, &bar_tfull, w);
-                issue_job(P, J_S2, r, stage0, tb, idesc, bar_full, bar_empty, &bar_tfull, w);
+                issue_job(P, J_S1, r, stage0, tb, bar_full, bar_empty, &bar_tfull, w);
+                issue_job(P, J_S2, r, stage0, tb, bar_full, bar_empty, &bar_tfull, w);
             }
             for (int64_t t = 0; t < P.steps_run && !w.dead; t++) {
                 long long *ma = (P.prof && t == P.prof_step && (cta == 0 || cta == G - 1)) ? P.prof + (cta == 0 ? 0 : 64) + 40 : nullptr;
                 if (has_gru) {
-                    issue_job(P, J_R1, r, stage0, tb, idesc, bar_full, bar_empty, &bar_tfull, w, ma ? ma + 0 : nullptr);
+                    issue_job(P, J_R1, r, stage0, tb, bar_full, bar_empty, &bar_tfull, w, ma ? ma + 0 : nullptr);
                     PROF_MARK(10);
-                    issue_job(P, J_R2, r, stage0, tb, idesc, bar_full, bar_empty, &bar_tfull, w, ma ? ma + 3 : nullptr);
+                    issue_job(P, J_R2, r, stage0, tb, bar_full, bar_empty, &bar_tfull, w, ma ? ma + 3 : nullptr);
                     PROF_MARK(11);
-                    issue_job(P, J_S1, r, stage0, tb, idesc, bar_full, bar_empty, &bar_tfull, w, ma ? ma + 6 : nullptr);
+                    issue_job(P, J_S1, r, stage0, tb, bar_full, bar_empty, &bar_tfull, w, ma ? ma + 6 : nullptr);
                     PROF_MARK(12);
                 }
                 if (has_fc) {
-                    issue_job(P, J_F1, r, stage0, tb, idesc, bar_full, bar_empty, &bar_tfull, w, ma ? ma + 12 : nullptr);
+                    issue_job(P, J_F1, r, stage0, tb, bar_full, bar_empty, &bar_tfull, w, ma ? ma + 12 : nullptr);
                     PROF_MARK(13);
-                    issue_job(P, J_F2, r, stage0, tb, idesc, bar_full, bar_empty, &bar_tfull, w, ma ? ma + 15 : nullptr);
+                    issue_job(P, J_F2, r, stage0, tb, bar_full, bar_empty, &bar_tfull, w, ma ? ma + 15 : nullptr);
                     PROF_MARK(14);
                 }
                 if (has_gru) {
-                    issue_job(P, J_S2, r, stage0, tb, idesc, bar_full, bar_empty, &bar_tfull, w, ma ? ma + 9 : nullptr);
+                    issue_job(P, J_S2, r, stage0, tb, bar_full, bar_empty, &bar_tfull, w, ma ? ma + 9 : nullptr);
                     PROF_MARK(15);
                 }
             }
@@ -592,6 +612,10 @@ __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
         const uint2 key = make_uint2((uint32_t)P.a.seed, (uint32_t)(P.a.seed >> 32));
         const int nmix = P.NC / 3;
         uint32_t tpar = 0;                                   // parity of bar_tfull: one completion per job with an epilogue
+        // recurrent state of this thread's (fold, 16 units), both layers, and rnn1's new state for s12: registers for the whole run
+        float hst1[16], hst2[16], h1new[16];
+#pragma unroll
+        for (int i = 0; i < 16; i++) hst1[i] = hst2[i] = h1new[i] = 0.f;        // h1 = h2 = 0 (:194-195)
         auto publish = [&](int p) {                          // every writing thread fences, one thread releases the counter
             fence_proxy_async_global();
             epi_bar();
@@ -616,7 +640,8 @@ __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
             if (has_gru) {
                 wait_acc();
                 if (etid == 0) PROF_MARK(20);
-                epi_gru(P, 0, mt_g, nt_g, t, tb, stg, etid, q, half, lane);
+                epi_gru<0>(P, mt_g, nt_g, t, tb, sbias, hst1, h1new, q, half, lane);
+                if (etid == 0) PROF_MARK(16);
                 tc_fence_before();
             }
             publish(0);
@@ -624,7 +649,8 @@ __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
             if (has_gru) {
                 wait_acc();
                 if (etid == 0) PROF_MARK(22);
-                epi_gru(P, 1, mt_g, nt_g, t, tb, stg, etid, q, half, lane);
+                epi_gru<1>(P, mt_g, nt_g, t, tb, sbias, hst2, h1new, q, half, lane);
+                if (etid == 0) PROF_MARK(17);
                 tc_fence_before();
             }
             publish(1);
@@ -632,7 +658,8 @@ __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
             if (has_fc) {
                 wait_acc();
                 if (etid == 0) PROF_MARK(24);
-                epi_fc(P, 0, mt_f, nt_f, tb, stg, etid, q, half, lane);
+                epi_fc<0>(P, mt_f, nt_f, tb, sbias, q, half, lane);
+                if (etid == 0) PROF_MARK(18);
                 tc_fence_before();
             }
             publish(2);
@@ -640,7 +667,8 @@ __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
             if (has_fc) {
                 wait_acc();
                 if (etid == 0) PROF_MARK(26);
-                epi_fc(P, 1, mt_f, nt_f, tb, stg, etid, q, half, lane);
+                epi_fc<1>(P, mt_f, nt_f, tb, sbias, q, half, lane);
+                if (etid == 0) PROF_MARK(19);
                 tc_fence_before();
             }
             publish(3);
@@ -712,9 +740,9 @@ __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
             publish(4);
             if (etid == 0) PROF_MARK(30);
             // uniform exit on a fired watchdog
-            if (etid == 0) stg[0] = (w.dead || ld_volatile_s32(P.gs.abort_flag)) ? 1.f : 0.f;
+            if (etid == 0) dead_s = (w.dead || ld_volatile_s32(P.gs.abort_flag)) ? 1 : 0;
             epi_bar();
-            w.dead = stg[0] != 0.f;
+            w.dead = dead_s != 0;
             epi_bar();
         }
     }
@@ -871,24 +899,14 @@ int mma_plan(wrnn_handle *h) {
     pl.img_bytes = total;
     // everything the device offers minus the static part (barriers): the stage ring takes what staging / fc3 rows leave
     pl.smem_bytes = (h->smem_optin - 1024) / 1024 * 1024;
-    if (pl.smem_bytes < (size_t)FIXED_SMEM + 2 * (A_FC + 2 * KC * 128 * 16)) return 0;
+    if (pl.smem_bytes < (size_t)FIXED_SMEM + 2 * (W_FC + ACT_STAGE)) return 0;
     WRNN_CUDA(h, cudaFuncSetAttribute(mma::mma_loop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes));
     pl.ok = true;
     return 0;
 }
 
-// fold-tile width: the smallest multiple of 16 that puts the 16 x NTILES GRU jobs of a phase on distinct SMs
-// Fold-tile width N (a multiple of 16, <= 128): every CTA gets at most one GRU job and one fc job per step.  A tcgen05
-// MMA costs max(56, N / 2) clocks whatever N is below 112 (measured, scripts/mb_umma.cu), so narrow tiles are not
-// cheaper per instruction; they only shorten the operand copies and the epilogues.  Preferred: the narrowest tile that
-// gives GRU and fc jobs their own CTAs (20 jobs per fold tile), else the narrowest that fits the 16 GRU jobs per tile.
-int mma_pick_nt(int64_t B, int G) {
-    for (int nt = 16; nt <= 128; nt += 16)
-        if ((int64_t)(mma::MT_GRU + mma::MT_FC) * ((B + nt - 1) / nt) <= G) return nt;
-    for (int nt = 16; nt <= 128; nt += 16)
-        if ((int64_t)mma::MT_GRU * ((B + nt - 1) / nt) <= G) return nt;
-    return 128;
-}
+// The fold tile is the M of the MMA: 128 folds = the 128 TMEM lanes, fixed.  16 GRU jobs + 4 fc jobs per fold tile; up to
+// num_sms / 16 tiles (9 on a B200: 1152 folds) so that every CTA has at most one GRU job; fc jobs fill CTAs from the top.
 int64_t mma_max_folds(const wrnn_handle *h) { return (int64_t)128 * (h->num_sms / mma::MT_GRU); }
 
 int mma_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
@@ -897,7 +915,7 @@ int mma_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
     Params P;
     P.a = a;
     P.G = h->num_sms;
-    P.NT = h->mma_force_nt > 0 ? h->mma_force_nt : mma_pick_nt(a.B, P.G);
+    P.NT = FT;
     P.NTILES = (int)((a.B + P.NT - 1) / P.NT);
     if (MT_GRU * P.NTILES > P.G)
         return fail(h, WRNN_ERR_ARG, "tensor-core loop kernel: %lld folds in tiles of %d need %d CTAs, the device has %d",
@@ -905,7 +923,11 @@ int mma_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
     P.ring_bytes = (int)(pl.smem_bytes - FIXED_SMEM) / 1024 * 1024;
     P.NC = h->d.NC;
     P.steps_run = a.S;
-    if (const char *e = getenv("WRNN_MMA_STEPS")) P.steps_run = std::min<int64_t>(a.S, std::max(1, atoi(e)));
+    P.dbg_state = 0;
+    if (const char *e = getenv("WRNN_MMA_STEPS")) {
+        P.steps_run = std::min<int64_t>(a.S, std::max(1, atoi(e)));
+        P.dbg_state = 1;
+    }
     P.Aimg = pl.Aimg;
     for (int j = 0; j < NJOB; j++) P.offA[j] = pl.offA[j];
     P.bias = pl.bias;
@@ -948,7 +970,7 @@ int mma_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
             "producer: step begin", "producer: rnn1 issued", "producer: rnn2 issued", "producer: recurrent-1 issued", "producer: fc begin",
             "producer: fc1 issued", "producer: fc2 issued", "producer: recurrent-2 issued", "", "",
             "mma: rnn1 issued", "mma: rnn2 issued", "mma: recurrent-1 issued", "mma: fc1 issued", "mma: fc2 issued", "mma: recurrent-2 issued",
-            "", "", "", "",
+            "epilogue: rnn1 gates done (warp 2)", "epilogue: rnn2 gates done (warp 2)", "epilogue: fc1 done (warp 2)", "epilogue: fc2 done (warp 2)",
             "epilogue: rnn1 accumulators ready", "epilogue: rnn1 published", "epilogue: rnn2 accumulators ready", "epilogue: rnn2 published",
             "epilogue: fc1 accumulator ready", "epilogue: fc1 published", "epilogue: fc2 accumulator ready", "epilogue: fc2 published",
             "fc3 phase: fc2 of all CTAs seen", "fc3 phase: folds done", "fc3 phase: published", ""};
