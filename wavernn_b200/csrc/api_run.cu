@@ -304,7 +304,7 @@ int check_abort(wrnn_handle *h, cudaStream_t st) {
     }
     if (flag) {
         cudaMemsetAsync((char *)h->ws_sync.p + 64, 0, 4, st);      // reported once, then re-armed
-        return fail(h, WRNN_ERR_CUDA, "per-sample loop kernel aborted: exchange watchdog fired (code %d)", flag);
+        return fail(h, WRNN_ERR_CUDA, "per-sample loop kernel aborted: exchange watchdog fired (code 0x%x)", flag);
     }
     return 0;
 }

@@ -1,29 +1,34 @@
 // Per-sample loop, tensor-core kernel for large fold batches (config 5: hundreds of folds per GPU).
 //
 // `generate`'s hot loop (models/fatchord_version.py:201-241) for B folds at once is, per step, a chain of skinny
-// GEMMs  out[rows x B] = W[rows x K] . act[K x B]:  rnn1 (:210), rnn2 (:213-214), fc1 (:217-218), fc2 (:220-221),
-// fc3 (:223).  The FMA kernels (loop_res.cu ...) spend the same time per fold whatever B is; here the four big
-// layers run on the 5th-generation tensor cores:
+// GEMMs  out[B x rows] = act[B x K] . W[rows x K]^T:  rnn1 (:210), rnn2 (:213-214), fc1 (:217-218), fc2 (:220-221),
+// fc3 (:223).  The FMA kernels (loop_res.cu ...) spend the same time per fold whatever B is; here all five layers run
+// on the 5th-generation tensor cores:
 //
-//   * swap-AB: weights are the M operand (128-row tiles), folds are N (NT = 16..128 per tile), `tcgen05.mma`
-//     cta_group::1 kind::f16 issued by one thread, accumulators in TMEM, read back with `tcgen05.ld` into the fused
-//     GRU-gate / ReLU epilogue;
+//   * folds are the M operand: a fold tile is 128 folds = the 128 TMEM lanes, weight rows are N (96 = [r|z|n] x 32 units
+//     for a GRU job, 64 for fc1 / fc2, 32 for fc3); `tcgen05.mma` cta_group::1 kind::f16 issued by one thread,
+//     accumulators in TMEM, read back with `tcgen05.ld` by the thread that owns the fold: gates, ReLU and the MoL draw
+//     (utils/distribution.py:87-123) are thread-local, no shared-memory staging and no shuffles;
 //   * precision: every operand is a bf16 hi + bf16 lo pair (x = hi + lo to ~2^-17), three MMAs per k-step
 //     (hi.hi + hi.lo + lo.hi) accumulated in fp32: products carry ~1e-5 relative error, far inside the 1e-3 bound
 //     on teacher-forced logits that plain bf16 breaks after a few thousand recurrent steps;
 //   * operands live in global memory (L2-resident) already in the K-major, no-swizzle shared-memory image the MMA
 //     descriptors address, "[k-chunk of 8][row][8 elements]", so a pipeline stage is two plain `cp.async.bulk`
 //     copies (one weight block, one activation block) completing on an mbarrier: no tensor maps, no swizzle;
-//   * one persistent cooperative launch for all S steps; per step four MMA phases (rnn1, rnn2, fc1, fc2) and one
-//     fp32 FFMA phase (fc3 + MoL sampling + next step's conditioning operand), separated by split-phase grid
-//     barriers (epilogue warps arrive, the TMA producer waits); every phase is spread over all SMs as
-//     (row tile, fold tile) jobs;
+//   * fold tiles are independent recurrences (:194-196), so nothing is grid-wide: a tile is served by 16 GRU CTAs
+//     (32 units each) and 8 fc CTAs (64 rows each, one of them also runs fc3 + the sampler), which hand operands to one
+//     another through L2 and five per-tile counters (rnn1, rnn2, fc1, fc2, sample published);
+//   * only what depends on the step before is on the sample-to-sample chain.  The conditioning columns (mel, aux) of
+//     every layer are known for all steps: a pre-pass lays them out as MMA operands for the whole call and their
+//     products are issued one step AHEAD into the accumulators; the recurrent products (W_hh . h) are formed one step
+//     ahead too; the previous sample, the one scalar that is new, enters rnn1 / rnn2 / fc1 as a rank-1 fp32 term in
+//     the epilogues.  On the chain per step: rnn1 gates -> 8 stages of K = 64 (rnn2) -> gates -> 8 (fc1) -> 8 (fc2) -> 8 (fc3)
+//     -> draw;
 //   * algebra: the I layer and both residual adds are folded into composed matrices formed on the host in double
-//     (W_ih1 W_I etc., as in loop_res.cu), so the conditioning features and the previous sample enter every layer as
-//     extra K columns of the same MMA chain.
+//     (W_ih1 W_I etc., as in loop_res.cu).
 //
-// Warp roles in a CTA (320 threads): warp 0 = TMA producer, warp 1 = MMA issuer (owns TMEM), warps 2..9 = epilogue
-// (TMEM -> registers -> shared staging -> gates -> global operands) and the FFMA phase.
+// Warp roles in a CTA (320 threads): warp 0 = TMA producer (8 lanes), warp 1 = MMA issuer (owns TMEM), warps 2..9 =
+// epilogues (TMEM -> registers -> global operands).
 #include <cuda_bf16.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -42,66 +47,100 @@ namespace mma {
 
 constexpr int H = 512, FCD = 512, AUX = 32, FEAT = 80;
 constexpr int UT = 32;                     // GRU units per row tile: weight rows [r(32) | z(32) | n(32)] = N = 96 of an MMA
-constexpr int GRU_ROWS = 3 * UT, FC_ROWS = 128;
+constexpr int GRU_ROWS = 3 * UT, FC_ROWS = 64;
 constexpr int FT = 128;                    // folds per tile = M of the MMA = TMEM lanes: lane i of the accumulators is fold i
-constexpr int MT_GRU = H / UT, MT_FC = FCD / FC_ROWS;     // 16, 4 row tiles
-constexpr int KC = 4;                      // k-chunks (of 8 elements) per pipeline stage: K = 32 = two MMA k-steps
-constexpr int MAXSTAGE = 8;                // ring depth is chosen at launch: as many stages as shared memory holds, up to 8
-constexpr int W_GRU = 2 * KC * GRU_ROWS * 16, W_FC = 2 * KC * FC_ROWS * 16;     // weight block of a stage, hi + lo: 12288 / 16384 B
-constexpr int ACT_STAGE = 2 * KC * FT * 16;                                      // activation block of a stage, hi + lo: 16384 B
-constexpr int CGROUPS = 7;                 // conditioning operand: 28 chunks = 224 elements per fold
-constexpr int HGROUPS = H / 32;            // 16 stage groups in a 512-wide operand
+constexpr int MT_GRU = H / UT, MT_FC = FCD / FC_ROWS;     // 16, 8 row tiles
+constexpr int MAXTILES = 16;               // fold tiles per launch (counter table; a B200 holds 9)
+constexpr int KC = 8;                      // k-chunks (of 8 elements) per pipeline stage: K = 64 = four MMA k-steps.  The TMA engine
+                                           // spends ~360 clocks on a bulk copy of 4..16 KB whatever its size: few, large copies
+constexpr int MAXSTAGE = 10;               // ring depth is chosen at launch: as many stages as shared memory holds
+constexpr int W_GRU = 2 * KC * GRU_ROWS * 16, W_FC = 2 * KC * FC_ROWS * 16;     // weight block of a stage, hi + lo: 24576 / 16384 B
+constexpr int ACT_STAGE = 2 * KC * FT * 16;                                      // activation block of a stage, hi + lo: 32768 B
+constexpr int CGROUPS = 4;                 // conditioning operand: 32 chunks = 256 elements per fold (209 used)
+constexpr int HGROUPS = H / (8 * KC);      // 8 stage groups in a 512-wide operand
 constexpr int THREADS = 320, EPI_THREADS = 256, EPI_WARPS = 8;
-constexpr int SBIAS = 2 * 2 * GRU_ROWS + 2 * FC_ROWS;     // this CTA's biases in shared memory: rnn1 / rnn2 (input, recurrent), fc1 / fc2
-constexpr int NCP = 32;                    // fc3 rows padded (MoL: 30)
+constexpr int NCP = 32;                    // fc3 rows padded (MoL: 30) = N of the fc3 job
+// this CTA's bias rows and previous-sample columns in shared memory
+constexpr int SB_G = 0;                                  // rnn1 [input 96 | recurrent 96], rnn2 [input 96 | recurrent 96]
+constexpr int SB_F = 4 * GRU_ROWS;                       // fc1 [64], fc2 [64]
+constexpr int SB_XG = SB_F + 2 * FC_ROWS;                // previous-sample column of rnn1 [96], rnn2 [96]
+constexpr int SB_XF = SB_XG + 2 * GRU_ROWS;              // ... of fc1 [64]
+constexpr int SB_B3 = SB_XF + FC_ROWS;                   // fc3 bias [32]
+constexpr int SBIAS = SB_B3 + NCP;
 constexpr int TMEM_COLS = 512;
-constexpr int FIXED_SMEM = (SBIAS + NCP * FCD + EPI_WARPS * 256) * 4;            // biases + fc3 rows + per-warp scratch
+constexpr int FIXED_SMEM = SBIAS * 4;
 // conditioning operand element order (which features each layer concatenates):
-//   [a4 (32) | a2 (32) | x_prev (1) | m (80) | a1 (32) | a3 (32) | zero (15)]
-// so that rnn1 reads chunks 8..23, rnn2 chunks 4..23, fc1 chunks 8..27, fc2 chunks 0..3.
+//   [a4 (32) | a2 (32) | x_prev slot, zero (1) | m (80) | a1 (32) | a3 (32) | zero (47)]
+// in groups of 64: rnn1 reads groups 1..2, rnn2 0..2, fc1 1..3, fc2 group 0 (weights of the features a layer does not
+// read are zero).
 constexpr int C_A4 = 0, C_A2 = 32, C_X = 64, C_M = 65, C_A1 = 145, C_A3 = 177, C_END = 209;
 
-// Job types.  A job = one (row tile, fold tile) MMA chain into one TMEM accumulator.  Per step a GRU CTA runs
-//   J_R1 (rnn1, conditioning columns only)  -> gates -> J_R2 (rnn2: W_ih2a . h1' + conditioning columns) -> gates,
-// then, OFF the sample-to-sample chain while the fc CTAs work, the two recurrent products of the NEXT step,
-//   J_S1 (W_hh1 . h1') and J_S2 (W_hh2 . h2'), whose accumulators stay in TMEM until the next step's gates read them;
-// an fc CTA runs J_F1 (fc1) -> ReLU -> J_F2 (fc2) -> ReLU.  (loop_res.cu's "shadow products", on tensor cores.)
-enum { J_R1 = 0, J_R2, J_S1, J_S2, J_F1, J_F2, NJOB };
-enum { ARR_C = 0, ARR_H1NEW, ARR_H2NEW, ARR_S12, ARR_Y1 };
+// Job types.  A job = one MMA chain of (row tile, fold tile) into one TMEM accumulator.
+//   ..A ("ahead"): the conditioning columns of a layer for step t + 1, issued during step t (start the accumulator);
+//   ..C ("chain"): the columns that depend on the step's own activations (accumulate on top);
+//   S1 / S2: recurrent products W_hh . h' of the NEXT step (loop_res.cu's "shadow products", on tensor cores).
+enum { J_R1A = 0, J_R2A, J_R2C, J_S1, J_S2, J_F1A, J_F1C, J_F2A, J_F2C, J_F3, NJOB };
+enum { ARR_C = 0, ARR_H1NEW, ARR_H2NEW, ARR_S12, ARR_Y1, ARR_Y2 };
+enum { PH_RNN1 = 0, PH_RNN2, PH_FC1, PH_FC2, PH_SAMPLE, NPHASE };     // per-tile counters: who has published what
+enum { TF_R1 = 0, TF_R2, TF_F1, TF_F2, TF_F3, NTF };                   // accumulator-ready barriers, one per epilogue
 // TMEM accumulator (first column) of each job: 128 lanes = folds, columns = weight rows.  rnn1's gates read X1 + H1,
-// rnn2's X2 + H2 (96 columns each: [r | z | n] x 32 units), the fc jobs share the last 128 columns.
-__host__ __device__ inline int job_acc(int jt) { return jt == J_R1 ? 0 : jt == J_S1 ? 96 : jt == J_R2 ? 192 : jt == J_S2 ? 288 : 384; }
-__host__ __device__ inline int job_stages(int jt) { return jt == J_R1 ? 4 : jt == J_R2 ? 21 : jt == J_F1 ? 21 : jt == J_F2 ? 17 : 16; }
-__host__ __device__ inline int job_rows(int jt) { return jt >= J_F1 ? FC_ROWS : GRU_ROWS; }
-// grid counter a job's loads wait for (value G * (t + 1)), -1 = ordered behind the previous job of the same CTA
-__host__ __device__ inline int job_gate(int jt) { return jt == J_R1 ? 4 : jt == J_R2 ? 0 : jt == J_S1 ? -1 : jt == J_F2 ? 2 : 1; }
+// rnn2's X2 + H2 (96 columns each: [r | z | n] x 32 units); fc1, fc2 64 columns each; fc3 reuses fc1's first 32.
+__host__ __device__ inline int job_acc(int jt) {
+    switch (jt) {
+        case J_R1A: return 0;
+        case J_S1: return 96;
+        case J_R2A: case J_R2C: return 192;
+        case J_S2: return 288;
+        case J_F2A: case J_F2C: return 448;
+        default: return 384;                // fc1, fc3
+    }
+}
+__host__ __device__ inline int job_stages(int jt) {
+    switch (jt) {
+        case J_R1A: return 2;
+        case J_R2A: case J_F1A: return 3;
+        case J_F2A: return 1;
+        default: return HGROUPS;
+    }
+}
+__host__ __device__ inline int job_rows(int jt) { return jt == J_F3 ? NCP : jt >= J_F1A ? FC_ROWS : GRU_ROWS; }
+__host__ __device__ inline int job_tiles(int jt) { return jt == J_F3 ? 1 : jt >= J_F1A ? MT_FC : MT_GRU; }
+__host__ __device__ inline bool job_starts_acc(int jt) { return jt != J_R2C && jt != J_F1C && jt != J_F2C; }
+__host__ __device__ inline int job_commit(int jt) {      // which accumulator-ready barrier a finished job arrives on, or -1
+    return jt == J_R1A ? TF_R1 : jt == J_R2C ? TF_R2 : jt == J_F1C ? TF_F1 : jt == J_F2C ? TF_F2 : jt == J_F3 ? TF_F3 : -1;
+}
 struct StageInfo { int arr, g; };
 __host__ __device__ inline StageInfo stage_info(int jt, int s) {
     switch (jt) {
-        case J_R1: return StageInfo{ARR_C, 2 + s};
-        case J_R2: return s < 16 ? StageInfo{ARR_H1NEW, s} : StageInfo{ARR_C, 1 + (s - 16)};
-        case J_S1: return StageInfo{ARR_H1NEW, s};
+        case J_R1A: return StageInfo{ARR_C, 1 + s};
+        case J_R2A: return StageInfo{ARR_C, s};
+        case J_R2C: case J_S1: return StageInfo{ARR_H1NEW, s};
         case J_S2: return StageInfo{ARR_H2NEW, s};
-        case J_F1: return s < 16 ? StageInfo{ARR_S12, s} : StageInfo{ARR_C, 2 + (s - 16)};
-        default: return s < 16 ? StageInfo{ARR_Y1, s} : StageInfo{ARR_C, 0};
+        case J_F1A: return StageInfo{ARR_C, 1 + s};
+        case J_F1C: return StageInfo{ARR_S12, s};
+        case J_F2A: return StageInfo{ARR_C, 0};
+        case J_F2C: return StageInfo{ARR_Y1, s};
+        default: return StageInfo{ARR_Y2, s};
     }
 }
 
 struct Params {
     LoopArgs a;
-    int NT, NTILES, G, NC;
-    int dbg_state;                 // WRNN_MMA_STEPS set: also store the fp32 recurrent state (wrnn_debug_mma_state)
+    int NTILES, G, NC;
+    int dbg_state;                 // WRNN_MMA_STEPS set: also store the fp32 state / fc2 output (wrnn_debug_mma_state)
     int64_t steps_run;             // == a.S except under WRNN_MMA_STEPS (bring-up: stop after n steps and inspect the state)
-    int ring_bytes;                // shared memory of the stage ring (the staging / fc3 / scratch region follows it)
+    int ring_bytes;                // shared memory of the stage ring (the bias rows follow it)
     const uint8_t *Aimg;           // packed weights: job type j at offA[j], [row tile][stage][hi|lo][KC][rows][8] bf16
     int64_t offA[NJOB];
-    const float *bias;             // P1: [16][2][96] | P2: [16][2][96] | P3: [512] | P4: [512]
-    const float *Wf3, *bf3;        // [NCP][512], [NCP] fp32
-    uint8_t *H1[2], *H2[2], *S12, *Y1, *C;      // B operands, [fold tile][group][hi|lo][KC][NT][8] bf16
-    float *h1f, *h2f, *y2f;        // [NTILES*NT][512] fp32 state / fc2 output
+    const float *bias;             // rnn1 [16][2][96] | rnn2 [16][2][96] | fc1 [512] | fc2 [512] | x columns rnn1 [16][96] | rnn2 [16][96] | fc1 [512] | fc3 bias [32]
+    uint8_t *H1[2], *H2[2], *S12, *Y1, *Y2;     // activation operands, [fold tile][group][hi|lo][KC][128][8] bf16
+    const uint8_t *Cop;            // conditioning operand of every step: [S][fold tile][7 groups][hi|lo][KC][128][8] bf16
+    float *xp;                     // previous sample, [2][NTILES * 128] (double-buffered by step parity)
+    float *h1f, *h2f, *y2f;        // debug only: [NTILES * 128][512] fp32 state / fc2 output
     GridSync gs;
     long long *prof;               // debug (WRNN_MMA_PROF=step): clock64 timeline of that step from CTA 0 and CTA G-1, else null
     int64_t prof_step;
+    int exp;                       // debug (WRNN_MMA_EXP): timing experiments that break the results; 0 in production
 };
 
 #define PROF_MARK(slot)                                                                              \
@@ -182,10 +221,11 @@ __device__ __forceinline__ uint32_t make_idesc(int M, int N) {
 struct Watch {                  // a lost arrival becomes an error flag, not a hung GPU box
     int *abort_flag;
     bool dead;
+    int site;                   // which wait this thread is in (reported in the abort code): role * 16 + detail
 };
 __device__ __forceinline__ bool give_up(Watch &w, long long t0, unsigned &spins) {
     if ((++spins & 1023u) == 0u) {
-        if (clock64() - t0 > WATCHDOG_CLOCKS) { atomicExch(w.abort_flag, 3); w.dead = true; }
+        if (clock64() - t0 > WATCHDOG_CLOCKS) { atomicCAS(w.abort_flag, 0, 0x10000 | (w.site << 8) | (int)(blockIdx.x & 0xff)); w.dead = true; }
         else if (ld_volatile_s32(w.abort_flag)) w.dead = true;
     }
     return w.dead;
@@ -197,17 +237,19 @@ __device__ __forceinline__ void mbar_wait(void *b, uint32_t parity, Watch &w) {
     while (!mbar_try_wait(b, parity))
         if (give_up(w, t0, spins)) return;
 }
-// Split-phase grid barrier, ONE MONOTONIC COUNTER PER PHASE of the step (five, each on its own 128-byte line): a CTA
-// that has no job in a phase publishes it at once and runs ahead to the next thing it has to wait for, so a single
-// counter summed over phases would reach "G arrivals" before every CTA has finished the phase in question.  Per phase,
-// counter[p] >= G * (t + 1) does mean that every CTA has published phase p of step t: no CTA can publish phase p of
-// step t + 1 before it has passed the fc3 phase of step t, which waits for everybody's fc2 phase of step t.
-__device__ __forceinline__ unsigned long long *phase_counter(const GridSync &gs, int p) { return gs.counter + 16 * (p + 1); }
-__device__ __forceinline__ void grid_wait(const GridSync &gs, int p, unsigned long long want, Watch &w) {
-    if (w.dead) return;
+// Hand-over between the CTAs of one fold tile: ONE MONOTONIC COUNTER PER (phase, fold tile), each on its own 128-byte
+// line.  The CTAs that produce a phase's operands (16 GRU CTAs, 8 fc CTAs, 1 sampler) add one each per step once their
+// stores are ordered; a consumer waits for arrivals * (t + 1).  Fold tiles never wait for one another.
+__device__ __forceinline__ unsigned long long *tile_counter(const GridSync &gs, int phase, int nt) {
+    return gs.counter + 16 * (1 + phase * MAXTILES + nt);
+}
+__device__ __forceinline__ int phase_arrivals(int phase) { return phase <= PH_RNN2 ? MT_GRU : phase <= PH_FC2 ? MT_FC : 1; }
+__device__ __forceinline__ void tile_wait(const GridSync &gs, int phase, int nt, int64_t steps_done, Watch &w) {
+    if (w.dead || steps_done <= 0) return;
+    const unsigned long long want = (unsigned long long)phase_arrivals(phase) * (unsigned long long)steps_done;
     const long long t0 = clock64();
     unsigned spins = 0;
-    const unsigned long long *c = phase_counter(gs, p);
+    const unsigned long long *c = tile_counter(gs, phase, nt);
     while (ld_acquire_u64(c) < want)
         if (give_up(w, t0, spins)) return;
 }
@@ -237,77 +279,87 @@ __device__ __forceinline__ void split8(const float (&v)[8], uint4 &hi, uint4 &lo
 }
 // byte offset of the 16-byte slot (fold fi of tile nt, feature chunk `chunk`) in a B operand with NG stage groups
 __device__ __forceinline__ size_t b_slot(int NT, int NG, int nt, int chunk, int fi, int hl) {
-    return ((size_t)(nt * NG + (chunk >> 2)) * 2 + hl) * (size_t)(KC * NT * 16) + (size_t)((chunk & 3) * NT + fi) * 16;
+    return ((size_t)(nt * NG + chunk / KC) * 2 + hl) * (size_t)(KC * NT * 16) + (size_t)((chunk % KC) * NT + fi) * 16;
 }
 
-// MoL draw for one fold by one warp from 3*nmix logits in shared memory: same arithmetic as mol_sample_warp
-__device__ __forceinline__ float mol_sample_smem(const float *lg, int nmix, float myu1, float u2, int lane, int *pick) {
-    float t = -INFINITY;
-    if (lane < nmix) t = lg[lane] - logf(-logf(myu1));
-    int idx = lane;
+// ---------------------------------------------------------------------------- MoL draw, one thread per fold
+// Same arithmetic as mol_sample_warp (loop_common.cuh; utils/distribution.py:87-123): Gumbel-max over the mixture
+// logits (first index wins a tie), then mean + exp(max(log_scale, -32.236...)) * (log u - log(1 - u)), clamped to [-1, 1].
+constexpr int NMIX = 10;        // MOL: n_classes = 30 = 3 x 10 (fatchord_version.py:103-104)
+__device__ __forceinline__ float mol_sample_thread(const float (&lg)[NCP], const float (&u1)[NMIX], float u2, int *pick) {
+    float best = -INFINITY, mean = 0.f, ls = 0.f;
+    int idx = 0;
 #pragma unroll
-    for (int o = 16; o >= 1; o >>= 1) {
-        const float ot = __shfl_xor_sync(0xffffffffu, t, o);
-        const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
-        if (ot > t || (ot == t && oi < idx)) { t = ot; idx = oi; }
+    for (int i = 0; i < NMIX; i++) {
+        const float tv = lg[i] - logf(-logf(u1[i]));
+        if (tv > best) { best = tv; idx = i; mean = lg[NMIX + i]; ls = lg[2 * NMIX + i]; }
     }
-    const float mean = lg[nmix + idx];
-    const float ls = fmaxf(lg[2 * nmix + idx], -32.23619130191664f);
+    ls = fmaxf(ls, -32.23619130191664f);
     float x = mean + expf(ls) * (logf(u2) - logf(1.f - u2));
     x = fminf(fmaxf(x, -1.f), 1.f);
     *pick = idx;
     return x;
 }
 
-// conditioning operand of step `t` for fold b (one warp), in two halves so that the 832-byte row (HBM, cold) can be
-// fetched before the warp has to wait for anything: load_cond_row -> scr[0..207], build_cond_operand reorders, splits
-// into bf16 hi/lo and stores the 28 chunks.
-__device__ __forceinline__ void load_cond_row(const Params &P, int64_t b, int64_t t, float *scr, int lane) {
-    const int64_t S = P.a.S;
+// ---------------------------------------------------------------------------- conditioning operand, all steps (pre-pass)
+// [B][S][80 mel + 4 x 32 aux] fp32 rows (fold_cond_kernel's output) -> the MMA operand image of every step: element
+// order of C_*, bf16 hi / lo.  One warp per (step, fold); folds of the padded last tile are written as zeros.
+__global__ void __launch_bounds__(256) cond_operand_kernel(const float *__restrict__ cond, int64_t B, int64_t S, int ntiles,
+                                                           uint8_t *__restrict__ Cop) {
+    __shared__ float scr_all[8][FEAT + 4 * AUX];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t NF = (int64_t)ntiles * FT, idx = (int64_t)blockIdx.x * 8 + warp;
+    if (idx >= S * NF) return;
+    const int64_t t = idx / NF, b = idx - t * NF;
     const int RW = FEAT + 4 * AUX;
-    const float *row = P.a.cond + ((size_t)b * S + (t < S ? t : 0)) * RW;
+    float *scr = scr_all[warp];
+    if (b < B) {
+        const float *row = cond + ((size_t)b * S + t) * RW;
 #pragma unroll
-    for (int i = 0; i < 7; i++) {
-        const int e = lane + 32 * i;
-        if (e < RW) scr[e] = t < S ? __ldg(row + e) : 0.f;
+        for (int i = 0; i < 7; i++) {
+            const int e = lane + 32 * i;
+            if (e < RW) scr[e] = __ldg(row + e);
+        }
     }
-}
-__device__ __forceinline__ void build_cond_operand(const Params &P, int64_t b, float xprev, const float *scr, int lane) {
     __syncwarp();
-    if (lane < 4 * CGROUPS) {
+    if (lane < KC * CGROUPS) {
         float v[8];
 #pragma unroll
         for (int i = 0; i < 8; i++) {
             const int e = lane * 8 + i;
-            float x;
-            if (e < C_A2) x = scr[FEAT + 3 * AUX + (e - C_A4)];
-            else if (e < C_X) x = scr[FEAT + AUX + (e - C_A2)];
-            else if (e == C_X) x = xprev;
-            else if (e < C_A1) x = scr[e - C_M];
-            else if (e < C_A3) x = scr[FEAT + (e - C_A1)];
-            else if (e < C_END) x = scr[FEAT + 2 * AUX + (e - C_A3)];
-            else x = 0.f;
+            float x = 0.f;
+            if (b < B) {
+                if (e < C_A2) x = scr[FEAT + 3 * AUX + (e - C_A4)];
+                else if (e < C_X) x = scr[FEAT + AUX + (e - C_A2)];
+                else if (e == C_X) x = 0.f;                      // the previous sample enters in the epilogues
+                else if (e < C_A1) x = scr[e - C_M];
+                else if (e < C_A3) x = scr[FEAT + (e - C_A1)];
+                else if (e < C_END) x = scr[FEAT + 2 * AUX + (e - C_A3)];
+            }
             v[i] = x;
         }
-        const float v0[4] = {v[0], v[1], v[2], v[3]}, v1[4] = {v[4], v[5], v[6], v[7]};
-        uint2 h0, l0, h1, l1;
-        split4(v0, h0, l0);
-        split4(v1, h1, l1);
-        const int nt = (int)(b / P.NT), fi = (int)(b % P.NT);
-        *reinterpret_cast<uint4 *>(P.C + b_slot(P.NT, CGROUPS, nt, lane, fi, 0)) = make_uint4(h0.x, h0.y, h1.x, h1.y);
-        *reinterpret_cast<uint4 *>(P.C + b_slot(P.NT, CGROUPS, nt, lane, fi, 1)) = make_uint4(l0.x, l0.y, l1.x, l1.y);
+        uint4 hi, lo;
+        split8(v, hi, lo);
+        const int nt = (int)(b / FT), fi = (int)(b % FT);
+        uint8_t *base = Cop + ((size_t)t * ntiles) * CGROUPS * ACT_STAGE;
+        *reinterpret_cast<uint4 *>(base + b_slot(FT, CGROUPS, nt, lane, fi, 0)) = hi;
+        *reinterpret_cast<uint4 *>(base + b_slot(FT, CGROUPS, nt, lane, fi, 1)) = lo;
     }
-    __syncwarp();
 }
 
-// operand array a job reads at step t (t = -1: the prologue's recurrent products on the zero state)
-__device__ __forceinline__ const uint8_t *b_array(const Params &P, int arr, int64_t t) {
-    switch (arr) {
-        case ARR_C: return P.C;
-        case ARR_H1NEW: return P.H1[(t + 1) & 1];
-        case ARR_H2NEW: return P.H2[(t + 1) & 1];
-        case ARR_S12: return P.S12;
-        default: return P.Y1;
+// ---------------------------------------------------------------------------- pipeline: ring, producer, issuer
+// stage block a job reads at step t.  Activation arrays alternate with the step; the conditioning operand is indexed by it.
+__device__ __forceinline__ const uint8_t *stage_src(const Params &P, StageInfo si, int nt, int64_t t) {
+    switch (si.arr) {
+        case ARR_C: {
+            const int64_t tt = t < P.a.S ? t : P.a.S - 1;
+            return P.Cop + (((size_t)tt * P.NTILES + nt) * CGROUPS + si.g) * ACT_STAGE;
+        }
+        case ARR_H1NEW: return P.H1[(t + 1) & 1] + (size_t)(nt * HGROUPS + si.g) * ACT_STAGE;
+        case ARR_H2NEW: return P.H2[(t + 1) & 1] + (size_t)(nt * HGROUPS + si.g) * ACT_STAGE;
+        case ARR_S12: return P.S12 + (size_t)(nt * HGROUPS + si.g) * ACT_STAGE;
+        case ARR_Y1: return P.Y1 + (size_t)(nt * HGROUPS + si.g) * ACT_STAGE;
+        default: return P.Y2 + (size_t)(nt * HGROUPS + si.g) * ACT_STAGE;
     }
 }
 
@@ -318,11 +370,11 @@ struct Ring {                   // the stage ring of this CTA and a position in 
         if (++slot == nstage) { slot = 0; par ^= 1u; }
     }
 };
-// A CTA that only ever runs GRU jobs (96-row weight blocks) packs its stages tighter than one that also has an fc job;
-// the ring is as deep as its share of shared memory allows (5 stages of 28 KB for a GRU CTA).
-__device__ __forceinline__ Ring make_ring(const Params &P, bool has_fc) {
+// A CTA that only runs fc jobs (8 KB weight blocks) packs its stages tighter than one with a GRU job (12 KB); the ring
+// is as deep as shared memory allows (3 stages of 56 KB, or 4 of 48 KB).
+__device__ __forceinline__ Ring make_ring(const Params &P, bool has_gru) {
     Ring r;
-    r.w_slot = has_fc ? W_FC : W_GRU;
+    r.w_slot = has_gru ? W_GRU : W_FC;
     r.stage_bytes = r.w_slot + ACT_STAGE;
     r.nstage = min((uint32_t)MAXSTAGE, (uint32_t)P.ring_bytes / r.stage_bytes);
     r.slot = 0;
@@ -330,74 +382,124 @@ __device__ __forceinline__ Ring make_ring(const Params &P, bool has_fc) {
     return r;
 }
 
-// One job of the TMA producer lanes: (wait for the grid counter,) stream the stages of (job type, row tile, fold tile).
-// A thread completes only about one bulk copy per 700 clocks whatever its size (scripts/mb_umma.cu: 16 B/clk/SM from one
-// issuing thread, 52 from four lanes, ~67 = the L2 limit from eight), so the copies are spread over NPROD = 8 lanes of
-// the producer warp: stage k of the running count belongs to lane pair (k & 3), the even lane arms the barrier with the
-// byte count of both copies and brings the weight block, the odd lane brings the activation block.  Every lane keeps
-// the same ring position; a copy may complete its bytes on the barrier before the other lane has armed it (the phase
-// cannot end before the arrive).
+// One job of the TMA producer lanes: (wait for a tile counter,) stream the stages of (job type, row tile, fold tile).
+// A bulk-copy INSTRUCTION occupies its warp for ~320 clocks whatever its size and however many lanes are active, and a
+// thread completes about one copy per 700 clocks (scripts/mb_umma.cu; measured here: lanes taking turns with one copy
+// per instruction moved a stage per 640 clocks whatever its size; eight lanes issuing four stages at once reach the
+// L2 -> SM limit of ~64 B/clk but deliver the first stage late).  So a stage is ONE instruction of a lane pair, the even
+// lane bringing the weight block, the odd lane the activation block, and the four pairs of the NPROD = 8 lanes take the
+// stages in turn (min(4, ring depth) of them): in order, a stage per ~320 clocks of issue, ~900 of transfer.  The even lane arms the barrier with the
+// byte count of the stage; a copy may complete its bytes before the arrive (the phase cannot end before it).
+// The weight blocks do not depend on anybody: for a gated job up to a ring-full of stages is armed and gets its weight
+// block BEFORE the wait on the tile counter, so that only activation bytes (half a block per lane) move afterwards.
+// `t`: the step whose operands the job reads (conditioning row t; activation buffers written during step t).
+// `gate`: phase whose counter must show `gate_steps` published steps of fold tile nt before the loads start, or -1.
 constexpr int NPROD = 8;
-__device__ __forceinline__ void produce_job(const Params &P, int jt, int mt, int nt, int64_t t, Ring &r, uint32_t &count, int lane,
-                                            uint8_t *stages, uint64_t *bar_full, uint64_t *bar_empty, Watch &w, long long *pacc = nullptr) {
-    const int nst = job_stages(jt), gate = job_gate(jt);
-    const uint32_t abytes = 2u * KC * (uint32_t)job_rows(jt) * 16u, bbytes = ACT_STAGE;       // weight block, activation block
-    if (gate >= 0) {            // this job's operands were written by that phase of every CTA
-        grid_wait(P.gs, gate, (unsigned long long)P.G * (unsigned long long)(t + 1), w);
-        fence_proxy_async_global();
+struct Pipe {
+    Ring r;
+    uint32_t count;
+    uint8_t *stages;
+    uint64_t *bar_full, *bar_empty;
+};
+__device__ __forceinline__ void produce_job(const Params &P, int jt, int mt, int nt, int64_t t, int gate, int64_t gate_steps, Pipe &pp,
+                                            int lane, Watch &w, long long *pacc = nullptr, long long *pgate = nullptr) {
+    const int nst = ((P.exp & 1) && (jt == J_S1 || jt == J_S2)) ? 1 : job_stages(jt);
+    const uint32_t wbytes = 2u * KC * (uint32_t)job_rows(jt) * 16u;
+    const uint8_t *Wbase = P.Aimg + P.offA[jt] + (size_t)mt * nst * wbytes;
+    Ring &r = pp.r;
+    const bool wlane = (lane & 1) == 0;
+    long long waited = 0;           // debug timeline only
+    // The lane pairs run independently, each waiting on the "slot empty" barriers of its own stages by phase parity: a pair
+    // must never be a whole ring ahead of the pair that owns the stage before it in the same slot, or its parity test
+    // would be answered by the phase before.  Its own previous stage bounds its lead to (pairs) stages: pairs <= ring depth.
+    const uint32_t npair = min(4u, r.nstage);
+    const int early = (gate >= 0 && !(P.exp & 2)) ? min(nst, (int)r.nstage) : 0;
+    {
+        Ring re = r;
+        uint32_t cnt = pp.count;
+        for (int s = 0; s < early; s++, cnt++) {
+            if (cnt % npair == (uint32_t)(lane >> 1)) {
+                w.site = 0x10 + jt;
+                mbar_wait(&pp.bar_empty[re.slot], re.par ^ 1u, w);
+                if (wlane) {
+                    mbar_expect_tx(&pp.bar_full[re.slot], wbytes + ACT_STAGE);
+                    bulk_g2s(pp.stages + (size_t)re.slot * re.stage_bytes, Wbase + (size_t)s * wbytes, wbytes, &pp.bar_full[re.slot]);
+                }
+            }
+            re.advance();
+        }
     }
-    const uint8_t *Abase = P.Aimg + P.offA[jt] + (size_t)mt * nst * abytes;
-    for (int s = 0; s < nst; s++, count++) {
-        if ((count & 3u) == (uint32_t)(lane >> 1)) {
-            const long long c0 = pacc ? clock64() : 0;
-            mbar_wait(&bar_empty[r.slot], r.par ^ 1u, w);
-            if (pacc && lane == 0) *pacc += clock64() - c0;
-            uint8_t *dst = stages + (size_t)r.slot * r.stage_bytes;
-            if ((lane & 1) == 0) {
-                mbar_expect_tx(&bar_full[r.slot], abytes + bbytes);
-                bulk_g2s(dst, Abase + (size_t)s * abytes, abytes, &bar_full[r.slot]);
-            } else {
-                const StageInfo si = stage_info(jt, s);
-                const int NG = si.arr == ARR_C ? CGROUPS : HGROUPS;
-                bulk_g2s(dst + r.w_slot, b_array(P, si.arr, t) + (size_t)(nt * NG + si.g) * bbytes, bbytes, &bar_full[r.slot]);
+    if (gate >= 0) {            // the operands were written with generic stores by other SMs: acquire, then cross to the async proxy
+        w.site = 0x20 + jt;
+        tile_wait(P.gs, gate, nt, gate_steps, w);
+        fence_proxy_async_global();
+        if (pgate && lane == 0) *pgate = clock64();
+    }
+    for (int s = 0; s < nst; s++, pp.count++) {
+        if (pp.count % npair == (uint32_t)(lane >> 1)) {
+            uint8_t *dst = pp.stages + (size_t)r.slot * r.stage_bytes;
+            const uint8_t *act = stage_src(P, stage_info(jt, s), nt, t);
+            if (s >= early) {       // the whole stage: one instruction, two copies
+                const long long c0 = pacc ? clock64() : 0;
+                w.site = 0x30 + jt;
+                mbar_wait(&pp.bar_empty[r.slot], r.par ^ 1u, w);
+                if (pacc) waited += clock64() - c0;
+                if (wlane) mbar_expect_tx(&pp.bar_full[r.slot], wbytes + ACT_STAGE);
+                bulk_g2s(wlane ? dst : dst + r.w_slot, wlane ? Wbase + (size_t)s * wbytes : act, wlane ? wbytes : (uint32_t)ACT_STAGE,
+                         &pp.bar_full[r.slot]);
+            } else {                // armed, weights under way: the activation block, half per lane
+                const uint32_t half = wlane ? 0u : (uint32_t)ACT_STAGE / 2;
+                bulk_g2s(dst + r.w_slot + half, act + half, ACT_STAGE / 2, &pp.bar_full[r.slot]);
             }
         }
         r.advance();
     }
+    if (pacc && lane == 0) *pacc = waited;
 }
 
 // One job of the MMA issuer thread: three MMAs (hi.hi, hi.lo, lo.hi) per k-step into the job's accumulator.
-__device__ __forceinline__ void issue_job(const Params &P, int jt, Ring &r, uint32_t stage0, uint32_t tb,
-                                          uint64_t *bar_full, uint64_t *bar_empty, uint64_t *bar_tfull, Watch &w, long long *macc = nullptr) {
-    const int nst = job_stages(jt);
+struct Issue {
+    Ring r;
+    uint32_t stage0, tb;
+    uint64_t *bar_full, *bar_empty, *bar_tf;
+    int exp;
+};
+__device__ __forceinline__ void issue_job(int jt, Issue &is, Watch &w, long long *macc = nullptr) {
+    const int nst = ((is.exp & 1) && (jt == J_S1 || jt == J_S2)) ? 1 : job_stages(jt);
     const uint32_t rows = job_rows(jt);
     // A = activations (M = 128 folds), B = weights (N = rows); both K-major, no swizzle, [k-chunk][row][8].  Descriptors
     // differ only in the 14-bit start-address field (16-byte units): constant part once per job.
     const uint64_t dW0 = make_desc(0, rows * 16u, 128), dX0 = make_desc(0, FT * 16u, 128);
     const uint32_t stepW = 2u * rows, stepX = 2u * FT;          // two k-chunks, in 16-byte units
     const uint32_t loW = KC * rows, loX = KC * FT;               // hi -> lo image
-    const uint32_t d = tb + (uint32_t)job_acc(jt);
+    const uint32_t d = is.tb + (uint32_t)job_acc(jt);
     const uint32_t idesc = make_idesc(FT, (int)rows);
+    const bool fresh = job_starts_acc(jt);
+    Ring &r = is.r;
+    long long a0 = 0, a1 = 0, a2 = 0;       // debug timeline only
     for (int s = 0; s < nst; s++) {
         const long long c0 = macc ? clock64() : 0;
-        mbar_wait(&bar_full[r.slot], r.par, w);
+        w.site = 0x40 + jt;
+        mbar_wait(&is.bar_full[r.slot], r.par, w);
         tc_fence_after();
         const long long c1 = macc ? clock64() : 0;
-        const uint32_t aW = (stage0 + r.slot * r.stage_bytes) >> 4, aX = aW + (r.w_slot >> 4);
+        const uint32_t aW = (is.stage0 + r.slot * r.stage_bytes) >> 4, aX = aW + (r.w_slot >> 4);
 #pragma unroll
         for (int ks = 0; ks < KC / 2; ks++) {
             const uint64_t wh = dW0 + (aW + ks * stepW), wl = dW0 + (aW + loW + ks * stepW);
             const uint64_t xh = dX0 + (aX + ks * stepX), xl = dX0 + (aX + loX + ks * stepX);
-            umma_bf16(d, xh, wh, idesc, (s == 0 && ks == 0) ? 0u : 1u);
+            umma_bf16(d, xh, wh, idesc, (fresh && s == 0 && ks == 0) ? 0u : 1u);
             umma_bf16(d, xh, wl, idesc, 1u);
             umma_bf16(d, xl, wh, idesc, 1u);
         }
         const long long c2 = macc ? clock64() : 0;
-        umma_commit(&bar_empty[r.slot]);          // the stage is free once these MMAs have read it
-        if (macc) { const long long c3 = clock64(); macc[0] += c1 - c0; macc[1] += c2 - c1; macc[2] += c3 - c2; }
+        umma_commit(&is.bar_empty[r.slot]);          // the stage is free once these MMAs have read it
+        if (macc) { const long long c3 = clock64(); a0 += c1 - c0; a1 += c2 - c1; a2 += c3 - c2; }
         r.advance();
     }
-    if (jt != J_S1 && jt != J_S2) umma_commit(bar_tfull);       // accumulator (and every earlier MMA) complete
+    if (macc) { macc[0] = a0; macc[1] = a1; macc[2] = a2; }
+    const int tf = job_commit(jt);
+    if (tf >= 0) umma_commit(&is.bar_tf[tf]);        // this accumulator (and every MMA issued before) is complete
 }
 
 // ---------------------------------------------------------------------------- epilogues (256 threads, warps 2..9)
@@ -406,18 +508,18 @@ __device__ __forceinline__ void issue_job(const Params &P, int jt, Ring &r, uint
 // staging, no barrier inside an epilogue; the two warps of a quarter split the columns (`half`).  Operand stores are one
 // 16-byte chunk (8 units) per image per thread, consecutive lanes = consecutive folds = consecutive addresses.
 //
-// GRU gates (fatchord_version.py:210-216): X (input side) and H (recurrent side, formed one step ahead) hold columns
-// [r | z | n] x 32 units; the thread keeps the state of its (fold, 16 units) in registers for the whole run (`hst`).
-// rnn2 also emits s12 = h1' + h2' (fc1 reads x + h1 + h2; x is folded into fc1's weights).
+// GRU gates (fatchord_version.py:210-216): X (input side: conditioning columns, issued ahead, + for rnn2 the h1' columns)
+// and H (recurrent side, formed one step ahead) hold columns [r | z | n] x 32 units; the previous sample `xp` adds its
+// column of the composed input matrix in fp32.  The thread keeps the state of its (fold, 16 units) in registers for the
+// whole run (`hst`).  rnn2 also emits s12 = h1' + h2' (fc1 reads x + h1 + h2; x is folded into fc1's weights).
 template <int LAYER>
-__device__ __forceinline__ void epi_gru(const Params &P, int mt, int nt, int64_t t, uint32_t tb, const float *sb, float (&hst)[16],
-                                        float (&h1new)[16], int q, int half, int lane) {
+__device__ __forceinline__ void epi_gru(const Params &P, int mt, int nt, int64_t t, uint32_t tb, const float *sb, float xp,
+                                        float (&hst)[16], float (&h1new)[16], int q, int half, int lane) {
     const int fi = q * 32 + lane, u0 = half * 16, gu = mt * UT + u0;
     const size_t fold = (size_t)nt * FT + fi;
-    const float *bi = sb + LAYER * 2 * GRU_ROWS, *bh = bi + GRU_ROWS;
-    float *hf = LAYER == 0 ? P.h1f : P.h2f;
+    const float *bi = sb + SB_G + LAYER * 2 * GRU_ROWS, *bh = bi + GRU_ROWS, *wx = sb + SB_XG + LAYER * GRU_ROWS;
     uint8_t *Hn = LAYER == 0 ? P.H1[(t + 1) & 1] : P.H2[(t + 1) & 1];
-    const uint32_t base = tb + ((uint32_t)(q * 32) << 16), colX = base + (uint32_t)job_acc(LAYER == 0 ? J_R1 : J_R2) + u0,
+    const uint32_t base = tb + ((uint32_t)(q * 32) << 16), colX = base + (uint32_t)job_acc(LAYER == 0 ? J_R1A : J_R2A) + u0,
                    colH = base + (uint32_t)job_acc(LAYER == 0 ? J_S1 : J_S2) + u0;
 #pragma unroll
     for (int g = 0; g < 2; g++) {
@@ -433,13 +535,13 @@ __device__ __forceinline__ void epi_gru(const Params &P, int mt, int nt, int64_t
 #pragma unroll
         for (int i = 0; i < 8; i++) {
             const int u = u0 + 8 * g + i;
-            hn[i] = gru_update_fast(__uint_as_float(xr[i]) + bi[u], __uint_as_float(xz[i]) + bi[UT + u], __uint_as_float(xn[i]) + bi[2 * UT + u],
-                                    __uint_as_float(hr[i]) + bh[u], __uint_as_float(hz[i]) + bh[UT + u], __uint_as_float(hn_[i]) + bh[2 * UT + u],
-                                    hst[8 * g + i]);
+            hn[i] = gru_update_fast(fmaf(wx[u], xp, __uint_as_float(xr[i]) + bi[u]), fmaf(wx[UT + u], xp, __uint_as_float(xz[i]) + bi[UT + u]),
+                                    fmaf(wx[2 * UT + u], xp, __uint_as_float(xn[i]) + bi[2 * UT + u]), __uint_as_float(hr[i]) + bh[u],
+                                    __uint_as_float(hz[i]) + bh[UT + u], __uint_as_float(hn_[i]) + bh[2 * UT + u], hst[8 * g + i]);
             hst[8 * g + i] = hn[i];
         }
         if (P.dbg_state) {                  // fp32 copy of the state for wrnn_debug_mma_state only
-            float4 *dst = reinterpret_cast<float4 *>(hf + fold * H + gu + 8 * g);
+            float4 *dst = reinterpret_cast<float4 *>((LAYER == 0 ? P.h1f : P.h2f) + fold * H + gu + 8 * g);
             dst[0] = make_float4(hn[0], hn[1], hn[2], hn[3]);
             dst[1] = make_float4(hn[4], hn[5], hn[6], hn[7]);
         }
@@ -462,15 +564,16 @@ __device__ __forceinline__ void epi_gru(const Params &P, int mt, int nt, int64_t
     }
 }
 
-// fc1 / fc2 + ReLU (:217-221): 128 rows = 128 columns, 64 per thread.  fc1 -> bf16 hi/lo operand of fc2, fc2 -> fp32 rows for fc3
+// fc1 / fc2 + ReLU (:217-221): 64 rows = 64 columns, 32 per thread, out as the bf16 hi/lo operand of the next layer
 template <int LAYER>
-__device__ __forceinline__ void epi_fc(const Params &P, int mt, int nt, uint32_t tb, const float *sb, int q, int half, int lane) {
-    const int fi = q * 32 + lane, r0 = half * 64, gr = mt * FC_ROWS + r0;
+__device__ __forceinline__ void epi_fc(const Params &P, int mt, int nt, uint32_t tb, const float *sb, float xp, int q, int half, int lane) {
+    const int fi = q * 32 + lane, r0 = half * 32, gr = mt * FC_ROWS + r0;
     const size_t fold = (size_t)nt * FT + fi;
-    const float *bb = sb + 4 * GRU_ROWS + LAYER * FC_ROWS + r0;
-    const uint32_t col = tb + ((uint32_t)(q * 32) << 16) + (uint32_t)job_acc(J_F1) + r0;
-#pragma unroll 2
-    for (int g = 0; g < 8; g += 2) {
+    const float *bb = sb + SB_F + LAYER * FC_ROWS + r0, *wx = sb + SB_XF + r0;
+    uint8_t *out = LAYER == 0 ? P.Y1 : P.Y2;
+    const uint32_t col = tb + ((uint32_t)(q * 32) << 16) + (uint32_t)job_acc(LAYER == 0 ? J_F1C : J_F2C) + r0;
+#pragma unroll
+    for (int g = 0; g < 4; g += 2) {
         uint32_t a[8], b[8];
         tmem_ld8_nowait(col + 8 * g, a);
         tmem_ld8_nowait(col + 8 * g + 8, b);
@@ -478,18 +581,19 @@ __device__ __forceinline__ void epi_fc(const Params &P, int mt, int nt, uint32_t
         float va[8], vb[8];
 #pragma unroll
         for (int i = 0; i < 8; i++) {
-            va[i] = fmaxf(__uint_as_float(a[i]) + bb[8 * g + i], 0.f);
-            vb[i] = fmaxf(__uint_as_float(b[i]) + bb[8 * g + 8 + i], 0.f);
+            float pa = __uint_as_float(a[i]) + bb[8 * g + i], pb = __uint_as_float(b[i]) + bb[8 * g + 8 + i];
+            if (LAYER == 0) { pa = fmaf(wx[8 * g + i], xp, pa); pb = fmaf(wx[8 * g + 8 + i], xp, pb); }
+            va[i] = fmaxf(pa, 0.f);
+            vb[i] = fmaxf(pb, 0.f);
         }
-        if (LAYER == 0) {
-            uint4 hi, lo;
-            split8(va, hi, lo);
-            *reinterpret_cast<uint4 *>(P.Y1 + b_slot(FT, HGROUPS, nt, (gr >> 3) + g, fi, 0)) = hi;
-            *reinterpret_cast<uint4 *>(P.Y1 + b_slot(FT, HGROUPS, nt, (gr >> 3) + g, fi, 1)) = lo;
-            split8(vb, hi, lo);
-            *reinterpret_cast<uint4 *>(P.Y1 + b_slot(FT, HGROUPS, nt, (gr >> 3) + g + 1, fi, 0)) = hi;
-            *reinterpret_cast<uint4 *>(P.Y1 + b_slot(FT, HGROUPS, nt, (gr >> 3) + g + 1, fi, 1)) = lo;
-        } else {
+        uint4 hi, lo;
+        split8(va, hi, lo);
+        *reinterpret_cast<uint4 *>(out + b_slot(FT, HGROUPS, nt, (gr >> 3) + g, fi, 0)) = hi;
+        *reinterpret_cast<uint4 *>(out + b_slot(FT, HGROUPS, nt, (gr >> 3) + g, fi, 1)) = lo;
+        split8(vb, hi, lo);
+        *reinterpret_cast<uint4 *>(out + b_slot(FT, HGROUPS, nt, (gr >> 3) + g + 1, fi, 0)) = hi;
+        *reinterpret_cast<uint4 *>(out + b_slot(FT, HGROUPS, nt, (gr >> 3) + g + 1, fi, 1)) = lo;
+        if (LAYER == 1 && P.dbg_state) {
             float4 *dst = reinterpret_cast<float4 *>(P.y2f + fold * FCD + gr + 8 * g);
             dst[0] = make_float4(va[0], va[1], va[2], va[3]);
             dst[1] = make_float4(va[4], va[5], va[6], va[7]);
@@ -499,38 +603,100 @@ __device__ __forceinline__ void epi_fc(const Params &P, int mt, int nt, uint32_t
     }
 }
 
+// fc3 (:223) + MoL draw (utils/distribution.py:87-123): the 30 logits of a fold are 30 columns of its own TMEM lane.
+// Called by the four warps with half == 0 (one per lane quarter).  Writes the sample, the mixture pick and the previous
+// sample of step t + 1.
+__device__ __forceinline__ void epi_sample(const Params &P, int nt, int64_t t, uint32_t tb, const float *sb, int q, int lane) {
+    const int fi = q * 32 + lane;
+    const int64_t b = (int64_t)nt * FT + fi, S = P.a.S;
+    uint32_t acc[32];
+    tmem_ld32(tb + ((uint32_t)(q * 32) << 16) + (uint32_t)job_acc(J_F3), acc);
+    float *xnext = P.xp + (size_t)((t + 1) & 1) * P.NTILES * FT + b;
+    if (b >= P.a.B) { *xnext = 0.f; return; }            // padded fold of the last tile
+    float lg[NCP];
+#pragma unroll
+    for (int i = 0; i < NCP; i++) lg[i] = __uint_as_float(acc[i]) + sb[SB_B3 + i];
+    const bool live = t < P.a.fold_len[b];
+    if (P.a.logits_out && live) {
+        float *dst = P.a.logits_out + ((size_t)b * S + t) * P.NC;
+#pragma unroll
+        for (int i = 0; i < 3 * NMIX; i++) dst[i] = lg[i];
+    }
+    float u1[NMIX], u2;
+    if (P.a.u1) {
+        const float *src = P.a.u1 + ((size_t)t * P.a.Btot + P.a.b0 + b) * NMIX;
+#pragma unroll
+        for (int i = 0; i < NMIX; i++) u1[i] = __ldg(src + i);
+        u2 = __ldg(P.a.u2 + (size_t)t * P.a.Btot + P.a.b0 + b);
+    } else {
+        const uint2 key = make_uint2((uint32_t)P.a.seed, (uint32_t)(P.a.seed >> 32));
+#pragma unroll
+        for (int j = 0; j < 3; j++) {
+            const uint4 r4 = philox4x32(make_uint4((uint32_t)t, (uint32_t)(P.a.b0 + b), (uint32_t)j, 1u), key);
+            const uint32_t rr[4] = {r4.x, r4.y, r4.z, r4.w};
+#pragma unroll
+            for (int k = 0; k < 4; k++)
+                if (4 * j + k < NMIX) u1[4 * j + k] = u_clip(rr[k]);
+        }
+        u2 = u_clip(philox4x32(make_uint4((uint32_t)t, (uint32_t)(P.a.b0 + b), 0u, 2u), key).x);
+    }
+    int pick = 0;
+    float xv = mol_sample_thread(lg, u1, u2, &pick);
+    if (live) {
+        P.a.samples[(size_t)b * S + t] = xv;
+        P.a.picks[(size_t)b * S + t] = pick;
+    } else {
+        xv = 0.f;
+    }
+    if (P.a.teacher) xv = t + 1 < S ? P.a.teacher[(size_t)b * S + t + 1] : 0.f;
+    *xnext = xv;
+}
+
 __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
     extern __shared__ __align__(1024) uint8_t smem[];
-    __shared__ __align__(8) uint64_t bar_full[MAXSTAGE], bar_empty[MAXSTAGE], bar_tfull;
+    __shared__ __align__(8) uint64_t bar_full[MAXSTAGE], bar_empty[MAXSTAGE], bar_tf[NTF], bar_done;
     __shared__ uint32_t tmem_base_s;
     __shared__ int dead_s;
     uint8_t *stages = smem;
-    float *sbias = reinterpret_cast<float *>(smem + P.ring_bytes);      // this CTA's bias rows, layout of SBIAS
-    float *wf3 = sbias + SBIAS;                             // [NCP][512]
-    float *scr = wf3 + NCP * FCD;                           // per epilogue warp: 256 floats
+    float *sbias = reinterpret_cast<float *>(smem + P.ring_bytes);      // this CTA's bias rows / previous-sample columns (SB_*)
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, cta = blockIdx.x;
     const int G = P.G;
-    const int64_t S = P.a.S, B = P.a.B;
-    Watch w{P.gs.abort_flag, false};
-    // static roles: GRU (row tile, fold tile) jobs fill CTAs from 0 up, fc jobs from G - 1 down; at most one of each per CTA
+    const int64_t NF = (int64_t)P.NTILES * FT;
+    Watch w{P.gs.abort_flag, false, 0};
+    // static roles: GRU (row tile, fold tile) jobs fill CTAs from 0 up, fc jobs from G - 1 down; at most one of each per CTA;
+    // the fc CTA of row tile 0 also runs the tile's fc3 job and its sampler
     const bool has_gru = cta < MT_GRU * P.NTILES, has_fc = G - 1 - cta < MT_FC * P.NTILES;
     const int mt_g = cta % MT_GRU, nt_g = cta / MT_GRU, mt_f = (G - 1 - cta) % MT_FC, nt_f = (G - 1 - cta) / MT_FC;
+    const bool has_f3 = has_fc && mt_f == 0;
+    if (!has_gru && !has_fc) return;
 
     if (tid == 0) {
         for (int i = 0; i < MAXSTAGE; i++) { mbar_init(&bar_full[i], 1); mbar_init(&bar_empty[i], 1); }
-        mbar_init(&bar_tfull, 1);
+        for (int i = 0; i < NTF; i++) mbar_init(&bar_tf[i], 1);
+        mbar_init(&bar_done, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) tmem_alloc(&tmem_base_s, TMEM_COLS);
-    for (int i = tid; i < NCP * FCD; i += THREADS) wf3[i] = P.Wf3[i];
-    for (int i = tid; i < SBIAS; i += THREADS) {            // P.bias: rnn1 [16][2][96] | rnn2 [16][2][96] | fc1 [512] | fc2 [512]
+    for (int i = tid; i < SBIAS; i += THREADS) {
+        const float *gb = P.bias;                                               // rnn1 [16][2][96] | rnn2 [16][2][96]
+        const float *fb = gb + (size_t)2 * MT_GRU * 2 * GRU_ROWS;               // fc1 [512] | fc2 [512]
+        const float *xg = fb + 2 * FCD;                                         // x columns rnn1 [16][96] | rnn2 [16][96]
+        const float *xf = xg + (size_t)2 * MT_GRU * GRU_ROWS;                   // x column fc1 [512]
+        const float *b3 = xf + FCD;                                             // fc3 bias [32]
         float v = 0.f;
-        if (i < 4 * GRU_ROWS) {
-            if (has_gru) v = P.bias[(size_t)((i / (2 * GRU_ROWS)) * MT_GRU + mt_g) * 2 * GRU_ROWS + i % (2 * GRU_ROWS)];
-        } else if (has_fc) {
-            const int j = i - 4 * GRU_ROWS;
-            v = P.bias[(size_t)2 * MT_GRU * 2 * GRU_ROWS + (size_t)(j / FC_ROWS) * FCD + mt_f * FC_ROWS + j % FC_ROWS];
+        if (i < SB_F) {
+            if (has_gru) v = gb[(size_t)((i / (2 * GRU_ROWS)) * MT_GRU + mt_g) * 2 * GRU_ROWS + i % (2 * GRU_ROWS)];
+        } else if (i < SB_XG) {
+            const int j = i - SB_F;
+            if (has_fc) v = fb[(size_t)(j / FC_ROWS) * FCD + mt_f * FC_ROWS + j % FC_ROWS];
+        } else if (i < SB_XF) {
+            const int j = i - SB_XG;
+            if (has_gru) v = xg[(size_t)((j / GRU_ROWS) * MT_GRU + mt_g) * GRU_ROWS + j % GRU_ROWS];
+        } else if (i < SB_B3) {
+            if (has_fc) v = xf[mt_f * FC_ROWS + (i - SB_XF)];
+        } else {
+            v = b3[i - SB_B3];
         }
         sbias[i] = v;
     }
@@ -538,213 +704,196 @@ __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
     __syncthreads();
     tc_fence_after();
     const uint32_t tb = tmem_base_s;
+    const bool profiled_cta = P.prof && (cta == 0 || cta == G - 1);
+    long long *prof_base = P.prof + (cta == 0 ? 0 : 64);
 
     if (warp == 0) {
         // ======================================================================= TMA producer
         if (lane < NPROD) {
-            Ring r = make_ring(P, has_fc);
-            uint32_t count = 0;
-            if (has_gru) {      // step "-1": recurrent products of step 0 on the zero state (h = 0, :194-195)
-                produce_job(P, J_S1, mt_g, nt_g, -1, r, count, lane, stages, bar_full, bar_empty, w);
-                produce_job(P, J_S2, mt_g, nt_g, -1, r, count, lane, stages, bar_full, bar_empty, w);
+            Pipe pp{make_ring(P, has_gru), 0u, stages, bar_full, bar_empty};
+            // step "-1": recurrent products of step 0 on the zero state (h = 0, :194-195) and step 0's conditioning columns
+            if (has_gru) {
+                produce_job(P, J_S1, mt_g, nt_g, -1, -1, 0, pp, lane, w);
+                produce_job(P, J_R1A, mt_g, nt_g, 0, -1, 0, pp, lane, w);
+                produce_job(P, J_S2, mt_g, nt_g, -1, -1, 0, pp, lane, w);
+                produce_job(P, J_R2A, mt_g, nt_g, 0, -1, 0, pp, lane, w);
+            }
+            if (has_fc) {
+                produce_job(P, J_F1A, mt_f, nt_f, 0, -1, 0, pp, lane, w);
+                produce_job(P, J_F2A, mt_f, nt_f, 0, -1, 0, pp, lane, w);
             }
             for (int64_t t = 0; t < P.steps_run && !w.dead; t++) {
-                long long *pa = (P.prof && t == P.prof_step && (cta == 0 || cta == G - 1)) ? P.prof + (cta == 0 ? 0 : 64) + 32 : nullptr;
+                long long *pa = (profiled_cta && t == P.prof_step) ? prof_base + 32 : nullptr;
+                const bool more = t + 1 < P.steps_run;
                 if (has_gru) {
                     PROF_MARK(0);
-                    produce_job(P, J_R1, mt_g, nt_g, t, r, count, lane, stages, bar_full, bar_empty, w, pa ? pa + 0 : nullptr);
+                    produce_job(P, J_R2C, mt_g, nt_g, t, PH_RNN1, t + 1, pp, lane, w, pa ? pa + 0 : nullptr, pa ? prof_base + 8 : nullptr);
                     PROF_MARK(1);
-                    produce_job(P, J_R2, mt_g, nt_g, t, r, count, lane, stages, bar_full, bar_empty, w, pa ? pa + 1 : nullptr);
+                    if (more) produce_job(P, J_S1, mt_g, nt_g, t, -1, 0, pp, lane, w, pa ? pa + 1 : nullptr);
+                    if (more) produce_job(P, J_R1A, mt_g, nt_g, t + 1, -1, 0, pp, lane, w);
                     PROF_MARK(2);
-                    produce_job(P, J_S1, mt_g, nt_g, t, r, count, lane, stages, bar_full, bar_empty, w, pa ? pa + 2 : nullptr);
-                    PROF_MARK(3);
                 }
                 if (has_fc) {
+                    PROF_MARK(3);
+                    produce_job(P, J_F1C, mt_f, nt_f, t, PH_RNN2, t + 1, pp, lane, w, pa ? pa + 2 : nullptr, pa ? prof_base + 9 : nullptr);
                     PROF_MARK(4);
-                    produce_job(P, J_F1, mt_f, nt_f, t, r, count, lane, stages, bar_full, bar_empty, w, pa ? pa + 4 : nullptr);
+                    produce_job(P, J_F2C, mt_f, nt_f, t, PH_FC1, t + 1, pp, lane, w, pa ? pa + 3 : nullptr, pa ? prof_base + 19 : nullptr);
                     PROF_MARK(5);
-                    produce_job(P, J_F2, mt_f, nt_f, t, r, count, lane, stages, bar_full, bar_empty, w, pa ? pa + 5 : nullptr);
-                    PROF_MARK(6);
+                    if (has_f3) {
+                        produce_job(P, J_F3, 0, nt_f, t, PH_FC2, t + 1, pp, lane, w, pa ? pa + 4 : nullptr, pa ? prof_base + 31 : nullptr);
+                        PROF_MARK(6);
+                        // fc3's accumulator shares fc1's columns: the sampler must have read it
+                        if (more) produce_job(P, J_F1A, mt_f, nt_f, t + 1, PH_SAMPLE, t + 1, pp, lane, w);
+                        if (more) produce_job(P, J_F2A, mt_f, nt_f, t + 1, -1, 0, pp, lane, w);
+                    } else if (more) {
+                        produce_job(P, J_F1A, mt_f, nt_f, t + 1, -1, 0, pp, lane, w);
+                        // fc2's accumulator is free once this CTA's own fc2 epilogue is through: implied by the tile's counter
+                        produce_job(P, J_F2A, mt_f, nt_f, t + 1, PH_FC2, t + 1, pp, lane, w);
+                    }
                 }
-                if (has_gru) {
-                    produce_job(P, J_S2, mt_g, nt_g, t, r, count, lane, stages, bar_full, bar_empty, w, pa ? pa + 3 : nullptr);
+                if (has_gru && more) {         // nothing reads the recurrent products of the step after the last
+                    produce_job(P, J_S2, mt_g, nt_g, t, PH_RNN2, t + 1, pp, lane, w, pa ? pa + 5 : nullptr);
+                    produce_job(P, J_R2A, mt_g, nt_g, t + 1, -1, 0, pp, lane, w);
                     PROF_MARK(7);
                 }
             }
         }
     } else if (warp == 1) {
-        // ======================================================================= MMA issuer
+        // ======================================================================= MMA issuer: the producer's job order, no gates
         if (lane == 0) {
-            Ring r = make_ring(P, has_fc);
-            const uint32_t stage0 = smem_u32(stages);
+            Issue is{make_ring(P, has_gru), smem_u32(stages), tb, bar_full, bar_empty, bar_tf, P.exp};
             if (has_gru) {
-                issue_job(P, J_S1, r, stage0, tb, bar_full, bar_empty, &bar_tfull, w);
-                issue_job(P, J_S2, r, stage0, tb, bar_full, bar_empty, &bar_tfull, w);
+                issue_job(J_S1, is, w);
+                issue_job(J_R1A, is, w);
+                issue_job(J_S2, is, w);
+                issue_job(J_R2A, is, w);
+            }
+            if (has_fc) {
+                issue_job(J_F1A, is, w);
+                issue_job(J_F2A, is, w);
             }
             for (int64_t t = 0; t < P.steps_run && !w.dead; t++) {
-                long long *ma = (P.prof && t == P.prof_step && (cta == 0 || cta == G - 1)) ? P.prof + (cta == 0 ? 0 : 64) + 40 : nullptr;
+                long long *ma = (profiled_cta && t == P.prof_step) ? prof_base + 40 : nullptr;
+                const bool more = t + 1 < P.steps_run;
                 if (has_gru) {
-                    issue_job(P, J_R1, r, stage0, tb, bar_full, bar_empty, &bar_tfull, w, ma ? ma + 0 : nullptr);
+                    issue_job(J_R2C, is, w, ma ? ma + 0 : nullptr);
                     PROF_MARK(10);
-                    issue_job(P, J_R2, r, stage0, tb, bar_full, bar_empty, &bar_tfull, w, ma ? ma + 3 : nullptr);
+                    if (more) issue_job(J_S1, is, w, ma ? ma + 3 : nullptr);
+                    if (more) issue_job(J_R1A, is, w);
                     PROF_MARK(11);
-                    issue_job(P, J_S1, r, stage0, tb, bar_full, bar_empty, &bar_tfull, w, ma ? ma + 6 : nullptr);
-                    PROF_MARK(12);
                 }
                 if (has_fc) {
-                    issue_job(P, J_F1, r, stage0, tb, bar_full, bar_empty, &bar_tfull, w, ma ? ma + 12 : nullptr);
+                    issue_job(J_F1C, is, w, ma ? ma + 6 : nullptr);
+                    PROF_MARK(12);
+                    issue_job(J_F2C, is, w, ma ? ma + 9 : nullptr);
                     PROF_MARK(13);
-                    issue_job(P, J_F2, r, stage0, tb, bar_full, bar_empty, &bar_tfull, w, ma ? ma + 15 : nullptr);
-                    PROF_MARK(14);
+                    if (has_f3) {
+                        issue_job(J_F3, is, w, ma ? ma + 12 : nullptr);
+                        PROF_MARK(14);
+                    }
+                    if (more) {
+                        issue_job(J_F1A, is, w);
+                        issue_job(J_F2A, is, w);
+                    }
                 }
-                if (has_gru) {
-                    issue_job(P, J_S2, r, stage0, tb, bar_full, bar_empty, &bar_tfull, w, ma ? ma + 9 : nullptr);
+                if (has_gru && more) {
+                    issue_job(J_S2, is, w, ma ? ma + 15 : nullptr);
+                    issue_job(J_R2A, is, w);
                     PROF_MARK(15);
                 }
             }
+            // every MMA issued (hence every copy it consumed) is through before the CTA gives up TMEM and shared memory
+            umma_commit(&bar_done);
+            w.site = 0x4f;
+            mbar_wait(&bar_done, 0u, w);
         }
         __syncwarp();
     } else {
-        // ======================================================================= epilogue warps + fc3 / sampling phase
+        // ======================================================================= epilogue warps
         const int etid = tid - 64, ewarp = warp - 2;
-        const int q = warp & 3, half = ewarp >> 2;          // TMEM lane quarter this warp may read; which accumulator / idle
-        float *myscr = scr + ewarp * 256;
-        const uint2 key = make_uint2((uint32_t)P.a.seed, (uint32_t)(P.a.seed >> 32));
-        const int nmix = P.NC / 3;
-        uint32_t tpar = 0;                                   // parity of bar_tfull: one completion per job with an epilogue
+        const int q = warp & 3, half = ewarp >> 2;          // TMEM lane quarter this warp may read; which half of the columns
+        const int fi = q * 32 + lane;
+        uint32_t tfpar = 0;                                  // every accumulator-ready barrier completes once per step
         // recurrent state of this thread's (fold, 16 units), both layers, and rnn1's new state for s12: registers for the whole run
         float hst1[16], hst2[16], h1new[16];
 #pragma unroll
         for (int i = 0; i < 16; i++) hst1[i] = hst2[i] = h1new[i] = 0.f;        // h1 = h2 = 0 (:194-195)
-        auto publish = [&](int p) {                          // every writing thread fences, one thread releases the counter
+        auto publish = [&](int phase, int nt) {              // every writing thread fences, one thread releases the counter
             fence_proxy_async_global();
             epi_bar();
-            if (etid == 0) red_release_add_u64(phase_counter(P.gs, p), 1ull);
+            if (etid == 0) red_release_add_u64(tile_counter(P.gs, phase, nt), 1ull);
         };
-        auto wait_acc = [&]() {
-            mbar_wait(&bar_tfull, tpar, w);
-            tpar ^= 1u;
+        auto wait_acc = [&](int tf) {
+            w.site = 0x50 + tf;
+            mbar_wait(&bar_tf[tf], tfpar, w);
             __syncwarp();       // lanes leave the spin loop one by one; tcgen05.ld is .sync.aligned: converge first
             tc_fence_after();
         };
-        // ---- step "-1": conditioning operand of step 0 (x_prev = 0 or the teacher's first sample)
-        for (int64_t b = cta + (int64_t)G * ewarp; b < B; b += (int64_t)G * EPI_WARPS) {
-            const float x0 = P.a.teacher ? P.a.teacher[(size_t)b * S] : 0.f;
-            load_cond_row(P, b, 0, myscr, lane);
-            build_cond_operand(P, b, x0, myscr, lane);
-        }
-        publish(4);
-
         for (int64_t t = 0; t < P.steps_run; t++) {
             if (w.dead) break;                               // uniform: set below from a flag read after a barrier
             if (has_gru) {
-                wait_acc();
-                if (etid == 0) PROF_MARK(20);
-                epi_gru<0>(P, mt_g, nt_g, t, tb, sbias, hst1, h1new, q, half, lane);
-                if (etid == 0) PROF_MARK(16);
+                wait_acc(TF_R1);
+                if (etid == 0) {
+                    PROF_MARK(20);
+                    w.site = 0x60;
+                    tile_wait(P.gs, PH_SAMPLE, nt_g, t, w);      // the sample of step t - 1 is out
+                }
+                epi_bar();
+                if (etid == 0) PROF_MARK(21);
+                const float xp = __ldcg(P.xp + (size_t)(t & 1) * NF + (size_t)nt_g * FT + fi);
+                epi_gru<0>(P, mt_g, nt_g, t, tb, sbias, xp, hst1, h1new, q, half, lane);
                 tc_fence_before();
-            }
-            publish(0);
-            if (etid == 0) PROF_MARK(21);
-            if (has_gru) {
-                wait_acc();
                 if (etid == 0) PROF_MARK(22);
-                epi_gru<1>(P, mt_g, nt_g, t, tb, sbias, hst2, h1new, q, half, lane);
-                if (etid == 0) PROF_MARK(17);
-                tc_fence_before();
-            }
-            publish(1);
-            if (etid == 0) PROF_MARK(23);
-            if (has_fc) {
-                wait_acc();
+                publish(PH_RNN1, nt_g);
+                if (etid == 0) PROF_MARK(23);
+                wait_acc(TF_R2);
                 if (etid == 0) PROF_MARK(24);
-                epi_fc<0>(P, mt_f, nt_f, tb, sbias, q, half, lane);
-                if (etid == 0) PROF_MARK(18);
+                epi_gru<1>(P, mt_g, nt_g, t, tb, sbias, xp, hst2, h1new, q, half, lane);
                 tc_fence_before();
-            }
-            publish(2);
-            if (etid == 0) PROF_MARK(25);
-            if (has_fc) {
-                wait_acc();
+                if (etid == 0) PROF_MARK(25);
+                publish(PH_RNN2, nt_g);
                 if (etid == 0) PROF_MARK(26);
-                epi_fc<1>(P, mt_f, nt_f, tb, sbias, q, half, lane);
-                if (etid == 0) PROF_MARK(19);
+            }
+            if (has_fc) {
+                wait_acc(TF_F1);
+                if (etid == 0) PROF_MARK(27);
+                // published before rnn1 of this step began; the loads that filled fc1's stages were ordered behind rnn2's counter
+                const float xp = __ldcg(P.xp + (size_t)(t & 1) * NF + (size_t)nt_f * FT + fi);
+                epi_fc<0>(P, mt_f, nt_f, tb, sbias, xp, q, half, lane);
                 tc_fence_before();
+                publish(PH_FC1, nt_f);
+                if (etid == 0) PROF_MARK(28);
+                wait_acc(TF_F2);
+                if (etid == 0) PROF_MARK(29);
+                epi_fc<1>(P, mt_f, nt_f, tb, sbias, 0.f, q, half, lane);
+                tc_fence_before();
+                publish(PH_FC2, nt_f);
+                if (etid == 0) PROF_MARK(30);
+                if (has_f3) {
+                    wait_acc(TF_F3);
+                    if (etid == 0) PROF_MARK(16);
+                    if (half == 0) epi_sample(P, nt_f, t, tb, sbias, q, lane);
+                    tc_fence_before();
+                    if (etid == 0) PROF_MARK(17);
+                    __threadfence();
+                    epi_bar();
+                    if (etid == 0) red_release_add_u64(tile_counter(P.gs, PH_SAMPLE, nt_f), 1ull);
+                    if (etid == 0) PROF_MARK(18);
+                }
             }
-            publish(3);
-            if (etid == 0) PROF_MARK(27);
-            // ---------------- fc3 (:223) in fp32 + MoL draw (utils/distribution.py:87-123) + next conditioning operand.
-            // What does not depend on fc2 is done before the wait: next step's conditioning row (HBM) and the noise.
-            const int64_t bfirst = cta + (int64_t)G * ewarp;
-            float myu1 = 0.5f, u2 = 0.5f;
-            auto draw_noise = [&](int64_t b) {
-                if (P.a.u1) {
-                    if (lane < nmix) myu1 = P.a.u1[((size_t)t * P.a.Btot + P.a.b0 + b) * nmix + lane];
-                    u2 = P.a.u2[(size_t)t * P.a.Btot + P.a.b0 + b];
-                } else {
-                    const uint4 r4 = philox4x32(make_uint4((uint32_t)t, (uint32_t)(P.a.b0 + b), (uint32_t)(lane >> 2), 1u), key);
-                    const uint32_t rr[4] = {r4.x, r4.y, r4.z, r4.w};
-                    myu1 = u_clip(rr[lane & 3]);
-                    const uint4 r2 = philox4x32(make_uint4((uint32_t)t, (uint32_t)(P.a.b0 + b), 0u, 2u), key);
-                    u2 = u_clip(r2.x);
-                }
-            };
-            if (bfirst < B) {
-                load_cond_row(P, bfirst, t + 1, myscr, lane);
-                draw_noise(bfirst);
-            }
-            if (etid == 0) grid_wait(P.gs, 3, (unsigned long long)G * (unsigned long long)(t + 1), w);
-            epi_bar();
-            if (etid == 0) PROF_MARK(28);
-            for (int64_t b = bfirst; b < B; b += (int64_t)G * EPI_WARPS) {
-                if (b != bfirst) {
-                    load_cond_row(P, b, t + 1, myscr, lane);
-                    draw_noise(b);
-                }
-                float4 y[4];
-#pragma unroll
-                for (int jj = 0; jj < 4; jj++) y[jj] = __ldcg(reinterpret_cast<const float4 *>(P.y2f + (size_t)b * FCD + 128 * jj + lane * 4));
-                float acc[NCP];
-#pragma unroll
-                for (int r = 0; r < NCP; r++) {
-                    float a = 0.f;
-#pragma unroll
-                    for (int jj = 0; jj < 4; jj++) {
-                        const float4 wv = *reinterpret_cast<const float4 *>(wf3 + r * FCD + 128 * jj + lane * 4);
-                        a = fmaf(wv.x, y[jj].x, a);
-                        a = fmaf(wv.y, y[jj].y, a);
-                        a = fmaf(wv.z, y[jj].z, a);
-                        a = fmaf(wv.w, y[jj].w, a);
-                    }
-                    acc[r] = a;
-                }
-                warp_reduce_scatter<NCP>(acc, lane);
-                const int row = reduce_scatter_base<NCP>(lane);
-                const float lg = acc[0] + __ldg(P.bf3 + row);
-                __syncwarp();
-                myscr[224 + row] = lg;
-                __syncwarp();
-                const bool live = t < P.a.fold_len[b];
-                if (P.a.logits_out && live && lane < P.NC) P.a.logits_out[((size_t)b * S + t) * P.NC + lane] = myscr[224 + lane];
-                int pick = 0;
-                float xv = mol_sample_smem(myscr + 224, nmix, myu1, u2, lane, &pick);
-                if (!live) xv = 0.f;
-                if (lane == 0 && live) {
-                    P.a.samples[(size_t)b * S + t] = xv;
-                    P.a.picks[(size_t)b * S + t] = pick;
-                }
-                if (P.a.teacher) xv = t + 1 < S ? P.a.teacher[(size_t)b * S + t + 1] : 0.f;
-                build_cond_operand(P, b, xv, myscr, lane);
-            }
-            if (etid == 0) PROF_MARK(29);
-            publish(4);
-            if (etid == 0) PROF_MARK(30);
+            tfpar ^= 1u;
             // uniform exit on a fired watchdog
             if (etid == 0) dead_s = (w.dead || ld_volatile_s32(P.gs.abort_flag)) ? 1 : 0;
             epi_bar();
             w.dead = dead_s != 0;
             epi_bar();
         }
+    }
+    // after an abort the waits fall through: give copies and MMAs still in flight time to land before shared memory and
+    // TMEM go away, so that the host can read the abort code instead of a launch failure
+    if (w.dead || ld_volatile_s32(P.gs.abort_flag)) {
+        const long long t0 = clock64();
+        while (clock64() - t0 < 4000000ll) {}
     }
     tc_fence_before();
     __syncthreads();
@@ -771,7 +920,7 @@ static inline float bf2f(uint16_t b) {
 bool mma_supported(const wrnn_handle *h) {
     const Dims &d = h->d;
     return h->mma.ok && d.mode == WRNN_MODE_MOL && d.H == mma::H && d.FC == mma::FCD && d.A == mma::AUX && d.F == mma::FEAT &&
-           d.NC <= mma::NCP;
+           d.NC == 3 * mma::NMIX;
 }
 int mma_min_folds() { return 48; }
 
@@ -780,7 +929,7 @@ int mma_plan(wrnn_handle *h) {
     const Dims &d = h->d;
     MmaPlan &pl = h->mma;
     pl.ok = false;
-    if (!(d.mode == WRNN_MODE_MOL && d.H == H && d.FC == FCD && d.A == AUX && d.F == FEAT && d.NC <= NCP)) return 0;
+    if (!(d.mode == WRNN_MODE_MOL && d.H == H && d.FC == FCD && d.A == AUX && d.F == FEAT && d.NC == 3 * NMIX)) return 0;
     if (h->num_sms < 16) return 0;
     auto get = [&](const char *k) -> const HostTensor * {
         auto it = h->w.find(k);
@@ -834,31 +983,33 @@ int mma_plan(wrnn_handle *h) {
     // weight on a 512-wide operand column k for job type jt
     auto main_w = [&](int jt, int grow, int k) -> double {
         switch (jt) {
-            case J_R2: return W2i->v[(size_t)grow * (H + AUX) + k];
+            case J_R2C: return W2i->v[(size_t)grow * (H + AUX) + k];
             case J_S1: return W1h->v[(size_t)grow * H + k];
             case J_S2: return W2h->v[(size_t)grow * H + k];
-            case J_F1: return F1->v[(size_t)grow * (H + AUX) + k];
-            default: return F2->v[(size_t)grow * (FCD + AUX) + k];
+            case J_F1C: return F1->v[(size_t)grow * (H + AUX) + k];
+            case J_F2C: return F2->v[(size_t)grow * (FCD + AUX) + k];
+            default: return grow < d.NC ? F3->v[(size_t)grow * FCD + k] : 0.0;       // fc3, rows padded to 32
         }
     };
-    const int cond_phase[NJOB] = {0, 1, -1, -1, 2, 3};     // which layer's conditioning columns a job carries
+    auto cond_layer = [](int jt) { return jt == J_R1A ? 0 : jt == J_R2A ? 1 : jt == J_F1A ? 2 : 3; };     // J_F2A: 3
     size_t total = 0;
     for (int jt = 0; jt < NJOB; jt++) {
         pl.offA[jt] = (int64_t)total;
-        total += (size_t)(jt >= J_F1 ? MT_FC : MT_GRU) * job_stages(jt) * 2 * KC * job_rows(jt) * 16;
+        total += (size_t)job_tiles(jt) * job_stages(jt) * 2 * KC * job_rows(jt) * 16;
     }
-    std::vector<uint16_t> img(total / 2 + 2048, 0);       // + slack: the 96-row image is addressed as 128 rows
+    std::vector<uint16_t> img(total / 2, 0);
     for (int jt = 0; jt < NJOB; jt++) {
-        const int rows = job_rows(jt), mts = jt >= J_F1 ? MT_FC : MT_GRU, nst = job_stages(jt);
+        const int rows = job_rows(jt), mts = job_tiles(jt), nst = job_stages(jt);
         for (int mt = 0; mt < mts; mt++)
             for (int s = 0; s < nst; s++) {
                 const StageInfo si = stage_info(jt, s);
                 uint16_t *blk = img.data() + (size_t)pl.offA[jt] / 2 + ((size_t)mt * nst + s) * (2 * KC * rows * 8);
                 for (int r = 0; r < rows; r++) {
-                    const int grow = jt < J_F1 ? (r / UT) * H + mt * UT + (r % UT) : mt * FC_ROWS + r;
+                    const int grow = rows == GRU_ROWS ? (r / UT) * H + mt * UT + (r % UT) : mt * FC_ROWS + r;
                     for (int kl = 0; kl < KC * 8; kl++) {
-                        const int feat = si.g * 32 + kl;
-                        const double wv = si.arr == ARR_C ? cond_w(cond_phase[jt], grow, feat) : main_w(jt, grow, feat);
+                        const int feat = si.g * (KC * 8) + kl;
+                        // the previous-sample slot of the operand is zero: its column is applied in the epilogues (xcol below)
+                        const double wv = si.arr == ARR_C ? (feat == C_X ? 0.0 : cond_w(cond_layer(jt), grow, feat)) : main_w(jt, grow, feat);
                         const float wf = (float)wv;
                         const uint16_t hi = f2bf(wf), lo = f2bf((float)(wv - (double)bf2f(hi)));
                         const size_t o = ((size_t)(kl / 8) * rows + r) * 8 + kl % 8;
@@ -868,7 +1019,10 @@ int mma_plan(wrnn_handle *h) {
                 }
             }
     }
-    std::vector<float> bias((size_t)2 * MT_GRU * 2 * GRU_ROWS + 2 * FCD, 0.f);
+    // biases, then the previous-sample column of the three composed input matrices (column 0 of W . W_I), then fc3's bias
+    const size_t off_fc = (size_t)2 * MT_GRU * 2 * GRU_ROWS, off_xg = off_fc + 2 * FCD, off_xf = off_xg + (size_t)2 * MT_GRU * GRU_ROWS,
+                 off_b3 = off_xf + FCD;
+    std::vector<float> bias(off_b3 + NCP, 0.f);
     for (int p = 0; p < 2; p++)
         for (int mt = 0; mt < MT_GRU; mt++)
             for (int r = 0; r < GRU_ROWS; r++) {
@@ -876,30 +1030,25 @@ int mma_plan(wrnn_handle *h) {
                 float *b = bias.data() + (size_t)(p * MT_GRU + mt) * 2 * GRU_ROWS;
                 b[r] = (float)((p == 0 ? bc1[grow] : bc2[grow]) + (double)(p == 0 ? B1i : B2i)->v[grow]);
                 b[GRU_ROWS + r] = (p == 0 ? B1h : B2h)->v[grow];
+                bias[off_xg + (size_t)(p * MT_GRU + mt) * GRU_ROWS + r] = (float)(p == 0 ? Wc1 : Wc2)[(size_t)grow * KI];
             }
     for (int r = 0; r < FCD; r++) {
-        bias[(size_t)2 * MT_GRU * 2 * GRU_ROWS + r] = (float)(bc3[r] + (double)F1b->v[r]);
-        bias[(size_t)2 * MT_GRU * 2 * GRU_ROWS + FCD + r] = F2b->v[r];
+        bias[off_fc + r] = (float)(bc3[r] + (double)F1b->v[r]);
+        bias[off_fc + FCD + r] = F2b->v[r];
+        bias[off_xf + r] = (float)Wc3[(size_t)r * KI];
     }
-    std::vector<float> wf3((size_t)NCP * FCD + NCP, 0.f);
-    for (int r = 0; r < d.NC; r++) {
-        memcpy(wf3.data() + (size_t)r * FCD, F3->v.data() + (size_t)r * FCD, FCD * sizeof(float));
-        wf3[(size_t)NCP * FCD + r] = F3b->v[r];
-    }
+    for (int r = 0; r < d.NC; r++) bias[off_b3 + r] = F3b->v[r];
     if (pl.Aimg) cudaFree(pl.Aimg);
     if (pl.bias) cudaFree(pl.bias);
-    if (pl.wf3) cudaFree(pl.wf3);
-    pl.Aimg = nullptr; pl.bias = nullptr; pl.wf3 = nullptr;
+    pl.Aimg = nullptr; pl.bias = nullptr;
     WRNN_CUDA(h, cudaMalloc((void **)&pl.Aimg, img.size() * 2));
     WRNN_CUDA(h, cudaMemcpy(pl.Aimg, img.data(), img.size() * 2, cudaMemcpyHostToDevice));
     WRNN_CUDA(h, cudaMalloc((void **)&pl.bias, bias.size() * 4));
     WRNN_CUDA(h, cudaMemcpy(pl.bias, bias.data(), bias.size() * 4, cudaMemcpyHostToDevice));
-    WRNN_CUDA(h, cudaMalloc((void **)&pl.wf3, wf3.size() * 4));
-    WRNN_CUDA(h, cudaMemcpy(pl.wf3, wf3.data(), wf3.size() * 4, cudaMemcpyHostToDevice));
     pl.img_bytes = total;
-    // everything the device offers minus the static part (barriers): the stage ring takes what staging / fc3 rows leave
+    // everything the device offers minus the static part (barriers): the stage ring takes what the bias rows leave
     pl.smem_bytes = (h->smem_optin - 1024) / 1024 * 1024;
-    if (pl.smem_bytes < (size_t)FIXED_SMEM + 2 * (W_FC + ACT_STAGE)) return 0;
+    if (pl.smem_bytes < (size_t)FIXED_SMEM + 3 * (W_GRU + ACT_STAGE)) return 0;
     WRNN_CUDA(h, cudaFuncSetAttribute(mma::mma_loop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes));
     pl.ok = true;
     return 0;
@@ -909,17 +1058,22 @@ int mma_plan(wrnn_handle *h) {
 // num_sms / 16 tiles (9 on a B200: 1152 folds) so that every CTA has at most one GRU job; fc jobs fill CTAs from the top.
 int64_t mma_max_folds(const wrnn_handle *h) { return (int64_t)128 * (h->num_sms / mma::MT_GRU); }
 
+// initial previous sample: 0, or the teacher's first sample (fatchord_version.py:197, forward(): x[:, 0])
+__global__ void xp_init_kernel(float *xp, const float *teacher, int64_t B, int64_t S, int64_t NF) {
+    const int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (b < 2 * NF) xp[b] = (b < B && teacher) ? teacher[(size_t)b * S] : 0.f;
+}
+
 int mma_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
     using namespace mma;
     const MmaPlan &pl = h->mma;
     Params P;
     P.a = a;
     P.G = h->num_sms;
-    P.NT = FT;
-    P.NTILES = (int)((a.B + P.NT - 1) / P.NT);
-    if (MT_GRU * P.NTILES > P.G)
+    P.NTILES = (int)((a.B + FT - 1) / FT);
+    if (MT_GRU * P.NTILES > P.G || P.NTILES > MAXTILES)
         return fail(h, WRNN_ERR_ARG, "tensor-core loop kernel: %lld folds in tiles of %d need %d CTAs, the device has %d",
-                    (long long)a.B, P.NT, MT_GRU * P.NTILES, P.G);
+                    (long long)a.B, FT, MT_GRU * P.NTILES, P.G);
     P.ring_bytes = (int)(pl.smem_bytes - FIXED_SMEM) / 1024 * 1024;
     P.NC = h->d.NC;
     P.steps_run = a.S;
@@ -931,27 +1085,38 @@ int mma_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
     P.Aimg = pl.Aimg;
     for (int j = 0; j < NJOB; j++) P.offA[j] = pl.offA[j];
     P.bias = pl.bias;
-    P.Wf3 = pl.wf3;
-    P.bf3 = pl.wf3 + (size_t)NCP * FCD;
-    const size_t NF = (size_t)P.NTILES * P.NT;
-    const size_t bH = NF * H * 4, bC = NF * CGROUPS * 128, bF = NF * H * sizeof(float);     // hi + lo bf16 = 4 B per element
-    const size_t total = 6 * bH + bC + 3 * bF + 4096;
-    WRNN_TRY(ws_reserve(h, h->ws_act, total));
-    WRNN_CUDA(h, cudaMemsetAsync(h->ws_act.p, 0, total, st));       // h1 = h2 = 0 (:194-195), padded folds stay zero
+    const size_t NF = (size_t)P.NTILES * FT;
+    const size_t bH = NF * H * 4, bF = NF * H * sizeof(float);       // operands: hi + lo bf16 = 4 B per element
+    const size_t bX = (2 * NF * sizeof(float) + 1023) / 1024 * 1024;
+    const size_t bC = (size_t)a.S * P.NTILES * CGROUPS * ACT_STAGE;  // conditioning operand of every step
+    const size_t state = 7 * bH + bX + 3 * bF;
+    WRNN_TRY(ws_reserve(h, h->ws_act, state + bC + 4096));
+    WRNN_CUDA(h, cudaMemsetAsync(h->ws_act.p, 0, state, st));       // h1 = h2 = 0 (:194-195), padded folds stay zero
     uint8_t *p8 = (uint8_t *)h->ws_act.p;
     P.H1[0] = p8; p8 += bH; P.H1[1] = p8; p8 += bH;
     P.H2[0] = p8; p8 += bH; P.H2[1] = p8; p8 += bH;
-    P.S12 = p8; p8 += bH; P.Y1 = p8; p8 += bH;
-    P.C = p8; p8 += (bC + 1023) / 1024 * 1024;
-    P.h1f = (float *)p8; p8 += bF; P.h2f = (float *)p8; p8 += bF; P.y2f = (float *)p8;
+    P.S12 = p8; p8 += bH; P.Y1 = p8; p8 += bH; P.Y2 = p8; p8 += bH;
+    P.xp = (float *)p8; p8 += bX;
+    P.h1f = (float *)p8; p8 += bF; P.h2f = (float *)p8; p8 += bF; P.y2f = (float *)p8; p8 += bF;
+    uint8_t *Cop = p8;
+    P.Cop = Cop;
     h->mma_dbg[0] = P.h1f; h->mma_dbg[1] = P.h2f; h->mma_dbg[2] = P.y2f;
-    WRNN_TRY(ws_reserve(h, h->ws_mma_sync, 1024));                    // five phase counters, 128 bytes apart, from +128
-    WRNN_CUDA(h, cudaMemsetAsync(h->ws_mma_sync.p, 0, 1024, st));
+    {       // pre-pass: the conditioning operand of all steps, and the first previous sample
+        const int64_t warps = a.S * (int64_t)NF;
+        cond_operand_kernel<<<(unsigned)((warps + 7) / 8), 256, 0, st>>>(a.cond, a.B, a.S, P.NTILES, Cop);
+        xp_init_kernel<<<(unsigned)((2 * NF + 255) / 256), 256, 0, st>>>(P.xp, a.teacher, a.B, a.S, (int64_t)NF);
+        WRNN_CUDA(h, cudaGetLastError());
+        h->launches += 2;
+    }
+    const size_t sync_bytes = (size_t)(1 + NPHASE * MAXTILES) * 128;  // one 128-byte line per (phase, fold tile) counter, from +128
+    WRNN_TRY(ws_reserve(h, h->ws_mma_sync, sync_bytes));
+    WRNN_CUDA(h, cudaMemsetAsync(h->ws_mma_sync.p, 0, sync_bytes, st));
     P.gs.counter = (unsigned long long *)h->ws_mma_sync.p;
     P.gs.abort_flag = (int *)((char *)h->ws_sync.p + 64);             // the call's sticky abort flag (api_run.cu)
     WRNN_CUDA(h, cudaFuncSetAttribute(mma_loop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes));
     P.prof = nullptr;
     P.prof_step = -1;
+    P.exp = getenv("WRNN_MMA_EXP") ? atoi(getenv("WRNN_MMA_EXP")) : 0;
     const char *pe = getenv("WRNN_MMA_PROF");
     if (pe) {
         WRNN_TRY(ws_reserve(h, h->ws_prof, 128 * sizeof(long long)));
@@ -967,30 +1132,33 @@ int mma_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
         WRNN_CUDA(h, cudaStreamSynchronize(st));
         WRNN_CUDA(h, cudaMemcpy(pr.data(), P.prof, 128 * sizeof(long long), cudaMemcpyDeviceToHost));
         static const char *names[32] = {
-            "producer: step begin", "producer: rnn1 issued", "producer: rnn2 issued", "producer: recurrent-1 issued", "producer: fc begin",
-            "producer: fc1 issued", "producer: fc2 issued", "producer: recurrent-2 issued", "", "",
-            "mma: rnn1 issued", "mma: rnn2 issued", "mma: recurrent-1 issued", "mma: fc1 issued", "mma: fc2 issued", "mma: recurrent-2 issued",
-            "epilogue: rnn1 gates done (warp 2)", "epilogue: rnn2 gates done (warp 2)", "epilogue: fc1 done (warp 2)", "epilogue: fc2 done (warp 2)",
-            "epilogue: rnn1 accumulators ready", "epilogue: rnn1 published", "epilogue: rnn2 accumulators ready", "epilogue: rnn2 published",
-            "epilogue: fc1 accumulator ready", "epilogue: fc1 published", "epilogue: fc2 accumulator ready", "epilogue: fc2 published",
-            "fc3 phase: fc2 of all CTAs seen", "fc3 phase: folds done", "fc3 phase: published", ""};
+            "producer: step begin", "producer: rnn2 issued", "producer: recurrent-1 + next rnn1 cond issued", "producer: fc begin",
+            "producer: fc1 issued", "producer: fc2 issued", "producer: fc3 issued", "producer: recurrent-2 + next rnn2 cond issued", "producer: rnn1 of the tile seen (rnn2 loads start)",
+            "producer: rnn2 of the tile seen (fc1 loads start)",
+            "mma: rnn2 issued", "mma: recurrent-1 + next rnn1 cond issued", "mma: fc1 issued", "mma: fc2 issued", "mma: fc3 issued",
+            "mma: recurrent-2 + next rnn2 cond issued",
+            "sampler: fc3 accumulator ready", "sampler: drawn", "sampler: published", "producer: fc1 of the tile seen (fc2 loads start)",
+            "rnn1: accumulators ready", "rnn1: previous sample seen", "rnn1: gates done (warp 2)", "rnn1: published",
+            "rnn2: accumulators ready", "rnn2: gates done (warp 2)", "rnn2: published",
+            "fc1: accumulator ready", "fc1: published", "fc2: accumulator ready", "fc2: published", "producer: fc2 of the tile seen (fc3 loads start)"};
         for (int c = 0; c < 2; c++) {
             const long long *q = pr.data() + 64 * c;
             long long t0 = 0;
             for (int i = 0; i < 32; i++)
                 if (q[i] && (!t0 || q[i] < t0)) t0 = q[i];
             fprintf(stderr, "[mma prof] CTA %s, step %lld, folds %lld, fold tile %d\n", c == 0 ? "0" : "G-1", (long long)P.prof_step,
-                    (long long)a.B, P.NT);
+                    (long long)a.B, FT);
             std::vector<std::pair<long long, int>> ev;
             for (int i = 0; i < 32; i++)
                 if (q[i]) ev.push_back({q[i] - t0, i});
             std::sort(ev.begin(), ev.end());
             for (auto &e : ev) fprintf(stderr, "[mma prof]   %8lld  %s\n", e.first, names[e.second]);
-            static const char *jn[6] = {"rnn1", "rnn2", "recurrent-1", "recurrent-2", "fc1", "fc2"};
-            for (int jt = 0; jt < 6; jt++)
-                if (q[40 + 3 * jt + 1])
+            static const char *jn[6] = {"rnn2", "recurrent-1", "fc1", "fc2", "fc3", "recurrent-2"};
+            static const int jtype[6] = {J_R2C, J_S1, J_F1C, J_F2C, J_F3, J_S2};
+            for (int j = 0; j < 6; j++)
+                if (q[40 + 3 * j + 1])
                     fprintf(stderr, "[mma prof]   %-12s %2d stages: MMA thread full-wait %6lld, issue %6lld, commit %5lld; producer lane 0 empty-wait %6lld\n",
-                            jn[jt], job_stages(jt), q[40 + 3 * jt], q[40 + 3 * jt + 1], q[40 + 3 * jt + 2], q[32 + jt]);
+                            jn[j], job_stages(jtype[j]), q[40 + 3 * j], q[40 + 3 * j + 1], q[40 + 3 * j + 2], q[32 + j]);
         }
     }
     return 0;
