@@ -260,10 +260,10 @@ def run_config5(args, voc, dims, rank, world, stream, flush, barrier):
         'loop': {'kernel': kernel, 'ms': k_ms, 'us_per_step': 1000 * k_ms / t['steps'], 'folds': t['folds'], 'steps': t['steps'],
                  'ms_cond': t['ms_cond'], 'ms_tail': t['ms_tail'], 'fold_steps_per_s': fold_steps,
                  'fold_steps_per_s_resident_groups_r01': 1.75e6},
-        'dtype': 'bf16 hi+lo split operands (3 MMAs per product), fp32 accumulate in TMEM; fc3 + sampling fp32',
+        'dtype': 'bf16 hi+lo split operands (3 MMAs per product), fp32 accumulate in TMEM, all five layers; gates and the MoL draw fp32',
         'roofline': {'bound': 'tensor', 'achieved': FLOP_PER_FOLD_STEP * fold_steps / 1e12, 'unit': 'TFLOP/s',
                      'algorithmic_flop_per_fold_step': FLOP_PER_FOLD_STEP,
-                     'executed_flop_factor': 'x3 for the hi/lo split, x1.33 for the 96-of-128-row GRU tiles',
+                     'executed_flop_factor': 'x3 for the hi/lo split (the tensor pipe executes three bf16 MMAs per product); no padded rows',
                      'traffic': traffic['dram_bytes_per_launch'] if traffic else None,
                      'traffic_source': (traffic['source'] + ' via ' + traffic['file']) if traffic else
                      'no ncu capture of this kernel under profiles/ at this HEAD'},

@@ -135,7 +135,7 @@ struct Params {
     const float *bias;             // rnn1 [16][2][96] | rnn2 [16][2][96] | fc1 [512] | fc2 [512] | x columns rnn1 [16][96] | rnn2 [16][96] | fc1 [512] | fc3 bias [32]
     uint8_t *H1[2], *H2[2], *S12, *Y1, *Y2;     // activation operands, [fold tile][group][hi|lo][KC][128][8] bf16
     const uint8_t *Cop;            // conditioning operand of every step: [S][fold tile][7 groups][hi|lo][KC][128][8] bf16
-    float *xp;                     // previous sample, [2][NTILES * 128] (double-buffered by step parity)
+    uint2 *xp;                     // previous sample of every fold, tagged: {float bits, step it is the input of}, [NTILES * 128]
     float *h1f, *h2f, *y2f;        // debug only: [NTILES * 128][512] fp32 state / fc2 output
     GridSync gs;
     long long *prof;               // debug (WRNN_MMA_PROF=step): clock64 timeline of that step from CTA 0 and CTA G-1, else null
@@ -254,6 +254,24 @@ __device__ __forceinline__ void tile_wait(const GridSync &gs, int phase, int nt,
         if (give_up(w, t0, spins)) return;
 }
 __device__ __forceinline__ void epi_bar() { bar_sync(1, EPI_THREADS); }
+// The previous sample travels as ONE 8-byte word {value, step}: the reader polls the word itself (one L2 round trip once it
+// is there) instead of a counter followed by the data.  Steps only grow, so the slot needs neither reset nor a second buffer:
+// the sampler of step t writes {x, t + 1} after every reader of {.., t} is through (they all precede its own inputs).
+__device__ __forceinline__ uint2 ld_volatile_u2(const uint2 *p) {
+    uint2 v;
+    asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ float wait_prev_sample(const uint2 *slot, int64_t t, Watch &w) {
+    uint2 v = ld_volatile_u2(slot);
+    if (v.y != (uint32_t)t && !w.dead) {
+        const long long t0 = clock64();
+        unsigned spins = 0;
+        while ((v = ld_volatile_u2(slot)).y != (uint32_t)t)
+            if (give_up(w, t0, spins)) break;
+    }
+    return __uint_as_float(v.x);
+}
 
 // bf16 hi / lo split of four floats, packed: .x/.y = hi pairs, .z/.w = lo pairs
 __device__ __forceinline__ void split4(const float (&v)[4], uint2 &hi, uint2 &lo) {
@@ -286,16 +304,18 @@ __device__ __forceinline__ size_t b_slot(int NT, int NG, int nt, int chunk, int 
 // Same arithmetic as mol_sample_warp (loop_common.cuh; utils/distribution.py:87-123): Gumbel-max over the mixture
 // logits (first index wins a tie), then mean + exp(max(log_scale, -32.236...)) * (log u - log(1 - u)), clamped to [-1, 1].
 constexpr int NMIX = 10;        // MOL: n_classes = 30 = 3 x 10 (fatchord_version.py:103-104)
-__device__ __forceinline__ float mol_sample_thread(const float (&lg)[NCP], const float (&u1)[NMIX], float u2, int *pick) {
+// The noise terms do not depend on the logits: `gum[i]` = log(-log(u1[i])) and `lgt` = log u2 - log(1 - u2) are formed
+// while the fc3 products are still under way (mol_noise_thread), the same values the warp sampler subtracts / multiplies.
+__device__ __forceinline__ float mol_sample_thread(const float (&lg)[NCP], const float (&gum)[NMIX], float lgt, int *pick) {
     float best = -INFINITY, mean = 0.f, ls = 0.f;
     int idx = 0;
 #pragma unroll
     for (int i = 0; i < NMIX; i++) {
-        const float tv = lg[i] - logf(-logf(u1[i]));
+        const float tv = lg[i] - gum[i];
         if (tv > best) { best = tv; idx = i; mean = lg[NMIX + i]; ls = lg[2 * NMIX + i]; }
     }
     ls = fmaxf(ls, -32.23619130191664f);
-    float x = mean + expf(ls) * (logf(u2) - logf(1.f - u2));
+    float x = mean + expf(ls) * lgt;
     x = fminf(fmaxf(x, -1.f), 1.f);
     *pick = idx;
     return x;
@@ -603,26 +623,17 @@ __device__ __forceinline__ void epi_fc(const Params &P, int mt, int nt, uint32_t
     }
 }
 
-// fc3 (:223) + MoL draw (utils/distribution.py:87-123): the 30 logits of a fold are 30 columns of its own TMEM lane.
-// Called by the four warps with half == 0 (one per lane quarter).  Writes the sample, the mixture pick and the previous
-// sample of step t + 1.
-__device__ __forceinline__ void epi_sample(const Params &P, int nt, int64_t t, uint32_t tb, const float *sb, int q, int lane) {
-    const int fi = q * 32 + lane;
-    const int64_t b = (int64_t)nt * FT + fi, S = P.a.S;
-    uint32_t acc[32];
-    tmem_ld32(tb + ((uint32_t)(q * 32) << 16) + (uint32_t)job_acc(J_F3), acc);
-    float *xnext = P.xp + (size_t)((t + 1) & 1) * P.NTILES * FT + b;
-    if (b >= P.a.B) { *xnext = 0.f; return; }            // padded fold of the last tile
-    float lg[NCP];
-#pragma unroll
-    for (int i = 0; i < NCP; i++) lg[i] = __uint_as_float(acc[i]) + sb[SB_B3 + i];
-    const bool live = t < P.a.fold_len[b];
-    if (P.a.logits_out && live) {
-        float *dst = P.a.logits_out + ((size_t)b * S + t) * P.NC;
-#pragma unroll
-        for (int i = 0; i < 3 * NMIX; i++) dst[i] = lg[i];
-    }
+// Noise of (step t, fold of this thread), injected or Philox, reduced to the terms the draw uses.  Off the chain: called
+// before the wait for fc3's accumulator.
+__device__ __forceinline__ void mol_noise_thread(const Params &P, int nt, int64_t t, int q, int lane, float (&gum)[NMIX], float &lgt) {
+    const int64_t b = (int64_t)nt * FT + q * 32 + lane;
     float u1[NMIX], u2;
+    if (b >= P.a.B) {
+#pragma unroll
+        for (int i = 0; i < NMIX; i++) gum[i] = 0.f;
+        lgt = 0.f;
+        return;
+    }
     if (P.a.u1) {
         const float *src = P.a.u1 + ((size_t)t * P.a.Btot + P.a.b0 + b) * NMIX;
 #pragma unroll
@@ -640,8 +651,33 @@ __device__ __forceinline__ void epi_sample(const Params &P, int nt, int64_t t, u
         }
         u2 = u_clip(philox4x32(make_uint4((uint32_t)t, (uint32_t)(P.a.b0 + b), 0u, 2u), key).x);
     }
+#pragma unroll
+    for (int i = 0; i < NMIX; i++) gum[i] = logf(-logf(u1[i]));
+    lgt = logf(u2) - logf(1.f - u2);
+}
+
+// fc3 (:223) + MoL draw (utils/distribution.py:87-123): the 30 logits of a fold are 30 columns of its own TMEM lane.
+// Called by the four warps with half == 0 (one per lane quarter).  Writes the sample, the mixture pick and the previous
+// sample of step t + 1.
+__device__ __forceinline__ void epi_sample(const Params &P, int nt, int64_t t, uint32_t tb, const float *sb, const float (&gum)[NMIX],
+                                           float lgt, int q, int lane) {
+    const int fi = q * 32 + lane;
+    const int64_t b = (int64_t)nt * FT + fi, S = P.a.S;
+    uint32_t acc[32];
+    tmem_ld32(tb + ((uint32_t)(q * 32) << 16) + (uint32_t)job_acc(J_F3), acc);
+    uint2 *xnext = P.xp + b;
+    if (b >= P.a.B) { *xnext = make_uint2(0u, (uint32_t)(t + 1)); return; }            // padded fold of the last tile
+    float lg[NCP];
+#pragma unroll
+    for (int i = 0; i < NCP; i++) lg[i] = __uint_as_float(acc[i]) + sb[SB_B3 + i];
+    const bool live = t < P.a.fold_len[b];
+    if (P.a.logits_out && live) {
+        float *dst = P.a.logits_out + ((size_t)b * S + t) * P.NC;
+#pragma unroll
+        for (int i = 0; i < 3 * NMIX; i++) dst[i] = lg[i];
+    }
     int pick = 0;
-    float xv = mol_sample_thread(lg, u1, u2, &pick);
+    float xv = mol_sample_thread(lg, gum, lgt, &pick);
     if (live) {
         P.a.samples[(size_t)b * S + t] = xv;
         P.a.picks[(size_t)b * S + t] = pick;
@@ -649,7 +685,7 @@ __device__ __forceinline__ void epi_sample(const Params &P, int nt, int64_t t, u
         xv = 0.f;
     }
     if (P.a.teacher) xv = t + 1 < S ? P.a.teacher[(size_t)b * S + t + 1] : 0.f;
-    *xnext = xv;
+    *xnext = make_uint2(__float_as_uint(xv), (uint32_t)(t + 1));
 }
 
 __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
@@ -662,7 +698,6 @@ __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, cta = blockIdx.x;
     const int G = P.G;
-    const int64_t NF = (int64_t)P.NTILES * FT;
     Watch w{P.gs.abort_flag, false, 0};
     // static roles: GRU (row tile, fold tile) jobs fill CTAs from 0 up, fc jobs from G - 1 down; at most one of each per CTA;
     // the fc CTA of row tile 0 also runs the tile's fc3 job and its sampler
@@ -833,14 +868,11 @@ __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
             if (w.dead) break;                               // uniform: set below from a flag read after a barrier
             if (has_gru) {
                 wait_acc(TF_R1);
-                if (etid == 0) {
-                    PROF_MARK(20);
-                    w.site = 0x60;
-                    tile_wait(P.gs, PH_SAMPLE, nt_g, t, w);      // the sample of step t - 1 is out
-                }
-                epi_bar();
+                if (etid == 0) PROF_MARK(20);
+                w.site = 0x60;
+                const float xp = wait_prev_sample(P.xp + (size_t)nt_g * FT + fi, t, w);      // the sample of step t - 1 is out
                 if (etid == 0) PROF_MARK(21);
-                const float xp = __ldcg(P.xp + (size_t)(t & 1) * NF + (size_t)nt_g * FT + fi);
+                __syncwarp();
                 epi_gru<0>(P, mt_g, nt_g, t, tb, sbias, xp, hst1, h1new, q, half, lane);
                 tc_fence_before();
                 if (etid == 0) PROF_MARK(22);
@@ -858,7 +890,7 @@ __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
                 wait_acc(TF_F1);
                 if (etid == 0) PROF_MARK(27);
                 // published before rnn1 of this step began; the loads that filled fc1's stages were ordered behind rnn2's counter
-                const float xp = __ldcg(P.xp + (size_t)(t & 1) * NF + (size_t)nt_f * FT + fi);
+                const float xp = __uint_as_float(ld_volatile_u2(P.xp + (size_t)nt_f * FT + fi).x);
                 epi_fc<0>(P, mt_f, nt_f, tb, sbias, xp, q, half, lane);
                 tc_fence_before();
                 publish(PH_FC1, nt_f);
@@ -870,9 +902,11 @@ __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
                 publish(PH_FC2, nt_f);
                 if (etid == 0) PROF_MARK(30);
                 if (has_f3) {
+                    float gum[NMIX], lgt = 0.f;
+                    if (half == 0) mol_noise_thread(P, nt_f, t, q, lane, gum, lgt);
                     wait_acc(TF_F3);
                     if (etid == 0) PROF_MARK(16);
-                    if (half == 0) epi_sample(P, nt_f, t, tb, sbias, q, lane);
+                    if (half == 0) epi_sample(P, nt_f, t, tb, sbias, gum, lgt, q, lane);
                     tc_fence_before();
                     if (etid == 0) PROF_MARK(17);
                     __threadfence();
@@ -922,7 +956,7 @@ bool mma_supported(const wrnn_handle *h) {
     return h->mma.ok && d.mode == WRNN_MODE_MOL && d.H == mma::H && d.FC == mma::FCD && d.A == mma::AUX && d.F == mma::FEAT &&
            d.NC == 3 * mma::NMIX;
 }
-int mma_min_folds() { return 48; }
+int mma_min_folds() { return 61; }      // measured (scripts/mma_crossover.py): 36.4 us per step whatever the fold count; three resident groups of 20 take 35.7
 
 int mma_plan(wrnn_handle *h) {
     using namespace mma;
@@ -1059,9 +1093,9 @@ int mma_plan(wrnn_handle *h) {
 int64_t mma_max_folds(const wrnn_handle *h) { return (int64_t)128 * (h->num_sms / mma::MT_GRU); }
 
 // initial previous sample: 0, or the teacher's first sample (fatchord_version.py:197, forward(): x[:, 0])
-__global__ void xp_init_kernel(float *xp, const float *teacher, int64_t B, int64_t S, int64_t NF) {
+__global__ void xp_init_kernel(uint2 *xp, const float *teacher, int64_t B, int64_t S, int64_t NF) {
     const int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (b < 2 * NF) xp[b] = (b < B && teacher) ? teacher[(size_t)b * S] : 0.f;
+    if (b < NF) xp[b] = make_uint2(__float_as_uint((b < B && teacher) ? teacher[(size_t)b * S] : 0.f), 0u);
 }
 
 int mma_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
@@ -1087,7 +1121,7 @@ int mma_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
     P.bias = pl.bias;
     const size_t NF = (size_t)P.NTILES * FT;
     const size_t bH = NF * H * 4, bF = NF * H * sizeof(float);       // operands: hi + lo bf16 = 4 B per element
-    const size_t bX = (2 * NF * sizeof(float) + 1023) / 1024 * 1024;
+    const size_t bX = (NF * sizeof(uint2) + 1023) / 1024 * 1024;
     const size_t bC = (size_t)a.S * P.NTILES * CGROUPS * ACT_STAGE;  // conditioning operand of every step
     const size_t state = 7 * bH + bX + 3 * bF;
     WRNN_TRY(ws_reserve(h, h->ws_act, state + bC + 4096));
@@ -1096,7 +1130,7 @@ int mma_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
     P.H1[0] = p8; p8 += bH; P.H1[1] = p8; p8 += bH;
     P.H2[0] = p8; p8 += bH; P.H2[1] = p8; p8 += bH;
     P.S12 = p8; p8 += bH; P.Y1 = p8; p8 += bH; P.Y2 = p8; p8 += bH;
-    P.xp = (float *)p8; p8 += bX;
+    P.xp = (uint2 *)p8; p8 += bX;
     P.h1f = (float *)p8; p8 += bF; P.h2f = (float *)p8; p8 += bF; P.y2f = (float *)p8; p8 += bF;
     uint8_t *Cop = p8;
     P.Cop = Cop;
@@ -1104,7 +1138,7 @@ int mma_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
     {       // pre-pass: the conditioning operand of all steps, and the first previous sample
         const int64_t warps = a.S * (int64_t)NF;
         cond_operand_kernel<<<(unsigned)((warps + 7) / 8), 256, 0, st>>>(a.cond, a.B, a.S, P.NTILES, Cop);
-        xp_init_kernel<<<(unsigned)((2 * NF + 255) / 256), 256, 0, st>>>(P.xp, a.teacher, a.B, a.S, (int64_t)NF);
+        xp_init_kernel<<<(unsigned)((NF + 255) / 256), 256, 0, st>>>(P.xp, a.teacher, a.B, a.S, (int64_t)NF);
         WRNN_CUDA(h, cudaGetLastError());
         h->launches += 2;
     }
