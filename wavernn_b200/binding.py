@@ -276,6 +276,12 @@ class Vocoder:
     def set_mma_fold_tile(self, nt):
         self._ck(lib().wrnn_set_mma_fold_tile(self._h, int(nt)))
 
+    def prune_at_step(self, t, start_prune, prune_steps, target_sparsity, want_masked=False):
+        """16x1 block-prune the loaded GRU matrices to the sparsity the reference's schedule asks for at training step t
+        (`notebooks/Pruning - Scratchpad.ipynb:127-131`; wavernn_b200/prune.py drives it during training)."""
+        from .prune import sparsity_at
+        return self.prune_16x1(1.0 - sparsity_at(t, start_prune, prune_steps, target_sparsity), want_masked=want_masked)
+
     def prune_16x1(self, keep_fraction, want_masked=False):
         d = self.dims
         H, A = d.rnn_dims, d.aux_dims
