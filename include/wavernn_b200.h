@@ -82,6 +82,21 @@ int wrnn_load_weights(wrnn_handle *h, const wrnn_tensor *tensors, int32_t n);
  * dense matrices concatenated in the order rnn1.ih, rnn1.hh, rnn2.ih, rnn2.hh. */
 int wrnn_prune_16x1(wrnn_handle *h, float keep_fraction, float *masked_out);
 
+/* melspectrogram(y) of utils/dsp.py:72-75, the input branch of gen_wavernn.py:44-47 for a .wav file: librosa 0.6.3's
+ * stft (centre, reflect padding, periodic Hann window of win_length inside an n_fft frame), |D| through the Slaney
+ * area-normalised mel basis (librosa.filters.mel(sr, n_fft, n_mels, fmin)), 20 log10(max(1e-5, .)), then
+ * clip((S - min_level_db) / -min_level_db, 0, 1).  hparams.py:20-27 gives the reference's values
+ * {22050, 2048, 275, 1100, 80, 40.0, -100.0}.
+ * wav: n host floats in [-1, 1].  mel_out: [num_mels][frames] host floats, frames = 1 + n / hop_length, written when
+ * frames_cap >= frames; mel_out == NULL only returns *frames_out.  Direct DFT in double on the GPU: within 1e-4 of the
+ * float64 statement of the same pipeline (oracle/melspec.py) on the normalised scale. */
+typedef struct {
+    int32_t sample_rate, n_fft, hop_length, win_length, num_mels;
+    float fmin, min_level_db;
+} wrnn_mel_params;
+int wrnn_melspectrogram(wrnn_handle *h, const float *wav, int64_t n, const wrnn_mel_params *mp, float *mel_out,
+                        int64_t frames_cap, int64_t *frames_out, void *cuda_stream);
+
 /* ------------------------------------------------------------------ the path
  * wrnn_generate == WaveRNN.generate for `n_utt` independent utterances (the reference takes one;
  * fatchord_version.py:169-264).  mels[u] is (feat_dims, T[u]) row-major float32.  out[u] must hold

@@ -34,6 +34,11 @@ class wrnn_noise(C.Structure):
                 ('folds', C.c_int64)]
 
 
+class MelParams(C.Structure):          # wrnn_mel_params
+    _fields_ = [('sample_rate', C.c_int32), ('n_fft', C.c_int32), ('hop_length', C.c_int32), ('win_length', C.c_int32),
+                ('num_mels', C.c_int32), ('fmin', C.c_float), ('min_level_db', C.c_float)]
+
+
 _P = C.c_void_p
 _SIGS = {
     'wrnn_create': (C.c_int, [C.POINTER(wrnn_config), C.c_int, C.POINTER(_P)]),
@@ -41,6 +46,7 @@ _SIGS = {
     'wrnn_last_error': (C.c_char_p, [_P]),
     'wrnn_load_weights': (C.c_int, [_P, C.POINTER(wrnn_tensor), C.c_int32]),
     'wrnn_prune_16x1': (C.c_int, [_P, C.c_float, _P]),
+    'wrnn_melspectrogram': (C.c_int, [_P, _P, C.c_int64, _P, _P, C.c_int64, _P, _P]),
     'wrnn_generate': (C.c_int, [_P, C.POINTER(_P), C.POINTER(C.c_int32), C.c_int32, C.c_int32, C.c_int32,
                                 C.c_int32, C.c_int32, C.POINTER(wrnn_noise), C.c_uint64, C.POINTER(_P),
                                 C.POINTER(C.c_int64), _P]),
@@ -275,6 +281,17 @@ class Vocoder:
 
     def set_mma_fold_tile(self, nt):
         self._ck(lib().wrnn_set_mma_fold_tile(self._h, int(nt)))
+
+    def melspectrogram(self, wav, sample_rate=22050, n_fft=2048, hop_length=275, win_length=1100, num_mels=80, fmin=40.0,
+                       min_level_db=-100.0, stream=None):
+        """`melspectrogram(y)` of utils/dsp.py:72-75 on the GPU: float32 [num_mels][1 + len(wav) // hop_length]."""
+        wav = np.ascontiguousarray(wav, dtype=np.float32).reshape(-1)
+        mp = MelParams(int(sample_rate), int(n_fft), int(hop_length), int(win_length), int(num_mels), float(fmin), float(min_level_db))
+        frames = C.c_int64(0)
+        self._ck(lib().wrnn_melspectrogram(self._h, _ptr(wav), wav.size, C.byref(mp), None, 0, C.byref(frames), stream))
+        out = np.empty((int(num_mels), frames.value), dtype=np.float32)
+        self._ck(lib().wrnn_melspectrogram(self._h, _ptr(wav), wav.size, C.byref(mp), _ptr(out), frames.value, C.byref(frames), stream))
+        return out
 
     def prune_at_step(self, t, start_prune, prune_steps, target_sparsity, want_masked=False):
         """16x1 block-prune the loaded GRU matrices to the sparsity the reference's schedule asks for at training step t

@@ -140,7 +140,7 @@ void wrnn_destroy(wrnn_handle *h) {
     DeviceGuard guard(h->device);
     Workspace *all[] = {&h->ws_mel, &h->ws_up, &h->ws_res, &h->ws_cond, &h->ws_samples, &h->ws_picks, &h->ws_out,
                         &h->ws_noise, &h->ws_meta, &h->ws_tables, &h->ws_sync, &h->ws_mma_sync, &h->ws_act, &h->ws_tmp0, &h->ws_tmp1,
-                        &h->ws_teacher, &h->ws_logits, &h->ws_prof};
+                        &h->ws_teacher, &h->ws_logits, &h->ws_prof, &h->mel_tab};
     for (Workspace *w : all)
         if (w->p) cudaFree(w->p);
     float *ptrs[] = {h->cp.poly, h->cp.conv_in_t, h->cp.bn_scale, h->cp.bn_shift, h->cp.res_t, h->cp.conv_out_t, h->cp.conv_out_b,

@@ -130,7 +130,8 @@ struct wrnn_handle {
     bool have_noise = false;
 
     wrnn::Workspace ws_mel, ws_up, ws_res, ws_cond, ws_samples, ws_picks, ws_out, ws_noise,
-        ws_meta, ws_tables, ws_sync, ws_mma_sync, ws_act, ws_tmp0, ws_tmp1, ws_teacher, ws_logits, ws_prof;
+        ws_meta, ws_tables, ws_sync, ws_mma_sync, ws_act, ws_tmp0, ws_tmp1, ws_teacher, ws_logits, ws_prof, mel_tab;
+    wrnn_mel_params mel_tab_params = {0, 0, 0, 0, 0, 0.f, 0.f};     // what mel_tab (window, roots of unity, mel basis) was built for
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
     int64_t launches = 0;
     double *h_pinned_out = nullptr;
