@@ -82,6 +82,18 @@ int wrnn_load_weights(wrnn_handle *h, const wrnn_tensor *tensors, int32_t n);
  * dense matrices concatenated in the order rnn1.ih, rnn1.hh, rnn2.ih, rnn2.hh. */
 int wrnn_prune_16x1(wrnn_handle *h, float keep_fraction, float *masked_out);
 
+/* Chunked delivery of one batched utterance (the reference returns only when the last sample
+ * is drawn, fatchord_version.py:241-264).  Folds run in groups of `chunk_folds` (0 = 20, the resident kernel's group);
+ * after each group the samples that no later fold touches, [done so far, folds_done * (target + overlap)), get their
+ * cross-fade (and in the last chunk the fade-out), go to the host and are handed to `on_chunk` in time order while the
+ * next groups run.  `samples` points into library-owned pinned memory, valid until the next call on the handle.
+ * `out` (may be NULL) receives the whole waveform as wrnn_generate would write it: the chunks concatenated are equal to
+ * it bit for bit.  Returns after the last chunk. */
+typedef void (*wrnn_chunk_fn)(void *user, int64_t first_sample, const double *samples, int64_t n, int32_t last);
+int wrnn_generate_stream(wrnn_handle *h, const float *mel, int32_t T, int32_t target, int32_t overlap, int32_t mu_law,
+                         const wrnn_noise *noise, uint64_t seed, int32_t chunk_folds, wrnn_chunk_fn on_chunk, void *user,
+                         double *out, int64_t *out_len, void *cuda_stream);
+
 /* melspectrogram(y) of utils/dsp.py:72-75, the input branch of gen_wavernn.py:44-47 for a .wav file: librosa 0.6.3's
  * stft (centre, reflect padding, periodic Hann window of win_length inside an n_fft frame), |D| through the Slaney
  * area-normalised mel basis (librosa.filters.mel(sr, n_fft, n_mels, fmin)), 20 log10(max(1e-5, .)), then

@@ -40,12 +40,14 @@ class MelParams(C.Structure):          # wrnn_mel_params
 
 
 _P = C.c_void_p
+CHUNK_FN = C.CFUNCTYPE(None, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int32)      # wrnn_chunk_fn
 _SIGS = {
     'wrnn_create': (C.c_int, [C.POINTER(wrnn_config), C.c_int, C.POINTER(_P)]),
     'wrnn_destroy': (None, [_P]),
     'wrnn_last_error': (C.c_char_p, [_P]),
     'wrnn_load_weights': (C.c_int, [_P, C.POINTER(wrnn_tensor), C.c_int32]),
     'wrnn_prune_16x1': (C.c_int, [_P, C.c_float, _P]),
+    'wrnn_generate_stream': (C.c_int, [_P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _P, C.c_uint64, C.c_int32, _P, _P, _P, _P, _P]),
     'wrnn_melspectrogram': (C.c_int, [_P, _P, C.c_int64, _P, _P, C.c_int64, _P, _P]),
     'wrnn_generate': (C.c_int, [_P, C.POINTER(_P), C.POINTER(C.c_int32), C.c_int32, C.c_int32, C.c_int32,
                                 C.c_int32, C.c_int32, C.POINTER(wrnn_noise), C.c_uint64, C.POINTER(_P),
@@ -232,6 +234,32 @@ class Vocoder:
         self._ck(lib().wrnn_generate(self._h, ptrs, Ts, len(mels), int(bool(batched)), int(target), int(overlap),
                                      int(bool(mu_law)), nz, int(seed), optrs, lens, stream))
         return outs
+
+    def generate_stream(self, mel, target, overlap, mu_law, on_chunk=None, chunk_folds=0, noise=None, seed=0, stream=None):
+        """One batched utterance, delivered in time order as fold groups finish (wrnn_generate_stream).
+
+        on_chunk(first_sample, samples (float64 copy), last) is called from this thread while later groups are still
+        running on the GPU.  Returns the whole float64 waveform (equal to `generate`)."""
+        mels, ptrs, Ts = self._mel_args([mel])
+        out = np.empty(max((mels[0].shape[1] - 1) * self.dims.hop_length, 0), dtype=np.float64)
+        n_out = C.c_int64(0)
+        nz, keep = self._noise(noise)
+        errors = []
+
+        def trampoline(user, first, ptr, n, last):
+            if on_chunk is None or errors:
+                return
+            try:
+                on_chunk(int(first), np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_double)), shape=(int(n),)).copy(), bool(last))
+            except BaseException as e:      # noqa: BLE001  (must not unwind through the C frame)
+                errors.append(e)
+
+        cb = CHUNK_FN(trampoline)
+        self._ck(lib().wrnn_generate_stream(self._h, _ptr(mels[0]), int(Ts[0]), int(target), int(overlap), int(bool(mu_law)), nz,
+                                            int(seed), int(chunk_folds), cb, None, _ptr(out), C.byref(n_out), stream))
+        if errors:
+            raise errors[0]
+        return out
 
     def stage(self, mels, batched, target, overlap, mu_law, noise=None, stream=None):
         mels, ptrs, Ts = self._mel_args(mels)

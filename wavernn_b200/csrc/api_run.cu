@@ -13,6 +13,11 @@ struct StageOpts {
     bool prepadded = false;        // mels already carry `pad` frames on both sides (forward_logits)
     const float *teacher = nullptr;   // host [B][S]
     bool want_logits = false;
+    // chunked delivery (wrnn_generate_stream): fold groups of at most `chunk_folds`; after each group the part of the
+    // waveform that is final goes to the host and `chunk_events` / `chunk_end` say when and how far
+    int64_t chunk_folds = 0;
+    std::vector<cudaEvent_t> *chunk_events = nullptr;
+    std::vector<int64_t> *chunk_end = nullptr;
 };
 
 static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
@@ -259,12 +264,16 @@ int do_run(wrnn_handle *h, uint64_t seed, cudaStream_t st, const StageOpts &o) {
     const bool fresh_sync = h->ws_sync.p == nullptr;
     WRNN_TRY(ws_reserve(h, h->ws_sync, 128));
     WRNN_CUDA(h, cudaMemsetAsync(h->ws_sync.p, 0, fresh_sync ? 128 : 64, st));
-    const int kernel = loop_kernel_choice(h, h->B);
-    if (kernel != 1) {
+    const bool chunked = o.chunk_folds > 0;
+    const int kernel = loop_kernel_choice(h, chunked ? std::min<int64_t>(h->B, o.chunk_folds) : h->B);
+    const double *tab = (const double *)h->ws_tables.p;
+    if (kernel != 1 || chunked) {
         // these kernels take fold groups of <= 20 (folds are independent: any grouping is exact)
         // (the tensor-core kernel takes up to 1 152 folds per launch: one (row tile, fold tile) job per CTA)
-        const int64_t cap = kernel == 4 ? mma_max_folds(h) : kernel == 3 ? res_max_folds() : pipe_max_folds(),
-                      ng = (h->B + cap - 1) / cap, per = (h->B + ng - 1) / ng;
+        const int64_t cap0 = kernel == 4 ? mma_max_folds(h) : kernel == 3 ? res_max_folds() : kernel == 2 ? pipe_max_folds() : h->B,
+                      cap = chunked ? std::min(cap0, o.chunk_folds) : cap0, ng = (h->B + cap - 1) / cap,
+                      per = chunked ? cap : (h->B + ng - 1) / ng;
+        int64_t delivered = 0;          // samples of the waveform already final and on their way to the host
         const size_t CW = (size_t)(d.F + d.R);
         for (int64_t b0 = 0; b0 < h->B; b0 += per) {
             LoopArgs g = a;
@@ -276,17 +285,37 @@ int do_run(wrnn_handle *h, uint64_t seed, cudaStream_t st, const StageOpts &o) {
             g.picks = a.picks + (size_t)b0 * h->S;
             if (a.teacher) g.teacher = a.teacher + (size_t)b0 * h->S;
             if (a.logits_out) g.logits_out = a.logits_out + (size_t)b0 * h->S * d.NC;
-            WRNN_TRY(kernel == 4 ? mma_run(h, g, st) : kernel == 3 ? res_run(h, g, st) : pipe_run(h, g, st));
+            WRNN_TRY(kernel == 4 ? mma_run(h, g, st) : kernel == 3 ? res_run(h, g, st) : kernel == 2 ? pipe_run(h, g, st) : fma_run(h, g, st));
+            if (chunked) {
+                // fatchord_version.py:374-405 adds at most fold b - 1 and fold b into sample i, b = i / (target + overlap):
+                // with folds [0, done) through, everything below done * (target + overlap) is final (the fade-out of the
+                // last 20 hops, :255-258, lies in the last chunk)
+                const auto &ut = h->utts[0];
+                const int64_t done = b0 + g.B, stride = h->target + h->overlap;
+                const int64_t end = done >= h->B ? ut.wave_len : std::min<int64_t>(done * stride, ut.wave_len);
+                if (end > delivered) {
+                    WRNN_TRY(launch_tail(h, a.samples, a.picks, (const TailMeta *)((char *)h->ws_meta.p + ml.off_tail), 1, end, h->S,
+                                         h->batched, h->target, h->overlap, tab + tl.fin, tab + tl.fout, tab + tl.fo,
+                                         20 * (int64_t)d.hop, h->mu_law ? tab + tl.lut : nullptr, (double *)h->ws_out.p, st, delivered));
+                    WRNN_CUDA(h, cudaMemcpyAsync(h->h_pinned_out + delivered, (double *)h->ws_out.p + delivered,
+                                                 (size_t)(end - delivered) * sizeof(double), cudaMemcpyDeviceToHost, st));
+                }
+                cudaEvent_t ev;
+                WRNN_CUDA(h, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+                WRNN_CUDA(h, cudaEventRecord(ev, st));
+                o.chunk_events->push_back(ev);
+                o.chunk_end->push_back(end);
+                delivered = end;
+            }
         }
     } else {
         WRNN_TRY(fma_run(h, a, st));
     }
     WRNN_CUDA(h, cudaEventRecord(h->ev[2], st));
     // float64 tail (:243-258)
-    if (!o.want_logits && h->Btot == h->B) {      // under a fold range the float64 tail belongs to whoever gathers the shards
+    if (!o.want_logits && h->Btot == h->B && !chunked) {      // under a fold range the float64 tail belongs to whoever gathers the shards
         int64_t max_wave = 0;
         for (auto &ut : h->utts) max_wave = std::max(max_wave, ut.wave_len);
-        const double *tab = (const double *)h->ws_tables.p;
         WRNN_TRY(launch_tail(h, a.samples, a.picks, (const TailMeta *)((char *)h->ws_meta.p + ml.off_tail), n_utt,
                              max_wave, h->S, h->batched, h->target, h->overlap, tab + tl.fin, tab + tl.fout,
                              tab + tl.fo, 20 * (int64_t)d.hop, h->mu_law ? tab + tl.lut : nullptr,
@@ -349,6 +378,48 @@ int wrnn_fetch(wrnn_handle *h, double *const *out, int64_t *out_len, void *cuda_
         memcpy(out[u], h->h_pinned_out + ut.out_off, (size_t)ut.wave_len * sizeof(double));
         if (out_len) out_len[u] = ut.wave_len;
     }
+    return 0;
+}
+
+int wrnn_generate_stream(wrnn_handle *h, const float *mel, int32_t T, int32_t target, int32_t overlap, int32_t mu_law,
+                         const wrnn_noise *noise, uint64_t seed, int32_t chunk_folds, wrnn_chunk_fn on_chunk, void *user,
+                         double *out, int64_t *out_len, void *cuda_stream) {
+    if (!h || !mel || chunk_folds < 0) return fail(h, WRNN_ERR_ARG, "bad argument");
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    const float *mels[1] = {mel};
+    WRNN_TRY(do_stage(h, mels, &T, 1, 1, target, overlap, mu_law, noise, st, StageOpts()));
+    if (h->Btot != h->B) return fail(h, WRNN_ERR_STATE, "a fold range is staged: streaming delivers a whole utterance");
+    WRNN_DEVICE(h);
+    const size_t bytes = (size_t)h->total_out * sizeof(double);
+    if (h->h_pinned_out_bytes < bytes) {
+        if (h->h_pinned_out) cudaFreeHost(h->h_pinned_out);
+        h->h_pinned_out = nullptr;
+        WRNN_CUDA(h, cudaMallocHost((void **)&h->h_pinned_out, bytes + bytes / 4 + 64));
+        h->h_pinned_out_bytes = bytes + bytes / 4 + 64;
+    }
+    std::vector<cudaEvent_t> events;
+    std::vector<int64_t> ends;
+    StageOpts o;
+    o.chunk_folds = chunk_folds > 0 ? chunk_folds : res_max_folds();
+    o.chunk_events = &events;
+    o.chunk_end = &ends;
+    int rc = do_run(h, seed, st, o);          // enqueues every group, its tail and its copy; returns at once
+    int64_t from = 0;
+    for (size_t c = 0; c < events.size(); c++) {
+        if (rc == 0) {
+            const cudaError_t e = cudaEventSynchronize(events[c]);
+            if (e != cudaSuccess) rc = fail(h, WRNN_ERR_CUDA, "wrnn_generate_stream: %s", cudaGetErrorString(e));
+        }
+        if (rc == 0 && ends[c] > from) {
+            if (out) memcpy(out + from, h->h_pinned_out + from, (size_t)(ends[c] - from) * sizeof(double));
+            if (on_chunk) on_chunk(user, from, h->h_pinned_out + from, ends[c] - from, c + 1 == events.size());
+            from = ends[c];
+        }
+        cudaEventDestroy(events[c]);
+    }
+    if (rc) return rc;
+    WRNN_TRY(check_abort(h, st));
+    if (out_len) *out_len = h->utts[0].wave_len;
     return 0;
 }
 

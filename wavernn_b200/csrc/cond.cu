@@ -439,10 +439,10 @@ __global__ void tail_kernel(const float *__restrict__ samples, const int32_t *__
                             const TailMeta *__restrict__ meta, int64_t S, int batched, int64_t target,
                             int64_t overlap, const double *__restrict__ fade_in,
                             const double *__restrict__ fade_out, const double *__restrict__ fo, int64_t fo_len,
-                            const double *__restrict__ lut, double *__restrict__ out) {
+                            const double *__restrict__ lut, double *__restrict__ out, int64_t i0, int64_t i1) {
     const TailMeta m = meta[blockIdx.y];
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= m.wave_len) return;
+    const int64_t i = i0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;       // [i0, i1): all of it, or one streamed chunk
+    if (i >= m.wave_len || i >= i1) return;
     auto val = [&](int64_t b, int64_t pos) -> double {
         const size_t idx = (size_t)(m.fold0 + b) * S + pos;
         return lut ? lut[picks[idx]] : (double)samples[idx];
@@ -466,10 +466,11 @@ __global__ void tail_kernel(const float *__restrict__ samples, const int32_t *__
 int launch_tail(wrnn_handle *h, const float *samples, const int32_t *picks, const TailMeta *meta, int n_utt,
                 int64_t max_wave, int64_t S, int batched, int64_t target, int64_t overlap, const double *fade_in,
                 const double *fade_out, const double *fo, int64_t fo_len, const double *lut, double *out,
-                cudaStream_t st) {
-    dim3 grid((unsigned)((max_wave + 255) / 256), n_utt);
+                cudaStream_t st, int64_t first) {
+    // samples [first, max_wave) of every utterance (first > 0: a streamed chunk of one utterance)
+    dim3 grid((unsigned)((max_wave - first + 255) / 256), n_utt);
     tail_kernel<<<grid, 256, 0, st>>>(samples, picks, meta, S, batched, target, overlap, fade_in, fade_out, fo,
-                                      fo_len, lut, out);
+                                      fo_len, lut, out, first, max_wave);
     h->launches++;
     WRNN_CUDA(h, cudaGetLastError());
     return 0;

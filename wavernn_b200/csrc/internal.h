@@ -205,7 +205,7 @@ struct TailMeta { int64_t fold0, nfolds, wave_len, out_off; };   // per utteranc
 int launch_tail(wrnn_handle *h, const float *samples, const int32_t *picks, const TailMeta *meta,
                 int n_utt, int64_t max_wave, int64_t S, int batched, int64_t target, int64_t overlap,
                 const double *fade_in, const double *fade_out, const double *fo, int64_t fo_len,
-                const double *lut, double *out, cudaStream_t st);
+                const double *lut, double *out, cudaStream_t st, int64_t first = 0);
 int launch_unfold(wrnn_handle *h, const double *y, int64_t folds, int64_t target, int64_t overlap,
                   const double *fade_in, const double *fade_out, double *out, cudaStream_t st);
 int launch_mulaw(wrnn_handle *h, const float *y, int64_t n, int mu, const double *lut, double *out,
