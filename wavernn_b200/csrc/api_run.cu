@@ -204,7 +204,6 @@ int do_stage(wrnn_handle *h, const float *const *mels, const int32_t *T, int32_t
     }
     // ---- device workspaces for run ----
     WRNN_TRY(ws_reserve(h, h->ws_res, (size_t)res_off * d.R * sizeof(float)));
-    WRNN_TRY(ws_reserve(h, h->ws_cond, (size_t)h->B * h->S * (d.F + d.R) * sizeof(float)));
     WRNN_TRY(ws_reserve(h, h->ws_samples, (size_t)h->B * h->S * sizeof(float)));
     WRNN_TRY(ws_reserve(h, h->ws_picks, (size_t)h->B * h->S * sizeof(int32_t)));
     WRNN_TRY(ws_reserve(h, h->ws_out, (size_t)std::max<int64_t>(h->total_out, 1) * sizeof(double)));
@@ -233,12 +232,20 @@ int do_run(wrnn_handle *h, uint64_t seed, cudaStream_t st, const StageOpts &o) {
     WRNN_TRY(launch_pad_mel_batch(h, mel_raw, d_utt, n_utt, h->total_frames, melT, st));
     WRNN_TRY(launch_resnet_batch(h, melT, d_utt, (const ResTile *)((char *)h->ws_meta.p + ml.off_tile), (int)n_tiles,
                                  (float *)h->ws_res.p, st));
-    WRNN_TRY(launch_fold_cond(h, melT, (const float *)h->ws_res.p, (const FoldMeta *)((char *)h->ws_meta.p + ml.off_fold), h->B,
-                              h->S, (float *)h->ws_cond.p, st));
+    const bool chunked = o.chunk_folds > 0;
+    const int kernel = loop_kernel_choice(h, chunked ? std::min<int64_t>(h->B, o.chunk_folds) : h->B);
+    const FoldMeta *d_fold = (const FoldMeta *)((char *)h->ws_meta.p + ml.off_fold);
+    if (kernel != 4) {      // the tensor-core kernel lays the features out as its own MMA operand (loop_mma.cu): no fp32 fold batch
+        WRNN_TRY(ws_reserve(h, h->ws_cond, (size_t)h->B * h->S * (d.F + d.R) * sizeof(float)));
+        WRNN_TRY(launch_fold_cond(h, melT, (const float *)h->ws_res.p, d_fold, h->B, h->S, (float *)h->ws_cond.p, st));
+    }
     WRNN_CUDA(h, cudaEventRecord(h->ev[1], st));
     // per-sample loop (:201-241)
     LoopArgs a;
-    a.cond = (const float *)h->ws_cond.p;
+    a.cond = kernel != 4 ? (const float *)h->ws_cond.p : nullptr;
+    a.melT = melT;
+    a.res_out = (const float *)h->ws_res.p;
+    a.fold_meta = d_fold;
     a.B = h->B;
     a.S = h->S;
     a.fold_len = (const int32_t *)((char *)h->ws_meta.p + ml.off_len);
@@ -264,8 +271,6 @@ int do_run(wrnn_handle *h, uint64_t seed, cudaStream_t st, const StageOpts &o) {
     const bool fresh_sync = h->ws_sync.p == nullptr;
     WRNN_TRY(ws_reserve(h, h->ws_sync, 128));
     WRNN_CUDA(h, cudaMemsetAsync(h->ws_sync.p, 0, fresh_sync ? 128 : 64, st));
-    const bool chunked = o.chunk_folds > 0;
-    const int kernel = loop_kernel_choice(h, chunked ? std::min<int64_t>(h->B, o.chunk_folds) : h->B);
     const double *tab = (const double *)h->ws_tables.p;
     if (kernel != 1 || chunked) {
         // these kernels take fold groups of <= 20 (folds are independent: any grouping is exact)
@@ -279,7 +284,8 @@ int do_run(wrnn_handle *h, uint64_t seed, cudaStream_t st, const StageOpts &o) {
             LoopArgs g = a;
             g.B = std::min<int64_t>(per, h->B - b0);
             g.b0 = h->fold_lo + b0;
-            g.cond = a.cond + (size_t)b0 * h->S * CW;
+            g.cond = a.cond ? a.cond + (size_t)b0 * h->S * CW : nullptr;
+            g.fold_meta = d_fold + b0;
             g.fold_len = a.fold_len + b0;
             g.samples = a.samples + (size_t)b0 * h->S;
             g.picks = a.picks + (size_t)b0 * h->S;

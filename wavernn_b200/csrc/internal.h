@@ -79,7 +79,9 @@ struct MmaPlan {
 };
 
 struct LoopArgs {
-    const float *cond;         // [B][S][F+R]
+    const float *cond;         // [B][S][F+R]; null for the tensor-core kernel, which forms its own operand from:
+    const float *melT = nullptr, *res_out = nullptr;     // padded frames [.][F] and MelResNet rows [.][R] of the call
+    const void *fold_meta = nullptr;                     // FoldMeta[B] (device) of the folds of this launch
     int64_t B, S;
     int64_t Btot, b0;          // fold count of the whole call and this launch's first fold (noise / Philox addressing)
     const int32_t *fold_len;   // [B] steps valid per fold (== S when batched)

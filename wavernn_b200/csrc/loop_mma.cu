@@ -70,10 +70,11 @@ constexpr int SBIAS = SB_B3 + NCP;
 constexpr int TMEM_COLS = 512;
 constexpr int FIXED_SMEM = SBIAS * 4;
 // conditioning operand element order (which features each layer concatenates):
-//   [a4 (32) | a2 (32) | x_prev slot, zero (1) | m (80) | a1 (32) | a3 (32) | zero (47)]
+//   [a4 (32) | a2 (32) | m (80) | a1 (32) | a3 (32) | zero (48)]
 // in groups of 64: rnn1 reads groups 1..2, rnn2 0..2, fc1 1..3, fc2 group 0 (weights of the features a layer does not
-// read are zero).
-constexpr int C_A4 = 0, C_A2 = 32, C_X = 64, C_M = 65, C_A1 = 145, C_A3 = 177, C_END = 209;
+// read are zero); every 8-element chunk is 8 consecutive features of one source.  The previous sample has no slot: it
+// enters in the epilogues.
+constexpr int C_A4 = 0, C_A2 = 32, C_M = 64, C_A1 = 144, C_A3 = 176, C_END = 208;
 
 // Job types.  A job = one MMA chain of (row tile, fold tile) into one TMEM accumulator.
 //   ..A ("ahead"): the conditioning columns of a layer for step t + 1, issued during step t (start the accumulator);
@@ -322,49 +323,58 @@ __device__ __forceinline__ float mol_sample_thread(const float (&lg)[NCP], const
 }
 
 // ---------------------------------------------------------------------------- conditioning operand, all steps (pre-pass)
-// [B][S][80 mel + 4 x 32 aux] fp32 rows (fold_cond_kernel's output) -> the MMA operand image of every step: element
-// order of C_*, bf16 hi / lo.  One warp per (step, fold); folds of the padded last tile are written as zeros.
-__global__ void __launch_bounds__(256) cond_operand_kernel(const float *__restrict__ cond, int64_t B, int64_t S, int ntiles,
-                                                           uint8_t *__restrict__ Cop) {
-    __shared__ float scr_all[8][FEAT + 4 * AUX];
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int64_t NF = (int64_t)ntiles * FT, idx = (int64_t)blockIdx.x * 8 + warp;
-    if (idx >= S * NF) return;
-    const int64_t t = idx / NF, b = idx - t * NF;
-    const int RW = FEAT + 4 * AUX;
-    float *scr = scr_all[warp];
-    if (b < B) {
-        const float *row = cond + ((size_t)b * S + t) * RW;
-#pragma unroll
-        for (int i = 0; i < 7; i++) {
-            const int e = lane + 32 * i;
-            if (e < RW) scr[e] = __ldg(row + e);
-        }
-    }
-    __syncwarp();
-    if (lane < KC * CGROUPS) {
-        float v[8];
-#pragma unroll
-        for (int i = 0; i < 8; i++) {
-            const int e = lane * 8 + i;
-            float x = 0.f;
-            if (b < B) {
-                if (e < C_A2) x = scr[FEAT + 3 * AUX + (e - C_A4)];
-                else if (e < C_X) x = scr[FEAT + AUX + (e - C_A2)];
-                else if (e == C_X) x = 0.f;                      // the previous sample enters in the epilogues
-                else if (e < C_A1) x = scr[e - C_M];
-                else if (e < C_A3) x = scr[FEAT + (e - C_A1)];
-                else if (e < C_END) x = scr[FEAT + 2 * AUX + (e - C_A3)];
+// The conditioning features of every (step, fold) as the MMA operand image, straight from the frame-rate tensors: the
+// mel part is formed from the padded frames by the polyphase table (UpsampleNetwork's repeat + FIR stages and the crop,
+// fatchord_version.py:86-88; same taps, same order of operations as fold_cond_kernel, so the values are the ones the
+// FMA kernels read), the x275 nearest-repeat of aux (Stretch2d, :83-85) and the fold offsets (:293-340) are indices.
+// No fp32 fold batch is written for this kernel.  Thread = (step, fold tile, chunk of 8 features, fold): the 128 folds of
+// a tile are consecutive threads, so every store instruction writes 2 KB of contiguous operand.
+struct CondSrc {
+    const float *melT, *res_out, *poly;         // [frames][80], [frames][128], [hop][taps]
+    const FoldMeta *meta;                       // per fold of this launch
+    int hop, indent, taps, kmin;
+};
+__global__ void __launch_bounds__(256) cond_operand_kernel(const CondSrc c, int64_t B, int64_t S, int ntiles, uint8_t *__restrict__ Cop) {
+    const int fi = threadIdx.x & (FT - 1);
+    const int64_t blk = blockIdx.x;
+    const int chunk = (int)(blk % 16) * 2 + (threadIdx.x >> 7);         // 0..31
+    const int64_t rest = blk / 16;
+    const int nt = (int)(rest % ntiles);
+    const int64_t t = rest / ntiles, b = (int64_t)nt * FT + fi;
+    float v[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    const int e = chunk * 8;
+    if (b < B && e < C_END) {
+        const FoldMeta m = c.meta[b];
+        const int64_t l = m.start + t;
+        if (l < m.L) {
+            const int li = (int)l;
+            if (e >= C_M && e < C_A1) {
+                const int f = e - C_M, ii = li + c.indent, fr = ii / c.hop, ph = ii - fr * c.hop;
+                float4 v0 = make_float4(0.f, 0.f, 0.f, 0.f), v1 = v0;
+                for (int k = 0; k < c.taps; k++) {
+                    const int j = fr + c.kmin + k;
+                    if (j < 0 || j >= m.Tp) continue;
+                    const float wv = __ldg(c.poly + ph * c.taps + k);
+                    const float4 *src = reinterpret_cast<const float4 *>(c.melT + (size_t)(m.pm_off + j) * FEAT + f);
+                    const float4 q0 = __ldg(src), q1 = __ldg(src + 1);
+                    v0.x = fmaf(wv, q0.x, v0.x); v0.y = fmaf(wv, q0.y, v0.y); v0.z = fmaf(wv, q0.z, v0.z); v0.w = fmaf(wv, q0.w, v0.w);
+                    v1.x = fmaf(wv, q1.x, v1.x); v1.y = fmaf(wv, q1.y, v1.y); v1.z = fmaf(wv, q1.z, v1.z); v1.w = fmaf(wv, q1.w, v1.w);
+                }
+                v[0] = v0.x; v[1] = v0.y; v[2] = v0.z; v[3] = v0.w; v[4] = v1.x; v[5] = v1.y; v[6] = v1.z; v[7] = v1.w;
+            } else {
+                // aux rows are [a1 | a2 | a3 | a4] (fatchord_version.py:203-206); the operand order is [a4 | a2 | . | a1 | a3]
+                const int a = e < C_A2 ? 3 * AUX + (e - C_A4) : e < C_M ? AUX + (e - C_A2) : e < C_A3 ? (e - C_A1) : 2 * AUX + (e - C_A3);
+                const float4 *src = reinterpret_cast<const float4 *>(c.res_out + (size_t)(m.res_off + li / c.hop) * (4 * AUX) + a);
+                const float4 q0 = __ldg(src), q1 = __ldg(src + 1);
+                v[0] = q0.x; v[1] = q0.y; v[2] = q0.z; v[3] = q0.w; v[4] = q1.x; v[5] = q1.y; v[6] = q1.z; v[7] = q1.w;
             }
-            v[i] = x;
         }
-        uint4 hi, lo;
-        split8(v, hi, lo);
-        const int nt = (int)(b / FT), fi = (int)(b % FT);
-        uint8_t *base = Cop + ((size_t)t * ntiles) * CGROUPS * ACT_STAGE;
-        *reinterpret_cast<uint4 *>(base + b_slot(FT, CGROUPS, nt, lane, fi, 0)) = hi;
-        *reinterpret_cast<uint4 *>(base + b_slot(FT, CGROUPS, nt, lane, fi, 1)) = lo;
     }
+    uint4 hi, lo;
+    split8(v, hi, lo);
+    uint8_t *base = Cop + ((size_t)t * ntiles) * CGROUPS * ACT_STAGE;
+    __stcs(reinterpret_cast<uint4 *>(base + b_slot(FT, CGROUPS, nt, chunk, fi, 0)), hi);      // streamed: read once, a step at a time
+    __stcs(reinterpret_cast<uint4 *>(base + b_slot(FT, CGROUPS, nt, chunk, fi, 1)), lo);
 }
 
 // ---------------------------------------------------------------------------- pipeline: ring, producer, issuer
@@ -1002,15 +1012,16 @@ int mma_plan(wrnn_handle *h) {
     compose(F1, FCD, H + AUX, Wc3, bc3);
     // value of weight element (phase p, global row, conditioning element e of the operand order) / (512-wide operand, k)
     auto cond_w = [&](int p, int grow, int e) -> double {
-        const bool in_x = e >= C_X && e < C_A3;        // x_prev, m, a1: column e - 64 of the composed matrix
-        if (p == 0) return in_x ? Wc1[(size_t)grow * KI + (e - C_X)] : 0.0;
+        const bool in_x = e >= C_M && e < C_A3;        // m, a1: columns 1 .. 112 of the composed matrix (column 0 = x_prev: epilogues)
+        const int xc = 1 + (e - C_M);
+        if (p == 0) return in_x ? Wc1[(size_t)grow * KI + xc] : 0.0;
         if (p == 1) {
-            if (e >= C_A2 && e < C_X) return W2i->v[(size_t)grow * (H + AUX) + H + (e - C_A2)];
-            return in_x ? Wc2[(size_t)grow * KI + (e - C_X)] : 0.0;
+            if (e >= C_A2 && e < C_M) return W2i->v[(size_t)grow * (H + AUX) + H + (e - C_A2)];
+            return in_x ? Wc2[(size_t)grow * KI + xc] : 0.0;
         }
         if (p == 2) {
             if (e >= C_A3 && e < C_END) return F1->v[(size_t)grow * (H + AUX) + H + (e - C_A3)];
-            return in_x ? Wc3[(size_t)grow * KI + (e - C_X)] : 0.0;
+            return in_x ? Wc3[(size_t)grow * KI + xc] : 0.0;
         }
         return (e >= C_A4 && e < C_A2) ? F2->v[(size_t)grow * (FCD + AUX) + FCD + (e - C_A4)] : 0.0;
     };
@@ -1042,8 +1053,7 @@ int mma_plan(wrnn_handle *h) {
                     const int grow = rows == GRU_ROWS ? (r / UT) * H + mt * UT + (r % UT) : mt * FC_ROWS + r;
                     for (int kl = 0; kl < KC * 8; kl++) {
                         const int feat = si.g * (KC * 8) + kl;
-                        // the previous-sample slot of the operand is zero: its column is applied in the epilogues (xcol below)
-                        const double wv = si.arr == ARR_C ? (feat == C_X ? 0.0 : cond_w(cond_layer(jt), grow, feat)) : main_w(jt, grow, feat);
+                        const double wv = si.arr == ARR_C ? cond_w(cond_layer(jt), grow, feat) : main_w(jt, grow, feat);
                         const float wf = (float)wv;
                         const uint16_t hi = f2bf(wf), lo = f2bf((float)(wv - (double)bf2f(hi)));
                         const size_t o = ((size_t)(kl / 8) * rows + r) * 8 + kl % 8;
@@ -1136,8 +1146,12 @@ int mma_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
     P.Cop = Cop;
     h->mma_dbg[0] = P.h1f; h->mma_dbg[1] = P.h2f; h->mma_dbg[2] = P.y2f;
     {       // pre-pass: the conditioning operand of all steps, and the first previous sample
-        const int64_t warps = a.S * (int64_t)NF;
-        cond_operand_kernel<<<(unsigned)((warps + 7) / 8), 256, 0, st>>>(a.cond, a.B, a.S, P.NTILES, Cop);
+        if (!a.melT || !a.res_out || !a.fold_meta) return fail(h, WRNN_ERR_STATE, "tensor-core loop kernel: conditioning tensors not staged");
+        const CondSrc cs{a.melT, a.res_out, h->cp.poly, (const FoldMeta *)a.fold_meta, h->d.total_scale, (int)h->d.indent, h->cp.poly_taps,
+                         h->cp.poly_kmin};
+        const int64_t blocks = a.S * (int64_t)P.NTILES * 16;
+        if (blocks >= 0x7fffffff) return fail(h, WRNN_ERR_ARG, "tensor-core loop kernel: too many steps x fold tiles for one conditioning launch");
+        cond_operand_kernel<<<(unsigned)blocks, 256, 0, st>>>(cs, a.B, a.S, P.NTILES, Cop);
         xp_init_kernel<<<(unsigned)((NF + 255) / 256), 256, 0, st>>>(P.xp, a.teacher, a.B, a.S, (int64_t)NF);
         WRNN_CUDA(h, cudaGetLastError());
         h->launches += 2;
