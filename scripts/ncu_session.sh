@@ -15,6 +15,6 @@ for k in mma res; do
   echo "$k capture rc=$?"
 done
 python scripts/prof_target.py mma > $O/ncu_cond_plain.log 2>&1 &&
-ncu --set full --clock-control none -k regex:"fold_cond|resnet_batch" -c 2 -f -o $O/prof_cond python scripts/prof_target.py mma > $O/ncu_cond.log 2>&1
+ncu --set full --clock-control none -k regex:"cond_operand|resnet_batch" -c 2 -f -o $O/prof_cond python scripts/prof_target.py mma > $O/ncu_cond.log 2>&1
 echo "cond capture rc=$?"
 ls -la $O/*.ncu-rep $O/launches.csv
