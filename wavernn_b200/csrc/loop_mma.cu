@@ -82,7 +82,8 @@ constexpr int C_A4 = 0, C_A2 = 32, C_M = 64, C_A1 = 144, C_A3 = 176, C_END = 208
 //   S1 / S2: recurrent products W_hh . h' of the NEXT step (loop_res.cu's "shadow products", on tensor cores).
 enum { J_R1A = 0, J_R2A, J_R2C, J_S1, J_S2, J_F1A, J_F1C, J_F2A, J_F2C, J_F3, NJOB };
 enum { ARR_C = 0, ARR_H1NEW, ARR_H2NEW, ARR_S12, ARR_Y1, ARR_Y2 };
-enum { PH_RNN1 = 0, PH_RNN2, PH_FC1, PH_FC2, PH_SAMPLE, NPHASE };     // per-tile counters: who has published what
+enum { PH_RNN1 = 0, PH_RNN2, PH_FC1, PH_FC2, PH_SAMPLE, PH_H2, NPHASE };     // per-tile counters: who has published what
+// (PH_RNN2 = h1' + h2' is out, which is all fc1 waits for; PH_H2 = rnn2's own new state is out too, for the recurrent products)
 enum { TF_R1 = 0, TF_R2, TF_F1, TF_F2, TF_F3, NTF };                   // accumulator-ready barriers, one per epilogue
 // TMEM accumulator (first column) of each job: 128 lanes = folds, columns = weight rows.  rnn1's gates read X1 + H1,
 // rnn2's X2 + H2 (96 columns each: [r | z | n] x 32 units); fc1, fc2 64 columns each; fc3 reuses fc1's first 32.
@@ -173,7 +174,8 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t by
 // generic-proxy writes (st.global by the epilogue threads) are read by the TMA unit (async proxy) of other SMs: EVERY writing
 // thread orders its own stores against the async proxy before the CTA publishes the phase, and the producer thread does the
 // same after it has acquired the grid counter (the pattern of a TMA store after generic smem writes, applied to global)
-__device__ __forceinline__ void fence_proxy_async_global() { asm volatile("fence.proxy.async;" ::: "memory"); }
+// (the .global form: the plain `fence.proxy.async` also covers shared memory and cost 2.2 us of a 36 us step, five publishes)
+__device__ __forceinline__ void fence_proxy_async_global() { asm volatile("fence.proxy.async.global;" ::: "memory"); }
 __device__ __forceinline__ void tmem_alloc(uint32_t *dst_smem, uint32_t ncols) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "r"(ncols) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
@@ -244,7 +246,7 @@ __device__ __forceinline__ void mbar_wait(void *b, uint32_t parity, Watch &w) {
 __device__ __forceinline__ unsigned long long *tile_counter(const GridSync &gs, int phase, int nt) {
     return gs.counter + 16 * (1 + phase * MAXTILES + nt);
 }
-__device__ __forceinline__ int phase_arrivals(int phase) { return phase <= PH_RNN2 ? MT_GRU : phase <= PH_FC2 ? MT_FC : 1; }
+__device__ __forceinline__ int phase_arrivals(int phase) { return phase <= PH_RNN2 || phase == PH_H2 ? MT_GRU : phase <= PH_FC2 ? MT_FC : 1; }
 __device__ __forceinline__ void tile_wait(const GridSync &gs, int phase, int nt, int64_t steps_done, Watch &w) {
     if (w.dead || steps_done <= 0) return;
     const unsigned long long want = (unsigned long long)phase_arrivals(phase) * (unsigned long long)steps_done;
@@ -547,8 +549,9 @@ __device__ __forceinline__ void epi_gru(const Params &P, int mt, int nt, int64_t
                                         float (&hst)[16], float (&h1new)[16], int q, int half, int lane) {
     const int fi = q * 32 + lane, u0 = half * 16, gu = mt * UT + u0;
     const size_t fold = (size_t)nt * FT + fi;
-    const float *bi = sb + SB_G + LAYER * 2 * GRU_ROWS, *bh = bi + GRU_ROWS, *wx = sb + SB_XG + LAYER * GRU_ROWS;
-    uint8_t *Hn = LAYER == 0 ? P.H1[(t + 1) & 1] : P.H2[(t + 1) & 1];
+    // sb: input-side biases of r, z, n (the recurrent biases of r and z are folded into them on the host: the two sides
+    // are only ever added), recurrent bias of n, previous-sample column
+    const float *bi = sb + SB_G + LAYER * 2 * GRU_ROWS, *bhn = bi + GRU_ROWS + 2 * UT, *wx = sb + SB_XG + LAYER * GRU_ROWS;
     const uint32_t base = tb + ((uint32_t)(q * 32) << 16), colX = base + (uint32_t)job_acc(LAYER == 0 ? J_R1A : J_R2A) + u0,
                    colH = base + (uint32_t)job_acc(LAYER == 0 ? J_S1 : J_S2) + u0;
 #pragma unroll
@@ -566,8 +569,8 @@ __device__ __forceinline__ void epi_gru(const Params &P, int mt, int nt, int64_t
         for (int i = 0; i < 8; i++) {
             const int u = u0 + 8 * g + i;
             hn[i] = gru_update_fast(fmaf(wx[u], xp, __uint_as_float(xr[i]) + bi[u]), fmaf(wx[UT + u], xp, __uint_as_float(xz[i]) + bi[UT + u]),
-                                    fmaf(wx[2 * UT + u], xp, __uint_as_float(xn[i]) + bi[2 * UT + u]), __uint_as_float(hr[i]) + bh[u],
-                                    __uint_as_float(hz[i]) + bh[UT + u], __uint_as_float(hn_[i]) + bh[2 * UT + u], hst[8 * g + i]);
+                                    fmaf(wx[2 * UT + u], xp, __uint_as_float(xn[i]) + bi[2 * UT + u]), __uint_as_float(hr[i]),
+                                    __uint_as_float(hz[i]), __uint_as_float(hn_[i]) + bhn[u], hst[8 * g + i]);
             hst[8 * g + i] = hn[i];
         }
         if (P.dbg_state) {                  // fp32 copy of the state for wrnn_debug_mma_state only
@@ -576,11 +579,8 @@ __device__ __forceinline__ void epi_gru(const Params &P, int mt, int nt, int64_t
             dst[1] = make_float4(hn[4], hn[5], hn[6], hn[7]);
         }
         uint4 hi, lo;
-        split8(hn, hi, lo);
         const int chunk = (gu >> 3) + g;
-        *reinterpret_cast<uint4 *>(Hn + b_slot(FT, HGROUPS, nt, chunk, fi, 0)) = hi;
-        *reinterpret_cast<uint4 *>(Hn + b_slot(FT, HGROUPS, nt, chunk, fi, 1)) = lo;
-        if (LAYER == 1) {
+        if (LAYER == 1) {                   // what fc1 waits for goes out first; the new state itself follows (store_state)
             float sm[8];
 #pragma unroll
             for (int i = 0; i < 8; i++) sm[i] = h1new[8 * g + i] + hn[i];
@@ -588,9 +588,28 @@ __device__ __forceinline__ void epi_gru(const Params &P, int mt, int nt, int64_t
             *reinterpret_cast<uint4 *>(P.S12 + b_slot(FT, HGROUPS, nt, chunk, fi, 0)) = hi;
             *reinterpret_cast<uint4 *>(P.S12 + b_slot(FT, HGROUPS, nt, chunk, fi, 1)) = lo;
         } else {
+            split8(hn, hi, lo);
+            uint8_t *Hn = P.H1[(t + 1) & 1];
+            *reinterpret_cast<uint4 *>(Hn + b_slot(FT, HGROUPS, nt, chunk, fi, 0)) = hi;
+            *reinterpret_cast<uint4 *>(Hn + b_slot(FT, HGROUPS, nt, chunk, fi, 1)) = lo;
 #pragma unroll
             for (int i = 0; i < 8; i++) h1new[8 * g + i] = hn[i];
         }
+    }
+}
+// rnn2's new state as the operand of its recurrent products: off the chain, after h1' + h2' has been published
+__device__ __forceinline__ void store_state2(const Params &P, int mt, int nt, int64_t t, const float (&hst)[16], int q, int half, int lane) {
+    const int fi = q * 32 + lane, gu = mt * UT + half * 16;
+    uint8_t *Hn = P.H2[(t + 1) & 1];
+#pragma unroll
+    for (int g = 0; g < 2; g++) {
+        float hn[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) hn[i] = hst[8 * g + i];
+        uint4 hi, lo;
+        split8(hn, hi, lo);
+        *reinterpret_cast<uint4 *>(Hn + b_slot(FT, HGROUPS, nt, (gu >> 3) + g, fi, 0)) = hi;
+        *reinterpret_cast<uint4 *>(Hn + b_slot(FT, HGROUPS, nt, (gu >> 3) + g, fi, 1)) = lo;
     }
 }
 
@@ -797,7 +816,7 @@ __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
                     }
                 }
                 if (has_gru && more) {         // nothing reads the recurrent products of the step after the last
-                    produce_job(P, J_S2, mt_g, nt_g, t, PH_RNN2, t + 1, pp, lane, w, pa ? pa + 5 : nullptr);
+                    produce_job(P, J_S2, mt_g, nt_g, t, PH_H2, t + 1, pp, lane, w, pa ? pa + 5 : nullptr);
                     produce_job(P, J_R2A, mt_g, nt_g, t + 1, -1, 0, pp, lane, w);
                     PROF_MARK(7);
                 }
@@ -895,6 +914,8 @@ __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
                 if (etid == 0) PROF_MARK(25);
                 publish(PH_RNN2, nt_g);
                 if (etid == 0) PROF_MARK(26);
+                store_state2(P, mt_g, nt_g, t, hst2, q, half, lane);
+                publish(PH_H2, nt_g);
             }
             if (has_fc) {
                 wait_acc(TF_F1);
@@ -1072,8 +1093,10 @@ int mma_plan(wrnn_handle *h) {
             for (int r = 0; r < GRU_ROWS; r++) {
                 const int grow = (r / UT) * H + mt * UT + (r % UT);
                 float *b = bias.data() + (size_t)(p * MT_GRU + mt) * 2 * GRU_ROWS;
-                b[r] = (float)((p == 0 ? bc1[grow] : bc2[grow]) + (double)(p == 0 ? B1i : B2i)->v[grow]);
-                b[GRU_ROWS + r] = (p == 0 ? B1h : B2h)->v[grow];
+                const double bhh = (p == 0 ? B1h : B2h)->v[grow];
+                const bool n_gate = r >= 2 * UT;      // r and z: both sides are only ever added, one bias; n keeps its recurrent bias apart
+                b[r] = (float)((p == 0 ? bc1[grow] : bc2[grow]) + (double)(p == 0 ? B1i : B2i)->v[grow] + (n_gate ? 0.0 : bhh));
+                b[GRU_ROWS + r] = n_gate ? (float)bhh : 0.f;
                 bias[off_xg + (size_t)(p * MT_GRU + mt) * GRU_ROWS + r] = (float)(p == 0 ? Wc1 : Wc2)[(size_t)grow * KI];
             }
     for (int r = 0; r < FCD; r++) {
