@@ -369,7 +369,8 @@ def run_ours(args):
             'gpu_launches': int(launches) + (c5['launches'] if c5 else 0),
             'loop': {'kernel': kernel, 'ms': k_ms, 'us_per_step': us_step,
                      'folds': folds_loop, 'steps': steps_loop, 'ms_cond': t_last['ms_cond'], 'ms_tail': t_last['ms_tail'],
-                     'fold_steps_per_s': folds_loop * steps_loop / (k_ms * 1e-3)},
+                     'fold_steps_per_s': folds_loop * steps_loop / (k_ms * 1e-3),
+                     'exchange_calibration': dict(zip(('l2_round_trip_clk', 'gather_delay_scale'), voc.exchange_calibration()))},
             'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': hbm, 'unit': 'GB/s', 'frac': achieved / hbm,
                          'traffic': traffic['dram_bytes_per_launch'] if traffic else None,
                          'traffic_source': (traffic['source'] + ' via ' + traffic['file']) if traffic else

@@ -193,6 +193,10 @@ const char *wrnn_loop_kernel_name(wrnn_handle *h, int64_t folds);
  * 4 = "tcgen05-bf16x3" (csrc/loop_mma.cu: the contractions of fatchord_version.py:208-221 on the tensor
  * cores with bf16 hi/lo split operands and fp32 TMEM accumulators; default dims, MoL; auto from 61 folds up). */
 int wrnn_set_loop_kernel(wrnn_handle *h, int32_t which);
+/* What the register-resident kernel measured at its first run on this handle: the L2 round trip in SM clocks (a
+ * dependent `ld.global.cg` chain) and the factor by which it scaled the delays before the first look at an exchange
+ * (tuned at 1965 MHz on a B200).  Zero / one before the first run.  WRNN_NO_CALIBRATION=1 pins the scale to 1. */
+int wrnn_exchange_calibration(wrnn_handle *h, float *l2_round_trip_clk, float *delay_scale);
 /* Kept for callers of earlier builds: the tensor-core kernel's fold tile is the M of its MMAs (128 folds = the 128 TMEM
  * lanes) and no longer a choice.  The argument is validated (0, or a multiple of 16 <= 128) and otherwise ignored. */
 int wrnn_set_mma_fold_tile(wrnn_handle *h, int32_t nt);

@@ -244,3 +244,22 @@ def test_config2_full_size_properties(mode):
         both = (np.concatenate([n1[0], n2[0]], axis=1), np.concatenate([n1[1], n2[1]], axis=1))
         o1, o2 = v.generate([mel[0], mel2[0]], True, 11000, 550, False, noise=both)
         assert np.array_equal(o2, w2) and o1.shape == a.shape
+
+
+def test_exchange_calibration_is_measured_and_neutral_on_the_tuning_hardware():
+    """the gather delays are scaled by a measured L2 round trip.  On a B200 at its default
+    clocks the measurement lands inside the dead band and the tuned delays are used as they are."""
+    dims = VocoderDims(mode='MOL')
+    v = binding.Vocoder(dims, device=0)
+    v.load_weights(synth.synth_state_dict(dims, seed=0, style='init'))
+    assert v.exchange_calibration() == (0.0, 1.0)
+    mel = synth.synth_mel(26, seed=3)
+    v.set_loop_kernel(3)
+    v.generate([mel[0]], True, 300, 40, False, seed=1)
+    clk, scale = v.exchange_calibration()
+    assert 200.0 < clk < 1000.0, clk
+    assert 0.6 <= scale <= 2.0
+    if abs(clk / 297.5 - 1.0) < 0.05:
+        assert scale == 1.0
+    else:
+        assert abs(scale - min(2.0, max(0.6, clk / 297.5))) < 1e-3

@@ -73,6 +73,7 @@ _SIGS = {
     'wrnn_loop_kernel_name': (C.c_char_p, [_P, C.c_int64]),
     'wrnn_set_loop_kernel': (C.c_int, [_P, C.c_int32]),
     'wrnn_set_mma_fold_tile': (C.c_int, [_P, C.c_int32]),
+    'wrnn_exchange_calibration': (C.c_int, [_P, _P, _P]),
     'wrnn_debug_mma_state': (C.c_int, [_P, C.c_int32, C.c_int64, _P]),
     'wrnn_dm_create': (C.c_int, [C.c_int32, C.c_int32, C.c_int, C.POINTER(_P)]),
     'wrnn_dm_destroy': (None, [_P]),
@@ -306,6 +307,12 @@ class Vocoder:
         out = np.empty((folds, 512), dtype=np.float32)
         self._ck(lib().wrnn_debug_mma_state(self._h, int(which), int(folds), _ptr(out)))
         return out
+
+    def exchange_calibration(self):
+        """(L2 round trip in SM clocks, gather-delay scale) of the resident kernel's calibration pass; (0, 1) before its first run."""
+        a, b = C.c_float(), C.c_float()
+        self._ck(lib().wrnn_exchange_calibration(self._h, C.byref(a), C.byref(b)))
+        return a.value, b.value
 
     def set_mma_fold_tile(self, nt):
         self._ck(lib().wrnn_set_mma_fold_tile(self._h, int(nt)))

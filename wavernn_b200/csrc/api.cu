@@ -242,6 +242,13 @@ int wrnn_debug_mma_state(wrnn_handle *h, int32_t which, int64_t folds, float *ou
     return 0;
 }
 
+int wrnn_exchange_calibration(wrnn_handle *h, float *l2_round_trip_clk, float *delay_scale) {
+    if (!h) return WRNN_ERR_ARG;
+    if (l2_round_trip_clk) *l2_round_trip_clk = h->xchg_l2_clk;
+    if (delay_scale) *delay_scale = h->xchg_scale;
+    return 0;
+}
+
 int wrnn_set_mma_fold_tile(wrnn_handle *h, int32_t nt) {
     if (!h) return WRNN_ERR_ARG;
     if (nt != 0 && (nt < 16 || nt > 128 || nt % 16)) return fail(h, WRNN_ERR_ARG, "fold tile must be 0 (auto) or a multiple of 16 in [16, 128]");

@@ -115,6 +115,7 @@ struct wrnn_handle {
     wrnn::ResPlan res;
     wrnn::MmaPlan mma;
     float *mma_dbg[3] = {nullptr, nullptr, nullptr};   // h1, h2, fc2 output [folds][512] fp32 of the last tensor-core run
+    float xchg_l2_clk = 0.f, xchg_scale = 1.f;   // loop_res.cu calibrate_exchange: measured L2 round trip (SM clocks), delay scale
     int mma_force_nt = 0;              // debug / tests: fold-tile width of the tensor-core kernel (0 = auto)
     int force_kernel = 0;
     std::vector<double> lut_override;   // host-supplied mu-law table (wrnn_set_mulaw_lut)

@@ -1216,6 +1216,50 @@ int res_plan(wrnn_handle *h) {
     return 0;
 }
 
+// ---------------------------------------------------------------------------- gather-delay calibration
+// The delays before the first look at an exchange (GATHER_DELAY_*) are SM clocks and were tuned on a B200 whose L2 round
+// trip, measured by this kernel, was L2_RT_NOMINAL clocks.  Under a power cap or another SM clock the same round trip is
+// a different number of SM clocks; a premature first look costs 2.5x.  So, once per handle: a dependent
+// chain of 256 `ld.global.cg` through a 4 MB buffer (L2-resident, L1 bypassed), timed with clock64, and the delays are
+// scaled by measured / nominal (clamped to [0.6, 2]; left alone when the ratio is within the measurement's spread).  Tag validation keeps the kernel correct whatever the delays are.
+constexpr float L2_RT_NOMINAL = 297.5f;     // this chain on the tuning box (B200, 1965 MHz): 297.45 .. 298.7 over nine handles
+constexpr float L2_RT_DEADBAND = 0.05f;     // inside it the tuned delays are used as they are (scaling them by 0.76 cost 8 % of a step)
+__global__ void l2_chase_init_kernel(unsigned *buf, unsigned n, unsigned stride) {
+    const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) buf[i] = (i + stride) % n;
+}
+__global__ void l2_chase_kernel(const unsigned *buf, unsigned hops, long long *out) {
+    unsigned p = 0;
+    for (unsigned i = 0; i < hops; i++) p = __ldcg(buf + p);                 // warm the lines into L2
+    const long long t0 = clock64();
+    for (unsigned i = 0; i < hops; i++) p = __ldcg(buf + p);
+    const long long t1 = clock64();
+    out[0] = t1 - t0;
+    out[1] = p;
+}
+static int calibrate_exchange(wrnn_handle *h, cudaStream_t st) {
+    if (h->xchg_l2_clk > 0.f) return 0;
+    const unsigned n = 1u << 20, hops = 512, stride = 4099 * 32;             // 4 MB of words, one hop per 128-byte line and more
+    WRNN_TRY(ws_reserve(h, h->ws_tmp1, (size_t)n * 4 + 64));
+    unsigned *buf = (unsigned *)h->ws_tmp1.p;
+    long long *out = (long long *)(buf + n);
+    l2_chase_init_kernel<<<n / 256, 256, 0, st>>>(buf, n, stride);
+    long long best = 0;
+    for (int rep = 0; rep < 3; rep++) {                                       // the fastest of three: the chain has no reason to be slower
+        l2_chase_kernel<<<1, 1, 0, st>>>(buf, hops, out);
+        long long res[2] = {0, 0};
+        WRNN_CUDA(h, cudaMemcpyAsync(res, out, sizeof(res), cudaMemcpyDeviceToHost, st));
+        WRNN_CUDA(h, cudaStreamSynchronize(st));
+        if (rep == 0 || res[0] < best) best = res[0];
+    }
+    h->launches += 4;
+    h->xchg_l2_clk = (float)best / hops;
+    float sc = h->xchg_l2_clk / L2_RT_NOMINAL;
+    if (getenv("WRNN_NO_CALIBRATION") || (sc > 1.f - L2_RT_DEADBAND && sc < 1.f + L2_RT_DEADBAND)) sc = 1.f;
+    h->xchg_scale = sc < 0.6f ? 0.6f : sc > 2.f ? 2.f : sc;
+    return 0;
+}
+
 int res_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
     const Dims &d = h->d;
     const ResPlan &p = h->res;
@@ -1242,12 +1286,14 @@ int res_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
     P.abort_flag = (int *)((char *)h->ws_sync.p + 64);
     static const bool prof_env = getenv("WRNN_PROF") != nullptr;
     static const int d1_env = getenv("WRNN_D1") ? atoi(getenv("WRNN_D1")) : 0, d2_env = getenv("WRNN_D2") ? atoi(getenv("WRNN_D2")) : 0;
-    P.d1 = d1_env;
-    P.d2 = d2_env;
+    WRNN_TRY(calibrate_exchange(h, st));
+    auto scaled = [&](int env, int nominal) { return env ? env : (int)(nominal * h->xchg_scale + 0.5f); };
+    P.d1 = scaled(d1_env, GATHER_DELAY_H1);
+    P.d2 = scaled(d2_env, GATHER_DELAY_X2);
     static const int d3_env = getenv("WRNN_D3") ? atoi(getenv("WRNN_D3")) : 0;
-    P.d3 = d3_env;
+    P.d3 = scaled(d3_env, GATHER_DELAY_Y1);
     static const int d4_env = getenv("WRNN_D4") ? atoi(getenv("WRNN_D4")) : 0;
-    P.d4 = d4_env;
+    P.d4 = scaled(d4_env, GATHER_DELAY_Y2);
     static const bool force_dense = getenv("WRNN_DENSE") != nullptr;       // A/B measurement: dense job on the masked weights
     P.sparse = (p.sparse && !force_dense) ? 1 : 0;
     P.prof = nullptr;
