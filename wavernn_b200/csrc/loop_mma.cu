@@ -58,7 +58,11 @@ constexpr int W_GRU = 2 * KC * GRU_ROWS * 16, W_FC = 2 * KC * FC_ROWS * 16;     
 constexpr int ACT_STAGE = 2 * KC * FT * 16;                                      // activation block of a stage, hi + lo: 32768 B
 constexpr int CGROUPS = 4;                 // conditioning operand: 32 chunks = 256 elements per fold (209 used)
 constexpr int HGROUPS = H / (8 * KC);      // 8 stage groups in a 512-wide operand
-constexpr int THREADS = 320, EPI_THREADS = 256, EPI_WARPS = 8;
+constexpr int EPI_PARTS = 2;               // epilogue warps per TMEM lane quarter: each takes 1 / EPI_PARTS of an accumulator's columns.
+                                           // 4 (16 warps, 96 registers) was measured: no faster.  The GRU gate math is bound by the
+                                           // SFU: 128 folds x 32 units x 6 MUFU at 16 per clock = 1.5 k clk per epilogue however many warps
+constexpr int EPI_WARPS = 4 * EPI_PARTS, EPI_THREADS = 32 * EPI_WARPS, THREADS = 64 + EPI_THREADS;
+constexpr int UPT = UT / EPI_PARTS, RPT = FC_ROWS / EPI_PARTS;      // GRU units / fc rows per epilogue thread: 16 / 32
 constexpr int NCP = 32;                    // fc3 rows padded (MoL: 30) = N of the fc3 job
 // this CTA's bias rows and previous-sample columns in shared memory
 constexpr int SB_G = 0;                                  // rnn1 [input 96 | recurrent 96], rnn2 [input 96 | recurrent 96]
@@ -537,7 +541,7 @@ __device__ __forceinline__ void issue_job(int jt, Issue &is, Watch &w, long long
 // ---------------------------------------------------------------------------- epilogues (256 threads, warps 2..9)
 // Accumulators are [128 folds (TMEM lanes)] x [weight rows (columns)], so a thread owns ONE fold (lane 32 q + lane of the
 // warp's lane quarter q = warp % 4) and reads the r, z, n columns of a unit straight from its own lane: no shared-memory
-// staging, no barrier inside an epilogue; the two warps of a quarter split the columns (`half`).  Operand stores are one
+// staging, no barrier inside an epilogue; the EPI_PARTS warps of a quarter split the columns (`part`).  Operand stores are one
 // 16-byte chunk (8 units) per image per thread, consecutive lanes = consecutive folds = consecutive addresses.
 //
 // GRU gates (fatchord_version.py:210-216): X (input side: conditioning columns, issued ahead, + for rnn2 the h1' columns)
@@ -546,8 +550,8 @@ __device__ __forceinline__ void issue_job(int jt, Issue &is, Watch &w, long long
 // whole run (`hst`).  rnn2 also emits s12 = h1' + h2' (fc1 reads x + h1 + h2; x is folded into fc1's weights).
 template <int LAYER>
 __device__ __forceinline__ void epi_gru(const Params &P, int mt, int nt, int64_t t, uint32_t tb, const float *sb, float xp,
-                                        float (&hst)[16], float (&h1new)[16], int q, int half, int lane) {
-    const int fi = q * 32 + lane, u0 = half * 16, gu = mt * UT + u0;
+                                        float (&hst)[UPT], float (&h1new)[UPT], int q, int part, int lane, long long *pm = nullptr) {
+    const int fi = q * 32 + lane, u0 = part * UPT, gu = mt * UT + u0;
     const size_t fold = (size_t)nt * FT + fi;
     // sb: input-side biases of r, z, n (the recurrent biases of r and z are folded into them on the host: the two sides
     // are only ever added), recurrent bias of n, previous-sample column
@@ -555,7 +559,7 @@ __device__ __forceinline__ void epi_gru(const Params &P, int mt, int nt, int64_t
     const uint32_t base = tb + ((uint32_t)(q * 32) << 16), colX = base + (uint32_t)job_acc(LAYER == 0 ? J_R1A : J_R2A) + u0,
                    colH = base + (uint32_t)job_acc(LAYER == 0 ? J_S1 : J_S2) + u0;
 #pragma unroll
-    for (int g = 0; g < 2; g++) {
+    for (int g = 0; g < UPT / 8; g++) {
         uint32_t xr[8], xz[8], xn[8], hr[8], hz[8], hn_[8];
         tmem_ld8_nowait(colX + 8 * g, xr);
         tmem_ld8_nowait(colX + UT + 8 * g, xz);
@@ -564,6 +568,7 @@ __device__ __forceinline__ void epi_gru(const Params &P, int mt, int nt, int64_t
         tmem_ld8_nowait(colH + UT + 8 * g, hz);
         tmem_ld8_nowait(colH + 2 * UT + 8 * g, hn_);
         tmem_ld_wait();
+        if (pm && g == 0) pm[0] = clock64();
         float hn[8];
 #pragma unroll
         for (int i = 0; i < 8; i++) {
@@ -578,6 +583,7 @@ __device__ __forceinline__ void epi_gru(const Params &P, int mt, int nt, int64_t
             dst[0] = make_float4(hn[0], hn[1], hn[2], hn[3]);
             dst[1] = make_float4(hn[4], hn[5], hn[6], hn[7]);
         }
+        if (pm && g == 0) pm[1] = clock64();
         uint4 hi, lo;
         const int chunk = (gu >> 3) + g;
         if (LAYER == 1) {                   // what fc1 waits for goes out first; the new state itself follows (store_state)
@@ -598,11 +604,11 @@ __device__ __forceinline__ void epi_gru(const Params &P, int mt, int nt, int64_t
     }
 }
 // rnn2's new state as the operand of its recurrent products: off the chain, after h1' + h2' has been published
-__device__ __forceinline__ void store_state2(const Params &P, int mt, int nt, int64_t t, const float (&hst)[16], int q, int half, int lane) {
-    const int fi = q * 32 + lane, gu = mt * UT + half * 16;
+__device__ __forceinline__ void store_state2(const Params &P, int mt, int nt, int64_t t, const float (&hst)[UPT], int q, int part, int lane) {
+    const int fi = q * 32 + lane, gu = mt * UT + part * UPT;
     uint8_t *Hn = P.H2[(t + 1) & 1];
 #pragma unroll
-    for (int g = 0; g < 2; g++) {
+    for (int g = 0; g < UPT / 8; g++) {
         float hn[8];
 #pragma unroll
         for (int i = 0; i < 8; i++) hn[i] = hst[8 * g + i];
@@ -615,14 +621,14 @@ __device__ __forceinline__ void store_state2(const Params &P, int mt, int nt, in
 
 // fc1 / fc2 + ReLU (:217-221): 64 rows = 64 columns, 32 per thread, out as the bf16 hi/lo operand of the next layer
 template <int LAYER>
-__device__ __forceinline__ void epi_fc(const Params &P, int mt, int nt, uint32_t tb, const float *sb, float xp, int q, int half, int lane) {
-    const int fi = q * 32 + lane, r0 = half * 32, gr = mt * FC_ROWS + r0;
+__device__ __forceinline__ void epi_fc(const Params &P, int mt, int nt, uint32_t tb, const float *sb, float xp, int q, int part, int lane) {
+    const int fi = q * 32 + lane, r0 = part * RPT, gr = mt * FC_ROWS + r0;
     const size_t fold = (size_t)nt * FT + fi;
     const float *bb = sb + SB_F + LAYER * FC_ROWS + r0, *wx = sb + SB_XF + r0;
     uint8_t *out = LAYER == 0 ? P.Y1 : P.Y2;
     const uint32_t col = tb + ((uint32_t)(q * 32) << 16) + (uint32_t)job_acc(LAYER == 0 ? J_F1C : J_F2C) + r0;
 #pragma unroll
-    for (int g = 0; g < 4; g += 2) {
+    for (int g = 0; g < RPT / 8; g += 2) {
         uint32_t a[8], b[8];
         tmem_ld8_nowait(col + 8 * g, a);
         tmem_ld8_nowait(col + 8 * g + 8, b);
@@ -686,7 +692,7 @@ __device__ __forceinline__ void mol_noise_thread(const Params &P, int nt, int64_
 }
 
 // fc3 (:223) + MoL draw (utils/distribution.py:87-123): the 30 logits of a fold are 30 columns of its own TMEM lane.
-// Called by the four warps with half == 0 (one per lane quarter).  Writes the sample, the mixture pick and the previous
+// Called by the four warps with part == 0 (one per lane quarter).  Writes the sample, the mixture pick and the previous
 // sample of step t + 1.
 __device__ __forceinline__ void epi_sample(const Params &P, int nt, int64_t t, uint32_t tb, const float *sb, const float (&gum)[NMIX],
                                            float lgt, int q, int lane) {
@@ -875,13 +881,13 @@ __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
     } else {
         // ======================================================================= epilogue warps
         const int etid = tid - 64, ewarp = warp - 2;
-        const int q = warp & 3, half = ewarp >> 2;          // TMEM lane quarter this warp may read; which half of the columns
+        const int q = warp & 3, part = ewarp >> 2;          // TMEM lane quarter this warp may read; which part of the columns
         const int fi = q * 32 + lane;
         uint32_t tfpar = 0;                                  // every accumulator-ready barrier completes once per step
         // recurrent state of this thread's (fold, 16 units), both layers, and rnn1's new state for s12: registers for the whole run
-        float hst1[16], hst2[16], h1new[16];
+        float hst1[UPT], hst2[UPT], h1new[UPT];
 #pragma unroll
-        for (int i = 0; i < 16; i++) hst1[i] = hst2[i] = h1new[i] = 0.f;        // h1 = h2 = 0 (:194-195)
+        for (int i = 0; i < UPT; i++) hst1[i] = hst2[i] = h1new[i] = 0.f;        // h1 = h2 = 0 (:194-195)
         auto publish = [&](int phase, int nt) {              // every writing thread fences, one thread releases the counter
             fence_proxy_async_global();
             epi_bar();
@@ -902,19 +908,19 @@ __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
                 const float xp = wait_prev_sample(P.xp + (size_t)nt_g * FT + fi, t, w);      // the sample of step t - 1 is out
                 if (etid == 0) PROF_MARK(21);
                 __syncwarp();
-                epi_gru<0>(P, mt_g, nt_g, t, tb, sbias, xp, hst1, h1new, q, half, lane);
+                epi_gru<0>(P, mt_g, nt_g, t, tb, sbias, xp, hst1, h1new, q, part, lane, (profiled_cta && t == P.prof_step && etid == 0) ? prof_base + 58 : nullptr);
                 tc_fence_before();
                 if (etid == 0) PROF_MARK(22);
                 publish(PH_RNN1, nt_g);
                 if (etid == 0) PROF_MARK(23);
                 wait_acc(TF_R2);
                 if (etid == 0) PROF_MARK(24);
-                epi_gru<1>(P, mt_g, nt_g, t, tb, sbias, xp, hst2, h1new, q, half, lane);
+                epi_gru<1>(P, mt_g, nt_g, t, tb, sbias, xp, hst2, h1new, q, part, lane);
                 tc_fence_before();
                 if (etid == 0) PROF_MARK(25);
                 publish(PH_RNN2, nt_g);
                 if (etid == 0) PROF_MARK(26);
-                store_state2(P, mt_g, nt_g, t, hst2, q, half, lane);
+                store_state2(P, mt_g, nt_g, t, hst2, q, part, lane);
                 publish(PH_H2, nt_g);
             }
             if (has_fc) {
@@ -922,22 +928,22 @@ __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
                 if (etid == 0) PROF_MARK(27);
                 // published before rnn1 of this step began; the loads that filled fc1's stages were ordered behind rnn2's counter
                 const float xp = __uint_as_float(ld_volatile_u2(P.xp + (size_t)nt_f * FT + fi).x);
-                epi_fc<0>(P, mt_f, nt_f, tb, sbias, xp, q, half, lane);
+                epi_fc<0>(P, mt_f, nt_f, tb, sbias, xp, q, part, lane);
                 tc_fence_before();
                 publish(PH_FC1, nt_f);
                 if (etid == 0) PROF_MARK(28);
                 wait_acc(TF_F2);
                 if (etid == 0) PROF_MARK(29);
-                epi_fc<1>(P, mt_f, nt_f, tb, sbias, 0.f, q, half, lane);
+                epi_fc<1>(P, mt_f, nt_f, tb, sbias, 0.f, q, part, lane);
                 tc_fence_before();
                 publish(PH_FC2, nt_f);
                 if (etid == 0) PROF_MARK(30);
                 if (has_f3) {
                     float gum[NMIX], lgt = 0.f;
-                    if (half == 0) mol_noise_thread(P, nt_f, t, q, lane, gum, lgt);
+                    if (part == 0) mol_noise_thread(P, nt_f, t, q, lane, gum, lgt);
                     wait_acc(TF_F3);
                     if (etid == 0) PROF_MARK(16);
-                    if (half == 0) epi_sample(P, nt_f, t, tb, sbias, gum, lgt, q, lane);
+                    if (part == 0) epi_sample(P, nt_f, t, tb, sbias, gum, lgt, q, lane);
                     tc_fence_before();
                     if (etid == 0) PROF_MARK(17);
                     __threadfence();
@@ -1224,6 +1230,7 @@ int mma_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
                 if (q[i]) ev.push_back({q[i] - t0, i});
             std::sort(ev.begin(), ev.end());
             for (auto &e : ev) fprintf(stderr, "[mma prof]   %8lld  %s\n", e.first, names[e.second]);
+            if (q[58]) fprintf(stderr, "[mma prof]   inside rnn1 gates (warp 2): accumulators in registers %lld, gate math done %lld (same clock)\n", q[58] - t0, q[59] - t0);
             static const char *jn[6] = {"rnn2", "recurrent-1", "fc1", "fc2", "fc3", "recurrent-2"};
             static const int jtype[6] = {J_R2C, J_S1, J_F1C, J_F2C, J_F3, J_S2};
             for (int j = 0; j < 6; j++)
