@@ -244,6 +244,8 @@ def run_config5(args, voc, dims, rank, world, stream, flush, barrier):
     barrier()
     e2e_s = time.time() - t0
     value, (dev_ms_max, e2e_ms_max) = whole_job_rate(n_utt * wave_len * k, [dev_ms, e2e_s * 1000.0], device='cuda')
+    import torch
+    dm = run_deepmind(torch.cuda.current_device(), world, barrier)
     if rank != 0:
         return None
     k_ms = float(np.mean(loop_ms))
@@ -267,8 +269,34 @@ def run_config5(args, voc, dims, rank, world, stream, flush, barrier):
                      'traffic': traffic['dram_bytes_per_launch'] if traffic else None,
                      'traffic_source': (traffic['source'] + ' via ' + traffic['file']) if traffic else
                      'no ncu capture of this kernel under profiles/ at this HEAD'},
-        'launches': launches,
+        'deepmind': dm,
+        'launches': launches + (dm['launches'] if dm else 0),
     }
+
+
+def run_deepmind(device, world, barrier, n_seq=8, seconds=0.5):
+    """configs[4], second half: deepmind_version coarse/fine dual-softmax generation (models/deepmind_version.py:75-165),
+    hidden 896, `n_seq` independent sequences per GPU (the reference generates one), Philox noise, through the C ABI with
+    the int64 outputs copied to host arrays inside the timed call."""
+    from wavernn_b200 import binding, synth
+    from wavernn_b200.shard import whole_job_rate
+    import torch
+    steps = int(SAMPLE_RATE * seconds)
+    v = binding.DeepmindVocoder(896, 256, device=device)
+    v.load_weights(synth.synth_dm_state_dict(896, 256, seed=0))
+    v.generate(steps // 8, n_seq, seed=1)                      # warm-up: weight images, workspaces
+    barrier()
+    t0 = time.time()
+    out, c, f = v.generate(steps, n_seq, seed=2)
+    torch.cuda.synchronize()
+    dt = time.time() - t0
+    t = v.last_timing()
+    assert out.shape == (n_seq, steps) and out.min() >= -32768 and out.max() <= 32767
+    rate, (ms_max,) = whole_job_rate(n_seq * steps, [dt * 1000.0], device='cuda')
+    v.close()
+    return {'workload': f'{n_seq} sequences per GPU x {steps} samples, hidden 896, 16-bit coarse/fine', 'value': rate, 'unit': 'samples/s',
+            'rtf': rate / SAMPLE_RATE, 'ms': ms_max, 'loop_us_per_step': 1000 * t['ms_loop'] / steps, 'launches': int(t['launches']),
+            'timed': 'wall clock around the C-ABI call, host int64 outputs included'}
 
 
 def run_ours(args):
