@@ -269,6 +269,14 @@ def run_config5(args, voc, dims, rank, world, stream, flush, barrier):
                      'traffic': traffic['dram_bytes_per_launch'] if traffic else None,
                      'traffic_source': (traffic['source'] + ' via ' + traffic['file']) if traffic else
                      'no ncu capture of this kernel under profiles/ at this HEAD'},
+        # north_star: "whole-box batched samples/sec as a fraction of the weight-bandwidth roofline": a step of the loop
+        # re-reads every weight once whatever the fold count, so the bound is hbm_gbs / weight bytes steps per second
+        'weight_bandwidth_roofline': {'achieved': WEIGHT_BYTES_PER_STEP * t['steps'] / (k_ms * 1e-3) / 1e9, 'unit': 'GB/s',
+                                      'bound_steps_per_s': measured_peaks()[0] * 1e9 / WEIGHT_BYTES_PER_STEP,
+                                      'steps_per_s': t['steps'] / (k_ms * 1e-3),
+                                      'frac': WEIGHT_BYTES_PER_STEP * t['steps'] / (k_ms * 1e-3) / 1e9 / measured_peaks()[0],
+                                      'note': 'the weights are streamed from L2 (15.3 MB of bf16 hi/lo images, resident there), not HBM; '
+                                              'what binds is in roofline (tensor) and DESIGN.md 4.5'},
         'deepmind': dm,
         'launches': launches + (dm['launches'] if dm else 0),
     }
