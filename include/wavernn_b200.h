@@ -191,7 +191,7 @@ const char *wrnn_loop_kernel_name(wrnn_handle *h, int64_t folds);
  * kernel, any dims and fold count, reference order of operations), 2 = fma-pipelined (tagged exchange, shared-memory
  * weights), 3 = fma-resident (register-resident weights, groups of <= 20 folds, whatever the fold count),
  * 4 = "tcgen05-bf16x3" (csrc/loop_mma.cu: the contractions of fatchord_version.py:208-221 on the tensor
- * cores with bf16 hi/lo split operands and fp32 TMEM accumulators; default dims, MoL; auto from 61 folds up). */
+ * cores with bf16 hi/lo split operands and fp32 TMEM accumulators; default dims, MoL; auto from 41 folds up). */
 int wrnn_set_loop_kernel(wrnn_handle *h, int32_t which);
 /* What the register-resident kernel measured at its first run on this handle: the L2 round trip in SM clocks (a
  * dependent `ld.global.cg` chain) and the factor by which it scaled the delays before the first look at an exchange

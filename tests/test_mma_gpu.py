@@ -40,8 +40,8 @@ def relerr(a, b):
 def test_kernel_selection_by_fold_count():
     v = voc('init')
     assert v.loop_kernel_name(20) == 'fma-resident'            # config 2: latency-bound, register-resident FMA kernel
-    assert v.loop_kernel_name(60) == 'fma-resident'             # three resident groups: 35.7 us per step
-    assert v.loop_kernel_name(61) == 'tcgen05-bf16x3'          # from 61 folds the tensor-core kernel (36.4 us per step) is the faster one
+    assert v.loop_kernel_name(40) == 'fma-resident'             # two resident groups: 23.8 us per step
+    assert v.loop_kernel_name(41) == 'tcgen05-bf16x3'          # three groups would take 35.7 us, the tensor-core kernel 27.4
     assert v.loop_kernel_name(640) == 'tcgen05-bf16x3'         # config 5 per GPU
     v.set_loop_kernel(3)
     assert v.loop_kernel_name(640) == 'fma-resident'

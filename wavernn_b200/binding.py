@@ -300,7 +300,7 @@ class Vocoder:
         return lib().wrnn_loop_kernel_name(self._h, int(folds)).decode()
 
     def set_loop_kernel(self, which):
-        """0 auto, 1 fma, 2 fma-pipelined, 4 tcgen05-bf16x3 (tensor cores; auto from 61 folds up)."""
+        """0 auto, 1 fma, 2 fma-pipelined, 4 tcgen05-bf16x3 (tensor cores; auto from 41 folds up)."""
         self._ck(lib().wrnn_set_loop_kernel(self._h, int(which)))
 
     def debug_mma_state(self, which, folds):

@@ -72,7 +72,8 @@ struct ResPlan {
 struct MmaPlan {
     bool ok = false;
     uint8_t *Aimg = nullptr;       // device: bf16 hi/lo weight images of the four MMA phases
-    int64_t offA[10] = {0};              // one image per job type (loop_mma.cu: J_R1A .. J_F3)
+    int64_t offA[10] = {0};              // one image per job type (loop_mma.cu: J_R1A .. J_F2C)
+    int64_t offP3 = 0;                   // fc3 columns as an MMA operand, per fc row tile
     float *bias = nullptr;         // device: composed biases
     float *wf3 = nullptr;          // device: fc3 rows (fp32) + bias
     size_t img_bytes = 0, smem_bytes = 0;

@@ -71,8 +71,11 @@ constexpr int SB_XG = SB_F + 2 * FC_ROWS;                // previous-sample colu
 constexpr int SB_XF = SB_XG + 2 * GRU_ROWS;              // ... of fc1 [64]
 constexpr int SB_B3 = SB_XF + FC_ROWS;                   // fc3 bias [32]
 constexpr int SBIAS = SB_B3 + NCP;
+// fc3 inside the fc CTAs: this CTA's 64 fc2 outputs of the 128 folds as an MMA operand (K = 64, hi + lo) and the matching 64
+// columns of fc3 (32 rows, hi + lo), both in shared memory for the whole call, between the stage ring and the bias rows
+constexpr int P3_A = 2 * KC * FT * 16, P3_B = 2 * KC * NCP * 16;       // 32768 + 8192 B
 constexpr int TMEM_COLS = 512;
-constexpr int FIXED_SMEM = SBIAS * 4;
+constexpr int FIXED_SMEM = P3_A + P3_B + SBIAS * 4;
 // conditioning operand element order (which features each layer concatenates):
 //   [a4 (32) | a2 (32) | m (80) | a1 (32) | a3 (32) | zero (48)]
 // in groups of 64: rnn1 reads groups 1..2, rnn2 0..2, fc1 1..3, fc2 group 0 (weights of the features a layer does not
@@ -84,11 +87,11 @@ constexpr int C_A4 = 0, C_A2 = 32, C_M = 64, C_A1 = 144, C_A3 = 176, C_END = 208
 //   ..A ("ahead"): the conditioning columns of a layer for step t + 1, issued during step t (start the accumulator);
 //   ..C ("chain"): the columns that depend on the step's own activations (accumulate on top);
 //   S1 / S2: recurrent products W_hh . h' of the NEXT step (loop_res.cu's "shadow products", on tensor cores).
-enum { J_R1A = 0, J_R2A, J_R2C, J_S1, J_S2, J_F1A, J_F1C, J_F2A, J_F2C, J_F3, NJOB };
-enum { ARR_C = 0, ARR_H1NEW, ARR_H2NEW, ARR_S12, ARR_Y1, ARR_Y2 };
+enum { J_R1A = 0, J_R2A, J_R2C, J_S1, J_S2, J_F1A, J_F1C, J_F2A, J_F2C, NJOB };
+enum { ARR_C = 0, ARR_H1NEW, ARR_H2NEW, ARR_S12, ARR_Y1 };
 enum { PH_RNN1 = 0, PH_RNN2, PH_FC1, PH_FC2, PH_SAMPLE, PH_H2, NPHASE };     // per-tile counters: who has published what
 // (PH_RNN2 = h1' + h2' is out, which is all fc1 waits for; PH_H2 = rnn2's own new state is out too, for the recurrent products)
-enum { TF_R1 = 0, TF_R2, TF_F1, TF_F2, TF_F3, NTF };                   // accumulator-ready barriers, one per epilogue
+enum { TF_R1 = 0, TF_R2, TF_F1, TF_F2, TF_P3, NTF };                   // accumulator-ready barriers, one per epilogue
 // TMEM accumulator (first column) of each job: 128 lanes = folds, columns = weight rows.  rnn1's gates read X1 + H1,
 // rnn2's X2 + H2 (96 columns each: [r | z | n] x 32 units); fc1, fc2 64 columns each; fc3 reuses fc1's first 32.
 __host__ __device__ inline int job_acc(int jt) {
@@ -98,7 +101,7 @@ __host__ __device__ inline int job_acc(int jt) {
         case J_R2A: case J_R2C: return 192;
         case J_S2: return 288;
         case J_F2A: case J_F2C: return 448;
-        default: return 384;                // fc1, fc3
+        default: return 384;                // fc1
     }
 }
 __host__ __device__ inline int job_stages(int jt) {
@@ -109,11 +112,11 @@ __host__ __device__ inline int job_stages(int jt) {
         default: return HGROUPS;
     }
 }
-__host__ __device__ inline int job_rows(int jt) { return jt == J_F3 ? NCP : jt >= J_F1A ? FC_ROWS : GRU_ROWS; }
-__host__ __device__ inline int job_tiles(int jt) { return jt == J_F3 ? 1 : jt >= J_F1A ? MT_FC : MT_GRU; }
+__host__ __device__ inline int job_rows(int jt) { return jt >= J_F1A ? FC_ROWS : GRU_ROWS; }
+__host__ __device__ inline int job_tiles(int jt) { return jt >= J_F1A ? MT_FC : MT_GRU; }
 __host__ __device__ inline bool job_starts_acc(int jt) { return jt != J_R2C && jt != J_F1C && jt != J_F2C; }
 __host__ __device__ inline int job_commit(int jt) {      // which accumulator-ready barrier a finished job arrives on, or -1
-    return jt == J_R1A ? TF_R1 : jt == J_R2C ? TF_R2 : jt == J_F1C ? TF_F1 : jt == J_F2C ? TF_F2 : jt == J_F3 ? TF_F3 : -1;
+    return jt == J_R1A ? TF_R1 : jt == J_R2C ? TF_R2 : jt == J_F1C ? TF_F1 : jt == J_F2C ? TF_F2 : -1;
 }
 struct StageInfo { int arr, g; };
 __host__ __device__ inline StageInfo stage_info(int jt, int s) {
@@ -125,8 +128,7 @@ __host__ __device__ inline StageInfo stage_info(int jt, int s) {
         case J_F1A: return StageInfo{ARR_C, 1 + s};
         case J_F1C: return StageInfo{ARR_S12, s};
         case J_F2A: return StageInfo{ARR_C, 0};
-        case J_F2C: return StageInfo{ARR_Y1, s};
-        default: return StageInfo{ARR_Y2, s};
+        default: return StageInfo{ARR_Y1, s};          // J_F2C
     }
 }
 
@@ -138,8 +140,10 @@ struct Params {
     int ring_bytes;                // shared memory of the stage ring (the bias rows follow it)
     const uint8_t *Aimg;           // packed weights: job type j at offA[j], [row tile][stage][hi|lo][KC][rows][8] bf16
     int64_t offA[NJOB];
+    int64_t offP3;                 // fc3 columns as an operand: [8 fc row tiles][hi|lo][KC][32 rows][8] bf16, in Aimg
     const float *bias;             // rnn1 [16][2][96] | rnn2 [16][2][96] | fc1 [512] | fc2 [512] | x columns rnn1 [16][96] | rnn2 [16][96] | fc1 [512] | fc3 bias [32]
-    uint8_t *H1[2], *H2[2], *S12, *Y1, *Y2;     // activation operands, [fold tile][group][hi|lo][KC][128][8] bf16
+    uint8_t *H1[2], *H2[2], *S12, *Y1;          // activation operands, [fold tile][group][hi|lo][KC][128][8] bf16
+    float *part3;                  // fc3 partial sums of every fc CTA: [fold tile][8 row tiles][8 groups of 4 logits][128 folds] float4
     const uint8_t *Cop;            // conditioning operand of every step: [S][fold tile][7 groups][hi|lo][KC][128][8] bf16
     uint2 *xp;                     // previous sample of every fold, tagged: {float bits, step it is the input of}, [NTILES * 128]
     float *h1f, *h2f, *y2f;        // debug only: [NTILES * 128][512] fp32 state / fc2 output
@@ -149,6 +153,14 @@ struct Params {
     int exp;                       // debug (WRNN_MMA_EXP): timing experiments that break the results; 0 in production
 };
 
+#ifndef WRNN_STEP_MARK_MASK
+#define WRNN_STEP_MARK_MASK 0x1ff
+#endif
+#define STEP_MARK(k)                                                                                  \
+    do {                                                                                              \
+        if (((WRNN_STEP_MARK_MASK) >> (k)) & 1)                                                       \
+            if (P.prof && t >= P.prof_step && t < P.prof_step + 64) P.prof[192 + (k) * 64 + (t - P.prof_step)] = clock64(); \
+    } while (0)
 #define PROF_MARK(slot)                                                                              \
     do {                                                                                             \
         if (P.prof && t == P.prof_step && (cta == 0 || cta == G - 1)) P.prof[(cta == 0 ? 0 : 64) + (slot)] = clock64(); \
@@ -168,6 +180,13 @@ __device__ __forceinline__ void mbar_arrive(void *b) {
 __device__ __forceinline__ bool mbar_try_wait(void *b, uint32_t parity) {
     uint32_t ok;
     asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(ok) : "r"(smem_u32(b)), "r"(parity) : "memory");
+    return ok != 0;
+}
+// non-blocking test (`try_wait` may suspend the thread): used where the wait is short and on the sample-to-sample chain
+__device__ __forceinline__ bool mbar_test_wait(void *b, uint32_t parity) {
+    uint32_t ok;
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
                  : "=r"(ok) : "r"(smem_u32(b)), "r"(parity) : "memory");
     return ok != 0;
 }
@@ -260,7 +279,12 @@ __device__ __forceinline__ void tile_wait(const GridSync &gs, int phase, int nt,
     while (ld_acquire_u64(c) < want)
         if (give_up(w, t0, spins)) return;
 }
-__device__ __forceinline__ void epi_bar() { bar_sync(1, EPI_THREADS); }
+// Reconverge the warp before the named barrier (see publish() in the kernel: a warp that stays split in two fragments
+// across barriers and collectives runs them in turns on the hardware's forward-progress timer, ~20 k clocks a turn).
+__device__ __forceinline__ void epi_bar() {
+    __syncwarp();
+    bar_sync(1, EPI_THREADS);
+}
 // The previous sample travels as ONE 8-byte word {value, step}: the reader polls the word itself (one L2 round trip once it
 // is there) instead of a counter followed by the data.  Steps only grow, so the slot needs neither reset nor a second buffer:
 // the sampler of step t writes {x, t + 1} after every reader of {.., t} is through (they all precede its own inputs).
@@ -394,8 +418,7 @@ __device__ __forceinline__ const uint8_t *stage_src(const Params &P, StageInfo s
         case ARR_H1NEW: return P.H1[(t + 1) & 1] + (size_t)(nt * HGROUPS + si.g) * ACT_STAGE;
         case ARR_H2NEW: return P.H2[(t + 1) & 1] + (size_t)(nt * HGROUPS + si.g) * ACT_STAGE;
         case ARR_S12: return P.S12 + (size_t)(nt * HGROUPS + si.g) * ACT_STAGE;
-        case ARR_Y1: return P.Y1 + (size_t)(nt * HGROUPS + si.g) * ACT_STAGE;
-        default: return P.Y2 + (size_t)(nt * HGROUPS + si.g) * ACT_STAGE;
+        default: return P.Y1 + (size_t)(nt * HGROUPS + si.g) * ACT_STAGE;
     }
 }
 
@@ -538,6 +561,30 @@ __device__ __forceinline__ void issue_job(int jt, Issue &is, Watch &w, long long
     if (tf >= 0) umma_commit(&is.bar_tf[tf]);        // this accumulator (and every MMA issued before) is complete
 }
 
+// fc3 contribution of an fc CTA: 128 folds x 32 logits = [128 x 64] (this CTA's fc2 outputs, written to shared memory by
+// its epilogue) . [32 x 64]^T (its columns of fc3, resident), 4 k-steps x 3 MMAs into fc1's idle accumulator columns.
+__device__ __forceinline__ void issue_p3(Issue &is, uint32_t p3a, uint32_t p3b, uint64_t *bar_y2, uint32_t par, Watch &w) {
+    w.site = 0x4e;
+    if (!w.dead && !mbar_test_wait(bar_y2, par)) {       // short wait on the chain: spin, do not sleep
+        const long long t0 = clock64();
+        unsigned spins = 0;
+        while (!mbar_test_wait(bar_y2, par))
+            if (give_up(w, t0, spins)) break;
+    }
+    tc_fence_after();
+    const uint64_t dX0 = make_desc(0, FT * 16u, 128), dW0 = make_desc(0, NCP * 16u, 128);
+    const uint32_t aX = p3a >> 4, aW = p3b >> 4, d = is.tb + (uint32_t)job_acc(J_F1C), idesc = make_idesc(FT, NCP);
+#pragma unroll
+    for (int ks = 0; ks < KC / 2; ks++) {
+        const uint64_t xh = dX0 + (aX + ks * 2u * FT), xl = dX0 + (aX + KC * FT + ks * 2u * FT);
+        const uint64_t wh = dW0 + (aW + ks * 2u * NCP), wl = dW0 + (aW + KC * NCP + ks * 2u * NCP);
+        umma_bf16(d, xh, wh, idesc, ks == 0 ? 0u : 1u);
+        umma_bf16(d, xh, wl, idesc, 1u);
+        umma_bf16(d, xl, wh, idesc, 1u);
+    }
+    umma_commit(&is.bar_tf[TF_P3]);
+}
+
 // ---------------------------------------------------------------------------- epilogues (256 threads, warps 2..9)
 // Accumulators are [128 folds (TMEM lanes)] x [weight rows (columns)], so a thread owns ONE fold (lane 32 q + lane of the
 // warp's lane quarter q = warp % 4) and reads the r, z, n columns of a unit straight from its own lane: no shared-memory
@@ -619,14 +666,11 @@ __device__ __forceinline__ void store_state2(const Params &P, int mt, int nt, in
     }
 }
 
-// fc1 / fc2 + ReLU (:217-221): 64 rows = 64 columns, 32 per thread, out as the bf16 hi/lo operand of the next layer
-template <int LAYER>
-__device__ __forceinline__ void epi_fc(const Params &P, int mt, int nt, uint32_t tb, const float *sb, float xp, int q, int part, int lane) {
+// fc1 + ReLU (:217-218): 64 rows = 64 columns, RPT per thread, out as the bf16 hi/lo operand of fc2
+__device__ __forceinline__ void epi_fc1(const Params &P, int mt, int nt, uint32_t tb, const float *sb, float xp, int q, int part, int lane) {
     const int fi = q * 32 + lane, r0 = part * RPT, gr = mt * FC_ROWS + r0;
-    const size_t fold = (size_t)nt * FT + fi;
-    const float *bb = sb + SB_F + LAYER * FC_ROWS + r0, *wx = sb + SB_XF + r0;
-    uint8_t *out = LAYER == 0 ? P.Y1 : P.Y2;
-    const uint32_t col = tb + ((uint32_t)(q * 32) << 16) + (uint32_t)job_acc(LAYER == 0 ? J_F1C : J_F2C) + r0;
+    const float *bb = sb + SB_F + r0, *wx = sb + SB_XF + r0;
+    const uint32_t col = tb + ((uint32_t)(q * 32) << 16) + (uint32_t)job_acc(J_F1C) + r0;
 #pragma unroll
     for (int g = 0; g < RPT / 8; g += 2) {
         uint32_t a[8], b[8];
@@ -636,32 +680,78 @@ __device__ __forceinline__ void epi_fc(const Params &P, int mt, int nt, uint32_t
         float va[8], vb[8];
 #pragma unroll
         for (int i = 0; i < 8; i++) {
-            float pa = __uint_as_float(a[i]) + bb[8 * g + i], pb = __uint_as_float(b[i]) + bb[8 * g + 8 + i];
-            if (LAYER == 0) { pa = fmaf(wx[8 * g + i], xp, pa); pb = fmaf(wx[8 * g + 8 + i], xp, pb); }
-            va[i] = fmaxf(pa, 0.f);
-            vb[i] = fmaxf(pb, 0.f);
+            va[i] = fmaxf(fmaf(wx[8 * g + i], xp, __uint_as_float(a[i]) + bb[8 * g + i]), 0.f);
+            vb[i] = fmaxf(fmaf(wx[8 * g + 8 + i], xp, __uint_as_float(b[i]) + bb[8 * g + 8 + i]), 0.f);
         }
         uint4 hi, lo;
         split8(va, hi, lo);
-        *reinterpret_cast<uint4 *>(out + b_slot(FT, HGROUPS, nt, (gr >> 3) + g, fi, 0)) = hi;
-        *reinterpret_cast<uint4 *>(out + b_slot(FT, HGROUPS, nt, (gr >> 3) + g, fi, 1)) = lo;
+        *reinterpret_cast<uint4 *>(P.Y1 + b_slot(FT, HGROUPS, nt, (gr >> 3) + g, fi, 0)) = hi;
+        *reinterpret_cast<uint4 *>(P.Y1 + b_slot(FT, HGROUPS, nt, (gr >> 3) + g, fi, 1)) = lo;
         split8(vb, hi, lo);
-        *reinterpret_cast<uint4 *>(out + b_slot(FT, HGROUPS, nt, (gr >> 3) + g + 1, fi, 0)) = hi;
-        *reinterpret_cast<uint4 *>(out + b_slot(FT, HGROUPS, nt, (gr >> 3) + g + 1, fi, 1)) = lo;
-        if (LAYER == 1 && P.dbg_state) {
+        *reinterpret_cast<uint4 *>(P.Y1 + b_slot(FT, HGROUPS, nt, (gr >> 3) + g + 1, fi, 0)) = hi;
+        *reinterpret_cast<uint4 *>(P.Y1 + b_slot(FT, HGROUPS, nt, (gr >> 3) + g + 1, fi, 1)) = lo;
+    }
+}
+
+// fc2 + ReLU (:220-221), first half of the fused fc2 / fc3 epilogue.  The 64 outputs of a fold never leave the SM: they
+// go to shared memory as the A operand (K = 64) of a 12-MMA job against this CTA's 64 columns of fc3 (:223), whose
+// accumulator (128 folds x 32 logits) is this CTA's contribution to the fold's logits (second half: epi_fc3_part).  The
+// sampler adds the eight contributions of a tile instead of running a sixth MMA phase on an operand that would have to be
+// published and gathered first: one hand-over and 8 pipeline stages less per sample.
+__device__ __forceinline__ void epi_fc2(const Params &P, int mt, int nt, uint32_t tb, const float *sb, uint8_t *p3a, int q, int part, int lane) {
+    const int fi = q * 32 + lane, r0 = part * RPT, gr = mt * FC_ROWS + r0;
+    const size_t fold = (size_t)nt * FT + fi;
+    const float *bb = sb + SB_F + FC_ROWS + r0;
+    const uint32_t col = tb + ((uint32_t)(q * 32) << 16) + (uint32_t)job_acc(J_F2C) + r0;
+#pragma unroll
+    for (int g = 0; g < RPT / 8; g += 2) {
+        uint32_t a[8], b[8];
+        tmem_ld8_nowait(col + 8 * g, a);
+        tmem_ld8_nowait(col + 8 * g + 8, b);
+        tmem_ld_wait();
+        float va[8], vb[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            va[i] = fmaxf(__uint_as_float(a[i]) + bb[8 * g + i], 0.f);
+            vb[i] = fmaxf(__uint_as_float(b[i]) + bb[8 * g + 8 + i], 0.f);
+        }
+        if (P.dbg_state) {
             float4 *dst = reinterpret_cast<float4 *>(P.y2f + fold * FCD + gr + 8 * g);
             dst[0] = make_float4(va[0], va[1], va[2], va[3]);
             dst[1] = make_float4(va[4], va[5], va[6], va[7]);
             dst[2] = make_float4(vb[0], vb[1], vb[2], vb[3]);
             dst[3] = make_float4(vb[4], vb[5], vb[6], vb[7]);
         }
+        // [hi|lo][k-chunk][fold][8]: consecutive lanes, consecutive 16-byte words
+        const int chunk = (r0 >> 3) + g;
+        uint4 hi, lo;
+        split8(va, hi, lo);
+        *reinterpret_cast<uint4 *>(p3a + (size_t)(chunk * FT + fi) * 16) = hi;
+        *reinterpret_cast<uint4 *>(p3a + (size_t)((KC + chunk) * FT + fi) * 16) = lo;
+        split8(vb, hi, lo);
+        *reinterpret_cast<uint4 *>(p3a + (size_t)((chunk + 1) * FT + fi) * 16) = hi;
+        *reinterpret_cast<uint4 *>(p3a + (size_t)((KC + chunk + 1) * FT + fi) * 16) = lo;
     }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // generic shared-memory stores, read by the tensor core
+}
+// second half: the contribution (128 folds x 32 logits) from TMEM to global, [tile][row tile][group of 4 logits][fold]:
+// consecutive folds are consecutive 16-byte words on the writing and on the reading side
+__device__ __forceinline__ void epi_fc3_part(const Params &P, int mt, int nt, uint32_t tb, int q, int part, int lane) {
+    if (part != 0) return;
+    const int fi = q * 32 + lane;
+    uint32_t acc[32];
+    tmem_ld32(tb + ((uint32_t)(q * 32) << 16) + (uint32_t)job_acc(J_F1C), acc);      // fc1's columns, free until the next step's F1A
+    float4 *dst = reinterpret_cast<float4 *>(P.part3) + ((size_t)nt * MT_FC + mt) * (NCP / 4) * FT + fi;
+#pragma unroll
+    for (int i = 0; i < NCP / 4; i++)
+        dst[(size_t)i * FT] = make_float4(__uint_as_float(acc[4 * i]), __uint_as_float(acc[4 * i + 1]), __uint_as_float(acc[4 * i + 2]),
+                                          __uint_as_float(acc[4 * i + 3]));
 }
 
 // Noise of (step t, fold of this thread), injected or Philox, reduced to the terms the draw uses.  Off the chain: called
 // before the wait for fc3's accumulator.
-__device__ __forceinline__ void mol_noise_thread(const Params &P, int nt, int64_t t, int q, int lane, float (&gum)[NMIX], float &lgt) {
-    const int64_t b = (int64_t)nt * FT + q * 32 + lane;
+__device__ __forceinline__ void mol_noise_thread(const Params &P, int nt, int64_t t, int fi, float (&gum)[NMIX], float &lgt) {
+    const int64_t b = (int64_t)nt * FT + fi;
     float u1[NMIX], u2;
     if (b >= P.a.B) {
 #pragma unroll
@@ -691,45 +781,69 @@ __device__ __forceinline__ void mol_noise_thread(const Params &P, int nt, int64_
     lgt = logf(u2) - logf(1.f - u2);
 }
 
-// fc3 (:223) + MoL draw (utils/distribution.py:87-123): the 30 logits of a fold are 30 columns of its own TMEM lane.
-// Called by the four warps with part == 0 (one per lane quarter).  Writes the sample, the mixture pick and the previous
-// sample of step t + 1.
-__device__ __forceinline__ void epi_sample(const Params &P, int nt, int64_t t, uint32_t tb, const float *sb, const float (&gum)[NMIX],
-                                           float lgt, int q, int lane) {
-    const int fi = q * 32 + lane;
+// fc3 (:223) summed up + MoL draw (utils/distribution.py:87-123), once the tile has published fc2.  The fc CTAs of row
+// tiles 0 .. 3 each sample a quarter (32 folds) of the tile, so that a CTA gathers 32 KB, not 128.  Lane = (contribution
+// m = lane / 4, fold = 4 * warp + lane % 4): a thread loads the 8 x 16 bytes of one (fold, contribution), three
+// xor-shuffles add the eight contributions (fixed order: deterministic), the lanes with m == 0 add the bias, draw, and
+// write the sample, the mixture pick and the previous sample of step t + 1.
+__device__ __forceinline__ int sampler_fold(int quarter, int ewarp, int lane) { return quarter * 32 + (ewarp & 7) * 4 + (lane & 3); }
+__device__ __forceinline__ void epi_sample(const Params &P, int nt, int quarter, int64_t t, const float *sb, const float (&gum)[NMIX], float lgt,
+                                           int ewarp, int lane, long long *pm = nullptr) {
+    if (ewarp >= 8) return;                                  // warp-uniform (EPI_PARTS > 2: the first eight epilogue warps sample)
+    const int m = lane >> 2, fi = sampler_fold(quarter, ewarp, lane);
     const int64_t b = (int64_t)nt * FT + fi, S = P.a.S;
-    uint32_t acc[32];
-    tmem_ld32(tb + ((uint32_t)(q * 32) << 16) + (uint32_t)job_acc(J_F3), acc);
-    uint2 *xnext = P.xp + b;
-    if (b >= P.a.B) { *xnext = make_uint2(0u, (uint32_t)(t + 1)); return; }            // padded fold of the last tile
+    const float4 *src = reinterpret_cast<const float4 *>(P.part3) + ((size_t)nt * MT_FC + m) * (NCP / 4) * FT + fi;
+    if (pm) pm[0] = clock64();
+    float4 pv[NCP / 4];
+#pragma unroll
+    for (int i = 0; i < NCP / 4; i++) pv[i] = __ldcg(src + (size_t)i * FT);
     float lg[NCP];
 #pragma unroll
-    for (int i = 0; i < NCP; i++) lg[i] = __uint_as_float(acc[i]) + sb[SB_B3 + i];
-    const bool live = t < P.a.fold_len[b];
-    if (P.a.logits_out && live) {
-        float *dst = P.a.logits_out + ((size_t)b * S + t) * P.NC;
+    for (int i = 0; i < NCP / 4; i++) { lg[4 * i] = pv[i].x; lg[4 * i + 1] = pv[i].y; lg[4 * i + 2] = pv[i].z; lg[4 * i + 3] = pv[i].w; }
 #pragma unroll
-        for (int i = 0; i < 3 * NMIX; i++) dst[i] = lg[i];
+    for (int o = 4; o <= 16; o <<= 1)
+#pragma unroll
+        for (int i = 0; i < 3 * NMIX; i++) lg[i] += __shfl_xor_sync(0xffffffffu, lg[i], o);
+    // Only the lanes with m == 0 draw.  No early return: lanes that left a divergent region early would run ahead to the
+    // next CTA barrier, and a `bar.sync` reached by part of a warp left the rest of it unscheduled until the hardware's
+    // forward-progress timer fired (~20 k clocks, seen as steps of 52 k / 73 k / 93 k clocks): reconverge explicitly.
+    if (pm) pm[1] = clock64();
+    if (m == 0) {
+        uint2 *xnext = P.xp + b;
+        if (b >= P.a.B) {
+            *xnext = make_uint2(0u, (uint32_t)(t + 1));            // padded fold of the last tile
+        } else {
+#pragma unroll
+            for (int i = 0; i < 3 * NMIX; i++) lg[i] += sb[SB_B3 + i];
+            const bool live = t < P.a.fold_len[b];
+            if (P.a.logits_out && live) {
+                float *dst = P.a.logits_out + ((size_t)b * S + t) * P.NC;
+#pragma unroll
+                for (int i = 0; i < 3 * NMIX; i++) dst[i] = lg[i];
+            }
+            int pick = 0;
+            float xv = mol_sample_thread(lg, gum, lgt, &pick);
+            if (live) {
+                P.a.samples[(size_t)b * S + t] = xv;
+                P.a.picks[(size_t)b * S + t] = pick;
+            } else {
+                xv = 0.f;
+            }
+            if (P.a.teacher) xv = t + 1 < S ? P.a.teacher[(size_t)b * S + t + 1] : 0.f;
+            *xnext = make_uint2(__float_as_uint(xv), (uint32_t)(t + 1));
+        }
     }
-    int pick = 0;
-    float xv = mol_sample_thread(lg, gum, lgt, &pick);
-    if (live) {
-        P.a.samples[(size_t)b * S + t] = xv;
-        P.a.picks[(size_t)b * S + t] = pick;
-    } else {
-        xv = 0.f;
-    }
-    if (P.a.teacher) xv = t + 1 < S ? P.a.teacher[(size_t)b * S + t + 1] : 0.f;
-    *xnext = make_uint2(__float_as_uint(xv), (uint32_t)(t + 1));
+    __syncwarp();
 }
 
 __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
     extern __shared__ __align__(1024) uint8_t smem[];
-    __shared__ __align__(8) uint64_t bar_full[MAXSTAGE], bar_empty[MAXSTAGE], bar_tf[NTF], bar_done;
+    __shared__ __align__(8) uint64_t bar_full[MAXSTAGE], bar_empty[MAXSTAGE], bar_tf[NTF], bar_done, bar_y2;
     __shared__ uint32_t tmem_base_s;
     __shared__ int dead_s;
     uint8_t *stages = smem;
-    float *sbias = reinterpret_cast<float *>(smem + P.ring_bytes);      // this CTA's bias rows / previous-sample columns (SB_*)
+    uint8_t *p3a = smem + P.ring_bytes, *p3b = p3a + P3_A;               // fc3-inside-fc operands (fc CTAs)
+    float *sbias = reinterpret_cast<float *>(p3b + P3_B);               // this CTA's bias rows / previous-sample columns (SB_*)
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, cta = blockIdx.x;
     const int G = P.G;
@@ -738,13 +852,14 @@ __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
     // the fc CTA of row tile 0 also runs the tile's fc3 job and its sampler
     const bool has_gru = cta < MT_GRU * P.NTILES, has_fc = G - 1 - cta < MT_FC * P.NTILES;
     const int mt_g = cta % MT_GRU, nt_g = cta / MT_GRU, mt_f = (G - 1 - cta) % MT_FC, nt_f = (G - 1 - cta) / MT_FC;
-    const bool has_f3 = has_fc && mt_f == 0;
+    const bool has_f3 = has_fc && mt_f < 4;          // row tiles 0 .. 3 of the fc CTAs each sample a quarter of the tile's folds
     if (!has_gru && !has_fc) return;
 
     if (tid == 0) {
         for (int i = 0; i < MAXSTAGE; i++) { mbar_init(&bar_full[i], 1); mbar_init(&bar_empty[i], 1); }
         for (int i = 0; i < NTF; i++) mbar_init(&bar_tf[i], 1);
         mbar_init(&bar_done, 1);
+        mbar_init(&bar_y2, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) tmem_alloc(&tmem_base_s, TMEM_COLS);
@@ -769,6 +884,11 @@ __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
             v = b3[i - SB_B3];
         }
         sbias[i] = v;
+    }
+    if (has_fc) {       // this CTA's 64 columns of fc3 as an MMA operand; read by the tensor core (async proxy) from step 0 on
+        const uint4 *src = reinterpret_cast<const uint4 *>(P.Aimg + P.offP3 + (size_t)mt_f * P3_B);
+        for (int i = tid; i < P3_B / 16; i += THREADS) reinterpret_cast<uint4 *>(p3b)[i] = src[i];
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
     tc_fence_before();
     __syncthreads();
@@ -809,17 +929,13 @@ __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
                     PROF_MARK(4);
                     produce_job(P, J_F2C, mt_f, nt_f, t, PH_FC1, t + 1, pp, lane, w, pa ? pa + 3 : nullptr, pa ? prof_base + 19 : nullptr);
                     PROF_MARK(5);
-                    if (has_f3) {
-                        produce_job(P, J_F3, 0, nt_f, t, PH_FC2, t + 1, pp, lane, w, pa ? pa + 4 : nullptr, pa ? prof_base + 31 : nullptr);
-                        PROF_MARK(6);
-                        // fc3's accumulator shares fc1's columns: the sampler must have read it
-                        if (more) produce_job(P, J_F1A, mt_f, nt_f, t + 1, PH_SAMPLE, t + 1, pp, lane, w);
-                        if (more) produce_job(P, J_F2A, mt_f, nt_f, t + 1, -1, 0, pp, lane, w);
-                    } else if (more) {
-                        produce_job(P, J_F1A, mt_f, nt_f, t + 1, -1, 0, pp, lane, w);
-                        // fc2's accumulator is free once this CTA's own fc2 epilogue is through: implied by the tile's counter
-                        produce_job(P, J_F2A, mt_f, nt_f, t + 1, PH_FC2, t + 1, pp, lane, w);
+                    if (more) {
+                        // fc1's accumulator columns hold the fc3 contribution until this CTA's own epilogue has stored it, fc2's
+                        // until it has been read: both implied by the tile's fc2 counter
+                        produce_job(P, J_F1A, mt_f, nt_f, t + 1, PH_FC2, t + 1, pp, lane, w);
+                        produce_job(P, J_F2A, mt_f, nt_f, t + 1, -1, 0, pp, lane, w);
                     }
+                    PROF_MARK(6);
                 }
                 if (has_gru && more) {         // nothing reads the recurrent products of the step after the last
                     produce_job(P, J_S2, mt_g, nt_g, t, PH_H2, t + 1, pp, lane, w, pa ? pa + 5 : nullptr);
@@ -857,10 +973,8 @@ __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
                     PROF_MARK(12);
                     issue_job(J_F2C, is, w, ma ? ma + 9 : nullptr);
                     PROF_MARK(13);
-                    if (has_f3) {
-                        issue_job(J_F3, is, w, ma ? ma + 12 : nullptr);
-                        PROF_MARK(14);
-                    }
+                    issue_p3(is, smem_u32(p3a), smem_u32(p3b), &bar_y2, (uint32_t)(t & 1), w);
+                    PROF_MARK(14);
                     if (more) {
                         issue_job(J_F1A, is, w);
                         issue_job(J_F2A, is, w);
@@ -892,6 +1006,14 @@ __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
             fence_proxy_async_global();
             epi_bar();
             if (etid == 0) red_release_add_u64(tile_counter(P.gs, phase, nt), 1ull);
+            // Close the one-lane region here, and keep one-lane regions short everywhere in the epilogue (the sampler's poll
+            // of the tile counter is done by a whole warp).  With a long one-lane region after this point (lane 0 polling
+            // while lanes 1..31 went on to the next barrier), the first epilogue warp stayed split in two fragments through
+            // the sampler's barrier, loads and shuffles, and the fragments took turns on the hardware's forward-progress
+            // timer: steps of 52 k / 73 k / 93 k clocks instead of 52 k (36 us instead of 28.5 us per step), in some builds
+            // and not in others: a compiler barrier or an unrelated branch in between was enough to hide it, a 20 ns sleep
+            // of lane 0 made it 40 us.
+            __syncwarp();
         };
         auto wait_acc = [&](int tf) {
             w.site = 0x50 + tf;
@@ -907,49 +1029,67 @@ __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
                 w.site = 0x60;
                 const float xp = wait_prev_sample(P.xp + (size_t)nt_g * FT + fi, t, w);      // the sample of step t - 1 is out
                 if (etid == 0) PROF_MARK(21);
+                if (etid == 0 && cta == 0) STEP_MARK(5);
                 __syncwarp();
                 epi_gru<0>(P, mt_g, nt_g, t, tb, sbias, xp, hst1, h1new, q, part, lane, (profiled_cta && t == P.prof_step && etid == 0) ? prof_base + 58 : nullptr);
                 tc_fence_before();
                 if (etid == 0) PROF_MARK(22);
                 publish(PH_RNN1, nt_g);
                 if (etid == 0) PROF_MARK(23);
+                if (etid == 0 && cta == 0) STEP_MARK(6);
                 wait_acc(TF_R2);
                 if (etid == 0) PROF_MARK(24);
+                if (etid == 0 && cta == 0) STEP_MARK(7);
                 epi_gru<1>(P, mt_g, nt_g, t, tb, sbias, xp, hst2, h1new, q, part, lane);
                 tc_fence_before();
                 if (etid == 0) PROF_MARK(25);
                 publish(PH_RNN2, nt_g);
                 if (etid == 0) PROF_MARK(26);
+                if (etid == 0 && cta == 0) STEP_MARK(8);
                 store_state2(P, mt_g, nt_g, t, hst2, q, part, lane);
                 publish(PH_H2, nt_g);
             }
             if (has_fc) {
                 wait_acc(TF_F1);
                 if (etid == 0) PROF_MARK(27);
+                if (etid == 0 && cta == G - 1) STEP_MARK(0);
                 // published before rnn1 of this step began; the loads that filled fc1's stages were ordered behind rnn2's counter
                 const float xp = __uint_as_float(ld_volatile_u2(P.xp + (size_t)nt_f * FT + fi).x);
-                epi_fc<0>(P, mt_f, nt_f, tb, sbias, xp, q, part, lane);
+                epi_fc1(P, mt_f, nt_f, tb, sbias, xp, q, part, lane);
                 tc_fence_before();
                 publish(PH_FC1, nt_f);
                 if (etid == 0) PROF_MARK(28);
+                float gum[NMIX], lgt = 0.f;
+                if (has_f3 && ewarp < 8 && (lane >> 2) == 0) mol_noise_thread(P, nt_f, t, sampler_fold(mt_f, ewarp, lane), gum, lgt);      // off the chain
+                __syncwarp();
                 wait_acc(TF_F2);
                 if (etid == 0) PROF_MARK(29);
-                epi_fc<1>(P, mt_f, nt_f, tb, sbias, 0.f, q, part, lane);
+                if (etid == 0 && cta == G - 1) STEP_MARK(1);
+                epi_fc2(P, mt_f, nt_f, tb, sbias, p3a, q, part, lane);
+                tc_fence_before();
+                epi_bar();
+                if (etid == 0) mbar_arrive(&bar_y2);                  // the MMA thread forms this CTA's fc3 contribution
+                wait_acc(TF_P3);
+                epi_fc3_part(P, mt_f, nt_f, tb, q, part, lane);
                 tc_fence_before();
                 publish(PH_FC2, nt_f);
                 if (etid == 0) PROF_MARK(30);
+                if (etid == 0 && cta == G - 1) STEP_MARK(2);
+                __syncwarp();                                            // see publish(): no one-lane region may reach the sampler
                 if (has_f3) {
-                    float gum[NMIX], lgt = 0.f;
-                    if (part == 0) mol_noise_thread(P, nt_f, t, q, lane, gum, lgt);
-                    wait_acc(TF_F3);
-                    if (etid == 0) PROF_MARK(16);
-                    if (part == 0) epi_sample(P, nt_f, t, tb, sbias, gum, lgt, q, lane);
-                    tc_fence_before();
-                    if (etid == 0) PROF_MARK(17);
-                    __threadfence();
+                    if (ewarp == 0) {                                   // the whole warp polls (one request): no one-lane region
+                        w.site = 0x61;
+                        tile_wait(P.gs, PH_FC2, nt_f, t + 1, w);       // the eight contributions to fc3 are out
+                        if (lane == 0) PROF_MARK(16);
+                        if (lane == 0 && cta == G - 1) STEP_MARK(3);
+                        __syncwarp();
+                    }
                     epi_bar();
-                    if (etid == 0) red_release_add_u64(tile_counter(P.gs, PH_SAMPLE, nt_f), 1ull);
-                    if (etid == 0) PROF_MARK(18);
+                    epi_sample(P, nt_f, mt_f, t, sbias, gum, lgt, ewarp, lane, (profiled_cta && t == P.prof_step && etid == 0) ? prof_base + 62 : nullptr);
+                    if (etid == 0) PROF_MARK(17);
+                    if (etid == 0 && profiled_cta && t == P.prof_step + 100) prof_base[61] = clock64();      // 100 steps later: the period
+                    if (etid == 0 && P.prof && cta == G - 1 && t >= P.prof_step - 8 && t < P.prof_step + 56) P.prof[128 + (t - P.prof_step + 8)] = clock64();
+                    if (etid == 0 && cta == G - 1) STEP_MARK(4);
                 }
             }
             tfpar ^= 1u;
@@ -993,7 +1133,7 @@ bool mma_supported(const wrnn_handle *h) {
     return h->mma.ok && d.mode == WRNN_MODE_MOL && d.H == mma::H && d.FC == mma::FCD && d.A == mma::AUX && d.F == mma::FEAT &&
            d.NC == 3 * mma::NMIX;
 }
-int mma_min_folds() { return 61; }      // measured (scripts/mma_crossover.py): 36.4 us per step whatever the fold count; three resident groups of 20 take 35.7
+int mma_min_folds() { return 41; }      // measured (scripts/mma_crossover.py): 27.4 us per step up to 120 folds; two resident groups of 20 take 23.8, three 35.7
 
 int mma_plan(wrnn_handle *h) {
     using namespace mma;
@@ -1059,8 +1199,7 @@ int mma_plan(wrnn_handle *h) {
             case J_S1: return W1h->v[(size_t)grow * H + k];
             case J_S2: return W2h->v[(size_t)grow * H + k];
             case J_F1C: return F1->v[(size_t)grow * (H + AUX) + k];
-            case J_F2C: return F2->v[(size_t)grow * (FCD + AUX) + k];
-            default: return grow < d.NC ? F3->v[(size_t)grow * FCD + k] : 0.0;       // fc3, rows padded to 32
+            default: return F2->v[(size_t)grow * (FCD + AUX) + k];
         }
     };
     auto cond_layer = [](int jt) { return jt == J_R1A ? 0 : jt == J_R2A ? 1 : jt == J_F1A ? 2 : 3; };     // J_F2A: 3
@@ -1069,7 +1208,20 @@ int mma_plan(wrnn_handle *h) {
         pl.offA[jt] = (int64_t)total;
         total += (size_t)job_tiles(jt) * job_stages(jt) * 2 * KC * job_rows(jt) * 16;
     }
+    pl.offP3 = (int64_t)total;
+    total += (size_t)MT_FC * P3_B;
     std::vector<uint16_t> img(total / 2, 0);
+    for (int mt = 0; mt < MT_FC; mt++) {      // fc3 columns of fc2 row tile mt: [hi|lo][k-chunk][32 rows][8], rows 30, 31 zero
+        uint16_t *blk = img.data() + (size_t)pl.offP3 / 2 + (size_t)mt * (P3_B / 2);
+        for (int r = 0; r < d.NC; r++)
+            for (int k = 0; k < FC_ROWS; k++) {
+                const float wf = F3->v[(size_t)r * FCD + mt * FC_ROWS + k];
+                const uint16_t hi = f2bf(wf), lo = f2bf(wf - bf2f(hi));
+                const size_t o = ((size_t)(k / 8) * NCP + r) * 8 + k % 8;
+                blk[o] = hi;
+                blk[(size_t)KC * NCP * 8 + o] = lo;
+            }
+    }
     for (int jt = 0; jt < NJOB; jt++) {
         const int rows = job_rows(jt), mts = job_tiles(jt), nst = job_stages(jt);
         for (int mt = 0; mt < mts; mt++)
@@ -1157,20 +1309,23 @@ int mma_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
     }
     P.Aimg = pl.Aimg;
     for (int j = 0; j < NJOB; j++) P.offA[j] = pl.offA[j];
+    P.offP3 = pl.offP3;
     P.bias = pl.bias;
     const size_t NF = (size_t)P.NTILES * FT;
     const size_t bH = NF * H * 4, bF = NF * H * sizeof(float);       // operands: hi + lo bf16 = 4 B per element
     const size_t bX = (NF * sizeof(uint2) + 1023) / 1024 * 1024;
     const size_t bC = (size_t)a.S * P.NTILES * CGROUPS * ACT_STAGE;  // conditioning operand of every step
-    const size_t state = 7 * bH + bX + 3 * bF;
+    const size_t bP = (size_t)P.NTILES * MT_FC * FT * NCP * sizeof(float);
+    const size_t state = 6 * bH + bX + 3 * bF + bP;
     WRNN_TRY(ws_reserve(h, h->ws_act, state + bC + 4096));
     WRNN_CUDA(h, cudaMemsetAsync(h->ws_act.p, 0, state, st));       // h1 = h2 = 0 (:194-195), padded folds stay zero
     uint8_t *p8 = (uint8_t *)h->ws_act.p;
     P.H1[0] = p8; p8 += bH; P.H1[1] = p8; p8 += bH;
     P.H2[0] = p8; p8 += bH; P.H2[1] = p8; p8 += bH;
-    P.S12 = p8; p8 += bH; P.Y1 = p8; p8 += bH; P.Y2 = p8; p8 += bH;
+    P.S12 = p8; p8 += bH; P.Y1 = p8; p8 += bH;
     P.xp = (uint2 *)p8; p8 += bX;
     P.h1f = (float *)p8; p8 += bF; P.h2f = (float *)p8; p8 += bF; P.y2f = (float *)p8; p8 += bF;
+    P.part3 = (float *)p8; p8 += bP;
     uint8_t *Cop = p8;
     P.Cop = Cop;
     h->mma_dbg[0] = P.h1f; h->mma_dbg[1] = P.h2f; h->mma_dbg[2] = P.y2f;
@@ -1196,8 +1351,8 @@ int mma_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
     P.exp = getenv("WRNN_MMA_EXP") ? atoi(getenv("WRNN_MMA_EXP")) : 0;
     const char *pe = getenv("WRNN_MMA_PROF");
     if (pe) {
-        WRNN_TRY(ws_reserve(h, h->ws_prof, 128 * sizeof(long long)));
-        WRNN_CUDA(h, cudaMemsetAsync(h->ws_prof.p, 0, 128 * sizeof(long long), st));
+        WRNN_TRY(ws_reserve(h, h->ws_prof, 832 * sizeof(long long)));
+        WRNN_CUDA(h, cudaMemsetAsync(h->ws_prof.p, 0, 832 * sizeof(long long), st));
         P.prof = (long long *)h->ws_prof.p;
         P.prof_step = std::min<int64_t>(atoi(pe), P.steps_run - 1);
     }
@@ -1205,9 +1360,22 @@ int mma_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
     WRNN_CUDA(h, cudaLaunchCooperativeKernel((const void *)mma_loop_kernel, dim3(P.G), dim3(THREADS), args, pl.smem_bytes, st));
     h->launches++;
     if (pe) {     // debug: print the timeline of the profiled step (clocks relative to the CTA's first event of the step)
-        std::vector<long long> pr(128);
+        std::vector<long long> pr(832);
         WRNN_CUDA(h, cudaStreamSynchronize(st));
-        WRNN_CUDA(h, cudaMemcpy(pr.data(), P.prof, 128 * sizeof(long long), cudaMemcpyDeviceToHost));
+        WRNN_CUDA(h, cudaMemcpy(pr.data(), P.prof, 832 * sizeof(long long), cudaMemcpyDeviceToHost));
+        if (getenv("WRNN_MMA_PROF_STEPS")) {
+            fprintf(stderr, "[mma steps] per step: interval to the same event of the step before | CTA G-1 intervals: fc1 ready->fc2 ready->published->seen->drawn | CTA 0: seen->rnn1 pub->rnn2 ready->rnn2 pub\n");
+            for (int i = 1; i < 64; i++) {
+                auto v = [&](int k) { return pr[192 + k * 64 + i]; };
+                fprintf(stderr, "[mma steps] %2d  period %6lld | %6lld %6lld %6lld %6lld | %6lld %6lld %6lld | fc1 ready - drawn(prev) %6lld\n", i, v(4) - pr[192 + 4 * 64 + i - 1],
+                        v(1) - v(0), v(2) - v(1), v(3) - v(2), v(4) - v(3), v(6) - v(5), v(7) - v(6), v(8) - v(7), v(0) - pr[192 + 4 * 64 + i - 1]);
+            }
+        }
+        {
+            fprintf(stderr, "[mma prof] clocks between consecutive draws of CTA G-1, from 7 steps before the profiled step (its own duration is the 8th number):");
+            for (int i = 1; i < 64 && pr[128 + i]; i++) fprintf(stderr, " %lld", pr[128 + i] - pr[128 + i - 1]);
+            fprintf(stderr, "\n");
+        }
         static const char *names[32] = {
             "producer: step begin", "producer: rnn2 issued", "producer: recurrent-1 + next rnn1 cond issued", "producer: fc begin",
             "producer: fc1 issued", "producer: fc2 issued", "producer: fc3 issued", "producer: recurrent-2 + next rnn2 cond issued", "producer: rnn1 of the tile seen (rnn2 loads start)",
@@ -1230,9 +1398,11 @@ int mma_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
                 if (q[i]) ev.push_back({q[i] - t0, i});
             std::sort(ev.begin(), ev.end());
             for (auto &e : ev) fprintf(stderr, "[mma prof]   %8lld  %s\n", e.first, names[e.second]);
+            if (q[61] && q[17]) fprintf(stderr, "[mma prof]   100 steps later the sampler is at +%lld clk: %lld clk per step\n", q[61] - q[17], (q[61] - q[17]) / 100);
+            if (q[62]) fprintf(stderr, "[mma prof]   inside the sampler (warp 2): past the barrier %lld, contributions added %lld (same clock)\n", q[62] - t0, q[63] - t0);
             if (q[58]) fprintf(stderr, "[mma prof]   inside rnn1 gates (warp 2): accumulators in registers %lld, gate math done %lld (same clock)\n", q[58] - t0, q[59] - t0);
             static const char *jn[6] = {"rnn2", "recurrent-1", "fc1", "fc2", "fc3", "recurrent-2"};
-            static const int jtype[6] = {J_R2C, J_S1, J_F1C, J_F2C, J_F3, J_S2};
+            static const int jtype[6] = {J_R2C, J_S1, J_F1C, J_F2C, J_F2C, J_S2};
             for (int j = 0; j < 6; j++)
                 if (q[40 + 3 * j + 1])
                     fprintf(stderr, "[mma prof]   %-12s %2d stages: MMA thread full-wait %6lld, issue %6lld, commit %5lld; producer lane 0 empty-wait %6lld\n",
