@@ -66,9 +66,10 @@ constexpr int UPT = UT / EPI_PARTS, RPT = FC_ROWS / EPI_PARTS;      // GRU units
 constexpr int NCP = 32;                    // fc3 rows padded (MoL: 30) = N of the fc3 job
 // this CTA's bias rows and previous-sample columns in shared memory
 constexpr int SB_G = 0;                                  // rnn1 [input 96 | recurrent 96], rnn2 [input 96 | recurrent 96]
-constexpr int SB_F = 4 * GRU_ROWS;                       // fc1 [64], fc2 [64]
-constexpr int SB_XG = SB_F + 2 * FC_ROWS;                // previous-sample column of rnn1 [96], rnn2 [96]
-constexpr int SB_XF = SB_XG + 2 * GRU_ROWS;              // ... of fc1 [64]
+constexpr int SB_XG = SB_G + 4 * GRU_ROWS;               // previous-sample column of rnn1 [96], rnn2 [96]
+constexpr int SBIAS_GRU = SB_XG + 2 * GRU_ROWS;          // a CTA without an fc job keeps only these (and gets a fourth ring stage)
+constexpr int SB_F = SBIAS_GRU;                          // fc1 [64], fc2 [64]
+constexpr int SB_XF = SB_F + 2 * FC_ROWS;                // previous-sample column of fc1 [64]
 constexpr int SB_B3 = SB_XF + FC_ROWS;                   // fc3 bias [32]
 constexpr int SBIAS = SB_B3 + NCP;
 // fc3 inside the fc CTAs: this CTA's 64 fc2 outputs of the 128 folds as an MMA operand (K = 64, hi + lo) and the matching 64
@@ -137,7 +138,7 @@ struct Params {
     int NTILES, G, NC;
     int dbg_state;                 // WRNN_MMA_STEPS set: also store the fp32 state / fc2 output (wrnn_debug_mma_state)
     int64_t steps_run;             // == a.S except under WRNN_MMA_STEPS (bring-up: stop after n steps and inspect the state)
-    int ring_bytes;                // shared memory of the stage ring (the bias rows follow it)
+    int smem_total;                // dynamic shared memory of a CTA: stage ring | fc3 operands (fc CTAs) | bias rows
     const uint8_t *Aimg;           // packed weights: job type j at offA[j], [row tile][stage][hi|lo][KC][rows][8] bf16
     int64_t offA[NJOB];
     int64_t offP3;                 // fc3 columns as an operand: [8 fc row tiles][hi|lo][KC][32 rows][8] bf16, in Aimg
@@ -430,12 +431,15 @@ struct Ring {                   // the stage ring of this CTA and a position in 
     }
 };
 // A CTA that only runs fc jobs (8 KB weight blocks) packs its stages tighter than one with a GRU job (12 KB); the ring
-// is as deep as shared memory allows (3 stages of 56 KB, or 4 of 48 KB).
-__device__ __forceinline__ Ring make_ring(const Params &P, bool has_gru) {
+// is as deep as shared memory allows: 4 stages of 56 KB for a CTA with only a GRU job, 3 of 48 KB beside the fc3 operands.
+__device__ __forceinline__ int ring_bytes_of(const Params &P, bool has_fc) {
+    return (P.smem_total - (has_fc ? P3_A + P3_B + SBIAS * 4 : SBIAS_GRU * 4)) & ~127;
+}
+__device__ __forceinline__ Ring make_ring(const Params &P, bool has_gru, bool has_fc) {
     Ring r;
     r.w_slot = has_gru ? W_GRU : W_FC;
     r.stage_bytes = r.w_slot + ACT_STAGE;
-    r.nstage = min((uint32_t)MAXSTAGE, (uint32_t)P.ring_bytes / r.stage_bytes);
+    r.nstage = min((uint32_t)MAXSTAGE, (uint32_t)ring_bytes_of(P, has_fc) / r.stage_bytes);
     r.slot = 0;
     r.par = 0;
     return r;
@@ -837,13 +841,12 @@ __device__ __forceinline__ void epi_sample(const Params &P, int nt, int quarter,
 }
 
 __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
-    extern __shared__ __align__(1024) uint8_t smem[];
+    extern __shared__ __align__(128) uint8_t smem[];
     __shared__ __align__(8) uint64_t bar_full[MAXSTAGE], bar_empty[MAXSTAGE], bar_tf[NTF], bar_done, bar_y2;
     __shared__ uint32_t tmem_base_s;
     __shared__ int dead_s;
     uint8_t *stages = smem;
-    uint8_t *p3a = smem + P.ring_bytes, *p3b = p3a + P3_A;               // fc3-inside-fc operands (fc CTAs)
-    float *sbias = reinterpret_cast<float *>(p3b + P3_B);               // this CTA's bias rows / previous-sample columns (SB_*)
+    // (roles first: the layout depends on them)
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, cta = blockIdx.x;
     const int G = P.G;
@@ -852,7 +855,9 @@ __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
     // the fc CTA of row tile 0 also runs the tile's fc3 job and its sampler
     const bool has_gru = cta < MT_GRU * P.NTILES, has_fc = G - 1 - cta < MT_FC * P.NTILES;
     const int mt_g = cta % MT_GRU, nt_g = cta / MT_GRU, mt_f = (G - 1 - cta) % MT_FC, nt_f = (G - 1 - cta) / MT_FC;
-    const bool has_f3 = has_fc && mt_f < 4;          // row tiles 0 .. 3 of the fc CTAs each sample a quarter of the tile's folds
+    const bool has_f3 = has_fc && mt_f < 4;
+    uint8_t *p3a = smem + ring_bytes_of(P, has_fc), *p3b = p3a + P3_A;          // fc3-inside-fc operands (fc CTAs only)
+    float *sbias = reinterpret_cast<float *>(has_fc ? p3b + P3_B : p3a);       // this CTA's bias rows / previous-sample columns (SB_*)          // row tiles 0 .. 3 of the fc CTAs each sample a quarter of the tile's folds
     if (!has_gru && !has_fc) return;
 
     if (tid == 0) {
@@ -863,23 +868,23 @@ __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) tmem_alloc(&tmem_base_s, TMEM_COLS);
-    for (int i = tid; i < SBIAS; i += THREADS) {
+    for (int i = tid; i < (has_fc ? SBIAS : SBIAS_GRU); i += THREADS) {
         const float *gb = P.bias;                                               // rnn1 [16][2][96] | rnn2 [16][2][96]
         const float *fb = gb + (size_t)2 * MT_GRU * 2 * GRU_ROWS;               // fc1 [512] | fc2 [512]
         const float *xg = fb + 2 * FCD;                                         // x columns rnn1 [16][96] | rnn2 [16][96]
         const float *xf = xg + (size_t)2 * MT_GRU * GRU_ROWS;                   // x column fc1 [512]
         const float *b3 = xf + FCD;                                             // fc3 bias [32]
         float v = 0.f;
-        if (i < SB_F) {
+        if (i < SB_XG) {
             if (has_gru) v = gb[(size_t)((i / (2 * GRU_ROWS)) * MT_GRU + mt_g) * 2 * GRU_ROWS + i % (2 * GRU_ROWS)];
-        } else if (i < SB_XG) {
-            const int j = i - SB_F;
-            if (has_fc) v = fb[(size_t)(j / FC_ROWS) * FCD + mt_f * FC_ROWS + j % FC_ROWS];
-        } else if (i < SB_XF) {
+        } else if (i < SBIAS_GRU) {
             const int j = i - SB_XG;
             if (has_gru) v = xg[(size_t)((j / GRU_ROWS) * MT_GRU + mt_g) * GRU_ROWS + j % GRU_ROWS];
+        } else if (i < SB_XF) {
+            const int j = i - SB_F;
+            v = fb[(size_t)(j / FC_ROWS) * FCD + mt_f * FC_ROWS + j % FC_ROWS];
         } else if (i < SB_B3) {
-            if (has_fc) v = xf[mt_f * FC_ROWS + (i - SB_XF)];
+            v = xf[mt_f * FC_ROWS + (i - SB_XF)];
         } else {
             v = b3[i - SB_B3];
         }
@@ -900,7 +905,7 @@ __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
     if (warp == 0) {
         // ======================================================================= TMA producer
         if (lane < NPROD) {
-            Pipe pp{make_ring(P, has_gru), 0u, stages, bar_full, bar_empty};
+            Pipe pp{make_ring(P, has_gru, has_fc), 0u, stages, bar_full, bar_empty};
             // step "-1": recurrent products of step 0 on the zero state (h = 0, :194-195) and step 0's conditioning columns
             if (has_gru) {
                 produce_job(P, J_S1, mt_g, nt_g, -1, -1, 0, pp, lane, w);
@@ -947,7 +952,7 @@ __global__ void __launch_bounds__(THREADS, 1) mma_loop_kernel(const Params P) {
     } else if (warp == 1) {
         // ======================================================================= MMA issuer: the producer's job order, no gates
         if (lane == 0) {
-            Issue is{make_ring(P, has_gru), smem_u32(stages), tb, bar_full, bar_empty, bar_tf, P.exp};
+            Issue is{make_ring(P, has_gru, has_fc), smem_u32(stages), tb, bar_full, bar_empty, bar_tf, P.exp};
             if (has_gru) {
                 issue_job(J_S1, is, w);
                 issue_job(J_R1A, is, w);
@@ -1272,7 +1277,7 @@ int mma_plan(wrnn_handle *h) {
     WRNN_CUDA(h, cudaMemcpy(pl.bias, bias.data(), bias.size() * 4, cudaMemcpyHostToDevice));
     pl.img_bytes = total;
     // everything the device offers minus the static part (barriers): the stage ring takes what the bias rows leave
-    pl.smem_bytes = (h->smem_optin - 1024) / 1024 * 1024;
+    pl.smem_bytes = (h->smem_optin - 512) / 128 * 128;       // static shared memory: 27 mbarriers and two words
     if (pl.smem_bytes < (size_t)FIXED_SMEM + 3 * (W_GRU + ACT_STAGE)) return 0;
     WRNN_CUDA(h, cudaFuncSetAttribute(mma::mma_loop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes));
     pl.ok = true;
@@ -1299,7 +1304,7 @@ int mma_run(wrnn_handle *h, const LoopArgs &a, cudaStream_t st) {
     if (MT_GRU * P.NTILES > P.G || P.NTILES > MAXTILES)
         return fail(h, WRNN_ERR_ARG, "tensor-core loop kernel: %lld folds in tiles of %d need %d CTAs, the device has %d",
                     (long long)a.B, FT, MT_GRU * P.NTILES, P.G);
-    P.ring_bytes = (int)(pl.smem_bytes - FIXED_SMEM) / 1024 * 1024;
+    P.smem_total = (int)pl.smem_bytes;
     P.NC = h->d.NC;
     P.steps_run = a.S;
     P.dbg_state = 0;
