@@ -164,3 +164,21 @@ def test_unbatched_ragged_sequences_on_the_tensor_core_kernel():
         L = m.shape[-1] * dims.hop_length
         ref = ofc.generate(W, dims, m, False, 11000, 550, False, (noise[0][:L, i:i + 1], noise[1][:L, i:i + 1]))
         assert outs[i].shape == ref.shape and np.abs(outs[i] - ref).max() <= 5e-3
+
+
+def test_more_folds_than_one_launch_holds():
+    """1 300 folds (20 utterances x 65) exceed the 1 152 folds of one tensor-core launch: two launches of 650, and every
+    utterance equals its own single-utterance call under the same injected noise (fold groups are exact)."""
+    dims = VocoderDims(mode='MOL')
+    v = voc('init')
+    v.set_loop_kernel(4)
+    target, overlap, T, n_utt = 200, 50, 59, 20
+    mels = [synth.synth_mel(T, seed=100 + u)[0] for u in range(n_utt)]
+    per = binding.num_folds(T * dims.hop_length, target, overlap)
+    noise = synth.synth_noise_mol(target + 2 * overlap, per * n_utt, 99)
+    waves = v.generate(mels, True, target, overlap, False, noise=noise)
+    assert v.last_timing()['folds'] == per * n_utt > 1152
+    for u in (0, 7, 9, 10, 19):                 # utterance 9 / 10 straddle the launch boundary at fold 650
+        nz = tuple(np.ascontiguousarray(a[:, u * per:(u + 1) * per]) for a in noise)
+        one = v.generate([mels[u]], True, target, overlap, False, noise=nz)[0]
+        assert np.array_equal(one, waves[u]), u
