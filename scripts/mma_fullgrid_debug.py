@@ -21,10 +21,11 @@ mel = synth.synth_mel(T, seed=1234)
 with torch.no_grad():
     m, aux, wave_len = ofc.conditioning(W, dims, mel, True, target, overlap)
     B, S = int(m.shape[0]), int(m.shape[1])
-    noise = synth.synth_noise_mol(S, B, 4321)
-    res = ofc.run_loop(W, dims, m, aux, noise)
-ref = res['samples'].numpy()
-for rep in range(3):
+for rep, seed in enumerate((4321, 99, 7)):
+    noise = synth.synth_noise_mol(S, B, seed)
+    with torch.no_grad():
+        res = ofc.run_loop(W, dims, m, aux, noise)
+    ref = res['samples'].numpy()
     v.set_loop_kernel(4)
     v.generate([mel[0]], True, target, overlap, False, noise=noise)
     got = v.fetch_samples()
