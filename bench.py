@@ -277,12 +277,22 @@ def run_config5(args, voc, dims, rank, world, stream, flush, barrier):
                                       'frac': WEIGHT_BYTES_PER_STEP * t['steps'] / (k_ms * 1e-3) / 1e9 / measured_peaks()[0],
                                       'note': 'the weights are streamed from L2 (15.3 MB of bf16 hi/lo images, resident there), not HBM; '
                                               'what binds is in roofline (tensor) and DESIGN.md 4.5'},
+        # weight / operand read rate against the measured L2 -> SM streaming rate (profiles/r02_tcgen05_microbench.txt:
+        # 69 B/clk/SM with all 148 SMs streaming 32 KB bulk copies).  Bytes per step from the kernel's job table: a CTA with a
+        # GRU job streams 29 stages of 24 KB weights + 32 KB activations, an fc CTA 20 stages of 16 + 32 KB; 16 + 8 CTAs per tile
+        'l2_stream': (lambda tiles, us: {
+            'bytes_per_step': tiles * (16 * 29 * 57344 + 8 * 20 * 49152),
+            'weight_bytes_per_step': tiles * (16 * 29 * 24576 + 8 * 20 * 16384),
+            'achieved': tiles * (16 * 29 * 57344 + 8 * 20 * 49152) / (us * 1e-6) / 1e9, 'unit': 'GB/s',
+            'peak': 69.0 * 148 * 1.965, 'peak_source': '69 B/clk/SM x 148 SMs x 1965 MHz, measured (profiles/r02_tcgen05_microbench.txt)',
+            'frac': tiles * (16 * 29 * 57344 + 8 * 20 * 49152) / (us * 1e-6) / 1e9 / (69.0 * 148 * 1.965)})(
+                -(-t['folds'] // 128), 1000 * k_ms / t['steps']),
         'deepmind': dm,
         'launches': launches + (dm['launches'] if dm else 0),
     }
 
 
-def run_deepmind(device, world, barrier, n_seq=8, seconds=0.5):
+def run_deepmind(device, world, barrier, n_seq=8, seconds=2.0):      # seq_len = 44 100
     """configs[4], second half: deepmind_version coarse/fine dual-softmax generation (models/deepmind_version.py:75-165),
     hidden 896, `n_seq` independent sequences per GPU (the reference generates one), Philox noise, through the C ABI with
     the int64 outputs copied to host arrays inside the timed call."""
