@@ -36,7 +36,7 @@ def fatchord(name, dims, T, batched, mu_law=False, n_utt=1, prune=None, reps=2):
     t = v.last_timing()
     n = sum(len(o) for o in out)
     print(json.dumps({'config': name, 'utterances': n_utt, 'folds': t['folds'], 'steps': t['steps'],
-                      'kernel': v.loop_kernel_name(min(t['folds'], 20)), 'samples': n, 'seconds': round(dt, 4),
+                      'kernel': v.loop_kernel_name(t['folds']), 'samples': n, 'seconds': round(dt, 4),
                       'samples_per_s': round(n / dt), 'x_real_time': round(n / dt / SR, 2),
                       'loop_us_per_step': round(1000 * t['ms_loop'] / t['steps'], 2)}), flush=True)
 
@@ -57,6 +57,7 @@ if __name__ == '__main__':
     fatchord('2b: MoL batched T=800 (B=19, no tail pad)', mol, 800, True)
     fatchord('3: RAW 9-bit mu-law batched T=801 (B=20)', raw, 801, True, mu_law=True, reps=1)
     fatchord('4: config 2 with 16x1 block-pruned GRU (10 % kept), 16x1 block-sparse tables', mol, 801, True, prune=0.1)
-    fatchord('5 (8 of 256 utterances): MoL batched T=801, 160 folds in groups of 20', mol, 801, True, n_utt=8, reps=1)
+    fatchord('5, one GPU of eight (32 of 256 utterances): MoL batched T=801, 640 folds in one launch', mol, 801, True, n_utt=32, reps=1)
+    fatchord('5 shape, 8 utterances: 160 folds in one launch', mol, 801, True, n_utt=8, reps=1)
     deepmind(1)
     deepmind(8)
