@@ -83,3 +83,24 @@ def test_first_chunk_arrives_before_the_job_is_done(tmp_path):
     data, rate = wavio.load_wav(path)
     assert rate == dims.sample_rate and np.array_equal(data, wave.astype(np.float32))
     assert os.path.getsize(path) == 58 + 4 * len(wave)
+
+
+@pytest.mark.gpu
+def test_streamed_chunks_on_the_tensor_core_kernel():
+    """Chunks of 64 folds run on the tensor-core kernel (three launches for 160 folds) and still concatenate to the
+    waveform of the single 160-fold launch bit for bit: a fold's arithmetic does not depend on where in a tile it sits."""
+    from wavernn_b200 import binding, synth
+    from wavernn_b200.config import VocoderDims
+    dims = VocoderDims(mode='MOL')
+    v = binding.Vocoder(dims, device=0)
+    v.load_weights(synth.synth_state_dict(dims, seed=0, style='init'))
+    target, overlap = 500, 50
+    T = 160 * (target + overlap) // dims.hop_length
+    mel = synth.synth_mel(T, seed=6)
+    B = binding.num_folds(T * dims.hop_length, target, overlap)
+    noise = synth.synth_noise_mol(target + 2 * overlap, B, 5)
+    ref = v.generate([mel[0]], True, target, overlap, False, noise=noise)[0]
+    assert v.loop_kernel_name(B) == 'tcgen05-bf16x3' and v.loop_kernel_name(64) == 'tcgen05-bf16x3'
+    got = []
+    wave = v.generate_stream(mel[0], target, overlap, False, on_chunk=lambda first, x, last: got.append(len(x)), chunk_folds=64, noise=noise)
+    assert np.array_equal(wave, ref) and len(got) == 3 and got[0] == 64 * (target + overlap)
