@@ -220,6 +220,26 @@ int wrnn_dm_generate(wrnn_dm_handle *h, int64_t seq_len, int32_t n_seq, const fl
                      int64_t *fine, void *cuda_stream);
 int wrnn_dm_last_timing(wrnn_dm_handle *h, float *ms_loop, int64_t *kernel_launches);
 
+/* ------------------------------------------------------------------ Tacotron decoder loop */
+typedef struct wrnn_taco_handle wrnn_taco_handle;
+/* decoder_dims must be 256: PreNet's widths are fixed (models/tacotron.py:137) and the attention GRU's input is
+ * decoder_dims + decoder_dims // 2 (:218).  lstm_dims <= 512 (hparams.py:72), n_mels <= 128. */
+int wrnn_taco_create(int32_t decoder_dims, int32_t lstm_dims, int32_t n_mels, int device, wrnn_taco_handle **out);
+void wrnn_taco_destroy(wrnn_taco_handle *h);
+const char *wrnn_taco_last_error(const wrnn_taco_handle *h);
+/* Tensors of `Tacotron.state_dict()` by checkpoint key: every `decoder.*` parameter (models/tacotron.py:211-224) and
+ * `encoder_proj.weight` (:301); other keys are kept and ignored. */
+int wrnn_taco_load_weights(wrnn_taco_handle *h, const wrnn_tensor *tensors, int32_t n);
+/* The decoder loop of Tacotron.generate (models/tacotron.py:438-465) for one utterance: enc_seq (L, decoder_dims) is
+ * the CBHG encoder's output (host memory), r the reduction factor (`model.r`), steps the frame budget
+ * (`for t in range(0, steps, r)`), stop_threshold the model's buffer of that name (a step whose r frames are all below
+ * it ends the loop once t > 10, :455).  Outputs (host memory): mel (n_mels, n_iter * r) row-major, capacity
+ * n_mels * ceil(steps / r) * r floats; attn (n_iter, L), capacity ceil(steps / r) * L floats; *n_iter = decoder steps
+ * run.  The postnet and the linear projection after the loop (:458-459) stay with the caller. */
+int wrnn_taco_decode(wrnn_taco_handle *h, const float *enc_seq, int32_t L, int32_t r, int32_t steps, float stop_threshold,
+                     float *mel, float *attn, int32_t *n_iter, void *cuda_stream);
+int wrnn_taco_last_timing(wrnn_taco_handle *h, float *ms_loop, int64_t *kernel_launches);
+
 #ifdef __cplusplus
 }
 #endif

@@ -166,3 +166,32 @@ class injected_noise:
         torch.Tensor.uniform_ = self._u
         torch.distributions.Categorical.sample = self._s
         return False
+
+
+def build_tacotron(state_dict_np, enc_seq, r=2, stop_threshold=-3.4, decoder_dims=256, lstm_dims=512, n_mels=80):
+    """Reference `Tacotron` (hparams.py:67-77 dims) on CPU with the decoder-loop parameters of `state_dict_np` loaded and
+    its CBHG encoder's output replaced by `enc_seq` (a forward hook on `model.encoder`): the reference's own
+    `generate` then runs its decoder loop on a known input.  -> model; call `model.generate(x, steps)` with any
+    `x` of length L."""
+    import contextlib
+    import io
+    import torch
+    load()
+    sys.path.insert(0, REF_ROOT)
+    try:
+        import models.tacotron as tc
+    finally:
+        sys.path.remove(REF_ROOT)
+    torch.manual_seed(0)
+    with contextlib.redirect_stdout(io.StringIO()):
+        model = tc.Tacotron(embed_dims=256, num_chars=70, encoder_dims=decoder_dims // 2, decoder_dims=decoder_dims,
+                            n_mels=n_mels, fft_bins=n_mels, postnet_dims=128, encoder_K=16, lstm_dims=lstm_dims,
+                            postnet_K=8, num_highways=4, dropout=0.5, stop_threshold=stop_threshold)
+    missing, unexpected = model.load_state_dict({k: torch.from_numpy(v.copy()) for k, v in state_dict_np.items()},
+                                                strict=False)
+    if unexpected or any(k.startswith('decoder.') and k != 'decoder.r' for k in missing):
+        raise RuntimeError(f'decoder keys do not match the reference: missing {missing}, unexpected {unexpected}')
+    model.r = r
+    enc = torch.as_tensor(enc_seq).unsqueeze(0)
+    model.encoder.register_forward_hook(lambda mod, inp, out: enc)
+    return model

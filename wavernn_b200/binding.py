@@ -81,6 +81,12 @@ _SIGS = {
     'wrnn_dm_load_weights': (C.c_int, [_P, C.POINTER(wrnn_tensor), C.c_int32]),
     'wrnn_dm_generate': (C.c_int, [_P, C.c_int64, C.c_int32, _P, _P, C.c_uint64, _P, _P, _P, _P]),
     'wrnn_dm_last_timing': (C.c_int, [_P, C.POINTER(C.c_float), C.POINTER(C.c_int64)]),
+    'wrnn_taco_create': (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int, C.POINTER(_P)]),
+    'wrnn_taco_destroy': (None, [_P]),
+    'wrnn_taco_last_error': (C.c_char_p, [_P]),
+    'wrnn_taco_load_weights': (C.c_int, [_P, C.POINTER(wrnn_tensor), C.c_int32]),
+    'wrnn_taco_decode': (C.c_int, [_P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_float, _P, _P, C.POINTER(C.c_int32), _P]),
+    'wrnn_taco_last_timing': (C.c_int, [_P, C.POINTER(C.c_float), C.POINTER(C.c_int64)]),
 }
 
 _lib = None
@@ -469,4 +475,59 @@ class DeepmindVocoder:
     def last_timing(self):
         ms, k = C.c_float(), C.c_int64()
         self._ck(lib().wrnn_dm_last_timing(self._h, C.byref(ms), C.byref(k)))
+        return dict(ms_loop=ms.value, launches=k.value)
+
+
+class TacotronDecoder:
+    """Owns one `wrnn_taco_handle`: the decoder loop of `Tacotron.generate` (models/tacotron.py:438-465)."""
+
+    def __init__(self, decoder_dims=256, lstm_dims=512, n_mels=80, device=0):
+        self.decoder_dims, self.lstm_dims, self.n_mels = decoder_dims, lstm_dims, n_mels
+        self._h = _P()
+        rc = lib().wrnn_taco_create(int(decoder_dims), int(lstm_dims), int(n_mels), int(device), C.byref(self._h))
+        if rc != 0:
+            _raise(rc, lib().wrnn_taco_last_error(None))
+
+    def close(self):
+        if getattr(self, '_h', None):
+            lib().wrnn_taco_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, rc):
+        if rc != 0:
+            _raise(rc, lib().wrnn_taco_last_error(self._h))
+
+    def load_weights(self, state):
+        """state: `Tacotron.state_dict()` (numpy arrays or torch tensors); the `decoder.*` and `encoder_proj.weight`
+        entries are used."""
+        state = {k: v for k, v in state.items() if k.startswith('decoder.') or k == 'encoder_proj.weight'}
+        state = {k: (v.detach().cpu().numpy() if hasattr(v, 'detach') else np.asarray(v)) for k, v in state.items()}
+        state = {k: np.ascontiguousarray(v, dtype=np.float32) for k, v in state.items() if v.dtype.kind == 'f'}
+        arr, keep = _tensors(state)
+        self._ck(lib().wrnn_taco_load_weights(self._h, arr, len(state)))
+
+    def decode(self, enc_seq, steps=2000, r=2, stop_threshold=-3.4, stream=None):
+        """enc_seq (L, decoder_dims) -> mel (n_mels, n_iter * r), attn (n_iter, L)."""
+        enc = np.ascontiguousarray(enc_seq, dtype=np.float32)
+        if enc.ndim != 2 or enc.shape[1] != self.decoder_dims:
+            raise ValueError(f'enc_seq must be (L, {self.decoder_dims}), got {enc.shape}')
+        L = enc.shape[0]
+        max_iter = (int(steps) + int(r) - 1) // int(r)
+        mel = np.empty(self.n_mels * max_iter * r, dtype=np.float32)
+        attn = np.empty(max_iter * L, dtype=np.float32)
+        n = C.c_int32(0)
+        self._ck(lib().wrnn_taco_decode(self._h, _ptr(enc), L, int(r), int(steps), float(stop_threshold), _ptr(mel),
+                                        _ptr(attn), C.byref(n), stream))
+        n = n.value
+        return mel[:self.n_mels * n * r].reshape(self.n_mels, n * r).copy(), attn[:n * L].reshape(n, L).copy()
+
+    def last_timing(self):
+        ms, k = C.c_float(), C.c_int64()
+        self._ck(lib().wrnn_taco_last_timing(self._h, C.byref(ms), C.byref(k)))
         return dict(ms_loop=ms.value, launches=k.value)

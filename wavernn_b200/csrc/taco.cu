@@ -1,0 +1,682 @@
+// Tacotron decoder loop of `Tacotron.generate` (models/tacotron.py:438-465: encoder projection, then per decoder step
+// PreNet -> attention GRU cell -> location-sensitive smoothed attention -> context -> rnn_input -> two residual LSTM
+// cells -> mel projection of r frames, until every frame of a step is below the stop threshold) as ONE persistent
+// cooperative kernel: every SM keeps its rows of all decoder matrices (20 MB fp32 in total) in shared memory for the
+// whole utterance, the layers hand small vectors to one another through L2 and grid barriers.
+//
+// Seven barriers per decoder step instead of one per layer, by algebra on the host (compositions formed in double):
+//   A  mel frames of the step before AND prenet.fc1 of this step: fc1(mel[:, r-1]) = (W_fc1 . W_mel[last frame]) . x3 + b
+//   B  prenet.fc2 (+ ReLU); the stop rule on the frames A published; location features of the positions a CTA owns
+//   C  attention GRU cell (input [context | prenet], hidden)                                             (:236-238)
+//   D  processed query W . h_attn + b                                                                     (:190)
+//   E  energies v . tanh(query + enc_proj + loc) and sigmoid for the positions a CTA owns, and its PARTIAL context
+//      sum_l sigmoid(u_l) enc[l] and partial sum (context = sum of partials / sum of sums: no barrier between the
+//      normalisation and the context product)                                                           (:196-205,244)
+//   F  rnn_input and LSTM 1 at once: gates = (W_ih1 . W_rnn_input) . [context | h_attn] + W_hh1 . h1; x rows beside  (:256-262)
+//   G  LSTM 2 on x + h1; publishes x3 = x + h1 + h2 for A                                                (:270-277)
+// Dropout and zoneout are training-only (eval mode in generate, :423).
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "internal.h"
+#include "loop_common.cuh"
+
+namespace wrnn {
+
+constexpr int TC_THREADS = 512, TC_WARPS = TC_THREADS / 32;
+constexpr int TC_FILT = 32, TC_KS = 31, TC_HALO = (TC_KS - 1) / 2, TC_MAXR = 20;
+
+struct TacoParams {
+    int D, H, M, P1, P2, r, L, max_iter, cap;      // cap = max_iter * r columns of mel_out
+    float thr;
+    int NA, rpa, rpb, upc, rpd, upl;               // rows (A, B, D) / units (C: GRU, F/G: LSTM) per CTA
+    int PP, pc0, PC;                               // positions per owner CTA, first owner CTA, owners in use
+    int img_floats;
+    int off_A, off_bA, off_B, off_bB, off_C, off_bC, off_D, off_bD, off_F, off_bF, off_G, off_bG, off_E;
+    int sm_vec, sm_ctx, sm_misc;                   // smem float offsets behind the image
+    const float *image;                            // [G][img_floats]
+    const float *common;                           // conv w [32][2][31] (+pad to 2048) | v [D] | L.weight [D][32] | L.bias [D]
+    const float *enc, *encp;                       // [L][D]
+    float *p1, *p2, *ha, *pq, *part_ctx, *part_sum, *x2, *h1, *h2, *x3, *melf, *att_g, *cum_g;
+    float *mel_out, *attn_out;
+    int *n_iter;
+    GridSync gs;
+};
+
+__device__ __forceinline__ float warp_dot(const float *w, const float *x, int k4, int lane) {
+    float a0 = 0.f, a1 = 0.f;
+    const float4 *w4 = reinterpret_cast<const float4 *>(w), *x4 = reinterpret_cast<const float4 *>(x);
+    for (int i = lane; i < k4; i += 32) {
+        const float4 a = w4[i], b = x4[i];
+        a0 = fmaf(a.x, b.x, a0);
+        a1 = fmaf(a.y, b.y, a1);
+        a0 = fmaf(a.z, b.z, a0);
+        a1 = fmaf(a.w, b.w, a1);
+    }
+    a0 += a1;
+#pragma unroll
+    for (int o = 16; o >= 1; o >>= 1) a0 += __shfl_xor_sync(0xffffffffu, a0, o);
+    return a0;
+}
+
+__device__ __forceinline__ void stage_vec(float *dst, const float *src, int n, int tid) {     // written by other CTAs: L2 loads
+    for (int i = tid; i < (n >> 2); i += TC_THREADS) reinterpret_cast<float4 *>(dst)[i] = __ldcg(reinterpret_cast<const float4 *>(src) + i);
+}
+
+__global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoParams P) {
+    extern __shared__ __align__(16) float smem[];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, cta = blockIdx.x;
+    const int D = P.D, H = P.H, r = P.r, L = P.L;
+    float *img = smem, *vec = smem + P.sm_vec, *ctx = smem + P.sm_ctx, *misc = smem + P.sm_misc;
+    float *gsum = misc;                 // [<= 32] dot products of a stage
+    float *c1 = misc + 32, *c2 = c1 + P.upl;            // LSTM cell states of the owned units
+    for (int i = tid; i < P.img_floats / 4; i += TC_THREADS)
+        reinterpret_cast<float4 *>(img)[i] = reinterpret_cast<const float4 *>(P.image + (size_t)cta * P.img_floats)[i];
+    __syncthreads();                    // the owners' region below overlays image space their CTAs do not use
+
+    // ---- attention positions this CTA owns
+    const int pi = cta - P.pc0;
+    const bool owner = pi >= 0 && pi < P.PC;
+    const int l0 = owner ? pi * P.PP : 0, nl = owner ? max(0, min(P.PP, L - l0)) : 0;
+    float *encp_s = smem + P.off_E, *enc_s = encp_s + (size_t)P.PP * D, *ploc = enc_s + (size_t)P.PP * D;
+    float *cw = ploc + (size_t)P.PP * D;                 // [32][2][31] padded to 2048
+    float *loc = cw + 2048;                              // [2][PP + 30]
+    float *conv = loc + 2 * (P.PP + 2 * TC_HALO + 2);    // [32][PP]
+    float *sv = conv + TC_FILT * P.PP;                   // [PP] sigmoid(u)
+    float *cumv = sv + P.PP;                             // [PP] cumulative attention
+    float *red = cumv + P.PP;                            // [PP][8]
+    const int a = tid & 255, half = tid >> 8;            // energy thread = (attention dim a, position parity); D == 256
+    float lw[TC_FILT], lb = 0.f, va = 0.f;
+    if (owner && nl > 0) {
+        for (int i = tid; i < nl * D; i += TC_THREADS) {
+            encp_s[i] = P.encp[(size_t)l0 * D + i];
+            enc_s[i] = P.enc[(size_t)l0 * D + i];
+        }
+        for (int i = tid; i < TC_FILT * 2 * TC_KS; i += TC_THREADS) cw[i] = P.common[i];
+        for (int i = tid; i < P.PP; i += TC_THREADS) cumv[i] = 0.f;
+        va = P.common[2048 + a];
+#pragma unroll
+        for (int f = 0; f < TC_FILT; f++) lw[f] = P.common[2048 + D + a * TC_FILT + f];
+        lb = P.common[2048 + D + D * TC_FILT + a];
+    }
+    for (int i = tid; i < D; i += TC_THREADS) ctx[i] = 0.f;
+    for (int i = tid; i < 2 * P.upl; i += TC_THREADS) c1[i] = 0.f;
+    __syncthreads();
+
+    const float *WA = img + P.off_A, *bA = img + P.off_bA, *WB = img + P.off_B, *bB = img + P.off_bB;
+    const float *WC = img + P.off_C, *bC = img + P.off_bC, *WD = img + P.off_D, *bD = img + P.off_bD;
+    const float *WF = img + P.off_F, *bF = img + P.off_bF, *WG = img + P.off_G, *bG = img + P.off_bG;
+    const int a0 = cta * P.rpa, na = max(0, min(P.rpa, P.NA - a0));
+    const int b0 = cta * P.rpb, nb = max(0, min(P.rpb, P.P2 - b0));
+    const int g0 = cta * P.upc, ng = max(0, min(P.upc, D - g0));
+    const int d0 = cta * P.rpd, nd = max(0, min(P.rpd, D - d0));
+    const int u0 = cta * P.upl, nu = max(0, min(P.upl, H - u0));
+    const int KC = 2 * D + P.P2;        // GRU: [context | prenet | hidden]
+    const int KF = 2 * D + H;           // LSTM 1: [context | h_attn | h1]
+    const int nmel = P.M * r;
+    unsigned long long gen = 0;
+    int n_done = 0;
+
+    for (int it = 0;; it++) {
+        const int cur = it & 1, nxt = cur ^ 1;
+        // ---- A: mel frames of step it-1, prenet.fc1 of step it (x3 = 0 before the first step: fc1(go frame) = relu(b))
+        stage_vec(vec, P.x3, H, tid);
+        __syncthreads();
+        for (int j = warp; j < na; j += TC_WARPS) {
+            const float d = warp_dot(WA + (size_t)j * H, vec, H >> 2, lane);
+            if (lane == 0) {
+                const int row = a0 + j;
+                if (row < nmel) {
+                    if (it > 0) {
+                        const int m = row / r, jj = row - m * r;
+                        P.mel_out[(size_t)m * P.cap + (size_t)(it - 1) * r + jj] = d;
+                        P.melf[row] = d;
+                    }
+                } else {
+                    P.p1[row - nmel] = fmaxf(d + bA[j], 0.f);
+                }
+            }
+        }
+        grid_barrier(P.gs, gen);
+        n_done = it;
+        if (it == P.max_iter) break;
+        // ---- B: stop rule on the frames of step it-1 (:455: all below the threshold and t > 10), prenet.fc2,
+        //         location features (conv over [cumulative | attention] + L) of the owned positions for this step
+        {
+            int ok = 1;
+            if (it > 0 && (it - 1) * r > 10) {
+                for (int i = tid; i < nmel; i += TC_THREADS) ok &= (__ldcg(P.melf + i) < P.thr) ? 1 : 0;
+            } else {
+                ok = 0;
+            }
+            stage_vec(vec, P.p1, P.P1, tid);
+            if (__syncthreads_and(ok)) break;
+        }
+        for (int j = warp; j < nb; j += TC_WARPS) {
+            const float d = warp_dot(WB + (size_t)j * P.P1, vec, P.P1 >> 2, lane);
+            if (lane == 0) P.p2[b0 + j] = fmaxf(d + bB[j], 0.f);
+        }
+        if (nl > 0) {
+            const int span = nl + 2 * TC_HALO;
+            for (int i = tid; i < 2 * span; i += TC_THREADS) {
+                const int c = i / span, k = i - c * span, l = l0 - TC_HALO + k;
+                loc[c * (P.PP + 2 * TC_HALO + 2) + k] = (l >= 0 && l < L) ? __ldcg((c == 0 ? P.cum_g : P.att_g) + l) : 0.f;
+            }
+            __syncthreads();
+            for (int i = tid; i < TC_FILT * nl; i += TC_THREADS) {
+                const int f = i / nl, p = i - f * nl;
+                float acc = 0.f;
+#pragma unroll
+                for (int c = 0; c < 2; c++) {
+                    const float *w = cw + (f * 2 + c) * TC_KS, *x = loc + c * (P.PP + 2 * TC_HALO + 2) + p;
+                    for (int k = 0; k < TC_KS; k++) acc = fmaf(w[k], x[k], acc);
+                }
+                conv[f * P.PP + p] = acc;
+            }
+            __syncthreads();
+            for (int p = half; p < nl; p += 2) {
+                float acc = lb;
+#pragma unroll
+                for (int f = 0; f < TC_FILT; f++) acc = fmaf(lw[f], conv[f * P.PP + p], acc);
+                ploc[(size_t)p * D + a] = acc;
+            }
+        }
+        grid_barrier(P.gs, gen);
+        // ---- C: attention GRU cell
+        for (int i = tid; i < D; i += TC_THREADS) vec[i] = ctx[i];
+        stage_vec(vec + D, P.p2, P.P2, tid);
+        stage_vec(vec + D + P.P2, P.ha + (size_t)cur * D, D, tid);
+        __syncthreads();
+        for (int w = warp; w < 4 * ng; w += TC_WARPS) {
+            const int j = w >> 2, q = w & 3;
+            const float *row = WC + (size_t)j * (2 * KC + (D + P.P2) + D);
+            float d;
+            if (q < 2) d = warp_dot(row + (size_t)q * KC, vec, KC >> 2, lane);
+            else if (q == 2) d = warp_dot(row + 2 * KC, vec, (D + P.P2) >> 2, lane);
+            else d = warp_dot(row + 2 * KC + D + P.P2, vec + D + P.P2, D >> 2, lane);
+            if (lane == 0) gsum[w] = d;
+        }
+        __syncthreads();
+        if (tid < ng) {
+            const float *b = bC + tid * 4;
+            const float rr = sigmoidf_acc(gsum[tid * 4 + 0] + b[0]), zz = sigmoidf_acc(gsum[tid * 4 + 1] + b[1]);
+            const float nn = tanhf(gsum[tid * 4 + 2] + b[2] + rr * (gsum[tid * 4 + 3] + b[3]));
+            P.ha[(size_t)nxt * D + g0 + tid] = (1.f - zz) * nn + zz * vec[D + P.P2 + g0 + tid];
+        }
+        grid_barrier(P.gs, gen);
+        // ---- D: processed query
+        stage_vec(vec, P.ha + (size_t)nxt * D, D, tid);
+        __syncthreads();
+        for (int j = warp; j < nd; j += TC_WARPS) {
+            const float d = warp_dot(WD + (size_t)j * D, vec, D >> 2, lane);
+            if (lane == 0) P.pq[d0 + j] = d + bD[j];
+        }
+        grid_barrier(P.gs, gen);
+        // ---- E: energies, sigmoid and the partial context of the owned positions
+        if (nl > 0) {
+            stage_vec(vec, P.pq, D, tid);
+            __syncthreads();
+            for (int p = half; p < nl; p += 2) {
+                float v = va * tanhf(vec[a] + encp_s[(size_t)p * D + a] + ploc[(size_t)p * D + a]);
+#pragma unroll
+                for (int o = 16; o >= 1; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+                if (lane == 0) red[p * 8 + (warp & 7)] = v;
+            }
+            __syncthreads();
+            if (tid < nl) {
+                float e = 0.f;
+                for (int w = 0; w < D / 32; w++) e += red[tid * 8 + w];
+                sv[tid] = sigmoidf_acc(e);
+            }
+            __syncthreads();
+            if (tid < D) {
+                float acc = 0.f;
+                for (int p = 0; p < nl; p++) acc = fmaf(sv[p], enc_s[(size_t)p * D + tid], acc);
+                P.part_ctx[(size_t)pi * D + tid] = acc;
+            } else if (tid == D) {
+                float s = 0.f;
+                for (int p = 0; p < nl; p++) s += sv[p];
+                P.part_sum[pi] = s;
+            }
+        }
+        grid_barrier(P.gs, gen);
+        // ---- F: context = sum of partials / sum of sums; rnn_input + LSTM 1; owners normalise their scores
+        {
+            float total = 0.f;
+            for (int p = 0; p < P.PC; p++) total += __ldcg(P.part_sum + p);
+            if (tid < D) {
+                float acc = 0.f;
+                for (int p = 0; p < P.PC; p++) acc += __ldcg(P.part_ctx + (size_t)p * D + tid);
+                const float c = acc / total;
+                ctx[tid] = c;
+                vec[tid] = c;
+            }
+            if (tid < nl) {
+                const float att = sv[tid] / total;
+                const float cu = cumv[tid] + att;
+                cumv[tid] = cu;
+                P.att_g[l0 + tid] = att;
+                P.cum_g[l0 + tid] = cu;
+                P.attn_out[(size_t)it * L + l0 + tid] = att;
+            }
+        }
+        stage_vec(vec + D, P.ha + (size_t)nxt * D, D, tid);
+        stage_vec(vec + 2 * D, P.h1 + (size_t)cur * H, H, tid);
+        __syncthreads();
+        for (int w = warp; w < 5 * nu; w += TC_WARPS) {
+            float d;
+            if (w < 4 * nu) d = warp_dot(WF + (size_t)w * KF, vec, KF >> 2, lane);                        // w = unit * 4 + gate
+            else d = warp_dot(WF + (size_t)4 * P.upl * KF + (size_t)(w - 4 * nu) * 2 * D, vec, (2 * D) >> 2, lane);
+            if (lane == 0) gsum[w] = d;
+        }
+        __syncthreads();
+        if (tid < nu) {
+            const float *b = bF + tid * 5;
+            const float ig = sigmoidf_acc(gsum[tid * 4 + 0] + b[0]), fg = sigmoidf_acc(gsum[tid * 4 + 1] + b[1]);
+            const float gg = tanhf(gsum[tid * 4 + 2] + b[2]), og = sigmoidf_acc(gsum[tid * 4 + 3] + b[3]);
+            const float c = fg * c1[tid] + ig * gg, h = og * tanhf(c);
+            c1[tid] = c;
+            P.h1[(size_t)nxt * H + u0 + tid] = h;
+            P.x2[u0 + tid] = (gsum[4 * nu + tid] + b[4]) + h;
+        }
+        grid_barrier(P.gs, gen);
+        // ---- G: LSTM 2 on x + h1
+        stage_vec(vec, P.x2, H, tid);
+        stage_vec(vec + H, P.h2 + (size_t)cur * H, H, tid);
+        __syncthreads();
+        for (int w = warp; w < 4 * nu; w += TC_WARPS) {
+            const float d = warp_dot(WG + (size_t)w * 2 * H, vec, (2 * H) >> 2, lane);
+            if (lane == 0) gsum[w] = d;
+        }
+        __syncthreads();
+        if (tid < nu) {
+            const float *b = bG + tid * 4;
+            const float ig = sigmoidf_acc(gsum[tid * 4 + 0] + b[0]), fg = sigmoidf_acc(gsum[tid * 4 + 1] + b[1]);
+            const float gg = tanhf(gsum[tid * 4 + 2] + b[2]), og = sigmoidf_acc(gsum[tid * 4 + 3] + b[3]);
+            const float c = fg * c2[tid] + ig * gg, h = og * tanhf(c);
+            c2[tid] = c;
+            P.h2[(size_t)nxt * H + u0 + tid] = h;
+            P.x3[u0 + tid] = vec[u0 + tid] + h;
+        }
+        grid_barrier(P.gs, gen);
+    }
+    if (cta == 0 && tid == 0) *P.n_iter = n_done;
+}
+
+// enc_proj = enc_seq . W^T (models/tacotron.py:440, `encoder_proj`, no bias): one CTA per position
+__global__ void taco_encproj_kernel(const float *enc, const float *Wt /*[D in][D out]*/, float *encp, int D) {
+    extern __shared__ float row[];
+    const int l = blockIdx.x;
+    for (int i = threadIdx.x; i < D; i += blockDim.x) row[i] = enc[(size_t)l * D + i];
+    __syncthreads();
+    for (int o = threadIdx.x; o < D; o += blockDim.x) {
+        float acc = 0.f;
+        for (int k = 0; k < D; k++) acc = fmaf(row[k], Wt[(size_t)k * D + o], acc);
+        encp[(size_t)l * D + o] = acc;
+    }
+}
+
+}  // namespace wrnn
+
+// ============================================================================ host
+struct wrnn_taco_handle {
+    int D = 0, H = 0, M = 0, device = 0, num_sms = 0;
+    size_t smem_optin = 0;
+    std::string err;
+    std::map<std::string, wrnn::HostTensor> w;
+    int packed_r = 0;            // the reduction factor the image was packed for (0: none)
+    wrnn::TacoParams plan;       // layout fields only
+    float *image = nullptr, *common = nullptr, *projT = nullptr;
+    std::vector<double> WcF;     // (W_ih1 . W_rnn_input) [4H][2D] and its bias [4H]: independent of r, formed once
+    std::vector<double> bcF;
+    void *ws = nullptr;
+    size_t ws_bytes = 0;
+    cudaEvent_t ev[2] = {nullptr, nullptr};
+    int64_t launches = 0;
+};
+
+static thread_local std::string g_taco_err;
+
+namespace wrnn {
+
+static int taco_fail(wrnn_taco_handle *h, int code, const char *msg) {
+    if (h) h->err = msg;
+    else g_taco_err = msg;
+    if (code == WRNN_ERR_CUDA) cudaGetLastError();
+    return code;
+}
+#define TC_CUDA(h, expr)                                                                          \
+    do {                                                                                          \
+        cudaError_t e__ = (expr);                                                                 \
+        if (e__ != cudaSuccess) {                                                                 \
+            char b__[512];                                                                        \
+            snprintf(b__, sizeof b__, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e__), __FILE__, __LINE__); \
+            return wrnn::taco_fail((h), WRNN_ERR_CUDA, b__);                                      \
+        }                                                                                         \
+    } while (0)
+
+static int taco_pack(wrnn_taco_handle *h, int r) {
+    const int D = h->D, H = h->H, M = h->M, G = h->num_sms, P1 = 256, P2 = 128;
+    auto get = [&](const char *k, std::vector<int64_t> shape) -> const HostTensor * {
+        auto it = h->w.find(k);
+        if (it == h->w.end() || it->second.shape != shape) {
+            h->err = std::string("checkpoint key missing or misshapen: ") + k;
+            return nullptr;
+        }
+        return &it->second;
+    };
+    const HostTensor *Wp = get("encoder_proj.weight", {D, D}),
+                     *W1 = get("decoder.prenet.fc1.weight", {P1, M}), *b1 = get("decoder.prenet.fc1.bias", {P1}),
+                     *W2 = get("decoder.prenet.fc2.weight", {P2, P1}), *b2 = get("decoder.prenet.fc2.bias", {P2}),
+                     *Cw = get("decoder.attn_net.conv.weight", {TC_FILT, 2, TC_KS}),
+                     *Lw = get("decoder.attn_net.L.weight", {D, TC_FILT}), *Lb = get("decoder.attn_net.L.bias", {D}),
+                     *Wq = get("decoder.attn_net.W.weight", {D, D}), *bq = get("decoder.attn_net.W.bias", {D}),
+                     *Vw = get("decoder.attn_net.v.weight", {1, D}),
+                     *Gi = get("decoder.attn_rnn.weight_ih", {3 * D, D + P2}), *Gh = get("decoder.attn_rnn.weight_hh", {3 * D, D}),
+                     *Gbi = get("decoder.attn_rnn.bias_ih", {3 * D}), *Gbh = get("decoder.attn_rnn.bias_hh", {3 * D}),
+                     *Wr = get("decoder.rnn_input.weight", {H, 2 * D}), *br = get("decoder.rnn_input.bias", {H}),
+                     *Ai = get("decoder.res_rnn1.weight_ih", {4 * H, H}), *Ah = get("decoder.res_rnn1.weight_hh", {4 * H, H}),
+                     *Abi = get("decoder.res_rnn1.bias_ih", {4 * H}), *Abh = get("decoder.res_rnn1.bias_hh", {4 * H}),
+                     *Bi = get("decoder.res_rnn2.weight_ih", {4 * H, H}), *Bh = get("decoder.res_rnn2.weight_hh", {4 * H, H}),
+                     *Bbi = get("decoder.res_rnn2.bias_ih", {4 * H}), *Bbh = get("decoder.res_rnn2.bias_hh", {4 * H}),
+                     *Wm = get("decoder.mel_proj.weight", {M * TC_MAXR, H});
+    if (!Wp || !W1 || !b1 || !W2 || !b2 || !Cw || !Lw || !Lb || !Wq || !bq || !Vw || !Gi || !Gh || !Gbi || !Gbh || !Wr || !br ||
+        !Ai || !Ah || !Abi || !Abh || !Bi || !Bh || !Bbi || !Bbh || !Wm)
+        return WRNN_ERR_STATE;
+    TacoParams &p = h->plan;
+    p.D = D; p.H = H; p.M = M; p.P1 = P1; p.P2 = P2; p.r = r;
+    p.NA = M * r + P1;
+    p.rpa = (p.NA + G - 1) / G;
+    p.rpb = (P2 + G - 1) / G;
+    p.upc = (D + G - 1) / G;
+    p.rpd = (D + G - 1) / G;
+    p.upl = (H + G - 1) / G;
+    const int KC = 2 * D + P2, KF = 2 * D + H, unitC = 2 * KC + (D + P2) + D;
+    auto r4 = [](int x) { return (x + 3) & ~3; };
+    int o = 0;
+    p.off_A = o;  o += p.rpa * H;
+    p.off_bA = o; o += r4(p.rpa);
+    p.off_B = o;  o += p.rpb * P1;
+    p.off_bB = o; o += r4(p.rpb);
+    p.off_C = o;  o += p.upc * unitC;
+    p.off_bC = o; o += r4(p.upc * 4);
+    p.off_D = o;  o += p.rpd * D;
+    p.off_bD = o; o += r4(p.rpd);
+    p.off_F = o;  o += p.upl * (4 * KF + 2 * D);
+    p.off_bF = o; o += r4(p.upl * 5);
+    p.off_G = o;  o += p.upl * 4 * 2 * H;
+    p.off_bG = o; o += r4(p.upl * 4);
+    p.img_floats = r4(o);
+    // (W_ih1 . W_rnn_input) and its bias, in double (once per checkpoint)
+    if (h->WcF.empty()) {
+        h->WcF.assign((size_t)4 * H * 2 * D, 0.0);
+        h->bcF.assign((size_t)4 * H, 0.0);
+        for (int g = 0; g < 4 * H; g++) {
+            double *dst = h->WcF.data() + (size_t)g * 2 * D;
+            double bacc = (double)Abi->v[g] + (double)Abh->v[g];
+            for (int j = 0; j < H; j++) {
+                const double wij = Ai->v[(size_t)g * H + j];
+                const float *src = Wr->v.data() + (size_t)j * 2 * D;
+                for (int k = 0; k < 2 * D; k++) dst[k] += wij * (double)src[k];
+                bacc += wij * (double)br->v[j];
+            }
+            h->bcF[g] = bacc;
+        }
+    }
+    // prenet.fc1 composed with the mel projection of the last frame of a step: [P1][H]
+    std::vector<double> W1c((size_t)P1 * H, 0.0);
+    for (int k = 0; k < P1; k++)
+        for (int m = 0; m < M; m++) {
+            const double w = W1->v[(size_t)k * M + m];
+            const float *src = Wm->v.data() + (size_t)(m * TC_MAXR + r - 1) * H;
+            double *dst = W1c.data() + (size_t)k * H;
+            for (int x = 0; x < H; x++) dst[x] += w * (double)src[x];
+        }
+    std::vector<float> img((size_t)G * p.img_floats, 0.f);
+    for (int c = 0; c < G; c++) {
+        float *im = img.data() + (size_t)c * p.img_floats;
+        for (int j = 0; j < p.rpa; j++) {
+            const int row = c * p.rpa + j;
+            if (row >= p.NA) break;
+            float *dst = im + p.off_A + (size_t)j * H;
+            if (row < M * r) {
+                const int m = row / r, jj = row - m * r;
+                memcpy(dst, Wm->v.data() + (size_t)(m * TC_MAXR + jj) * H, (size_t)H * sizeof(float));
+            } else {
+                const int k = row - M * r;
+                for (int x = 0; x < H; x++) dst[x] = (float)W1c[(size_t)k * H + x];
+                im[p.off_bA + j] = b1->v[k];
+            }
+        }
+        for (int j = 0; j < p.rpb; j++) {
+            const int row = c * p.rpb + j;
+            if (row >= P2) break;
+            memcpy(im + p.off_B + (size_t)j * P1, W2->v.data() + (size_t)row * P1, (size_t)P1 * sizeof(float));
+            im[p.off_bB + j] = b2->v[row];
+        }
+        for (int j = 0; j < p.upc; j++) {                   // GRU gate order r, z, n (torch.nn.GRUCell)
+            const int u = c * p.upc + j;
+            if (u >= D) break;
+            float *dst = im + p.off_C + (size_t)j * unitC;
+            for (int g = 0; g < 2; g++) {
+                memcpy(dst + (size_t)g * KC, Gi->v.data() + (size_t)(g * D + u) * (D + P2), (size_t)(D + P2) * sizeof(float));
+                memcpy(dst + (size_t)g * KC + D + P2, Gh->v.data() + (size_t)(g * D + u) * D, (size_t)D * sizeof(float));
+                im[p.off_bC + j * 4 + g] = (float)((double)Gbi->v[g * D + u] + (double)Gbh->v[g * D + u]);
+            }
+            memcpy(dst + 2 * KC, Gi->v.data() + (size_t)(2 * D + u) * (D + P2), (size_t)(D + P2) * sizeof(float));
+            memcpy(dst + 2 * KC + D + P2, Gh->v.data() + (size_t)(2 * D + u) * D, (size_t)D * sizeof(float));
+            im[p.off_bC + j * 4 + 2] = Gbi->v[2 * D + u];
+            im[p.off_bC + j * 4 + 3] = Gbh->v[2 * D + u];
+        }
+        for (int j = 0; j < p.rpd; j++) {
+            const int row = c * p.rpd + j;
+            if (row >= D) break;
+            memcpy(im + p.off_D + (size_t)j * D, Wq->v.data() + (size_t)row * D, (size_t)D * sizeof(float));
+            im[p.off_bD + j] = bq->v[row];
+        }
+        for (int j = 0; j < p.upl; j++) {                   // LSTM gate order i, f, g, o (torch.nn.LSTMCell)
+            const int u = c * p.upl + j;
+            if (u >= H) break;
+            for (int g = 0; g < 4; g++) {
+                float *dst = im + p.off_F + (size_t)(j * 4 + g) * KF;
+                const double *wc = h->WcF.data() + (size_t)(g * H + u) * 2 * D;
+                for (int k = 0; k < 2 * D; k++) dst[k] = (float)wc[k];
+                memcpy(dst + 2 * D, Ah->v.data() + (size_t)(g * H + u) * H, (size_t)H * sizeof(float));
+                im[p.off_bF + j * 5 + g] = (float)h->bcF[g * H + u];
+                float *dg = im + p.off_G + (size_t)(j * 4 + g) * 2 * H;
+                memcpy(dg, Bi->v.data() + (size_t)(g * H + u) * H, (size_t)H * sizeof(float));
+                memcpy(dg + H, Bh->v.data() + (size_t)(g * H + u) * H, (size_t)H * sizeof(float));
+                im[p.off_bG + j * 4 + g] = (float)((double)Bbi->v[g * H + u] + (double)Bbh->v[g * H + u]);
+            }
+            memcpy(im + p.off_F + (size_t)4 * p.upl * KF + (size_t)j * 2 * D, Wr->v.data() + (size_t)u * 2 * D, (size_t)2 * D * sizeof(float));
+            im[p.off_bF + j * 5 + 4] = br->v[u];
+        }
+    }
+    std::vector<float> common((size_t)2048 + D + (size_t)D * TC_FILT + D, 0.f);
+    memcpy(common.data(), Cw->v.data(), (size_t)TC_FILT * 2 * TC_KS * sizeof(float));
+    memcpy(common.data() + 2048, Vw->v.data(), (size_t)D * sizeof(float));
+    memcpy(common.data() + 2048 + D, Lw->v.data(), (size_t)D * TC_FILT * sizeof(float));
+    memcpy(common.data() + 2048 + D + (size_t)D * TC_FILT, Lb->v.data(), (size_t)D * sizeof(float));
+    std::vector<float> projT((size_t)D * D);
+    for (int oo = 0; oo < D; oo++)
+        for (int k = 0; k < D; k++) projT[(size_t)k * D + oo] = Wp->v[(size_t)oo * D + k];
+    for (float **q : {&h->image, &h->common, &h->projT}) {
+        if (*q) cudaFree(*q);
+        *q = nullptr;
+    }
+    TC_CUDA(h, cudaMalloc((void **)&h->image, img.size() * sizeof(float)));
+    TC_CUDA(h, cudaMemcpy(h->image, img.data(), img.size() * sizeof(float), cudaMemcpyHostToDevice));
+    TC_CUDA(h, cudaMalloc((void **)&h->common, common.size() * sizeof(float)));
+    TC_CUDA(h, cudaMemcpy(h->common, common.data(), common.size() * sizeof(float), cudaMemcpyHostToDevice));
+    TC_CUDA(h, cudaMalloc((void **)&h->projT, projT.size() * sizeof(float)));
+    TC_CUDA(h, cudaMemcpy(h->projT, projT.data(), projT.size() * sizeof(float), cudaMemcpyHostToDevice));
+    h->packed_r = r;
+    return 0;
+}
+
+}  // namespace wrnn
+
+using namespace wrnn;
+
+extern "C" {
+
+int wrnn_taco_create(int32_t decoder_dims, int32_t lstm_dims, int32_t n_mels, int device, wrnn_taco_handle **out) {
+    if (!out) return taco_fail(nullptr, WRNN_ERR_ARG, "null argument");
+    *out = nullptr;
+    // PreNet's widths are fixed at 256 / 128 (models/tacotron.py:137) and the attention GRU's input is
+    // decoder_dims + decoder_dims // 2 = context + prenet (:218), so the reference itself only runs at decoder_dims 256
+    if (decoder_dims != 256) return taco_fail(nullptr, WRNN_ERR_ARG, "decoder_dims must be 256 (PreNet's output is 128 = decoder_dims // 2)");
+    if (lstm_dims < 8 || lstm_dims % 4 || lstm_dims > 512 || n_mels < 1 || n_mels > 128)
+        return taco_fail(nullptr, WRNN_ERR_ARG, "lstm_dims must be a multiple of 4 up to 512, n_mels 1 .. 128");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) return taco_fail(nullptr, WRNN_ERR_CUDA, "no CUDA device: this library has no CPU fallback");
+    if (device < 0 || device >= ndev) return taco_fail(nullptr, WRNN_ERR_ARG, "device out of range");
+    cudaDeviceProp prop;
+    wrnn::DeviceGuard guard(device);
+    if (guard.err != cudaSuccess || cudaGetDeviceProperties(&prop, device) != cudaSuccess)
+        return taco_fail(nullptr, WRNN_ERR_CUDA, "cannot open device");
+    wrnn_taco_handle *h = new wrnn_taco_handle();
+    h->D = decoder_dims; h->H = lstm_dims; h->M = n_mels; h->device = device;
+    h->num_sms = prop.multiProcessorCount;
+    h->smem_optin = prop.sharedMemPerBlockOptin;
+    cudaEventCreate(&h->ev[0]);
+    cudaEventCreate(&h->ev[1]);
+    *out = h;
+    return 0;
+}
+
+void wrnn_taco_destroy(wrnn_taco_handle *h) {
+    if (!h) return;
+    wrnn::DeviceGuard guard(h->device);
+    for (float *q : {h->image, h->common, h->projT})
+        if (q) cudaFree(q);
+    if (h->ws) cudaFree(h->ws);
+    for (int i = 0; i < 2; i++)
+        if (h->ev[i]) cudaEventDestroy(h->ev[i]);
+    delete h;
+}
+
+const char *wrnn_taco_last_error(const wrnn_taco_handle *h) { return h ? h->err.c_str() : g_taco_err.c_str(); }
+
+int wrnn_taco_load_weights(wrnn_taco_handle *h, const wrnn_tensor *tensors, int32_t n) {
+    if (!h || (!tensors && n > 0)) return taco_fail(h, WRNN_ERR_ARG, "null argument");
+    for (int i = 0; i < n; i++) {
+        const wrnn_tensor &t = tensors[i];
+        if (!t.name || !t.data || t.ndim < 0 || t.ndim > 4) return taco_fail(h, WRNN_ERR_ARG, "bad tensor");
+        if (t.dtype != 0) continue;
+        HostTensor ht;
+        int64_t numel = 1;
+        for (int k = 0; k < t.ndim; k++) { ht.shape.push_back(t.shape[k]); numel *= t.shape[k]; }
+        ht.v.assign((const float *)t.data, (const float *)t.data + numel);
+        h->w[t.name] = std::move(ht);
+    }
+    h->packed_r = 0;
+    h->WcF.clear();
+    h->bcF.clear();
+    return 0;
+}
+
+int wrnn_taco_decode(wrnn_taco_handle *h, const float *enc_seq, int32_t L, int32_t r, int32_t steps, float stop_threshold,
+                     float *mel, float *attn, int32_t *n_iter, void *cuda_stream) {
+    if (!h || !enc_seq || !mel || !attn || !n_iter) return taco_fail(h, WRNN_ERR_ARG, "null argument");
+    if (L < 1 || r < 1 || r > TC_MAXR || steps < 1) return taco_fail(h, WRNN_ERR_ARG, "need L >= 1, 1 <= r <= 20 (Decoder.max_r), steps >= 1");
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    wrnn::DeviceGuard guard(h->device);
+    TC_CUDA(h, guard.err);
+    if (h->packed_r != r) {
+        if (h->w.empty()) return taco_fail(h, WRNN_ERR_STATE, "weights not loaded: call wrnn_taco_load_weights first");
+        const int rc = taco_pack(h, r);
+        if (rc) return rc;
+    }
+    const int D = h->D, H = h->H, M = h->M, G = h->num_sms;
+    TacoParams P = h->plan;
+    P.L = L;
+    P.max_iter = (steps + r - 1) / r;                    // `for t in range(0, steps, r)` (:446)
+    P.cap = P.max_iter * r;
+    P.thr = stop_threshold;
+    // attention positions go to the CTAs that own no LSTM units when there are at least 8 of them (their F / G image
+    // space is free for the position data), else to all CTAs
+    const int n_lstm = (H + P.upl - 1) / P.upl;
+    const bool disjoint = G - n_lstm >= 8;
+    P.pc0 = disjoint ? n_lstm : 0;
+    const int owners = disjoint ? G - n_lstm : G;
+    P.PP = (L + owners - 1) / owners;
+    P.PC = (L + P.PP - 1) / P.PP;
+    const int e_floats = 3 * P.PP * D + 2048 + 2 * (P.PP + 2 * TC_HALO + 2) + TC_FILT * P.PP + 2 * P.PP + 8 * P.PP + 8;
+    P.off_E = disjoint ? P.off_F : P.img_floats;
+    P.sm_vec = std::max(P.img_floats, (P.off_E + e_floats + 3) & ~3);
+    P.sm_ctx = P.sm_vec + std::max(2 * D + H, 2 * H);
+    P.sm_misc = P.sm_ctx + D;
+    const size_t smem_bytes = ((size_t)P.sm_misc + 32 + 2 * P.upl + 8) * sizeof(float);
+    if (smem_bytes > h->smem_optin) {
+        char b[256];
+        snprintf(b, sizeof b, "decoder loop needs %zu bytes of shared memory per SM (r = %d, %d characters), the device allows %zu",
+                 smem_bytes, r, L, h->smem_optin);
+        return taco_fail(h, WRNN_ERR_ARG, b);
+    }
+    // workspace: sync[128 B] | state vectors | n_iter | enc, enc_proj | mel_out [M][cap] | attn_out [max_iter][L]
+    size_t off = 128;
+    auto take = [&](size_t floats) { const size_t o = off; off += ((floats * 4 + 127) & ~(size_t)127); return o; };
+    const size_t o_p1 = take(P.P1), o_p2 = take(P.P2), o_ha = take(2 * D), o_pq = take(D), o_pc = take((size_t)owners * D),
+                 o_ps = take(owners), o_x2 = take(H), o_h1 = take(2 * H), o_h2 = take(2 * H), o_x3 = take(H),
+                 o_melf = take((size_t)M * TC_MAXR), o_att = take(L), o_cum = take(L), o_n = take(1);
+    const size_t state_end = off;
+    const size_t o_enc = take((size_t)L * D), o_encp = take((size_t)L * D), o_mel = take((size_t)M * P.cap),
+                 o_attn = take((size_t)P.max_iter * L);
+    if (off > h->ws_bytes) {
+        if (h->ws) cudaFree(h->ws);
+        h->ws = nullptr; h->ws_bytes = 0;
+        TC_CUDA(h, cudaMalloc(&h->ws, off + off / 8));
+        h->ws_bytes = off + off / 8;
+    }
+    char *ws = (char *)h->ws;
+    auto F = [&](size_t o) { return (float *)(ws + o); };
+    TC_CUDA(h, cudaMemsetAsync(ws, 0, state_end, st));
+    TC_CUDA(h, cudaMemcpyAsync(ws + o_enc, enc_seq, (size_t)L * D * 4, cudaMemcpyHostToDevice, st));
+    P.image = h->image; P.common = h->common; P.enc = F(o_enc); P.encp = F(o_encp);
+    P.p1 = F(o_p1); P.p2 = F(o_p2); P.ha = F(o_ha); P.pq = F(o_pq); P.part_ctx = F(o_pc); P.part_sum = F(o_ps);
+    P.x2 = F(o_x2); P.h1 = F(o_h1); P.h2 = F(o_h2); P.x3 = F(o_x3); P.melf = F(o_melf); P.att_g = F(o_att); P.cum_g = F(o_cum);
+    P.mel_out = F(o_mel); P.attn_out = F(o_attn); P.n_iter = (int *)(ws + o_n);
+    P.gs.counter = (unsigned long long *)ws;
+    P.gs.abort_flag = (int *)(ws + 64);
+    TC_CUDA(h, cudaFuncSetAttribute(taco_loop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+    TC_CUDA(h, cudaEventRecord(h->ev[0], st));
+    taco_encproj_kernel<<<L, 256, D * sizeof(float), st>>>(P.enc, h->projT, F(o_encp), D);
+    void *args[] = {(void *)&P};
+    TC_CUDA(h, cudaLaunchCooperativeKernel((const void *)taco_loop_kernel, dim3(G), dim3(TC_THREADS), args, smem_bytes, st));
+    TC_CUDA(h, cudaEventRecord(h->ev[1], st));
+    h->launches = 2;
+    int head[2] = {0, 0};           // abort flag, n_iter
+    TC_CUDA(h, cudaMemcpyAsync(&head[0], ws + 64, sizeof(int), cudaMemcpyDeviceToHost, st));
+    TC_CUDA(h, cudaMemcpyAsync(&head[1], ws + o_n, sizeof(int), cudaMemcpyDeviceToHost, st));
+    TC_CUDA(h, cudaStreamSynchronize(st));
+    TC_CUDA(h, cudaGetLastError());
+    if (head[0]) return taco_fail(h, WRNN_ERR_CUDA, "Tacotron decoder loop kernel aborted: grid barrier watchdog fired");
+    const int n = head[1];
+    if (n < 1 || n > P.max_iter) return taco_fail(h, WRNN_ERR_CUDA, "Tacotron decoder loop kernel returned an impossible step count");
+    // mel: (n_mels, n * r) row-major as `torch.cat(mel_outputs, dim=2)[0]`; attn: (n, L)
+    TC_CUDA(h, cudaMemcpy2DAsync(mel, (size_t)n * r * 4, ws + o_mel, (size_t)P.cap * 4, (size_t)n * r * 4, M, cudaMemcpyDeviceToHost, st));
+    TC_CUDA(h, cudaMemcpyAsync(attn, ws + o_attn, (size_t)n * L * 4, cudaMemcpyDeviceToHost, st));
+    TC_CUDA(h, cudaStreamSynchronize(st));
+    *n_iter = n;
+    return 0;
+}
+
+int wrnn_taco_last_timing(wrnn_taco_handle *h, float *ms_loop, int64_t *kernel_launches) {
+    if (!h) return WRNN_ERR_ARG;
+    float ms = 0;
+    TC_CUDA(h, cudaEventSynchronize(h->ev[1]));
+    TC_CUDA(h, cudaEventElapsedTime(&ms, h->ev[0], h->ev[1]));
+    if (ms_loop) *ms_loop = ms;
+    if (kernel_launches) *kernel_launches = h->launches;
+    return 0;
+}
+
+}  // extern "C"

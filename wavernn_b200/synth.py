@@ -107,3 +107,50 @@ def synth_dm_state_dict(hidden_size: int = 896, quantisation: int = 256, seed: i
             w = r.uniform(-0.2, 0.2, size=shape)
         out[key] = np.ascontiguousarray(w, dtype=np.float32)
     return out
+
+
+def taco_decoder_spec(decoder_dims: int = 256, lstm_dims: int = 512, n_mels: int = 80, max_r: int = 20):
+    """Keys and shapes of the Tacotron decoder loop's parameters (`models/tacotron.py:171-227,300-303`)."""
+    D, H, M = decoder_dims, lstm_dims, n_mels
+    return [('encoder_proj.weight', (D, D)),
+            ('decoder.prenet.fc1.weight', (256, M)), ('decoder.prenet.fc1.bias', (256,)),
+            ('decoder.prenet.fc2.weight', (128, 256)), ('decoder.prenet.fc2.bias', (128,)),
+            ('decoder.attn_net.conv.weight', (32, 2, 31)),
+            ('decoder.attn_net.L.weight', (D, 32)), ('decoder.attn_net.L.bias', (D,)),
+            ('decoder.attn_net.W.weight', (D, D)), ('decoder.attn_net.W.bias', (D,)),
+            ('decoder.attn_net.v.weight', (1, D)),
+            ('decoder.attn_rnn.weight_ih', (3 * D, D + D // 2)), ('decoder.attn_rnn.weight_hh', (3 * D, D)),
+            ('decoder.attn_rnn.bias_ih', (3 * D,)), ('decoder.attn_rnn.bias_hh', (3 * D,)),
+            ('decoder.rnn_input.weight', (H, 2 * D)), ('decoder.rnn_input.bias', (H,)),
+            ('decoder.res_rnn1.weight_ih', (4 * H, H)), ('decoder.res_rnn1.weight_hh', (4 * H, H)),
+            ('decoder.res_rnn1.bias_ih', (4 * H,)), ('decoder.res_rnn1.bias_hh', (4 * H,)),
+            ('decoder.res_rnn2.weight_ih', (4 * H, H)), ('decoder.res_rnn2.weight_hh', (4 * H, H)),
+            ('decoder.res_rnn2.bias_ih', (4 * H,)), ('decoder.res_rnn2.bias_hh', (4 * H,)),
+            ('decoder.mel_proj.weight', (M * max_r, H))]
+
+
+def synth_taco_state_dict(decoder_dims: int = 256, lstm_dims: int = 512, n_mels: int = 80, seed: int = 0,
+                          gain: float = 2.0):
+    """Seeded decoder-loop checkpoint: uniform +-gain/sqrt(fan_in) matrices (the attention energies, the gates and
+    the mel frames move over a useful range at gain 2), small biases."""
+    out = {}
+    for key, shape in taco_decoder_spec(decoder_dims, lstm_dims, n_mels):
+        r = _rs(seed, 'taco.' + key)
+        if len(shape) >= 2:
+            b = gain / np.sqrt(int(np.prod(shape[1:])))
+            if key.endswith('attn_net.v.weight'):
+                b *= 6.0            # energies of +-8: a peaked attention that moves, not a flat one
+            w = r.uniform(-b, b, size=shape)
+        else:
+            w = r.uniform(-0.2, 0.2, size=shape)
+        out[key] = np.ascontiguousarray(w, dtype=np.float32)
+    # a trained LSA keeps most energies far below zero (smoothed attention = sigmoid / sum of sigmoids): lean the query
+    # bias against v so that only a few positions per step come near sigmoid's upper half
+    out['decoder.attn_net.W.bias'] -= (0.15 * np.sign(out['decoder.attn_net.v.weight'][0])).astype(np.float32)
+    return out
+
+
+def synth_encoder_seq(L: int, decoder_dims: int = 256, seed: int = 77):
+    """Stand-in for the CBHG encoder's output (a bidirectional GRU's hidden states: values in (-1, 1))."""
+    r = np.random.RandomState(seed)
+    return np.ascontiguousarray(np.tanh(r.normal(0.0, 0.8, size=(L, decoder_dims))), dtype=np.float32)
