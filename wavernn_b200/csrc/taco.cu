@@ -17,6 +17,7 @@
 // Dropout and zoneout are training-only (eval mode in generate, :423).
 #include <math.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -46,18 +47,28 @@ struct TacoParams {
     float *p1, *p2, *ha, *pq, *part_ctx, *part_sum, *x2, *h1, *h2, *x3, *melf, *att_g, *cum_g;
     float *mel_out, *attn_out;
     int *n_iter;
+    long long *prof;                               // debug (WRNN_TACO_PROF): [2 CTAs][32] clocks per site, summed over steps
     GridSync gs;
 };
 
 __device__ __forceinline__ float warp_dot(const float *w, const float *x, int k4, int lane) {
     float a0 = 0.f, a1 = 0.f;
     const float4 *w4 = reinterpret_cast<const float4 *>(w), *x4 = reinterpret_cast<const float4 *>(x);
-    for (int i = lane; i < k4; i += 32) {
-        const float4 a = w4[i], b = x4[i];
-        a0 = fmaf(a.x, b.x, a0);
-        a1 = fmaf(a.y, b.y, a1);
-        a0 = fmaf(a.z, b.z, a0);
-        a1 = fmaf(a.w, b.w, a1);
+    for (int i0 = lane; i0 < k4; i0 += 128) {                   // four float4 pairs in flight per lane
+        float4 a[4], b[4];
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            const int i = i0 + 32 * q;
+            a[q] = i < k4 ? w4[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+            b[q] = i < k4 ? x4[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            a0 = fmaf(a[q].x, b[q].x, a0);
+            a1 = fmaf(a[q].y, b[q].y, a1);
+            a0 = fmaf(a[q].z, b[q].z, a0);
+            a1 = fmaf(a[q].w, b[q].w, a1);
+        }
     }
     a0 += a1;
 #pragma unroll
@@ -91,6 +102,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
     float *sv = conv + TC_FILT * P.PP;                   // [PP] sigmoid(u)
     float *cumv = sv + P.PP;                             // [PP] cumulative attention
     float *red = cumv + P.PP;                            // [PP][8]
+    float *psum_s = misc + 32 + 2 * P.upl, *chalf = psum_s + 160;      // [<= 148] partial sums, [D] second half of the context sum
     const int a = tid & 255, half = tid >> 8;            // energy thread = (attention dim a, position parity); D == 256
     float lw[TC_FILT], lb = 0.f, va = 0.f;
     if (owner && nl > 0) {
@@ -104,6 +116,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
 #pragma unroll
         for (int f = 0; f < TC_FILT; f++) lw[f] = P.common[2048 + D + a * TC_FILT + f];
         lb = P.common[2048 + D + D * TC_FILT + a];
+        for (int p = half; p < nl; p += 2) ploc[(size_t)p * D + a] = lb;      // step 0: cumulative = attention = 0
     }
     for (int i = tid; i < D; i += TC_THREADS) ctx[i] = 0.f;
     for (int i = tid; i < 2 * P.upl; i += TC_THREADS) c1[i] = 0.f;
@@ -122,12 +135,36 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
     const int nmel = P.M * r;
     unsigned long long gen = 0;
     int n_done = 0;
+    __shared__ long long prof_acc[32];
+    long long prof_last = 0;
+    const bool prof_on = P.prof != nullptr && tid == 0 && (cta == 0 || cta == P.pc0);
+    if (tid < 32) prof_acc[tid] = 0;
+#define TMARK(i)                                      \
+    if (prof_on) {                                    \
+        const long long c__ = clock64();              \
+        prof_acc[i] += c__ - prof_last;               \
+        prof_last = c__;                              \
+    }
+
+    // staging: every vector is at most 1024 floats, so a thread holds at most one float4 of each; the loads of all the
+    // vectors of a stage are issued before the first is stored (one L2 round trip per stage, not one per vector)
+    const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    auto ld4 = [&](const float *src, int n) { return tid < (n >> 2) ? __ldcg(reinterpret_cast<const float4 *>(src) + tid) : z4; };
+    auto st4 = [&](float *dst, int n, const float4 &v) { if (tid < (n >> 2)) reinterpret_cast<float4 *>(dst)[tid] = v; };
+    // activation of LSTM gate row w = unit * 4 + gate, applied by the warp that formed the row (gates i, f, g, o)
+    auto lstm_act = [&](int w, float x) { return (w & 3) == 2 ? tanhf(x) : sigmoidf_acc(x); };
 
     for (int it = 0;; it++) {
         const int cur = it & 1, nxt = cur ^ 1;
-        // ---- A: mel frames of step it-1, prenet.fc1 of step it (x3 = 0 before the first step: fc1(go frame) = relu(b))
-        stage_vec(vec, P.x3, H, tid);
+        // ---- A: mel frames of step it-1, prenet.fc1 of step it (x3 = 0 before the first step: fc1(go frame) = relu(b));
+        //         position owners finish the location features of this step (L . conv + b; the conv was formed in G)
+        if (prof_on) prof_last = clock64();
+        {
+            const float4 v = ld4(P.x3, H);
+            st4(vec, H, v);
+        }
         __syncthreads();
+        TMARK(0);
         for (int j = warp; j < na; j += TC_WARPS) {
             const float d = warp_dot(WA + (size_t)j * H, vec, H >> 2, lane);
             if (lane == 0) {
@@ -143,43 +180,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
                 }
             }
         }
-        grid_barrier(P.gs, gen);
-        n_done = it;
-        if (it == P.max_iter) break;
-        // ---- B: stop rule on the frames of step it-1 (:455: all below the threshold and t > 10), prenet.fc2,
-        //         location features (conv over [cumulative | attention] + L) of the owned positions for this step
-        {
-            int ok = 1;
-            if (it > 0 && (it - 1) * r > 10) {
-                for (int i = tid; i < nmel; i += TC_THREADS) ok &= (__ldcg(P.melf + i) < P.thr) ? 1 : 0;
-            } else {
-                ok = 0;
-            }
-            stage_vec(vec, P.p1, P.P1, tid);
-            if (__syncthreads_and(ok)) break;
-        }
-        for (int j = warp; j < nb; j += TC_WARPS) {
-            const float d = warp_dot(WB + (size_t)j * P.P1, vec, P.P1 >> 2, lane);
-            if (lane == 0) P.p2[b0 + j] = fmaxf(d + bB[j], 0.f);
-        }
-        if (nl > 0) {
-            const int span = nl + 2 * TC_HALO;
-            for (int i = tid; i < 2 * span; i += TC_THREADS) {
-                const int c = i / span, k = i - c * span, l = l0 - TC_HALO + k;
-                loc[c * (P.PP + 2 * TC_HALO + 2) + k] = (l >= 0 && l < L) ? __ldcg((c == 0 ? P.cum_g : P.att_g) + l) : 0.f;
-            }
-            __syncthreads();
-            for (int i = tid; i < TC_FILT * nl; i += TC_THREADS) {
-                const int f = i / nl, p = i - f * nl;
-                float acc = 0.f;
-#pragma unroll
-                for (int c = 0; c < 2; c++) {
-                    const float *w = cw + (f * 2 + c) * TC_KS, *x = loc + c * (P.PP + 2 * TC_HALO + 2) + p;
-                    for (int k = 0; k < TC_KS; k++) acc = fmaf(w[k], x[k], acc);
-                }
-                conv[f * P.PP + p] = acc;
-            }
-            __syncthreads();
+        if (nl > 0 && it > 0) {
             for (int p = half; p < nl; p += 2) {
                 float acc = lb;
 #pragma unroll
@@ -187,12 +188,45 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
                 ploc[(size_t)p * D + a] = acc;
             }
         }
+        TMARK(1);
         grid_barrier(P.gs, gen);
+        TMARK(2);
+        n_done = it;
+        if (it == P.max_iter) break;
+        // ---- B: stop rule on the frames of step it-1 (:455: all below the threshold and t > 10), prenet.fc2
+        {
+            const bool check = it > 0 && (it - 1) * r > 10;
+            float mv[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};     // nmel <= 128 * 20 = 5 threads' worth at most
+            if (check) {
+#pragma unroll
+                for (int q = 0; q < 4; q++)
+                    if (tid + q * TC_THREADS < nmel) mv[q] = __ldcg(P.melf + tid + q * TC_THREADS);
+            }
+            const float4 v = ld4(P.p1, P.P1);
+            st4(vec, P.P1, v);
+            int ok = check ? 1 : 0;
+#pragma unroll
+            for (int q = 0; q < 4; q++) ok &= (mv[q] < P.thr) ? 1 : 0;
+            for (int i = tid + 4 * TC_THREADS; check && i < nmel; i += TC_THREADS) ok &= (__ldcg(P.melf + i) < P.thr) ? 1 : 0;
+            if (__syncthreads_and(ok)) break;
+        }
+        TMARK(3);
+        for (int j = warp; j < nb; j += TC_WARPS) {
+            const float d = warp_dot(WB + (size_t)j * P.P1, vec, P.P1 >> 2, lane);
+            if (lane == 0) P.p2[b0 + j] = fmaxf(d + bB[j], 0.f);
+        }
+        TMARK(4);
+        grid_barrier(P.gs, gen);
+        TMARK(5);
         // ---- C: attention GRU cell
-        for (int i = tid; i < D; i += TC_THREADS) vec[i] = ctx[i];
-        stage_vec(vec + D, P.p2, P.P2, tid);
-        stage_vec(vec + D + P.P2, P.ha + (size_t)cur * D, D, tid);
+        {
+            const float4 v1 = ld4(P.p2, P.P2), v2 = ld4(P.ha + (size_t)cur * D, D);
+            if (tid < D) vec[tid] = ctx[tid];
+            st4(vec + D, P.P2, v1);
+            st4(vec + D + P.P2, D, v2);
+        }
         __syncthreads();
+        TMARK(6);
         for (int w = warp; w < 4 * ng; w += TC_WARPS) {
             const int j = w >> 2, q = w & 3;
             const float *row = WC + (size_t)j * (2 * KC + (D + P.P2) + D);
@@ -200,27 +234,37 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
             if (q < 2) d = warp_dot(row + (size_t)q * KC, vec, KC >> 2, lane);
             else if (q == 2) d = warp_dot(row + 2 * KC, vec, (D + P.P2) >> 2, lane);
             else d = warp_dot(row + 2 * KC + D + P.P2, vec + D + P.P2, D >> 2, lane);
-            if (lane == 0) gsum[w] = d;
+            if (lane == 0) gsum[w] = q < 2 ? sigmoidf_acc(d + bC[w]) : d + bC[w];
         }
         __syncthreads();
         if (tid < ng) {
-            const float *b = bC + tid * 4;
-            const float rr = sigmoidf_acc(gsum[tid * 4 + 0] + b[0]), zz = sigmoidf_acc(gsum[tid * 4 + 1] + b[1]);
-            const float nn = tanhf(gsum[tid * 4 + 2] + b[2] + rr * (gsum[tid * 4 + 3] + b[3]));
+            const float rr = gsum[tid * 4 + 0], zz = gsum[tid * 4 + 1];
+            const float nn = tanhf(gsum[tid * 4 + 2] + rr * gsum[tid * 4 + 3]);
             P.ha[(size_t)nxt * D + g0 + tid] = (1.f - zz) * nn + zz * vec[D + P.P2 + g0 + tid];
         }
+        TMARK(7);
         grid_barrier(P.gs, gen);
+        TMARK(8);
         // ---- D: processed query
-        stage_vec(vec, P.ha + (size_t)nxt * D, D, tid);
+        {
+            const float4 v = ld4(P.ha + (size_t)nxt * D, D);
+            st4(vec, D, v);
+        }
         __syncthreads();
+        TMARK(9);
         for (int j = warp; j < nd; j += TC_WARPS) {
             const float d = warp_dot(WD + (size_t)j * D, vec, D >> 2, lane);
             if (lane == 0) P.pq[d0 + j] = d + bD[j];
         }
+        TMARK(10);
         grid_barrier(P.gs, gen);
+        TMARK(11);
         // ---- E: energies, sigmoid and the partial context of the owned positions
         if (nl > 0) {
-            stage_vec(vec, P.pq, D, tid);
+            {
+                const float4 v = ld4(P.pq, D);
+                st4(vec, D, v);
+            }
             __syncthreads();
             for (int p = half; p < nl; p += 2) {
                 float v = va * tanhf(vec[a] + encp_s[(size_t)p * D + a] + ploc[(size_t)p * D + a]);
@@ -231,7 +275,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
             __syncthreads();
             if (tid < nl) {
                 float e = 0.f;
-                for (int w = 0; w < D / 32; w++) e += red[tid * 8 + w];
+                for (int w = 0; w < 8; w++) e += red[tid * 8 + w];
                 sv[tid] = sigmoidf_acc(e);
             }
             __syncthreads();
@@ -245,17 +289,33 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
                 P.part_sum[pi] = s;
             }
         }
+        TMARK(12);
         grid_barrier(P.gs, gen);
+        TMARK(13);
         // ---- F: context = sum of partials / sum of sums; rnn_input + LSTM 1; owners normalise their scores
         {
+            const float4 v2 = ld4(P.ha + (size_t)nxt * D, D), v3 = ld4(P.h1 + (size_t)cur * H, H);
+            // partial sums: thread p loads one; partial contexts: (d, half) sums every second partial, eight loads in flight
+            const float ps = tid < P.PC ? __ldcg(P.part_sum + tid) : 0.f;
+            float acc = 0.f;
+            for (int p0 = half; p0 < P.PC; p0 += 16) {
+                float t8[8];
+#pragma unroll
+                for (int q = 0; q < 8; q++) t8[q] = (p0 + 2 * q < P.PC) ? __ldcg(P.part_ctx + (size_t)(p0 + 2 * q) * D + a) : 0.f;
+#pragma unroll
+                for (int q = 0; q < 8; q++) acc += t8[q];
+            }
+            st4(vec + D, D, v2);
+            st4(vec + 2 * D, H, v3);
+            if (tid < P.PC) psum_s[tid] = ps;
+            if (half) chalf[a] = acc;
+            __syncthreads();
             float total = 0.f;
-            for (int p = 0; p < P.PC; p++) total += __ldcg(P.part_sum + p);
-            if (tid < D) {
-                float acc = 0.f;
-                for (int p = 0; p < P.PC; p++) acc += __ldcg(P.part_ctx + (size_t)p * D + tid);
-                const float c = acc / total;
-                ctx[tid] = c;
-                vec[tid] = c;
+            for (int p = 0; p < P.PC; p++) total += psum_s[p];
+            if (!half) {
+                const float c = (acc + chalf[a]) / total;
+                ctx[a] = c;
+                vec[a] = c;
             }
             if (tid < nl) {
                 const float att = sv[tid] / total;
@@ -266,46 +326,85 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
                 P.attn_out[(size_t)it * L + l0 + tid] = att;
             }
         }
-        stage_vec(vec + D, P.ha + (size_t)nxt * D, D, tid);
-        stage_vec(vec + 2 * D, P.h1 + (size_t)cur * H, H, tid);
         __syncthreads();
+        TMARK(14);
         for (int w = warp; w < 5 * nu; w += TC_WARPS) {
-            float d;
-            if (w < 4 * nu) d = warp_dot(WF + (size_t)w * KF, vec, KF >> 2, lane);                        // w = unit * 4 + gate
-            else d = warp_dot(WF + (size_t)4 * P.upl * KF + (size_t)(w - 4 * nu) * 2 * D, vec, (2 * D) >> 2, lane);
-            if (lane == 0) gsum[w] = d;
+            if (w < 4 * nu) {                                                                               // w = unit * 4 + gate
+                const float d = warp_dot(WF + (size_t)w * KF, vec, KF >> 2, lane);
+                if (lane == 0) gsum[w] = lstm_act(w, d + bF[(w >> 2) * 5 + (w & 3)]);
+            } else {
+                const float d = warp_dot(WF + (size_t)4 * P.upl * KF + (size_t)(w - 4 * nu) * 2 * D, vec, (2 * D) >> 2, lane);
+                if (lane == 0) gsum[w] = d + bF[(w - 4 * nu) * 5 + 4];
+            }
         }
         __syncthreads();
         if (tid < nu) {
-            const float *b = bF + tid * 5;
-            const float ig = sigmoidf_acc(gsum[tid * 4 + 0] + b[0]), fg = sigmoidf_acc(gsum[tid * 4 + 1] + b[1]);
-            const float gg = tanhf(gsum[tid * 4 + 2] + b[2]), og = sigmoidf_acc(gsum[tid * 4 + 3] + b[3]);
-            const float c = fg * c1[tid] + ig * gg, h = og * tanhf(c);
+            const float c = gsum[tid * 4 + 1] * c1[tid] + gsum[tid * 4 + 0] * gsum[tid * 4 + 2], h = gsum[tid * 4 + 3] * tanhf(c);
             c1[tid] = c;
             P.h1[(size_t)nxt * H + u0 + tid] = h;
-            P.x2[u0 + tid] = (gsum[4 * nu + tid] + b[4]) + h;
+            P.x2[u0 + tid] = gsum[4 * nu + tid] + h;
         }
+        TMARK(15);
         grid_barrier(P.gs, gen);
-        // ---- G: LSTM 2 on x + h1
-        stage_vec(vec, P.x2, H, tid);
-        stage_vec(vec + H, P.h2 + (size_t)cur * H, H, tid);
+        TMARK(16);
+        // ---- G: LSTM 2 on x + h1; position owners convolve [cumulative | attention] for the next step
+        {
+            const float4 v1 = ld4(P.x2, H), v2 = ld4(P.h2 + (size_t)cur * H, H);
+            float hl[2] = {0.f, 0.f};
+            const int span = nl + 2 * TC_HALO;
+            if (nl > 0 && tid < 2 * span) {
+                const int c = tid / span, k = tid - c * span, l = l0 - TC_HALO + k;
+                hl[0] = (l >= 0 && l < L) ? __ldcg((c == 0 ? P.cum_g : P.att_g) + l) : 0.f;
+            }
+            if (nl > 0 && tid + TC_THREADS < 2 * span) {
+                const int i = tid + TC_THREADS, c = i / span, k = i - c * span, l = l0 - TC_HALO + k;
+                hl[1] = (l >= 0 && l < L) ? __ldcg((c == 0 ? P.cum_g : P.att_g) + l) : 0.f;
+            }
+            st4(vec, H, v1);
+            st4(vec + H, H, v2);
+            if (nl > 0) {
+#pragma unroll
+                for (int q = 0; q < 2; q++) {
+                    const int i = tid + q * TC_THREADS;
+                    if (i < 2 * span) {
+                        const int c = i / span, k = i - c * span;
+                        loc[c * (P.PP + 2 * TC_HALO + 2) + k] = hl[q];
+                    }
+                }
+            }
+        }
         __syncthreads();
+        TMARK(17);
         for (int w = warp; w < 4 * nu; w += TC_WARPS) {
             const float d = warp_dot(WG + (size_t)w * 2 * H, vec, (2 * H) >> 2, lane);
-            if (lane == 0) gsum[w] = d;
+            if (lane == 0) gsum[w] = lstm_act(w, d + bG[w]);
+        }
+        if (nl > 0) {
+            for (int i = tid; i < TC_FILT * nl; i += TC_THREADS) {
+                const int f = i / nl, p = i - f * nl;
+                float acc = 0.f;
+#pragma unroll
+                for (int c = 0; c < 2; c++) {
+                    const float *w = cw + (f * 2 + c) * TC_KS, *x = loc + c * (P.PP + 2 * TC_HALO + 2) + p;
+#pragma unroll
+                    for (int k = 0; k < TC_KS; k++) acc = fmaf(w[k], x[k], acc);
+                }
+                conv[f * P.PP + p] = acc;
+            }
         }
         __syncthreads();
         if (tid < nu) {
-            const float *b = bG + tid * 4;
-            const float ig = sigmoidf_acc(gsum[tid * 4 + 0] + b[0]), fg = sigmoidf_acc(gsum[tid * 4 + 1] + b[1]);
-            const float gg = tanhf(gsum[tid * 4 + 2] + b[2]), og = sigmoidf_acc(gsum[tid * 4 + 3] + b[3]);
-            const float c = fg * c2[tid] + ig * gg, h = og * tanhf(c);
+            const float c = gsum[tid * 4 + 1] * c2[tid] + gsum[tid * 4 + 0] * gsum[tid * 4 + 2], h = gsum[tid * 4 + 3] * tanhf(c);
             c2[tid] = c;
             P.h2[(size_t)nxt * H + u0 + tid] = h;
             P.x3[u0 + tid] = vec[u0 + tid] + h;
         }
+        TMARK(18);
         grid_barrier(P.gs, gen);
+        TMARK(19);
     }
+    if (prof_on)
+        for (int i = 0; i < 32; i++) P.prof[(cta == 0 ? 0 : 32) + i] = prof_acc[i];
     if (cta == 0 && tid == 0) *P.n_iter = n_done;
 }
 
@@ -614,7 +713,7 @@ int wrnn_taco_decode(wrnn_taco_handle *h, const float *enc_seq, int32_t L, int32
     P.sm_vec = std::max(P.img_floats, (P.off_E + e_floats + 3) & ~3);
     P.sm_ctx = P.sm_vec + std::max(2 * D + H, 2 * H);
     P.sm_misc = P.sm_ctx + D;
-    const size_t smem_bytes = ((size_t)P.sm_misc + 32 + 2 * P.upl + 8) * sizeof(float);
+    const size_t smem_bytes = ((size_t)P.sm_misc + 32 + 2 * P.upl + 160 + D + 8) * sizeof(float);
     if (smem_bytes > h->smem_optin) {
         char b[256];
         snprintf(b, sizeof b, "decoder loop needs %zu bytes of shared memory per SM (r = %d, %d characters), the device allows %zu",
@@ -646,6 +745,13 @@ int wrnn_taco_decode(wrnn_taco_handle *h, const float *enc_seq, int32_t L, int32
     P.mel_out = F(o_mel); P.attn_out = F(o_attn); P.n_iter = (int *)(ws + o_n);
     P.gs.counter = (unsigned long long *)ws;
     P.gs.abort_flag = (int *)(ws + 64);
+    P.prof = nullptr;
+    long long *d_prof = nullptr;
+    if (getenv("WRNN_TACO_PROF")) {
+        TC_CUDA(h, cudaMalloc((void **)&d_prof, 64 * sizeof(long long)));
+        TC_CUDA(h, cudaMemsetAsync(d_prof, 0, 64 * sizeof(long long), st));
+        P.prof = d_prof;
+    }
     TC_CUDA(h, cudaFuncSetAttribute(taco_loop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
     TC_CUDA(h, cudaEventRecord(h->ev[0], st));
     taco_encproj_kernel<<<L, 256, D * sizeof(float), st>>>(P.enc, h->projT, F(o_encp), D);
@@ -659,6 +765,16 @@ int wrnn_taco_decode(wrnn_taco_handle *h, const float *enc_seq, int32_t L, int32
     TC_CUDA(h, cudaStreamSynchronize(st));
     TC_CUDA(h, cudaGetLastError());
     if (head[0]) return taco_fail(h, WRNN_ERR_CUDA, "Tacotron decoder loop kernel aborted: grid barrier watchdog fired");
+    if (d_prof) {
+        long long pr[64];
+        cudaMemcpy(pr, d_prof, sizeof pr, cudaMemcpyDeviceToHost);
+        cudaFree(d_prof);
+        static const char *site[20] = {"A stage", "A dots", "A barrier", "B stage+stop", "B dots+loc", "B barrier", "C stage", "C dots+gates", "C barrier",
+                                       "D stage", "D dots", "D barrier", "E", "E barrier", "F stage+ctx", "F dots+gates", "F barrier", "G stage", "G dots+gates", "G barrier"};
+        const int nn = std::max(1, head[1]);
+        fprintf(stderr, "taco prof (clk per decoder step; CTA 0 | first position owner)\n");
+        for (int i = 0; i < 20; i++) fprintf(stderr, "  %-14s %7.0f | %7.0f\n", site[i], (double)pr[i] / nn, (double)pr[32 + i] / nn);
+    }
     const int n = head[1];
     if (n < 1 || n > P.max_iter) return taco_fail(h, WRNN_ERR_CUDA, "Tacotron decoder loop kernel returned an impossible step count");
     // mel: (n_mels, n * r) row-major as `torch.cat(mel_outputs, dim=2)[0]`; attn: (n, L)
