@@ -44,7 +44,8 @@ struct TacoParams {
     const float *image;                            // [G][img_floats]
     const float *common;                           // conv w [32][2][31] (+pad to 2048) | v [D] | L.weight [D][32] | L.bias [D]
     const float *enc, *encp;                       // [L][D]
-    float *p1, *p2, *ha, *pq, *part_ctx, *part_sum, *x2, *h1, *h2, *x3, *melf, *att_g, *cum_g;
+    uint2 *p1, *p2, *ha, *pq, *x2, *h1, *h2, *x3, *att_g, *cum_g;      // tagged words {value, 1 + producing step}
+    float *part_ctx, *part_sum, *melf;
     float *mel_out, *attn_out;
     int *n_iter;
     long long *prof;                               // debug (WRNN_TACO_PROF): [2 CTAs][32] clocks per site, summed over steps
@@ -80,6 +81,31 @@ __device__ __forceinline__ void stage_vec(float *dst, const float *src, int n, i
     for (int i = tid; i < (n >> 2); i += TC_THREADS) reinterpret_cast<float4 *>(dst)[i] = __ldcg(reinterpret_cast<const float4 *>(src) + i);
 }
 
+__device__ __forceinline__ uint2 ld_word(const uint2 *p) {
+    uint2 v;
+    asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_word(uint2 *p, float value, unsigned tag) {
+    asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(__float_as_uint(value)), "r"(tag) : "memory");
+}
+// the value of a tagged word once its producer has stored it; a watchdog turns a lost hand-over into the abort flag
+__device__ __forceinline__ float wait_word(const uint2 *p, unsigned tag, int *abort_flag) {
+    uint2 w = ld_word(p);
+    if (w.y != tag) {
+        const long long t0 = clock64();
+        unsigned spins = 0;
+        do {
+            w = ld_word(p);
+            if ((++spins & 255u) == 0u && (clock64() - t0 > 4000000000ll || ld_volatile_s32(abort_flag))) {       // ~2 s
+                atomicExch(abort_flag, 1);
+                break;
+            }
+        } while (w.y != tag);
+    }
+    return __uint_as_float(w.x);
+}
+
 __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoParams P) {
     extern __shared__ __align__(16) float smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, cta = blockIdx.x;
@@ -98,7 +124,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
     float *encp_s = smem + P.off_E, *enc_s = encp_s + (size_t)P.PP * D, *ploc = enc_s + (size_t)P.PP * D;
     float *cw = ploc + (size_t)P.PP * D;                 // [32][2][31] padded to 2048
     float *loc = cw + 2048;                              // [2][PP + 30]
-    float *conv = loc + 2 * (P.PP + 2 * TC_HALO + 2);    // [32][PP]
+    const int LS = (P.PP + 2 * TC_HALO + 3) & ~3;        // row stride of loc: what follows stays 16-byte aligned
+    float *conv = loc + 2 * LS;                          // [PP][32]
     float *sv = conv + TC_FILT * P.PP;                   // [PP] sigmoid(u)
     float *cumv = sv + P.PP;                             // [PP] cumulative attention
     float *red = cumv + P.PP;                            // [PP][8]
@@ -146,23 +173,26 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
         prof_last = c__;                              \
     }
 
-    // staging: every vector is at most 1024 floats, so a thread holds at most one float4 of each; the loads of all the
-    // vectors of a stage are issued before the first is stored (one L2 round trip per stage, not one per vector)
-    const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
-    auto ld4 = [&](const float *src, int n) { return tid < (n >> 2) ? __ldcg(reinterpret_cast<const float4 *>(src) + tid) : z4; };
-    auto st4 = [&](float *dst, int n, const float4 &v) { if (tid < (n >> 2)) reinterpret_cast<float4 *>(dst)[tid] = v; };
+    // Hand-over between stages: every exchanged value travels as an 8-byte word {value, tag} written with one store;
+    // tag = 1 + the decoder step that produced it.  A consumer thread polls the words it stages itself, so a stage
+    // starts one L2 round trip after its last producer stored: no fence, no counter, no second trip for the data.
+    // One full grid barrier per step remains (E -> F: the partial contexts are too many words to poll); it is also what
+    // makes single buffers safe (every buffer is rewritten only after a barrier that all of its readers have passed).
+    auto fetch = [&](const uint2 *src, int n, unsigned tag, float *dst) {
+        for (int i = tid; i < n; i += TC_THREADS) dst[i] = wait_word(src + i, tag, P.gs.abort_flag);
+    };
     // activation of LSTM gate row w = unit * 4 + gate, applied by the warp that formed the row (gates i, f, g, o)
     auto lstm_act = [&](int w, float x) { return (w & 3) == 2 ? tanhf(x) : sigmoidf_acc(x); };
+    float *vec2 = misc + ((32 + 2 * P.upl + 160 + D + 3) & ~3);      // [H] second staging vector (the recurrent products formed ahead)
+    float *hh1s = vec2 + H, *hh2s = hh1s + 4 * P.upl;      // W_hh1 . h1 and W_hh2 . h2 of the owned gate rows
 
     for (int it = 0;; it++) {
         const int cur = it & 1, nxt = cur ^ 1;
+        const unsigned tag_prev = (unsigned)it, tag_now = (unsigned)it + 1u;
         // ---- A: mel frames of step it-1, prenet.fc1 of step it (x3 = 0 before the first step: fc1(go frame) = relu(b));
         //         position owners finish the location features of this step (L . conv + b; the conv was formed in G)
         if (prof_on) prof_last = clock64();
-        {
-            const float4 v = ld4(P.x3, H);
-            st4(vec, H, v);
-        }
+        fetch(P.x3, H, tag_prev, vec);
         __syncthreads();
         TMARK(0);
         for (int j = warp; j < na; j += TC_WARPS) {
@@ -176,57 +206,52 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
                         P.melf[row] = d;
                     }
                 } else {
-                    P.p1[row - nmel] = fmaxf(d + bA[j], 0.f);
+                    st_word(P.p1 + (row - nmel), fmaxf(d + bA[j], 0.f), tag_now);
                 }
             }
         }
         if (nl > 0 && it > 0) {
             for (int p = half; p < nl; p += 2) {
                 float acc = lb;
+                const float4 *c4 = reinterpret_cast<const float4 *>(conv + p * TC_FILT);
 #pragma unroll
-                for (int f = 0; f < TC_FILT; f++) acc = fmaf(lw[f], conv[f * P.PP + p], acc);
+                for (int f4 = 0; f4 < TC_FILT / 4; f4++) {
+                    const float4 c = c4[f4];
+                    acc = fmaf(lw[4 * f4 + 0], c.x, acc);
+                    acc = fmaf(lw[4 * f4 + 1], c.y, acc);
+                    acc = fmaf(lw[4 * f4 + 2], c.z, acc);
+                    acc = fmaf(lw[4 * f4 + 3], c.w, acc);
+                }
                 ploc[(size_t)p * D + a] = acc;
             }
         }
-        TMARK(1);
-        grid_barrier(P.gs, gen);
-        TMARK(2);
         n_done = it;
         if (it == P.max_iter) break;
-        // ---- B: stop rule on the frames of step it-1 (:455: all below the threshold and t > 10), prenet.fc2
-        {
-            const bool check = it > 0 && (it - 1) * r > 10;
-            float mv[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};     // nmel <= 128 * 20 = 5 threads' worth at most
-            if (check) {
-#pragma unroll
-                for (int q = 0; q < 4; q++)
-                    if (tid + q * TC_THREADS < nmel) mv[q] = __ldcg(P.melf + tid + q * TC_THREADS);
-            }
-            const float4 v = ld4(P.p1, P.P1);
-            st4(vec, P.P1, v);
-            int ok = check ? 1 : 0;
-#pragma unroll
-            for (int q = 0; q < 4; q++) ok &= (mv[q] < P.thr) ? 1 : 0;
-            for (int i = tid + 4 * TC_THREADS; check && i < nmel; i += TC_THREADS) ok &= (__ldcg(P.melf + i) < P.thr) ? 1 : 0;
-            if (__syncthreads_and(ok)) break;
-        }
-        TMARK(3);
+        __syncthreads();
+        TMARK(1);
+        // ---- B: prenet.fc2; ahead of its use in G: W_hh2 . h2
+        fetch(P.h2 + (size_t)cur * H, nu > 0 ? H : 0, tag_prev, vec2);
+        fetch(P.p1, nb > 0 ? P.P1 : 0, tag_now, vec);
+        __syncthreads();
+        TMARK(2);
         for (int j = warp; j < nb; j += TC_WARPS) {
             const float d = warp_dot(WB + (size_t)j * P.P1, vec, P.P1 >> 2, lane);
-            if (lane == 0) P.p2[b0 + j] = fmaxf(d + bB[j], 0.f);
+            if (lane == 0) st_word(P.p2 + b0 + j, fmaxf(d + bB[j], 0.f), tag_now);
         }
-        TMARK(4);
-        grid_barrier(P.gs, gen);
-        TMARK(5);
-        // ---- C: attention GRU cell
-        {
-            const float4 v1 = ld4(P.p2, P.P2), v2 = ld4(P.ha + (size_t)cur * D, D);
-            if (tid < D) vec[tid] = ctx[tid];
-            st4(vec + D, P.P2, v1);
-            st4(vec + D + P.P2, D, v2);
+        for (int w = warp; w < 4 * nu; w += TC_WARPS) {
+            const float d = warp_dot(WG + (size_t)w * 2 * H + H, vec2, H >> 2, lane);
+            if (lane == 0) hh2s[w] = d;
         }
         __syncthreads();
-        TMARK(6);
+        TMARK(3);
+        // ---- C: attention GRU cell
+        if (ng > 0) {
+            if (tid < D) vec[tid] = ctx[tid];
+            fetch(P.ha + (size_t)cur * D, D, tag_prev, vec + D + P.P2);
+            fetch(P.p2, P.P2, tag_now, vec + D);
+        }
+        __syncthreads();
+        TMARK(4);
         for (int w = warp; w < 4 * ng; w += TC_WARPS) {
             const int j = w >> 2, q = w & 3;
             const float *row = WC + (size_t)j * (2 * KC + (D + P.P2) + D);
@@ -240,31 +265,28 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
         if (tid < ng) {
             const float rr = gsum[tid * 4 + 0], zz = gsum[tid * 4 + 1];
             const float nn = tanhf(gsum[tid * 4 + 2] + rr * gsum[tid * 4 + 3]);
-            P.ha[(size_t)nxt * D + g0 + tid] = (1.f - zz) * nn + zz * vec[D + P.P2 + g0 + tid];
-        }
-        TMARK(7);
-        grid_barrier(P.gs, gen);
-        TMARK(8);
-        // ---- D: processed query
-        {
-            const float4 v = ld4(P.ha + (size_t)nxt * D, D);
-            st4(vec, D, v);
+            st_word(P.ha + (size_t)nxt * D + g0 + tid, (1.f - zz) * nn + zz * vec[D + P.P2 + g0 + tid], tag_now);
         }
         __syncthreads();
-        TMARK(9);
+        TMARK(5);
+        // ---- D: processed query; ahead of its use in F: W_hh1 . h1
+        fetch(P.h1 + (size_t)cur * H, nu > 0 ? H : 0, tag_prev, vec2);
+        fetch(P.ha + (size_t)nxt * D, nd > 0 ? D : 0, tag_now, vec);
+        __syncthreads();
+        TMARK(6);
         for (int j = warp; j < nd; j += TC_WARPS) {
             const float d = warp_dot(WD + (size_t)j * D, vec, D >> 2, lane);
-            if (lane == 0) P.pq[d0 + j] = d + bD[j];
+            if (lane == 0) st_word(P.pq + d0 + j, d + bD[j], tag_now);
         }
-        TMARK(10);
-        grid_barrier(P.gs, gen);
-        TMARK(11);
+        for (int w = warp; w < 4 * nu; w += TC_WARPS) {
+            const float d = warp_dot(WF + (size_t)w * KF + 2 * D, vec2, H >> 2, lane);
+            if (lane == 0) hh1s[w] = d;
+        }
+        __syncthreads();
+        TMARK(7);
         // ---- E: energies, sigmoid and the partial context of the owned positions
         if (nl > 0) {
-            {
-                const float4 v = ld4(P.pq, D);
-                st4(vec, D, v);
-            }
+            fetch(P.pq, D, tag_now, vec);
             __syncthreads();
             for (int p = half; p < nl; p += 2) {
                 float v = va * tanhf(vec[a] + encp_s[(size_t)p * D + a] + ploc[(size_t)p * D + a]);
@@ -289,29 +311,43 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
                 P.part_sum[pi] = s;
             }
         }
-        TMARK(12);
+        TMARK(8);
         grid_barrier(P.gs, gen);
-        TMARK(13);
-        // ---- F: context = sum of partials / sum of sums; rnn_input + LSTM 1; owners normalise their scores
+        TMARK(9);
+        // ---- F: the stop rule on the frames of step it-1 (:455: all below the threshold and t > 10; they were complete
+        //         before the barrier); context = sum of partials / sum of sums; rnn_input + LSTM 1; owners normalise
         {
-            const float4 v2 = ld4(P.ha + (size_t)nxt * D, D), v3 = ld4(P.h1 + (size_t)cur * H, H);
-            // partial sums: thread p loads one; partial contexts: (d, half) sums every second partial, eight loads in flight
+            const bool check = it > 0 && (it - 1) * r > 10;
+            float mv[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+            if (check) {
+#pragma unroll
+                for (int q = 0; q < 4; q++)
+                    if (tid + q * TC_THREADS < nmel) mv[q] = __ldcg(P.melf + tid + q * TC_THREADS);
+            }
+            const uint2 wha = tid < D ? __ldcg(P.ha + (size_t)nxt * D + tid) : make_uint2(0u, 0u);     // complete before the barrier
             const float ps = tid < P.PC ? __ldcg(P.part_sum + tid) : 0.f;
             float acc = 0.f;
-            for (int p0 = half; p0 < P.PC; p0 += 16) {
-                float t8[8];
+            for (int p0 = half; p0 < P.PC; p0 += 20) {          // (d, half) sums every second partial, ten loads in flight
+                float t10[10];
 #pragma unroll
-                for (int q = 0; q < 8; q++) t8[q] = (p0 + 2 * q < P.PC) ? __ldcg(P.part_ctx + (size_t)(p0 + 2 * q) * D + a) : 0.f;
+                for (int q = 0; q < 10; q++) t10[q] = (p0 + 2 * q < P.PC) ? __ldcg(P.part_ctx + (size_t)(p0 + 2 * q) * D + a) : 0.f;
 #pragma unroll
-                for (int q = 0; q < 8; q++) acc += t8[q];
+                for (int q = 0; q < 10; q++) acc += t10[q];
             }
-            st4(vec + D, D, v2);
-            st4(vec + 2 * D, H, v3);
-            if (tid < P.PC) psum_s[tid] = ps;
+            if (tid < D) vec[D + tid] = __uint_as_float(wha.x);
+            // sum of the partial sums: per warp by shuffles, then across the warps in order
+            float wsum = ps;
+#pragma unroll
+            for (int o = 16; o >= 1; o >>= 1) wsum += __shfl_xor_sync(0xffffffffu, wsum, o);
+            if (lane == 0) psum_s[warp] = wsum;
             if (half) chalf[a] = acc;
-            __syncthreads();
+            int ok = check ? 1 : 0;
+#pragma unroll
+            for (int q = 0; q < 4; q++) ok &= (mv[q] < P.thr) ? 1 : 0;
+            for (int i = tid + 4 * TC_THREADS; check && i < nmel; i += TC_THREADS) ok &= (__ldcg(P.melf + i) < P.thr) ? 1 : 0;
+            if (__syncthreads_and(ok)) break;
             float total = 0.f;
-            for (int p = 0; p < P.PC; p++) total += psum_s[p];
+            for (int w = 0; w < (P.PC + 31) / 32; w++) total += psum_s[w];
             if (!half) {
                 const float c = (acc + chalf[a]) / total;
                 ctx[a] = c;
@@ -321,17 +357,17 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
                 const float att = sv[tid] / total;
                 const float cu = cumv[tid] + att;
                 cumv[tid] = cu;
-                P.att_g[l0 + tid] = att;
-                P.cum_g[l0 + tid] = cu;
+                st_word(P.att_g + l0 + tid, att, tag_now);
+                st_word(P.cum_g + l0 + tid, cu, tag_now);
                 P.attn_out[(size_t)it * L + l0 + tid] = att;
             }
         }
         __syncthreads();
-        TMARK(14);
+        TMARK(10);
         for (int w = warp; w < 5 * nu; w += TC_WARPS) {
             if (w < 4 * nu) {                                                                               // w = unit * 4 + gate
-                const float d = warp_dot(WF + (size_t)w * KF, vec, KF >> 2, lane);
-                if (lane == 0) gsum[w] = lstm_act(w, d + bF[(w >> 2) * 5 + (w & 3)]);
+                const float d = warp_dot(WF + (size_t)w * KF, vec, (2 * D) >> 2, lane);
+                if (lane == 0) gsum[w] = lstm_act(w, d + hh1s[w] + bF[(w >> 2) * 5 + (w & 3)]);
             } else {
                 const float d = warp_dot(WF + (size_t)4 * P.upl * KF + (size_t)(w - 4 * nu) * 2 * D, vec, (2 * D) >> 2, lane);
                 if (lane == 0) gsum[w] = d + bF[(w - 4 * nu) * 5 + 4];
@@ -341,67 +377,48 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
         if (tid < nu) {
             const float c = gsum[tid * 4 + 1] * c1[tid] + gsum[tid * 4 + 0] * gsum[tid * 4 + 2], h = gsum[tid * 4 + 3] * tanhf(c);
             c1[tid] = c;
-            P.h1[(size_t)nxt * H + u0 + tid] = h;
-            P.x2[u0 + tid] = gsum[4 * nu + tid] + h;
+            st_word(P.x2 + u0 + tid, gsum[4 * nu + tid] + h, tag_now);
+            st_word(P.h1 + (size_t)nxt * H + u0 + tid, h, tag_now);
         }
-        TMARK(15);
-        grid_barrier(P.gs, gen);
-        TMARK(16);
+        __syncthreads();
+        TMARK(11);
         // ---- G: LSTM 2 on x + h1; position owners convolve [cumulative | attention] for the next step
-        {
-            const float4 v1 = ld4(P.x2, H), v2 = ld4(P.h2 + (size_t)cur * H, H);
-            float hl[2] = {0.f, 0.f};
+        fetch(P.x2, nu > 0 ? H : 0, tag_now, vec);
+        if (nl > 0) {
             const int span = nl + 2 * TC_HALO;
-            if (nl > 0 && tid < 2 * span) {
-                const int c = tid / span, k = tid - c * span, l = l0 - TC_HALO + k;
-                hl[0] = (l >= 0 && l < L) ? __ldcg((c == 0 ? P.cum_g : P.att_g) + l) : 0.f;
-            }
-            if (nl > 0 && tid + TC_THREADS < 2 * span) {
-                const int i = tid + TC_THREADS, c = i / span, k = i - c * span, l = l0 - TC_HALO + k;
-                hl[1] = (l >= 0 && l < L) ? __ldcg((c == 0 ? P.cum_g : P.att_g) + l) : 0.f;
-            }
-            st4(vec, H, v1);
-            st4(vec + H, H, v2);
-            if (nl > 0) {
-#pragma unroll
-                for (int q = 0; q < 2; q++) {
-                    const int i = tid + q * TC_THREADS;
-                    if (i < 2 * span) {
-                        const int c = i / span, k = i - c * span;
-                        loc[c * (P.PP + 2 * TC_HALO + 2) + k] = hl[q];
-                    }
-                }
+            for (int i = tid; i < 2 * span; i += TC_THREADS) {
+                const int c = i / span, k = i - c * span, l = l0 - TC_HALO + k;
+                loc[c * LS + k] = (l >= 0 && l < L) ? wait_word((c == 0 ? P.cum_g : P.att_g) + l, tag_now, P.gs.abort_flag) : 0.f;
             }
         }
         __syncthreads();
-        TMARK(17);
+        TMARK(12);
         for (int w = warp; w < 4 * nu; w += TC_WARPS) {
-            const float d = warp_dot(WG + (size_t)w * 2 * H, vec, (2 * H) >> 2, lane);
-            if (lane == 0) gsum[w] = lstm_act(w, d + bG[w]);
+            const float d = warp_dot(WG + (size_t)w * 2 * H, vec, H >> 2, lane);
+            if (lane == 0) gsum[w] = lstm_act(w, d + hh2s[w] + bG[w]);
         }
         if (nl > 0) {
             for (int i = tid; i < TC_FILT * nl; i += TC_THREADS) {
-                const int f = i / nl, p = i - f * nl;
+                const int p = i / TC_FILT, f = i - p * TC_FILT;
                 float acc = 0.f;
 #pragma unroll
                 for (int c = 0; c < 2; c++) {
-                    const float *w = cw + (f * 2 + c) * TC_KS, *x = loc + c * (P.PP + 2 * TC_HALO + 2) + p;
+                    const float *w = cw + (f * 2 + c) * TC_KS, *x = loc + c * LS + p;
 #pragma unroll
                     for (int k = 0; k < TC_KS; k++) acc = fmaf(w[k], x[k], acc);
                 }
-                conv[f * P.PP + p] = acc;
+                conv[p * TC_FILT + f] = acc;
             }
         }
         __syncthreads();
         if (tid < nu) {
             const float c = gsum[tid * 4 + 1] * c2[tid] + gsum[tid * 4 + 0] * gsum[tid * 4 + 2], h = gsum[tid * 4 + 3] * tanhf(c);
             c2[tid] = c;
-            P.h2[(size_t)nxt * H + u0 + tid] = h;
-            P.x3[u0 + tid] = vec[u0 + tid] + h;
+            st_word(P.x3 + u0 + tid, vec[u0 + tid] + h, tag_now);
+            st_word(P.h2 + (size_t)nxt * H + u0 + tid, h, tag_now);
         }
-        TMARK(18);
-        grid_barrier(P.gs, gen);
-        TMARK(19);
+        __syncthreads();
+        TMARK(13);
     }
     if (prof_on)
         for (int i = 0; i < 32; i++) P.prof[(cta == 0 ? 0 : 32) + i] = prof_acc[i];
@@ -708,12 +725,12 @@ int wrnn_taco_decode(wrnn_taco_handle *h, const float *enc_seq, int32_t L, int32
     const int owners = disjoint ? G - n_lstm : G;
     P.PP = (L + owners - 1) / owners;
     P.PC = (L + P.PP - 1) / P.PP;
-    const int e_floats = 3 * P.PP * D + 2048 + 2 * (P.PP + 2 * TC_HALO + 2) + TC_FILT * P.PP + 2 * P.PP + 8 * P.PP + 8;
+    const int e_floats = 3 * P.PP * D + 2048 + 2 * ((P.PP + 2 * TC_HALO + 3) & ~3) + TC_FILT * P.PP + 2 * P.PP + 8 * P.PP + 8;
     P.off_E = disjoint ? P.off_F : P.img_floats;
     P.sm_vec = std::max(P.img_floats, (P.off_E + e_floats + 3) & ~3);
     P.sm_ctx = P.sm_vec + std::max(2 * D + H, 2 * H);
     P.sm_misc = P.sm_ctx + D;
-    const size_t smem_bytes = ((size_t)P.sm_misc + 32 + 2 * P.upl + 160 + D + 8) * sizeof(float);
+    const size_t smem_bytes = ((size_t)P.sm_misc + 32 + 2 * P.upl + 160 + D + H + 8 * P.upl + 12) * sizeof(float);
     if (smem_bytes > h->smem_optin) {
         char b[256];
         snprintf(b, sizeof b, "decoder loop needs %zu bytes of shared memory per SM (r = %d, %d characters), the device allows %zu",
@@ -723,9 +740,9 @@ int wrnn_taco_decode(wrnn_taco_handle *h, const float *enc_seq, int32_t L, int32
     // workspace: sync[128 B] | state vectors | n_iter | enc, enc_proj | mel_out [M][cap] | attn_out [max_iter][L]
     size_t off = 128;
     auto take = [&](size_t floats) { const size_t o = off; off += ((floats * 4 + 127) & ~(size_t)127); return o; };
-    const size_t o_p1 = take(P.P1), o_p2 = take(P.P2), o_ha = take(2 * D), o_pq = take(D), o_pc = take((size_t)owners * D),
-                 o_ps = take(owners), o_x2 = take(H), o_h1 = take(2 * H), o_h2 = take(2 * H), o_x3 = take(H),
-                 o_melf = take((size_t)M * TC_MAXR), o_att = take(L), o_cum = take(L), o_n = take(1);
+    const size_t o_p1 = take(2 * P.P1), o_p2 = take(2 * P.P2), o_ha = take(4 * D), o_pq = take(2 * D), o_pc = take((size_t)owners * D),
+                 o_ps = take(owners), o_x2 = take(2 * H), o_h1 = take(4 * H), o_h2 = take(4 * H), o_x3 = take(2 * H),
+                 o_melf = take((size_t)M * TC_MAXR), o_att = take(2 * (size_t)L), o_cum = take(2 * (size_t)L), o_n = take(1);
     const size_t state_end = off;
     const size_t o_enc = take((size_t)L * D), o_encp = take((size_t)L * D), o_mel = take((size_t)M * P.cap),
                  o_attn = take((size_t)P.max_iter * L);
@@ -740,8 +757,9 @@ int wrnn_taco_decode(wrnn_taco_handle *h, const float *enc_seq, int32_t L, int32
     TC_CUDA(h, cudaMemsetAsync(ws, 0, state_end, st));
     TC_CUDA(h, cudaMemcpyAsync(ws + o_enc, enc_seq, (size_t)L * D * 4, cudaMemcpyHostToDevice, st));
     P.image = h->image; P.common = h->common; P.enc = F(o_enc); P.encp = F(o_encp);
-    P.p1 = F(o_p1); P.p2 = F(o_p2); P.ha = F(o_ha); P.pq = F(o_pq); P.part_ctx = F(o_pc); P.part_sum = F(o_ps);
-    P.x2 = F(o_x2); P.h1 = F(o_h1); P.h2 = F(o_h2); P.x3 = F(o_x3); P.melf = F(o_melf); P.att_g = F(o_att); P.cum_g = F(o_cum);
+    auto U = [&](size_t o) { return (uint2 *)(ws + o); };
+    P.p1 = U(o_p1); P.p2 = U(o_p2); P.ha = U(o_ha); P.pq = U(o_pq); P.part_ctx = F(o_pc); P.part_sum = F(o_ps);
+    P.x2 = U(o_x2); P.h1 = U(o_h1); P.h2 = U(o_h2); P.x3 = U(o_x3); P.melf = F(o_melf); P.att_g = U(o_att); P.cum_g = U(o_cum);
     P.mel_out = F(o_mel); P.attn_out = F(o_attn); P.n_iter = (int *)(ws + o_n);
     P.gs.counter = (unsigned long long *)ws;
     P.gs.abort_flag = (int *)(ws + 64);
@@ -769,11 +787,11 @@ int wrnn_taco_decode(wrnn_taco_handle *h, const float *enc_seq, int32_t L, int32
         long long pr[64];
         cudaMemcpy(pr, d_prof, sizeof pr, cudaMemcpyDeviceToHost);
         cudaFree(d_prof);
-        static const char *site[20] = {"A stage", "A dots", "A barrier", "B stage+stop", "B dots+loc", "B barrier", "C stage", "C dots+gates", "C barrier",
-                                       "D stage", "D dots", "D barrier", "E", "E barrier", "F stage+ctx", "F dots+gates", "F barrier", "G stage", "G dots+gates", "G barrier"};
+        static const char *site[20] = {"A wait x3", "A dots", "B wait p1", "B dots+hh2", "C wait p2", "C dots+gates", "D wait h_attn", "D dots+hh1", "E",
+                                       "barrier", "F stop+ctx", "F dots+gates", "G wait x2", "G dots+gates", "", "", "", "", "", ""};
         const int nn = std::max(1, head[1]);
         fprintf(stderr, "taco prof (clk per decoder step; CTA 0 | first position owner)\n");
-        for (int i = 0; i < 20; i++) fprintf(stderr, "  %-14s %7.0f | %7.0f\n", site[i], (double)pr[i] / nn, (double)pr[32 + i] / nn);
+        for (int i = 0; i < 14; i++) fprintf(stderr, "  %-14s %7.0f | %7.0f\n", site[i], (double)pr[i] / nn, (double)pr[32 + i] / nn);
     }
     const int n = head[1];
     if (n < 1 || n > P.max_iter) return taco_fail(h, WRNN_ERR_CUDA, "Tacotron decoder loop kernel returned an impossible step count");
