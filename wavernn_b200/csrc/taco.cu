@@ -37,6 +37,7 @@ struct TacoParams {
     int D, H, M, P1, P2, r, L, max_iter, cap;      // cap = max_iter * r columns of mel_out
     float thr;
     int NA, rpa, rpb, upc, rpd, upl;               // rows (A, B, D) / units (C: GRU, F/G: LSTM) per CTA
+    int GA;                                        // CTAs that share the A rows (the position owners are kept out of it)
     int PP, pc0, PC;                               // positions per owner CTA, first owner CTA, owners in use
     int img_floats;
     int off_A, off_bA, off_B, off_bB, off_C, off_bC, off_D, off_bD, off_F, off_bF, off_G, off_bG, off_E;
@@ -83,11 +84,11 @@ __device__ __forceinline__ void stage_vec(float *dst, const float *src, int n, i
 
 __device__ __forceinline__ uint2 ld_word(const uint2 *p) {
     uint2 v;
-    asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p) : "memory");
+    asm volatile("ld.relaxed.gpu.global.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p) : "memory");
     return v;
 }
 __device__ __forceinline__ void st_word(uint2 *p, float value, unsigned tag) {
-    asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(__float_as_uint(value)), "r"(tag) : "memory");
+    asm volatile("st.relaxed.gpu.global.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(__float_as_uint(value)), "r"(tag) : "memory");
 }
 // the value of a tagged word once its producer has stored it; a watchdog turns a lost hand-over into the abort flag
 __device__ __forceinline__ float wait_word(const uint2 *p, unsigned tag, int *abort_flag) {
@@ -104,6 +105,28 @@ __device__ __forceinline__ float wait_word(const uint2 *p, unsigned tag, int *ab
         } while (w.y != tag);
     }
     return __uint_as_float(w.x);
+}
+
+// the grid barrier in two halves: a CTA arrives as soon as it has nothing more to publish and waits after the work that
+// needs nothing from the others
+__device__ __forceinline__ void grid_arrive(const GridSync &gs, unsigned long long &gen) {
+    __syncthreads();
+    gen++;
+    if (threadIdx.x == 0) red_release_add_u64(gs.counter, 1ull);
+}
+__device__ __forceinline__ void grid_wait(const GridSync &gs, unsigned long long gen) {
+    if (threadIdx.x == 0) {
+        const unsigned long long want = gen * gridDim.x;
+        const long long t0 = clock64();
+        unsigned spins = 0;
+        while (ld_acquire_u64(gs.counter) < want) {
+            if ((++spins & 63u) == 0u && (clock64() - t0 > 4000000000ll || ld_volatile_s32(gs.abort_flag))) {   // ~2 s
+                atomicExch(gs.abort_flag, 1);
+                break;
+            }
+        }
+    }
+    __syncthreads();
 }
 
 __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoParams P) {
@@ -152,7 +175,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
     const float *WA = img + P.off_A, *bA = img + P.off_bA, *WB = img + P.off_B, *bB = img + P.off_bB;
     const float *WC = img + P.off_C, *bC = img + P.off_bC, *WD = img + P.off_D, *bD = img + P.off_bD;
     const float *WF = img + P.off_F, *bF = img + P.off_bF, *WG = img + P.off_G, *bG = img + P.off_bG;
-    const int a0 = cta * P.rpa, na = max(0, min(P.rpa, P.NA - a0));
+    const int a0 = cta * P.rpa, na = cta < P.GA ? max(0, min(P.rpa, P.NA - a0)) : 0;
     const int b0 = cta * P.rpb, nb = max(0, min(P.rpb, P.P2 - b0));
     const int g0 = cta * P.upc, ng = max(0, min(P.upc, D - g0));
     const int d0 = cta * P.rpd, nd = max(0, min(P.rpd, D - d0));
@@ -183,8 +206,23 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
     };
     // activation of LSTM gate row w = unit * 4 + gate, applied by the warp that formed the row (gates i, f, g, o)
     auto lstm_act = [&](int w, float x) { return (w & 3) == 2 ? tanhf(x) : sigmoidf_acc(x); };
-    float *vec2 = misc + ((32 + 2 * P.upl + 160 + D + 3) & ~3);      // [H] second staging vector (the recurrent products formed ahead)
+    float *vec2 = misc + ((32 + 2 * P.upl + 160 + D + 3) & ~3);      // [H] second staging vector (the products formed ahead)
     float *hh1s = vec2 + H, *hh2s = hh1s + 4 * P.upl;      // W_hh1 . h1 and W_hh2 . h2 of the owned gate rows
+    float *fha = hh2s + 4 * P.upl;                         // [5 upl] h_attn columns of the LSTM 1 gate rows and of the x rows
+    float *ghh = fha + 5 * P.upl;                          // [4 upc] W_hh . h_attn of the GRU rows (r, z, -, n) for the NEXT step
+    float *hown = ghh + 4 * P.upc;                         // [upc] h_attn of the owned GRU units
+    for (int i = tid; i < 5 * P.upc; i += TC_THREADS) ghh[i] = 0.f;
+    // up to three vectors of <= 512 words staged in ONE L2 round trip: first looks issued together, stragglers polled
+    auto fetch3 = [&](const uint2 *s1, int n1, unsigned t1, float *d1, const uint2 *s2, int n2, unsigned t2, float *d2,
+                      const uint2 *s3, int n3, unsigned t3, float *d3) {
+        uint2 w1 = make_uint2(0u, t1), w2 = make_uint2(0u, t2), w3 = make_uint2(0u, t3);
+        if (tid < n1) w1 = ld_word(s1 + tid);
+        if (tid < n2) w2 = ld_word(s2 + tid);
+        if (tid < n3) w3 = ld_word(s3 + tid);
+        if (tid < n1) d1[tid] = w1.y == t1 ? __uint_as_float(w1.x) : wait_word(s1 + tid, t1, P.gs.abort_flag);
+        if (tid < n2) d2[tid] = w2.y == t2 ? __uint_as_float(w2.x) : wait_word(s2 + tid, t2, P.gs.abort_flag);
+        if (tid < n3) d3[tid] = w3.y == t3 ? __uint_as_float(w3.x) : wait_word(s3 + tid, t3, P.gs.abort_flag);
+    };
 
     for (int it = 0;; it++) {
         const int cur = it & 1, nxt = cur ^ 1;
@@ -229,8 +267,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
         if (it == P.max_iter) break;
         __syncthreads();
         TMARK(1);
-        // ---- B: prenet.fc2; ahead of its use in G: W_hh2 . h2
-        fetch(P.h2 + (size_t)cur * H, nu > 0 ? H : 0, tag_prev, vec2);
+        // ---- B: prenet.fc2
         fetch(P.p1, nb > 0 ? P.P1 : 0, tag_now, vec);
         __syncthreads();
         TMARK(2);
@@ -238,39 +275,36 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
             const float d = warp_dot(WB + (size_t)j * P.P1, vec, P.P1 >> 2, lane);
             if (lane == 0) st_word(P.p2 + b0 + j, fmaxf(d + bB[j], 0.f), tag_now);
         }
-        for (int w = warp; w < 4 * nu; w += TC_WARPS) {
-            const float d = warp_dot(WG + (size_t)w * 2 * H + H, vec2, H >> 2, lane);
-            if (lane == 0) hh2s[w] = d;
-        }
         __syncthreads();
         TMARK(3);
         // ---- C: attention GRU cell
         if (ng > 0) {
             if (tid < D) vec[tid] = ctx[tid];
-            fetch(P.ha + (size_t)cur * D, D, tag_prev, vec + D + P.P2);
             fetch(P.p2, P.P2, tag_now, vec + D);
         }
         __syncthreads();
         TMARK(4);
-        for (int w = warp; w < 4 * ng; w += TC_WARPS) {
+        for (int w = warp; w < 4 * ng; w += TC_WARPS) {           // the hidden-state columns were formed ahead (ghh)
             const int j = w >> 2, q = w & 3;
             const float *row = WC + (size_t)j * (2 * KC + (D + P.P2) + D);
-            float d;
-            if (q < 2) d = warp_dot(row + (size_t)q * KC, vec, KC >> 2, lane);
-            else if (q == 2) d = warp_dot(row + 2 * KC, vec, (D + P.P2) >> 2, lane);
-            else d = warp_dot(row + 2 * KC + D + P.P2, vec + D + P.P2, D >> 2, lane);
-            if (lane == 0) gsum[w] = q < 2 ? sigmoidf_acc(d + bC[w]) : d + bC[w];
+            if (q == 3) {
+                if (lane == 0) gsum[w] = ghh[w] + bC[w];
+            } else {
+                const float d = warp_dot(row + (size_t)q * KC, vec, (D + P.P2) >> 2, lane);
+                if (lane == 0) gsum[w] = q < 2 ? sigmoidf_acc(d + ghh[w] + bC[w]) : d + bC[w];
+            }
         }
         __syncthreads();
         if (tid < ng) {
             const float rr = gsum[tid * 4 + 0], zz = gsum[tid * 4 + 1];
             const float nn = tanhf(gsum[tid * 4 + 2] + rr * gsum[tid * 4 + 3]);
-            st_word(P.ha + (size_t)nxt * D + g0 + tid, (1.f - zz) * nn + zz * vec[D + P.P2 + g0 + tid], tag_now);
+            const float hn = (1.f - zz) * nn + zz * hown[tid];
+            hown[tid] = hn;
+            st_word(P.ha + (size_t)nxt * D + g0 + tid, hn, tag_now);
         }
         __syncthreads();
         TMARK(5);
-        // ---- D: processed query; ahead of its use in F: W_hh1 . h1
-        fetch(P.h1 + (size_t)cur * H, nu > 0 ? H : 0, tag_prev, vec2);
+        // ---- D: processed query
         fetch(P.ha + (size_t)nxt * D, nd > 0 ? D : 0, tag_now, vec);
         __syncthreads();
         TMARK(6);
@@ -278,12 +312,45 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
             const float d = warp_dot(WD + (size_t)j * D, vec, D >> 2, lane);
             if (lane == 0) st_word(P.pq + d0 + j, d + bD[j], tag_now);
         }
-        for (int w = warp; w < 4 * nu; w += TC_WARPS) {
-            const float d = warp_dot(WF + (size_t)w * KF + 2 * D, vec2, H >> 2, lane);
-            if (lane == 0) hh1s[w] = d;
-        }
         __syncthreads();
         TMARK(7);
+        // ---- in the shadow of E (position owners only) and of the barrier: every product whose input is known by now.
+        //      W_hh1 . h1 and W_hh2 . h2 (states of the step before), the h_attn columns of LSTM 1's composed gate rows
+        //      and of the x rows, and W_hh . h_attn of the attention GRU for the NEXT step
+        auto shadow = [&]() {
+            if (nu == 0 && ng == 0) return;
+            fetch3(P.h1 + (size_t)cur * H, nu > 0 ? H : 0, tag_prev, vec, P.h2 + (size_t)cur * H, nu > 0 ? H : 0, tag_prev, vec + H,
+                   P.ha + (size_t)nxt * D, D, tag_now, vec2);
+            __syncthreads();
+            const int j1 = 4 * nu, j2 = 8 * nu, j3 = 12 * nu, j4 = 13 * nu, j5 = j4 + 4 * ng;
+            for (int w = warp; w < j5; w += TC_WARPS) {
+                if (w < j1) {
+                    const float d = warp_dot(WF + (size_t)w * KF + 2 * D, vec, H >> 2, lane);
+                    if (lane == 0) hh1s[w] = d;
+                } else if (w < j2) {
+                    const float d = warp_dot(WG + (size_t)(w - j1) * 2 * H + H, vec + H, H >> 2, lane);
+                    if (lane == 0) hh2s[w - j1] = d;
+                } else if (w < j3) {
+                    const float d = warp_dot(WF + (size_t)(w - j2) * KF + D, vec2, D >> 2, lane);
+                    if (lane == 0) fha[w - j2] = d;
+                } else if (w < j4) {
+                    const float d = warp_dot(WF + (size_t)4 * P.upl * KF + (size_t)(w - j3) * 2 * D + D, vec2, D >> 2, lane);
+                    if (lane == 0) fha[4 * nu + (w - j3)] = d;
+                } else {
+                    const int g = w - j4, j = g >> 2, q = g & 3;
+                    if (q != 2) {
+                        const float *row = WC + (size_t)j * (2 * KC + (D + P.P2) + D);
+                        const float d = warp_dot(q < 2 ? row + (size_t)q * KC + D + P.P2 : row + 2 * KC + D + P.P2, vec2, D >> 2, lane);
+                        if (lane == 0) ghh[g] = d;
+                    }
+                }
+            }
+            __syncthreads();
+        };
+        if (nl == 0) {
+            grid_arrive(P.gs, gen);
+            shadow();
+        }
         // ---- E: energies, sigmoid and the partial context of the owned positions
         if (nl > 0) {
             fetch(P.pq, D, tag_now, vec);
@@ -311,8 +378,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
                 P.part_sum[pi] = s;
             }
         }
+        if (nl > 0) {
+            grid_arrive(P.gs, gen);
+            shadow();
+        }
         TMARK(8);
-        grid_barrier(P.gs, gen);
+        grid_wait(P.gs, gen);
         TMARK(9);
         // ---- F: the stop rule on the frames of step it-1 (:455: all below the threshold and t > 10; they were complete
         //         before the barrier); context = sum of partials / sum of sums; rnn_input + LSTM 1; owners normalise
@@ -324,7 +395,6 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
                 for (int q = 0; q < 4; q++)
                     if (tid + q * TC_THREADS < nmel) mv[q] = __ldcg(P.melf + tid + q * TC_THREADS);
             }
-            const uint2 wha = tid < D ? __ldcg(P.ha + (size_t)nxt * D + tid) : make_uint2(0u, 0u);     // complete before the barrier
             const float ps = tid < P.PC ? __ldcg(P.part_sum + tid) : 0.f;
             float acc = 0.f;
             for (int p0 = half; p0 < P.PC; p0 += 20) {          // (d, half) sums every second partial, ten loads in flight
@@ -334,7 +404,6 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
 #pragma unroll
                 for (int q = 0; q < 10; q++) acc += t10[q];
             }
-            if (tid < D) vec[D + tid] = __uint_as_float(wha.x);
             // sum of the partial sums: per warp by shuffles, then across the warps in order
             float wsum = ps;
 #pragma unroll
@@ -365,12 +434,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
         __syncthreads();
         TMARK(10);
         for (int w = warp; w < 5 * nu; w += TC_WARPS) {
-            if (w < 4 * nu) {                                                                               // w = unit * 4 + gate
-                const float d = warp_dot(WF + (size_t)w * KF, vec, (2 * D) >> 2, lane);
-                if (lane == 0) gsum[w] = lstm_act(w, d + hh1s[w] + bF[(w >> 2) * 5 + (w & 3)]);
+            if (w < 4 * nu) {                                                   // w = unit * 4 + gate; context columns only
+                const float d = warp_dot(WF + (size_t)w * KF, vec, D >> 2, lane);
+                if (lane == 0) gsum[w] = lstm_act(w, d + fha[w] + hh1s[w] + bF[(w >> 2) * 5 + (w & 3)]);
             } else {
-                const float d = warp_dot(WF + (size_t)4 * P.upl * KF + (size_t)(w - 4 * nu) * 2 * D, vec, (2 * D) >> 2, lane);
-                if (lane == 0) gsum[w] = d + bF[(w - 4 * nu) * 5 + 4];
+                const float d = warp_dot(WF + (size_t)4 * P.upl * KF + (size_t)(w - 4 * nu) * 2 * D, vec, D >> 2, lane);
+                if (lane == 0) gsum[w] = d + fha[w] + bF[(w - 4 * nu) * 5 + 4];
             }
         }
         __syncthreads();
@@ -508,11 +577,15 @@ static int taco_pack(wrnn_taco_handle *h, int r) {
     TacoParams &p = h->plan;
     p.D = D; p.H = H; p.M = M; p.P1 = P1; p.P2 = P2; p.r = r;
     p.NA = M * r + P1;
-    p.rpa = (p.NA + G - 1) / G;
     p.rpb = (P2 + G - 1) / G;
     p.upc = (D + G - 1) / G;
     p.rpd = (D + G - 1) / G;
     p.upl = (H + G - 1) / G;
+    {
+        const int n_lstm = (H + p.upl - 1) / p.upl;
+        p.GA = G - n_lstm >= 8 ? n_lstm : G;           // the same split as the position owners' in wrnn_taco_decode
+    }
+    p.rpa = (p.NA + p.GA - 1) / p.GA;
     const int KC = 2 * D + P2, KF = 2 * D + H, unitC = 2 * KC + (D + P2) + D;
     auto r4 = [](int x) { return (x + 3) & ~3; };
     int o = 0;
@@ -559,7 +632,7 @@ static int taco_pack(wrnn_taco_handle *h, int r) {
         float *im = img.data() + (size_t)c * p.img_floats;
         for (int j = 0; j < p.rpa; j++) {
             const int row = c * p.rpa + j;
-            if (row >= p.NA) break;
+            if (row >= p.NA || c >= p.GA) break;
             float *dst = im + p.off_A + (size_t)j * H;
             if (row < M * r) {
                 const int m = row / r, jj = row - m * r;
@@ -730,7 +803,7 @@ int wrnn_taco_decode(wrnn_taco_handle *h, const float *enc_seq, int32_t L, int32
     P.sm_vec = std::max(P.img_floats, (P.off_E + e_floats + 3) & ~3);
     P.sm_ctx = P.sm_vec + std::max(2 * D + H, 2 * H);
     P.sm_misc = P.sm_ctx + D;
-    const size_t smem_bytes = ((size_t)P.sm_misc + 32 + 2 * P.upl + 160 + D + H + 8 * P.upl + 12) * sizeof(float);
+    const size_t smem_bytes = ((size_t)P.sm_misc + 32 + 2 * P.upl + 160 + D + H + 13 * P.upl + 5 * P.upc + 12) * sizeof(float);
     if (smem_bytes > h->smem_optin) {
         char b[256];
         snprintf(b, sizeof b, "decoder loop needs %zu bytes of shared memory per SM (r = %d, %d characters), the device allows %zu",
@@ -787,7 +860,7 @@ int wrnn_taco_decode(wrnn_taco_handle *h, const float *enc_seq, int32_t L, int32
         long long pr[64];
         cudaMemcpy(pr, d_prof, sizeof pr, cudaMemcpyDeviceToHost);
         cudaFree(d_prof);
-        static const char *site[20] = {"A wait x3", "A dots", "B wait p1", "B dots+hh2", "C wait p2", "C dots+gates", "D wait h_attn", "D dots+hh1", "E",
+        static const char *site[20] = {"A wait x3", "A dots", "B wait p1", "B dots", "C wait p2", "C dots+gates", "D wait h_attn", "D dots", "E / ahead",
                                        "barrier", "F stop+ctx", "F dots+gates", "G wait x2", "G dots+gates", "", "", "", "", "", ""};
         const int nn = std::max(1, head[1]);
         fprintf(stderr, "taco prof (clk per decoder step; CTA 0 | first position owner)\n");
