@@ -16,6 +16,8 @@ fatchord WaveRNN MoL (rnn 512, fc 512, hop 275), batched target=11000 overlap=55
   config5 : the same line carries a second record, BASELINE.json configs[4] per GPU: 32 utterances of T=801 in ONE
           call (640 folds x 12100 steps; 256 utterances on 8 GPUs), through the tensor-core loop kernel (tcgen05, bf16
           hi/lo operands), with its own value / e2e / roofline (bound: tensor, against the measured sustained bf16 rate).
+  tacotron : a third record, SURVEY.md section 8(f)-3: the decoder loop of Tacotron.generate on `taco_loop_kernel`
+          (us per decoder step, mel frames/s, end to end with host buffers, the CPU restatement beside it).
   cpu_baseline : the reference's own un-patched generate() (staged copy, oracle/_ref) on the host cores, whole utterance.
 """
 import argparse
@@ -317,6 +319,47 @@ def run_deepmind(device, world, barrier, n_seq=8, seconds=2.0):      # SURVEY 8(
             'timed': 'wall clock around the C-ABI call, host int64 outputs included'}
 
 
+def run_tacotron(device, cpu_leg, L=150, r=2, frames=1600):
+    """the decoder loop of `Tacotron.generate` (models/tacotron.py:438-465) on `taco_loop_kernel`
+    through the C ABI: encoder output (host) in, mel frames and attention rows (host) out, no stop (threshold -inf) so
+    that the step count is fixed.  `cpu` = the oracle restatement (the reference's own ATen calls, bit-equal to the
+    reference's generate on CPU) on the host cores for a bounded number of the same steps."""
+    from wavernn_b200 import binding, synth
+    sd = synth.synth_taco_state_dict(seed=0)
+    enc = synth.synth_encoder_seq(L, seed=78)
+    dec = binding.TacotronDecoder(device=device)
+    dec.load_weights(sd)
+    dec.decode(enc, steps=64, r=r, stop_threshold=-1e30)                       # warm-up: packing, workspace
+    ms, wall = [], []
+    for _ in range(3):
+        t0 = time.time()
+        mel, attn = dec.decode(enc, steps=frames, r=r, stop_threshold=-1e30)
+        wall.append(time.time() - t0)
+        ms.append(dec.last_timing()['ms_loop'])
+    n = attn.shape[0]
+    assert mel.shape == (80, n * r) and n == frames // r and np.all(np.isfinite(mel))
+    rec = {'workload': f'one utterance, {L} characters, r = {r}, {n} decoder steps = {n * r} mel frames (no stop), decoder_dims 256, '
+                       f'lstm_dims 512 (hparams.py:67-73)',
+           'kernel': 'taco_loop_kernel', 'us_per_step': 1000 * min(ms) / n, 'frames_per_s': n * r / (min(ms) * 1e-3),
+           'rtf': n * r * 275 / SAMPLE_RATE / (min(ms) * 1e-3),
+           'e2e': {'frames_per_s': n * r / min(wall), 'ms': 1000 * min(wall), 'h2d_bytes': int(enc.nbytes),
+                   'd2h_bytes': int(mel.nbytes + attn.nbytes)},
+           'launches': 2 * 4, 'dtype': 'f32'}
+    dec.close()
+    if cpu_leg:
+        from oracle import tacotron as otc
+        import torch
+        torch.set_num_threads(os.cpu_count() or 1)
+        otc.decode(sd, enc, steps=8, r=r, stop_threshold=-1e30)
+        t0 = time.time()
+        cpu_steps = 200
+        otc.decode(sd, enc, steps=cpu_steps * r, r=r, stop_threshold=-1e30)
+        dt = time.time() - t0
+        rec['cpu'] = {'us_per_step': 1e6 * dt / cpu_steps, 'frames_per_s': cpu_steps * r / dt, 'cores': os.cpu_count() or 1,
+                      'kind': 'port', 'sample': f'{cpu_steps} of the {n} decoder steps ({dt:.2f} s)'}
+    return rec
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -438,6 +481,10 @@ def run_ours(args):
             c5['roofline']['frac'] = c5['roofline']['achieved'] / bf16
             c5['roofline']['peak_source'] = peak_src + ' bf16_tflops_sustained'
             line['config5'] = c5
+        if not args.no_tacotron:
+            taco = run_tacotron(torch.cuda.current_device(), world == 1 and not args.no_cpu)
+            line['gpu_launches'] += taco.pop('launches')
+            line['tacotron'] = taco
         if world == 1 and not args.no_cpu:
             threads = os.cpu_count() or 1
             from wavernn_b200 import synth
@@ -460,6 +507,7 @@ def main():
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
     ap.add_argument('--no-cpu', action='store_true', help='skip the cpu_baseline leg')
     ap.add_argument('--no-config5', action='store_true', help='skip the 32-utterance record')
+    ap.add_argument('--no-tacotron', action='store_true', help='skip the Tacotron decoder-loop record')
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == 'ours' else args.warmup
     if args.impl == 'reference':

@@ -142,3 +142,111 @@ def test_kernel_argument_errors():
     with pytest.raises(WrnnError):
         dec.decode(synth.synth_encoder_seq(10), steps=10, r=21)         # r > Decoder.max_r
     dec.close()
+
+
+def test_adapter_plumbing_against_the_reference_model():
+    """`wavernn_b200.tacotron.generate` bound to the reference's own Tacotron object (build container only): with the
+    decoder loop played by the oracle, the adapter's encoder / postnet plumbing must return exactly what the
+    reference's `generate` returns."""
+    from oracle import ref_shim, tacotron as otc
+    if not ref_shim.available():
+        pytest.skip('reference tree not present')
+    import wavernn_b200.tacotron as bt
+
+    class OracleDecoder:
+        def __init__(self, **kw):
+            self.kw = kw
+
+        def load_weights(self, state):
+            self.state = {k: v.detach().cpu().numpy() for k, v in state.items()}
+
+        def decode(self, enc, steps, r, stop_threshold):
+            return otc.decode(self.state, enc, steps=steps, r=r, stop_threshold=stop_threshold)
+
+    sd = synth.synth_taco_state_dict(seed=0)
+    enc = synth.synth_encoder_seq(37, seed=77)
+    model = ref_shim.build_tacotron(sd, enc, r=2)
+    x = [1 + (i % 60) for i in range(37)]
+    want = model.generate(x, steps=60)
+    real = bt.TacotronDecoder
+    bt.TacotronDecoder = OracleDecoder
+    try:
+        got = bt.generate(model, x, steps=60)
+    finally:
+        bt.TacotronDecoder = real
+        model.__dict__.pop('_b200_taco_decoder', None)
+    for a, b in zip(want, got):
+        assert a.shape == b.shape and np.array_equal(a, b)
+    assert model.training
+
+
+@pytest.mark.gpu
+def test_adapter_on_gpu_with_a_stand_in_model():
+    """The adapter end to end on the GPU: a model object with the reference's attribute names (embedding as the encoder,
+    one convolution as the postnet), the decoder loop on the kernel; mel against the oracle, linear against the same
+    postnet applied to the oracle's mel."""
+    import torch
+    from torch import nn
+    from oracle import tacotron as otc
+    import wavernn_b200.tacotron as bt
+
+    sd = synth.synth_taco_state_dict(seed=2)
+
+    class Bag(nn.Module):
+        pass
+
+    def bag_from(prefix):
+        root = Bag()
+        for k, v in sd.items():
+            if not k.startswith(prefix):
+                continue
+            parts = k[len(prefix):].split('.')
+            node = root
+            for name in parts[:-1]:
+                if not hasattr(node, name):
+                    setattr(node, name, Bag())
+                node = getattr(node, name)
+            node.register_parameter(parts[-1], nn.Parameter(torch.from_numpy(v.copy())))
+        return root
+
+    class Postnet(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.conv = nn.Conv1d(80, 64, 3, padding=1)
+
+        def forward(self, x):
+            return torch.tanh(self.conv(x)).transpose(1, 2)
+
+    class StandIn(nn.Module):
+        def __init__(self):
+            super().__init__()
+            torch.manual_seed(11)
+            self.encoder = nn.Embedding(70, 256)
+            self.encoder_proj = nn.Linear(256, 256, bias=False)
+            self.encoder_proj.weight.data.copy_(torch.from_numpy(sd['encoder_proj.weight']))
+            self.decoder = bag_from('decoder.')
+            self.postnet = Postnet()
+            self.post_proj = nn.Linear(64, 80, bias=False)
+            self.register_buffer('stop_threshold', torch.tensor(-3.4))
+            self.r = 2
+
+    model = StandIn().cuda()
+    x = [3 + (i * 7) % 60 for i in range(45)]
+    mel, linear, attn = bt.generate(model, x, steps=80)
+    enc = model.encoder(torch.as_tensor(x, device='cuda')).detach().cpu().numpy()
+    o_mel, o_attn = otc.decode(sd, enc, steps=80, r=2)
+    assert mel.shape == o_mel.shape == (80, 80) and attn.shape == (40, 45) and linear.shape == (80, 80)
+    assert np.abs(mel - o_mel).max() < MEL_TOL and np.abs(attn - o_attn).max() < ATTN_TOL
+    with torch.no_grad():
+        want_lin = model.post_proj(model.postnet(torch.as_tensor(o_mel, device='cuda').unsqueeze(0))).transpose(1, 2)[0].cpu().numpy()
+    assert np.abs(linear - want_lin).max() < 1e-4
+    assert model.training
+    # the second call reuses the packed decoder; a parameter update re-packs it
+    dec1 = model.__dict__['_b200_taco_decoder'][1]
+    bt.generate(model, x, steps=20)
+    assert model.__dict__['_b200_taco_decoder'][1] is dec1
+    with torch.no_grad():
+        model.decoder.mel_proj.weight.mul_(0.5)
+    mel2, _, _ = bt.generate(model, x, steps=20)
+    assert model.__dict__['_b200_taco_decoder'][1] is not dec1
+    assert np.abs(mel2[:, :2] - 0.5 * mel[:, :2]).max() < MEL_TOL

@@ -49,6 +49,7 @@ struct TacoParams {
     float *part_ctx, *part_sum, *melf;
     float *mel_out, *attn_out;
     int *n_iter;
+    int d_first, d_poll;                           // clocks before the first look at a fresh vector / between looks
     long long *prof;                               // debug (WRNN_TACO_PROF): [2 CTAs][32] clocks per site, summed over steps
     GridSync gs;
 };
@@ -91,12 +92,19 @@ __device__ __forceinline__ void st_word(uint2 *p, float value, unsigned tag) {
     asm volatile("st.relaxed.gpu.global.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(__float_as_uint(value)), "r"(tag) : "memory");
 }
 // the value of a tagged word once its producer has stored it; a watchdog turns a lost hand-over into the abort flag
-__device__ __forceinline__ float wait_word(const uint2 *p, unsigned tag, int *abort_flag) {
+__device__ __forceinline__ void spin_clocks(int n) {
+    if (n > 0) {
+        const long long t0 = clock64();
+        while (clock64() - t0 < n) {}
+    }
+}
+__device__ __forceinline__ float wait_word(const uint2 *p, unsigned tag, int *abort_flag, int d_poll = 0) {
     uint2 w = ld_word(p);
     if (w.y != tag) {
         const long long t0 = clock64();
         unsigned spins = 0;
         do {
+            spin_clocks(d_poll);
             w = ld_word(p);
             if ((++spins & 255u) == 0u && (clock64() - t0 > 4000000000ll || ld_volatile_s32(abort_flag))) {       // ~2 s
                 atomicExch(abort_flag, 1);
@@ -202,7 +210,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
     // One full grid barrier per step remains (E -> F: the partial contexts are too many words to poll); it is also what
     // makes single buffers safe (every buffer is rewritten only after a barrier that all of its readers have passed).
     auto fetch = [&](const uint2 *src, int n, unsigned tag, float *dst) {
-        for (int i = tid; i < n; i += TC_THREADS) dst[i] = wait_word(src + i, tag, P.gs.abort_flag);
+        if (n > 0) spin_clocks(P.d_first);
+        for (int i = tid; i < n; i += TC_THREADS) dst[i] = wait_word(src + i, tag, P.gs.abort_flag, P.d_poll);
     };
     // activation of LSTM gate row w = unit * 4 + gate, applied by the warp that formed the row (gates i, f, g, o)
     auto lstm_act = [&](int w, float x) { return (w & 3) == 2 ? tanhf(x) : sigmoidf_acc(x); };
@@ -219,9 +228,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
         if (tid < n1) w1 = ld_word(s1 + tid);
         if (tid < n2) w2 = ld_word(s2 + tid);
         if (tid < n3) w3 = ld_word(s3 + tid);
-        if (tid < n1) d1[tid] = w1.y == t1 ? __uint_as_float(w1.x) : wait_word(s1 + tid, t1, P.gs.abort_flag);
-        if (tid < n2) d2[tid] = w2.y == t2 ? __uint_as_float(w2.x) : wait_word(s2 + tid, t2, P.gs.abort_flag);
-        if (tid < n3) d3[tid] = w3.y == t3 ? __uint_as_float(w3.x) : wait_word(s3 + tid, t3, P.gs.abort_flag);
+        if (tid < n1) d1[tid] = w1.y == t1 ? __uint_as_float(w1.x) : wait_word(s1 + tid, t1, P.gs.abort_flag, P.d_poll);
+        if (tid < n2) d2[tid] = w2.y == t2 ? __uint_as_float(w2.x) : wait_word(s2 + tid, t2, P.gs.abort_flag, P.d_poll);
+        if (tid < n3) d3[tid] = w3.y == t3 ? __uint_as_float(w3.x) : wait_word(s3 + tid, t3, P.gs.abort_flag, P.d_poll);
     };
 
     for (int it = 0;; it++) {
@@ -836,6 +845,10 @@ int wrnn_taco_decode(wrnn_taco_handle *h, const float *enc_seq, int32_t L, int32
     P.mel_out = F(o_mel); P.attn_out = F(o_attn); P.n_iter = (int *)(ws + o_n);
     P.gs.counter = (unsigned long long *)ws;
     P.gs.abort_flag = (int *)(ws + 64);
+    // measured on B200 (scripts/taco_delay_sweep.py): a first look 300 .. 600 clocks after the own publish is 12 % faster
+    // than an immediate one (a look that fails costs a second L2 round trip and queues ahead of the late stores)
+    P.d_first = getenv("WRNN_TACO_D1") ? atoi(getenv("WRNN_TACO_D1")) : 450;
+    P.d_poll = getenv("WRNN_TACO_D2") ? atoi(getenv("WRNN_TACO_D2")) : 0;
     P.prof = nullptr;
     long long *d_prof = nullptr;
     if (getenv("WRNN_TACO_PROF")) {
