@@ -2,6 +2,7 @@
 
   python scripts/prof_target.py mma     640 folds x 300 steps on the tensor-core kernel
   python scripts/prof_target.py res     one utterance, 20 folds x 2 200 steps on the register-resident kernel
+  python scripts/prof_target.py taco    Tacotron decoder loop, 150 characters, 200 decoder steps
 `mma`: 640 folds x 300 steps on the tensor-core kernel (T=582, target 200, overlap 50: the shape tests/test_mma_gpu.py checks).
 """
 import os
@@ -14,6 +15,12 @@ from wavernn_b200 import binding, synth      # noqa: E402
 from wavernn_b200.config import VocoderDims  # noqa: E402
 
 what = sys.argv[1] if len(sys.argv) > 1 else 'mma'
+if what == 'taco':      # the Tacotron decoder loop: 150 characters, r = 2, 200 decoder steps
+    dec = binding.TacotronDecoder(device=0)
+    dec.load_weights(synth.synth_taco_state_dict(seed=0))
+    mel, attn = dec.decode(synth.synth_encoder_seq(150, seed=78), steps=400, r=2, stop_threshold=-1e30)
+    print(what, mel.shape, attn.shape, dec.last_timing())
+    sys.exit(0)
 dims = VocoderDims(mode='MOL')
 v = binding.Vocoder(dims, device=0)
 v.load_weights(synth.synth_state_dict(dims, seed=0, style='init'))
