@@ -46,7 +46,8 @@ struct TacoParams {
     const float *common;                           // conv w [32][2][31] (+pad to 2048) | v [D] | L.weight [D][32] | L.bias [D]
     const float *enc, *encp;                       // [L][D]
     uint2 *p1, *p2, *ha, *pq, *x2, *h1, *h2, *x3, *att_g, *cum_g;      // tagged words {value, 1 + producing step}
-    float *part_ctx, *part_sum, *melf;
+    uint2 *melf;                                   // frames of the last step, tagged like the rest (read by the stop rule)
+    float *part_ctx, *part_sum;
     float *mel_out, *attn_out;
     int *n_iter;
     int d_first, d_poll;                           // clocks before the first look at a fresh vector / between looks
@@ -117,10 +118,16 @@ __device__ __forceinline__ float wait_word(const uint2 *p, unsigned tag, int *ab
 
 // the grid barrier in two halves: a CTA arrives as soon as it has nothing more to publish and waits after the work that
 // needs nothing from the others
-__device__ __forceinline__ void grid_arrive(const GridSync &gs, unsigned long long &gen) {
+// `release`: the CTA has plain stores the others read after the barrier (the position owners' partial sums).  Everything
+// else travels as self-validating tagged words, so a CTA without such stores arrives with a relaxed add and spares itself
+// the fence (measured: ~2 k clocks of thread 0, which the whole CTA then waits for at its next __syncthreads)
+__device__ __forceinline__ void grid_arrive(const GridSync &gs, unsigned long long &gen, bool release) {
     __syncthreads();
     gen++;
-    if (threadIdx.x == 0) red_release_add_u64(gs.counter, 1ull);
+    if (threadIdx.x == 0) {
+        if (release) red_release_add_u64(gs.counter, 1ull);
+        else asm volatile("red.relaxed.gpu.global.add.u64 [%0], %1;" ::"l"(gs.counter), "l"(1ull) : "memory");
+    }
 }
 __device__ __forceinline__ void grid_wait(const GridSync &gs, unsigned long long gen) {
     if (threadIdx.x == 0) {
@@ -209,8 +216,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
     // starts one L2 round trip after its last producer stored: no fence, no counter, no second trip for the data.
     // One full grid barrier per step remains (E -> F: the partial contexts are too many words to poll); it is also what
     // makes single buffers safe (every buffer is rewritten only after a barrier that all of its readers have passed).
-    auto fetch = [&](const uint2 *src, int n, unsigned tag, float *dst) {
-        if (n > 0) spin_clocks(P.d_first);
+    auto fetch = [&](const uint2 *src, int n, unsigned tag, float *dst, bool delay = true) {
+        if (n > 0 && delay) spin_clocks(P.d_first);
         for (int i = tid; i < n; i += TC_THREADS) dst[i] = wait_word(src + i, tag, P.gs.abort_flag, P.d_poll);
     };
     // activation of LSTM gate row w = unit * 4 + gate, applied by the warp that formed the row (gates i, f, g, o)
@@ -250,7 +257,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
                     if (it > 0) {
                         const int m = row / r, jj = row - m * r;
                         P.mel_out[(size_t)m * P.cap + (size_t)(it - 1) * r + jj] = d;
-                        P.melf[row] = d;
+                        st_word(P.melf + row, d, tag_now);
                     }
                 } else {
                     st_word(P.p1 + (row - nmel), fmaxf(d + bA[j], 0.f), tag_now);
@@ -357,18 +364,30 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
             __syncthreads();
         };
         if (nl == 0) {
-            grid_arrive(P.gs, gen);
+            grid_arrive(P.gs, gen, false);
             shadow();
         }
         // ---- E: energies, sigmoid and the partial context of the owned positions
         if (nl > 0) {
             fetch(P.pq, D, tag_now, vec);
             __syncthreads();
-            for (int p = half; p < nl; p += 2) {
-                float v = va * tanhf(vec[a] + encp_s[(size_t)p * D + a] + ploc[(size_t)p * D + a]);
+            for (int p0 = half; p0 < nl; p0 += 8) {              // four positions per pass: their shuffle trees overlap
+                float v[4];
 #pragma unroll
-                for (int o = 16; o >= 1; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-                if (lane == 0) red[p * 8 + (warp & 7)] = v;
+                for (int q = 0; q < 4; q++) {
+                    const int p = p0 + 2 * q;
+                    v[q] = p < nl ? va * tanhf(vec[a] + encp_s[(size_t)p * D + a] + ploc[(size_t)p * D + a]) : 0.f;
+                }
+#pragma unroll
+                for (int o = 16; o >= 1; o >>= 1) {
+#pragma unroll
+                    for (int q = 0; q < 4; q++) v[q] += __shfl_xor_sync(0xffffffffu, v[q], o);
+                }
+                if (lane == 0) {
+#pragma unroll
+                    for (int q = 0; q < 4; q++)
+                        if (p0 + 2 * q < nl) red[(p0 + 2 * q) * 8 + (warp & 7)] = v[q];
+                }
             }
             __syncthreads();
             if (tid < nl) {
@@ -388,7 +407,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
             }
         }
         if (nl > 0) {
-            grid_arrive(P.gs, gen);
+            grid_arrive(P.gs, gen, true);
             shadow();
         }
         TMARK(8);
@@ -398,12 +417,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
         //         before the barrier); context = sum of partials / sum of sums; rnn_input + LSTM 1; owners normalise
         {
             const bool check = it > 0 && (it - 1) * r > 10;
-            float mv[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
-            if (check) {
+            uint2 mw[4];                                        // first looks now, validated after the other loads are out
 #pragma unroll
-                for (int q = 0; q < 4; q++)
-                    if (tid + q * TC_THREADS < nmel) mv[q] = __ldcg(P.melf + tid + q * TC_THREADS);
-            }
+            for (int q = 0; q < 4; q++)
+                mw[q] = (check && tid + q * TC_THREADS < nmel) ? ld_word(P.melf + tid + q * TC_THREADS) : make_uint2(0xff800000u, tag_now);
             const float ps = tid < P.PC ? __ldcg(P.part_sum + tid) : 0.f;
             float acc = 0.f;
             for (int p0 = half; p0 < P.PC; p0 += 20) {          // (d, half) sums every second partial, ten loads in flight
@@ -421,8 +438,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
             if (half) chalf[a] = acc;
             int ok = check ? 1 : 0;
 #pragma unroll
-            for (int q = 0; q < 4; q++) ok &= (mv[q] < P.thr) ? 1 : 0;
-            for (int i = tid + 4 * TC_THREADS; check && i < nmel; i += TC_THREADS) ok &= (__ldcg(P.melf + i) < P.thr) ? 1 : 0;
+            for (int q = 0; q < 4; q++) {
+                const float mv = mw[q].y == tag_now ? __uint_as_float(mw[q].x)
+                                                    : wait_word(P.melf + tid + q * TC_THREADS, tag_now, P.gs.abort_flag);
+                ok &= (mv < P.thr) ? 1 : 0;
+            }
+            for (int i = tid + 4 * TC_THREADS; check && i < nmel; i += TC_THREADS) ok &= (wait_word(P.melf + i, tag_now, P.gs.abort_flag) < P.thr) ? 1 : 0;
             if (__syncthreads_and(ok)) break;
             float total = 0.f;
             for (int w = 0; w < (P.PC + 31) / 32; w++) total += psum_s[w];
@@ -824,7 +845,7 @@ int wrnn_taco_decode(wrnn_taco_handle *h, const float *enc_seq, int32_t L, int32
     auto take = [&](size_t floats) { const size_t o = off; off += ((floats * 4 + 127) & ~(size_t)127); return o; };
     const size_t o_p1 = take(2 * P.P1), o_p2 = take(2 * P.P2), o_ha = take(4 * D), o_pq = take(2 * D), o_pc = take((size_t)owners * D),
                  o_ps = take(owners), o_x2 = take(2 * H), o_h1 = take(4 * H), o_h2 = take(4 * H), o_x3 = take(2 * H),
-                 o_melf = take((size_t)M * TC_MAXR), o_att = take(2 * (size_t)L), o_cum = take(2 * (size_t)L), o_n = take(1);
+                 o_melf = take(2 * (size_t)M * TC_MAXR), o_att = take(2 * (size_t)L), o_cum = take(2 * (size_t)L), o_n = take(1);
     const size_t state_end = off;
     const size_t o_enc = take((size_t)L * D), o_encp = take((size_t)L * D), o_mel = take((size_t)M * P.cap),
                  o_attn = take((size_t)P.max_iter * L);
@@ -841,7 +862,7 @@ int wrnn_taco_decode(wrnn_taco_handle *h, const float *enc_seq, int32_t L, int32
     P.image = h->image; P.common = h->common; P.enc = F(o_enc); P.encp = F(o_encp);
     auto U = [&](size_t o) { return (uint2 *)(ws + o); };
     P.p1 = U(o_p1); P.p2 = U(o_p2); P.ha = U(o_ha); P.pq = U(o_pq); P.part_ctx = F(o_pc); P.part_sum = F(o_ps);
-    P.x2 = U(o_x2); P.h1 = U(o_h1); P.h2 = U(o_h2); P.x3 = U(o_x3); P.melf = F(o_melf); P.att_g = U(o_att); P.cum_g = U(o_cum);
+    P.x2 = U(o_x2); P.h1 = U(o_h1); P.h2 = U(o_h2); P.x3 = U(o_x3); P.melf = U(o_melf); P.att_g = U(o_att); P.cum_g = U(o_cum);
     P.mel_out = F(o_mel); P.attn_out = F(o_attn); P.n_iter = (int *)(ws + o_n);
     P.gs.counter = (unsigned long long *)ws;
     P.gs.abort_flag = (int *)(ws + 64);
