@@ -7,6 +7,7 @@
 //   E  O3 + ReLU      F  O4 -> fine logits; the fine sample is drawn at the start of the next step (:148-152)
 // The reference runs one sequence; `n_seq` independent sequences (<= 8 per launch) share the weights.
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <map>
@@ -18,7 +19,7 @@
 
 namespace wrnn {
 
-constexpr int DM_THREADS = 256, DM_WARPS = DM_THREADS / 32, DM_MAXN = 8;
+constexpr int DM_THREADS = 512, DM_WARPS = DM_THREADS / 32, DM_MAXN = 8;
 
 struct DmParams {
     int H, S2, Q, N;             // hidden, hidden/2, quantisation, sequences in this launch
@@ -34,6 +35,7 @@ struct DmParams {
     int64_t Ntot, n0;
     int32_t *coarse, *fine;      // [N][T]
     uint64_t seed;
+    long long *prof;             // debug (WRNN_DM_PROF): clocks per site of CTA 0, summed over steps
     GridSync gs;
 };
 
@@ -69,6 +71,116 @@ __device__ __forceinline__ void stage_cg(float *dst, const float *src, int n, in
     for (int i = tid; i < (n >> 2); i += DM_THREADS) reinterpret_cast<float4 *>(dst)[i] = __ldcg(reinterpret_cast<const float4 *>(src) + i);
 }
 
+
+// softmax + Categorical draw of N <= 8 sequences by the whole block, with the bits of `categorical_warp` (loop_common.cuh):
+// that routine gives a lane the classes lane + 32 j and runs three dependent passes of expf over them in ONE warp, ~9.6 k
+// clocks per draw and two draws per step = 45 % of the step (measured, WRNN_DM_PROF).  Here a sequence gets 8 / 4 / 2 warps
+// (1-2 / 3-4 / 5-8 sequences), a warp takes a range of j, expf is evaluated once, and every sum that `categorical_warp`
+// forms sequentially per lane (j ascending from 0.f, then the xor tree) is formed in that same order by the first warp of
+// the sequence from values parked in shared memory, so the picks are identical bit for bit.  C <= 256.
+__device__ __forceinline__ void dm_sample_block(const float *lrow, int C, int N, const float *qsrc, size_t qstride, uint2 key,
+                                                uint32_t c0, uint32_t c1base, uint32_t stream, float *scr, int *res, int tid) {
+    const int warp = tid >> 5, lane = tid & 31;
+    const int WPS = N <= 2 ? 8 : N <= 4 ? 4 : 2, JW = 8 / WPS;
+    const int n = warp / WPS, g = warp - n * WPS;
+    const bool act = n < N;
+    float *ebuf = scr;                       // [N][8][32] values parked per (sequence, j, lane)
+    float *vbuf = scr + DM_MAXN * 256;       // [N][8][32] best value per (sequence, warp of the sequence, lane)
+    int *ibuf = reinterpret_cast<int *>(vbuf + DM_MAXN * 256);
+    float *wmax = reinterpret_cast<float *>(ibuf + DM_MAXN * 256);       // [16] | sval [8] | psval [8]
+    float *sval = wmax + DM_WARPS, *psval = sval + DM_MAXN;
+    const float *lg = lrow + (size_t)(act ? n : 0) * C;
+    float l[4], e[4];
+    float m = -INFINITY;
+#pragma unroll
+    for (int jj = 0; jj < 4; jj++) {
+        const int i = lane + 32 * (g * JW + jj);
+        l[jj] = (act && jj < JW && i < C) ? lg[i] : -INFINITY;
+        m = fmaxf(m, l[jj]);
+    }
+#pragma unroll
+    for (int o = 16; o >= 1; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if (lane == 0) wmax[warp] = m;
+    __syncthreads();
+    if (act) {
+        m = wmax[n * WPS];
+        for (int k = 1; k < WPS; k++) m = fmaxf(m, wmax[n * WPS + k]);
+    }
+#pragma unroll
+    for (int jj = 0; jj < 4; jj++) {
+        const int j = g * JW + jj, i = lane + 32 * j;
+        e[jj] = (act && jj < JW && i < C) ? expf(l[jj] - m) : 0.f;
+        if (act && jj < JW) ebuf[(n * 8 + j) * 32 + lane] = e[jj];
+    }
+    __syncthreads();
+    if (act && g == 0) {
+        float s = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; j++)
+            if (lane + 32 * j < C) s += ebuf[(n * 8 + j) * 32 + lane];
+#pragma unroll
+        for (int o = 16; o >= 1; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        if (lane == 0) sval[n] = s;
+    }
+    __syncthreads();
+    const float s = act ? sval[n] : 1.f;
+#pragma unroll
+    for (int jj = 0; jj < 4; jj++) {
+        const int j = g * JW + jj;
+        e[jj] = e[jj] / s;                   // p = expf(l - m) / s
+        if (act && jj < JW) ebuf[(n * 8 + j) * 32 + lane] = e[jj];
+    }
+    __syncthreads();
+    if (act && g == 0) {
+        float ps = 0.f;                      // Categorical renormalises: probs / probs.sum(-1)
+#pragma unroll
+        for (int j = 0; j < 8; j++)
+            if (lane + 32 * j < C) ps += ebuf[(n * 8 + j) * 32 + lane];
+#pragma unroll
+        for (int o = 16; o >= 1; o >>= 1) ps += __shfl_xor_sync(0xffffffffu, ps, o);
+        if (lane == 0) psval[n] = ps;
+    }
+    __syncthreads();
+    float best = -INFINITY;
+    int bi = 0x7fffffff;
+    if (act) {
+        const float ps = psval[n];
+        const int call = (g * JW) >> 2;      // the Philox call of categorical_warp that covers this warp's j range
+        uint4 r = make_uint4(0, 0, 0, 0);
+        if (!qsrc) r = philox4x32(make_uint4(c0, c1base + (uint32_t)n, (uint32_t)(call * 32 + lane), stream), key);
+        const uint32_t rr[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+        for (int jj = 0; jj < 4; jj++) {
+            const int j = g * JW + jj, i = lane + 32 * j;
+            if (jj < JW && i < C) {
+                const float p = e[jj] / ps;
+                const float q = qsrc ? qsrc[(size_t)n * qstride + i] : exp1(rr[j & 3]);
+                const float v = p / q;
+                if (v > best) { best = v; bi = i; }    // ascending i per lane: first max kept
+            }
+        }
+        vbuf[(n * 8 + g) * 32 + lane] = best;
+        ibuf[(n * 8 + g) * 32 + lane] = bi;
+    }
+    __syncthreads();
+    if (act && g == 0) {
+        best = -INFINITY;
+        bi = 0x7fffffff;
+        for (int k = 0; k < WPS; k++) {
+            const float v = vbuf[(n * 8 + k) * 32 + lane];
+            if (v > best) { best = v; bi = ibuf[(n * 8 + k) * 32 + lane]; }
+        }
+#pragma unroll
+        for (int o = 16; o >= 1; o >>= 1) {
+            const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+            const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+            if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
+        }
+        if (lane == 0) res[n] = bi;
+    }
+    __syncthreads();
+}
+
 __global__ void __launch_bounds__(DM_THREADS, 1) dm_loop_kernel(const DmParams P) {
     extern __shared__ __align__(16) float smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, cta = blockIdx.x;
@@ -77,6 +189,9 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dm_loop_kernel(const DmParams P
     float *xbuf = wimg + P.img_floats;               // [N][H] staged inputs
     float *rsum = xbuf + (size_t)DM_MAXN * H;        // [upc][3][N] R.hidden of the owned units
     float *lrow = rsum + (size_t)P.upc * 3 * DM_MAXN;   // [N][Q] staged logits
+    float *sscr = lrow + (size_t)DM_MAXN * Q;           // sampler scratch (dm_sample_block)
+    __shared__ int picks[DM_MAXN];
+    const bool fast_draw = Q <= 256;
     __shared__ int prev_c[DM_MAXN], prev_f[DM_MAXN], cur_c[DM_MAXN];
     for (int i = tid; i < P.img_floats / 4; i += DM_THREADS)
         reinterpret_cast<float4 *>(wimg)[i] = reinterpret_cast<const float4 *>(P.image + (size_t)cta * P.img_floats)[i];
@@ -92,25 +207,48 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dm_loop_kernel(const DmParams P
     const uint2 key = make_uint2((uint32_t)P.seed, (uint32_t)(P.seed >> 32));
     unsigned long long gen = 0;
     float o[DM_MAXN];
+    __shared__ long long prof_acc[16];
+    long long prof_last = 0;
+    const bool prof_on = P.prof != nullptr && tid == 0 && cta == 0;
+    if (tid < 16) prof_acc[tid] = 0;
+#define DMARK(i)                                      \
+    if (prof_on) {                                    \
+        const long long c__ = clock64();              \
+        prof_acc[i] += c__ - prof_last;               \
+        prof_last = c__;                              \
+    }
 
     for (int64_t t = 0; t <= P.T; t++) {
         const float *hcur = P.hidden + (size_t)(t & 1) * N * H;
         float *hnxt = P.hidden + (size_t)((t + 1) & 1) * N * H;
         // ---- fine sample of step t-1 (every CTA draws the same value; CTA 0 records it)
+        if (prof_on) prof_last = clock64();
         if (t > 0) {
             stage_cg(lrow, P.lf, N * Q, tid);
             __syncthreads();
-            for (int n = warp; n < N; n += DM_WARPS) {
-                const float *qs = P.qf ? P.qf + ((size_t)(t - 1) * P.Ntot + P.n0 + n) * Q : nullptr;
-                const int k = categorical_warp(lrow + (size_t)n * Q, Q, qs, key, (uint32_t)(t - 1), (uint32_t)(P.n0 + n), 5u, lane);
-                if (lane == 0) {
-                    prev_f[n] = k;
-                    prev_c[n] = cur_c[n];
-                    if (cta == 0) P.fine[(size_t)n * P.T + t - 1] = k;
+            DMARK(0);
+            if (fast_draw) {
+                dm_sample_block(lrow, Q, N, P.qf ? P.qf + ((size_t)(t - 1) * P.Ntot + P.n0) * Q : nullptr, (size_t)Q, key, (uint32_t)(t - 1),
+                                (uint32_t)P.n0, 5u, sscr, picks, tid);
+                if (tid < N) {
+                    prev_f[tid] = picks[tid];
+                    prev_c[tid] = cur_c[tid];
+                    if (cta == 0) P.fine[(size_t)tid * P.T + t - 1] = picks[tid];
+                }
+            } else {
+                for (int n = warp; n < N; n += DM_WARPS) {
+                    const float *qs = P.qf ? P.qf + ((size_t)(t - 1) * P.Ntot + P.n0 + n) * Q : nullptr;
+                    const int k = categorical_warp(lrow + (size_t)n * Q, Q, qs, key, (uint32_t)(t - 1), (uint32_t)(P.n0 + n), 5u, lane);
+                    if (lane == 0) {
+                        prev_f[n] = k;
+                        prev_c[n] = cur_c[n];
+                        if (cta == 0) P.fine[(size_t)n * P.T + t - 1] = k;
+                    }
                 }
             }
             __syncthreads();
         }
+        DMARK(1);
         if (t == P.T) break;
         // ---- A: R.hidden for owned units; coarse units update now
         stage_cg(xbuf, hcur, N * H, tid);
@@ -136,7 +274,9 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dm_loop_kernel(const DmParams P
                 hnxt[(size_t)n * H + unit] = uu * xbuf[n * H + unit] + (1.f - uu) * ee;                    // :125
             }
         }
+        DMARK(2);
         grid_barrier(P.gs, gen);
+        DMARK(3);
         // ---- B: O1 + ReLU on hidden_coarse
         stage_cg(xbuf, hnxt, N * H, tid);          // only [:, :S2] is new; the rest is ignored
         __syncthreads();
@@ -148,7 +288,9 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dm_loop_kernel(const DmParams P
                 for (int n = 0; n < DM_MAXN; n++) if (n < N) P.o1[(size_t)n * S2 + a0 + j] = fmaxf(o[n] + bO1[j], 0.f);
             }
         }
+        DMARK(4);
         grid_barrier(P.gs, gen);
+        DMARK(5);
         // ---- C: O2 -> coarse logits
         stage_cg(xbuf, P.o1, N * S2, tid);
         __syncthreads();
@@ -160,17 +302,28 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dm_loop_kernel(const DmParams P
                 for (int n = 0; n < DM_MAXN; n++) if (n < N) P.lc[(size_t)n * Q + c0 + j] = o[n] + bO2[j];
             }
         }
+        DMARK(6);
         grid_barrier(P.gs, gen);
+        DMARK(7);
         // ---- D: coarse sample (redundant), fine gates
         stage_cg(lrow, P.lc, N * Q, tid);
         stage_cg(xbuf, hcur, N * H, tid);          // previous hidden_fine for the fine update
         __syncthreads();
-        for (int n = warp; n < N; n += DM_WARPS) {
-            const float *qs = P.qc ? P.qc + ((size_t)t * P.Ntot + P.n0 + n) * Q : nullptr;
-            const int k = categorical_warp(lrow + (size_t)n * Q, Q, qs, key, (uint32_t)t, (uint32_t)(P.n0 + n), 4u, lane);
-            if (lane == 0) {
-                cur_c[n] = k;
-                if (cta == 0) P.coarse[(size_t)n * P.T + t] = k;
+        if (fast_draw) {
+            dm_sample_block(lrow, Q, N, P.qc ? P.qc + ((size_t)t * P.Ntot + P.n0) * Q : nullptr, (size_t)Q, key, (uint32_t)t, (uint32_t)P.n0, 4u,
+                            sscr, picks, tid);
+            if (tid < N) {
+                cur_c[tid] = picks[tid];
+                if (cta == 0) P.coarse[(size_t)tid * P.T + t] = picks[tid];
+            }
+        } else {
+            for (int n = warp; n < N; n += DM_WARPS) {
+                const float *qs = P.qc ? P.qc + ((size_t)t * P.Ntot + P.n0 + n) * Q : nullptr;
+                const int k = categorical_warp(lrow + (size_t)n * Q, Q, qs, key, (uint32_t)t, (uint32_t)(P.n0 + n), 4u, lane);
+                if (lane == 0) {
+                    cur_c[n] = k;
+                    if (cta == 0) P.coarse[(size_t)n * P.T + t] = k;
+                }
             }
         }
         __syncthreads();
@@ -188,7 +341,9 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dm_loop_kernel(const DmParams P
                 hnxt[(size_t)n * H + unit] = uu * xbuf[n * H + unit] + (1.f - uu) * ee;                    // :145
             }
         }
+        DMARK(8);
         grid_barrier(P.gs, gen);
+        DMARK(9);
         // ---- E: O3 + ReLU on hidden_fine
         stage_cg(xbuf, hnxt, N * H, tid);
         __syncthreads();
@@ -200,7 +355,9 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dm_loop_kernel(const DmParams P
                 for (int n = 0; n < DM_MAXN; n++) if (n < N) P.o3[(size_t)n * S2 + a0 + j] = fmaxf(o[n] + bO3[j], 0.f);
             }
         }
+        DMARK(10);
         grid_barrier(P.gs, gen);
+        DMARK(11);
         // ---- F: O4 -> fine logits
         stage_cg(xbuf, P.o3, N * S2, tid);
         __syncthreads();
@@ -212,8 +369,12 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dm_loop_kernel(const DmParams P
                 for (int n = 0; n < DM_MAXN; n++) if (n < N) P.lf[(size_t)n * Q + c0 + j] = o[n] + bO4[j];
             }
         }
+        DMARK(12);
         grid_barrier(P.gs, gen);
+        DMARK(13);
     }
+    if (prof_on)
+        for (int i = 0; i < 16; i++) P.prof[i] = prof_acc[i];
 }
 
 }  // namespace wrnn
@@ -284,7 +445,7 @@ static int dm_pack(wrnn_dm_handle *h) {
     p.off_I = o;  o += p.upc * 9;
     p.off_b = o;  o += p.upc * 3 + 2 * p.r1 + 2 * p.r2;
     p.img_floats = (o + 3) & ~3;
-    h->smem_bytes = ((size_t)p.img_floats + (size_t)DM_MAXN * H + (size_t)p.upc * 3 * DM_MAXN + (size_t)DM_MAXN * Q) * sizeof(float);
+    h->smem_bytes = ((size_t)p.img_floats + (size_t)DM_MAXN * H + (size_t)p.upc * 3 * DM_MAXN + (size_t)DM_MAXN * Q + 3 * (size_t)DM_MAXN * 256 + 64) * sizeof(float);
     if (h->smem_bytes > h->smem_optin) return dm_fail(h, WRNN_ERR_ARG, "deepmind model too large for the shared-memory resident kernel");
     std::vector<float> img((size_t)G * p.img_floats, 0.f);
     for (int c = 0; c < G; c++) {
@@ -444,12 +605,28 @@ int wrnn_dm_generate(wrnn_dm_handle *h, int64_t seq_len, int32_t n_seq, const fl
         P.coarse = (int32_t *)(ws + o_c) + (size_t)n0 * seq_len;
         P.fine = (int32_t *)(ws + o_f) + (size_t)n0 * seq_len;
         P.seed = seed;
+        P.prof = nullptr;
+        long long *d_prof = nullptr;
+        if (getenv("WRNN_DM_PROF")) {
+            DM_CUDA(h, cudaMalloc((void **)&d_prof, 16 * sizeof(long long)));
+            DM_CUDA(h, cudaMemsetAsync(d_prof, 0, 16 * sizeof(long long), st));
+            P.prof = d_prof;
+        }
         void *args[] = {(void *)&P};
         DM_CUDA(h, cudaLaunchCooperativeKernel((const void *)dm_loop_kernel, dim3(h->num_sms), dim3(DM_THREADS), args, h->smem_bytes, st));
         h->launches++;
         int flag = 0;
         DM_CUDA(h, cudaMemcpyAsync(&flag, ws + 64, sizeof(int), cudaMemcpyDeviceToHost, st));
         DM_CUDA(h, cudaStreamSynchronize(st));
+        if (d_prof) {
+            long long pr[16];
+            cudaMemcpy(pr, d_prof, sizeof pr, cudaMemcpyDeviceToHost);
+            cudaFree(d_prof);
+            static const char *site[14] = {"stage lf", "sample f", "A R.h + gates", "A barrier", "B O1", "B barrier", "C O2", "C barrier",
+                                           "D stage + sample c + gates", "D barrier", "E O3", "E barrier", "F O4", "F barrier"};
+            fprintf(stderr, "dm prof, %d sequences (clk per step, CTA 0)\n", P.N);
+            for (int i = 0; i < 14; i++) fprintf(stderr, "  %-28s %7.0f\n", site[i], (double)pr[i] / (double)seq_len);
+        }
         if (flag) return dm_fail(h, WRNN_ERR_CUDA, "deepmind loop kernel aborted: grid barrier watchdog fired");
     }
     DM_CUDA(h, cudaEventRecord(h->ev[1], st));
