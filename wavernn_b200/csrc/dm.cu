@@ -49,14 +49,13 @@ __device__ __forceinline__ void warp_rows(const float *W, int ld, int K, const f
     for (int k4 = lane; k4 < (K >> 2); k4 += 32) {
         const float4 w = w4[k4];
 #pragma unroll
-        for (int n = 0; n < NMAX; n++)
-            if (n < N) {
-                const float4 x = reinterpret_cast<const float4 *>(X + (size_t)n * ldx)[k4];
-                acc[n] = fmaf(w.x, x.x, acc[n]);
-                acc[n] = fmaf(w.y, x.y, acc[n]);
-                acc[n] = fmaf(w.z, x.z, acc[n]);
-                acc[n] = fmaf(w.w, x.w, acc[n]);
-            }
+        for (int n = 0; n < NMAX; n++) {        // all NMAX sets, absent sequences included (their rows of X are shared memory
+            const float4 x = reinterpret_cast<const float4 *>(X + (size_t)n * ldx)[k4];      // nobody reads the result of)
+            acc[n] = fmaf(w.x, x.x, acc[n]);
+            acc[n] = fmaf(w.y, x.y, acc[n]);
+            acc[n] = fmaf(w.z, x.z, acc[n]);
+            acc[n] = fmaf(w.w, x.w, acc[n]);
+        }
     }
 #pragma unroll
     for (int n = 0; n < NMAX; n++) {
@@ -65,6 +64,56 @@ __device__ __forceinline__ void warp_rows(const float *W, int ld, int K, const f
         out[n] = acc[n];
     }
     (void)ld;
+}
+
+// `nrows` rows x NS sequences as jobs of (one row, GS consecutive sequences) spread over all warps: with 4 rows and 8
+// sequences one warp per row leaves 12 of 16 warps idle; a job keeps `warp_rows`' per-lane order for every (row, sequence),
+// so the sums are the same bits.  emit(row, sequence, value) is called by lane 0.
+template <int NS, int GS, typename F>
+__device__ __forceinline__ void rows_split(const float *W, int ldw, int K, const float *X, int ldx, int nrows, int N, int warp, int lane, F emit,
+                                           int part = 0, int parts = 1) {
+    constexpr int NG = NS / GS;
+    float out[GS];
+    const int jobs = nrows * NG, jb = (int)((long long)jobs * part / parts), je = (int)((long long)jobs * (part + 1) / parts);
+    for (int job = jb + warp; job < je; job += DM_WARPS) {
+        const int j = job / NG, n0 = (job - j * NG) * GS;
+        if (n0 >= N) continue;
+        warp_rows<GS>(W + (size_t)j * ldw, ldw, K, X + (size_t)n0 * ldx, ldx, N - n0, lane, out);
+        if (lane == 0) {
+#pragma unroll
+            for (int g = 0; g < GS; g++)
+                if (n0 + g < N) emit(j, n0 + g, out[g]);
+        }
+    }
+}
+
+// rows x cols floats, row stride ld (global) / lds (shared), cols % 4 == 0
+__device__ __forceinline__ void stage_cg_2d(float *dst, int lds, const float *src, int ld, int rows, int cols, int tid) {
+    const int c4 = cols >> 2;
+    for (int i = tid; i < rows * c4; i += DM_THREADS) {
+        const int r = i / c4, c = i - r * c4;
+        reinterpret_cast<float4 *>(dst + (size_t)r * lds)[c] = __ldcg(reinterpret_cast<const float4 *>(src + (size_t)r * ld) + c);
+    }
+}
+// the grid barrier in two halves: work that needs nothing from the other CTAs goes between arrive and wait
+__device__ __forceinline__ void dm_arrive(const GridSync &gs, unsigned long long &gen) {
+    __syncthreads();
+    gen++;
+    if (threadIdx.x == 0) red_release_add_u64(gs.counter, 1ull);
+}
+__device__ __forceinline__ void dm_wait(const GridSync &gs, unsigned long long gen) {
+    if (threadIdx.x == 0) {
+        const unsigned long long want = gen * gridDim.x;
+        const long long t0 = clock64();
+        unsigned spins = 0;
+        while (ld_acquire_u64(gs.counter) < want) {
+            if ((++spins & 63u) == 0u && (clock64() - t0 > 4000000000ll || ld_volatile_s32(gs.abort_flag))) {   // ~2 s
+                atomicExch(gs.abort_flag, 1);
+                break;
+            }
+        }
+    }
+    __syncthreads();
 }
 
 __device__ __forceinline__ void stage_cg(float *dst, const float *src, int n, int tid) {     // written by other CTAs
@@ -181,13 +230,16 @@ __device__ __forceinline__ void dm_sample_block(const float *lrow, int C, int N,
     __syncthreads();
 }
 
+// NS = accumulator sets compiled in (1, 2, 4 or 8 >= N): the products carry no predicated sets for absent sequences
+template <int NS>
 __global__ void __launch_bounds__(DM_THREADS, 1) dm_loop_kernel(const DmParams P) {
     extern __shared__ __align__(16) float smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, cta = blockIdx.x;
     const int H = P.H, S2 = P.S2, Q = P.Q, N = P.N;
     float *wimg = smem;
     float *xbuf = wimg + P.img_floats;               // [N][H] staged inputs
-    float *rsum = xbuf + (size_t)DM_MAXN * H;        // [upc][3][N] R.hidden of the owned units
+    float *xo = xbuf + (size_t)DM_MAXN * H;          // [N][S2] o1 / o3 as staged
+    float *rsum = xo + (size_t)DM_MAXN * S2;         // [upc][3][N] R.hidden of the owned units, formed one step ahead
     float *lrow = rsum + (size_t)P.upc * 3 * DM_MAXN;   // [N][Q] staged logits
     float *sscr = lrow + (size_t)DM_MAXN * Q;           // sampler scratch (dm_sample_block)
     __shared__ int picks[DM_MAXN];
@@ -196,6 +248,8 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dm_loop_kernel(const DmParams P
     for (int i = tid; i < P.img_floats / 4; i += DM_THREADS)
         reinterpret_cast<float4 *>(wimg)[i] = reinterpret_cast<const float4 *>(P.image + (size_t)cta * P.img_floats)[i];
     if (tid < DM_MAXN) prev_c[tid] = prev_f[tid] = cur_c[tid] = 0;
+    for (int i = tid; i < DM_MAXN * H; i += DM_THREADS) xbuf[i] = 0.f;                 // hidden = 0 (:167-169)
+    for (int i = tid; i < P.upc * 3 * DM_MAXN; i += DM_THREADS) rsum[i] = 0.f;         // R . 0
     __syncthreads();
     const float *R = wimg + P.off_R, *O1 = wimg + P.off_O1, *O2 = wimg + P.off_O2, *O3 = wimg + P.off_O3, *O4 = wimg + P.off_O4;
     const float *Iw = wimg + P.off_I;      // per unit: 3 gates x 3 input weights (coarse units use 2)
@@ -206,7 +260,6 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dm_loop_kernel(const DmParams P
     const int c0 = cta * P.r2, nc = max(0, min(P.r2, Q - c0));
     const uint2 key = make_uint2((uint32_t)P.seed, (uint32_t)(P.seed >> 32));
     unsigned long long gen = 0;
-    float o[DM_MAXN];
     __shared__ long long prof_acc[16];
     long long prof_last = 0;
     const bool prof_on = P.prof != nullptr && tid == 0 && cta == 0;
@@ -219,7 +272,6 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dm_loop_kernel(const DmParams P
     }
 
     for (int64_t t = 0; t <= P.T; t++) {
-        const float *hcur = P.hidden + (size_t)(t & 1) * N * H;
         float *hnxt = P.hidden + (size_t)((t + 1) & 1) * N * H;
         // ---- fine sample of step t-1 (every CTA draws the same value; CTA 0 records it)
         if (prof_on) prof_last = clock64();
@@ -250,18 +302,8 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dm_loop_kernel(const DmParams P
         }
         DMARK(1);
         if (t == P.T) break;
-        // ---- A: R.hidden for owned units; coarse units update now
-        stage_cg(xbuf, hcur, N * H, tid);
-        __syncthreads();
-        for (int j = warp; j < 3 * nu; j += DM_WARPS) {
-            warp_rows<DM_MAXN>(R + (size_t)j * H, H, H, xbuf, H, N, lane, o);
-            if (lane == 0)
-                {
-#pragma unroll
-                for (int n = 0; n < DM_MAXN; n++) if (n < N) rsum[j * DM_MAXN + n] = o[n];
-            }        // j = u*3 + gate
-        }
-        __syncthreads();
+        // ---- A: coarse units update (R . hidden was formed in the barrier waits of E and F of the step before; xbuf still
+        //         holds that hidden state)
         for (int i = tid; i < nu * N; i += DM_THREADS) {
             const int u = i / N, n = i - u * N, unit = u0 + u;
             if (unit < S2) {
@@ -278,36 +320,22 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dm_loop_kernel(const DmParams P
         grid_barrier(P.gs, gen);
         DMARK(3);
         // ---- B: O1 + ReLU on hidden_coarse
-        stage_cg(xbuf, hnxt, N * H, tid);          // only [:, :S2] is new; the rest is ignored
+        stage_cg_2d(xbuf, H, hnxt, H, N, S2, tid);        // the coarse half; the fine half stays the previous step's for D
         __syncthreads();
-        for (int j = warp; j < na; j += DM_WARPS) {
-            warp_rows<DM_MAXN>(O1 + (size_t)j * S2, S2, S2, xbuf, H, N, lane, o);
-            if (lane == 0)
-                {
-#pragma unroll
-                for (int n = 0; n < DM_MAXN; n++) if (n < N) P.o1[(size_t)n * S2 + a0 + j] = fmaxf(o[n] + bO1[j], 0.f);
-            }
-        }
+        rows_split<NS, (NS >= 4 ? 2 : 1)>(O1, S2, S2, xbuf, H, na, N, warp, lane,
+                       [&](int j, int n, float v) { P.o1[(size_t)n * S2 + a0 + j] = fmaxf(v + bO1[j], 0.f); });
         DMARK(4);
         grid_barrier(P.gs, gen);
         DMARK(5);
         // ---- C: O2 -> coarse logits
-        stage_cg(xbuf, P.o1, N * S2, tid);
+        stage_cg(xo, P.o1, N * S2, tid);
         __syncthreads();
-        for (int j = warp; j < nc; j += DM_WARPS) {
-            warp_rows<DM_MAXN>(O2 + (size_t)j * S2, S2, S2, xbuf, S2, N, lane, o);
-            if (lane == 0)
-                {
-#pragma unroll
-                for (int n = 0; n < DM_MAXN; n++) if (n < N) P.lc[(size_t)n * Q + c0 + j] = o[n] + bO2[j];
-            }
-        }
+        rows_split<NS, (NS >= 4 ? 2 : 1)>(O2, S2, S2, xo, S2, nc, N, warp, lane, [&](int j, int n, float v) { P.lc[(size_t)n * Q + c0 + j] = v + bO2[j]; });
         DMARK(6);
         grid_barrier(P.gs, gen);
         DMARK(7);
         // ---- D: coarse sample (redundant), fine gates
         stage_cg(lrow, P.lc, N * Q, tid);
-        stage_cg(xbuf, hcur, N * H, tid);          // previous hidden_fine for the fine update
         __syncthreads();
         if (fast_draw) {
             dm_sample_block(lrow, Q, N, P.qc ? P.qc + ((size_t)t * P.Ntot + P.n0) * Q : nullptr, (size_t)Q, key, (uint32_t)t, (uint32_t)P.n0, 4u,
@@ -345,32 +373,24 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dm_loop_kernel(const DmParams P
         grid_barrier(P.gs, gen);
         DMARK(9);
         // ---- E: O3 + ReLU on hidden_fine
-        stage_cg(xbuf, hnxt, N * H, tid);
+        stage_cg_2d(xbuf + S2, H, hnxt + S2, H, N, S2, tid);     // xbuf = the whole new hidden state from here on
         __syncthreads();
-        for (int j = warp; j < na; j += DM_WARPS) {
-            warp_rows<DM_MAXN>(O3 + (size_t)j * S2, S2, S2, xbuf + S2, H, N, lane, o);
-            if (lane == 0)
-                {
-#pragma unroll
-                for (int n = 0; n < DM_MAXN; n++) if (n < N) P.o3[(size_t)n * S2 + a0 + j] = fmaxf(o[n] + bO3[j], 0.f);
-            }
-        }
+        rows_split<NS, (NS >= 4 ? 2 : 1)>(O3, S2, S2, xbuf + S2, H, na, N, warp, lane,
+                       [&](int j, int n, float v) { P.o3[(size_t)n * S2 + a0 + j] = fmaxf(v + bO3[j], 0.f); });
         DMARK(10);
-        grid_barrier(P.gs, gen);
+        // R . hidden for the NEXT step's gates, first half of the jobs, between this barrier's arrive and wait
+        dm_arrive(P.gs, gen);
+        rows_split<NS, (NS >= 4 ? 4 : NS)>(R, H, H, xbuf, H, 3 * nu, N, warp, lane, [&](int j, int n, float v) { rsum[j * DM_MAXN + n] = v; }, 0, 2);
+        dm_wait(P.gs, gen);
         DMARK(11);
         // ---- F: O4 -> fine logits
-        stage_cg(xbuf, P.o3, N * S2, tid);
+        stage_cg(xo, P.o3, N * S2, tid);
         __syncthreads();
-        for (int j = warp; j < nc; j += DM_WARPS) {
-            warp_rows<DM_MAXN>(O4 + (size_t)j * S2, S2, S2, xbuf, S2, N, lane, o);
-            if (lane == 0)
-                {
-#pragma unroll
-                for (int n = 0; n < DM_MAXN; n++) if (n < N) P.lf[(size_t)n * Q + c0 + j] = o[n] + bO4[j];
-            }
-        }
+        rows_split<NS, (NS >= 4 ? 2 : 1)>(O4, S2, S2, xo, S2, nc, N, warp, lane, [&](int j, int n, float v) { P.lf[(size_t)n * Q + c0 + j] = v + bO4[j]; });
         DMARK(12);
-        grid_barrier(P.gs, gen);
+        dm_arrive(P.gs, gen);                   // second half (j = u*3 + gate)
+        rows_split<NS, (NS >= 4 ? 4 : NS)>(R, H, H, xbuf, H, 3 * nu, N, warp, lane, [&](int j, int n, float v) { rsum[j * DM_MAXN + n] = v; }, 1, 2);
+        dm_wait(P.gs, gen);
         DMARK(13);
     }
     if (prof_on)
@@ -445,7 +465,7 @@ static int dm_pack(wrnn_dm_handle *h) {
     p.off_I = o;  o += p.upc * 9;
     p.off_b = o;  o += p.upc * 3 + 2 * p.r1 + 2 * p.r2;
     p.img_floats = (o + 3) & ~3;
-    h->smem_bytes = ((size_t)p.img_floats + (size_t)DM_MAXN * H + (size_t)p.upc * 3 * DM_MAXN + (size_t)DM_MAXN * Q + 3 * (size_t)DM_MAXN * 256 + 64) * sizeof(float);
+    h->smem_bytes = ((size_t)p.img_floats + (size_t)DM_MAXN * H + (size_t)DM_MAXN * S2 + (size_t)p.upc * 3 * DM_MAXN + (size_t)DM_MAXN * Q + 3 * (size_t)DM_MAXN * 256 + 64) * sizeof(float);
     if (h->smem_bytes > h->smem_optin) return dm_fail(h, WRNN_ERR_ARG, "deepmind model too large for the shared-memory resident kernel");
     std::vector<float> img((size_t)G * p.img_floats, 0.f);
     for (int c = 0; c < G; c++) {
@@ -585,7 +605,9 @@ int wrnn_dm_generate(wrnn_dm_handle *h, int64_t seq_len, int32_t n_seq, const fl
         DM_CUDA(h, cudaMemcpyAsync(ws + o_qc, q_coarse, nq * 4, cudaMemcpyHostToDevice, st));
         DM_CUDA(h, cudaMemcpyAsync(ws + o_qf, q_fine, nq * 4, cudaMemcpyHostToDevice, st));
     }
-    DM_CUDA(h, cudaFuncSetAttribute(dm_loop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_bytes));
+    const void *kernels[4] = {(const void *)dm_loop_kernel<1>, (const void *)dm_loop_kernel<2>, (const void *)dm_loop_kernel<4>,
+                              (const void *)dm_loop_kernel<8>};
+    for (const void *k : kernels) DM_CUDA(h, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_bytes));
     h->launches = 0;
     DM_CUDA(h, cudaEventRecord(h->ev[0], st));
     for (int n0 = 0; n0 < n_seq; n0 += DM_MAXN) {          // sequences are independent: groups of <= 8 per launch
@@ -613,7 +635,7 @@ int wrnn_dm_generate(wrnn_dm_handle *h, int64_t seq_len, int32_t n_seq, const fl
             P.prof = d_prof;
         }
         void *args[] = {(void *)&P};
-        DM_CUDA(h, cudaLaunchCooperativeKernel((const void *)dm_loop_kernel, dim3(h->num_sms), dim3(DM_THREADS), args, h->smem_bytes, st));
+        DM_CUDA(h, cudaLaunchCooperativeKernel(kernels[P.N <= 1 ? 0 : P.N <= 2 ? 1 : P.N <= 4 ? 2 : 3], dim3(h->num_sms), dim3(DM_THREADS), args, h->smem_bytes, st));
         h->launches++;
         int flag = 0;
         DM_CUDA(h, cudaMemcpyAsync(&flag, ws + 64, sizeof(int), cudaMemcpyDeviceToHost, st));
@@ -622,8 +644,8 @@ int wrnn_dm_generate(wrnn_dm_handle *h, int64_t seq_len, int32_t n_seq, const fl
             long long pr[16];
             cudaMemcpy(pr, d_prof, sizeof pr, cudaMemcpyDeviceToHost);
             cudaFree(d_prof);
-            static const char *site[14] = {"stage lf", "sample f", "A R.h + gates", "A barrier", "B O1", "B barrier", "C O2", "C barrier",
-                                           "D stage + sample c + gates", "D barrier", "E O3", "E barrier", "F O4", "F barrier"};
+            static const char *site[14] = {"stage lf", "sample f", "A gates", "A barrier", "B O1", "B barrier", "C O2", "C barrier",
+                                           "D stage + sample c + gates", "D barrier", "E O3", "E barrier + R.h 1/2", "F O4", "F barrier + R.h 2/2"};
             fprintf(stderr, "dm prof, %d sequences (clk per step, CTA 0)\n", P.N);
             for (int i = 0; i < 14; i++) fprintf(stderr, "  %-28s %7.0f\n", site[i], (double)pr[i] / (double)seq_len);
         }
