@@ -85,12 +85,15 @@ __device__ __forceinline__ void stage_vec(float *dst, const float *src, int n, i
 }
 
 __device__ __forceinline__ uint2 ld_word(const uint2 *p) {
-    uint2 v;
-    asm volatile("ld.relaxed.gpu.global.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p) : "memory");
-    return v;
+    // ONE 64-bit scalar access: single-copy atomic in the PTX memory model (a .v2.u32 access is modelled as two), so a
+    // word never shows a new tag beside an old value
+    unsigned long long v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return make_uint2((unsigned)v, (unsigned)(v >> 32));
 }
 __device__ __forceinline__ void st_word(uint2 *p, float value, unsigned tag) {
-    asm volatile("st.relaxed.gpu.global.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(__float_as_uint(value)), "r"(tag) : "memory");
+    const unsigned long long v = (unsigned long long)__float_as_uint(value) | ((unsigned long long)tag << 32);
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 // the value of a tagged word once its producer has stored it; a watchdog turns a lost hand-over into the abort flag
 __device__ __forceinline__ void spin_clocks(int n) {
