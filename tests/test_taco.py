@@ -124,6 +124,36 @@ def test_kernel_long_text():
 
 
 @pytest.mark.gpu
+def test_kernel_other_dims():
+    """lstm_dims 256 and 40 mel bands (2 LSTM units and fewer rows per CTA), r = 3."""
+    from wavernn_b200.binding import TacotronDecoder
+    from oracle import tacotron as otc
+    sd = synth.synth_taco_state_dict(lstm_dims=256, n_mels=40, seed=5)
+    enc = synth.synth_encoder_seq(75, seed=8)
+    dec = TacotronDecoder(lstm_dims=256, n_mels=40)
+    dec.load_weights(sd)
+    mel, attn = dec.decode(enc, steps=90, r=3)
+    o_mel, o_attn = otc.decode(sd, enc, steps=90, r=3)
+    assert mel.shape == o_mel.shape == (40, 90)
+    assert np.abs(mel - o_mel).max() < MEL_TOL and np.abs(attn - o_attn).max() < ATTN_TOL
+    dec.close()
+
+
+@pytest.mark.gpu
+def test_kernel_text_too_long_is_an_error_not_a_crash():
+    """More characters than the position owners' shared memory holds: a clear error, and the handle stays usable."""
+    from wavernn_b200.binding import TacotronDecoder
+    sd = synth.synth_taco_state_dict(seed=0)
+    dec = TacotronDecoder()
+    dec.load_weights(sd)
+    with pytest.raises((ValueError, RuntimeError), match='shared memory'):
+        dec.decode(synth.synth_encoder_seq(3000, seed=1), steps=4, r=2)
+    mel, attn = dec.decode(synth.synth_encoder_seq(20, seed=1), steps=8, r=2)
+    assert mel.shape == (80, 8) and attn.shape == (4, 20) and np.all(np.isfinite(mel))
+    dec.close()
+
+
+@pytest.mark.gpu
 def test_kernel_argument_errors():
     from wavernn_b200.binding import TacotronDecoder
     WrnnError = (ValueError, RuntimeError)
