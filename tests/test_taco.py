@@ -220,47 +220,9 @@ def test_adapter_on_gpu_with_a_stand_in_model():
     from oracle import tacotron as otc
     import wavernn_b200.tacotron as bt
 
+    from taco_standin import build_stand_in
     sd = synth.synth_taco_state_dict(seed=2)
-
-    class Bag(nn.Module):
-        pass
-
-    def bag_from(prefix):
-        root = Bag()
-        for k, v in sd.items():
-            if not k.startswith(prefix):
-                continue
-            parts = k[len(prefix):].split('.')
-            node = root
-            for name in parts[:-1]:
-                if not hasattr(node, name):
-                    setattr(node, name, Bag())
-                node = getattr(node, name)
-            node.register_parameter(parts[-1], nn.Parameter(torch.from_numpy(v.copy())))
-        return root
-
-    class Postnet(nn.Module):
-        def __init__(self):
-            super().__init__()
-            self.conv = nn.Conv1d(80, 64, 3, padding=1)
-
-        def forward(self, x):
-            return torch.tanh(self.conv(x)).transpose(1, 2)
-
-    class StandIn(nn.Module):
-        def __init__(self):
-            super().__init__()
-            torch.manual_seed(11)
-            self.encoder = nn.Embedding(70, 256)
-            self.encoder_proj = nn.Linear(256, 256, bias=False)
-            self.encoder_proj.weight.data.copy_(torch.from_numpy(sd['encoder_proj.weight']))
-            self.decoder = bag_from('decoder.')
-            self.postnet = Postnet()
-            self.post_proj = nn.Linear(64, 80, bias=False)
-            self.register_buffer('stop_threshold', torch.tensor(-3.4))
-            self.r = 2
-
-    model = StandIn().cuda()
+    model = build_stand_in(sd).cuda()
     x = [3 + (i * 7) % 60 for i in range(45)]
     mel, linear, attn = bt.generate(model, x, steps=80)
     enc = model.encoder(torch.as_tensor(x, device='cuda')).detach().cpu().numpy()
