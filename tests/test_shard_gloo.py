@@ -159,3 +159,54 @@ def test_combine_fold_samples_single_process_equals_oracle_tail():
         dims, mel, target, overlap, mu_law, samples, want = _sharded_case(mode)
         got = combine_fold_samples(samples, want.shape[0], target, overlap, dims.hop_length, dims.n_classes if mu_law else None)
         assert np.array_equal(got, want)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Tacotron decoder loop: sentences are independent, so N GPUs = N replicas, each decoding the
+# sentences `shard_utterances` gives it; nothing crosses ranks but the timing reduction.  The decoder here is the
+# CPU oracle standing in for the kernel (the host logic is what is under test).
+def _taco_worker(rank, world, port, q):
+    import numpy as np
+    from oracle import tacotron as otc
+    from wavernn_b200 import synth
+    os.environ['MASTER_ADDR'] = '127.0.0.1'
+    os.environ['MASTER_PORT'] = str(port)
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    try:
+        sd = synth.synth_taco_state_dict(seed=0)
+        lengths = [12, 30, 21]
+        mine = shard_utterances(len(lengths), world, rank)
+        out = {}
+        for i in mine:
+            mel, attn = otc.decode(sd, synth.synth_encoder_seq(lengths[i], seed=100 + i), steps=12, r=2)
+            out[i] = (mel.shape, float(np.abs(mel).sum()), attn.shape)
+        frames = sum(v[0][1] for v in out.values())
+        rate, ms_max = whole_job_rate(frames, [10.0 * len(mine)])
+        q.put((rank, out, rate, ms_max))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_world_size_2_gloo_sentences_shard_as_replicas():
+    import numpy as np
+    from oracle import tacotron as otc
+    from wavernn_b200 import synth
+    world, port = 2, _free_port()
+    ctx = mp.get_context('spawn')
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_taco_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = sorted(q.get(timeout=180) for _ in range(world))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    merged = {}
+    for _, out, rate, ms_max in got:
+        merged.update(out)
+        assert ms_max == [20.0]                                             # the slower rank decodes two sentences
+        assert rate == pytest.approx(3 * 12 / 0.020)                        # all frames of the job over that time
+    sd = synth.synth_taco_state_dict(seed=0)
+    for i, L in enumerate([12, 30, 21]):
+        mel, attn = otc.decode(sd, synth.synth_encoder_seq(L, seed=100 + i), steps=12, r=2)
+        assert merged[i] == (mel.shape, float(np.abs(mel).sum()), attn.shape)
