@@ -53,7 +53,7 @@ def test_text_to_waveform(tmp_path):
     assert m.shape == (1, 80, 120) and attention.shape == (60, 40)
     assert float(m.min()) >= 0.0 and float(m.max()) <= 1.0
     assert wav.shape == ((120 - 1) * dims.hop_length,) and wav.dtype == np.float64
-    assert np.all(np.isfinite(wav)) and np.abs(wav).max() <= 1.0 + 1e-6
+    assert np.all(np.isfinite(wav)) and np.abs(wav).max() <= 1.5          # samples clip at +-1, the cross-fade of two folds can reach sqrt(2)
     assert (tmp_path / 'a.wav').stat().st_size > 44
     # the same text and seed again: both loops are deterministic
     m2, _, wav2 = _speak(tts, voc, x, 120, tmp_path / 'b.wav', seed=7)
@@ -62,10 +62,16 @@ def test_text_to_waveform(tmp_path):
 
 
 def test_stop_rule_sets_the_waveform_length(tmp_path):
-    """Every frame counts as silent (threshold +1e9): the decoder kernel stops at the first t > 10 (seven steps of r = 2),
-    and the vocoder produces (14 - 1) * hop samples."""
+    """Every frame counts as silent (threshold +1e9): the decoder kernel stops at the first t > 10.  With r = 7 that is
+    t = 14, three steps = 21 frames, and the vocoder produces (21 - 1) * hop samples.  With r = 2 it is seven steps = 14
+    frames, fewer than the 20 hops `generate` fades out over (fatchord_version.py:256-258): the reference fails there with
+    a broadcast ValueError, the library with a ValueError that says so."""
     tts, voc, dims = _models(stop_threshold=1e9)
     x = [3 + (i * 7) % 60 for i in range(25)]
+    tts.r = 7
     m, attention, wav = _speak(tts, voc, x, 400, tmp_path / 'c.wav', seed=1)
-    assert m.shape == (1, 80, 14) and attention.shape == (7, 25)
-    assert wav.shape == (13 * dims.hop_length,)
+    assert m.shape == (1, 80, 21) and attention.shape == (3, 25)
+    assert wav.shape == (20 * dims.hop_length,)
+    tts.r = 2
+    with pytest.raises(ValueError, match='too short'):
+        _speak(tts, voc, x, 400, tmp_path / 'd.wav', seed=1)
