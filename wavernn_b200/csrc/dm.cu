@@ -87,12 +87,62 @@ __device__ __forceinline__ void rows_split(const float *W, int ldw, int K, const
     }
 }
 
+// R . hidden: a job = the THREE gate rows of one unit x GS sequences, so a staged activation chunk is read once for three
+// rows (the product is bound by shared-memory reads of the activations: one row per job re-reads them 21 times per CTA).
+// Per (row, sequence) the chunks are still taken lane, lane + 32, ... in ascending order and reduced by the same xor tree.
+template <int NS, int GS, typename F>
+__device__ __forceinline__ void unit_rows_split(const float *W, int K, const float *X, int ldx, int nunits, int N, int warp, int lane, F emit,
+                                                int part, int parts) {
+    constexpr int NG = NS / GS;
+    const int jobs = nunits * NG, jb = (int)((long long)jobs * part / parts), je = (int)((long long)jobs * (part + 1) / parts);
+    for (int job = jb + warp; job < je; job += DM_WARPS) {
+        const int u = job / NG, n0 = (job - u * NG) * GS;
+        if (n0 >= N) continue;
+        float acc[3][GS];
+#pragma unroll
+        for (int g = 0; g < 3; g++)
+#pragma unroll
+            for (int n = 0; n < GS; n++) acc[g][n] = 0.f;
+        const float4 *w4 = reinterpret_cast<const float4 *>(W + (size_t)u * 3 * K);
+        const int k4n = K >> 2;
+        for (int k4 = lane; k4 < k4n; k4 += 32) {
+            float4 w[3];
+#pragma unroll
+            for (int g = 0; g < 3; g++) w[g] = w4[g * k4n + k4];
+#pragma unroll
+            for (int n = 0; n < GS; n++) {
+                const float4 x = reinterpret_cast<const float4 *>(X + (size_t)(n0 + n) * ldx)[k4];
+#pragma unroll
+                for (int g = 0; g < 3; g++) {
+                    acc[g][n] = fmaf(w[g].x, x.x, acc[g][n]);
+                    acc[g][n] = fmaf(w[g].y, x.y, acc[g][n]);
+                    acc[g][n] = fmaf(w[g].z, x.z, acc[g][n]);
+                    acc[g][n] = fmaf(w[g].w, x.w, acc[g][n]);
+                }
+            }
+        }
+#pragma unroll
+        for (int g = 0; g < 3; g++)
+#pragma unroll
+            for (int n = 0; n < GS; n++) {
+#pragma unroll
+                for (int o = 16; o >= 1; o >>= 1) acc[g][n] += __shfl_xor_sync(0xffffffffu, acc[g][n], o);
+                if (lane == 0 && n0 + n < N) emit(u * 3 + g, n0 + n, acc[g][n]);
+            }
+    }
+}
+
 // rows x cols floats, row stride ld (global) / lds (shared), cols % 4 == 0
 __device__ __forceinline__ void stage_cg_2d(float *dst, int lds, const float *src, int ld, int rows, int cols, int tid) {
-    const int c4 = cols >> 2;
-    for (int i = tid; i < rows * c4; i += DM_THREADS) {
-        const int r = i / c4, c = i - r * c4;
-        reinterpret_cast<float4 *>(dst + (size_t)r * lds)[c] = __ldcg(reinterpret_cast<const float4 *>(src + (size_t)r * ld) + c);
+    const int c4 = cols >> 2, n4 = rows * c4;
+    for (int base = 0; base < n4; base += 2 * DM_THREADS) {          // two loads in flight per thread: one L2 round trip for 8 x 448
+        const int i0 = base + tid, i1 = i0 + DM_THREADS;
+        const int r0 = i0 / c4, q0 = i0 - r0 * c4, r1 = i1 / c4, q1 = i1 - r1 * c4;
+        float4 v0, v1;
+        if (i0 < n4) v0 = __ldcg(reinterpret_cast<const float4 *>(src + (size_t)r0 * ld) + q0);
+        if (i1 < n4) v1 = __ldcg(reinterpret_cast<const float4 *>(src + (size_t)r1 * ld) + q1);
+        if (i0 < n4) reinterpret_cast<float4 *>(dst + (size_t)r0 * lds)[q0] = v0;
+        if (i1 < n4) reinterpret_cast<float4 *>(dst + (size_t)r1 * lds)[q1] = v1;
     }
 }
 // the grid barrier in two halves: work that needs nothing from the other CTAs goes between arrive and wait
@@ -328,7 +378,7 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dm_loop_kernel(const DmParams P
         grid_barrier(P.gs, gen);
         DMARK(5);
         // ---- C: O2 -> coarse logits
-        stage_cg(xo, P.o1, N * S2, tid);
+        stage_cg_2d(xo, S2, P.o1, S2, N, S2, tid);
         __syncthreads();
         rows_split<NS, (NS >= 4 ? 2 : 1)>(O2, S2, S2, xo, S2, nc, N, warp, lane, [&](int j, int n, float v) { P.lc[(size_t)n * Q + c0 + j] = v + bO2[j]; });
         DMARK(6);
@@ -380,16 +430,16 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dm_loop_kernel(const DmParams P
         DMARK(10);
         // R . hidden for the NEXT step's gates, first half of the jobs, between this barrier's arrive and wait
         dm_arrive(P.gs, gen);
-        rows_split<NS, (NS >= 4 ? 4 : NS)>(R, H, H, xbuf, H, 3 * nu, N, warp, lane, [&](int j, int n, float v) { rsum[j * DM_MAXN + n] = v; }, 0, 2);
+        unit_rows_split<NS, (NS >= 4 ? 4 : NS)>(R, H, xbuf, H, nu, N, warp, lane, [&](int j, int n, float v) { rsum[j * DM_MAXN + n] = v; }, 0, 2);
         dm_wait(P.gs, gen);
         DMARK(11);
         // ---- F: O4 -> fine logits
-        stage_cg(xo, P.o3, N * S2, tid);
+        stage_cg_2d(xo, S2, P.o3, S2, N, S2, tid);
         __syncthreads();
         rows_split<NS, (NS >= 4 ? 2 : 1)>(O4, S2, S2, xo, S2, nc, N, warp, lane, [&](int j, int n, float v) { P.lf[(size_t)n * Q + c0 + j] = v + bO4[j]; });
         DMARK(12);
         dm_arrive(P.gs, gen);                   // second half (j = u*3 + gate)
-        rows_split<NS, (NS >= 4 ? 4 : NS)>(R, H, H, xbuf, H, 3 * nu, N, warp, lane, [&](int j, int n, float v) { rsum[j * DM_MAXN + n] = v; }, 1, 2);
+        unit_rows_split<NS, (NS >= 4 ? 4 : NS)>(R, H, xbuf, H, nu, N, warp, lane, [&](int j, int n, float v) { rsum[j * DM_MAXN + n] = v; }, 1, 2);
         dm_wait(P.gs, gen);
         DMARK(13);
     }
