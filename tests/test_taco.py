@@ -146,7 +146,7 @@ def test_kernel_text_too_long_is_an_error_not_a_crash():
     sd = synth.synth_taco_state_dict(seed=0)
     dec = TacotronDecoder()
     dec.load_weights(sd)
-    with pytest.raises((ValueError, RuntimeError), match='shared memory'):
+    with pytest.raises((ValueError, RuntimeError), match='shared memory|512 characters'):
         dec.decode(synth.synth_encoder_seq(3000, seed=1), steps=4, r=2)
     mel, attn = dec.decode(synth.synth_encoder_seq(20, seed=1), steps=8, r=2)
     assert mel.shape == (80, 8) and attn.shape == (4, 20) and np.all(np.isfinite(mel))

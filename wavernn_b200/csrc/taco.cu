@@ -4,16 +4,19 @@
 // cooperative kernel: every SM keeps its rows of all decoder matrices (20 MB fp32 in total) in shared memory for the
 // whole utterance, the layers hand small vectors to one another through L2 and grid barriers.
 //
-// Seven barriers per decoder step instead of one per layer, by algebra on the host (compositions formed in double):
+// Seven dependent stages per decoder step instead of one per layer, by algebra on the host (compositions formed in double)
+// and in the prologue (per-position projections), handed over as tagged 8-byte words polled by the consumers:
 //   A  mel frames of the step before AND prenet.fc1 of this step: fc1(mel[:, r-1]) = (W_fc1 . W_mel[last frame]) . x3 + b
-//   B  prenet.fc2 (+ ReLU); the stop rule on the frames A published; location features of the positions a CTA owns
+//   B  prenet.fc2 (+ ReLU)
 //   C  attention GRU cell (input [context | prenet], hidden)                                             (:236-238)
 //   D  processed query W . h_attn + b                                                                     (:190)
-//   E  energies v . tanh(query + enc_proj + loc) and sigmoid for the positions a CTA owns, and its PARTIAL context
-//      sum_l sigmoid(u_l) enc[l] and partial sum (context = sum of partials / sum of sums: no barrier between the
-//      normalisation and the context product)                                                           (:196-205,244)
-//   F  rnn_input and LSTM 1 at once: gates = (W_ih1 . W_rnn_input) . [context | h_attn] + W_hh1 . h1; x rows beside  (:256-262)
+//   E  energies v . tanh(query + enc_proj + loc) and sigmoid for the positions a CTA owns                (:196-205)
+//   F  rnn_input and LSTM 1 at once: gates = (W_ih1 . W_rnn_input) . [context | h_attn] + W_hh1 . h1; x rows beside (:256-262)
 //   G  LSTM 2 on x + h1; publishes x3 = x + h1 + h2 for A                                                (:270-277)
+// The context vector (:244) is never formed: it enters F's rows and C's rows only through products with fixed rows, and
+// context = sum_l a_l enc[l], so W[row] . context = sum_l a_l (W[row][context columns] . enc[l]) with the bracket a constant
+// of the utterance, built once per call.  E therefore hands over L attention weights, not 256-wide partial contexts, and
+// the step's one grid barrier carries no data (it only bounds the skew between CTAs; its counter is read off the chain).
 // Dropout and zoneout are training-only (eval mode in generate, :423).
 #include <math.h>
 #include <stdio.h>
@@ -41,13 +44,14 @@ struct TacoParams {
     int PP, pc0, PC;                               // positions per owner CTA, first owner CTA, owners in use
     int img_floats;
     int off_A, off_bA, off_B, off_bB, off_C, off_bC, off_D, off_bD, off_F, off_bF, off_G, off_bG, off_E;
-    int sm_vec, sm_ctx, sm_misc;                   // smem float offsets behind the image
+    int sm_vec, sm_misc;                           // smem float offsets behind the image
+    int Lp, sm_pf, sm_pc;                          // padded text length; per-position projections of the context columns (below)
     const float *image;                            // [G][img_floats]
     const float *common;                           // conv w [32][2][31] (+pad to 2048) | v [D] | L.weight [D][32] | L.bias [D]
     const float *enc, *encp;                       // [L][D]
     uint2 *p1, *p2, *ha, *pq, *x2, *h1, *h2, *x3, *att_g, *cum_g;      // tagged words {value, 1 + producing step}
     uint2 *melf;                                   // frames of the last step, tagged like the rest (read by the stop rule)
-    float *part_ctx, *part_sum;
+    uint2 *s_g;                                    // [L] sigmoid(u_l) of this step, tagged
     float *mel_out, *attn_out;
     int *n_iter;
     int d_first, d_poll;                           // clocks before the first look at a fresh vector / between looks
@@ -151,7 +155,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
     extern __shared__ __align__(16) float smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, cta = blockIdx.x;
     const int D = P.D, H = P.H, r = P.r, L = P.L;
-    float *img = smem, *vec = smem + P.sm_vec, *ctx = smem + P.sm_ctx, *misc = smem + P.sm_misc;
+    float *img = smem, *vec = smem + P.sm_vec, *misc = smem + P.sm_misc;
+    float *PF = smem + P.sm_pf, *PCt = smem + P.sm_pc;      // [5 upl][Lp], [3 upc][Lp]: W[row][context columns] . enc[l]
     float *gsum = misc;                 // [<= 32] dot products of a stage
     float *c1 = misc + 32, *c2 = c1 + P.upl;            // LSTM cell states of the owned units
     for (int i = tid; i < P.img_floats / 4; i += TC_THREADS)
@@ -170,7 +175,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
     float *sv = conv + TC_FILT * P.PP;                   // [PP] sigmoid(u)
     float *cumv = sv + P.PP;                             // [PP] cumulative attention
     float *red = cumv + P.PP;                            // [PP][8]
-    float *psum_s = misc + 32 + 2 * P.upl, *chalf = psum_s + 160;      // [<= 148] partial sums, [D] second half of the context sum
+    float *wsum_s = misc + 32 + 2 * P.upl;               // [16] per-warp sums of sigmoid(u)
     const int a = tid & 255, half = tid >> 8;            // energy thread = (attention dim a, position parity); D == 256
     float lw[TC_FILT], lb = 0.f, va = 0.f;
     if (owner && nl > 0) {
@@ -186,7 +191,6 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
         lb = P.common[2048 + D + D * TC_FILT + a];
         for (int p = half; p < nl; p += 2) ploc[(size_t)p * D + a] = lb;      // step 0: cumulative = attention = 0
     }
-    for (int i = tid; i < D; i += TC_THREADS) ctx[i] = 0.f;
     for (int i = tid; i < 2 * P.upl; i += TC_THREADS) c1[i] = 0.f;
     __syncthreads();
 
@@ -201,6 +205,30 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
     const int KC = 2 * D + P.P2;        // GRU: [context | prenet | hidden]
     const int KF = 2 * D + H;           // LSTM 1: [context | h_attn | h1]
     const int nmel = P.M * r;
+    // The context vector is never formed.  It enters LSTM 1, the x rows and the attention GRU only through products with
+    // fixed rows, and context = sum_l a_l enc[l], so W[row] . context = sum_l a_l (W[row][context columns] . enc[l]): the
+    // bracket is a per-utterance constant.  Built here once per call (26 rows x L dots of 256), it turns the hand-over
+    // "256-wide partial contexts of 20 owners, behind a grid barrier" into "L attention weights as tagged words".
+    const int Lp = P.Lp, unitC_ = 2 * KC + (D + P.P2) + D;
+    for (int i = warp; i < (5 * nu + 3 * ng) * L; i += TC_WARPS) {
+        const int row = i / L, l = i - row * L;
+        const float *wrow;
+        float *dst;
+        if (row < 4 * nu) { wrow = WF + (size_t)row * KF; dst = PF + (size_t)row * Lp; }
+        else if (row < 5 * nu) { wrow = WF + (size_t)4 * P.upl * KF + (size_t)(row - 4 * nu) * 2 * D; dst = PF + (size_t)row * Lp; }
+        else {
+            const int g = row - 5 * nu, j = g / 3, q = g - j * 3;
+            wrow = WC + (size_t)j * unitC_ + (q < 2 ? (size_t)q * KC : (size_t)2 * KC);
+            dst = PCt + (size_t)g * Lp;
+        }
+        const float d = warp_dot(wrow, P.enc + (size_t)l * D, D >> 2, lane);
+        if (lane == 0) dst[l] = d;
+    }
+    for (int i = tid; i < 5 * P.upl * (Lp - L); i += TC_THREADS) PF[(size_t)(i / (Lp - L)) * Lp + L + i % (Lp - L)] = 0.f;
+    for (int i = tid; i < 3 * P.upc * (Lp - L); i += TC_THREADS) PCt[(size_t)(i / (Lp - L)) * Lp + L + i % (Lp - L)] = 0.f;
+    float *gctx = wsum_s + 16;          // [3 upc] context part of the GRU rows (r, z, n_i) for the NEXT step
+    for (int i = tid; i < 3 * P.upc; i += TC_THREADS) gctx[i] = 0.f;
+    __syncthreads();
     unsigned long long gen = 0;
     int n_done = 0;
     __shared__ long long prof_acc[32];
@@ -297,19 +325,16 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
         __syncthreads();
         TMARK(3);
         // ---- C: attention GRU cell
-        if (ng > 0) {
-            if (tid < D) vec[tid] = ctx[tid];
-            fetch(P.p2, P.P2, tag_now, vec + D);
-        }
+        if (ng > 0) fetch(P.p2, P.P2, tag_now, vec);
         __syncthreads();
         TMARK(4);
-        for (int w = warp; w < 4 * ng; w += TC_WARPS) {           // the hidden-state columns were formed ahead (ghh)
+        for (int w = warp; w < 4 * ng; w += TC_WARPS) {           // hidden-state and context columns were formed ahead (ghh, gctx)
             const int j = w >> 2, q = w & 3;
             const float *row = WC + (size_t)j * (2 * KC + (D + P.P2) + D);
             if (q == 3) {
                 if (lane == 0) gsum[w] = ghh[w] + bC[w];
             } else {
-                const float d = warp_dot(row + (size_t)q * KC, vec, (D + P.P2) >> 2, lane);
+                const float d = warp_dot(row + (size_t)q * KC + D, vec, P.P2 >> 2, lane) + gctx[j * 3 + q];      // prenet columns
                 if (lane == 0) gsum[w] = q < 2 ? sigmoidf_acc(d + ghh[w] + bC[w]) : d + bC[w];
             }
         }
@@ -336,32 +361,25 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
         // ---- in the shadow of E (position owners only) and of the barrier: every product whose input is known by now.
         //      W_hh1 . h1 and W_hh2 . h2 (states of the step before), the h_attn columns of LSTM 1's composed gate rows
         //      and of the x rows, and W_hh . h_attn of the attention GRU for the NEXT step
+        uint2 early_s = make_uint2(0u, 0u);
         auto shadow = [&]() {
             if (nu == 0 && ng == 0) return;
             fetch3(P.h1 + (size_t)cur * H, nu > 0 ? H : 0, tag_prev, vec, P.h2 + (size_t)cur * H, nu > 0 ? H : 0, tag_prev, vec + H,
                    P.ha + (size_t)nxt * D, D, tag_now, vec2);
             __syncthreads();
-            const int j1 = 4 * nu, j2 = 8 * nu, j3 = 12 * nu, j4 = 13 * nu, j5 = j4 + 4 * ng;
-            for (int w = warp; w < j5; w += TC_WARPS) {
+            const int j1 = 4 * nu, j2 = 8 * nu, j3 = 12 * nu;
+            for (int w = warp; w < j3; w += TC_WARPS) {
+                // a first look at this step's attention weights goes out ahead of the last round of jobs: F validates it
+                if (w + TC_WARPS >= j3 && tid < L) early_s = ld_word(P.s_g + tid);
                 if (w < j1) {
                     const float d = warp_dot(WF + (size_t)w * KF + 2 * D, vec, H >> 2, lane);
                     if (lane == 0) hh1s[w] = d;
                 } else if (w < j2) {
                     const float d = warp_dot(WG + (size_t)(w - j1) * 2 * H + H, vec + H, H >> 2, lane);
                     if (lane == 0) hh2s[w - j1] = d;
-                } else if (w < j3) {
+                } else {
                     const float d = warp_dot(WF + (size_t)(w - j2) * KF + D, vec2, D >> 2, lane);
                     if (lane == 0) fha[w - j2] = d;
-                } else if (w < j4) {
-                    const float d = warp_dot(WF + (size_t)4 * P.upl * KF + (size_t)(w - j3) * 2 * D + D, vec2, D >> 2, lane);
-                    if (lane == 0) fha[4 * nu + (w - j3)] = d;
-                } else {
-                    const int g = w - j4, j = g >> 2, q = g & 3;
-                    if (q != 2) {
-                        const float *row = WC + (size_t)j * (2 * KC + (D + P.P2) + D);
-                        const float d = warp_dot(q < 2 ? row + (size_t)q * KC + D + P.P2 : row + 2 * KC + D + P.P2, vec2, D >> 2, lane);
-                        if (lane == 0) ghh[g] = d;
-                    }
                 }
             }
             __syncthreads();
@@ -396,49 +414,35 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
             if (tid < nl) {
                 float e = 0.f;
                 for (int w = 0; w < 8; w++) e += red[tid * 8 + w];
-                sv[tid] = sigmoidf_acc(e);
-            }
-            __syncthreads();
-            if (tid < D) {
-                float acc = 0.f;
-                for (int p = 0; p < nl; p++) acc = fmaf(sv[p], enc_s[(size_t)p * D + tid], acc);
-                P.part_ctx[(size_t)pi * D + tid] = acc;
-            } else if (tid == D) {
-                float s = 0.f;
-                for (int p = 0; p < nl; p++) s += sv[p];
-                P.part_sum[pi] = s;
+                const float sg = sigmoidf_acc(e);
+                sv[tid] = sg;
+                st_word(P.s_g + l0 + tid, sg, tag_now);
             }
         }
         if (nl > 0) {
-            grid_arrive(P.gs, gen, true);
+            grid_arrive(P.gs, gen, false);
             shadow();
         }
         TMARK(8);
-        grid_wait(P.gs, gen);
+        // ---- F: the stop rule on the frames of step it-1 (:455: all below the threshold and t > 10); the attention
+        //         weights arrive; rnn_input + LSTM 1 through the per-position projections; owners normalise their scores
+        float inv_total = 0.f;
         TMARK(9);
-        // ---- F: the stop rule on the frames of step it-1 (:455: all below the threshold and t > 10; they were complete
-        //         before the barrier); context = sum of partials / sum of sums; rnn_input + LSTM 1; owners normalise
         {
             const bool check = it > 0 && (it - 1) * r > 10;
             uint2 mw[4];                                        // first looks now, validated after the other loads are out
 #pragma unroll
             for (int q = 0; q < 4; q++)
                 mw[q] = (check && tid + q * TC_THREADS < nmel) ? ld_word(P.melf + tid + q * TC_THREADS) : make_uint2(0xff800000u, tag_now);
-            const float ps = tid < P.PC ? __ldcg(P.part_sum + tid) : 0.f;
-            float acc = 0.f;
-            for (int p0 = half; p0 < P.PC; p0 += 20) {          // (d, half) sums every second partial, ten loads in flight
-                float t10[10];
-#pragma unroll
-                for (int q = 0; q < 10; q++) t10[q] = (p0 + 2 * q < P.PC) ? __ldcg(P.part_ctx + (size_t)(p0 + 2 * q) * D + a) : 0.f;
-#pragma unroll
-                for (int q = 0; q < 10; q++) acc += t10[q];
-            }
-            // sum of the partial sums: per warp by shuffles, then across the warps in order
-            float wsum = ps;
+            // the attention weights before normalisation: one tagged word per position, one look per thread
+            float sg = 0.f;
+            if (tid < L) sg = early_s.y == tag_now ? __uint_as_float(early_s.x) : wait_word(P.s_g + tid, tag_now, P.gs.abort_flag, P.d_poll);
+            if (tid < Lp) vec[tid] = sg;
+            // their sum: per warp by the xor tree, then across the warps in order (the same bits in every CTA)
+            float wsum = sg;
 #pragma unroll
             for (int o = 16; o >= 1; o >>= 1) wsum += __shfl_xor_sync(0xffffffffu, wsum, o);
-            if (lane == 0) psum_s[warp] = wsum;
-            if (half) chalf[a] = acc;
+            if (lane == 0) wsum_s[warp] = wsum;
             int ok = check ? 1 : 0;
 #pragma unroll
             for (int q = 0; q < 4; q++) {
@@ -449,12 +453,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
             for (int i = tid + 4 * TC_THREADS; check && i < nmel; i += TC_THREADS) ok &= (wait_word(P.melf + i, tag_now, P.gs.abort_flag) < P.thr) ? 1 : 0;
             if (__syncthreads_and(ok)) break;
             float total = 0.f;
-            for (int w = 0; w < (P.PC + 31) / 32; w++) total += psum_s[w];
-            if (!half) {
-                const float c = (acc + chalf[a]) / total;
-                ctx[a] = c;
-                vec[a] = c;
-            }
+            for (int w = 0; w < (L + 31) / 32; w++) total += wsum_s[w];
+            inv_total = 1.f / total;
             if (tid < nl) {
                 const float att = sv[tid] / total;
                 const float cu = cumv[tid] + att;
@@ -466,13 +466,25 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
         }
         __syncthreads();
         TMARK(10);
-        for (int w = warp; w < 5 * nu; w += TC_WARPS) {
-            if (w < 4 * nu) {                                                   // w = unit * 4 + gate; context columns only
-                const float d = warp_dot(WF + (size_t)w * KF, vec, D >> 2, lane);
+        for (int w = warp; w < 5 * nu + 6 * ng; w += TC_WARPS) {
+            if (w >= 5 * nu + 3 * ng) {                                         // W_hh . h_attn of the GRU rows (r, z, n) for the next step
+                const int g = w - 5 * nu - 3 * ng, j = g / 3, q = g - j * 3;
+                const float *row = WC + (size_t)j * (2 * KC + (D + P.P2) + D);
+                const float d = warp_dot(q < 2 ? row + (size_t)q * KC + D + P.P2 : row + 2 * KC + D + P.P2, vec2, D >> 2, lane);
+                if (lane == 0) ghh[j * 4 + (q < 2 ? q : 3)] = d;
+                continue;
+            }
+            if (w >= 5 * nu) {                                                  // context part of the GRU rows for the next step
+                const float d = warp_dot(PCt + (size_t)(w - 5 * nu) * Lp, vec, Lp >> 2, lane) * inv_total;
+                if (lane == 0) gctx[w - 5 * nu] = d;
+                continue;
+            }
+            const float d = warp_dot(PF + (size_t)w * Lp, vec, Lp >> 2, lane) * inv_total;       // W[row] . context
+            if (w < 4 * nu) {                                                   // w = unit * 4 + gate
                 if (lane == 0) gsum[w] = lstm_act(w, d + fha[w] + hh1s[w] + bF[(w >> 2) * 5 + (w & 3)]);
-            } else {
-                const float d = warp_dot(WF + (size_t)4 * P.upl * KF + (size_t)(w - 4 * nu) * 2 * D, vec, D >> 2, lane);
-                if (lane == 0) gsum[w] = d + fha[w] + bF[(w - 4 * nu) * 5 + 4];
+            } else {                                                            // x row: its h_attn columns here too
+                const float dh = warp_dot(WF + (size_t)4 * P.upl * KF + (size_t)(w - 4 * nu) * 2 * D + D, vec2, D >> 2, lane);
+                if (lane == 0) gsum[w] = d + dh + bF[(w - 4 * nu) * 5 + 4];
             }
         }
         __syncthreads();
@@ -485,7 +497,21 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
         __syncthreads();
         TMARK(11);
         // ---- G: LSTM 2 on x + h1; position owners convolve [cumulative | attention] for the next step
+        // the step's grid barrier carries no data any more (every hand-over is self-validating); it only bounds the skew
+        // between CTAs.  Its counter is read here, the read in flight while x2 arrives, and is complete by now in practice
+        unsigned long long arrived = 0;
+        if (tid == 0) arrived = ld_acquire_u64(P.gs.counter);
         fetch(P.x2, nu > 0 ? H : 0, tag_now, vec);
+        if (tid == 0 && arrived < gen * gridDim.x) {
+            const long long t0 = clock64();
+            unsigned spins = 0;
+            while (ld_acquire_u64(P.gs.counter) < gen * gridDim.x) {
+                if ((++spins & 63u) == 0u && (clock64() - t0 > 4000000000ll || ld_volatile_s32(P.gs.abort_flag))) {
+                    atomicExch(P.gs.abort_flag, 1);
+                    break;
+                }
+            }
+        }
         if (nl > 0) {
             const int span = nl + 2 * TC_HALO;
             for (int i = tid; i < 2 * span; i += TC_THREADS) {
@@ -833,9 +859,12 @@ int wrnn_taco_decode(wrnn_taco_handle *h, const float *enc_seq, int32_t L, int32
     P.PC = (L + P.PP - 1) / P.PP;
     const int e_floats = 3 * P.PP * D + 2048 + 2 * ((P.PP + 2 * TC_HALO + 3) & ~3) + TC_FILT * P.PP + 2 * P.PP + 8 * P.PP + 8;
     P.off_E = disjoint ? P.off_F : P.img_floats;
-    P.sm_vec = std::max(P.img_floats, (P.off_E + e_floats + 3) & ~3);
-    P.sm_ctx = P.sm_vec + std::max(2 * D + H, 2 * H);
-    P.sm_misc = P.sm_ctx + D;
+    P.Lp = (L + 3) & ~3;
+    P.sm_pf = std::max(P.img_floats, (P.off_E + e_floats + 3) & ~3);
+    P.sm_pc = P.sm_pf + 5 * P.upl * P.Lp;
+    P.sm_vec = P.sm_pc + 3 * P.upc * P.Lp;
+    P.sm_misc = P.sm_vec + std::max(std::max(2 * D + H, 2 * H), P.Lp);
+    if (L > TC_THREADS) return taco_fail(h, WRNN_ERR_ARG, "more than 512 characters: the attention weights of a step are one word per thread");
     const size_t smem_bytes = ((size_t)P.sm_misc + 32 + 2 * P.upl + 160 + D + H + 13 * P.upl + 5 * P.upc + 12) * sizeof(float);
     if (smem_bytes > h->smem_optin) {
         char b[256];
@@ -846,8 +875,8 @@ int wrnn_taco_decode(wrnn_taco_handle *h, const float *enc_seq, int32_t L, int32
     // workspace: sync[128 B] | state vectors | n_iter | enc, enc_proj | mel_out [M][cap] | attn_out [max_iter][L]
     size_t off = 128;
     auto take = [&](size_t floats) { const size_t o = off; off += ((floats * 4 + 127) & ~(size_t)127); return o; };
-    const size_t o_p1 = take(2 * P.P1), o_p2 = take(2 * P.P2), o_ha = take(4 * D), o_pq = take(2 * D), o_pc = take((size_t)owners * D),
-                 o_ps = take(owners), o_x2 = take(2 * H), o_h1 = take(4 * H), o_h2 = take(4 * H), o_x3 = take(2 * H),
+    const size_t o_p1 = take(2 * P.P1), o_p2 = take(2 * P.P2), o_ha = take(4 * D), o_pq = take(2 * D), o_sg = take(2 * (size_t)L),
+                 o_x2 = take(2 * H), o_h1 = take(4 * H), o_h2 = take(4 * H), o_x3 = take(2 * H),
                  o_melf = take(2 * (size_t)M * TC_MAXR), o_att = take(2 * (size_t)L), o_cum = take(2 * (size_t)L), o_n = take(1);
     const size_t state_end = off;
     const size_t o_enc = take((size_t)L * D), o_encp = take((size_t)L * D), o_mel = take((size_t)M * P.cap),
@@ -864,7 +893,7 @@ int wrnn_taco_decode(wrnn_taco_handle *h, const float *enc_seq, int32_t L, int32
     TC_CUDA(h, cudaMemcpyAsync(ws + o_enc, enc_seq, (size_t)L * D * 4, cudaMemcpyHostToDevice, st));
     P.image = h->image; P.common = h->common; P.enc = F(o_enc); P.encp = F(o_encp);
     auto U = [&](size_t o) { return (uint2 *)(ws + o); };
-    P.p1 = U(o_p1); P.p2 = U(o_p2); P.ha = U(o_ha); P.pq = U(o_pq); P.part_ctx = F(o_pc); P.part_sum = F(o_ps);
+    P.p1 = U(o_p1); P.p2 = U(o_p2); P.ha = U(o_ha); P.pq = U(o_pq); P.s_g = U(o_sg);
     P.x2 = U(o_x2); P.h1 = U(o_h1); P.h2 = U(o_h2); P.x3 = U(o_x3); P.melf = U(o_melf); P.att_g = U(o_att); P.cum_g = U(o_cum);
     P.mel_out = F(o_mel); P.attn_out = F(o_attn); P.n_iter = (int *)(ws + o_n);
     P.gs.counter = (unsigned long long *)ws;
