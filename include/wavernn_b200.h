@@ -232,7 +232,8 @@ const char *wrnn_taco_last_error(const wrnn_taco_handle *h);
 int wrnn_taco_load_weights(wrnn_taco_handle *h, const wrnn_tensor *tensors, int32_t n);
 /* The decoder loop of Tacotron.generate (models/tacotron.py:438-465) for one utterance: enc_seq (L, decoder_dims) is
  * the CBHG encoder's output (host memory), 1 <= L <= 512 characters (the attention weights of a step travel one word per
- * thread; longer texts return WRNN_ERR_ARG), r the reduction factor (`model.r`), steps the frame budget
+ * thread; longer texts return WRNN_ERR_ARG, and so does a text whose per-position tables do not fit the shared memory
+ * beside the weights: about 500 characters at r = 7, fewer at larger r), r the reduction factor (`model.r`), steps the frame budget
  * (`for t in range(0, steps, r)`), stop_threshold the model's buffer of that name (a step whose r frames are all below
  * it ends the loop once t > 10, :455).  Outputs (host memory): mel (n_mels, n_iter * r) row-major, capacity
  * n_mels * ceil(steps / r) * r floats; attn (n_iter, L), capacity ceil(steps / r) * L floats; *n_iter = decoder steps
