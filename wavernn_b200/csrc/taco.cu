@@ -84,10 +84,6 @@ __device__ __forceinline__ float warp_dot(const float *w, const float *x, int k4
     return a0;
 }
 
-__device__ __forceinline__ void stage_vec(float *dst, const float *src, int n, int tid) {     // written by other CTAs: L2 loads
-    for (int i = tid; i < (n >> 2); i += TC_THREADS) reinterpret_cast<float4 *>(dst)[i] = __ldcg(reinterpret_cast<const float4 *>(src) + i);
-}
-
 __device__ __forceinline__ uint2 ld_word(const uint2 *p) {
     // ONE 64-bit scalar access: single-copy atomic in the PTX memory model (a .v2.u32 access is modelled as two), so a
     // word never shows a new tag beside an old value
@@ -167,7 +163,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
     const int pi = cta - P.pc0;
     const bool owner = pi >= 0 && pi < P.PC;
     const int l0 = owner ? pi * P.PP : 0, nl = owner ? max(0, min(P.PP, L - l0)) : 0;
-    float *encp_s = smem + P.off_E, *enc_s = encp_s + (size_t)P.PP * D, *ploc = enc_s + (size_t)P.PP * D;
+    float *encp_s = smem + P.off_E, *ploc = encp_s + (size_t)P.PP * D;
     float *cw = ploc + (size_t)P.PP * D;                 // [32][2][31] padded to 2048
     float *loc = cw + 2048;                              // [2][PP + 30]
     const int LS = (P.PP + 2 * TC_HALO + 3) & ~3;        // row stride of loc: what follows stays 16-byte aligned
@@ -179,10 +175,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) taco_loop_kernel(const TacoPara
     const int a = tid & 255, half = tid >> 8;            // energy thread = (attention dim a, position parity); D == 256
     float lw[TC_FILT], lb = 0.f, va = 0.f;
     if (owner && nl > 0) {
-        for (int i = tid; i < nl * D; i += TC_THREADS) {
-            encp_s[i] = P.encp[(size_t)l0 * D + i];
-            enc_s[i] = P.enc[(size_t)l0 * D + i];
-        }
+        for (int i = tid; i < nl * D; i += TC_THREADS) encp_s[i] = P.encp[(size_t)l0 * D + i];
         for (int i = tid; i < TC_FILT * 2 * TC_KS; i += TC_THREADS) cw[i] = P.common[i];
         for (int i = tid; i < P.PP; i += TC_THREADS) cumv[i] = 0.f;
         va = P.common[2048 + a];
@@ -857,7 +850,7 @@ int wrnn_taco_decode(wrnn_taco_handle *h, const float *enc_seq, int32_t L, int32
     const int owners = disjoint ? G - n_lstm : G;
     P.PP = (L + owners - 1) / owners;
     P.PC = (L + P.PP - 1) / P.PP;
-    const int e_floats = 3 * P.PP * D + 2048 + 2 * ((P.PP + 2 * TC_HALO + 3) & ~3) + TC_FILT * P.PP + 2 * P.PP + 8 * P.PP + 8;
+    const int e_floats = 2 * P.PP * D + 2048 + 2 * ((P.PP + 2 * TC_HALO + 3) & ~3) + TC_FILT * P.PP + 2 * P.PP + 8 * P.PP + 8;
     P.off_E = disjoint ? P.off_F : P.img_floats;
     P.Lp = (L + 3) & ~3;
     P.sm_pf = std::max(P.img_floats, (P.off_E + e_floats + 3) & ~3);
