@@ -171,14 +171,34 @@ __device__ __forceinline__ void stage_cg(float *dst, const float *src, int n, in
 }
 
 
+// The Exp(1) draws a thread will need in `dm_sample_block` (same thread -> (sequence, class) mapping, same Philox call and
+// component, or the injected value): they depend on the step only, so they are formed in a barrier's slack, off the chain.
+__device__ __forceinline__ void dm_draw_noise(float (&q)[4], int C, int N, const float *qsrc, size_t qstride, uint2 key, uint32_t c0,
+                                              uint32_t c1base, uint32_t stream, int tid) {
+    const int warp = tid >> 5, lane = tid & 31;
+    const int WPS = N <= 2 ? 8 : N <= 4 ? 4 : 2, JW = 8 / WPS;
+    const int n = warp / WPS, g = warp - n * WPS;
+#pragma unroll
+    for (int jj = 0; jj < 4; jj++) q[jj] = 1.f;
+    if (n >= N) return;
+    const int call = (g * JW) >> 2;          // the Philox call of categorical_warp that covers this warp's j range
+    uint4 r = make_uint4(0, 0, 0, 0);
+    if (!qsrc) r = philox4x32(make_uint4(c0, c1base + (uint32_t)n, (uint32_t)(call * 32 + lane), stream), key);
+    const uint32_t rr[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+    for (int jj = 0; jj < 4; jj++) {
+        const int j = g * JW + jj, i = lane + 32 * j;
+        if (jj < JW && i < C) q[jj] = qsrc ? qsrc[(size_t)n * qstride + i] : exp1(rr[j & 3]);
+    }
+}
+
 // softmax + Categorical draw of N <= 8 sequences by the whole block, with the bits of `categorical_warp` (loop_common.cuh):
 // that routine gives a lane the classes lane + 32 j and runs three dependent passes of expf over them in ONE warp, ~9.6 k
 // clocks per draw and two draws per step = 45 % of the step (measured, WRNN_DM_PROF).  Here a sequence gets 8 / 4 / 2 warps
 // (1-2 / 3-4 / 5-8 sequences), a warp takes a range of j, expf is evaluated once, and every sum that `categorical_warp`
 // forms sequentially per lane (j ascending from 0.f, then the xor tree) is formed in that same order by the first warp of
 // the sequence from values parked in shared memory, so the picks are identical bit for bit.  C <= 256.
-__device__ __forceinline__ void dm_sample_block(const float *lrow, int C, int N, const float *qsrc, size_t qstride, uint2 key,
-                                                uint32_t c0, uint32_t c1base, uint32_t stream, float *scr, int *res, int tid) {
+__device__ __forceinline__ void dm_sample_block(const float *lrow, int C, int N, const float (&qpre)[4], float *scr, int *res, int tid) {
     const int warp = tid >> 5, lane = tid & 31;
     const int WPS = N <= 2 ? 8 : N <= 4 ? 4 : 2, JW = 8 / WPS;
     const int n = warp / WPS, g = warp - n * WPS;
@@ -244,17 +264,12 @@ __device__ __forceinline__ void dm_sample_block(const float *lrow, int C, int N,
     int bi = 0x7fffffff;
     if (act) {
         const float ps = psval[n];
-        const int call = (g * JW) >> 2;      // the Philox call of categorical_warp that covers this warp's j range
-        uint4 r = make_uint4(0, 0, 0, 0);
-        if (!qsrc) r = philox4x32(make_uint4(c0, c1base + (uint32_t)n, (uint32_t)(call * 32 + lane), stream), key);
-        const uint32_t rr[4] = {r.x, r.y, r.z, r.w};
 #pragma unroll
         for (int jj = 0; jj < 4; jj++) {
             const int j = g * JW + jj, i = lane + 32 * j;
             if (jj < JW && i < C) {
                 const float p = e[jj] / ps;
-                const float q = qsrc ? qsrc[(size_t)n * qstride + i] : exp1(rr[j & 3]);
-                const float v = p / q;
+                const float v = p / qpre[jj];
                 if (v > best) { best = v; bi = i; }    // ascending i per lane: first max kept
             }
         }
@@ -310,6 +325,7 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dm_loop_kernel(const DmParams P
     const int c0 = cta * P.r2, nc = max(0, min(P.r2, Q - c0));
     const uint2 key = make_uint2((uint32_t)P.seed, (uint32_t)(P.seed >> 32));
     unsigned long long gen = 0;
+    float q_coarse[4] = {1.f, 1.f, 1.f, 1.f}, q_fine[4] = {1.f, 1.f, 1.f, 1.f};      // Exp(1) noise of the two draws, formed ahead
     __shared__ long long prof_acc[16];
     long long prof_last = 0;
     const bool prof_on = P.prof != nullptr && tid == 0 && cta == 0;
@@ -330,8 +346,7 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dm_loop_kernel(const DmParams P
             __syncthreads();
             DMARK(0);
             if (fast_draw) {
-                dm_sample_block(lrow, Q, N, P.qf ? P.qf + ((size_t)(t - 1) * P.Ntot + P.n0) * Q : nullptr, (size_t)Q, key, (uint32_t)(t - 1),
-                                (uint32_t)P.n0, 5u, sscr, picks, tid);
+                dm_sample_block(lrow, Q, N, q_fine, sscr, picks, tid);
                 if (tid < N) {
                     prev_f[tid] = picks[tid];
                     prev_c[tid] = cur_c[tid];
@@ -367,7 +382,10 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dm_loop_kernel(const DmParams P
             }
         }
         DMARK(2);
-        grid_barrier(P.gs, gen);
+        dm_arrive(P.gs, gen);                   // in this barrier's slack: the Exp(1) noise of the coarse draw of this step (D)
+        if (fast_draw) dm_draw_noise(q_coarse, Q, N, P.qc ? P.qc + ((size_t)t * P.Ntot + P.n0) * Q : nullptr, (size_t)Q, key, (uint32_t)t,
+                                     (uint32_t)P.n0, 4u, tid);
+        dm_wait(P.gs, gen);
         DMARK(3);
         // ---- B: O1 + ReLU on hidden_coarse
         stage_cg_2d(xbuf, H, hnxt, H, N, S2, tid);        // the coarse half; the fine half stays the previous step's for D
@@ -375,7 +393,10 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dm_loop_kernel(const DmParams P
         rows_split<NS, (NS >= 4 ? 2 : 1)>(O1, S2, S2, xbuf, H, na, N, warp, lane,
                        [&](int j, int n, float v) { P.o1[(size_t)n * S2 + a0 + j] = fmaxf(v + bO1[j], 0.f); });
         DMARK(4);
-        grid_barrier(P.gs, gen);
+        dm_arrive(P.gs, gen);                   // and here the noise of the fine draw, made at the top of the next step
+        if (fast_draw) dm_draw_noise(q_fine, Q, N, P.qf ? P.qf + ((size_t)t * P.Ntot + P.n0) * Q : nullptr, (size_t)Q, key, (uint32_t)t,
+                                     (uint32_t)P.n0, 5u, tid);
+        dm_wait(P.gs, gen);
         DMARK(5);
         // ---- C: O2 -> coarse logits
         stage_cg_2d(xo, S2, P.o1, S2, N, S2, tid);
@@ -388,8 +409,7 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dm_loop_kernel(const DmParams P
         stage_cg(lrow, P.lc, N * Q, tid);
         __syncthreads();
         if (fast_draw) {
-            dm_sample_block(lrow, Q, N, P.qc ? P.qc + ((size_t)t * P.Ntot + P.n0) * Q : nullptr, (size_t)Q, key, (uint32_t)t, (uint32_t)P.n0, 4u,
-                            sscr, picks, tid);
+            dm_sample_block(lrow, Q, N, q_coarse, sscr, picks, tid);
             if (tid < N) {
                 cur_c[tid] = picks[tid];
                 if (cta == 0) P.coarse[(size_t)tid * P.T + t] = picks[tid];
