@@ -132,6 +132,32 @@ __device__ __forceinline__ void unit_rows_split(const float *W, int K, const flo
     }
 }
 
+// One (unit, GS sequences) job of R . hidden over the float4 chunks [c0, c1) of the rows, CONTINUING the per-lane
+// accumulators: lane l takes its chunks l, l + 32, ... in ascending order, so ranges visited in ascending order over
+// several calls give the bits of one pass (`unit_rows_split`).
+template <int GS>
+__device__ __forceinline__ void unit_rows_range(const float *W, int K, const float *X, int ldx, int u, int n0, int c0, int c1, int lane,
+                                                float (&acc)[3][GS]) {
+    const float4 *w4 = reinterpret_cast<const float4 *>(W + (size_t)u * 3 * K);
+    const int k4n = K >> 2;
+    for (int k4 = c0 + ((lane - c0) & 31); k4 < c1; k4 += 32) {
+        float4 w[3];
+#pragma unroll
+        for (int g = 0; g < 3; g++) w[g] = w4[g * k4n + k4];
+#pragma unroll
+        for (int n = 0; n < GS; n++) {
+            const float4 x = reinterpret_cast<const float4 *>(X + (size_t)(n0 + n) * ldx)[k4];
+#pragma unroll
+            for (int g = 0; g < 3; g++) {
+                acc[g][n] = fmaf(w[g].x, x.x, acc[g][n]);
+                acc[g][n] = fmaf(w[g].y, x.y, acc[g][n]);
+                acc[g][n] = fmaf(w[g].z, x.z, acc[g][n]);
+                acc[g][n] = fmaf(w[g].w, x.w, acc[g][n]);
+            }
+        }
+    }
+}
+
 // rows x cols floats, row stride ld (global) / lds (shared), cols % 4 == 0
 __device__ __forceinline__ void stage_cg_2d(float *dst, int lds, const float *src, int ld, int rows, int cols, int tid) {
     const int c4 = cols >> 2, n4 = rows * c4;
@@ -325,6 +351,14 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dm_loop_kernel(const DmParams P
     const int c0 = cta * P.r2, nc = max(0, min(P.r2, Q - c0));
     const uint2 key = make_uint2((uint32_t)P.seed, (uint32_t)(P.seed >> 32));
     unsigned long long gen = 0;
+    // R . hidden of the next step, spread over the slack of four barriers when every (unit, sequence group) job has a warp
+    // of its own: the accumulators then live in registers from C to F (quarter of the columns per barrier)
+    constexpr int GSR = NS >= 4 ? 4 : NS, NGR = NS / GSR;
+    const bool spread = nu * NGR <= DM_WARPS;
+    const int ru = warp / NGR, rn0 = (warp - ru * NGR) * GSR;
+    const bool rjob = spread && warp < nu * NGR && rn0 < N;
+    const int rq = (H >> 2) / 4;        // float4 chunks per quarter of a row
+    float racc[3][GSR];
     float q_coarse[4] = {1.f, 1.f, 1.f, 1.f}, q_fine[4] = {1.f, 1.f, 1.f, 1.f};      // Exp(1) noise of the two draws, formed ahead
     __shared__ long long prof_acc[16];
     long long prof_last = 0;
@@ -403,7 +437,15 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dm_loop_kernel(const DmParams P
         __syncthreads();
         rows_split<NS, (NS >= 4 ? 2 : 1)>(O2, S2, S2, xo, S2, nc, N, warp, lane, [&](int j, int n, float v) { P.lc[(size_t)n * Q + c0 + j] = v + bO2[j]; });
         DMARK(6);
-        grid_barrier(P.gs, gen);
+        dm_arrive(P.gs, gen);
+        if (rjob) {
+#pragma unroll
+            for (int g = 0; g < 3; g++)
+#pragma unroll
+                for (int n = 0; n < GSR; n++) racc[g][n] = 0.f;
+            unit_rows_range<GSR>(R, H, xbuf, H, ru, rn0, 0, rq, lane, racc);                 // coarse columns, first half
+        }
+        dm_wait(P.gs, gen);
         DMARK(7);
         // ---- D: coarse sample (redundant), fine gates
         stage_cg(lrow, P.lc, N * Q, tid);
@@ -440,7 +482,9 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dm_loop_kernel(const DmParams P
             }
         }
         DMARK(8);
-        grid_barrier(P.gs, gen);
+        dm_arrive(P.gs, gen);
+        if (rjob) unit_rows_range<GSR>(R, H, xbuf, H, ru, rn0, rq, 2 * rq, lane, racc);             // coarse columns, second half
+        dm_wait(P.gs, gen);
         DMARK(9);
         // ---- E: O3 + ReLU on hidden_fine
         stage_cg_2d(xbuf + S2, H, hnxt + S2, H, N, S2, tid);     // xbuf = the whole new hidden state from here on
@@ -450,7 +494,11 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dm_loop_kernel(const DmParams P
         DMARK(10);
         // R . hidden for the NEXT step's gates, first half of the jobs, between this barrier's arrive and wait
         dm_arrive(P.gs, gen);
-        unit_rows_split<NS, (NS >= 4 ? 4 : NS)>(R, H, xbuf, H, nu, N, warp, lane, [&](int j, int n, float v) { rsum[j * DM_MAXN + n] = v; }, 0, 2);
+        if (spread) {
+            if (rjob) unit_rows_range<GSR>(R, H, xbuf, H, ru, rn0, 2 * rq, 3 * rq, lane, racc);         // fine columns, first half
+        } else {
+            unit_rows_split<NS, GSR>(R, H, xbuf, H, nu, N, warp, lane, [&](int j, int n, float v) { rsum[j * DM_MAXN + n] = v; }, 0, 2);
+        }
         dm_wait(P.gs, gen);
         DMARK(11);
         // ---- F: O4 -> fine logits
@@ -459,7 +507,21 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dm_loop_kernel(const DmParams P
         rows_split<NS, (NS >= 4 ? 2 : 1)>(O4, S2, S2, xo, S2, nc, N, warp, lane, [&](int j, int n, float v) { P.lf[(size_t)n * Q + c0 + j] = v + bO4[j]; });
         DMARK(12);
         dm_arrive(P.gs, gen);                   // second half (j = u*3 + gate)
-        unit_rows_split<NS, (NS >= 4 ? 4 : NS)>(R, H, xbuf, H, nu, N, warp, lane, [&](int j, int n, float v) { rsum[j * DM_MAXN + n] = v; }, 1, 2);
+        if (spread) {
+            if (rjob) {
+                unit_rows_range<GSR>(R, H, xbuf, H, ru, rn0, 3 * rq, H >> 2, lane, racc);               // fine columns, second half
+#pragma unroll
+                for (int g = 0; g < 3; g++)
+#pragma unroll
+                    for (int n = 0; n < GSR; n++) {
+#pragma unroll
+                        for (int o = 16; o >= 1; o >>= 1) racc[g][n] += __shfl_xor_sync(0xffffffffu, racc[g][n], o);
+                        if (lane == 0 && rn0 + n < N) rsum[(ru * 3 + g) * DM_MAXN + rn0 + n] = racc[g][n];
+                    }
+            }
+        } else {
+            unit_rows_split<NS, GSR>(R, H, xbuf, H, nu, N, warp, lane, [&](int j, int n, float v) { rsum[j * DM_MAXN + n] = v; }, 1, 2);
+        }
         dm_wait(P.gs, gen);
         DMARK(13);
     }
