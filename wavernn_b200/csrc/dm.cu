@@ -424,6 +424,7 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dm_loop_kernel(const DmParams P
         // ---- B: O1 + ReLU on hidden_coarse
         stage_cg_2d(xbuf, H, hnxt, H, N, S2, tid);        // the coarse half; the fine half stays the previous step's for D
         __syncthreads();
+        DMARK(14);
         rows_split<NS, (NS >= 4 ? 2 : 1)>(O1, S2, S2, xbuf, H, na, N, warp, lane,
                        [&](int j, int n, float v) { P.o1[(size_t)n * S2 + a0 + j] = fmaxf(v + bO1[j], 0.f); });
         DMARK(4);
@@ -776,10 +777,11 @@ int wrnn_dm_generate(wrnn_dm_handle *h, int64_t seq_len, int32_t n_seq, const fl
             long long pr[16];
             cudaMemcpy(pr, d_prof, sizeof pr, cudaMemcpyDeviceToHost);
             cudaFree(d_prof);
-            static const char *site[14] = {"stage lf", "sample f", "A gates", "A barrier", "B O1", "B barrier", "C O2", "C barrier",
+            static const char *site[14] = {"stage lf", "sample f", "A gates", "A barrier", "B O1 products", "B barrier", "C O2", "C barrier",
                                            "D stage + sample c + gates", "D barrier", "E O3", "E barrier + R.h 1/2", "F O4", "F barrier + R.h 2/2"};
             fprintf(stderr, "dm prof, %d sequences (clk per step, CTA 0)\n", P.N);
             for (int i = 0; i < 14; i++) fprintf(stderr, "  %-28s %7.0f\n", site[i], (double)pr[i] / (double)seq_len);
+            fprintf(stderr, "  B load of hidden_coarse      %7.0f\n", (double)pr[14] / (double)seq_len);
         }
         if (flag) return dm_fail(h, WRNN_ERR_CUDA, "deepmind loop kernel aborted: grid barrier watchdog fired");
     }
