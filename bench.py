@@ -345,6 +345,26 @@ def run_tacotron(device, cpu_leg, L=150, r=2, frames=1600):
            'e2e': {'frames_per_s': n * r / min(wall), 'ms': 1000 * min(wall), 'h2d_bytes': int(enc.nbytes),
                    'd2h_bytes': int(mel.nbytes + attn.nbytes)},
            'launches': 2 * 4, 'dtype': 'f32'}
+    # what bounds it: seven dependent hand-overs per decoder step (tagged words through L2), each at best one
+    # store propagation + one poll round trip (1 300 clk measured with the 450-clk delayed look) + a one-warp product and
+    # its publish (350 clk); the weights never leave shared memory, so HBM sees the 26 MB image once per launch
+    sm_mhz = 1965.0
+    floor_us = 7 * (1300 + 350) / sm_mhz
+    tr = None
+    for path in sorted(glob.glob(os.path.join(ROOT, 'profiles', '*_traffic.json'))):
+        try:
+            d = json.load(open(path))
+        except Exception:
+            continue
+        if 'taco_loop_kernel' in d:
+            tr = dict(d['taco_loop_kernel'], file=os.path.relpath(path, ROOT))
+    weight_bytes = 20_680_960        # the 5 170 240 fp32 decoder parameters a step touches at r = 2
+    rec['roofline'] = {'bound': 'latency', 'hand_overs_per_step': 7, 'latency_floor_us': floor_us,
+                       'frac_of_floor': floor_us / rec['us_per_step'],
+                       'algorithmic_weight_bytes_per_step': weight_bytes, 'weights': 'resident in shared memory for the whole call',
+                       'shared_memory_weight_rate_GBps': weight_bytes / (rec['us_per_step'] * 1e-6) / 1e9,
+                       'traffic': tr['dram_bytes_captured'] if tr else None,
+                       'traffic_source': (tr['capture'] + ', ' + tr['source'] + ' via ' + tr['file']) if tr else None}
     dec.close()
     if cpu_leg:
         from oracle import tacotron as otc
