@@ -1,6 +1,6 @@
 """Bring-up / measurement of the tensor-core loop kernel (csrc/loop_mma.cu) on a B200, through the public binding.
 
-  python scripts/mma_check.py [parity] [timing]
+  python tests/manual/mma_check.py [parity] [timing]
 
 parity: teacher-forced logits and free-running samples of the forced "tcgen05-bf16x3" kernel against the CPU oracle
         (oracle/fatchord.py) at 2 / 64 / 130 / 640 folds, for several fold-tile widths;
@@ -15,7 +15,7 @@ import time
 import numpy as np
 import torch
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 
 from oracle import fatchord as ofc          # noqa: E402  (checker only)

@@ -1,6 +1,6 @@
 """Bring-up: state of the tensor-core loop kernel after n steps (WRNN_MMA_STEPS=n) against the oracle, per phase.
 
-  WRNN_MMA_STEPS=1 python scripts/mma_debug.py [folds-target]
+  WRNN_MMA_STEPS=1 python tests/manual/mma_debug.py [folds-target]
 """
 import os
 import sys
@@ -9,7 +9,7 @@ import numpy as np
 import torch
 import torch.nn.functional as F
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 
 from oracle import fatchord as ofc          # noqa: E402

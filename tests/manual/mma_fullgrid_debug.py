@@ -5,7 +5,7 @@ import sys
 import numpy as np
 import torch
 
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 from oracle import fatchord as ofc                 # noqa: E402
 from wavernn_b200 import binding, synth            # noqa: E402
 from wavernn_b200.config import VocoderDims         # noqa: E402

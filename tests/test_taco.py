@@ -5,7 +5,7 @@ CPU: the oracle restatement against the fixtures the reference's own `Tacotron.g
 fixtures.  Tolerance: the kernel sums in a different order and folds rnn_input into LSTM 1 and prenet.fc1 into the mel
 projection (compositions formed in double): mel frames (range about +-1.5) are held to 2e-5 absolute and attention
 rows (they sum to 1) to 5e-6 over up to 200 free-running decoder steps (measured on B200: 1.1e-6 and 2.2e-7 on the
-fixtures, 3.4e-6 and 1.3e-6 at worst over 200 random shapes, scripts/taco_stress.py); the step
+fixtures, 3.4e-6 and 1.3e-6 at worst over 200 random shapes, tests/manual/taco_stress.py); the step
 count of the stop rule is exact.
 """
 import glob
