@@ -46,24 +46,55 @@ __device__ __forceinline__ void warp_rows(const float *W, int ld, int K, const f
 #pragma unroll
     for (int n = 0; n < NMAX; n++) acc[n] = 0.f;
     const float4 *w4 = reinterpret_cast<const float4 *>(W);
-    for (int k4 = lane; k4 < (K >> 2); k4 += 32) {
-        const float4 w = w4[k4];
+    const int k4n = K >> 2;
+    if (NMAX <= 2) {
+        // four chunks per pass, their loads issued before the first FMA (a lane still adds its chunks lane, lane + 32, ...
+        // in ascending order: the bits of the simple loop below)
+        const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int k0 = lane; k0 < k4n; k0 += 128) {
+            float4 w[4], x[NMAX][4];
 #pragma unroll
-        for (int n = 0; n < NMAX; n++) {        // all NMAX sets, absent sequences included (their rows of X are shared memory
-            const float4 x = reinterpret_cast<const float4 *>(X + (size_t)n * ldx)[k4];      // nobody reads the result of)
-            acc[n] = fmaf(w.x, x.x, acc[n]);
-            acc[n] = fmaf(w.y, x.y, acc[n]);
-            acc[n] = fmaf(w.z, x.z, acc[n]);
-            acc[n] = fmaf(w.w, x.w, acc[n]);
+            for (int c = 0; c < 4; c++) {
+                const int k4 = k0 + 32 * c;
+                w[c] = k4 < k4n ? w4[k4] : z;
+#pragma unroll
+                for (int n = 0; n < NMAX; n++) x[n][c] = k4 < k4n ? reinterpret_cast<const float4 *>(X + (size_t)n * ldx)[k4] : z;
+            }
+#pragma unroll
+            for (int c = 0; c < 4; c++)
+                if (k0 + 32 * c < k4n) {
+#pragma unroll
+                    for (int n = 0; n < NMAX; n++) {
+                        acc[n] = fmaf(w[c].x, x[n][c].x, acc[n]);
+                        acc[n] = fmaf(w[c].y, x[n][c].y, acc[n]);
+                        acc[n] = fmaf(w[c].z, x[n][c].z, acc[n]);
+                        acc[n] = fmaf(w[c].w, x[n][c].w, acc[n]);
+                    }
+                }
+        }
+    } else {
+        for (int k4 = lane; k4 < k4n; k4 += 32) {
+            const float4 w = w4[k4];
+#pragma unroll
+            for (int n = 0; n < NMAX; n++) {        // all NMAX sets, absent sequences included (their rows of X are shared memory
+                const float4 x = reinterpret_cast<const float4 *>(X + (size_t)n * ldx)[k4];      // nobody reads the result of)
+                acc[n] = fmaf(w.x, x.x, acc[n]);
+                acc[n] = fmaf(w.y, x.y, acc[n]);
+                acc[n] = fmaf(w.z, x.z, acc[n]);
+                acc[n] = fmaf(w.w, x.w, acc[n]);
+            }
         }
     }
+    // the NMAX xor trees level by level, so that their shuffles overlap (each tree's own order is unchanged)
 #pragma unroll
-    for (int n = 0; n < NMAX; n++) {
+    for (int o = 16; o >= 1; o >>= 1) {
 #pragma unroll
-        for (int o = 16; o >= 1; o >>= 1) acc[n] += __shfl_xor_sync(0xffffffffu, acc[n], o);
-        out[n] = acc[n];
+        for (int n = 0; n < NMAX; n++) acc[n] += __shfl_xor_sync(0xffffffffu, acc[n], o);
     }
+#pragma unroll
+    for (int n = 0; n < NMAX; n++) out[n] = acc[n];
     (void)ld;
+    (void)N;
 }
 
 // `nrows` rows x NS sequences as jobs of (one row, GS consecutive sequences) spread over all warps: with 4 rows and 8
