@@ -8,8 +8,8 @@ B="python bench.py --steps 2 --warmup 3 --no-cpu"
 $B > $O/ncu_bench_plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/launches.csv $B > $O/ncu_bench.log 2>&1
 echo "launch list rc=$?"
-for k in mma res taco; do
-  pat=mma_loop; [ $k = res ] && pat=res_loop; [ $k = taco ] && pat=taco_loop
+for k in mma res taco dm; do
+  pat=mma_loop; [ $k = res ] && pat=res_loop; [ $k = taco ] && pat=taco_loop; [ $k = dm ] && pat=dm_loop
   python scripts/prof_target.py $k > $O/ncu_${k}_plain.log 2>&1 &&
   ncu --set full --clock-control none --import-source on -k regex:$pat -c 1 -f -o $O/prof_$k python scripts/prof_target.py $k > $O/ncu_$k.log 2>&1
   echo "$k capture rc=$?"

@@ -3,6 +3,7 @@
   python scripts/prof_target.py mma     640 folds x 300 steps on the tensor-core kernel
   python scripts/prof_target.py res     one utterance, 20 folds x 2 200 steps on the register-resident kernel
   python scripts/prof_target.py taco    Tacotron decoder loop, 150 characters, 200 decoder steps
+  python scripts/prof_target.py dm      deepmind kernel, 8 sequences x 2 000 samples
 `mma`: 640 folds x 300 steps on the tensor-core kernel (T=582, target 200, overlap 50: the shape tests/test_mma_gpu.py checks).
 """
 import os
@@ -15,6 +16,12 @@ from wavernn_b200 import binding, synth      # noqa: E402
 from wavernn_b200.config import VocoderDims  # noqa: E402
 
 what = sys.argv[1] if len(sys.argv) > 1 else 'mma'
+if what == 'dm':        # deepmind coarse/fine kernel: 8 sequences x 2 000 samples
+    v = binding.DeepmindVocoder(896, 256, device=0)
+    v.load_weights(synth.synth_dm_state_dict(896, 256, seed=0))
+    out, c, f = v.generate(2000, 8, seed=3)
+    print(what, out.shape, v.last_timing())
+    sys.exit(0)
 if what == 'taco':      # the Tacotron decoder loop: 150 characters, r = 2, 200 decoder steps
     dec = binding.TacotronDecoder(device=0)
     dec.load_weights(synth.synth_taco_state_dict(seed=0))
