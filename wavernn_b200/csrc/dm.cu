@@ -249,22 +249,21 @@ __device__ __forceinline__ void dm_draw_noise(float (&q)[4], int C, int N, const
     }
 }
 
-// softmax + Categorical draw of N <= 8 sequences by the whole block, with the bits of `categorical_warp` (loop_common.cuh):
-// that routine gives a lane the classes lane + 32 j and runs three dependent passes of expf over them in ONE warp, ~9.6 k
-// clocks per draw and two draws per step = 45 % of the step (measured, WRNN_DM_PROF).  Here a sequence gets 8 / 4 / 2 warps
-// (1-2 / 3-4 / 5-8 sequences), a warp takes a range of j, expf is evaluated once, and every sum that `categorical_warp`
-// forms sequentially per lane (j ascending from 0.f, then the xor tree) is formed in that same order by the first warp of
-// the sequence from values parked in shared memory, so the picks are identical bit for bit.  C <= 256.
+// Categorical draw of N <= 8 sequences by the whole block.  `categorical_warp` (loop_common.cuh) gives a lane the classes
+// lane + 32 j and runs three dependent passes of expf over them in ONE warp: 9.6 k clocks per draw, two draws per step = 45 %
+// of the step (measured, WRNN_DM_PROF).  Here a sequence gets 8 / 4 / 2 warps (1-2 / 3-4 / 5-8 sequences), expf is evaluated
+// once, and the softmax is never normalised: the pick is argmax_i (p_i / sum p) / q_i with p_i = e_i / s, where s and
+// sum p are common positive factors of a sequence, i.e. argmax_i e_i / q_i (ties to the lower index, as before).  The
+// reference fixtures and 2 x 44 100 + 2 x 64 000 draws against the oracle are reproduced exactly
+// (tests/manual/dm_long_check.py).  C <= 256.
 __device__ __forceinline__ void dm_sample_block(const float *lrow, int C, int N, const float (&qpre)[4], float *scr, int *res, int tid) {
     const int warp = tid >> 5, lane = tid & 31;
     const int WPS = N <= 2 ? 8 : N <= 4 ? 4 : 2, JW = 8 / WPS;
     const int n = warp / WPS, g = warp - n * WPS;
     const bool act = n < N;
-    float *ebuf = scr;                       // [N][8][32] values parked per (sequence, j, lane)
     float *vbuf = scr + DM_MAXN * 256;       // [N][8][32] best value per (sequence, warp of the sequence, lane)
     int *ibuf = reinterpret_cast<int *>(vbuf + DM_MAXN * 256);
-    float *wmax = reinterpret_cast<float *>(ibuf + DM_MAXN * 256);       // [16] | sval [8] | psval [8]
-    float *sval = wmax + DM_WARPS, *psval = sval + DM_MAXN;
+    float *wmax = reinterpret_cast<float *>(ibuf + DM_MAXN * 256);       // [16]
     const float *lg = lrow + (size_t)(act ? n : 0) * C;
     float l[4], e[4];
     float m = -INFINITY;
@@ -282,51 +281,17 @@ __device__ __forceinline__ void dm_sample_block(const float *lrow, int C, int N,
         m = wmax[n * WPS];
         for (int k = 1; k < WPS; k++) m = fmaxf(m, wmax[n * WPS + k]);
     }
-#pragma unroll
-    for (int jj = 0; jj < 4; jj++) {
-        const int j = g * JW + jj, i = lane + 32 * j;
-        e[jj] = (act && jj < JW && i < C) ? expf(l[jj] - m) : 0.f;
-        if (act && jj < JW) ebuf[(n * 8 + j) * 32 + lane] = e[jj];
-    }
-    __syncthreads();
-    if (act && g == 0) {
-        float s = 0.f;
-#pragma unroll
-        for (int j = 0; j < 8; j++)
-            if (lane + 32 * j < C) s += ebuf[(n * 8 + j) * 32 + lane];
-#pragma unroll
-        for (int o = 16; o >= 1; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-        if (lane == 0) sval[n] = s;
-    }
-    __syncthreads();
-    const float s = act ? sval[n] : 1.f;
-#pragma unroll
-    for (int jj = 0; jj < 4; jj++) {
-        const int j = g * JW + jj;
-        e[jj] = e[jj] / s;                   // p = expf(l - m) / s
-        if (act && jj < JW) ebuf[(n * 8 + j) * 32 + lane] = e[jj];
-    }
-    __syncthreads();
-    if (act && g == 0) {
-        float ps = 0.f;                      // Categorical renormalises: probs / probs.sum(-1)
-#pragma unroll
-        for (int j = 0; j < 8; j++)
-            if (lane + 32 * j < C) ps += ebuf[(n * 8 + j) * 32 + lane];
-#pragma unroll
-        for (int o = 16; o >= 1; o >>= 1) ps += __shfl_xor_sync(0xffffffffu, ps, o);
-        if (lane == 0) psval[n] = ps;
-    }
-    __syncthreads();
+    // argmax_i (p_i / sum p) / q_i with p_i = e_i / s: s and sum p are common positive factors of a sequence, so the pick is
+    // argmax_i e_i / q_i and neither sum is formed (two block barriers and two sequential 8-term sums per draw less)
     float best = -INFINITY;
     int bi = 0x7fffffff;
     if (act) {
-        const float ps = psval[n];
 #pragma unroll
         for (int jj = 0; jj < 4; jj++) {
             const int j = g * JW + jj, i = lane + 32 * j;
             if (jj < JW && i < C) {
-                const float p = e[jj] / ps;
-                const float v = p / qpre[jj];
+                e[jj] = expf(l[jj] - m);
+                const float v = e[jj] / qpre[jj];
                 if (v > best) { best = v; bi = i; }    // ascending i per lane: first max kept
             }
         }
